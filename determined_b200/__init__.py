@@ -1,0 +1,59 @@
+"""determined_b200 — a B200-native training harness with Determined's capabilities.
+
+Public names mirror reference ``harness/determined/__init__.py:1-30``.  ``import determined_b200
+as det`` is the drop-in for ``import determined as det``; :func:`install_alias` additionally
+registers the package under the name ``determined`` for unmodified user code.
+"""
+from determined_b200.__version__ import __version__
+from determined_b200._info import (
+    ClusterInfo, RendezvousInfo, ResourcesInfo, TrialInfo, get_cluster_info,
+)
+from determined_b200.errors import InvalidHP
+from determined_b200._experiment_config import ExperimentConfig
+from determined_b200._import import import_from_path
+from determined_b200 import constants, errors, util, gpu, core
+
+LOG_FORMAT = "%(levelname)s: [%(process)s] %(name)s: %(message)s"
+
+
+def install_alias(name: str = "determined") -> None:
+    """Make ``import determined`` (and submodules) resolve to this package."""
+    import importlib
+    import sys
+
+    class _AliasFinder:
+        def find_spec(self, fullname, path=None, target=None):  # type: ignore
+            if fullname != name and not fullname.startswith(name + "."):
+                return None
+            real = "determined_b200" + fullname[len(name):]
+            try:
+                mod = importlib.import_module(real)
+            except ImportError:
+                return None
+            sys.modules[fullname] = mod
+            return importlib.util.spec_from_loader(fullname, loader=_Loader(mod))
+
+    class _Loader:
+        def __init__(self, mod):  # type: ignore
+            self.mod = mod
+
+        def create_module(self, spec):  # type: ignore
+            return self.mod
+
+        def exec_module(self, module):  # type: ignore
+            pass
+
+    import importlib.util
+
+    if not any(type(f).__name__ == "_AliasFinder" for f in sys.meta_path):
+        sys.meta_path.insert(0, _AliasFinder())
+    sys.modules.setdefault(name, sys.modules[__name__])
+
+
+def __getattr__(attr: str):  # lazy heavy submodules (torch import) – keeps `import determined_b200` light
+    if attr in ("pytorch", "launch", "exec", "searcher", "tensorboard", "experimental", "transformers", "cli",
+                "master", "models", "ops", "parallel", "utils", "ipc", "keras", "lightning", "layers", "common"):
+        import importlib
+
+        return importlib.import_module(f"determined_b200.{attr}")
+    raise AttributeError(attr)

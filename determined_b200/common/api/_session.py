@@ -1,0 +1,130 @@
+"""HTTP session to the master with bearer-token auth and bounded retries.
+
+Parity: reference ``harness/determined/common/api/_session.py:90-284`` (``Session`` with
+``get/post/put/patch/delete``, retry policy on connection errors and 502/503/504).
+"""
+import json as _json
+import logging
+import time
+from typing import Any, Dict, Optional, Tuple, Union
+
+from determined_b200.common.api import errors
+
+logger = logging.getLogger("determined.api")
+
+RETRY_STATUSES = (502, 503, 504)
+DEFAULT_MAX_RETRIES = 5
+
+
+def canonicalize_master_url(url: str) -> str:
+    if "://" not in url:
+        url = "http://" + url
+    scheme, rest = url.split("://", 1)
+    host = rest.rstrip("/")
+    if ":" not in host.split("/")[0]:
+        host = host + (":443" if scheme == "https" else ":8080")
+    return f"{scheme}://{host}"
+
+
+class BaseSession:
+    def __init__(self, master: str, token: Optional[str] = None, cert: Any = None,
+                 max_retries: int = DEFAULT_MAX_RETRIES, timeout: Optional[float] = None) -> None:
+        self.master = canonicalize_master_url(master)
+        self.token = token
+        self.cert = cert
+        self._max_retries = max_retries
+        self._timeout = timeout
+        self._http = None
+
+    def _client(self) -> Any:
+        if self._http is None:
+            import requests
+
+            self._http = requests.Session()
+        return self._http
+
+    def _headers(self, extra: Optional[Dict[str, str]]) -> Dict[str, str]:
+        h = {"Content-Type": "application/json"}
+        if self.token:
+            h["Authorization"] = f"Bearer {self.token}"
+        if extra:
+            h.update(extra)
+        return h
+
+    def _do_request(self, method: str, path: str, params: Optional[Dict[str, Any]] = None,
+                    json: Any = None, data: Any = None, headers: Optional[Dict[str, str]] = None,
+                    timeout: Optional[Union[Tuple, float]] = None, stream: bool = False) -> Any:
+        import requests
+
+        url = self.master + (path if path.startswith("/") else "/" + path)
+        if json is not None and data is None:
+            from determined_b200 import util
+
+            data = util.json_encode(json)
+        attempt, delay = 0, 0.2
+        while True:
+            try:
+                r = self._client().request(method, url, params=params, data=data, headers=self._headers(headers),
+                                           timeout=timeout or self._timeout, stream=stream)
+            except (requests.ConnectionError, requests.Timeout) as e:
+                if attempt >= self._max_retries:
+                    raise errors.MasterNotFoundException(f"cannot reach master at {self.master}: {e}") from e
+                attempt += 1
+                time.sleep(delay)
+                delay = min(delay * 2, 5.0)
+                continue
+            if r.status_code in RETRY_STATUSES and attempt < self._max_retries:
+                attempt += 1
+                time.sleep(delay)
+                delay = min(delay * 2, 5.0)
+                continue
+            break
+        if r.status_code >= 400:
+            try:
+                body = r.json()
+                msg = body.get("message") or body.get("error", {}).get("message") or r.text
+            except Exception:
+                body, msg = None, r.text
+            if r.status_code == 404:
+                raise errors.NotFoundException(msg, body)
+            if r.status_code == 401:
+                raise errors.UnauthenticatedException(msg, body)
+            if r.status_code == 403:
+                raise errors.ForbiddenException(msg, body)
+            raise errors.APIException(r.status_code, msg, body)
+        return r
+
+    def get(self, path: str, **kw: Any) -> Any:
+        return self._do_request("GET", path, **kw)
+
+    def delete(self, path: str, **kw: Any) -> Any:
+        return self._do_request("DELETE", path, **kw)
+
+    def post(self, path: str, **kw: Any) -> Any:
+        return self._do_request("POST", path, **kw)
+
+    def patch(self, path: str, **kw: Any) -> Any:
+        return self._do_request("PATCH", path, **kw)
+
+    def put(self, path: str, **kw: Any) -> Any:
+        return self._do_request("PUT", path, **kw)
+
+    def close(self) -> None:
+        if self._http is not None:
+            self._http.close()
+            self._http = None
+
+
+class UnauthSession(BaseSession):
+    def __init__(self, master: str, cert: Any = None, max_retries: int = DEFAULT_MAX_RETRIES) -> None:
+        super().__init__(master, None, cert, max_retries)
+
+
+class Session(BaseSession):
+    def __init__(self, master: str, username: Optional[str] = None, token: Optional[str] = None,
+                 cert: Any = None, max_retries: int = DEFAULT_MAX_RETRIES) -> None:
+        super().__init__(master, token, cert, max_retries)
+        self.username = username
+
+    def with_retry(self, max_retries: int) -> "Session":
+        return Session(self.master, self.username, self.token, self.cert, max_retries)

@@ -1,0 +1,141 @@
+"""Login + on-disk token cache.
+
+Parity: reference ``harness/determined/common/api/authentication.py`` (``login``,
+``TokenStore`` at ``~/.config/determined/auth.json`` keyed by master URL, ``salt_and_hash``,
+``DET_USER``/``DET_PASS``/``DET_USER_TOKEN`` env overrides, session-token fast path inside tasks).
+"""
+import contextlib
+import getpass
+import hashlib
+import json
+import os
+import pathlib
+from typing import Any, Dict, Optional
+
+from determined_b200.common.api import _session, errors
+
+PASSWORD_SALT = "GubPEmmotfiK9TMD6Zdw"
+DEFAULT_USER = "determined"
+
+
+def salt_and_hash(password: str) -> str:
+    if not password:
+        return password
+    return hashlib.sha512((PASSWORD_SALT + password).encode()).hexdigest()
+
+
+def _config_dir() -> pathlib.Path:
+    base = os.environ.get("DET_CONFIG_DIR") or os.path.join(
+        os.environ.get("XDG_CONFIG_HOME", os.path.expanduser("~/.config")), "determined_b200")
+    return pathlib.Path(base)
+
+
+class TokenStore:
+    """``{"version":2, "masters": {url: {"active_user": u, "tokens": {u: token}}}}``"""
+
+    def __init__(self, master_url: str, path: Optional[pathlib.Path] = None) -> None:
+        self.master_url = _session.canonicalize_master_url(master_url)
+        self.path = path or (_config_dir() / "auth.json")
+        self._d = self._load()
+
+    def _load(self) -> Dict[str, Any]:
+        try:
+            d = json.loads(self.path.read_text())
+            if not isinstance(d, dict) or "masters" not in d:
+                raise errors.CorruptTokenCacheException()
+            return d
+        except FileNotFoundError:
+            return {"version": 2, "masters": {}}
+        except json.JSONDecodeError:
+            raise errors.CorruptTokenCacheException()
+
+    def _save(self) -> None:
+        self.path.parent.mkdir(parents=True, exist_ok=True)
+        tmp = self.path.with_suffix(".tmp")
+        tmp.write_text(json.dumps(self._d, indent=1))
+        os.chmod(tmp, 0o600)
+        os.replace(tmp, self.path)
+
+    def _m(self) -> Dict[str, Any]:
+        return self._d["masters"].setdefault(self.master_url, {"tokens": {}})
+
+    def get_active_user(self) -> Optional[str]:
+        return self._m().get("active_user")
+
+    def get_token(self, user: str) -> Optional[str]:
+        return self._m()["tokens"].get(user)
+
+    def set_token(self, user: str, token: str) -> None:
+        self._m()["tokens"][user] = token
+        self._save()
+
+    def set_active(self, user: str) -> None:
+        self._m()["active_user"] = user
+        self._save()
+
+    def drop_user(self, user: str) -> None:
+        self._m()["tokens"].pop(user, None)
+        if self._m().get("active_user") == user:
+            self._m().pop("active_user")
+        self._save()
+
+    def clear_active(self) -> None:
+        self._m().pop("active_user", None)
+        self._save()
+
+
+def login(master: str, username: str, password: str, cert: Any = None) -> _session.Session:
+    s = _session.UnauthSession(master, cert)
+    r = s.post("/api/v1/auth/login", json={"username": username, "password": salt_and_hash(password),
+                                            "isHashed": True})
+    token = r.json()["token"]
+    return _session.Session(master, username, token, cert)
+
+
+def _token_valid(master: str, token: str) -> bool:
+    try:
+        _session.Session(master, None, token, None, max_retries=1).get("/api/v1/me")
+        return True
+    except (errors.UnauthenticatedException, errors.ForbiddenException):
+        return False
+
+
+def login_with_cache(master: str, requested_user: Optional[str] = None, password: Optional[str] = None,
+                     cert: Any = None) -> _session.Session:
+    """Order: task session token (``DET_SESSION_TOKEN``) → ``DET_USER_TOKEN`` → cached token →
+    ``DET_USER``/``DET_PASS`` → default user with blank password → interactive prompt."""
+    env = os.environ
+    if env.get("DET_SESSION_TOKEN") and env.get("DET_MASTER") and requested_user is None:
+        return _session.Session(master, env.get("DET_USER", DEFAULT_USER), env["DET_SESSION_TOKEN"], cert)
+    if env.get("DET_USER_TOKEN") and requested_user is None:
+        return _session.Session(master, env.get("DET_USER", DEFAULT_USER), env["DET_USER_TOKEN"], cert)
+    store = None
+    with contextlib.suppress(errors.CorruptTokenCacheException, OSError):
+        store = TokenStore(master)
+    user = requested_user or env.get("DET_USER") or (store.get_active_user() if store else None) or DEFAULT_USER
+    if store is not None and password is None:
+        tok = store.get_token(user)
+        if tok and _token_valid(master, tok):
+            return _session.Session(master, user, tok, cert)
+    if password is None:
+        password = env.get("DET_PASS")
+    if password is None and user == DEFAULT_USER:
+        password = ""
+    if password is None:
+        password = getpass.getpass(f"Password for user '{user}': ")
+    sess = login(master, user, password, cert)
+    if store is not None:
+        with contextlib.suppress(OSError):
+            store.set_token(user, sess.token or "")
+            store.set_active(user)
+    return sess
+
+
+def logout(master: str, user: Optional[str] = None, cert: Any = None) -> None:
+    store = TokenStore(master)
+    user = user or store.get_active_user() or DEFAULT_USER
+    tok = store.get_token(user)
+    if tok:
+        with contextlib.suppress(errors.APIException, errors.MasterNotFoundException):
+            _session.Session(master, user, tok, cert, max_retries=0).post("/api/v1/auth/logout")
+    store.drop_user(user)

@@ -1,0 +1,135 @@
+"""Shared-filesystem storage: checkpoints are plain directories ``<base>/<uuid>/``.
+
+Parity: reference ``harness/determined/common/storage/shared.py:27-278``.  "Direct access": the
+trial writes straight into the final directory, so there is no upload step — this is what makes
+the ASHA save/restore path (BASELINE config #5) cheap on a single box.
+"""
+import contextlib
+import glob as globlib
+import logging
+import os
+import pathlib
+import shutil
+from typing import Any, Dict, Iterator, List, Optional, Union
+
+from determined_b200 import util
+from determined_b200.common.storage import base
+
+logger = logging.getLogger("determined.storage")
+
+
+def copytree(src: str, dst: str, selector: Optional[base.Selector] = None,
+             paths: Optional[base.Paths] = None) -> None:
+    """Selector/paths-aware recursive copy.  ``paths`` contains relative names (dirs end in ``/``);
+    a selected directory is created even if none of its children are selected."""
+    src = os.fspath(src)
+    os.makedirs(dst, exist_ok=True)
+    for cur, dirs, files in os.walk(src):
+        rel_cur = os.path.relpath(cur, src)
+        rel_cur = "" if rel_cur == "." else rel_cur + "/"
+        keep_dirs = []
+        for d in dirs:
+            rel = rel_cur + d + "/"
+            if paths is not None and rel not in paths:
+                # still descend if any selected path lives below
+                if not any(p.startswith(rel) for p in paths):
+                    continue
+            if selector is not None and not selector(rel):
+                continue
+            keep_dirs.append(d)
+            os.makedirs(os.path.join(dst, rel), exist_ok=True)
+        dirs[:] = keep_dirs
+        for f in files:
+            rel = rel_cur + f
+            if paths is not None and rel not in paths:
+                continue
+            if selector is not None and not selector(rel):
+                continue
+            s, t = os.path.join(cur, f), os.path.join(dst, rel)
+            os.makedirs(os.path.dirname(t), exist_ok=True)
+            if os.path.islink(s):
+                if os.path.lexists(t):
+                    os.unlink(t)
+                os.symlink(os.readlink(s), t)
+            else:
+                shutil.copy2(s, t)
+
+
+def full_storage_path(host_path: str, storage_path: Optional[str] = None,
+                      container_path: Optional[str] = None) -> str:
+    if not os.path.isabs(host_path):
+        raise ValueError("`host_path` must be an absolute path.")
+    root = host_path if container_path is None else container_path
+    if storage_path is None:
+        return root
+    ab = os.path.normpath(os.path.join(host_path, storage_path))
+    if not (ab == host_path or ab.startswith(host_path.rstrip("/") + "/")):
+        raise ValueError("storage path must be a subdirectory of host path.")
+    return os.path.join(root, os.path.relpath(ab, host_path))
+
+
+class SharedFSStorageManager(base.StorageManager):
+    @classmethod
+    def from_config(cls, config: Dict[str, Any], container_path: Optional[str]) -> "SharedFSStorageManager":
+        allowed = {"host_path", "storage_path", "container_path", "propagation"}
+        extra = set(config) - allowed
+        if extra:
+            raise TypeError(f"unexpected shared_fs keys: {sorted(extra)}")
+        # Single box, no containers: the host path *is* the path we see.
+        return cls(full_storage_path(config["host_path"], config.get("storage_path"), None))
+
+    def post_store_path(self, src: Union[str, os.PathLike], dst: str) -> None:
+        # direct access: nothing to do.
+        return None
+
+    def store_path_is_direct_access(self) -> bool:
+        return True
+
+    @contextlib.contextmanager
+    def restore_path(self, src: str, selector: Optional[base.Selector] = None) -> Iterator[pathlib.Path]:
+        # Zero-copy: hand out the real directory.  (selector is irrelevant: nothing is copied.)
+        d = os.path.join(self._base_path, src)
+        if not os.path.isdir(d):
+            raise FileNotFoundError(f"checkpoint directory not found: {d}")
+        yield pathlib.Path(d)
+
+    def delete(self, tgt: str, globs: List[str]) -> Dict[str, int]:
+        d = os.path.join(self._base_path, tgt)
+        if not os.path.exists(d):
+            logger.info("storage directory does not exist: %s", d)
+            return {}
+        if not os.path.isdir(d):
+            raise NotADirectoryError(d)
+        if "**/*" in globs:
+            util.rmtree_nfs_safe(d)
+            return {}
+        files, dirs = [], []
+        for g in globs:
+            for p in globlib.glob(os.path.join(globlib.escape(d), g), recursive=True):
+                if os.path.commonpath([d, os.path.normpath(p)]) != d:
+                    logger.warning("refusing to delete path outside checkpoint dir: %s", p)
+                    continue
+                (files if (os.path.isfile(p) or os.path.islink(p)) else dirs).append(p)
+        for p in files:
+            with contextlib.suppress(FileNotFoundError):
+                os.remove(p)
+        for p in dirs:
+            if os.path.isdir(p):
+                util.rmtree_nfs_safe(p)
+        left = base.list_directory(d)
+        if not left:
+            util.rmtree_nfs_safe(d)
+        return left
+
+    def upload(self, src: Union[str, os.PathLike], dst: str, paths: Optional[base.Paths] = None) -> None:
+        src = os.fspath(src)
+        target = os.path.join(self._base_path, dst)
+        if os.path.realpath(src) == os.path.realpath(target):
+            return
+        copytree(src, target, paths=paths)
+
+    def download(self, src: str, dst: Union[str, os.PathLike], selector: Optional[base.Selector] = None) -> None:
+        source = os.path.join(self._base_path, src)
+        if not os.path.isdir(source):
+            raise FileNotFoundError(f"checkpoint directory not found: {source}")
+        copytree(source, os.fspath(dst), selector=selector)

@@ -1,0 +1,117 @@
+"""ctypes binding of ``libdetb200.so`` (C ABI declared in ``include/detb200.h``).
+
+The library is built in-tree by :mod:`determined_b200._native.build`.  If CUDA is available and
+the library is missing we fail loudly — a silent PyTorch fallback on a GPU box would hide that the
+native path is not the one running.
+"""
+import ctypes
+import os
+import pathlib
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int64, c_void_p
+from typing import Any, Optional
+
+_HERE = pathlib.Path(__file__).resolve().parent
+LIB_PATH = _HERE.parent / "_native" / "libdetb200.so"
+_lib: Optional[ctypes.CDLL] = None
+
+ABI_VERSION = 1
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def available() -> bool:
+    return LIB_PATH.exists()
+
+
+def _sig(lib: ctypes.CDLL, name: str, restype: Any, argtypes: Any) -> None:
+    fn = getattr(lib, name, None)
+    if fn is None:
+        return
+    fn.restype = restype
+    fn.argtypes = argtypes
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        if os.environ.get("DETB200_AUTOBUILD", "1") == "1":
+            from determined_b200._native import build as nb
+
+            nb.build()
+        if not LIB_PATH.exists():
+            raise NativeError(f"{LIB_PATH} is missing: run `python -m determined_b200._native.build`")
+    lib = ctypes.CDLL(str(LIB_PATH), mode=ctypes.RTLD_GLOBAL)
+    lib.detb200_last_error.restype = c_char_p
+    lib.detb200_abi_version.restype = c_int
+    if lib.detb200_abi_version() != ABI_VERSION:
+        raise NativeError("libdetb200.so ABI mismatch; rebuild")
+    p, i, i64, f, d = c_void_p, c_int, c_int64, c_float, c_double
+    _sig(lib, "detb200_optim_tick", i, [p, p, p])
+    _sig(lib, "detb200_adam_flat", i, [p, p, p, p, p, i64, p, p, p, p, f, f, f, f, i, f, i, i, p])
+    _sig(lib, "detb200_sgd_flat", i, [p, p, p, i64, p, p, p, p, f, f, f, i, f, i, i, p])
+    _sig(lib, "detb200_adadelta_flat", i, [p, p, p, p, i64, p, p, p, f, f, f, f, i, i, p])
+    _sig(lib, "detb200_sumsq_scratch_bytes", i64, [])
+    _sig(lib, "detb200_sumsq", i, [p, i64, p, p, p, i, p])
+    _sig(lib, "detb200_clip_coef", i, [p, i, f, f, p, p, p])
+    _sig(lib, "detb200_scale_flat", i, [p, i64, p, f, p])
+    _sig(lib, "detb200_ctrl_bytes", i64, [])
+    _sig(lib, "detb200_ipc_handle_bytes", i, [])
+    _sig(lib, "detb200_symm_alloc", i, [POINTER(c_void_p), i64])
+    _sig(lib, "detb200_symm_free", i, [p])
+    _sig(lib, "detb200_ipc_export", i, [p, p])
+    _sig(lib, "detb200_ipc_open", i, [p, POINTER(c_void_p)])
+    _sig(lib, "detb200_ipc_close", i, [p])
+    _sig(lib, "detb200_enable_peer_access", i, [i])
+    _sig(lib, "detb200_comm_stats_ptr", p, [p])
+    _sig(lib, "detb200_comm_read_stats", i, [p, i, POINTER(c_float), p])
+    _sig(lib, "detb200_allreduce_fused", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, i64, i64, f, p, p, i, i, d, p])
+    _sig(lib, "detb200_rs_adam_ag", i, [POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), i, i, i, i64, i64,
+                                        p, p, p, p, f, p, p, p, p, f, f, f, f, i, i, i, d, p])
+    _sig(lib, "detb200_broadcast", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, i, i64, i64, i, d, p])
+    _sig(lib, "detb200_norm_fwd", i, [p, p, p, p, p, p, i64, i, f, i, i, p])
+    _sig(lib, "detb200_norm_bwd_workspace_elems", i64, [i64, i, i])
+    _sig(lib, "detb200_norm_bwd", i, [p, p, p, p, p, p, p, p, p, i64, i, i, i, p])
+    _sig(lib, "detb200_xent_fwd", i, [p, p, p, p, i64, i, i64, i, p])
+    _sig(lib, "detb200_xent_bwd", i, [p, p, p, p, p, i64, i, i64, i, p])
+    # tcgen05 GEMM family (csrc/gemm_sm100.cu)
+    _sig(lib, "detb200_gemm_bf16", i, [p, p, p, p, i, i, i, i, i, p])
+    _sig(lib, "detb200_ag_gemm_bf16", i, [p, POINTER(c_void_p), p, p, i, i, i, i, i, i, p])
+    _sig(lib, "detb200_gemm_workspace_bytes", i64, [])
+    # attention (csrc/attention.cu)
+    _sig(lib, "detb200_attn_fwd", i, [p, p, p, p, p, i, i, i, i, f, i, p])
+    _sig(lib, "detb200_attn_bwd", i, [p, p, p, p, p, p, p, p, p, p, i, i, i, i, f, i, p])
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        lib = load()
+        msg = lib.detb200_last_error()
+        raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg.decode() if msg else ''}")
+
+
+def ptr(t: Any) -> Optional[int]:
+    """Device pointer of a tensor (None → NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr(stream: Any = None) -> int:
+    import torch
+
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def dtype_code(dt: Any) -> int:
+    import torch
+
+    if dt == torch.float32:
+        return 0
+    if dt == torch.bfloat16:
+        return 1
+    raise NativeError(f"unsupported dtype {dt} (float32 and bfloat16 only)")

@@ -1,0 +1,170 @@
+"""TensorBoard event-file syncing (reference ``harness/determined/tensorboard/*``).
+
+``TensorboardManager.sync()`` ships new/modified files under the local ``base_path`` to
+``<storage>/<cluster_id>/tensorboard/experiment/<e>/trial/<t>/`` (path contract:
+reference ``tensorboard/build.py:9-24``).  Uploads happen on a background thread
+(reference ``tensorboard/base.py:22-187``); ``close()`` drains it.
+"""
+import logging
+import os
+import pathlib
+import queue
+import shutil
+import tempfile
+import threading
+from typing import Any, Callable, Dict, List, Optional, Tuple
+
+from determined_b200.common import storage
+
+logger = logging.getLogger("determined.tensorboard")
+
+
+def get_sync_path(cluster_id: str, experiment_id: Any, trial_id: Any) -> pathlib.Path:
+    return pathlib.Path(cluster_id, "tensorboard", "experiment", str(experiment_id), "trial", str(trial_id))
+
+
+def get_experiment_sync_path(cluster_id: str, experiment_id: Any) -> pathlib.Path:
+    return pathlib.Path(cluster_id, "tensorboard", "experiment", str(experiment_id))
+
+
+def get_base_path(checkpoint_config: Dict[str, Any]) -> pathlib.Path:
+    allocation_id = os.environ.get("DET_ALLOCATION_ID", "")
+    rank = os.environ.get("RANK", "0")
+    if checkpoint_config.get("base_path"):
+        base = pathlib.Path(checkpoint_config["base_path"])
+    else:
+        base = pathlib.Path(tempfile.gettempdir())
+    return base / f"tensorboard-{allocation_id}-{rank}"
+
+
+def get_rank_aware_path(path: pathlib.Path, rank: int) -> pathlib.Path:
+    """``events.out.tfevents.123`` stays; other files get ``#<rank>`` inserted before the suffix."""
+    if rank == 0 or "tfevents" in path.name:
+        return path
+    stem, suffix = path.stem, path.suffix
+    return path.with_name(f"{stem}#{rank}{suffix}")
+
+
+class TensorboardManager:
+    def __init__(self, base_path: pathlib.Path, sync_path: pathlib.Path, async_upload: bool = True) -> None:
+        self.base_path = pathlib.Path(base_path)
+        self.sync_path = pathlib.Path(sync_path)
+        self.base_path.mkdir(parents=True, exist_ok=True)
+        self._seen: Dict[pathlib.Path, float] = {}
+        self._q: "queue.Queue[Any]" = queue.Queue()
+        self._thread: Optional[threading.Thread] = None
+        self._async = async_upload
+
+    def _changed(self, selector: Callable[[pathlib.Path], bool]) -> List[pathlib.Path]:
+        out = []
+        for root, _, files in os.walk(self.base_path):
+            for f in files:
+                p = pathlib.Path(root, f)
+                try:
+                    mt = p.stat().st_mtime
+                except FileNotFoundError:
+                    continue
+                if self._seen.get(p) == mt or not selector(p):
+                    continue
+                self._seen[p] = mt
+                out.append(p)
+        return out
+
+    def _upload(self, pairs: List[Tuple[pathlib.Path, pathlib.Path]]) -> None:
+        raise NotImplementedError
+
+    def sync(self, selector: Callable[[pathlib.Path], bool] = lambda _: True,
+             mangler: Callable[[pathlib.Path, int], pathlib.Path] = get_rank_aware_path, rank: int = 0) -> None:
+        pairs = []
+        for p in self._changed(selector):
+            rel = p.relative_to(self.base_path)
+            pairs.append((p, self.sync_path / mangler(rel, rank)))
+        if not pairs:
+            return
+        if not self._async:
+            self._upload(pairs)
+            return
+        if self._thread is None:
+            self._thread = threading.Thread(target=self._drain, daemon=True, name="tensorboard-sync")
+            self._thread.start()
+        self._q.put(pairs)
+
+    def _drain(self) -> None:
+        while True:
+            pairs = self._q.get()
+            if pairs is None:
+                return
+            try:
+                self._upload(pairs)
+            except Exception as e:
+                logger.warning("tensorboard sync failed: %s", e)
+
+    def close(self) -> None:
+        if self._thread is not None:
+            self._q.put(None)
+            self._thread.join(timeout=60)
+            self._thread = None
+
+    def delete(self) -> None:
+        raise NotImplementedError
+
+    def __enter__(self) -> "TensorboardManager":
+        return self
+
+    def __exit__(self, *_: Any) -> None:
+        self.close()
+
+
+class SharedFSTensorboardManager(TensorboardManager):
+    def __init__(self, storage_path: str, base_path: pathlib.Path, sync_path: pathlib.Path, **kw: Any) -> None:
+        super().__init__(base_path, sync_path, **kw)
+        self.storage_path = pathlib.Path(storage_path)
+
+    def _upload(self, pairs: List[Tuple[pathlib.Path, pathlib.Path]]) -> None:
+        for src, dst in pairs:
+            target = self.storage_path / dst
+            target.parent.mkdir(parents=True, exist_ok=True)
+            shutil.copy2(src, target)
+
+    def delete(self) -> None:
+        shutil.rmtree(self.storage_path / self.sync_path, ignore_errors=True)
+
+
+class StorageTensorboardManager(TensorboardManager):
+    """Cloud backends: reuse the checkpoint StorageManager's ``upload`` with a staged tree."""
+
+    def __init__(self, manager: storage.StorageManager, base_path: pathlib.Path, sync_path: pathlib.Path, **kw: Any) -> None:
+        super().__init__(base_path, sync_path, **kw)
+        self._manager = manager
+
+    def _upload(self, pairs: List[Tuple[pathlib.Path, pathlib.Path]]) -> None:
+        with tempfile.TemporaryDirectory() as td:
+            for src, dst in pairs:
+                t = pathlib.Path(td) / dst.relative_to(self.sync_path)
+                t.parent.mkdir(parents=True, exist_ok=True)
+                shutil.copy2(src, t)
+            self._manager.upload(td, str(self.sync_path))
+
+    def delete(self) -> None:
+        self._manager.delete(str(self.sync_path), ["**/*"])
+
+
+def build(cluster_id: str, experiment_id: Any, trial_id: Any, checkpoint_config: Dict[str, Any],
+          container_path: Optional[str] = None, async_upload: bool = True) -> TensorboardManager:
+    kind = checkpoint_config.get("type")
+    base = get_base_path(checkpoint_config)
+    sync = get_sync_path(cluster_id, experiment_id, trial_id)
+    if kind in ("shared_fs", "directory"):
+        mgr = storage.build(checkpoint_config, container_path)
+        return SharedFSTensorboardManager(mgr._base_path, base, sync, async_upload=async_upload)
+    if kind in ("s3", "gcs", "azure"):
+        return StorageTensorboardManager(storage.build(checkpoint_config, container_path), base, sync,
+                                         async_upload=async_upload)
+    raise TypeError(f"Unknown storage type for tensorboard: {kind}")
+
+
+def get_metric_writer() -> Any:
+    """A ``torch.utils.tensorboard.SummaryWriter``-backed batch metric writer, if available."""
+    from determined_b200.tensorboard.metric_writers import BatchMetricWriter
+
+    return BatchMetricWriter.try_build()

@@ -1,0 +1,130 @@
+/*
+ * detb200 — C ABI of the B200 (sm_100a) native kernel library used by determined_b200.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a positive cudaError_t or a negative DETB200_ERR_* code;
+ *     detb200_last_error() returns a human-readable description (thread local);
+ *   - all pointers are DEVICE pointers unless a parameter is documented as host memory;
+ *   - `stream` is the CUDA stream to launch on; nothing synchronises unless documented;
+ *   - step-varying scalars (learning rate, step count, scale factors, skip flags) are read from
+ *     device memory so that every launch can be captured in a CUDA graph;
+ *   - dtype codes: 0 = float32, 1 = bfloat16.
+ *
+ * Each entry cites the reference call site it replaces (paths relative to the reference tree).
+ */
+#ifndef DETB200_H
+#define DETB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* detb200_stream_t;
+
+#define DETB200_ERR_BAD_ARG (-1)
+#define DETB200_ERR_TOO_LARGE (-2)
+#define DETB200_ERR_UNSUPPORTED (-3)
+#define DETB200_MAX_RANKS 16
+
+const char* detb200_last_error(void);
+int detb200_abi_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused flat-buffer optimizers (csrc/optim.cu).
+ * Reference: optimizer.step() at harness/determined/pytorch/_pytorch_context.py:899-907,
+ * per-parameter grad.div_ :805-812, optimizer.zero_grad() :909-910.
+ * One launch reads p,g,(state) once and writes p,(state) once and, if zero_grad!=0, g=0.
+ * effective grad = g * static_grad_scale * (*grad_scale if non-NULL); update skipped when
+ * skip!=NULL and *skip!=0 (AMP found-inf), gradients are still zeroed.
+ * ------------------------------------------------------------------------------------------- */
+int detb200_optim_tick(int* step, const int* skip, detb200_stream_t stream);
+int detb200_adam_flat(float* p, float* g, float* m, float* v, void* p_lowp_bf16 /* nullable */, int64_t n,
+                      const float* lr, const int* step, const float* grad_scale /* nullable */,
+                      const int* skip /* nullable */, float beta1, float beta2, float eps, float weight_decay,
+                      int decoupled_wd /* 1 = AdamW */, float static_grad_scale, int zero_grad, int maximize,
+                      detb200_stream_t stream);
+int detb200_sgd_flat(float* p, float* g, float* momentum_buf /* nullable */, int64_t n, const float* lr,
+                     const int* step /* required with momentum */, const float* grad_scale, const int* skip,
+                     float momentum, float dampening, float weight_decay, int nesterov, float static_grad_scale,
+                     int zero_grad, int maximize, detb200_stream_t stream);
+int detb200_adadelta_flat(float* p, float* g, float* square_avg, float* acc_delta, int64_t n, const float* lr,
+                          const float* grad_scale, const int* skip, float rho, float eps, float weight_decay,
+                          float static_grad_scale, int zero_grad, int maximize, detb200_stream_t stream);
+
+/* Gradient-norm pieces of clip_grad_norm_ (reference _pytorch_context.py:885-888).
+ * detb200_sumsq: *out (+)= sum(x^2); deterministic two-stage reduction.  `scratch` is
+ * detb200_sumsq_scratch_bytes() bytes of device memory, zero-initialised once by the caller and
+ * owned by one stream at a time.  nonfinite_flag (nullable) is OR-ed with 1 if the sum is not finite. */
+int64_t detb200_sumsq_scratch_bytes(void);
+int detb200_sumsq(const float* x, int64_t n, void* scratch, float* out, int* nonfinite_flag, int accumulate,
+                  detb200_stream_t stream);
+/* coef = extra_scale * min(1, max_norm / (sqrt(sum(terms)) + 1e-6)); norm_out nullable. */
+int detb200_clip_coef(const float* sumsq_terms, int nterms, float max_norm, float extra_scale, float* coef_out,
+                      float* norm_out, detb200_stream_t stream);
+int detb200_scale_flat(float* x, int64_t n, const float* dyn_scale /* nullable */, float static_scale,
+                       detb200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * In-kernel collectives over NVLink peer memory (csrc/comm.cu).
+ * Reference: DDP all-reduce installed at _pytorch_context.py:296-299, Horovod DistributedOptimizer
+ * :357-368, GradScaler.unscale_ :886-887, hvd.broadcast_parameters _pytorch_trial.py:602-606,
+ * DeepSpeed ZeRO step (user engine.step(), pytorch/deepspeed/_deepspeed_trial.py:364-499).
+ * peer_bufs / peer_ctrls are HOST arrays of `world` device pointers (own buffer at index `rank`,
+ * peers' buffers as mapped with detb200_ipc_open).  phases: 1 start barrier | 2 work | 4 end
+ * barrier; pass 7 on real multi-GPU runs.  timeout_s<=0 disables the in-kernel deadline.
+ * ------------------------------------------------------------------------------------------- */
+int64_t detb200_ctrl_bytes(void);
+int detb200_ipc_handle_bytes(void);
+int detb200_symm_alloc(void** ptr, int64_t bytes);     /* cudaMalloc + zero fill (synchronises) */
+int detb200_symm_free(void* ptr);
+int detb200_ipc_export(void* ptr, void* handle_out /* host, detb200_ipc_handle_bytes() */);
+int detb200_ipc_open(const void* handle /* host */, void** ptr_out);
+int detb200_ipc_close(void* ptr);
+int detb200_enable_peer_access(int peer_device);
+void* detb200_comm_stats_ptr(void* ctrl);               /* device float[2][DETB200_MAX_RANKS]: sumsq per rank, then nonfinite per rank */
+int detb200_comm_read_stats(const void* ctrl, int world, float* stats_out /* host float[2] */,
+                            detb200_stream_t stream);   /* synchronises the stream */
+int detb200_allreduce_fused(void* const* peer_bufs, void* const* peer_ctrls, int rank, int world,
+                            int64_t offset_elems, int64_t n_elems, float scale,
+                            const float* inv_loss_scale /* nullable */, int* found_inf /* nullable */,
+                            int first_of_step, int phases, double timeout_s, detb200_stream_t stream);
+/* mode 0: reduce + AdamW + weight push in one pass; mode 1: reduce into grad_shard (+stats);
+ * mode 2: AdamW from grad_shard + weight push. */
+int detb200_rs_adam_ag(void* const* peer_grad_bufs, void* const* peer_ctrls, void* const* peer_param_bufs,
+                       int param_is_bf16, int rank, int world, int64_t offset_elems, int64_t n_elems,
+                       float* master_shard, float* m_shard, float* v_shard, float* grad_shard /* nullable in mode 0 */,
+                       float scale, const float* lr, const int* step, const float* grad_scale, const int* skip,
+                       float beta1, float beta2, float eps, float weight_decay, int mode, int first_of_step,
+                       int phases, double timeout_s, detb200_stream_t stream);
+int detb200_broadcast(void* const* peer_bufs, void* const* peer_ctrls, int rank, int world, int root,
+                      int64_t offset_elems, int64_t n_elems, int phases, double timeout_s,
+                      detb200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * LayerNorm / RMSNorm (csrc/norm.cu).  Reference: ATen/apex/Megatron fused LN used by the GPT-2 and
+ * GPT-NeoX examples (examples/deepspeed/gpt_neox/Dockerfile:11).  cols even, <= 8192.
+ * ------------------------------------------------------------------------------------------- */
+int detb200_norm_fwd(const void* x, const void* gamma, const void* beta /* nullable */, void* y,
+                     float* mean /* nullable, rows */, float* rstd /* rows */, int64_t rows, int cols, float eps,
+                     int dtype, int rms, detb200_stream_t stream);
+int64_t detb200_norm_bwd_workspace_elems(int64_t rows, int cols, int rms);
+int detb200_norm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                     void* dx, void* dgamma, void* dbeta /* nullable */, float* workspace, int64_t rows, int cols,
+                     int dtype, int rms, detb200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Softmax cross-entropy (csrc/xent.cu).  Reference: log_softmax + nll_loss in
+ * examples/tutorials/mnist_pytorch/model.py:34, train.py:43 and the HF/NeoX LM losses.
+ * ------------------------------------------------------------------------------------------- */
+int detb200_xent_fwd(const void* logits, const int64_t* target, float* loss /* rows */, float* lse /* rows */,
+                     int64_t rows, int vocab, int64_t ignore_index, int dtype, detb200_stream_t stream);
+int detb200_xent_bwd(const void* logits, const int64_t* target, const float* lse, const float* grad_scale,
+                     void* dlogits /* may alias logits */, int64_t rows, int vocab, int64_t ignore_index,
+                     int dtype, detb200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DETB200_H */
