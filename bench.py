@@ -1,0 +1,315 @@
+#!/usr/bin/env python3
+"""Headline benchmark: samples/sec per trial for BASELINE config #2 — CIFAR-10 ResNet-18
+PyTorchTrial, bf16 autocast, ``aggregation_frequency=2``, fused gradient all-reduce — at
+``slots_per_trial`` = N GPUs of one node (weak scaling: fixed per-slot batch).
+
+    python bench.py --gpus 1 --steps 200 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 200 --warmup 20
+    python bench.py --impl reference ...      # the UNMODIFIED reference harness, same trial
+
+A "step" is one ``train_batch`` call (one micro-batch per slot); with aggregation_frequency=2
+every second step all-reduces and runs the optimizer, so K is rounded up to an even number.
+``value`` is measured with the input pool resident on the device; ``e2e`` repeats the run through
+the same public API (``pytorch.init`` + ``Trainer.fit``) with every step's inputs copied from pinned
+host memory and every step's loss copied back to the host.  Both are timed on the device with CUDA
+events bracketed by barrier + synchronize; the max over ranks is reported.  Data is synthetic and
+weights are random-init (no network on the box).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+PER_SLOT_BATCH = 256
+AGG_FREQ = 2
+POOL = 48            # 48 x 256 x 3x32x32 fp32 = 151 MB of distinct inputs (> 126 MB L2)
+BASELINE_PUBLISHED = None   # the reference publishes no throughput number
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int) -> None:
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self) -> None:
+        assert self.proc is not None and self.proc.stdout is not None
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [c.strip() for c in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def _dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local, world
+
+
+class Bracket:
+    """Barrier + synchronize on both sides of exactly K steps; device time by CUDA events."""
+
+    def __init__(self, warmup: int, steps: int, sampler) -> None:
+        import torch
+
+        self.torch = torch
+        self.first, self.last = warmup, warmup + steps - 1
+        self.ev0 = torch.cuda.Event(enable_timing=True)
+        self.ev1 = torch.cuda.Event(enable_timing=True)
+        self.wall0 = self.wall1 = None
+        self.sampler = sampler
+        self.ms = None
+
+    def _barrier(self) -> None:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized():
+            dist.barrier()
+
+    def begin(self) -> None:
+        self._barrier()
+        self.torch.cuda.synchronize()
+        if self.sampler is not None:
+            self.sampler.start()
+        self.wall0 = time.perf_counter()
+        self.ev0.record()
+
+    def end(self) -> None:
+        self.ev1.record()
+        self.torch.cuda.synchronize()
+        self.wall1 = time.perf_counter()
+        self._barrier()
+        self.ms = self.ev0.elapsed_time(self.ev1)
+
+    def max_over_ranks_ms(self) -> float:
+        import torch.distributed as dist
+
+        t = self.torch.tensor([self.ms], device="cuda", dtype=self.torch.float64)
+        if dist.is_available() and dist.is_initialized():
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+
+def run_ours(args, on_device: bool, sampler):
+    import torch
+
+    from benchmarks import cifar_trial
+    from determined_b200 import pytorch
+
+    torch.backends.cudnn.benchmark = True
+    bracket = Bracket(args.warmup, args.steps, sampler)
+    counters = {}
+
+    class BenchCallback(pytorch.PyTorchCallback):
+        def on_training_batch_start(self, batch_idx: int) -> None:
+            if batch_idx == bracket.first:
+                eng = counters["ctx"]._get_engine()
+                counters["launch0"] = getattr(eng, "kernel_launches", 0)
+                bracket.begin()
+
+        def on_training_batch_end(self, batch_idx: int) -> None:
+            if batch_idx == bracket.last:
+                bracket.end()
+                eng = counters["ctx"]._get_engine()
+                counters["launch1"] = getattr(eng, "kernel_launches", 0)
+
+    timing = {"callback": BenchCallback()}
+    Trial = cifar_trial.make_trial(pytorch, per_slot_batch=PER_SLOT_BATCH, pool=POOL, on_device=on_device,
+                                   use_b200_extras=not args.no_graphs, timing=timing)
+    total = args.warmup + args.steps
+    ckdir = tempfile.mkdtemp(prefix="bench-ckpt-")
+    exp_conf = {"checkpoint_storage": {"type": "shared_fs", "host_path": ckdir},
+                "optimizations": {"aggregation_frequency": AGG_FREQ, "average_aggregated_gradients": True}}
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp(prefix="bench-cwd-"))   # checkpoints copy the cwd as code/: keep it empty
+    try:
+        with pytorch.init(hparams={"global_batch_size": PER_SLOT_BATCH * args.world}, exp_conf=exp_conf,
+                          aggregation_frequency=AGG_FREQ, enable_tensorboard_logging=False) as ctx:
+            counters["ctx"] = ctx
+            trial = Trial(ctx)
+            pytorch.Trainer(trial, ctx).fit(max_length=pytorch.Batch(total), reporting_period=pytorch.Batch(total),
+                                            checkpoint_policy="none")
+            ms = bracket.max_over_ranks_ms()
+            launches = counters.get("launch1", 0) - counters.get("launch0", 0)
+            fused = type(trial.opt).__name__
+    finally:
+        os.chdir(cwd)
+    return ms, launches, fused
+
+
+def run_reference(args, sampler):
+    """Same trial through the unmodified reference harness (baseline/_ref) and its stock DDP path."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "determined")):
+        return None, "reference not installed under baseline/_ref (see DESIGN.md)"
+    sys.path.insert(0, os.path.join(ROOT, "baseline", "stubs"))
+    sys.path.insert(0, ref)
+    import torch
+    import torch.distributed as dist
+
+    rank, local, world = _dist_env()
+    os.environ.setdefault("USE_TORCH_DISTRIBUTED", "1" if world > 1 else "")
+    if not os.environ["USE_TORCH_DISTRIBUTED"]:
+        os.environ.pop("USE_TORCH_DISTRIBUTED")
+    try:
+        import determined as det  # noqa: F401
+        from determined import core, pytorch
+    except Exception as e:  # pragma: no cover
+        return None, f"reference import failed: {type(e).__name__}: {e}"
+    from benchmarks import cifar_trial
+
+    torch.backends.cudnn.benchmark = True
+    distributed = None
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group(backend="nccl")
+        distributed = core.DistributedContext.from_torch_distributed()
+    bracket = Bracket(args.warmup, args.steps, sampler)
+
+    def hook(batch_idx: int) -> None:
+        # called at the top of train_batch: batch W starts the clock, batch W+K stops it, so the
+        # bracket holds exactly steps W .. W+K-1 including their per-step D2H of the loss
+        if batch_idx == bracket.first:
+            bracket.begin()
+        elif batch_idx == bracket.last + 1:
+            bracket.end()
+
+    timing = {"hook": hook}
+    Trial = cifar_trial.make_trial(pytorch, per_slot_batch=PER_SLOT_BATCH, pool=POOL, on_device=False,
+                                   use_b200_extras=False, timing=timing)
+    total = args.warmup + args.steps + 1
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp(prefix="bench-ref-cwd-"))
+    try:
+        with pytorch.init(hparams={"global_batch_size": PER_SLOT_BATCH * world}, distributed=distributed,
+                          aggregation_frequency=AGG_FREQ, enable_tensorboard_logging=False) as ctx:
+            trial = Trial(ctx)
+            pytorch.Trainer(trial, ctx).fit(max_length=pytorch.Batch(total), reporting_period=pytorch.Batch(total),
+                                            checkpoint_policy="none")
+        ms = bracket.max_over_ranks_ms()
+    finally:
+        os.chdir(cwd)
+    return ms, None
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-graphs", action="store_true", help="ours: disable CUDA-graph replay of train_batch")
+    ap.add_argument("--skip-e2e", action="store_true")
+    args = ap.parse_args()
+    rank, local, world = _dist_env()
+    args.world = world
+    if args.gpus != world and rank == 0 and world == 1 and args.gpus > 1:
+        # convenience: re-launch ourselves under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"),
+               os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    args.warmup = max(args.warmup, 4)
+    args.warmup += args.warmup % AGG_FREQ          # start the bracket on an aggregation boundary
+    args.steps += args.steps % AGG_FREQ
+
+    import torch
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
+        return
+    torch.cuda.set_device(local % torch.cuda.device_count())
+    sampler = ClockSampler(local) if rank == 0 else None
+    samples = PER_SLOT_BATCH * world * args.steps
+    config = {"model": "resnet18-cifar10 (11.2M params), PyTorchTrial, SGD nesterov", "global_batch": PER_SLOT_BATCH * world,
+              "per_slot_batch": PER_SLOT_BATCH, "image": "3x32x32", "aggregation_frequency": AGG_FREQ,
+              "parallelism": f"dp{world}", "l2_policy": f"input pool of {POOL} distinct batches (151 MB) > 126 MB L2"}
+
+    if args.impl == "reference":
+        ms, why = run_reference(args, sampler)
+        if ms is None:
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": why}))
+            return
+        clocks = sampler.stop() if sampler is not None else None
+        if rank == 0:
+            v = samples / (ms / 1e3)
+            print(json.dumps({"impl": "reference", "metric": "samples/sec per trial", "value": v, "unit": "samples/s",
+                              "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                              "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                              "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                              "config": dict(config, harness="reference determined 0.31.1-dev0, torch DDP/NCCL, eager"),
+                              "e2e": {"value": v, "unit": "samples/s",
+                                      "h2d_bytes_per_step": PER_SLOT_BATCH * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 4},
+                              "clocks": clocks}))
+        return
+
+    ms, launches, fused = run_ours(args, on_device=True, sampler=sampler)
+    clocks = sampler.stop() if sampler is not None else None
+    e2e = None
+    if not args.skip_e2e:
+        ms2, _, _ = run_ours(args, on_device=False, sampler=None)
+        e2e = {"value": samples / (ms2 / 1e3), "unit": "samples/s", "ms_per_step": ms2 / args.steps,
+               "h2d_bytes_per_step": PER_SLOT_BATCH * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 4}
+    if rank == 0:
+        v = samples / (ms / 1e3)
+        print(json.dumps({"impl": "ours", "metric": "samples/sec per trial", "value": v, "unit": "samples/s",
+                          "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+                          "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": (v / BASELINE_PUBLISHED) if BASELINE_PUBLISHED else None,
+                          "dtype": "bf16", "data": "synthetic",
+                          "config": dict(config, harness=f"determined_b200 fused engine ({fused}), "
+                                         f"{'eager' if args.no_graphs else 'CUDA-graph replay'}"),
+                          "e2e": e2e, "gpu_launches": launches, "clocks": clocks}))
+
+
+if __name__ == "__main__":
+    main()

@@ -144,25 +144,25 @@ class _FusedMixin:
 
     # -- checkpoint compatibility with stock torch optimizers ------------------------------------
     def state_dict(self) -> Dict[str, Any]:
+        """Same structure as the stock torch optimizer's (so either can load the other's): state
+        tensors are detached copies, and a per-parameter ``step`` is synthesised from the group's
+        device-side counter."""
         steps = [int(gs.step.item()) for gs in self._detb200_groups]
-        added = []
-        for s in self._detb200_layout.slots:
-            st = self.state[s.param]  # type: ignore[attr-defined]
-            if "step" not in st and (st or self._detb200_kind != "sgd") and steps[s.group] > 0:
-                st["step"] = torch.tensor(float(steps[s.group]))
-                added.append(st)
-        try:
-            sd = super().state_dict()  # type: ignore[misc]
-            # detach from the flat storage so a saved checkpoint does not alias live training state
-            for st in sd["state"].values():
-                for k, v in list(st.items()):
-                    if isinstance(v, torch.Tensor) and v.is_cuda:
-                        st[k] = v.clone()
-            sd["detb200_fused"] = {"kind": self._detb200_kind, "steps": steps}
-            return sd
-        finally:
-            for st in added:
-                st.pop("step", None)
+        sd = super().state_dict()  # type: ignore[misc]
+        group_of = {}
+        for gi, g in enumerate(sd["param_groups"]):
+            for pid in g["params"]:
+                group_of[pid] = gi
+        new_state: Dict[Any, Dict[str, Any]] = {}
+        for pid, st in sd["state"].items():
+            entry = {k: (v.detach().clone() if isinstance(v, torch.Tensor) else v) for k, v in st.items()}
+            if self._detb200_kind != "sgd" and entry:
+                entry["step"] = torch.tensor(float(steps[group_of.get(pid, 0)]))
+            if entry:
+                new_state[pid] = entry
+        sd["state"] = new_state
+        sd["detb200_fused"] = {"kind": self._detb200_kind, "steps": steps}
+        return sd
 
     def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
         sd = dict(state_dict)

@@ -25,6 +25,13 @@ class PyTorchCallback:
     def on_training_epoch_end(self, epoch_idx: int) -> None:
         pass
 
+    def on_training_batch_start(self, batch_idx: int) -> None:
+        """Before each ``train_batch`` (extension: the reference has no per-batch hooks).  Keep it
+        cheap and do not synchronise the device here unless you mean to."""
+
+    def on_training_batch_end(self, batch_idx: int) -> None:
+        """After each ``train_batch`` has been *launched* (the device may still be running it)."""
+
     def on_training_workload_end(self, avg_metrics: Dict[str, Any], batch_metrics: Dict[str, Any]) -> None:
         """After each reporting period, with the (cross-rank averaged) training metrics."""
 

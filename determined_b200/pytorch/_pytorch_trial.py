@@ -136,6 +136,7 @@ class _GraphedStep:
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.static_in: Any = None
         self.static_out: Any = None
+        self.launches = 0     # native kernels recorded in the graph (for launch accounting)
 
 
 def _copy_into(dst: Any, src: Any) -> None:
@@ -157,6 +158,13 @@ def _clone_tree(x: Any) -> Any:
     if isinstance(x, (list, tuple)):
         return type(x)(_clone_tree(v) for v in x)
     return x
+
+
+def _graph_outputs(out: Dict[str, Any]) -> Dict[str, Any]:
+    """Static graph outputs are overwritten by the next replay.  Scalars are copied to pinned
+    memory right after this returns (stream-ordered before the next replay), so they may alias;
+    anything bigger is cloned."""
+    return {k: (v.clone() if isinstance(v, torch.Tensor) and v.numel() != 1 else v) for k, v in out.items()}
 
 
 def _same_shapes(a: Any, b: Any) -> bool:
@@ -215,6 +223,14 @@ class _PyTorchTrialController:
         self._graphs_failed = False
         self.step_timer = core.StepTimer()
         self._metric_writer: Any = None
+        self._batch_hooks = [cb for cb in self.callbacks.values()
+                             if util.is_overridden(cb.on_training_batch_start, _callback.PyTorchCallback)
+                             or util.is_overridden(cb.on_training_batch_end, _callback.PyTorchCallback)]
+        # pinned ring for scalar metrics: every batch's scalars are copied D2H asynchronously as soon
+        # as they are produced; the host only waits once per reporting window
+        self._pin_ring: Optional[torch.Tensor] = None
+        self._pin_used = 0
+        self._pin_event: Any = None
 
         if not context.models:
             raise errors.InvalidExperimentException(
@@ -450,7 +466,11 @@ class _PyTorchTrialController:
                 for cb in self.callbacks.values():
                     cb.on_training_epoch_start(epoch_idx)
             num_inputs += self.trial.get_batch_length(batch)
-            per_batch.append(self._train_batch(batch, epoch_idx, batch_idx))
+            for cb in self._batch_hooks:
+                cb.on_training_batch_start(batch_idx)
+            per_batch.append(self._stage_metrics(self._train_batch(batch, epoch_idx, batch_idx)))
+            for cb in self._batch_hooks:
+                cb.on_training_batch_end(batch_idx)
             # bookkeeping for the batch that just finished
             self.state.batches_trained += 1
             if in_epoch == epoch_len - 1:
@@ -466,7 +486,7 @@ class _PyTorchTrialController:
                 reached.add(_Boundary.TRAIN)
             if reached:
                 break
-        host_metrics = _metric_utils.materialize_metrics(per_batch)   # the one D2H of this window
+        host_metrics = self._collect_metrics(per_batch)   # the one host sync of this window
         dt = time.time() - t0
         if per_batch:
             logger.info(util.make_timing_log("trained", dt, num_inputs, len(per_batch)))
@@ -491,6 +511,38 @@ class _PyTorchTrialController:
         for sched in ctx.lr_schedulers:
             self._auto_step_lr_scheduler_per_batch(batch_idx, sched)
         return out
+
+    _PIN_SLOTS = 4096
+
+    def _stage_metrics(self, out: Dict[str, Any]) -> Dict[str, Any]:
+        """Replace 0-d device tensors by ``("pin", slot)`` markers after queueing an async D2H copy
+        into pinned memory (no host synchronisation here)."""
+        if self.context.device.type != "cuda":
+            return out
+        if self._pin_ring is None:
+            self._pin_ring = torch.empty(self._PIN_SLOTS, dtype=torch.float32).pin_memory()
+        staged: Dict[str, Any] = {}
+        for k, v in out.items():
+            if isinstance(v, torch.Tensor) and v.is_cuda and v.numel() == 1 and self._pin_used < self._PIN_SLOTS:
+                slot = self._pin_used
+                self._pin_used += 1
+                self._pin_ring[slot:slot + 1].copy_(v.detach().reshape(1).to(torch.float32), non_blocking=True)
+                staged[k] = ("pin", slot)
+            else:
+                staged[k] = v
+        return staged
+
+    def _collect_metrics(self, per_batch: List[Dict[str, Any]]) -> List[Dict[str, Any]]:
+        if self._pin_used:
+            torch.cuda.current_stream(self.context.device).synchronize()
+            assert self._pin_ring is not None
+            vals = self._pin_ring[: self._pin_used].tolist()
+            for m in per_batch:
+                for k, v in m.items():
+                    if isinstance(v, tuple) and len(v) == 2 and v[0] == "pin":
+                        m[k] = vals[v[1]]
+            self._pin_used = 0
+        return _metric_utils.materialize_metrics(per_batch)
 
     def _eager_train_batch(self, batch: Any, epoch_idx: int, batch_idx: int) -> Dict[str, Any]:
         out = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
@@ -527,7 +579,10 @@ class _PyTorchTrialController:
             if sync is not None:
                 sync()
         gs.graph.replay()
-        return _clone_tree(gs.static_out)
+        eng = self.context._get_engine()
+        if hasattr(eng, "kernel_launches"):
+            eng.kernel_launches += gs.launches
+        return _graph_outputs(gs.static_out)
 
     def _needs_more_warmup(self, boundary: bool) -> bool:
         # each phase must have run eagerly at least once so lazily created state exists
@@ -541,15 +596,18 @@ class _PyTorchTrialController:
             if sync is not None:
                 sync()
         g = torch.cuda.CUDAGraph()
+        eng = self.context._get_engine()
+        n0 = getattr(eng, "kernel_launches", 0)
         with torch.cuda.graph(g):
             out = self.trial.train_batch(batch=gs.static_in, epoch_idx=epoch_idx, batch_idx=batch_idx)
             if isinstance(out, torch.Tensor):
                 out = {"loss": out}
             gs.static_out = {k: (v.detach() if isinstance(v, torch.Tensor) else v) for k, v in out.items()}
         gs.graph = g
+        gs.launches = getattr(eng, "kernel_launches", 0) - n0
         # capture does not execute: replay once so this batch is actually trained on
         g.replay()
-        return _clone_tree(gs.static_out)
+        return _graph_outputs(gs.static_out)
 
     def _auto_step_lr_scheduler_per_batch(self, batch_idx: int, sched: _lr_scheduler.LRScheduler) -> None:
         """Step schedulers only on aggregation boundaries, catching up the batches in between."""

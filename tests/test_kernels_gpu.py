@@ -1,0 +1,218 @@
+"""Numerics of every native kernel against a plain PyTorch fp32 reference of the same op."""
+import ctypes
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from determined_b200.ops import _lib
+
+    return _lib
+
+
+@pytest.mark.parametrize("kind", ["sgd", "sgd_mom", "sgd_nesterov", "adam", "adamw", "adadelta"])
+@pytest.mark.parametrize("n", [1, 7, 4096 + 3, 1 << 20])
+def test_fused_optimizers_match_torch(kind, n):
+    from determined_b200.ops import optim
+    from determined_b200.parallel.flat import FlatLayout
+
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    shapes = [(n,)] if n < 1000 else [(n // 2,), (n - n // 2 - 5,), (5,)]
+    mk = lambda: [torch.nn.Parameter(torch.randn(s, device=dev)) for s in shapes]  # noqa: E731
+    ref_p, fus_p = mk(), None
+    fus_p = [torch.nn.Parameter(p.detach().clone()) for p in ref_p]
+    def build(ps):
+        if kind == "sgd":
+            return torch.optim.SGD(ps, lr=0.1, weight_decay=0.01)
+        if kind == "sgd_mom":
+            return torch.optim.SGD(ps, lr=0.1, momentum=0.9, dampening=0.1)
+        if kind == "sgd_nesterov":
+            return torch.optim.SGD(ps, lr=0.1, momentum=0.9, nesterov=True, weight_decay=1e-3)
+        if kind == "adam":
+            return torch.optim.Adam(ps, lr=1e-2, weight_decay=0.01)
+        if kind == "adamw":
+            return torch.optim.AdamW(ps, lr=1e-2, weight_decay=0.1, betas=(0.9, 0.95))
+        return torch.optim.Adadelta(ps, lr=1.0, rho=0.9, weight_decay=1e-3)
+    ref, fus = build(ref_p), build(fus_p)
+    lay = FlatLayout(fus.param_groups, dev)
+    assert optim.fuse_optimizer_(fus, lay)
+    for step in range(4):
+        grads = [torch.randn_like(p) for p in ref_p]
+        for p, g in zip(ref_p, grads):
+            p.grad = g.clone()
+        for p, g in zip(fus_p, grads):
+            p.grad.copy_(g)
+        ref.step()
+        fus.step(zero_grad=True)
+        for a, b in zip(ref_p, fus_p):
+            torch.testing.assert_close(b.detach(), a.detach(), rtol=2e-5, atol=2e-6)
+        assert float(lay.flat_grad.abs().max()) == 0.0
+    # state dict round trip through the stock optimizer
+    sd = fus.state_dict()
+    ref2 = build([torch.nn.Parameter(p.detach().clone()) for p in ref_p])
+    sd.pop("detb200_fused")
+    ref2.load_state_dict(sd)
+
+
+def test_adam_grad_scale_and_skip():
+    from determined_b200.ops import optim
+    from determined_b200.parallel.flat import FlatLayout
+
+    dev = torch.device("cuda")
+    p = torch.nn.Parameter(torch.randn(1000, device=dev))
+    q = torch.nn.Parameter(p.detach().clone())
+    ref, fus = torch.optim.AdamW([p], lr=1e-2), torch.optim.AdamW([q], lr=1e-2)
+    lay = FlatLayout(fus.param_groups, dev)
+    optim.fuse_optimizer_(fus, lay)
+    g = torch.randn_like(p)
+    p.grad = g * 0.25
+    q.grad.copy_(g)
+    scale = torch.tensor([0.5], device=dev)
+    ref.step()
+    fus.step(grad_scale=scale, static_scale=0.5)
+    torch.testing.assert_close(q.detach(), p.detach(), rtol=2e-5, atol=2e-6)
+    before = q.detach().clone()
+    q.grad.copy_(g)
+    skip = torch.ones(1, dtype=torch.int32, device=dev)
+    fus.step(skip=skip, zero_grad=True)
+    torch.testing.assert_close(q.detach(), before, rtol=0, atol=0)
+    assert float(q.grad.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("n", [5, 1024, (1 << 22) + 1])
+def test_sumsq_and_clip_coef(n):
+    from determined_b200.ops import optim
+
+    dev = torch.device("cuda")
+    x = torch.randn(n + 3, device=dev)[:n] if False else torch.randn(n, device=dev)
+    sc = optim.NormScratch(dev)
+    for _ in range(2):  # the scratch ticket must re-arm itself
+        out = optim.sumsq(x, sc)
+        torch.testing.assert_close(out[0].double(), x.double().pow(2).sum(), rtol=1e-5, atol=1e-6)
+    optim.sumsq(x, sc, accumulate=True)
+    torch.testing.assert_close(sc.sumsq[0].double(), 2 * x.double().pow(2).sum(), rtol=1e-5, atol=1e-6)
+    optim.sumsq(x, sc)
+    coef = optim.clip_coef(sc.sumsq, 1.0, sc, extra_scale=2.0)
+    norm = x.double().norm()
+    torch.testing.assert_close(coef[0].double(), 2.0 * torch.clamp(1.0 / (norm + 1e-6), max=1.0), rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(sc.norm[0].double(), norm, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols", [(1, 2), (37, 1024), (513, 2560), (64, 8192), (300, 770)])
+@pytest.mark.parametrize("rms", [False, True])
+def test_norm_fwd_bwd(dtype, rows, cols, rms):
+    from determined_b200.ops import norm
+
+    torch.manual_seed(1)
+    dev = torch.device("cuda")
+    x = torch.randn(rows, cols, device=dev, dtype=dtype, requires_grad=True)
+    g = (torch.randn(cols, device=dev) * 0.5 + 1).to(dtype).requires_grad_()
+    b = torch.randn(cols, device=dev).to(dtype).requires_grad_()
+    dy = torch.randn(rows, cols, device=dev, dtype=dtype)
+    xr, gr, br = (t.detach().float().requires_grad_() for t in (x, g, b))
+    if rms:
+        y = norm.rms_norm(x, g, 1e-6)
+        yr = xr * torch.rsqrt(xr.pow(2).mean(-1, keepdim=True) + 1e-6) * gr
+    else:
+        y = norm.layer_norm(x, g, b, 1e-5)
+        yr = torch.nn.functional.layer_norm(xr, (cols,), gr, br, 1e-5)
+    y.backward(dy)
+    yr.backward(dy.float())
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(y.float(), yr, **tol)
+    torch.testing.assert_close(x.grad.float(), xr.grad, **tol)
+    gtol = dict(rtol=3e-2, atol=3e-2 * (rows ** 0.5)) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(g.grad.float(), gr.grad, **gtol)
+    if not rms:
+        torch.testing.assert_close(b.grad.float(), br.grad, **gtol)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,vocab", [(1, 10), (33, 50257), (128, 50304), (7, 131)])
+def test_xent_fwd_bwd(dtype, rows, vocab):
+    from determined_b200.ops import xent
+
+    torch.manual_seed(2)
+    dev = torch.device("cuda")
+    logits = (torch.randn(rows, vocab, device=dev) * 3).to(dtype).requires_grad_()
+    tgt = torch.randint(0, vocab, (rows,), device=dev)
+    if rows > 2:
+        tgt[1] = -100
+    ref_logits = logits.detach().float().requires_grad_()
+    loss = xent.cross_entropy(logits, tgt)
+    ref = torch.nn.functional.cross_entropy(ref_logits, tgt, ignore_index=-100)
+    (loss * 2).backward()
+    (ref * 2).backward()
+    torch.testing.assert_close(loss, ref, rtol=1e-4, atol=1e-4)
+    tol = dict(rtol=2e-2, atol=1e-3) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(logits.grad.float(), ref_logits.grad, **tol)
+    # in-place backward gives the same gradient
+    l2 = logits.detach().clone().requires_grad_()
+    xent.cross_entropy(l2 * 1.0, tgt, inplace_backward=True).mul(2).backward()
+    torch.testing.assert_close(l2.grad.float(), ref_logits.grad, **tol)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_allreduce_fused_emulated_ranks(world):
+    """Single-GPU emulation: all `world` rank buffers live on this device and the reduce phase is
+    launched once per emulated rank (no inter-kernel spinning — see B200_PROFILING.md)."""
+    from determined_b200.ops import _lib, comm
+
+    lib = _lib.load()
+    dev = torch.device("cuda")
+    n = 4 * world * 1000
+    groups = [comm.PeerGroup(0, 1, None, dev) for _ in range(world)]
+    bufs = [comm.SymmetricBuffer(4 * n, dev) for _ in range(world)]
+    tens = [b.tensor(torch.float32, n) for b in bufs]
+    torch.manual_seed(3)
+    for t in tens:
+        t.copy_(torch.randn(n, device=dev))
+    expect = torch.stack([t.clone() for t in tens]).double().sum(0) * (0.5 / world)
+    ptrs = (ctypes.c_void_p * world)(*[b.ptr for b in bufs])
+    ctrls = (ctypes.c_void_p * world)(*[g.ctrl.ptr for g in groups])
+    found = torch.zeros(1, dtype=torch.int32, device=dev)
+    for r in range(world):
+        _lib.check(lib.detb200_allreduce_fused(ptrs, ctrls, r, world, 0, n, 0.5 / world, None, found.data_ptr(), 1, 2,
+                                               0.0, _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    for t in tens:
+        torch.testing.assert_close(t.double(), expect, rtol=1e-5, atol=1e-6)
+
+
+def test_resnet_step_fused_vs_torch():
+    """One optimizer's worth of ResNet-18 params: fused engine (world=1) must track torch SGD."""
+    from determined_b200 import core, pytorch
+    from determined_b200.models.resnet_cifar import resnet18_cifar
+
+    torch.manual_seed(0)
+    torch.backends.cudnn.allow_tf32 = False     # exact fp32 on both sides
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = torch.device("cuda")
+    ref_model = resnet18_cifar().to(dev)
+    x = torch.randn(16, 3, 32, 32, device=dev)
+    y = torch.randint(0, 10, (16,), device=dev)
+    with pytorch.init(hparams={"global_batch_size": 16}) as ctx:
+        import copy
+
+        model = ctx.wrap_model(copy.deepcopy(ref_model))
+        opt = ctx.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4))
+        ref_opt = torch.optim.SGD(ref_model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+        assert type(opt).__name__ == "FusedSGD"
+        ctx._current_batch_idx = 0
+        for i in range(3):
+            ctx._current_batch_idx = i
+            loss = torch.nn.functional.cross_entropy(model(x), y)
+            ctx.backward(loss)
+            ctx.step_optimizer(opt)
+            rl = torch.nn.functional.cross_entropy(ref_model(x), y)
+            ref_opt.zero_grad()
+            rl.backward()
+            ref_opt.step()
+            torch.testing.assert_close(loss, rl, rtol=1e-3, atol=1e-3)
+        for a, b in zip(model.parameters(), ref_model.parameters()):
+            torch.testing.assert_close(a, b, rtol=5e-3, atol=1e-3)
