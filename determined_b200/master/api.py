@@ -1,0 +1,1429 @@
+"""REST API of the single-box master (grpc-gateway-style JSON over HTTP, camelCase fields,
+uint64 as strings) — the wire contract in SURVEY §10.
+
+Parity: reference ``proto/src/determined/api/v1/api.proto`` + ``master/internal/api_*.go``.
+Implemented: the endpoints the harness, CLI and SDK call — auth (login/logout/me), master info,
+experiments (create/get/list/activate/pause/cancel/kill/archive/delete/patch, trials, checkpoints,
+best metric, model-def download), trials (get, searcher operation/completed_operation/progress/
+early_exit/runner metadata, metrics report + query, logs), checkpoints (report/get/rm/patch),
+allocations (preemption long-poll + ack + pending, rendezvous, all_gather, proxy address, daemon
+mark), runs/start, task logs, agents/slots, resource pools + job queue, templates, model registry,
+workspaces/projects, users, webhooks, trial-source-info, preview-search, custom-searcher events.
+Built on ``http.server.ThreadingHTTPServer`` (stdlib only).
+"""
+import base64
+import json
+import logging
+import re
+import secrets
+import threading
+import time
+import urllib.parse
+from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
+from typing import Any, Callable, Dict, List, Optional, Tuple
+
+from determined_b200 import __version__
+from determined_b200.common.api import authentication as auth
+from determined_b200.master import core, db as dbmod, expconf
+from determined_b200.master import searcher as S
+
+logger = logging.getLogger("determined.master.api")
+
+
+class HTTPError(Exception):
+    def __init__(self, status: int, message: str) -> None:
+        super().__init__(message)
+        self.status, self.message = status, message
+
+
+ROUTES: List[Tuple[str, "re.Pattern[str]", Callable, bool]] = []
+
+
+def route(method: str, pattern: str, auth_required: bool = True) -> Callable:
+    rx = re.compile("^" + re.sub(r"\{(\w+)\}", r"(?P<\1>[^/]+)", pattern) + "/?$")
+
+    def deco(fn: Callable) -> Callable:
+        ROUTES.append((method, rx, fn, auth_required))
+        return fn
+    return deco
+
+
+def _ts(t: Optional[float]) -> Optional[str]:
+    if t is None:
+        return None
+    return time.strftime("%Y-%m-%dT%H:%M:%S", time.gmtime(t)) + (".%06dZ" % int((t % 1) * 1e6))
+
+
+def _state(prefix: str, s: Optional[str]) -> str:
+    return f"{prefix}_{s}" if s else f"{prefix}_UNSPECIFIED"
+
+
+class Ctx:
+    def __init__(self, master: core.Master, user: Optional[Dict[str, Any]], query: Dict[str, List[str]], body: Any,
+                 raw: bytes) -> None:
+        self.m, self.user, self.query, self.body, self.raw = master, user, query, body, raw
+
+    def q(self, name: str, default: Any = None) -> Any:
+        v = self.query.get(name)
+        return v[0] if v else default
+
+    def qi(self, name: str, default: int = 0) -> int:
+        try:
+            return int(self.q(name, default))
+        except (TypeError, ValueError):
+            return default
+
+
+# ---------------------------------------------------------------------------------------------
+# serializers
+# ---------------------------------------------------------------------------------------------
+def exp_json(m: core.Master, row: Any) -> Dict[str, Any]:
+    cfg = dbmod.U(row["config"], {})
+    u = m.db.one("SELECT username FROM users WHERE id=?", (row["owner_id"],))
+    ntr = m.db.one("SELECT COUNT(*) c FROM trials WHERE experiment_id=?", (row["id"],))["c"]
+    live = m.experiments.get(row["id"])
+    state = live.state if live is not None else row["state"]
+    return {"id": row["id"], "name": cfg.get("name"), "description": cfg.get("description"), "labels": cfg.get("labels") or [],
+            "state": _state("STATE", state), "startTime": _ts(row["start_time"]), "endTime": _ts(row["end_time"]),
+            "archived": bool(row["archived"]), "numTrials": ntr, "progress": row["progress"], "username": u["username"] if u else None,
+            "userId": row["owner_id"], "searcherType": (cfg.get("searcher") or {}).get("name"),
+            "searcherMetric": (cfg.get("searcher") or {}).get("metric"), "resourcePool": (cfg.get("resources") or {}).get("resource_pool") or "default",
+            "projectId": row["project_id"], "parentId": row["parent_id"], "notes": row["notes"], "jobId": row["job_id"],
+            "config": cfg, "originalConfig": row["original_config"], "unmanaged": bool(row["unmanaged"])}
+
+
+def trial_json(m: core.Master, row: Any) -> Dict[str, Any]:
+    live = m.trials.get(row["id"])
+    state = live.state if live is not None else row["state"]
+    lv = m.db.one("SELECT steps_completed, metrics, report_time FROM metrics WHERE trial_id=? AND grp='validation' ORDER BY id DESC LIMIT 1", (row["id"],))
+    lt = m.db.one("SELECT steps_completed, metrics, report_time FROM metrics WHERE trial_id=? AND grp='training' ORDER BY id DESC LIMIT 1", (row["id"],))
+    out = {"id": row["id"], "experimentId": row["experiment_id"], "state": _state("STATE", state), "hparams": dbmod.U(row["hparams"], {}),
+           "startTime": _ts(row["start_time"]), "endTime": _ts(row["end_time"]), "restarts": row["restarts"],
+           "totalBatchesProcessed": row["total_batches"], "latestCheckpoint": row["latest_checkpoint"],
+           "warmStartCheckpointUuid": row["warm_start_checkpoint"], "taskId": row["task_id"], "runnerState": row["runner_state"],
+           "searcherMetricValue": row["best_validation"], "bestValidation": None, "latestValidation": None, "latestTraining": None,
+           "seed": row["seed"], "requestId": row["request_id"]}
+    if lv is not None:
+        out["latestValidation"] = {"totalBatches": lv["steps_completed"], "endTime": _ts(lv["report_time"]),
+                                   "metrics": {"avgMetrics": dbmod.U(lv["metrics"], {})}}
+    if lt is not None:
+        out["latestTraining"] = {"totalBatches": lt["steps_completed"], "endTime": _ts(lt["report_time"]),
+                                 "metrics": {"avgMetrics": dbmod.U(lt["metrics"], {})}}
+    return out
+
+
+def ckpt_json(m: core.Master, row: Any) -> Dict[str, Any]:
+    t = m.db.one("SELECT experiment_id, hparams FROM trials WHERE id=?", (row["trial_id"],))
+    exp_cfg = None
+    if t is not None:
+        e = m.db.one("SELECT config FROM experiments WHERE id=?", (t["experiment_id"],))
+        exp_cfg = dbmod.U(e["config"], {}) if e is not None else None
+    val = m.db.one("SELECT metrics FROM metrics WHERE trial_id=? AND grp='validation' AND steps_completed=? ORDER BY id DESC LIMIT 1",
+                   (row["trial_id"], row["steps_completed"]))
+    metric_name = ((exp_cfg or {}).get("searcher") or {}).get("metric")
+    vm = dbmod.U(val["metrics"], {}) if val is not None else {}
+    return {"uuid": row["uuid"], "taskId": row["task_id"], "allocationId": row["allocation_id"], "reportTime": _ts(row["report_time"]),
+            "state": _state("STATE", row["state"]), "resources": {k: str(v) for k, v in dbmod.U(row["resources"], {}).items()},
+            "metadata": dbmod.U(row["metadata"], {}), "storageId": row["storage_id"],
+            "training": {"trialId": row["trial_id"], "experimentId": t["experiment_id"] if t else None, "experimentConfig": exp_cfg,
+                         "hparams": dbmod.U(t["hparams"], {}) if t else None, "validationMetrics": {"avgMetrics": vm},
+                         "searcherMetric": vm.get(metric_name) if metric_name else None}}
+
+
+def user_json(row: Any) -> Dict[str, Any]:
+    return {"id": row["id"], "username": row["username"], "admin": bool(row["admin"]), "active": bool(row["active"]),
+            "displayName": row["display_name"], "modifiedAt": _ts(row["modified_at"])}
+
+
+def page(items: List[Any], ctx: Ctx) -> Tuple[List[Any], Dict[str, Any]]:
+    off, lim = ctx.qi("offset", 0), ctx.qi("limit", 0)
+    total = len(items)
+    if off < 0:
+        off = max(total + off, 0)
+    sub = items[off: off + lim] if lim > 0 else items[off:]
+    return sub, {"offset": off, "limit": lim, "startIndex": off, "endIndex": off + len(sub), "total": total}
+
+
+# ---------------------------------------------------------------------------------------------
+# auth / master
+# ---------------------------------------------------------------------------------------------
+@route("POST", "/api/v1/auth/login", auth_required=False)
+def login(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    row = ctx.m.db.one("SELECT * FROM users WHERE username=?", (b.get("username"),))
+    pw = b.get("password") or ""
+    if not b.get("isHashed", False) and pw:
+        pw = auth.salt_and_hash(pw)
+    if row is None or not row["active"] or (row["password_hash"] or "") != (pw or auth.salt_and_hash("")) and (row["password_hash"] or "") != pw:
+        raise HTTPError(401, "invalid credentials")
+    tok = secrets.token_hex(24)
+    ctx.m.db.exec("INSERT INTO sessions(token,user_id,expiry) VALUES(?,?,?)", (tok, row["id"], time.time() + 30 * 86400))
+    return {"token": tok, "user": user_json(row)}
+
+
+@route("POST", "/api/v1/auth/logout")
+def logout(ctx: Ctx) -> Any:
+    ctx.m.db.exec("DELETE FROM sessions WHERE token=?", (ctx.user["token"],))
+    return {}
+
+
+@route("GET", "/api/v1/me")
+def me(ctx: Ctx) -> Any:
+    return {"user": user_json(ctx.m.db.one("SELECT * FROM users WHERE id=?", (ctx.user["id"],)))}
+
+
+@route("GET", "/api/v1/master", auth_required=False)
+@route("GET", "/info", auth_required=False)
+def master_info(ctx: Ctx) -> Any:
+    return {"version": __version__, "masterId": ctx.m.cluster_id, "clusterId": ctx.m.cluster_id, "clusterName": "b200-box",
+            "telemetryEnabled": False, "ssoProviders": [], "externalLoginUri": "", "rbacEnabled": False, "branding": "determined_b200",
+            "strictJobQueueControl": False, "userManagementEnabled": True, "product": "PRODUCT_COMMUNITY"}
+
+
+@route("GET", "/api/v1/master/config")
+def master_config(ctx: Ctx) -> Any:
+    return {"config": {"resource_manager": {"type": "agent", "scheduler": {"type": ctx.m.pool.scheduler, "fitting_policy": ctx.m.pool.policy,
+                                                                            "preemption": {"enabled": ctx.m.pool.preemption}}},
+                       "checkpoint_storage": ctx.m.cluster_defaults.get("checkpoint_storage")}}
+
+
+# -- users ---------------------------------------------------------------------------------------
+@route("GET", "/api/v1/users")
+def list_users(ctx: Ctx) -> Any:
+    rows = [user_json(r) for r in ctx.m.db.all("SELECT * FROM users ORDER BY id")]
+    items, pg = page(rows, ctx)
+    return {"users": items, "pagination": pg}
+
+
+@route("POST", "/api/v1/users")
+def create_user(ctx: Ctx) -> Any:
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    b = ctx.body or {}
+    u = b.get("user") or {}
+    pw = b.get("password") or ""
+    if not b.get("isHashed", False) and pw:
+        pw = auth.salt_and_hash(pw)
+    try:
+        uid = ctx.m.db.exec("INSERT INTO users(username,password_hash,admin,active,display_name,modified_at) VALUES(?,?,?,?,?,?)",
+                            (u.get("username"), pw or auth.salt_and_hash(""), int(bool(u.get("admin"))), int(u.get("active", True)), u.get("displayName"), time.time()))
+    except Exception as e:
+        raise HTTPError(409, f"cannot create user: {e}")
+    return {"user": user_json(ctx.m.db.one("SELECT * FROM users WHERE id=?", (uid,)))}
+
+
+@route("PATCH", "/api/v1/users/{uid}")
+def patch_user(ctx: Ctx, uid: str) -> Any:
+    if not ctx.user["admin"] and int(uid) != ctx.user["id"]:
+        raise HTTPError(403, "forbidden")
+    b = ctx.body or {}
+    u = b.get("user", b)
+    for col, key in (("active", "active"), ("admin", "admin"), ("display_name", "displayName"), ("username", "username")):
+        if key in u and u[key] is not None:
+            ctx.m.db.exec(f"UPDATE users SET {col}=?, modified_at=? WHERE id=?", (int(u[key]) if isinstance(u[key], bool) else u[key], time.time(), int(uid)))
+    if u.get("password") is not None:
+        pw = u["password"] if u.get("isHashed") else auth.salt_and_hash(u["password"])
+        ctx.m.db.exec("UPDATE users SET password_hash=? WHERE id=?", (pw, int(uid)))
+    return {"user": user_json(ctx.m.db.one("SELECT * FROM users WHERE id=?", (int(uid),)))}
+
+
+@route("POST", "/api/v1/users/{uid}/password")
+def set_password(ctx: Ctx, uid: str) -> Any:
+    if not ctx.user["admin"] and int(uid) != ctx.user["id"]:
+        raise HTTPError(403, "forbidden")
+    pw = ctx.body if isinstance(ctx.body, str) else (ctx.body or {}).get("password", "")
+    ctx.m.db.exec("UPDATE users SET password_hash=?, modified_at=? WHERE id=?", (pw, time.time(), int(uid)))
+    return {"user": user_json(ctx.m.db.one("SELECT * FROM users WHERE id=?", (int(uid),)))}
+
+
+# ---------------------------------------------------------------------------------------------
+# experiments
+# ---------------------------------------------------------------------------------------------
+@route("POST", "/api/v1/experiments")
+def create_experiment(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    files = b.get("modelDefinition") or []
+    blob = None
+    if files:
+        import io
+        import tarfile
+
+        buf = io.BytesIO()
+        with tarfile.open(fileobj=buf, mode="w:gz") as tf:
+            for f in files:
+                data = base64.b64decode(f.get("content") or "")
+                ti = tarfile.TarInfo(f["path"])
+                if f.get("type") == 53 or str(f.get("type")) == "53" or f["path"].endswith("/"):
+                    ti.type = tarfile.DIRTYPE
+                    ti.mode = f.get("mode", 0o755) & 0o7777 or 0o755
+                    tf.addfile(ti)
+                    continue
+                ti.size = len(data)
+                ti.mode = (f.get("mode", 0o644) & 0o7777) or 0o644
+                ti.mtime = int(f.get("mtime", time.time()))
+                tf.addfile(ti, io.BytesIO(data))
+        blob = buf.getvalue()
+    try:
+        exp, cfg = ctx.m.create_experiment(b.get("config", ""), blob, owner=ctx.user["username"], activate=bool(b.get("activate", True)),
+                                           parent_id=b.get("parentId"), template=b.get("template"), validate_only=bool(b.get("validateOnly")),
+                                           project_id=int(b.get("projectId") or 1), unmanaged=bool(b.get("unmanaged")))
+    except expconf.ConfigError as e:
+        raise HTTPError(400, "invalid experiment configuration: " + "; ".join(e.errors))
+    except core.NotFound as e:
+        raise HTTPError(404, str(e))
+    except ValueError as e:
+        raise HTTPError(400, f"invalid experiment: {e}")
+    if exp is None:
+        return {"experiment": None, "config": cfg, "warnings": []}
+    row = ctx.m.db.one("SELECT * FROM experiments WHERE id=?", (exp.id,))
+    return {"experiment": exp_json(ctx.m, row), "config": cfg, "warnings": []}
+
+
+@route("GET", "/api/v1/experiments")
+def list_experiments(ctx: Ctx) -> Any:
+    where, args = ["1=1"], []
+    if ctx.q("archived") is not None:
+        where.append("archived=?")
+        args.append(1 if ctx.q("archived") in ("true", "1", True) else 0)
+    if ctx.q("projectId"):
+        where.append("project_id=?")
+        args.append(ctx.qi("projectId"))
+    states = ctx.query.get("states") or []
+    rows = ctx.m.db.all(f"SELECT * FROM experiments WHERE {' AND '.join(where)} ORDER BY id " + ("DESC" if ctx.q("orderBy") == "ORDER_BY_DESC" else "ASC"), args)
+    out = [exp_json(ctx.m, r) for r in rows]
+    if states:
+        out = [e for e in out if e["state"] in states]
+    users = ctx.query.get("users") or []
+    if users:
+        out = [e for e in out if e["username"] in users]
+    if ctx.q("name"):
+        out = [e for e in out if ctx.q("name") in (e["name"] or "")]
+    items, pg = page(out, ctx)
+    return {"experiments": items, "pagination": pg}
+
+
+def _exp_row(ctx: Ctx, eid: str) -> Any:
+    row = ctx.m.db.one("SELECT * FROM experiments WHERE id=?", (int(eid),))
+    if row is None:
+        raise HTTPError(404, f"experiment {eid} not found")
+    return row
+
+
+@route("GET", "/api/v1/experiments/{eid}")
+def get_experiment(ctx: Ctx, eid: str) -> Any:
+    row = _exp_row(ctx, eid)
+    return {"experiment": exp_json(ctx.m, row), "jobSummary": None}
+
+
+def _exp_action(name: str) -> Callable:
+    def handler(ctx: Ctx, eid: str) -> Any:
+        _exp_row(ctx, eid)
+        with ctx.m.lock:
+            exp = ctx.m.experiments.get(int(eid))
+            if exp is None:
+                raise HTTPError(409, f"experiment {eid} is in a terminal state")
+            getattr(exp, name)()
+        ctx.m.kick()
+        return {}
+    return handler
+
+
+route("POST", "/api/v1/experiments/{eid}/activate")(_exp_action("activate"))
+route("POST", "/api/v1/experiments/{eid}/pause")(_exp_action("pause"))
+route("POST", "/api/v1/experiments/{eid}/cancel")(_exp_action("cancel"))
+route("POST", "/api/v1/experiments/{eid}/kill")(_exp_action("kill"))
+
+
+@route("POST", "/api/v1/experiments/{eid}/archive")
+def archive_experiment(ctx: Ctx, eid: str) -> Any:
+    row = _exp_row(ctx, eid)
+    if row["state"] not in core.TERMINAL:
+        raise HTTPError(409, "only terminal experiments can be archived")
+    ctx.m.db.exec("UPDATE experiments SET archived=1 WHERE id=?", (int(eid),))
+    return {}
+
+
+@route("POST", "/api/v1/experiments/{eid}/unarchive")
+def unarchive_experiment(ctx: Ctx, eid: str) -> Any:
+    _exp_row(ctx, eid)
+    ctx.m.db.exec("UPDATE experiments SET archived=0 WHERE id=?", (int(eid),))
+    return {}
+
+
+@route("DELETE", "/api/v1/experiments/{eid}")
+def delete_experiment(ctx: Ctx, eid: str) -> Any:
+    row = _exp_row(ctx, eid)
+    if row["state"] not in core.TERMINAL:
+        raise HTTPError(409, "only terminal experiments can be deleted")
+    e = int(eid)
+    from determined_b200.common import storage
+
+    cfg = dbmod.U(row["config"], {})
+    try:
+        mgr = storage.build(cfg["checkpoint_storage"], None)
+        for c in ctx.m.db.all("SELECT c.uuid FROM checkpoints c JOIN trials t ON t.id=c.trial_id WHERE t.experiment_id=?", (e,)):
+            try:
+                mgr.delete(c["uuid"], ["**/*"])
+            except Exception:
+                pass
+    except Exception:
+        pass
+    tids = [r["id"] for r in ctx.m.db.all("SELECT id FROM trials WHERE experiment_id=?", (e,))]
+    for t in tids:
+        ctx.m.db.exec("DELETE FROM metrics WHERE trial_id=?", (t,))
+        ctx.m.db.exec("DELETE FROM checkpoints WHERE trial_id=?", (t,))
+        ctx.m.db.exec("DELETE FROM task_logs WHERE task_id=?", (f"trial-{t}",))
+    ctx.m.db.exec("DELETE FROM trials WHERE experiment_id=?", (e,))
+    ctx.m.db.exec("DELETE FROM experiments WHERE id=?", (e,))
+    ctx.m.experiments.pop(e, None)
+    return {}
+
+
+@route("PATCH", "/api/v1/experiments/{eid}")
+def patch_experiment(ctx: Ctx, eid: str) -> Any:
+    row = _exp_row(ctx, eid)
+    b = (ctx.body or {}).get("experiment", ctx.body or {})
+    cfg = dbmod.U(row["config"], {})
+    changed = False
+    for k in ("name", "description", "labels"):
+        if k in b and b[k] is not None:
+            cfg[k] = b[k]
+            changed = True
+    if "notes" in b:
+        ctx.m.db.exec("UPDATE experiments SET notes=? WHERE id=?", (b["notes"], int(eid)))
+    res = b.get("resources") or {}
+    with ctx.m.lock:
+        live = ctx.m.experiments.get(int(eid))
+        for key, setter in (("priority", ctx.m.pool.set_priority), ("weight", ctx.m.pool.set_weight), ("maxSlots", ctx.m.pool.set_max_slots)):
+            if res.get(key) is not None:
+                ck = {"maxSlots": "max_slots"}.get(key, key)
+                cfg.setdefault("resources", {})[ck] = res[key]
+                changed = True
+                if live is not None:
+                    live.config.setdefault("resources", {})[ck] = res[key]
+                    setter(live.job_id, res[key])
+        if b.get("checkpointStorage"):
+            for k, ck in (("saveExperimentBest", "save_experiment_best"), ("saveTrialBest", "save_trial_best"), ("saveTrialLatest", "save_trial_latest")):
+                if k in b["checkpointStorage"]:
+                    cfg.setdefault("checkpoint_storage", {})[ck] = b["checkpointStorage"][k]
+                    changed = True
+        if changed:
+            ctx.m.db.exec("UPDATE experiments SET config=? WHERE id=?", (dbmod.J(cfg), int(eid)))
+            if live is not None:
+                for k in ("name", "description", "labels"):
+                    if k in cfg:
+                        live.config[k] = cfg[k]
+    ctx.m.kick()
+    return {"experiment": exp_json(ctx.m, _exp_row(ctx, eid))}
+
+
+@route("GET", "/api/v1/experiments/{eid}/trials")
+def exp_trials(ctx: Ctx, eid: str) -> Any:
+    _exp_row(ctx, eid)
+    rows = ctx.m.db.all("SELECT * FROM trials WHERE experiment_id=? ORDER BY id", (int(eid),))
+    items, pg = page([trial_json(ctx.m, r) for r in rows], ctx)
+    return {"trials": items, "pagination": pg}
+
+
+@route("GET", "/api/v1/experiments/{eid}/checkpoints")
+def exp_checkpoints(ctx: Ctx, eid: str) -> Any:
+    _exp_row(ctx, eid)
+    rows = ctx.m.db.all("SELECT c.* FROM checkpoints c JOIN trials t ON t.id=c.trial_id WHERE t.experiment_id=? ORDER BY c.report_time", (int(eid),))
+    out = [ckpt_json(ctx.m, r) for r in rows]
+    states = ctx.query.get("states") or []
+    if states:
+        out = [c for c in out if c["state"] in states]
+    if ctx.q("sortByMetric") or ctx.q("sortBy") == "SORT_BY_SEARCHER_METRIC":
+        sib = bool((dbmod.U(_exp_row(ctx, eid)["config"], {}).get("searcher") or {}).get("smaller_is_better", True))
+        key = ctx.q("sortByMetric")
+        def metric_of(c: Dict[str, Any]) -> float:
+            v = (c["training"]["validationMetrics"]["avgMetrics"] or {}).get(key) if key else c["training"]["searcherMetric"]
+            return float("inf") if v is None else (float(v) if sib else -float(v))
+        out.sort(key=metric_of)
+    if ctx.q("orderBy") == "ORDER_BY_DESC" and not (ctx.q("sortByMetric") or ctx.q("sortBy") == "SORT_BY_SEARCHER_METRIC"):
+        out.reverse()
+    items, pg = page(out, ctx)
+    return {"checkpoints": items, "pagination": pg}
+
+
+@route("GET", "/api/v1/experiments/{eid}/searcher/best_searcher_validation_metric")
+def best_metric(ctx: Ctx, eid: str) -> Any:
+    row = _exp_row(ctx, eid)
+    cfg = dbmod.U(row["config"], {})
+    metric = (cfg.get("searcher") or {}).get("metric")
+    sib = bool((cfg.get("searcher") or {}).get("smaller_is_better", True))
+    best = None
+    for r in ctx.m.db.all("SELECT m.metrics FROM metrics m JOIN trials t ON t.id=m.trial_id WHERE t.experiment_id=? AND m.grp='validation'", (int(eid),)):
+        v = dbmod.U(r["metrics"], {}).get(metric)
+        if isinstance(v, (int, float)) and (best is None or (v < best) == sib):
+            best = float(v)
+    if best is None:
+        raise HTTPError(404, "no validations for experiment")
+    return {"metric": best}
+
+
+@route("GET", "/api/v1/experiments/{eid}/model_def")
+def model_def(ctx: Ctx, eid: str) -> Any:
+    row = _exp_row(ctx, eid)
+    return {"b64Tgz": base64.b64encode(row["model_definition"] or b"").decode()}
+
+
+@route("GET", "/api/v1/tasks/{task_id}/context_directory")
+def context_directory(ctx: Ctx, task_id: str) -> Any:
+    t = ctx.m.db.one("SELECT experiment_id FROM trials WHERE task_id=?", (task_id,))
+    if t is None:
+        raise HTTPError(404, "task not found")
+    row = ctx.m.db.one("SELECT model_definition FROM experiments WHERE id=?", (t["experiment_id"],))
+    return {"b64Tgz": base64.b64encode(row["model_definition"] or b"").decode()}
+
+
+@route("POST", "/api/v1/preview-hp-search")
+def preview_search(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    cfg = expconf.parse(b.get("config", "{}"))
+    expconf.validate_sanity(cfg)
+    cfg = expconf.with_defaults(cfg)
+    res = S.simulate(cfg["searcher"], cfg.get("hyperparameters") or {}, seed=int(b.get("seed", 0)))
+    unit = S.new_search_method(cfg["searcher"]).unit() or "batches"
+    trials = [{"occurrences": n, "operations": [{"validateAfter": {"length": str(length)}}]} for length, n in sorted(res["results"].items())]
+    return {"simulation": {"config": cfg, "seed": int(b.get("seed", 0)), "trials": trials, "unit": unit}}
+
+
+# -- custom searcher events ------------------------------------------------------------------------
+@route("GET", "/api/v1/experiments/{eid}/searcher_events")
+def searcher_events(ctx: Ctx, eid: str) -> Any:
+    deadline = time.time() + min(ctx.qi("timeout_seconds", 60), 120)
+    while True:
+        with ctx.m.lock:
+            exp = ctx.m.experiments.get(int(eid))
+            if exp is None:
+                _exp_row(ctx, eid)
+                return {"searcherEvents": []}
+            meth = exp.searcher.method
+            if not isinstance(meth, S.CustomSearch):
+                raise HTTPError(400, "experiment does not use a custom searcher")
+            if meth.events:
+                return {"searcherEvents": list(meth.events)}
+        if time.time() > deadline:
+            return {"searcherEvents": []}
+        time.sleep(0.2)
+
+
+@route("POST", "/api/v1/experiments/{eid}/searcher_operations")
+def searcher_operations(ctx: Ctx, eid: str) -> Any:
+    b = ctx.body or {}
+    with ctx.m.lock:
+        exp = ctx.m.experiments.get(int(eid))
+        if exp is None:
+            raise HTTPError(404, "experiment not active")
+        meth = exp.searcher.method
+        if not isinstance(meth, S.CustomSearch):
+            raise HTTPError(400, "experiment does not use a custom searcher")
+        ops: List[Any] = []
+        for o in b.get("searcherOperations") or []:
+            if "createTrial" in o:
+                c = o["createTrial"]
+                hp = c.get("hyperparams")
+                hp = json.loads(hp) if isinstance(hp, str) else (hp or {})
+                ops.append(S.Create(c["requestId"], exp.searcher.rand.int64(0, (1 << 31) - 1), hp, c.get("checkpoint")))
+            elif "trialOperation" in o and "validateAfter" in o["trialOperation"]:
+                v = o["trialOperation"]["validateAfter"]
+                ops.append(S.ValidateAfter(v["requestId"], int(v["length"])))
+            elif "closeTrial" in o:
+                ops.append(S.Close(o["closeTrial"]["requestId"]))
+            elif "shutDown" in o:
+                sd = o["shutDown"] or {}
+                ops.append(S.Shutdown(bool(sd.get("cancel")), bool(sd.get("failure"))))
+            elif "setSearcherProgress" in o:
+                meth.progress_value = float(o["setSearcherProgress"].get("progress", 0))
+        trig = b.get("triggeredByEvent") or {}
+        if trig.get("id") is not None:
+            meth.pop_events_through(int(trig["id"]))
+        exp.process_operations(exp.searcher.record_external_ops(ops))
+    return {}
+
+
+# ---------------------------------------------------------------------------------------------
+# trials
+# ---------------------------------------------------------------------------------------------
+def _trial_row(ctx: Ctx, tid: str) -> Any:
+    row = ctx.m.db.one("SELECT * FROM trials WHERE id=?", (int(tid),))
+    if row is None:
+        raise HTTPError(404, f"trial {tid} not found")
+    return row
+
+
+@route("GET", "/api/v1/trials/{tid}")
+def get_trial(ctx: Ctx, tid: str) -> Any:
+    return {"trial": trial_json(ctx.m, _trial_row(ctx, tid))}
+
+
+@route("PATCH", "/api/v1/trials/{tid}")
+def patch_trial(ctx: Ctx, tid: str) -> Any:
+    """Unmanaged-trial heartbeat / state (reference ``core/_heartbeat.py:67-69,129-131``)."""
+    _trial_row(ctx, tid)
+    st = (ctx.body or {}).get("state")
+    if st:
+        s = st.replace("STATE_", "")
+        ctx.m.db.exec("UPDATE trials SET state=?, last_activity=?, end_time=? WHERE id=?",
+                      (s, time.time(), time.time() if s in core.TERMINAL else None, int(tid)))
+        if s in core.TERMINAL:
+            t = ctx.m.db.one("SELECT experiment_id FROM trials WHERE id=?", (int(tid),))
+            ctx.m.db.exec("UPDATE experiments SET state=?, end_time=? WHERE id=? AND unmanaged=1", (s, time.time(), t["experiment_id"]))
+    else:
+        ctx.m.db.exec("UPDATE trials SET last_activity=? WHERE id=?", (time.time(), int(tid)))
+    return {"trial": trial_json(ctx.m, _trial_row(ctx, tid))}
+
+
+@route("POST", "/api/v1/experiments/{eid}/trials")
+def create_unmanaged_trial(ctx: Ctx, eid: str) -> Any:
+    """``core_v2`` unmanaged mode: the client creates its own trial row."""
+    row = _exp_row(ctx, eid)
+    b = ctx.body or {}
+    tid = ctx.m.db.exec("INSERT INTO trials(experiment_id,request_id,state,hparams,seed,start_time,searcher_state) VALUES(?,?,?,?,?,?,?)",
+                        (int(eid), secrets.token_hex(8), "ACTIVE", dbmod.J(b.get("hparams") or {}), 0, time.time(), "{}"))
+    ctx.m.db.exec("UPDATE trials SET task_id=? WHERE id=?", (f"trial-{tid}", tid))
+    return {"trial": trial_json(ctx.m, _trial_row(ctx, str(tid)))}
+
+
+@route("GET", "/api/v1/trials/{tid}/searcher/operation")
+def trial_searcher_op(ctx: Ctx, tid: str) -> Any:
+    with ctx.m.lock:
+        try:
+            t = ctx.m.get_trial(int(tid))
+        except core.NotFound as e:
+            raise HTTPError(404, str(e))
+        op = t.current_op()
+        if op is None or t.experiment.state not in (core.ACTIVE, core.PAUSED):
+            return {"op": None, "completed": True}
+        return {"op": {"validateAfter": {"length": str(op)}}, "completed": False}
+
+
+@route("POST", "/api/v1/trials/{tid}/searcher/completed_operation")
+def trial_completed_op(ctx: Ctx, tid: str) -> Any:
+    b = ctx.body or {}
+    length = int((b.get("op") or {}).get("length") or (b.get("completedOperation", {}).get("op", {}) or {}).get("length", 0))
+    metric = b.get("searcherMetric", (b.get("completedOperation") or {}).get("searcherMetric"))
+    with ctx.m.lock:
+        t = ctx.m.get_trial(int(tid))
+        try:
+            t.experiment.op_completed(t, length, metric)
+        except core.Conflict as e:
+            raise HTTPError(409, str(e))
+    return {}
+
+
+@route("POST", "/api/v1/trials/{tid}/progress")
+def trial_progress(ctx: Ctx, tid: str) -> Any:
+    v = ctx.body
+    if isinstance(v, dict):
+        v = v.get("progress", 0)
+    with ctx.m.lock:
+        t = ctx.m.get_trial(int(tid))
+        t.experiment.trial_progress(t, float(v or 0))
+    return {}
+
+
+@route("POST", "/api/v1/trials/{tid}/early_exit")
+def trial_early_exit(ctx: Ctx, tid: str) -> Any:
+    b = ctx.body or {}
+    reason = b.get("reason") or (b.get("earlyExit") or {}).get("reason") or ""
+    reason = reason.replace("EXITED_REASON_", "")
+    if reason not in (S.ExitedReason.INVALID_HP, S.ExitedReason.INIT_INVALID_HP, "USER_REQUESTED_STOP"):
+        raise HTTPError(400, f"unknown exited reason {reason!r}")
+    if reason == "USER_REQUESTED_STOP":
+        reason = S.ExitedReason.USER_CANCELED
+    with ctx.m.lock:
+        t = ctx.m.get_trial(int(tid))
+        try:
+            t.experiment.trial_early_exit(t, reason)
+        except core.Conflict as e:
+            raise HTTPError(400, str(e))
+    return {}
+
+
+@route("POST", "/api/v1/trials/{tid}/runner/metadata")
+def trial_runner_metadata(ctx: Ctx, tid: str) -> Any:
+    st = (ctx.body or {}).get("state", "")
+    with ctx.m.lock:
+        t = ctx.m.trials.get(int(tid))
+        if t is not None:
+            t.runner_state = st
+    ctx.m.db.exec("UPDATE trials SET runner_state=? WHERE id=?", (st, int(tid)))
+    return {}
+
+
+@route("POST", "/api/v1/trials/{tid}/metrics")
+def report_metrics(ctx: Ctx, tid: str) -> Any:
+    b = ctx.body or {}
+    grp = b.get("group", "training")
+    mm = b.get("metrics") or {}
+    inner = mm.get("metrics") or {}
+    steps = int(mm.get("stepsCompleted") or 0)
+    ctx.m.db.exec("INSERT INTO metrics(trial_id,trial_run_id,grp,steps_completed,metrics,batch_metrics,report_time) VALUES(?,?,?,?,?,?,?)",
+                  (int(tid), int(mm.get("trialRunId") or 0), grp, steps, dbmod.J(inner.get("avgMetrics") or {}),
+                   dbmod.J(inner.get("batchMetrics")) if inner.get("batchMetrics") else None, time.time()))
+    if grp in ("training", "validation"):
+        with ctx.m.lock:
+            t = ctx.m.trials.get(int(tid))
+            if t is not None:
+                if grp == "training":
+                    t.total_batches = max(t.total_batches, steps)
+                else:
+                    t.latest_validation_batches = steps
+                t.persist()
+            else:
+                ctx.m.db.exec("UPDATE trials SET total_batches=MAX(total_batches, ?) WHERE id=?", (steps, int(tid)))
+    return {}
+
+
+@route("GET", "/api/v1/trials/{tid}/metrics")
+@route("GET", "/api/v1/trials/metrics/trial_metrics")
+def get_metrics(ctx: Ctx, tid: Optional[str] = None) -> Any:
+    ids = [int(tid)] if tid else [int(x) for x in ctx.query.get("trialIds", [])]
+    grp = ctx.q("group")
+    out = []
+    for i in ids:
+        sql, args = "SELECT * FROM metrics WHERE trial_id=?", [i]
+        if grp:
+            sql += " AND grp=?"
+            args.append(grp)
+        for r in ctx.m.db.all(sql + " ORDER BY steps_completed, id", args):
+            out.append({"trialId": r["trial_id"], "group": r["grp"], "totalBatches": r["steps_completed"], "trialRunId": r["trial_run_id"],
+                        "endTime": _ts(r["report_time"]), "metrics": {"avgMetrics": dbmod.U(r["metrics"], {}), "batchMetrics": dbmod.U(r["batch_metrics"])}})
+    return {"metrics": out}
+
+
+@route("GET", "/api/v1/trials/{tid}/checkpoints")
+def trial_checkpoints(ctx: Ctx, tid: str) -> Any:
+    _trial_row(ctx, tid)
+    rows = ctx.m.db.all("SELECT * FROM checkpoints WHERE trial_id=? ORDER BY report_time", (int(tid),))
+    out = [ckpt_json(ctx.m, r) for r in rows]
+    states = ctx.query.get("states") or []
+    if states:
+        out = [c for c in out if c["state"] in states]
+    if ctx.q("orderBy") == "ORDER_BY_DESC":
+        out.reverse()
+    items, pg = page(out, ctx)
+    return {"checkpoints": items, "pagination": pg}
+
+
+@route("POST", "/api/v1/trials/{tid}/kill")
+def kill_trial(ctx: Ctx, tid: str) -> Any:
+    with ctx.m.lock:
+        t = ctx.m.get_trial(int(tid))
+        if t.allocation is not None:
+            t.allocation.kill()
+        t.ops = []
+        t.close_requested = True
+        t.early_exit_reason = t.early_exit_reason or S.ExitedReason.USER_CANCELED
+        t.persist()
+    return {}
+
+
+def _logs(ctx: Ctx, task_id: str) -> Any:
+    follow = ctx.q("follow") in ("true", "1")
+    after = ctx.qi("offset", 0)
+    limit = ctx.qi("limit", 0) or 5000
+    deadline = time.time() + (min(ctx.qi("timeout_seconds", 20), 60) if follow else 0)
+    while True:
+        rows = ctx.m.db.get_logs(task_id, after, limit)
+        if rows or not follow or time.time() > deadline:
+            break
+        running = ctx.m.db.one("SELECT COUNT(*) c FROM allocations WHERE task_id=? AND state='RUNNING'", (task_id,))["c"]
+        if not running:
+            break
+        time.sleep(0.25)
+    return {"logs": [{"id": r["id"], "taskId": r["task_id"], "allocationId": r["allocation_id"], "timestamp": _ts(r["ts"]), "level": "LOG_LEVEL_" + (r["level"] or "INFO"),
+                      "rankId": r["rank_id"], "stdtype": r["stdtype"], "source": r["source"], "log": r["log"], "message": r["log"]} for r in rows]}
+
+
+@route("GET", "/api/v1/trials/{tid}/logs")
+def trial_logs(ctx: Ctx, tid: str) -> Any:
+    _trial_row(ctx, tid)
+    return _logs(ctx, f"trial-{int(tid)}")
+
+
+@route("GET", "/api/v1/tasks/{task_id}/logs")
+def task_logs(ctx: Ctx, task_id: str) -> Any:
+    return _logs(ctx, task_id)
+
+
+@route("POST", "/task-logs")
+@route("POST", "/api/v1/task/logs")
+def post_task_logs(ctx: Ctx) -> Any:
+    rows = []
+    items = ctx.body if isinstance(ctx.body, list) else (ctx.body or {}).get("logs", [])
+    for it in items:
+        rows.append((it.get("task_id") or it.get("taskId"), it.get("allocation_id"), time.time(), it.get("level", "INFO"),
+                     it.get("rank_id", it.get("rank")), it.get("stdtype", "stdout"), it.get("source", "task"), it.get("log", "")))
+    if rows:
+        ctx.m.db.add_logs(rows)
+    return {}
+
+
+# ---------------------------------------------------------------------------------------------
+# checkpoints
+# ---------------------------------------------------------------------------------------------
+@route("POST", "/api/v1/checkpoints")
+def report_checkpoint(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    ck = b.get("checkpoint", b)
+    uuid_ = ck.get("uuid")
+    if not uuid_:
+        raise HTTPError(400, "checkpoint uuid required")
+    md = ck.get("metadata") or {}
+    res = {k: int(v) for k, v in (ck.get("resources") or {}).items()}
+    t = ctx.m.db.one("SELECT id FROM trials WHERE task_id=?", (ck.get("taskId"),))
+    tid = t["id"] if t is not None else None
+    steps = int(md.get("steps_completed", 0) or 0)
+    state = (ck.get("state") or "STATE_COMPLETED").replace("STATE_", "")
+    ctx.m.db.exec("INSERT OR REPLACE INTO checkpoints(uuid,trial_id,task_id,allocation_id,state,resources,metadata,report_time,steps_completed,storage_id,size) VALUES(?,?,?,?,?,?,?,?,?,?,?)",
+                  (uuid_, tid, ck.get("taskId"), ck.get("allocationId"), state, dbmod.J(res), dbmod.J(md), time.time(), steps, ck.get("storageId"), sum(res.values())))
+    if tid is not None and state == "COMPLETED":
+        with ctx.m.lock:
+            tr = ctx.m.trials.get(tid)
+            if tr is not None:
+                tr.latest_checkpoint = uuid_
+                tr.total_batches = max(tr.total_batches, steps)
+                tr.persist()
+            else:
+                ctx.m.db.exec("UPDATE trials SET latest_checkpoint=? WHERE id=?", (uuid_, tid))
+    return {}
+
+
+def _ckpt_row(ctx: Ctx, uuid_: str) -> Any:
+    row = ctx.m.db.one("SELECT * FROM checkpoints WHERE uuid=?", (uuid_,))
+    if row is None:
+        raise HTTPError(404, f"checkpoint {uuid_} not found")
+    return row
+
+
+@route("GET", "/api/v1/checkpoints/{uuid_}")
+def get_checkpoint(ctx: Ctx, uuid_: str) -> Any:
+    return {"checkpoint": ckpt_json(ctx.m, _ckpt_row(ctx, uuid_))}
+
+
+@route("POST", "/api/v1/checkpoints/{uuid_}/metadata")
+def post_checkpoint_metadata(ctx: Ctx, uuid_: str) -> Any:
+    row = _ckpt_row(ctx, uuid_)
+    md = dbmod.U(row["metadata"], {})
+    md.update(((ctx.body or {}).get("checkpoint") or {}).get("metadata") or (ctx.body or {}).get("metadata") or {})
+    ctx.m.db.exec("UPDATE checkpoints SET metadata=? WHERE uuid=?", (dbmod.J(md), uuid_))
+    return {"checkpoint": ckpt_json(ctx.m, _ckpt_row(ctx, uuid_))}
+
+
+@route("PATCH", "/api/v1/checkpoints")
+def patch_checkpoints(ctx: Ctx) -> Any:
+    for c in (ctx.body or {}).get("checkpoints", []):
+        row = ctx.m.db.one("SELECT * FROM checkpoints WHERE uuid=?", (c.get("uuid"),))
+        if row is None:
+            continue
+        if "resources" in c and c["resources"] is not None:
+            res = (c["resources"] or {}).get("resources", c["resources"])
+            res = {k: int(v) for k, v in (res or {}).items()}
+            ctx.m.db.exec("UPDATE checkpoints SET resources=?, size=?, state=? WHERE uuid=?",
+                          (dbmod.J(res), sum(res.values()), "COMPLETED" if res else "DELETED", c["uuid"]))
+    return {}
+
+
+def _delete_ckpts(ctx: Ctx, uuids: List[str], globs: List[str]) -> None:
+    from determined_b200.common import storage
+
+    for u in uuids:
+        row = ctx.m.db.one("SELECT c.*, t.experiment_id FROM checkpoints c LEFT JOIN trials t ON t.id=c.trial_id WHERE c.uuid=?", (u,))
+        if row is None:
+            raise HTTPError(404, f"checkpoint {u} not found")
+        if ctx.m.db.one("SELECT id FROM model_versions WHERE checkpoint_uuid=?", (u,)) is not None:
+            raise HTTPError(400, f"checkpoint {u} is registered in the model registry and cannot be deleted")
+        e = ctx.m.db.one("SELECT config FROM experiments WHERE id=?", (row["experiment_id"],))
+        cfg = dbmod.U(e["config"], {}) if e is not None else {"checkpoint_storage": ctx.m.cluster_defaults["checkpoint_storage"]}
+        mgr = storage.build(cfg["checkpoint_storage"], None)
+        left = mgr.delete(u, globs)
+        full = "**/*" in globs or not left
+        ctx.m.db.exec("UPDATE checkpoints SET resources=?, size=?, state=? WHERE uuid=?",
+                      (dbmod.J(left), sum(left.values()), "DELETED" if full else ("PARTIALLY_DELETED" if len(left) < len(dbmod.U(row["resources"], {})) else row["state"]), u))
+
+
+@route("DELETE", "/api/v1/checkpoints")
+def delete_checkpoints(ctx: Ctx) -> Any:
+    _delete_ckpts(ctx, (ctx.body or {}).get("checkpointUuids", []), ["**/*"])
+    return {}
+
+
+@route("POST", "/api/v1/checkpoints/rm")
+def rm_checkpoints(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    _delete_ckpts(ctx, b.get("checkpointUuids", []), b.get("checkpointGlobs") or ["**/*"])
+    return {}
+
+
+@route("POST", "/api/v1/runs/start")
+def runs_start(ctx: Ctx) -> Any:
+    return {"storageId": None}
+
+
+@route("POST", "/api/v1/trial-source-info")
+def trial_source_info(ctx: Ctx) -> Any:
+    i = (ctx.body or {}).get("trialSourceInfo") or {}
+    ctx.m.db.exec("INSERT INTO trial_source_infos(trial_id,checkpoint_uuid,type,model_id,model_version) VALUES(?,?,?,?,?)",
+                  (i.get("trialId"), i.get("checkpointUuid"), i.get("trialSourceInfoType"), i.get("modelId"), i.get("modelVersion")))
+    return {"trialId": i.get("trialId"), "checkpointUuid": i.get("checkpointUuid")}
+
+
+# ---------------------------------------------------------------------------------------------
+# allocations
+# ---------------------------------------------------------------------------------------------
+def _alloc(ctx: Ctx, aid: str) -> core.Allocation:
+    try:
+        return ctx.m.get_allocation(aid)
+    except core.NotFound as e:
+        raise HTTPError(404, str(e))
+
+
+@route("GET", "/api/v1/allocations/{aid}/signals/preemption")
+def preemption_signal(ctx: Ctx, aid: str) -> Any:
+    a = _alloc(ctx, aid)
+    timeout = min(float(ctx.q("timeout_seconds", ctx.q("timeoutSeconds", 60)) or 0), 120.0)
+    return {"preempt": a.wait_preemption(timeout)}
+
+
+@route("POST", "/api/v1/allocations/{aid}/signals/ack_preemption")
+def ack_preemption(ctx: Ctx, aid: str) -> Any:
+    a = ctx.m.allocations.get(aid)
+    if a is not None:
+        a.preempt_acked = True
+    return {}
+
+
+@route("POST", "/api/v1/allocations/{aid}/signals/pending_preemption")
+def pending_preemption(ctx: Ctx, aid: str) -> Any:
+    _alloc(ctx, aid).preempt()
+    return {}
+
+
+@route("GET", "/api/v1/allocations/{aid}/resources/{rid}/rendezvous")
+def rendezvous(ctx: Ctx, aid: str, rid: str) -> Any:
+    a = _alloc(ctx, aid)
+    return {"rendezvousInfo": {"addresses": ["127.0.0.1"], "rank": 0, "slots": [len(a.slot_ids)]}}
+
+
+@route("POST", "/api/v1/allocations/{aid}/all_gather")
+def all_gather(ctx: Ctx, aid: str) -> Any:
+    a = _alloc(ctx, aid)
+    b = ctx.body or {}
+    try:
+        data = a.all_gather(b.get("requestUuid", ""), int(b.get("rank", len(a.allgathers.get(b.get("requestUuid", ""), {})))),
+                            int(b.get("numPeers", 1)), b.get("data"))
+    except TimeoutError as e:
+        raise HTTPError(408, str(e))
+    return {"data": data}
+
+
+@route("POST", "/api/v1/allocations/{aid}/proxy_address")
+@route("POST", "/api/v1/allocations/{aid}/resources/{rid}/daemon")
+@route("POST", "/api/v1/allocations/{aid}/ready")
+@route("POST", "/api/v1/allocations/{aid}/waiting")
+def alloc_noop(ctx: Ctx, aid: str, rid: Optional[str] = None) -> Any:
+    _alloc(ctx, aid)
+    return {}
+
+
+@route("GET", "/api/v1/allocations/{aid}")
+def get_allocation(ctx: Ctx, aid: str) -> Any:
+    r = ctx.m.db.one("SELECT * FROM allocations WHERE id=?", (aid,))
+    if r is None:
+        raise HTTPError(404, "allocation not found")
+    return {"allocation": {"allocationId": r["id"], "taskId": r["task_id"], "state": "STATE_" + r["state"], "slots": r["slots"],
+                           "startTime": _ts(r["start_time"]), "endTime": _ts(r["end_time"]), "exitCode": r["exit_code"]}}
+
+
+# ---------------------------------------------------------------------------------------------
+# cluster: agents / slots / pools / job queue
+# ---------------------------------------------------------------------------------------------
+def _agent_json(m: core.Master) -> Dict[str, Any]:
+    ag = m.pool.agents[m.agent_id]
+    slots = {}
+    for i in range(ag.num_slots):
+        g = m.gpus[i] if i < len(m.gpus) else None
+        owner = ag.used.get(i)
+        slots[str(i)] = {"id": str(i), "enabled": (ag.slot_enabled or [True] * ag.num_slots)[i],
+                         "device": {"id": i, "brand": g.name if g else "cpu", "uuid": g.uuid if g else f"cpu-{i}", "type": "TYPE_CUDA" if g else "TYPE_CPU"},
+                         "container": {"id": owner, "state": "STATE_RUNNING"} if owner else None, "draining": False}
+    return {"id": m.agent_id, "registeredTime": _ts(m.start_time), "slots": slots, "resourcePools": [m.pool.name], "enabled": ag.enabled,
+            "draining": False, "addresses": ["127.0.0.1"], "version": __version__, "label": ag.label}
+
+
+@route("GET", "/api/v1/agents")
+def agents(ctx: Ctx) -> Any:
+    return {"agents": [_agent_json(ctx.m)], "pagination": {"total": 1}}
+
+
+@route("GET", "/api/v1/agents/{agent_id}")
+def get_agent(ctx: Ctx, agent_id: str) -> Any:
+    if agent_id != ctx.m.agent_id:
+        raise HTTPError(404, "agent not found")
+    return {"agent": _agent_json(ctx.m)}
+
+
+@route("GET", "/api/v1/agents/{agent_id}/slots")
+def get_slots(ctx: Ctx, agent_id: str) -> Any:
+    return {"slots": list(_agent_json(ctx.m)["slots"].values())}
+
+
+def _set_enabled(ctx: Ctx, agent_id: str, slot: Optional[str], enabled: bool) -> Any:
+    if agent_id != ctx.m.agent_id:
+        raise HTTPError(404, "agent not found")
+    with ctx.m.lock:
+        ag = ctx.m.pool.agents[agent_id]
+        if slot is None:
+            ag.enabled = enabled
+        else:
+            if ag.slot_enabled is None:
+                ag.slot_enabled = [True] * ag.num_slots
+            ag.slot_enabled[int(slot)] = enabled
+    ctx.m.kick()
+    return {"agent": _agent_json(ctx.m)}
+
+
+route("POST", "/api/v1/agents/{agent_id}/enable")(lambda ctx, agent_id: _set_enabled(ctx, agent_id, None, True))
+route("POST", "/api/v1/agents/{agent_id}/disable")(lambda ctx, agent_id: _set_enabled(ctx, agent_id, None, False))
+route("POST", "/api/v1/agents/{agent_id}/slots/{slot}/enable")(lambda ctx, agent_id, slot: _set_enabled(ctx, agent_id, slot, True))
+route("POST", "/api/v1/agents/{agent_id}/slots/{slot}/disable")(lambda ctx, agent_id, slot: _set_enabled(ctx, agent_id, slot, False))
+
+
+@route("GET", "/api/v1/resource-pools")
+def resource_pools(ctx: Ctx) -> Any:
+    p = ctx.m.pool
+    ag = p.agents[ctx.m.agent_id]
+    return {"resourcePools": [{"name": p.name, "description": "one 8xB200 node", "type": "RESOURCE_POOL_TYPE_STATIC", "numAgents": 1,
+                               "slotsAvailable": ag.num_slots, "slotsUsed": ag.num_used(), "slotType": "DEVICE_TYPE_CUDA" if ctx.m.num_gpus else "DEVICE_TYPE_CPU",
+                               "defaultComputePool": True, "defaultAuxPool": True, "preemptible": p.preemption, "schedulerType": "SCHEDULER_TYPE_" + p.scheduler.upper(),
+                               "schedulerFittingPolicy": "FITTING_POLICY_" + p.policy.upper(), "slotsPerAgent": ag.num_slots, "location": "on-prem", "auxContainerCapacity": 100,
+                               "auxContainersRunning": len(ag.zero_slot_tasks)}], "pagination": {"total": 1}}
+
+
+@route("GET", "/api/v1/job-queues-v2")
+@route("GET", "/api/v1/job-queues")
+def job_queue(ctx: Ctx) -> Any:
+    with ctx.m.lock:
+        rows = ctx.m.pool.job_queue()
+    jobs: Dict[str, Dict[str, Any]] = {}
+    for r in rows:
+        j = jobs.setdefault(r["job_id"], {"jobId": r["job_id"], "type": "TYPE_EXPERIMENT", "entityId": r["job_id"].replace("exp-", ""), "priority": r["priority"],
+                                          "weight": r["weight"], "allocatedSlots": 0, "requestedSlots": 0, "resourcePool": ctx.m.pool.name, "name": r["name"],
+                                          "summary": {"state": "STATE_QUEUED", "jobsAhead": 0}})
+        j["requestedSlots"] += r["slots"]
+        if r["state"] == "SCHEDULED":
+            j["allocatedSlots"] += r["slots"]
+            j["summary"]["state"] = "STATE_SCHEDULED"
+    return {"jobs": list(jobs.values()), "pagination": {"total": len(jobs)}}
+
+
+@route("POST", "/api/v1/job-queues")
+def update_job_queue(ctx: Ctx) -> Any:
+    with ctx.m.lock:
+        for u in (ctx.body or {}).get("updates", []):
+            jid = u.get("jobId")
+            if u.get("priority") is not None:
+                ctx.m.pool.set_priority(jid, int(u["priority"]))
+            if u.get("weight") is not None:
+                ctx.m.pool.set_weight(jid, float(u["weight"]))
+            for exp in ctx.m.experiments.values():
+                if exp.job_id == jid:
+                    if u.get("priority") is not None:
+                        exp.config.setdefault("resources", {})["priority"] = int(u["priority"])
+                    if u.get("weight") is not None:
+                        exp.config.setdefault("resources", {})["weight"] = float(u["weight"])
+    ctx.m.kick()
+    return {}
+
+
+# ---------------------------------------------------------------------------------------------
+# templates, model registry, workspaces / projects, webhooks
+# ---------------------------------------------------------------------------------------------
+@route("GET", "/api/v1/templates")
+def list_templates(ctx: Ctx) -> Any:
+    return {"templates": [{"name": r["name"], "config": dbmod.U(r["config"], {}), "workspaceId": r["workspace_id"]} for r in ctx.m.db.all("SELECT * FROM templates ORDER BY name")]}
+
+
+@route("GET", "/api/v1/templates/{name}")
+def get_template(ctx: Ctx, name: str) -> Any:
+    r = ctx.m.db.one("SELECT * FROM templates WHERE name=?", (name,))
+    if r is None:
+        raise HTTPError(404, "template not found")
+    return {"template": {"name": r["name"], "config": dbmod.U(r["config"], {}), "workspaceId": r["workspace_id"]}}
+
+
+@route("PUT", "/api/v1/templates/{name}")
+@route("POST", "/api/v1/templates/{name}")
+@route("PATCH", "/api/v1/templates/{name}")
+def put_template(ctx: Ctx, name: str) -> Any:
+    b = ctx.body or {}
+    cfg = b.get("config", b.get("template", {}).get("config", b))
+    if isinstance(cfg, str):
+        cfg = expconf.parse(cfg)
+    ctx.m.db.exec("INSERT INTO templates(name,config) VALUES(?,?) ON CONFLICT(name) DO UPDATE SET config=excluded.config", (name, dbmod.J(cfg)))
+    return {"template": {"name": name, "config": cfg}}
+
+
+@route("DELETE", "/api/v1/templates/{name}")
+def delete_template(ctx: Ctx, name: str) -> Any:
+    ctx.m.db.exec("DELETE FROM templates WHERE name=?", (name,))
+    return {}
+
+
+def _model_json(m: core.Master, r: Any) -> Dict[str, Any]:
+    n = m.db.one("SELECT COUNT(*) c FROM model_versions WHERE model_id=?", (r["id"],))["c"]
+    u = m.db.one("SELECT username FROM users WHERE id=?", (r["user_id"],))
+    return {"id": r["id"], "name": r["name"], "description": r["description"], "metadata": dbmod.U(r["metadata"], {}), "labels": dbmod.U(r["labels"], []),
+            "creationTime": _ts(r["creation_time"]), "lastUpdatedTime": _ts(r["last_updated_time"]), "numVersions": n, "username": u["username"] if u else None,
+            "userId": r["user_id"], "archived": bool(r["archived"]), "notes": r["notes"], "workspaceId": r["workspace_id"]}
+
+
+def _mv_json(m: core.Master, r: Any) -> Dict[str, Any]:
+    model = m.db.one("SELECT * FROM models WHERE id=?", (r["model_id"],))
+    ck = m.db.one("SELECT * FROM checkpoints WHERE uuid=?", (r["checkpoint_uuid"],))
+    return {"id": r["id"], "version": r["version"], "model": _model_json(m, model), "checkpoint": ckpt_json(m, ck) if ck is not None else {"uuid": r["checkpoint_uuid"]},
+            "name": r["name"], "comment": r["comment"], "metadata": dbmod.U(r["metadata"], {}), "labels": dbmod.U(r["labels"], []),
+            "creationTime": _ts(r["creation_time"]), "notes": r["notes"], "userId": r["user_id"]}
+
+
+def _model(ctx: Ctx, name: str) -> Any:
+    r = ctx.m.db.one("SELECT * FROM models WHERE name=? OR CAST(id AS TEXT)=?", (name, name))
+    if r is None:
+        raise HTTPError(404, f"model {name!r} not found")
+    return r
+
+
+@route("GET", "/api/v1/models")
+def list_models(ctx: Ctx) -> Any:
+    rows = [_model_json(ctx.m, r) for r in ctx.m.db.all("SELECT * FROM models ORDER BY id")]
+    if ctx.q("name"):
+        rows = [r for r in rows if ctx.q("name") in r["name"]]
+    items, pg = page(rows, ctx)
+    return {"models": items, "pagination": pg}
+
+
+@route("POST", "/api/v1/models")
+def create_model(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    try:
+        mid = ctx.m.db.exec("INSERT INTO models(name,description,metadata,labels,user_id,creation_time,last_updated_time,notes) VALUES(?,?,?,?,?,?,?,?)",
+                            (b.get("name"), b.get("description", ""), dbmod.J(b.get("metadata") or {}), dbmod.J(b.get("labels") or []), ctx.user["id"], time.time(), time.time(), b.get("notes", "")))
+    except Exception as e:
+        raise HTTPError(409, f"cannot create model: {e}")
+    return {"model": _model_json(ctx.m, ctx.m.db.one("SELECT * FROM models WHERE id=?", (mid,)))}
+
+
+@route("GET", "/api/v1/models/{name}")
+def get_model(ctx: Ctx, name: str) -> Any:
+    return {"model": _model_json(ctx.m, _model(ctx, urllib.parse.unquote(name)))}
+
+
+@route("PATCH", "/api/v1/models/{name}")
+def patch_model(ctx: Ctx, name: str) -> Any:
+    r = _model(ctx, urllib.parse.unquote(name))
+    b = (ctx.body or {}).get("model", ctx.body or {})
+    for col, key, enc in (("description", "description", None), ("metadata", "metadata", dbmod.J), ("labels", "labels", dbmod.J), ("notes", "notes", None), ("name", "name", None)):
+        if key in b and b[key] is not None:
+            ctx.m.db.exec(f"UPDATE models SET {col}=?, last_updated_time=? WHERE id=?", (enc(b[key]) if enc else b[key], time.time(), r["id"]))
+    return {"model": _model_json(ctx.m, ctx.m.db.one("SELECT * FROM models WHERE id=?", (r["id"],)))}
+
+
+@route("POST", "/api/v1/models/{name}/archive")
+def archive_model(ctx: Ctx, name: str) -> Any:
+    ctx.m.db.exec("UPDATE models SET archived=1 WHERE id=?", (_model(ctx, urllib.parse.unquote(name))["id"],))
+    return {}
+
+
+@route("POST", "/api/v1/models/{name}/unarchive")
+def unarchive_model(ctx: Ctx, name: str) -> Any:
+    ctx.m.db.exec("UPDATE models SET archived=0 WHERE id=?", (_model(ctx, urllib.parse.unquote(name))["id"],))
+    return {}
+
+
+@route("DELETE", "/api/v1/models/{name}")
+def delete_model(ctx: Ctx, name: str) -> Any:
+    r = _model(ctx, urllib.parse.unquote(name))
+    ctx.m.db.exec("DELETE FROM model_versions WHERE model_id=?", (r["id"],))
+    ctx.m.db.exec("DELETE FROM models WHERE id=?", (r["id"],))
+    return {}
+
+
+@route("GET", "/api/v1/models/{name}/versions")
+def list_model_versions(ctx: Ctx, name: str) -> Any:
+    r = _model(ctx, urllib.parse.unquote(name))
+    rows = ctx.m.db.all("SELECT * FROM model_versions WHERE model_id=? ORDER BY version", (r["id"],))
+    out = [_mv_json(ctx.m, v) for v in rows]
+    if ctx.q("orderBy") == "ORDER_BY_DESC":
+        out.reverse()
+    items, pg = page(out, ctx)
+    return {"model": _model_json(ctx.m, r), "modelVersions": items, "pagination": pg}
+
+
+@route("POST", "/api/v1/models/{name}/versions")
+def create_model_version(ctx: Ctx, name: str) -> Any:
+    r = _model(ctx, urllib.parse.unquote(name))
+    b = ctx.body or {}
+    if ctx.m.db.one("SELECT uuid FROM checkpoints WHERE uuid=?", (b.get("checkpointUuid"),)) is None:
+        raise HTTPError(404, f"checkpoint {b.get('checkpointUuid')} not found")
+    last = ctx.m.db.one("SELECT MAX(version) v FROM model_versions WHERE model_id=?", (r["id"],))["v"] or 0
+    vid = ctx.m.db.exec("INSERT INTO model_versions(model_id,version,checkpoint_uuid,name,comment,metadata,labels,user_id,creation_time,notes) VALUES(?,?,?,?,?,?,?,?,?,?)",
+                        (r["id"], last + 1, b["checkpointUuid"], b.get("name", ""), b.get("comment", ""), dbmod.J(b.get("metadata") or {}), dbmod.J(b.get("labels") or []),
+                         ctx.user["id"], time.time(), b.get("notes", "")))
+    ctx.m.db.exec("UPDATE models SET last_updated_time=? WHERE id=?", (time.time(), r["id"]))
+    return {"modelVersion": _mv_json(ctx.m, ctx.m.db.one("SELECT * FROM model_versions WHERE id=?", (vid,)))}
+
+
+@route("GET", "/api/v1/models/{name}/versions/{version}")
+def get_model_version(ctx: Ctx, name: str, version: str) -> Any:
+    r = _model(ctx, urllib.parse.unquote(name))
+    v = ctx.m.db.one("SELECT * FROM model_versions WHERE model_id=? AND version=?", (r["id"], int(version)))
+    if v is None:
+        raise HTTPError(404, "model version not found")
+    return {"modelVersion": _mv_json(ctx.m, v)}
+
+
+@route("DELETE", "/api/v1/models/{name}/versions/{version}")
+def delete_model_version(ctx: Ctx, name: str, version: str) -> Any:
+    r = _model(ctx, urllib.parse.unquote(name))
+    ctx.m.db.exec("DELETE FROM model_versions WHERE model_id=? AND version=?", (r["id"], int(version)))
+    return {}
+
+
+@route("GET", "/api/v1/workspaces")
+def list_workspaces(ctx: Ctx) -> Any:
+    rows = [{"id": r["id"], "name": r["name"], "archived": bool(r["archived"]), "immutable": bool(r["immutable"]), "userId": r["user_id"],
+             "numProjects": ctx.m.db.one("SELECT COUNT(*) c FROM projects WHERE workspace_id=?", (r["id"],))["c"]} for r in ctx.m.db.all("SELECT * FROM workspaces ORDER BY id")]
+    if ctx.q("name"):
+        rows = [r for r in rows if r["name"] == ctx.q("name")]
+    items, pg = page(rows, ctx)
+    return {"workspaces": items, "pagination": pg}
+
+
+@route("POST", "/api/v1/workspaces")
+def create_workspace(ctx: Ctx) -> Any:
+    try:
+        wid = ctx.m.db.exec("INSERT INTO workspaces(name,user_id) VALUES(?,?)", ((ctx.body or {}).get("name"), ctx.user["id"]))
+    except Exception as e:
+        raise HTTPError(409, f"cannot create workspace: {e}")
+    return {"workspace": {"id": wid, "name": (ctx.body or {}).get("name"), "archived": False, "immutable": False, "userId": ctx.user["id"], "numProjects": 0}}
+
+
+@route("GET", "/api/v1/workspaces/{wid}")
+def get_workspace(ctx: Ctx, wid: str) -> Any:
+    r = ctx.m.db.one("SELECT * FROM workspaces WHERE id=?", (int(wid),))
+    if r is None:
+        raise HTTPError(404, "workspace not found")
+    return {"workspace": {"id": r["id"], "name": r["name"], "archived": bool(r["archived"]), "immutable": bool(r["immutable"]), "userId": r["user_id"]}}
+
+
+@route("DELETE", "/api/v1/workspaces/{wid}")
+def delete_workspace(ctx: Ctx, wid: str) -> Any:
+    if int(wid) == 1:
+        raise HTTPError(400, "cannot delete the default workspace")
+    if ctx.m.db.one("SELECT id FROM experiments WHERE project_id IN (SELECT id FROM projects WHERE workspace_id=?)", (int(wid),)) is not None:
+        raise HTTPError(409, "workspace still has experiments")
+    ctx.m.db.exec("DELETE FROM projects WHERE workspace_id=?", (int(wid),))
+    ctx.m.db.exec("DELETE FROM workspaces WHERE id=?", (int(wid),))
+    return {"completed": True}
+
+
+@route("GET", "/api/v1/workspaces/{wid}/projects")
+def list_projects(ctx: Ctx, wid: str) -> Any:
+    rows = [{"id": r["id"], "name": r["name"], "workspaceId": r["workspace_id"], "description": r["description"], "archived": bool(r["archived"]),
+             "immutable": bool(r["immutable"]), "userId": r["user_id"], "notes": dbmod.U(r["notes"], []),
+             "numExperiments": ctx.m.db.one("SELECT COUNT(*) c FROM experiments WHERE project_id=?", (r["id"],))["c"]}
+            for r in ctx.m.db.all("SELECT * FROM projects WHERE workspace_id=? ORDER BY id", (int(wid),))]
+    items, pg = page(rows, ctx)
+    return {"projects": items, "pagination": pg}
+
+
+@route("POST", "/api/v1/workspaces/{wid}/projects")
+def create_project(ctx: Ctx, wid: str) -> Any:
+    b = ctx.body or {}
+    try:
+        pid = ctx.m.db.exec("INSERT INTO projects(name,workspace_id,description,user_id) VALUES(?,?,?,?)", (b.get("name"), int(wid), b.get("description", ""), ctx.user["id"]))
+    except Exception as e:
+        raise HTTPError(409, f"cannot create project: {e}")
+    return {"project": {"id": pid, "name": b.get("name"), "workspaceId": int(wid), "description": b.get("description", ""), "archived": False, "immutable": False,
+                        "userId": ctx.user["id"], "notes": [], "numExperiments": 0}}
+
+
+@route("GET", "/api/v1/projects/{pid}")
+def get_project(ctx: Ctx, pid: str) -> Any:
+    r = ctx.m.db.one("SELECT * FROM projects WHERE id=?", (int(pid),))
+    if r is None:
+        raise HTTPError(404, "project not found")
+    return {"project": {"id": r["id"], "name": r["name"], "workspaceId": r["workspace_id"], "description": r["description"], "archived": bool(r["archived"]),
+                        "immutable": bool(r["immutable"]), "userId": r["user_id"], "notes": dbmod.U(r["notes"], [])}}
+
+
+@route("DELETE", "/api/v1/projects/{pid}")
+def delete_project(ctx: Ctx, pid: str) -> Any:
+    if int(pid) == 1:
+        raise HTTPError(400, "cannot delete the default project")
+    if ctx.m.db.one("SELECT id FROM experiments WHERE project_id=?", (int(pid),)) is not None:
+        raise HTTPError(409, "project still has experiments")
+    ctx.m.db.exec("DELETE FROM projects WHERE id=?", (int(pid),))
+    return {"completed": True}
+
+
+@route("POST", "/api/v1/experiments/{eid}/move")
+def move_experiment(ctx: Ctx, eid: str) -> Any:
+    _exp_row(ctx, eid)
+    ctx.m.db.exec("UPDATE experiments SET project_id=? WHERE id=?", (int((ctx.body or {}).get("destinationProjectId", 1)), int(eid)))
+    return {}
+
+
+@route("GET", "/api/v1/webhooks")
+def list_webhooks(ctx: Ctx) -> Any:
+    return {"webhooks": [{"id": r["id"], "url": r["url"], "webhookType": r["webhook_type"], "triggers": dbmod.U(r["triggers"], [])} for r in ctx.m.db.all("SELECT * FROM webhooks")]}
+
+
+@route("POST", "/api/v1/webhooks")
+def create_webhook(ctx: Ctx) -> Any:
+    b = ctx.body or {}
+    wid = ctx.m.db.exec("INSERT INTO webhooks(url,webhook_type,triggers) VALUES(?,?,?)", (b.get("url"), b.get("webhookType", "WEBHOOK_TYPE_DEFAULT"), dbmod.J(b.get("triggers") or [])))
+    return {"webhook": {"id": wid, "url": b.get("url"), "webhookType": b.get("webhookType", "WEBHOOK_TYPE_DEFAULT"), "triggers": b.get("triggers") or []}}
+
+
+@route("DELETE", "/api/v1/webhooks/{wid}")
+def delete_webhook(ctx: Ctx, wid: str) -> Any:
+    ctx.m.db.exec("DELETE FROM webhooks WHERE id=?", (int(wid),))
+    return {}
+
+
+@route("GET", "/api/v1/tasks")
+def list_tasks(ctx: Ctx) -> Any:
+    return {"allocationIdToSummary": {a.id: {"taskId": a.trial.task_id, "allocationId": a.id, "name": f"trial {a.trial.id}", "slotsNeeded": a.slots,
+                                             "state": a.state, "resources": [{"agentDevices": {ctx.m.agent_id: {"devices": a.slot_ids}}}]} for a in ctx.m.allocations.values()}}
+
+
+@route("GET", "/metrics", auth_required=False)
+@route("GET", "/prom/det-state-metrics", auth_required=False)
+def prometheus(ctx: Ctx) -> Any:
+    """Prometheus text exposition (reference ``master/internal/prom``)."""
+    ag = ctx.m.pool.agents[ctx.m.agent_id]
+    lines = ["# TYPE det_slots_total gauge", f"det_slots_total {ag.num_slots}", "# TYPE det_slots_used gauge", f"det_slots_used {ag.num_used()}",
+             "# TYPE det_allocations_running gauge", f"det_allocations_running {len(ctx.m.allocations)}",
+             "# TYPE det_experiments_active gauge", f"det_experiments_active {sum(1 for e in ctx.m.experiments.values() if e.state == core.ACTIVE)}",
+             "# TYPE det_pending_requests gauge", f"det_pending_requests {len(ctx.m.pool.pending)}"]
+    return ("text/plain; version=0.0.4", "\n".join(lines) + "\n")
+
+
+# ---------------------------------------------------------------------------------------------
+# server
+# ---------------------------------------------------------------------------------------------
+class Handler(BaseHTTPRequestHandler):
+    protocol_version = "HTTP/1.1"
+    master: core.Master = None  # type: ignore
+
+    def log_message(self, fmt: str, *args: Any) -> None:
+        logger.debug("%s %s", self.address_string(), fmt % args)
+
+    def _user(self) -> Optional[Dict[str, Any]]:
+        h = self.headers.get("Authorization", "")
+        tok = h[7:] if h.startswith("Bearer ") else None
+        if not tok:
+            return None
+        r = self.master.db.one("SELECT s.token, s.expiry, u.* FROM sessions s JOIN users u ON u.id=s.user_id WHERE s.token=?", (tok,))
+        if r is None or (r["expiry"] or 0) < time.time() or not r["active"]:
+            return None
+        return {"id": r["id"], "username": r["username"], "admin": bool(r["admin"]), "token": tok}
+
+    def _send(self, status: int, payload: Any, ctype: str = "application/json") -> None:
+        if isinstance(payload, (dict, list)) or payload is None:
+            from determined_b200 import util
+
+            data = util.json_encode(payload if payload is not None else {}).encode()
+        elif isinstance(payload, str):
+            data = payload.encode()
+        else:
+            data = payload
+        self.send_response(status)
+        self.send_header("Content-Type", ctype)
+        self.send_header("Content-Length", str(len(data)))
+        self.end_headers()
+        try:
+            self.wfile.write(data)
+        except (BrokenPipeError, ConnectionResetError):
+            pass
+
+    def _dispatch(self, method: str) -> None:
+        u = urllib.parse.urlparse(self.path)
+        path = u.path
+        n = int(self.headers.get("Content-Length") or 0)
+        raw = self.rfile.read(n) if n else b""
+        body: Any = None
+        if raw:
+            try:
+                body = json.loads(raw)
+            except ValueError:
+                body = raw.decode(errors="replace")
+        for meth, rx, fn, need_auth in ROUTES:
+            if meth != method:
+                continue
+            mt = rx.match(path)
+            if mt is None:
+                continue
+            user = self._user()
+            if need_auth and user is None:
+                self._send(401, {"error": {"code": 16, "message": "unauthenticated"}, "message": "unauthenticated"})
+                return
+            ctx = Ctx(self.master, user, urllib.parse.parse_qs(u.query), body, raw)
+            try:
+                out = fn(ctx, **{k: urllib.parse.unquote(v) for k, v in mt.groupdict().items()})
+                if isinstance(out, tuple):
+                    self._send(200, out[1], out[0])
+                else:
+                    self._send(200, out)
+            except HTTPError as e:
+                self._send(e.status, {"error": {"code": e.status, "message": e.message}, "message": e.message})
+            except core.NotFound as e:
+                self._send(404, {"error": {"code": 5, "message": str(e)}, "message": str(e)})
+            except expconf.ConfigError as e:
+                self._send(400, {"error": {"code": 3, "message": str(e)}, "message": str(e)})
+            except Exception as e:  # noqa
+                logger.exception("handler for %s %s failed", method, path)
+                self._send(500, {"error": {"code": 13, "message": f"{type(e).__name__}: {e}"}, "message": f"{type(e).__name__}: {e}"})
+            return
+        self._send(404, {"error": {"code": 5, "message": f"no route for {method} {path}"}, "message": f"no route for {method} {path}"})
+
+    def do_GET(self) -> None:
+        self._dispatch("GET")
+
+    def do_POST(self) -> None:
+        self._dispatch("POST")
+
+    def do_PATCH(self) -> None:
+        self._dispatch("PATCH")
+
+    def do_PUT(self) -> None:
+        self._dispatch("PUT")
+
+    def do_DELETE(self) -> None:
+        self._dispatch("DELETE")
+
+
+class APIServer:
+    def __init__(self, master: core.Master, host: str = "127.0.0.1", port: int = 8080) -> None:
+        handler = type("BoundHandler", (Handler,), {"master": master})
+        self.httpd = ThreadingHTTPServer((host, port), handler)
+        self.httpd.daemon_threads = True
+        master.host, master.port = host, self.httpd.server_address[1]
+        self.thread: Optional[threading.Thread] = None
+
+    @property
+    def port(self) -> int:
+        return self.httpd.server_address[1]
+
+    def start(self) -> "APIServer":
+        self.thread = threading.Thread(target=self.httpd.serve_forever, daemon=True, name="api-server")
+        self.thread.start()
+        return self
+
+    def stop(self) -> None:
+        self.httpd.shutdown()
+        self.httpd.server_close()

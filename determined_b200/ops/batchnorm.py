@@ -1,0 +1,110 @@
+"""Fused channels-last BatchNorm2d (native: ``csrc/batchnorm.cu``).
+
+``convert_batchnorm_(model)`` re-classes every eligible ``nn.BatchNorm2d`` in place into
+:class:`FusedBatchNorm2d` (same parameters/buffers/state-dict keys, so checkpoints remain
+interchangeable with the reference's).  The harness calls it from ``context.wrap_model`` when the
+fused engine is on.  Inputs that are not channels-last CUDA tensors of a supported width fall back
+to ``F.batch_norm`` for that call.
+"""
+from typing import Any, Optional, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from determined_b200.ops import _lib
+
+_WS = {}
+
+
+def _workspace(device: torch.device, C: int) -> torch.Tensor:
+    # one workspace per (device, stream): kernels of different streams must not share the ticket
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream, C)
+    ws = _WS.get(key)
+    if ws is None:
+        lib = _lib.load()
+        ws = torch.zeros(int(lib.detb200_bn_workspace_bytes(C)), dtype=torch.uint8, device=device)
+        _WS[key] = ws
+    return ws
+
+
+def _eligible(x: torch.Tensor) -> bool:
+    if not (x.is_cuda and x.dim() == 4 and x.dtype in (torch.float32, torch.bfloat16)):
+        return False
+    C = x.shape[1]
+    V = 8 if x.dtype == torch.bfloat16 else 4
+    if C % V or (C // V) > 256 or 256 % (C // V):
+        return False
+    return x.is_contiguous(memory_format=torch.channels_last) and x.numel() > 0
+
+
+class _BNTrainFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx: Any, x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[torch.Tensor],
+                running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
+                nbt: Optional[torch.Tensor], momentum: float, eps: float) -> torch.Tensor:
+        lib = _lib.load()
+        N, C, H, W = x.shape
+        M = N * H * W
+        y = torch.empty_like(x, memory_format=torch.channels_last)
+        stats = torch.empty(4, C, dtype=torch.float32, device=x.device)   # mean, invstd, scale, shift
+        w = weight.float() if weight is not None and weight.dtype != torch.float32 else weight
+        b = bias.float() if bias is not None and bias.dtype != torch.float32 else bias
+        _lib.check(lib.detb200_bn_fwd_train(
+            x.data_ptr(), y.data_ptr(), M, C, _lib.ptr(w), _lib.ptr(b), _lib.ptr(running_mean), _lib.ptr(running_var),
+            _lib.ptr(nbt), stats[0].data_ptr(), stats[1].data_ptr(), stats[2].data_ptr(), stats[3].data_ptr(),
+            float(momentum), float(eps), 0, _workspace(x.device, C).data_ptr(), _lib.dtype_code(x.dtype),
+            _lib.stream_ptr()), "bn_fwd_train")
+        ctx.save_for_backward(x, w, stats)
+        ctx.has_w, ctx.has_b = weight is not None, bias is not None
+        ctx.wdtype = weight.dtype if weight is not None else None
+        ctx.bdtype = bias.dtype if bias is not None else None
+        ctx.mark_non_differentiable(*(t for t in (running_mean, running_var, nbt) if t is not None))
+        return y
+
+    @staticmethod
+    def backward(ctx: Any, dy: torch.Tensor) -> Tuple[Any, ...]:
+        lib = _lib.load()
+        x, w, stats = ctx.saved_tensors
+        N, C, H, W = x.shape
+        M = N * H * W
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        grads = torch.empty(5, C, dtype=torch.float32, device=x.device)   # dgamma, dbeta, coef[3]
+        _lib.check(lib.detb200_bn_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), M, C, _lib.ptr(w),
+                                      stats[0].data_ptr(), stats[1].data_ptr(), grads[0].data_ptr(),
+                                      grads[1].data_ptr(), grads[2].data_ptr(), _workspace(x.device, C).data_ptr(),
+                                      _lib.dtype_code(x.dtype), _lib.stream_ptr()), "bn_bwd")
+        dw = grads[0].to(ctx.wdtype) if ctx.has_w else None
+        db = grads[1].to(ctx.bdtype) if ctx.has_b else None
+        return dx, dw, db, None, None, None, None, None
+
+
+def batch_norm_train(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[torch.Tensor],
+                     running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
+                     num_batches_tracked: Optional[torch.Tensor], momentum: float, eps: float) -> torch.Tensor:
+    return _BNTrainFn.apply(x, weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps)
+
+
+class FusedBatchNorm2d(nn.BatchNorm2d):
+    """Drop-in ``nn.BatchNorm2d`` whose training forward/backward run the native kernels."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if (self.training and self.momentum is not None and self.track_running_stats and _eligible(x)
+                and self.running_mean is not None and self.running_mean.dtype == torch.float32):
+            return batch_norm_train(x, self.weight, self.bias, self.running_mean, self.running_var,
+                                    self.num_batches_tracked, self.momentum, self.eps)
+        return super().forward(x)
+
+
+def convert_batchnorm_(model: nn.Module) -> int:
+    """Re-class eligible BatchNorm2d modules in place; returns how many were converted."""
+    n = 0
+    for m in model.modules():
+        if type(m) is nn.BatchNorm2d and m.track_running_stats and m.momentum is not None:
+            m.__class__ = FusedBatchNorm2d
+            n += 1
+    return n

@@ -214,6 +214,14 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
         if self._use_apex:
             raise errors.InvalidExperimentException("Must call wrap_model() before configure_apex_amp.")
         model = model.to(self.device)
+        if self.device.type == "cuda" and self.experimental._fused_engine is not False:
+            # module-level fusion pass of the B200 engine: hot library ops whose ATen kernels are far
+            # off the HBM roofline are swapped for native ones (same parameters / state-dict keys)
+            from determined_b200.ops import batchnorm
+
+            n = batchnorm.convert_batchnorm_(model)
+            if n:
+                logger.info("fused engine: %d BatchNorm2d modules now run the native channels-last kernels", n)
         if self.experimental._auto_amp:
             model = self.autocast_forward_pass(model)
         self.models.append(model)

@@ -115,6 +115,23 @@ int detb200_norm_bwd(const void* dy, const void* x, const void* gamma, const flo
                      int dtype, int rms, detb200_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * BatchNorm, channels-last [M = N*H*W, C] (csrc/batchnorm.cu).  Reference: nn.BatchNorm2d in the user's
+ * model reaches ATen batch_norm_{collect_statistics,transform_input,backward_reduce,backward_elemt}
+ * _channels_last kernels.  C must be a multiple of 8 (bf16) / 4 (fp32) with C/vec dividing 256.
+ * `workspace`: detb200_bn_workspace_bytes(C) bytes, zero-initialised once, one stream at a time.
+ * ------------------------------------------------------------------------------------------- */
+int64_t detb200_bn_workspace_bytes(int C);
+int detb200_bn_fwd_train(const void* x, void* y, int64_t M, int C, const float* gamma, const float* beta,
+                         float* running_mean, float* running_var, long long* num_batches_tracked,
+                         float* mean, float* invstd, float* scale, float* shift, float momentum, float eps,
+                         int relu, void* workspace, int dtype, detb200_stream_t stream);
+int detb200_bn_apply(const void* x, void* y, int64_t M, int C, const float* scale, const float* shift, int relu,
+                     int dtype, detb200_stream_t stream);
+int detb200_bn_bwd(const void* dy, const void* x, void* dx /* may alias dy */, int64_t M, int C, const float* gamma,
+                   const float* mean, const float* invstd, float* dgamma, float* dbeta, float* coef /* 3*C */,
+                   void* workspace, int dtype, detb200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Softmax cross-entropy (csrc/xent.cu).  Reference: log_softmax + nll_loss in
  * examples/tutorials/mnist_pytorch/model.py:34, train.py:43 and the HF/NeoX LM losses.
  * ------------------------------------------------------------------------------------------- */

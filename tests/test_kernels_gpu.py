@@ -216,3 +216,41 @@ def test_resnet_step_fused_vs_torch():
             torch.testing.assert_close(loss, rl, rtol=1e-3, atol=1e-3)
         for a, b in zip(model.parameters(), ref_model.parameters()):
             torch.testing.assert_close(a, b, rtol=5e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(4, 64, 8, 8), (32, 128, 16, 16), (7, 512, 4, 4), (256, 64, 32, 32), (3, 8, 5, 7)])
+def test_batchnorm_train_fwd_bwd(dtype, shape):
+    from determined_b200.ops import batchnorm
+
+    torch.manual_seed(4)
+    dev = torch.device("cuda")
+    N, C, H, W = shape
+    x = (torch.randn(shape, device=dev) * 2 + 0.7).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_()
+    ref = torch.nn.BatchNorm2d(C).to(dev)
+    with torch.no_grad():
+        ref.weight.uniform_(0.5, 1.5)
+        ref.bias.uniform_(-0.5, 0.5)
+    import copy
+
+    mine = copy.deepcopy(ref)
+    assert batchnorm.convert_batchnorm_(mine) == 1
+    dy = torch.randn(shape, device=dev).to(dtype).contiguous(memory_format=torch.channels_last)
+    xr = x.detach().float().requires_grad_()
+    for _ in range(2):   # twice: running stats accumulate and the workspace ticket must re-arm
+        y = mine(x)
+        yr = ref(xr)
+    y.backward(dy)
+    yr.backward(dy.float())
+    tol = dict(rtol=2e-2, atol=3e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(y.float(), yr, **tol)
+    torch.testing.assert_close(x.grad.float(), xr.grad, **tol)
+    gtol = dict(rtol=3e-2, atol=0.05 * (N * H * W) ** 0.5) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(mine.weight.grad, ref.weight.grad, **gtol)
+    torch.testing.assert_close(mine.bias.grad, ref.bias.grad, **gtol)
+    torch.testing.assert_close(mine.running_mean, ref.running_mean, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(mine.running_var, ref.running_var, rtol=1e-3, atol=1e-3)
+    assert int(mine.num_batches_tracked) == int(ref.num_batches_tracked) == 2
+    # eval mode goes through the stock path and must agree exactly
+    mine.eval(); ref.eval()
+    torch.testing.assert_close(mine(x.detach().float()), ref(x.detach().float()), rtol=1e-4, atol=1e-4)
