@@ -59,7 +59,7 @@ template <typename T, int K, int NT, typename Load, typename Accum>
 __device__ __forceinline__ bool column_reduce(int64_t M, int C, float* __restrict__ part,
                                               unsigned int* __restrict__ ticket, Load load, Accum accum) {
   constexpr int V = Vec<T>::N;
-  constexpr int kU = 4;
+  constexpr int kU = 8;
   extern __shared__ float smem[];   // [ty][K*V*cthreads]
   const int cthreads = C / V;
   const int ty_n = kBT / cthreads;
@@ -122,54 +122,43 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, float* __restrict__ p
         for (int j = 0; j < V; ++j) { acc[0][j] += regs[0][j]; acc[1][j] = fmaf(regs[0][j], regs[0][j], acc[1][j]); }
       });
   if (!last) return;
-  // ---- final merge in the last CTA: Chan's parallel variance over the per-CTA partials.
-  // Thread t handles channel c = t % Cc and every G-th CTA (g = t / Cc), then the G partial
-  // results are merged through shared memory.  Rows seen by CTA b: ty_n per full sweep plus its
-  // share of the remainder (loop-invariant pieces hoisted: no 64-bit division inside the loop).
+  // ---- final merge in the last CTA.  Per-CTA partial sums are fp32 over <= a few thousand
+  // elements (accurate); the cross-CTA totals are accumulated in fp64 so var = E[x^2]-E[x]^2 has no
+  // cancellation problem and the loop is a plain, pipelinable sum (no dependent divide chain).
+  // Thread t handles channel c = t % Cc and every G-th CTA; the G partial sums meet in smem.
   extern __shared__ float smem[];
-  const int ty_n = kBT / (C / V);
-  const int64_t sweep = (int64_t)gridDim.x * ty_n;
-  const int full_rows = (int)(M / sweep) * ty_n;
-  const int rem = (int)(M % sweep);
+  double* dsm = reinterpret_cast<double*>(smem);
   const int Cc = C < kBT ? C : kBT;
   const int G = kBT / Cc;
   const int g = threadIdx.x / Cc;
+  const int nblk = (int)gridDim.x;
   for (int cbase = 0; cbase < C; cbase += Cc) {
     const int c = cbase + threadIdx.x % Cc;
-    float n = 0.f, mean = 0.f, m2 = 0.f;
-    for (int b = g; b < (int)gridDim.x; b += G) {
-      int lo = b * ty_n;
-      int extra = rem - lo;
-      extra = extra < 0 ? 0 : (extra > ty_n ? ty_n : extra);
-      float fb = (float)(full_rows + extra);
-      if (fb == 0.f) continue;
-      float sv = __ldcg(part + (int64_t)b * 2 * C + c);
-      float q = __ldcg(part + (int64_t)b * 2 * C + C + c);
-      float mb = sv / fb;
-      float m2b = fmaxf(q - sv * mb, 0.f);
-      float d = mb - mean;
-      float tot = n + fb;
-      mean += d * (fb / tot);
-      m2 += m2b + d * d * (n * fb / tot);
-      n = tot;
+    double s0 = 0.0, s1 = 0.0;
+    int b = g;
+    for (; b + 3 * G < nblk; b += 4 * G) {
+      float a0 = __ldcg(part + (int64_t)b * 2 * C + c), q0 = __ldcg(part + (int64_t)b * 2 * C + C + c);
+      float a1 = __ldcg(part + (int64_t)(b + G) * 2 * C + c), q1 = __ldcg(part + (int64_t)(b + G) * 2 * C + C + c);
+      float a2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + c), q2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + C + c);
+      float a3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + c), q3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + C + c);
+      s0 += ((double)a0 + (double)a1) + ((double)a2 + (double)a3);
+      s1 += ((double)q0 + (double)q1) + ((double)q2 + (double)q3);
+    }
+    for (; b < nblk; b += G) {
+      s0 += (double)__ldcg(part + (int64_t)b * 2 * C + c);
+      s1 += (double)__ldcg(part + (int64_t)b * 2 * C + C + c);
     }
     __syncthreads();
-    smem[(g * Cc + threadIdx.x % Cc) * 3 + 0] = n;
-    smem[(g * Cc + threadIdx.x % Cc) * 3 + 1] = mean;
-    smem[(g * Cc + threadIdx.x % Cc) * 3 + 2] = m2;
+    dsm[(g * Cc + threadIdx.x % Cc) * 2 + 0] = s0;
+    dsm[(g * Cc + threadIdx.x % Cc) * 2 + 1] = s1;
     __syncthreads();
     if (g == 0) {
-      for (int k = 1; k < G; ++k) {
-        float fb = smem[(k * Cc + threadIdx.x) * 3 + 0];
-        if (fb == 0.f) continue;
-        float mb = smem[(k * Cc + threadIdx.x) * 3 + 1], m2b = smem[(k * Cc + threadIdx.x) * 3 + 2];
-        float d = mb - mean;
-        float tot = n + fb;
-        mean += d * (fb / tot);
-        m2 += m2b + d * d * (n * fb / tot);
-        n = tot;
-      }
-      float var = m2 / n;
+      for (int k = 1; k < G; ++k) { s0 += dsm[(k * Cc + threadIdx.x) * 2]; s1 += dsm[(k * Cc + threadIdx.x) * 2 + 1]; }
+      const double n = (double)M;
+      const double mean_d = s0 / n;
+      double var_d = s1 / n - mean_d * mean_d;
+      if (var_d < 0.0) var_d = 0.0;
+      const float mean = (float)mean_d, var = (float)var_d;
       float inv = rsqrtf(var + p.eps);
       p.mean[c] = mean;
       p.invstd[c] = inv;
@@ -177,7 +166,7 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, float* __restrict__ p
       p.scale[c] = gm * inv;
       p.shift[c] = bta - mean * gm * inv;
       if (p.running_mean) {
-        float unbiased = n > 1.f ? m2 / (n - 1.f) : var;
+        float unbiased = M > 1 ? (float)(var_d * n / (n - 1.0)) : var;
         p.running_mean[c] = (1.f - p.momentum) * p.running_mean[c] + p.momentum * mean;
         p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * unbiased;
       }
@@ -240,9 +229,21 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
   for (int cbase = 0; cbase < C; cbase += Cc) {
     const int c = cbase + threadIdx.x % Cc;
     float s0 = 0.f, s1 = 0.f;
-    for (int b = g; b < (int)gridDim.x; b += G) {
-      s0 += __ldcg(part + (int64_t)b * 2 * C + c);
-      s1 += __ldcg(part + (int64_t)b * 2 * C + C + c);
+    {
+      const int nblk = (int)gridDim.x;
+      int b = g;
+      for (; b + 3 * G < nblk; b += 4 * G) {
+        float a0 = __ldcg(part + (int64_t)b * 2 * C + c), q0 = __ldcg(part + (int64_t)b * 2 * C + C + c);
+        float a1 = __ldcg(part + (int64_t)(b + G) * 2 * C + c), q1 = __ldcg(part + (int64_t)(b + G) * 2 * C + C + c);
+        float a2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + c), q2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + C + c);
+        float a3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + c), q3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + C + c);
+        s0 += (a0 + a1) + (a2 + a3);
+        s1 += (q0 + q1) + (q2 + q3);
+      }
+      for (; b < nblk; b += G) {
+        s0 += __ldcg(part + (int64_t)b * 2 * C + c);
+        s1 += __ldcg(part + (int64_t)b * 2 * C + C + c);
+      }
     }
     __syncthreads();
     smem[(g * Cc + threadIdx.x % Cc) * 2 + 0] = s0;
@@ -284,8 +285,9 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __rest
 
 inline int reduce_grid(int64_t M, int C, int V) {
   int ty_n = kBT / (C / V);
-  int64_t g = (M + (int64_t)ty_n * 16 - 1) / ((int64_t)ty_n * 16);
+  int64_t g = (M + (int64_t)ty_n * 32 - 1) / ((int64_t)ty_n * 32);
   if (g > 4 * kNumSMs) g = 4 * kNumSMs;
+  if (g > 32768 / C) g = 32768 / C;   // bounds the serial final merge: <= 128 partial loads per thread
   if (g < 1) g = 1;
   return (int)g;
 }

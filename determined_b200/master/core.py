@@ -559,6 +559,12 @@ class Master:
                 exp = self._hydrate(row)
                 self.experiments[exp.id] = exp
                 logger.info("restored experiment %d (%s) with %d trials", exp.id, exp.state, len(exp.trials))
+                # processes died with the old master: trials that only waited for their allocation
+                # to exit before closing can close now
+                queue: List[Any] = []
+                for t in list(exp.trials.values()):
+                    exp._maybe_finish_trial(t, queue)
+                exp.process_operations(queue)
             except Exception as e:
                 logger.error("failed to restore experiment %s: %s", row["id"], e)
                 self.db.exec("UPDATE experiments SET state='ERROR', end_time=? WHERE id=?", (time.time(), row["id"]))

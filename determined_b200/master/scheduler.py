@@ -179,7 +179,8 @@ def _order(reqs: Sequence[AllocateRequest]) -> List[AllocateRequest]:
 
 
 def priority_schedule(pending: Sequence[AllocateRequest], running: Dict[str, AllocateRequest],
-                      agents: Dict[str, Agent], policy: str = "best", preemption: bool = True) -> Decision:
+                      agents: Dict[str, Agent], policy: str = "best", preemption: bool = True,
+                      already_releasing: Optional[Set[str]] = None) -> Decision:
     """Strict priority (lower value first), FIFO within a priority.  When a request does not fit:
     lower-priority *preemptible* running tasks are preempted (lowest priority, newest first) if
     that makes it fit; while anything is waiting, lower priorities may only back-fill with
@@ -187,6 +188,12 @@ def priority_schedule(pending: Sequence[AllocateRequest], running: Dict[str, All
     d = Decision()
     local = _clone_agents(agents)
     usage = _job_usage(running)
+    # Tasks that were told to stop on an earlier tick still hold their slots: plan as if those
+    # slots were free (so the waiting high-priority task reserves them and nothing lower can
+    # sneak in); ResourcePool.tick() refuses any placement that touches a slot not yet vacated.
+    prior = set(already_releasing or ())
+    for rid in prior:
+        remove_allocation(local, rid)
     releasing: Set[str] = set()
     backfilling = False
     for prio in sorted({r.prio() for r in pending}):
@@ -198,15 +205,12 @@ def priority_schedule(pending: Sequence[AllocateRequest], running: Dict[str, All
             if asg is None:
                 unfit.append(req)
                 continue
-            if not releasing and (not backfilling or (preemption and req.preemptible)):
+            apply_assignment(local, req.allocation_id, asg)    # reserve: lower priorities cannot take it
+            if not backfilling or (preemption and req.preemptible):
                 if backfilling:
                     req.backfilled = True
-                apply_assignment(local, req.allocation_id, asg)
                 usage[req.job_id] = usage.get(req.job_id, 0) + req.slots_needed
                 d.to_allocate.append((req, asg))
-            else:
-                # reserve the capacity so later (lower) priorities cannot take it
-                apply_assignment(local, req.allocation_id, asg)
         if unfit:
             backfilling = True
         if not preemption:
@@ -217,7 +221,8 @@ def priority_schedule(pending: Sequence[AllocateRequest], running: Dict[str, All
                 apply_assignment(local, req.allocation_id, find_fit(req, local, policy) or {})
                 continue
             victims = sorted((r for r in running.values()
-                              if r.preemptible and r.prio() > prio and r.allocation_id not in releasing),
+                              if r.preemptible and r.prio() > prio and r.allocation_id not in releasing
+                              and r.allocation_id not in prior),
                              key=lambda r: (-r.prio(), -r.submit_time))
             trial = _clone_agents(local)
             chosen: List[str] = []
@@ -413,7 +418,7 @@ class ResourcePool:
         pend = list(self.pending.values())
         run = {k: v for k, v in self.running.items() if k not in self.releasing}
         if self.scheduler == "priority":
-            d = priority_schedule(pend, run, self.agents, self.policy, self.preemption)
+            d = priority_schedule(pend, run, self.agents, self.policy, self.preemption, set(self.releasing))
         elif self.scheduler == "round_robin":
             d = round_robin_schedule(pend, run, self.agents, self.policy)
         else:

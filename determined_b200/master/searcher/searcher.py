@@ -174,7 +174,9 @@ def simulate(searcher_cfg: Dict[str, Any], hparams: Dict[str, Any], seed: int = 
                 if reason is not None:
                     t["closed"] = True
                     t["exited"] = reason
+                    queues[rid].clear()
                     absorb(s.trial_exited_early(rid, reason))
+                    absorb(s.trial_closed(rid))      # the experiment closes an exited trial
                 else:
                     s.set_trial_progress(rid, float(t["trained"]))
                     absorb(s.validation_completed(rid, metric_fn(t["hparams"], t["trained"]), op))
