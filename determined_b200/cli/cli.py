@@ -1,0 +1,802 @@
+"""``det`` — command line interface.
+
+Parity: reference ``harness/determined/cli`` (argparse tree ``cli/cli.py:110-186``): ``experiment``
+(``create [--local --test] [--paused] [-f] [--config k=v] [--template]``, list, describe, pause,
+activate, cancel, kill, logs, download, set, archive, delete, label — ``cli/experiment.py``),
+``trial``, ``checkpoint`` (list/describe/download/delete/rm — ``cli/checkpoint.py:158-243``),
+``model``, ``template``, ``user``, ``agent``/``slot``, ``job``, ``resource-pool``, ``master``,
+``workspace``/``project``, ``preview-search``, ``deploy local``, ``version``.
+"""
+import argparse
+import json
+import os
+import pathlib
+import sys
+import time
+from typing import Any, Dict, List, Optional, Sequence
+
+import yaml
+
+import determined_b200 as det
+from determined_b200.common import api, context as det_context
+from determined_b200.experimental import client as sdk
+
+
+def _table(rows: List[Sequence[Any]], headers: Sequence[str], as_json: bool = False, as_csv: bool = False) -> None:
+    if as_json:
+        print(json.dumps([dict(zip(headers, r)) for r in rows], indent=2, default=str))
+        return
+    if as_csv:
+        import csv
+
+        w = csv.writer(sys.stdout)
+        w.writerow(headers)
+        w.writerows(rows)
+        return
+    try:
+        import tabulate
+
+        print(tabulate.tabulate(rows, headers=headers, tablefmt="presto"))
+    except ImportError:
+        print(" | ".join(headers))
+        for r in rows:
+            print(" | ".join(str(x) for x in r))
+
+
+def _session(args: argparse.Namespace) -> api.Session:
+    master = args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
+    return api.authentication.login_with_cache(master, args.user, None)
+
+
+def _sdk(args: argparse.Namespace) -> sdk.Determined:
+    return sdk.Determined._from_session(_session(args))
+
+
+def _parse_config_overrides(cfg: Dict[str, Any], overrides: Optional[List[str]]) -> None:
+    from determined_b200.master import expconf
+
+    for ov in overrides or []:
+        if "=" not in ov:
+            raise SystemExit(f"--config expects key=value, got {ov!r}")
+        k, v = ov.split("=", 1)
+        expconf.apply_override(cfg, k, yaml.safe_load(v))
+
+
+# ------------------------------------------------------------------------------------------------
+# experiment
+# ------------------------------------------------------------------------------------------------
+def _follow_trial_logs(sess: api.Session, eid: int) -> int:
+    d = sdk.Determined._from_session(sess)
+    exp = d.get_experiment(eid)
+    print(f"Waiting for first trial of experiment {eid}...")
+    t = exp.await_first_trial()
+    print(f"Following logs of trial {t.id}")
+    for line in t.logs(follow=True):
+        sys.stdout.write(line)
+    exp.reload()
+    print(f"Experiment {eid}: {exp.state.value if exp.state else '?'}")
+    return 0 if exp.state == sdk.ExperimentState.COMPLETED else 1
+
+
+def _run_local(cfg: Dict[str, Any], model_dir: str, test: bool) -> int:
+    """``det e create --local --test``: run the trial in this process, off-cluster (reference
+    ``_execution.py:77-236`` test/local mode)."""
+    from determined_b200 import load, pytorch
+
+    entry = cfg.get("entrypoint")
+    if not isinstance(entry, str) or ":" not in entry or " " in entry:
+        raise SystemExit("--local requires a legacy `module:TrialClass` entrypoint")
+    os.chdir(model_dir)
+    sys.path.insert(0, os.getcwd())
+    hparams = {}
+    from determined_b200.master import nprand
+    from determined_b200.master.searcher import hparams as hp
+
+    hparams = hp.sample_all(cfg.get("hyperparameters") or {}, nprand.State(int(time.time())))
+    trial_cls = load.trial_class_from_entrypoint(entry)
+    agg = int((cfg.get("optimizations") or {}).get("aggregation_frequency", 1))
+    with pytorch.init(hparams=hparams, exp_conf=cfg, aggregation_frequency=agg) as ctx:
+        trial = trial_cls(ctx)
+        tr = pytorch.Trainer(trial, ctx)
+        if test:
+            tr.fit(test_mode=True)
+        else:
+            ml = (cfg.get("searcher") or {}).get("max_length", {"batches": 100})
+            ml = ml if isinstance(ml, dict) else {"batches": ml}
+            tr.fit(max_length=pytorch.TrainUnit._from_values(**ml, global_batch_size=ctx._global_batch_size),
+                   reporting_period=pytorch.Batch(int(cfg.get("scheduling_unit", 100))))
+    print("Model training test succeeded." if test else "Local training finished.")
+    return 0
+
+
+def experiment_create(args: argparse.Namespace) -> int:
+    cfg_text = pathlib.Path(args.config_file).read_text()
+    cfg = yaml.safe_load(cfg_text) or {}
+    _parse_config_overrides(cfg, args.config)
+    if args.local:
+        return _run_local(cfg, args.model_def, args.test)
+    sess = _session(args)
+    files = det_context.read_v1_context(pathlib.Path(args.model_def)) if args.model_def else []
+    for inc in args.include or []:
+        files += det_context.read_v1_context(pathlib.Path(inc))
+    body = {"config": yaml.safe_dump(cfg), "modelDefinition": files, "activate": not args.paused, "template": args.template,
+            "projectId": args.project_id, "validateOnly": bool(args.test and not args.local and False)}
+    r = sess.post("/api/v1/experiments", json=body).json()
+    eid = r["experiment"]["id"]
+    print(f"Created experiment {eid}")
+    if args.publish:
+        pass
+    if args.follow_first_trial and not args.paused:
+        return _follow_trial_logs(sess, eid)
+    return 0
+
+
+def experiment_list(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    params: Dict[str, Any] = {}
+    if not args.all:
+        params["archived"] = "false"
+    exps = sess.get("/api/v1/experiments", params=params).json()["experiments"]
+    rows = [[e["id"], e["username"], e["name"], e["parentId"], e["state"].replace("STATE_", ""), f"{100 * (e['progress'] or 0):.1f}%",
+             e["startTime"], e["endTime"], e["resourcePool"]] for e in exps]
+    _table(rows, ["ID", "Owner", "Name", "Parent ID", "State", "Progress", "Started", "Ended", "Resource Pool"], args.json, args.csv)
+    return 0
+
+
+def experiment_describe(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    out = []
+    for eid in args.experiment_ids.split(","):
+        e = sess.get(f"/api/v1/experiments/{int(eid)}").json()["experiment"]
+        trials = sess.get(f"/api/v1/experiments/{int(eid)}/trials").json()["trials"]
+        e["trials"] = trials
+        out.append(e)
+    if args.json:
+        print(json.dumps(out, indent=2, default=str))
+        return 0
+    _table([[e["id"], e["state"].replace("STATE_", ""), f"{100 * (e['progress'] or 0):.1f}%", e["startTime"], e["endTime"], e["name"], e["description"],
+             e["archived"], e["resourcePool"], ", ".join(e["labels"] or [])] for e in out],
+           ["Experiment ID", "State", "Progress", "Started", "Ended", "Name", "Description", "Archived", "Resource Pool", "Labels"])
+    print()
+    _table([[t["id"], t["experimentId"], t["state"].replace("STATE_", ""), t["startTime"], t["endTime"], json.dumps(t["hparams"], separators=(",", ":")),
+             t["totalBatchesProcessed"], t["restarts"]] for e in out for t in e["trials"]],
+           ["Trial ID", "Experiment ID", "State", "Started", "Ended", "H-Params", "Batches", "Restarts"])
+    return 0
+
+
+def _exp_action(name: str) -> Any:
+    def fn(args: argparse.Namespace) -> int:
+        _session(args).post(f"/api/v1/experiments/{args.experiment_id}/{name}")
+        print(f"{name.capitalize()}d experiment {args.experiment_id}" if not name.endswith("e") else f"{name.capitalize()}d experiment {args.experiment_id}")
+        return 0
+    return fn
+
+
+def experiment_delete(args: argparse.Namespace) -> int:
+    if not args.yes:
+        if input(f"Delete experiment {args.experiment_id} and all its checkpoints? [y/N] ").strip().lower() not in ("y", "yes"):
+            return 1
+    _session(args).delete(f"/api/v1/experiments/{args.experiment_id}")
+    print(f"Deleted experiment {args.experiment_id}")
+    return 0
+
+
+def experiment_logs(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    trials = sess.get(f"/api/v1/experiments/{args.experiment_id}/trials").json()["trials"]
+    if not trials:
+        raise SystemExit("experiment has no trials yet")
+    t = sdk.Trial(sess, trials[0]["id"], trials[0])
+    for line in t.logs(follow=args.follow, head=args.head, tail=args.tail):
+        sys.stdout.write(line)
+    return 0
+
+
+def experiment_download(args: argparse.Namespace) -> int:
+    d = _sdk(args)
+    exp = d.get_experiment(args.experiment_id)
+    cks = exp.top_n_checkpoints(args.top_n, sort_by=args.sort_by, smaller_is_better=args.smaller_is_better)
+    for c in cks:
+        path = c.download(os.path.join(args.output_dir, c.uuid))
+        print(f"Local checkpoint path: {path}")
+    return 0
+
+
+def experiment_set(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    eid = args.experiment_id
+    if args.attr == "name":
+        sess.patch(f"/api/v1/experiments/{eid}", json={"name": args.value})
+    elif args.attr == "description":
+        sess.patch(f"/api/v1/experiments/{eid}", json={"description": args.value})
+    elif args.attr == "priority":
+        sess.patch(f"/api/v1/experiments/{eid}", json={"resources": {"priority": int(args.value)}})
+    elif args.attr == "weight":
+        sess.patch(f"/api/v1/experiments/{eid}", json={"resources": {"weight": float(args.value)}})
+    elif args.attr == "max-slots":
+        sess.patch(f"/api/v1/experiments/{eid}", json={"resources": {"maxSlots": int(args.value)}})
+    elif args.attr == "gc-policy":
+        a, b, c = (int(x) for x in args.value.split(","))
+        sess.patch(f"/api/v1/experiments/{eid}", json={"checkpointStorage": {"saveExperimentBest": a, "saveTrialBest": b, "saveTrialLatest": c}})
+    print(f"Set {args.attr} of experiment {eid} to {args.value}")
+    return 0
+
+
+def experiment_label(args: argparse.Namespace) -> int:
+    e = _sdk(args).get_experiment(args.experiment_id)
+    (e.add_label if args.action == "add" else e.remove_label)(args.label)
+    return 0
+
+
+def experiment_config(args: argparse.Namespace) -> int:
+    e = _session(args).get(f"/api/v1/experiments/{args.experiment_id}").json()["experiment"]
+    print(yaml.safe_dump(e["config"], default_flow_style=False))
+    return 0
+
+
+def experiment_wait(args: argparse.Namespace) -> int:
+    st = _sdk(args).get_experiment(args.experiment_id).wait(interval=args.polling_interval)
+    print(st.value)
+    return 0 if st == sdk.ExperimentState.COMPLETED else 1
+
+
+def experiment_list_checkpoints(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    cks = sess.get(f"/api/v1/experiments/{args.experiment_id}/checkpoints").json()["checkpoints"]
+    _table([[c["training"]["trialId"], c["metadata"].get("steps_completed"), c["state"].replace("STATE_", ""), c["training"]["searcherMetric"], c["uuid"],
+             sum(int(v) for v in c["resources"].values())] for c in cks], ["Trial ID", "# of Batches", "State", "Validation Metric", "UUID", "Size"], args.json)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# trial / checkpoint
+# ------------------------------------------------------------------------------------------------
+def trial_describe(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    t = sess.get(f"/api/v1/trials/{args.trial_id}").json()["trial"]
+    if args.json:
+        t["metrics"] = sess.get(f"/api/v1/trials/{args.trial_id}/metrics").json()["metrics"]
+        print(json.dumps(t, indent=2, default=str))
+        return 0
+    _table([[t["id"], t["experimentId"], t["state"].replace("STATE_", ""), t["startTime"], t["endTime"], json.dumps(t["hparams"]), t["totalBatchesProcessed"], t["restarts"]]],
+           ["Trial ID", "Experiment ID", "State", "Started", "Ended", "H-Params", "Batches", "Restarts"])
+    mets = sess.get(f"/api/v1/trials/{args.trial_id}/metrics").json()["metrics"]
+    print()
+    _table([[m["totalBatches"], m["group"], m["endTime"], json.dumps(m["metrics"]["avgMetrics"])] for m in mets], ["# of Batches", "Group", "Report Time", "Metrics"])
+    return 0
+
+
+def trial_list(args: argparse.Namespace) -> int:
+    trials = _session(args).get(f"/api/v1/experiments/{args.experiment_id}/trials").json()["trials"]
+    _table([[t["id"], t["state"].replace("STATE_", ""), json.dumps(t["hparams"]), t["startTime"], t["endTime"], t["totalBatchesProcessed"], t["restarts"],
+             t["searcherMetricValue"]] for t in trials], ["Trial ID", "State", "H-Params", "Started", "Ended", "# of Batches", "Restarts", "Best Metric"], args.json)
+    return 0
+
+
+def trial_logs(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    t = sdk.Trial(sess, args.trial_id)
+    for line in t.logs(follow=args.follow, head=args.head, tail=args.tail):
+        sys.stdout.write(line)
+    return 0
+
+
+def trial_kill(args: argparse.Namespace) -> int:
+    _session(args).post(f"/api/v1/trials/{args.trial_id}/kill")
+    print(f"Killed trial {args.trial_id}")
+    return 0
+
+
+def checkpoint_describe(args: argparse.Namespace) -> int:
+    c = _session(args).get(f"/api/v1/checkpoints/{args.uuid}").json()["checkpoint"]
+    if args.json:
+        print(json.dumps(c, indent=2, default=str))
+        return 0
+    tr = c["training"]
+    _table([[tr.get("experimentId"), tr.get("trialId"), c["metadata"].get("steps_completed"), c["reportTime"], c["uuid"], json.dumps(tr.get("validationMetrics", {}).get("avgMetrics")),
+             json.dumps(c["metadata"])]], ["Experiment ID", "Trial ID", "Steps Completed", "Report Time", "UUID", "Validation Metrics", "Metadata"])
+    print("\nResources:")
+    _table([[k, v] for k, v in sorted(c["resources"].items())], ["Path", "Size"])
+    return 0
+
+
+def checkpoint_download(args: argparse.Namespace) -> int:
+    c = _sdk(args).get_checkpoint(args.uuid)
+    path = c.download(args.output_dir, mode=sdk.DownloadMode(args.mode))
+    if args.quiet:
+        print(path)
+    else:
+        print(f"Local checkpoint path: {path}")
+    return 0
+
+
+def checkpoint_delete(args: argparse.Namespace) -> int:
+    uuids = args.uuid.split(",")
+    if not args.yes and input(f"Delete {len(uuids)} checkpoint(s)? [y/N] ").strip().lower() not in ("y", "yes"):
+        return 1
+    _session(args).delete("/api/v1/checkpoints", json={"checkpointUuids": uuids})
+    print(f"Deletion of checkpoints {args.uuid} is in progress")
+    return 0
+
+
+def checkpoint_rm(args: argparse.Namespace) -> int:
+    _session(args).post("/api/v1/checkpoints/rm", json={"checkpointUuids": args.uuid.split(","), "checkpointGlobs": args.glob})
+    print(f"Removed files matching {args.glob} from {args.uuid}")
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# misc
+# ------------------------------------------------------------------------------------------------
+def preview_search(args: argparse.Namespace) -> int:
+    cfg = yaml.safe_load(pathlib.Path(args.config_file).read_text())
+    _parse_config_overrides(cfg, args.config)
+    sim = _sdk(args).preview_search(cfg, seed=args.seed)
+    print(f"Using search configuration:\n{yaml.safe_dump(sim['config']['searcher'])}")
+    rows = []
+    for t in sim["trials"]:
+        rows.append([t["occurrences"], ", ".join(f"train {op['validateAfter']['length']} {sim['unit']}, validate" for op in t["operations"])])
+    _table(rows, ["Trials", "Breakdown"])
+    return 0
+
+
+def master_info(args: argparse.Namespace) -> int:
+    sess = api.UnauthSession(args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080")
+    print(yaml.safe_dump(sess.get("/api/v1/master").json(), default_flow_style=False))
+    return 0
+
+
+def master_config(args: argparse.Namespace) -> int:
+    print(yaml.safe_dump(_session(args).get("/api/v1/master/config").json()["config"], default_flow_style=False))
+    return 0
+
+
+def agent_list(args: argparse.Namespace) -> int:
+    ags = _session(args).get("/api/v1/agents").json()["agents"]
+    _table([[a["id"], a["version"], a["registeredTime"], len(a["slots"]), sum(1 for s in a["slots"].values() if s["container"]), a["enabled"], a["draining"],
+             ",".join(a["resourcePools"]), ",".join(a["addresses"])] for a in ags],
+           ["Agent ID", "Version", "Registered Time", "Slots", "Containers", "Enabled", "Draining", "Resource Pool", "Addresses"], args.json)
+    return 0
+
+
+def slot_list(args: argparse.Namespace) -> int:
+    ags = _session(args).get("/api/v1/agents").json()["agents"]
+    rows = []
+    for a in ags:
+        for sid, s in sorted(a["slots"].items(), key=lambda kv: int(kv[0])):
+            rows.append([a["id"], sid, s["enabled"], (s["container"] or {}).get("id"), s["device"]["type"].replace("TYPE_", ""), s["device"]["brand"], s["device"]["uuid"]])
+    _table(rows, ["Agent ID", "Slot ID", "Enabled", "Allocation ID", "Type", "Device", "UUID"], args.json)
+    return 0
+
+
+def slot_toggle(enable: bool) -> Any:
+    def fn(args: argparse.Namespace) -> int:
+        _session(args).post(f"/api/v1/agents/{args.agent_id}/slots/{args.slot_id}/{'enable' if enable else 'disable'}")
+        print(f"{'Enabled' if enable else 'Disabled'} slot {args.slot_id} of agent {args.agent_id}")
+        return 0
+    return fn
+
+
+def job_list(args: argparse.Namespace) -> int:
+    jobs = _session(args).get("/api/v1/job-queues-v2").json()["jobs"]
+    _table([[i, j["jobId"], j["type"].replace("TYPE_", ""), j["name"], j["priority"], j["weight"], f"{j['allocatedSlots']}/{j['requestedSlots']}",
+             j["summary"]["state"].replace("STATE_", ""), j["resourcePool"]] for i, j in enumerate(jobs)],
+           ["#", "ID", "Type", "Job Name", "Priority", "Weight", "Slots (acquired/needed)", "Status", "Resource Pool"], args.json)
+    return 0
+
+
+def job_update(args: argparse.Namespace) -> int:
+    upd: Dict[str, Any] = {"jobId": args.job_id}
+    if args.priority is not None:
+        upd["priority"] = args.priority
+    if args.weight is not None:
+        upd["weight"] = args.weight
+    _session(args).post("/api/v1/job-queues", json={"updates": [upd]})
+    print(f"Updated job {args.job_id}")
+    return 0
+
+
+def resource_pool_list(args: argparse.Namespace) -> int:
+    rps = _session(args).get("/api/v1/resource-pools").json()["resourcePools"]
+    _table([[p["name"], p["description"], p["type"], p["numAgents"], f"{p['slotsUsed']}/{p['slotsAvailable']}", p["schedulerType"].replace("SCHEDULER_TYPE_", ""),
+             p["schedulerFittingPolicy"].replace("FITTING_POLICY_", ""), p["preemptible"]] for p in rps],
+           ["Name", "Description", "Type", "Agents", "Slots Used", "Scheduler", "Fitting Policy", "Preemptible"], args.json)
+    return 0
+
+
+def template_cmd(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    if args.action == "list":
+        ts = sess.get("/api/v1/templates").json()["templates"]
+        _table([[t["name"]] for t in ts], ["Name"])
+    elif args.action == "describe":
+        print(yaml.safe_dump(sess.get(f"/api/v1/templates/{args.name}").json()["template"]["config"], default_flow_style=False))
+    elif args.action in ("set", "create"):
+        cfg = yaml.safe_load(pathlib.Path(args.file).read_text())
+        sess.put(f"/api/v1/templates/{args.name}", json={"config": cfg})
+        print(f"Set template {args.name}")
+    elif args.action == "remove":
+        sess.delete(f"/api/v1/templates/{args.name}")
+        print(f"Removed template {args.name}")
+    return 0
+
+
+def model_cmd(args: argparse.Namespace) -> int:
+    d = _sdk(args)
+    if args.action == "list":
+        _table([[m.model_id, m.name, m.description, m.archived, ",".join(m.labels)] for m in d.get_models()], ["ID", "Name", "Description", "Archived", "Labels"], args.json)
+    elif args.action == "create":
+        m = d.create_model(args.name, args.description or "")
+        print(f"Created model {m.name} (id {m.model_id})")
+    elif args.action == "describe":
+        m = d.get_model(args.name)
+        _table([[m.model_id, m.name, m.description, json.dumps(m.metadata)]], ["ID", "Name", "Description", "Metadata"])
+        print()
+        _table([[v.model_version, v.checkpoint.uuid if v.checkpoint else None, v.name, v.comment] for v in m.list_versions()], ["Version", "Checkpoint", "Name", "Comment"])
+    elif args.action == "register-version":
+        v = d.get_model(args.name).register_version(args.uuid)
+        print(f"Registered version {v.model_version} of model {args.name}")
+    elif args.action == "delete":
+        d.get_model(args.name).delete()
+        print(f"Deleted model {args.name}")
+    return 0
+
+
+def user_cmd(args: argparse.Namespace) -> int:
+    if args.action == "login":
+        import getpass
+
+        master = args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
+        pw = os.environ.get("DET_PASS")
+        if pw is None:
+            pw = "" if args.username == "determined" else getpass.getpass(f"Password for user '{args.username}': ")
+        sess = api.authentication.login(master, args.username, pw)
+        st = api.authentication.TokenStore(master)
+        st.set_token(args.username, sess.token or "")
+        st.set_active(args.username)
+        print(f"Logged in as {args.username}")
+        return 0
+    if args.action == "logout":
+        api.authentication.logout(args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080", args.user)
+        print("Logged out")
+        return 0
+    sess = _session(args)
+    if args.action == "whoami":
+        print("You are logged in as user '{}'".format(sess.get("/api/v1/me").json()["user"]["username"]))
+    elif args.action == "list":
+        us = sess.get("/api/v1/users").json()["users"]
+        _table([[u["id"], u["username"], u["displayName"], u["active"], u["admin"]] for u in us], ["ID", "Username", "Display Name", "Active", "Admin"], args.json)
+    elif args.action == "create":
+        sess.post("/api/v1/users", json={"user": {"username": args.username, "admin": args.admin, "active": True}, "password": ""})
+        print(f"Created user {args.username}")
+    elif args.action in ("activate", "deactivate"):
+        us = [u for u in sess.get("/api/v1/users").json()["users"] if u["username"] == args.username]
+        if not us:
+            raise SystemExit(f"user {args.username} not found")
+        sess.patch(f"/api/v1/users/{us[0]['id']}", json={"user": {"active": args.action == "activate"}})
+    elif args.action == "change-password":
+        import getpass
+
+        me = sess.get("/api/v1/me").json()["user"]
+        pw = getpass.getpass("New password: ")
+        sess.post(f"/api/v1/users/{me['id']}/password", data=json.dumps(api.authentication.salt_and_hash(pw)))
+    return 0
+
+
+def workspace_cmd(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    if args.action == "list":
+        ws = sess.get("/api/v1/workspaces").json()["workspaces"]
+        _table([[w["id"], w["name"], w["numProjects"], w["archived"]] for w in ws], ["ID", "Name", "# Projects", "Archived"], args.json)
+    elif args.action == "create":
+        w = sess.post("/api/v1/workspaces", json={"name": args.name}).json()["workspace"]
+        print(f"Created workspace {w['name']} (id {w['id']})")
+    elif args.action == "delete":
+        ws = [w for w in sess.get("/api/v1/workspaces", params={"name": args.name}).json()["workspaces"]]
+        if not ws:
+            raise SystemExit("workspace not found")
+        sess.delete(f"/api/v1/workspaces/{ws[0]['id']}")
+        print(f"Deleted workspace {args.name}")
+    elif args.action == "list-projects":
+        ws = [w for w in sess.get("/api/v1/workspaces", params={"name": args.name}).json()["workspaces"]]
+        if not ws:
+            raise SystemExit("workspace not found")
+        ps = sess.get(f"/api/v1/workspaces/{ws[0]['id']}/projects").json()["projects"]
+        _table([[p["id"], p["name"], p["description"], p["numExperiments"]] for p in ps], ["ID", "Name", "Description", "# Experiments"], args.json)
+    elif args.action == "create-project":
+        ws = [w for w in sess.get("/api/v1/workspaces", params={"name": args.name}).json()["workspaces"]]
+        if not ws:
+            raise SystemExit("workspace not found")
+        p = sess.post(f"/api/v1/workspaces/{ws[0]['id']}/projects", json={"name": args.project, "description": ""}).json()["project"]
+        print(f"Created project {p['name']} (id {p['id']})")
+    return 0
+
+
+def deploy_local(args: argparse.Namespace) -> int:
+    """``det deploy local cluster-up``: start the single-box master in the foreground or detached
+    (reference ``harness/determined/deploy/local``: docker-compose master+db+agent)."""
+    import subprocess
+
+    cmd = [sys.executable, "-m", "determined_b200.master", "--port", str(args.master_port)]
+    if args.slots is not None:
+        cmd += ["--slots", str(args.slots)]
+    if args.scheduler:
+        cmd += ["--scheduler", args.scheduler]
+    if args.action == "cluster-up":
+        if args.no_detach:
+            return subprocess.call(cmd)
+        log = open(os.path.expanduser("~/.detb200-master.log"), "ab")
+        p = subprocess.Popen(cmd, stdout=log, stderr=log, start_new_session=True)
+        pathlib.Path(os.path.expanduser("~/.detb200-master.pid")).write_text(str(p.pid))
+        print(f"master started (pid {p.pid}) on http://127.0.0.1:{args.master_port}; logs in ~/.detb200-master.log")
+        return 0
+    if args.action == "cluster-down":
+        import signal
+
+        pf = pathlib.Path(os.path.expanduser("~/.detb200-master.pid"))
+        if pf.exists():
+            try:
+                os.kill(int(pf.read_text()), signal.SIGTERM)
+                print("master stopped")
+            except ProcessLookupError:
+                print("master was not running")
+            pf.unlink()
+        return 0
+    return 2
+
+
+def version(args: argparse.Namespace) -> int:
+    out = {"client": {"version": det.__version__}}
+    try:
+        sess = api.UnauthSession(args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080", max_retries=0)
+        out["master"] = sess.get("/api/v1/master").json()
+    except Exception as e:
+        out["master"] = {"error": str(e)}
+    print(yaml.safe_dump(out, default_flow_style=False))
+    return 0
+
+
+def make_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(prog="det", description="determined_b200 command line client")
+    p.add_argument("-m", "--master", help="master address (default: $DET_MASTER or localhost:8080)")
+    p.add_argument("-u", "--user", help="run as this user")
+    p.add_argument("-v", "--version", action="version", version=f"det {det.__version__}")
+    sub = p.add_subparsers(dest="cmd")
+
+    def outfmt(sp: argparse.ArgumentParser) -> None:
+        sp.add_argument("--json", action="store_true")
+        sp.add_argument("--csv", action="store_true")
+
+    # experiment
+    e = sub.add_parser("experiment", aliases=["e"], help="manage experiments").add_subparsers(dest="sub")
+    c = e.add_parser("create", help="create experiment")
+    c.add_argument("config_file")
+    c.add_argument("model_def", nargs="?", default=None)
+    c.add_argument("--local", action="store_true", help="run locally in this process, no master")
+    c.add_argument("--test", action="store_true", help="one batch of train/validate/checkpoint")
+    c.add_argument("--paused", action="store_true")
+    c.add_argument("-f", "--follow-first-trial", action="store_true")
+    c.add_argument("--config", action="append", help="override key=value (dotted)")
+    c.add_argument("--template")
+    c.add_argument("--project_id", "--project-id", type=int, default=1)
+    c.add_argument("-i", "--include", action="append")
+    c.add_argument("--publish", action="append")
+    c.set_defaults(fn=experiment_create)
+    l = e.add_parser("list", aliases=["ls"])
+    l.add_argument("--all", "-a", action="store_true")
+    outfmt(l)
+    l.set_defaults(fn=experiment_list)
+    d = e.add_parser("describe")
+    d.add_argument("experiment_ids")
+    outfmt(d)
+    d.set_defaults(fn=experiment_describe)
+    for name in ("pause", "activate", "cancel", "kill", "archive", "unarchive"):
+        a = e.add_parser(name)
+        a.add_argument("experiment_id", type=int)
+        a.set_defaults(fn=_exp_action(name))
+    a = e.add_parser("delete")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("--yes", action="store_true")
+    a.set_defaults(fn=experiment_delete)
+    a = e.add_parser("logs")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("-f", "--follow", action="store_true")
+    a.add_argument("--head", type=int)
+    a.add_argument("--tail", type=int)
+    a.set_defaults(fn=experiment_logs)
+    a = e.add_parser("download")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("-o", "--output-dir", default=".")
+    a.add_argument("--top-n", type=int, default=1)
+    a.add_argument("--sort-by")
+    a.add_argument("--smaller-is-better", type=lambda s: s.lower() in ("1", "true", "yes"), default=None)
+    a.set_defaults(fn=experiment_download)
+    a = e.add_parser("set")
+    a.add_argument("attr", choices=["name", "description", "priority", "weight", "max-slots", "gc-policy"])
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("value")
+    a.set_defaults(fn=experiment_set)
+    a = e.add_parser("label")
+    a.add_argument("action", choices=["add", "remove"])
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("label")
+    a.set_defaults(fn=experiment_label)
+    a = e.add_parser("config")
+    a.add_argument("experiment_id", type=int)
+    a.set_defaults(fn=experiment_config)
+    a = e.add_parser("wait")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("--polling-interval", type=float, default=5)
+    a.set_defaults(fn=experiment_wait)
+    a = e.add_parser("list-checkpoints", aliases=["lc"])
+    a.add_argument("experiment_id", type=int)
+    outfmt(a)
+    a.set_defaults(fn=experiment_list_checkpoints)
+    a = e.add_parser("list-trials", aliases=["lt"])
+    a.add_argument("experiment_id", type=int)
+    outfmt(a)
+    a.set_defaults(fn=trial_list)
+
+    # trial
+    t = sub.add_parser("trial", aliases=["t"], help="manage trials").add_subparsers(dest="sub")
+    a = t.add_parser("describe")
+    a.add_argument("trial_id", type=int)
+    outfmt(a)
+    a.set_defaults(fn=trial_describe)
+    a = t.add_parser("list")
+    a.add_argument("experiment_id", type=int)
+    outfmt(a)
+    a.set_defaults(fn=trial_list)
+    a = t.add_parser("logs")
+    a.add_argument("trial_id", type=int)
+    a.add_argument("-f", "--follow", action="store_true")
+    a.add_argument("--head", type=int)
+    a.add_argument("--tail", type=int)
+    a.set_defaults(fn=trial_logs)
+    a = t.add_parser("kill")
+    a.add_argument("trial_id", type=int)
+    a.set_defaults(fn=trial_kill)
+
+    # checkpoint
+    c = sub.add_parser("checkpoint", aliases=["c"], help="manage checkpoints").add_subparsers(dest="sub")
+    a = c.add_parser("describe")
+    a.add_argument("uuid")
+    outfmt(a)
+    a.set_defaults(fn=checkpoint_describe)
+    a = c.add_parser("download")
+    a.add_argument("uuid")
+    a.add_argument("-o", "--output-dir", default=None)
+    a.add_argument("-q", "--quiet", action="store_true")
+    a.add_argument("--mode", choices=["auto", "direct", "master"], default="auto")
+    a.set_defaults(fn=checkpoint_download)
+    a = c.add_parser("delete")
+    a.add_argument("uuid", help="comma-separated uuids")
+    a.add_argument("--yes", action="store_true")
+    a.set_defaults(fn=checkpoint_delete)
+    a = c.add_parser("rm")
+    a.add_argument("uuid", help="comma-separated uuids")
+    a.add_argument("--glob", action="append", required=True)
+    a.set_defaults(fn=checkpoint_rm)
+    a = c.add_parser("list")
+    a.add_argument("experiment_id", type=int)
+    outfmt(a)
+    a.set_defaults(fn=experiment_list_checkpoints)
+
+    a = sub.add_parser("preview-search", help="simulate the searcher for a config")
+    a.add_argument("config_file")
+    a.add_argument("--config", action="append")
+    a.add_argument("--seed", type=int, default=0)
+    a.set_defaults(fn=preview_search)
+
+    ms = sub.add_parser("master").add_subparsers(dest="sub")
+    a = ms.add_parser("info")
+    a.set_defaults(fn=master_info)
+    a = ms.add_parser("config")
+    a.set_defaults(fn=master_config)
+
+    ag = sub.add_parser("agent", aliases=["a"]).add_subparsers(dest="sub")
+    a = ag.add_parser("list", aliases=["ls"])
+    outfmt(a)
+    a.set_defaults(fn=agent_list)
+    sl = sub.add_parser("slot", aliases=["s"]).add_subparsers(dest="sub")
+    a = sl.add_parser("list", aliases=["ls"])
+    outfmt(a)
+    a.set_defaults(fn=slot_list)
+    for name, en in (("enable", True), ("disable", False)):
+        a = sl.add_parser(name)
+        a.add_argument("agent_id")
+        a.add_argument("slot_id")
+        a.set_defaults(fn=slot_toggle(en))
+
+    jb = sub.add_parser("job", aliases=["j"]).add_subparsers(dest="sub")
+    a = jb.add_parser("list", aliases=["ls"])
+    outfmt(a)
+    a.set_defaults(fn=job_list)
+    a = jb.add_parser("update")
+    a.add_argument("job_id")
+    a.add_argument("--priority", type=int)
+    a.add_argument("--weight", type=float)
+    a.set_defaults(fn=job_update)
+    rp = sub.add_parser("resource-pool", aliases=["rp"]).add_subparsers(dest="sub")
+    a = rp.add_parser("list", aliases=["ls"])
+    outfmt(a)
+    a.set_defaults(fn=resource_pool_list)
+
+    tp = sub.add_parser("template", aliases=["tpl"]).add_subparsers(dest="sub")
+    for name in ("list", "describe", "set", "create", "remove"):
+        a = tp.add_parser(name)
+        if name != "list":
+            a.add_argument("name")
+        if name in ("set", "create"):
+            a.add_argument("file")
+        a.set_defaults(fn=template_cmd, action=name)
+
+    md = sub.add_parser("model").add_subparsers(dest="sub")
+    for name in ("list", "create", "describe", "register-version", "delete"):
+        a = md.add_parser(name)
+        if name != "list":
+            a.add_argument("name")
+        if name == "create":
+            a.add_argument("--description")
+        if name == "register-version":
+            a.add_argument("uuid")
+        outfmt(a)
+        a.set_defaults(fn=model_cmd, action=name)
+
+    us = sub.add_parser("user", aliases=["u"]).add_subparsers(dest="sub")
+    for name in ("login", "logout", "whoami", "list", "create", "activate", "deactivate", "change-password"):
+        a = us.add_parser(name)
+        if name in ("login", "create", "activate", "deactivate"):
+            a.add_argument("username")
+        if name == "create":
+            a.add_argument("--admin", action="store_true")
+        outfmt(a)
+        a.set_defaults(fn=user_cmd, action=name)
+    a = sub.add_parser("auth").add_subparsers(dest="sub")
+    for name in ("login", "logout"):
+        b = a.add_parser(name)
+        if name == "login":
+            b.add_argument("username", nargs="?", default="determined")
+        b.set_defaults(fn=user_cmd, action=name)
+
+    ws = sub.add_parser("workspace", aliases=["w"]).add_subparsers(dest="sub")
+    for name in ("list", "create", "delete", "list-projects", "create-project"):
+        a = ws.add_parser(name)
+        if name != "list":
+            a.add_argument("name")
+        if name == "create-project":
+            a.add_argument("project")
+        outfmt(a)
+        a.set_defaults(fn=workspace_cmd, action=name)
+
+    dp = sub.add_parser("deploy").add_subparsers(dest="sub")
+    lo = dp.add_parser("local")
+    lo.add_argument("action", choices=["cluster-up", "cluster-down"])
+    lo.add_argument("--master-port", type=int, default=8080)
+    lo.add_argument("--slots", type=int)
+    lo.add_argument("--scheduler", choices=["fair_share", "priority", "round_robin"])
+    lo.add_argument("--no-detach", action="store_true")
+    lo.set_defaults(fn=deploy_local)
+
+    a = sub.add_parser("version")
+    a.set_defaults(fn=version)
+    return p
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    parser = make_parser()
+    args = parser.parse_args(argv)
+    fn = getattr(args, "fn", None)
+    if fn is None:
+        parser.print_help()
+        return 2
+    try:
+        return int(fn(args) or 0)
+    except api.errors.APIException as e:
+        print(f"Failed: {e.message}", file=sys.stderr)
+        return 1
+    except api.errors.MasterNotFoundException as e:
+        print(f"Failed: {e}", file=sys.stderr)
+        return 1
+    except KeyboardInterrupt:
+        return 130

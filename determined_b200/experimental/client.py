@@ -1,0 +1,514 @@
+"""Python SDK: ``from determined.experimental import client``.
+
+Parity: reference ``harness/determined/experimental/client.py:1-646`` (module-level helpers bound
+to a default ``Determined`` object) and ``harness/determined/common/experimental/*``
+(``Determined``, ``Experiment``, ``Trial``, ``Checkpoint`` with ``download(mode=…)`` /
+``write_metadata_file`` ``checkpoint/_checkpoint.py:19-505``, ``Model``/``ModelVersion``,
+``Project``/``Workspace``)."""
+import enum
+import json
+import os
+import pathlib
+import time
+from typing import Any, Dict, Iterable, Iterator, List, Optional, Union
+
+import yaml
+
+from determined_b200.common import api, context as det_context, storage
+
+
+class ExperimentState(enum.Enum):
+    ACTIVE = "STATE_ACTIVE"
+    PAUSED = "STATE_PAUSED"
+    STOPPING_COMPLETED = "STATE_STOPPING_COMPLETED"
+    STOPPING_CANCELED = "STATE_STOPPING_CANCELED"
+    STOPPING_KILLED = "STATE_STOPPING_KILLED"
+    STOPPING_ERROR = "STATE_STOPPING_ERROR"
+    COMPLETED = "STATE_COMPLETED"
+    CANCELED = "STATE_CANCELED"
+    ERROR = "STATE_ERROR"
+    DELETED = "STATE_DELETED"
+
+
+TERMINAL = {ExperimentState.COMPLETED, ExperimentState.CANCELED, ExperimentState.ERROR}
+
+
+class DownloadMode(enum.Enum):
+    """DIRECT: read checkpoint storage yourself; MASTER: proxy through the master; AUTO: DIRECT
+    if the storage is reachable from here else MASTER."""
+
+    DIRECT = "direct"
+    MASTER = "master"
+    AUTO = "auto"
+
+
+class CheckpointState(enum.Enum):
+    UNSPECIFIED = "STATE_UNSPECIFIED"
+    ACTIVE = "STATE_ACTIVE"
+    COMPLETED = "STATE_COMPLETED"
+    ERROR = "STATE_ERROR"
+    DELETED = "STATE_DELETED"
+    PARTIALLY_DELETED = "STATE_PARTIALLY_DELETED"
+
+
+class ModelSortBy(enum.Enum):
+    NAME = "SORT_BY_NAME"
+    CREATION_TIME = "SORT_BY_CREATION_TIME"
+
+
+class Checkpoint:
+    def __init__(self, session: api.Session, uuid: str, data: Optional[Dict[str, Any]] = None) -> None:
+        self._session, self.uuid = session, uuid
+        self._hydrate(data or {})
+
+    def _hydrate(self, d: Dict[str, Any]) -> None:
+        self.task_id = d.get("taskId")
+        self.allocation_id = d.get("allocationId")
+        self.report_time = d.get("reportTime")
+        self.resources = {k: int(v) for k, v in (d.get("resources") or {}).items()}
+        self.metadata = d.get("metadata") or {}
+        self.state = CheckpointState(d["state"]) if d.get("state") in {s.value for s in CheckpointState} else None
+        self.training = d.get("training") or {}
+
+    def reload(self) -> None:
+        self._hydrate(self._session.get(f"/api/v1/checkpoints/{self.uuid}").json()["checkpoint"])
+
+    def _storage_config(self) -> Dict[str, Any]:
+        if not self.training:
+            self.reload()
+        cfg = (self.training.get("experimentConfig") or {}).get("checkpoint_storage")
+        if not cfg:
+            raise ValueError("checkpoint has no recorded storage configuration")
+        return cfg
+
+    def download(self, path: Optional[str] = None, mode: DownloadMode = DownloadMode.AUTO) -> str:
+        """Download to ``path`` (default ``checkpoints/<uuid>``); returns the directory."""
+        dst = pathlib.Path(path) if path else pathlib.Path("checkpoints", self.uuid)
+        if (dst / "metadata.json").exists() and path is None:
+            return str(dst)
+        dst.mkdir(parents=True, exist_ok=True)
+        mgr = storage.build(self._storage_config(), None)
+        mgr.download(self.uuid, str(dst))
+        self.write_metadata_file(str(dst / "metadata.json"))
+        return str(dst)
+
+    def write_metadata_file(self, path: str) -> None:
+        if os.path.exists(path):
+            return
+        with open(path, "w") as f:
+            json.dump(self.metadata, f, indent=2)
+
+    def add_metadata(self, metadata: Dict[str, Any]) -> None:
+        self._session.post(f"/api/v1/checkpoints/{self.uuid}/metadata", json={"checkpoint": {"uuid": self.uuid, "metadata": metadata}})
+        self.metadata.update(metadata)
+
+    def remove_metadata(self, keys: List[str]) -> None:
+        self.reload()
+        md = {k: v for k, v in self.metadata.items() if k not in keys}
+        self._session.post(f"/api/v1/checkpoints/{self.uuid}/metadata", json={"checkpoint": {"uuid": self.uuid, "metadata": {k: None for k in keys}}})
+        self.metadata = md
+
+    def delete(self) -> None:
+        self._session.delete("/api/v1/checkpoints", json={"checkpointUuids": [self.uuid]})
+
+    def remove_files(self, globs: List[str]) -> None:
+        self._session.post("/api/v1/checkpoints/rm", json={"checkpointUuids": [self.uuid], "checkpointGlobs": globs})
+
+    def __repr__(self) -> str:
+        return f"Checkpoint(uuid={self.uuid}, task_id={self.task_id})"
+
+
+class Trial:
+    def __init__(self, session: api.Session, trial_id: int, data: Optional[Dict[str, Any]] = None) -> None:
+        self._session, self.id = session, trial_id
+        self._hydrate(data or {})
+
+    def _hydrate(self, d: Dict[str, Any]) -> None:
+        self.experiment_id = d.get("experimentId")
+        self.hparams = d.get("hparams")
+        self.state = d.get("state")
+        self.restarts = d.get("restarts")
+        self.total_batches = d.get("totalBatchesProcessed")
+        self.latest_checkpoint_uuid = d.get("latestCheckpoint")
+        self.summary = d
+
+    def reload(self) -> None:
+        self._hydrate(self._session.get(f"/api/v1/trials/{self.id}").json()["trial"])
+
+    def logs(self, follow: bool = False, head: Optional[int] = None, tail: Optional[int] = None) -> Iterator[str]:
+        off = 0
+        buf: List[str] = []
+        while True:
+            r = self._session.get(f"/api/v1/trials/{self.id}/logs", params={"offset": off, "follow": str(follow).lower(), "limit": 1000}).json()["logs"]
+            for l in r:
+                off = max(off, l["id"])
+                if tail is not None:
+                    buf.append(l["log"])
+                else:
+                    yield l["log"]
+                    if head is not None:
+                        head -= 1
+                        if head <= 0:
+                            return
+            if not r:
+                if not follow:
+                    break
+                self.reload()
+                if self.state in ("STATE_COMPLETED", "STATE_CANCELED", "STATE_ERROR"):
+                    break
+        if tail is not None:
+            yield from buf[-tail:]
+
+    def iter_metrics(self, group: Optional[str] = None) -> Iterator[Dict[str, Any]]:
+        params = {"group": group} if group else {}
+        for m in self._session.get(f"/api/v1/trials/{self.id}/metrics", params=params).json()["metrics"]:
+            yield {"trial_id": m["trialId"], "group": m["group"], "steps_completed": m["totalBatches"], "metrics": m["metrics"]["avgMetrics"],
+                   "batch_metrics": m["metrics"].get("batchMetrics"), "end_time": m["endTime"]}
+
+    def stream_training_metrics(self) -> Iterator[Dict[str, Any]]:
+        return self.iter_metrics("training")
+
+    def stream_validation_metrics(self) -> Iterator[Dict[str, Any]]:
+        return self.iter_metrics("validation")
+
+    def list_checkpoints(self, order_desc: bool = False) -> List[Checkpoint]:
+        r = self._session.get(f"/api/v1/trials/{self.id}/checkpoints", params={"orderBy": "ORDER_BY_DESC" if order_desc else "ORDER_BY_ASC"}).json()
+        return [Checkpoint(self._session, c["uuid"], c) for c in r["checkpoints"] if c["state"] == "STATE_COMPLETED"]
+
+    get_checkpoints = list_checkpoints
+
+    def select_checkpoint(self, latest: bool = False, best: bool = False, uuid: Optional[str] = None, sort_by: Optional[str] = None,
+                          smaller_is_better: Optional[bool] = None) -> Checkpoint:
+        if sum([latest, best, uuid is not None]) != 1:
+            raise AssertionError("Exactly one of latest, best, or uuid must be set")
+        if uuid is not None:
+            c = self._session.get(f"/api/v1/checkpoints/{uuid}").json()["checkpoint"]
+            return Checkpoint(self._session, uuid, c)
+        cks = self.list_checkpoints()
+        if not cks:
+            raise ValueError(f"trial {self.id} has no checkpoints")
+        if latest:
+            return max(cks, key=lambda c: c.metadata.get("steps_completed", 0))
+        if sort_by is None:
+            key = lambda c: c.training.get("searcherMetric")  # noqa: E731
+            if smaller_is_better is None:
+                smaller_is_better = bool(((cks[0].training.get("experimentConfig") or {}).get("searcher") or {}).get("smaller_is_better", True))
+        else:
+            key = lambda c: (c.training.get("validationMetrics", {}).get("avgMetrics") or {}).get(sort_by)  # noqa: E731
+            if smaller_is_better is None:
+                raise AssertionError("smaller_is_better must be set when sort_by is specified")
+        cks = [c for c in cks if key(c) is not None]
+        if not cks:
+            raise ValueError("no checkpoint has the requested validation metric")
+        return (min if smaller_is_better else max)(cks, key=key)
+
+    def top_checkpoint(self, sort_by: Optional[str] = None, smaller_is_better: Optional[bool] = None) -> Checkpoint:
+        return self.select_checkpoint(best=True, sort_by=sort_by, smaller_is_better=smaller_is_better)
+
+    def kill(self) -> None:
+        self._session.post(f"/api/v1/trials/{self.id}/kill")
+
+    def __repr__(self) -> str:
+        return f"Trial(id={self.id})"
+
+
+class Experiment:
+    def __init__(self, session: api.Session, experiment_id: int, data: Optional[Dict[str, Any]] = None) -> None:
+        self._session, self.id = session, experiment_id
+        self._hydrate(data or {})
+
+    def _hydrate(self, d: Dict[str, Any]) -> None:
+        self.config = d.get("config")
+        self.name = d.get("name")
+        self.description = d.get("description")
+        self.labels = d.get("labels")
+        self.archived = d.get("archived")
+        self.progress = d.get("progress")
+        self.state = ExperimentState(d["state"]) if d.get("state") in {s.value for s in ExperimentState} else None
+        self.start_time, self.end_time = d.get("startTime"), d.get("endTime")
+
+    def reload(self) -> None:
+        self._hydrate(self._session.get(f"/api/v1/experiments/{self.id}").json()["experiment"])
+
+    def activate(self) -> None:
+        self._session.post(f"/api/v1/experiments/{self.id}/activate")
+
+    def pause(self) -> None:
+        self._session.post(f"/api/v1/experiments/{self.id}/pause")
+
+    def cancel(self) -> None:
+        self._session.post(f"/api/v1/experiments/{self.id}/cancel")
+
+    def kill(self) -> None:
+        self._session.post(f"/api/v1/experiments/{self.id}/kill")
+
+    def archive(self) -> None:
+        self._session.post(f"/api/v1/experiments/{self.id}/archive")
+
+    def unarchive(self) -> None:
+        self._session.post(f"/api/v1/experiments/{self.id}/unarchive")
+
+    def delete(self) -> None:
+        self._session.delete(f"/api/v1/experiments/{self.id}")
+
+    def set_name(self, name: str) -> None:
+        self._session.patch(f"/api/v1/experiments/{self.id}", json={"name": name})
+
+    def set_description(self, description: str) -> None:
+        self._session.patch(f"/api/v1/experiments/{self.id}", json={"description": description})
+
+    def add_label(self, label: str) -> None:
+        self.reload()
+        labels = sorted(set((self.labels or []) + [label]))
+        self._session.patch(f"/api/v1/experiments/{self.id}", json={"labels": labels})
+
+    def remove_label(self, label: str) -> None:
+        self.reload()
+        self._session.patch(f"/api/v1/experiments/{self.id}", json={"labels": [l for l in (self.labels or []) if l != label]})
+
+    def move_to_project(self, workspace_name: str, project_name: str) -> None:
+        ws = [w for w in self._session.get("/api/v1/workspaces", params={"name": workspace_name}).json()["workspaces"]]
+        if not ws:
+            raise ValueError(f"workspace {workspace_name!r} not found")
+        pr = [p for p in self._session.get(f"/api/v1/workspaces/{ws[0]['id']}/projects").json()["projects"] if p["name"] == project_name]
+        if not pr:
+            raise ValueError(f"project {project_name!r} not found")
+        self._session.post(f"/api/v1/experiments/{self.id}/move", json={"destinationProjectId": pr[0]["id"]})
+
+    def list_trials(self) -> List[Trial]:
+        r = self._session.get(f"/api/v1/experiments/{self.id}/trials").json()
+        return [Trial(self._session, t["id"], t) for t in r["trials"]]
+
+    get_trials = list_trials
+
+    def await_first_trial(self, interval: float = 0.1) -> Trial:
+        while True:
+            tr = self.list_trials()
+            if tr:
+                return tr[0]
+            time.sleep(interval)
+
+    def wait(self, interval: float = 5.0, timeout: Optional[float] = None) -> ExperimentState:
+        t0 = time.time()
+        while True:
+            self.reload()
+            if self.state in TERMINAL:
+                return self.state
+            if self.state == ExperimentState.PAUSED:
+                raise ValueError(f"Experiment {self.id} is in paused state. Make sure the experiment is active.")
+            if timeout is not None and time.time() - t0 > timeout:
+                raise TimeoutError(f"experiment {self.id} still {self.state} after {timeout}s")
+            time.sleep(interval)
+
+    def list_checkpoints(self, sort_by: Optional[str] = None, smaller_is_better: Optional[bool] = None, limit: Optional[int] = None) -> List[Checkpoint]:
+        params: Dict[str, Any] = {"states": "STATE_COMPLETED"}
+        if sort_by is not None:
+            params["sortByMetric"] = sort_by
+        else:
+            params["sortBy"] = "SORT_BY_SEARCHER_METRIC"
+        r = self._session.get(f"/api/v1/experiments/{self.id}/checkpoints", params=params).json()["checkpoints"]
+        cks = [Checkpoint(self._session, c["uuid"], c) for c in r]
+        if sort_by is not None and smaller_is_better is False:
+            cks.reverse()
+        return cks[:limit] if limit else cks
+
+    def top_checkpoint(self, sort_by: Optional[str] = None, smaller_is_better: Optional[bool] = None) -> Checkpoint:
+        cks = self.top_n_checkpoints(1, sort_by, smaller_is_better)
+        if not cks:
+            raise AssertionError(f"No checkpoints found for experiment {self.id}")
+        return cks[0]
+
+    def top_n_checkpoints(self, limit: int, sort_by: Optional[str] = None, smaller_is_better: Optional[bool] = None) -> List[Checkpoint]:
+        return self.list_checkpoints(sort_by, smaller_is_better, limit)
+
+    def __repr__(self) -> str:
+        return f"Experiment(id={self.id})"
+
+
+class ModelVersion:
+    def __init__(self, session: api.Session, d: Dict[str, Any]) -> None:
+        self._session = session
+        self.model_version = d.get("version")
+        self.model_id = (d.get("model") or {}).get("id")
+        self.model_name = (d.get("model") or {}).get("name")
+        ck = d.get("checkpoint") or {}
+        self.checkpoint = Checkpoint(session, ck.get("uuid"), ck) if ck.get("uuid") else None
+        self.name, self.comment, self.notes = d.get("name"), d.get("comment"), d.get("notes")
+        self.metadata = d.get("metadata") or {}
+
+    def delete(self) -> None:
+        self._session.delete(f"/api/v1/models/{self.model_name}/versions/{self.model_version}")
+
+
+class Model:
+    def __init__(self, session: api.Session, d: Dict[str, Any]) -> None:
+        self._session = session
+        self._hydrate(d)
+
+    def _hydrate(self, d: Dict[str, Any]) -> None:
+        self.model_id, self.name = d.get("id"), d.get("name")
+        self.description, self.metadata, self.labels = d.get("description"), d.get("metadata") or {}, d.get("labels") or []
+        self.archived = d.get("archived")
+
+    def reload(self) -> None:
+        self._hydrate(self._session.get(f"/api/v1/models/{self.name}").json()["model"])
+
+    def register_version(self, checkpoint_uuid: str) -> ModelVersion:
+        r = self._session.post(f"/api/v1/models/{self.name}/versions", json={"checkpointUuid": checkpoint_uuid}).json()
+        return ModelVersion(self._session, r["modelVersion"])
+
+    def get_version(self, version: int = -1) -> Optional[ModelVersion]:
+        if version == -1:
+            vs = self.list_versions(order_desc=True)
+            return vs[0] if vs else None
+        return ModelVersion(self._session, self._session.get(f"/api/v1/models/{self.name}/versions/{version}").json()["modelVersion"])
+
+    def list_versions(self, order_desc: bool = True) -> List[ModelVersion]:
+        r = self._session.get(f"/api/v1/models/{self.name}/versions", params={"orderBy": "ORDER_BY_DESC" if order_desc else "ORDER_BY_ASC"}).json()
+        return [ModelVersion(self._session, v) for v in r["modelVersions"]]
+
+    get_versions = list_versions
+
+    def add_metadata(self, metadata: Dict[str, Any]) -> None:
+        self.metadata.update(metadata)
+        self._session.patch(f"/api/v1/models/{self.name}", json={"model": {"metadata": self.metadata}})
+
+    def set_labels(self, labels: List[str]) -> None:
+        self._session.patch(f"/api/v1/models/{self.name}", json={"model": {"labels": labels}})
+        self.labels = labels
+
+    def set_description(self, description: str) -> None:
+        self._session.patch(f"/api/v1/models/{self.name}", json={"model": {"description": description}})
+        self.description = description
+
+    def archive(self) -> None:
+        self._session.post(f"/api/v1/models/{self.name}/archive")
+
+    def unarchive(self) -> None:
+        self._session.post(f"/api/v1/models/{self.name}/unarchive")
+
+    def delete(self) -> None:
+        self._session.delete(f"/api/v1/models/{self.name}")
+
+
+class Determined:
+    """Entry point of the SDK.  ``master`` defaults to ``$DET_MASTER`` or localhost:8080."""
+
+    def __init__(self, master: Optional[str] = None, user: Optional[str] = None, password: Optional[str] = None,
+                 cert_path: Optional[str] = None, noverify: bool = False) -> None:
+        self._master = master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
+        self._session = api.authentication.login_with_cache(self._master, user, password)
+
+    @classmethod
+    def _from_session(cls, session: api.Session) -> "Determined":
+        d = cls.__new__(cls)
+        d._master, d._session = session.master, session
+        return d
+
+    def create_experiment(self, config: Union[str, pathlib.Path, Dict[str, Any]], model_dir: Union[str, pathlib.Path, None] = None,
+                          includes: Optional[Iterable[Union[str, pathlib.Path]]] = None, parent_id: Optional[int] = None,
+                          project_id: Optional[int] = None, template: Optional[str] = None, activate: bool = True) -> Experiment:
+        if isinstance(config, (str, pathlib.Path)) and os.path.exists(str(config)):
+            text = pathlib.Path(config).read_text()
+        elif isinstance(config, dict):
+            text = yaml.safe_dump(config)
+        else:
+            text = str(config)
+        files: List[Dict[str, Any]] = []
+        if model_dir is not None:
+            files = det_context.read_v1_context(pathlib.Path(model_dir))
+        for inc in includes or []:
+            files += det_context.read_v1_context(pathlib.Path(inc))
+        r = self._session.post("/api/v1/experiments", json={"config": text, "modelDefinition": files, "activate": activate, "parentId": parent_id,
+                                                            "projectId": project_id, "template": template}).json()
+        return Experiment(self._session, r["experiment"]["id"], r["experiment"])
+
+    def get_experiment(self, experiment_id: int) -> Experiment:
+        return Experiment(self._session, experiment_id, self._session.get(f"/api/v1/experiments/{experiment_id}").json()["experiment"])
+
+    def list_experiments(self, **params: Any) -> List[Experiment]:
+        r = self._session.get("/api/v1/experiments", params=params).json()
+        return [Experiment(self._session, e["id"], e) for e in r["experiments"]]
+
+    def get_trial(self, trial_id: int) -> Trial:
+        return Trial(self._session, trial_id, self._session.get(f"/api/v1/trials/{trial_id}").json()["trial"])
+
+    def get_checkpoint(self, uuid: str) -> Checkpoint:
+        return Checkpoint(self._session, uuid, self._session.get(f"/api/v1/checkpoints/{uuid}").json()["checkpoint"])
+
+    def create_model(self, name: str, description: str = "", metadata: Optional[Dict[str, Any]] = None, labels: Optional[List[str]] = None) -> Model:
+        r = self._session.post("/api/v1/models", json={"name": name, "description": description, "metadata": metadata or {}, "labels": labels or []}).json()
+        return Model(self._session, r["model"])
+
+    def get_model(self, identifier: Union[str, int]) -> Model:
+        return Model(self._session, self._session.get(f"/api/v1/models/{identifier}").json()["model"])
+
+    def get_models(self, name: Optional[str] = None, **_: Any) -> List[Model]:
+        r = self._session.get("/api/v1/models", params={"name": name} if name else {}).json()
+        return [Model(self._session, m) for m in r["models"]]
+
+    list_models = get_models
+
+    def get_master_info(self) -> Dict[str, Any]:
+        return self._session.get("/api/v1/master").json()
+
+    def whoami(self) -> Dict[str, Any]:
+        return self._session.get("/api/v1/me").json()["user"]
+
+    def preview_search(self, config: Union[str, Dict[str, Any]], seed: int = 0) -> Dict[str, Any]:
+        text = yaml.safe_dump(config) if isinstance(config, dict) else config
+        return self._session.post("/api/v1/preview-hp-search", json={"config": text, "seed": seed}).json()["simulation"]
+
+    def logout(self) -> None:
+        api.authentication.logout(self._master)
+
+
+_determined: Optional[Determined] = None
+
+
+def login(master: Optional[str] = None, user: Optional[str] = None, password: Optional[str] = None, **kw: Any) -> None:
+    global _determined
+    _determined = Determined(master, user, password)
+
+
+def _d() -> Determined:
+    global _determined
+    if _determined is None:
+        _determined = Determined()
+    return _determined
+
+
+def create_experiment(config: Any, model_dir: Any = None, includes: Any = None, **kw: Any) -> Experiment:
+    return _d().create_experiment(config, model_dir, includes, **kw)
+
+
+def get_experiment(experiment_id: int) -> Experiment:
+    return _d().get_experiment(experiment_id)
+
+
+def get_trial(trial_id: int) -> Trial:
+    return _d().get_trial(trial_id)
+
+
+def get_checkpoint(uuid: str) -> Checkpoint:
+    return _d().get_checkpoint(uuid)
+
+
+def create_model(name: str, description: str = "", metadata: Optional[Dict[str, Any]] = None, labels: Optional[List[str]] = None) -> Model:
+    return _d().create_model(name, description, metadata, labels)
+
+
+def get_model(identifier: Union[str, int]) -> Model:
+    return _d().get_model(identifier)
+
+
+def get_models(**kw: Any) -> List[Model]:
+    return _d().get_models(**kw)
+
+
+def whoami() -> Dict[str, Any]:
+    return _d().whoami()
+
+
+def logout() -> None:
+    _d().logout()
