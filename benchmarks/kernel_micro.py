@@ -87,7 +87,7 @@ def bench_norm(rows):
     for rows_, cols in [(8192, 1024), (16384, 2560), (4096, 8192)]:
         x = torch.randn(rows_, cols, device="cuda", dtype=torch.bfloat16, requires_grad=True)
         ln = norm.LayerNorm(cols).cuda()
-        ref = torch.nn.LayerNorm(cols).cuda()
+        ref = torch.nn.LayerNorm(cols).cuda().to(torch.bfloat16)
         dy = torch.randn_like(x)
         y = ln(x)
         t_f = timeit(lambda: ln(x))

@@ -50,7 +50,7 @@ struct BnParams {
 
 // Column reduction skeleton shared by forward-stats and backward-reduce.  Each thread owns one
 // vector of channels (cg) and walks rows ty, ty+rows_per_iter, ...; K accumulators per channel.
-// Block partials go to `part` laid out [gridDim.x][K][C]; returns true in the last CTA to finish.
+// CTA partial sums are atomically added into `part` ([K][C] floats); returns true in the last CTA to finish.
 // `load(r, c0, regs)` fetches one row's vectors into registers (NT tensors x V floats) and
 // `accum(regs, acc)` folds them into the K x V accumulators.  The row loop is unrolled by kU with
 // all loads issued before any use so every thread keeps kU*NT 128-bit requests in flight (the
@@ -85,7 +85,9 @@ __device__ __forceinline__ bool column_reduce(int64_t M, int C, float* __restric
       accum(regs[0], acc);
     }
   }
-  // reduce across ty through shared memory
+  // reduce across ty through shared memory, then ONE atomicAdd per (k, channel) per CTA into the
+  // global accumulators `part` ([K][C] floats, zero on entry).  The last CTA to finish (ticket)
+  // returns true and owns the finalisation; it also re-zeroes the accumulators for the next call.
   const int width = K * V * cthreads;
 #pragma unroll
   for (int k = 0; k < K; ++k)
@@ -95,7 +97,7 @@ __device__ __forceinline__ bool column_reduce(int64_t M, int C, float* __restric
   for (int i = threadIdx.x; i < width; i += kBT) {
     float sum = 0.f;
     for (int t = 0; t < ty_n; ++t) sum += smem[t * width + i];
-    part[(int64_t)blockIdx.x * width + i] = sum;    // i = k*C + c  (V*cthreads == C)
+    atomicAdd(part + i, sum);                       // i = k*C + c  (V*cthreads == C)
   }
   __shared__ bool last;
   __threadfence();
@@ -115,61 +117,40 @@ __global__ void __launch_bounds__(kBT)
 bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, float* __restrict__ part,
                 unsigned int* __restrict__ ticket, BnParams p) {
   constexpr int V = Vec<T>::N;
+  // Shifted moments: accumulate sum(x - pivot) and sum((x - pivot)^2) with pivot = running mean
+  // (an estimate of the batch mean), so var = E[d^2] - E[d]^2 has no catastrophic cancellation in
+  // fp32 even when |mean| >> std.  Every CTA reads the same pivot: running_mean is only rewritten
+  // by the last CTA after all others are done.
+  const int cg = threadIdx.x % (C / V);
+  float pv[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) pv[j] = p.running_mean ? p.running_mean[cg * V + j] : 0.f;
   bool last = column_reduce<T, 2, 1>(M, C, part, ticket,
       [&](int64_t r, int c0, float (*regs)[V]) { Vec<T>::ld(x + r * C + c0, regs[0]); },
       [&](float (*regs)[V], float (*acc)[V]) {
 #pragma unroll
-        for (int j = 0; j < V; ++j) { acc[0][j] += regs[0][j]; acc[1][j] = fmaf(regs[0][j], regs[0][j], acc[1][j]); }
+        for (int j = 0; j < V; ++j) { float d = regs[0][j] - pv[j]; acc[0][j] += d; acc[1][j] = fmaf(d, d, acc[1][j]); }
       });
   if (!last) return;
-  // ---- final merge in the last CTA.  Per-CTA partial sums are fp32 over <= a few thousand
-  // elements (accurate); the cross-CTA totals are accumulated in fp64 so var = E[x^2]-E[x]^2 has no
-  // cancellation problem and the loop is a plain, pipelinable sum (no dependent divide chain).
-  // Thread t handles channel c = t % Cc and every G-th CTA; the G partial sums meet in smem.
-  extern __shared__ float smem[];
-  double* dsm = reinterpret_cast<double*>(smem);
-  const int Cc = C < kBT ? C : kBT;
-  const int G = kBT / Cc;
-  const int g = threadIdx.x / Cc;
-  const int nblk = (int)gridDim.x;
-  for (int cbase = 0; cbase < C; cbase += Cc) {
-    const int c = cbase + threadIdx.x % Cc;
-    double s0 = 0.0, s1 = 0.0;
-    int b = g;
-    for (; b + 3 * G < nblk; b += 4 * G) {
-      float a0 = __ldcg(part + (int64_t)b * 2 * C + c), q0 = __ldcg(part + (int64_t)b * 2 * C + C + c);
-      float a1 = __ldcg(part + (int64_t)(b + G) * 2 * C + c), q1 = __ldcg(part + (int64_t)(b + G) * 2 * C + C + c);
-      float a2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + c), q2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + C + c);
-      float a3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + c), q3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + C + c);
-      s0 += ((double)a0 + (double)a1) + ((double)a2 + (double)a3);
-      s1 += ((double)q0 + (double)q1) + ((double)q2 + (double)q3);
-    }
-    for (; b < nblk; b += G) {
-      s0 += (double)__ldcg(part + (int64_t)b * 2 * C + c);
-      s1 += (double)__ldcg(part + (int64_t)b * 2 * C + C + c);
-    }
-    __syncthreads();
-    dsm[(g * Cc + threadIdx.x % Cc) * 2 + 0] = s0;
-    dsm[(g * Cc + threadIdx.x % Cc) * 2 + 1] = s1;
-    __syncthreads();
-    if (g == 0) {
-      for (int k = 1; k < G; ++k) { s0 += dsm[(k * Cc + threadIdx.x) * 2]; s1 += dsm[(k * Cc + threadIdx.x) * 2 + 1]; }
-      const double n = (double)M;
-      const double mean_d = s0 / n;
-      double var_d = s1 / n - mean_d * mean_d;
-      if (var_d < 0.0) var_d = 0.0;
-      const float mean = (float)mean_d, var = (float)var_d;
-      float inv = rsqrtf(var + p.eps);
-      p.mean[c] = mean;
-      p.invstd[c] = inv;
-      float gm = p.gamma ? p.gamma[c] : 1.f, bta = p.beta ? p.beta[c] : 0.f;
-      p.scale[c] = gm * inv;
-      p.shift[c] = bta - mean * gm * inv;
-      if (p.running_mean) {
-        float unbiased = M > 1 ? (float)(var_d * n / (n - 1.0)) : var;
-        p.running_mean[c] = (1.f - p.momentum) * p.running_mean[c] + p.momentum * mean;
-        p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * unbiased;
-      }
+  const float invM = 1.f / (float)M;
+  for (int c = threadIdx.x; c < C; c += kBT) {
+    const float s0 = __ldcg(part + c), s1 = __ldcg(part + C + c);
+    part[c] = 0.f;
+    part[C + c] = 0.f;
+    const float pivot = p.running_mean ? p.running_mean[c] : 0.f;
+    const float dm = s0 * invM;
+    const float mean = pivot + dm;
+    const float var = fmaxf(s1 * invM - dm * dm, 0.f);
+    const float inv = rsqrtf(var + p.eps);
+    p.mean[c] = mean;
+    p.invstd[c] = inv;
+    const float gm = p.gamma ? p.gamma[c] : 1.f, bta = p.beta ? p.beta[c] : 0.f;
+    p.scale[c] = gm * inv;
+    p.shift[c] = bta - mean * gm * inv;
+    if (p.running_mean) {
+      const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+      p.running_mean[c] = (1.f - p.momentum) * pivot + p.momentum * mean;
+      p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * unbiased;
     }
   }
   if (threadIdx.x == 0 && p.num_batches_tracked) *p.num_batches_tracked += 1;
@@ -221,43 +202,17 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
         }
       });
   if (!last) return;
-  extern __shared__ float smem[];
   const float invM = 1.f / (float)M;
-  const int Cc = C < kBT ? C : kBT;
-  const int G = kBT / Cc;
-  const int g = threadIdx.x / Cc;
-  for (int cbase = 0; cbase < C; cbase += Cc) {
-    const int c = cbase + threadIdx.x % Cc;
-    float s0 = 0.f, s1 = 0.f;
-    {
-      const int nblk = (int)gridDim.x;
-      int b = g;
-      for (; b + 3 * G < nblk; b += 4 * G) {
-        float a0 = __ldcg(part + (int64_t)b * 2 * C + c), q0 = __ldcg(part + (int64_t)b * 2 * C + C + c);
-        float a1 = __ldcg(part + (int64_t)(b + G) * 2 * C + c), q1 = __ldcg(part + (int64_t)(b + G) * 2 * C + C + c);
-        float a2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + c), q2 = __ldcg(part + (int64_t)(b + 2 * G) * 2 * C + C + c);
-        float a3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + c), q3 = __ldcg(part + (int64_t)(b + 3 * G) * 2 * C + C + c);
-        s0 += (a0 + a1) + (a2 + a3);
-        s1 += (q0 + q1) + (q2 + q3);
-      }
-      for (; b < nblk; b += G) {
-        s0 += __ldcg(part + (int64_t)b * 2 * C + c);
-        s1 += __ldcg(part + (int64_t)b * 2 * C + C + c);
-      }
-    }
-    __syncthreads();
-    smem[(g * Cc + threadIdx.x % Cc) * 2 + 0] = s0;
-    smem[(g * Cc + threadIdx.x % Cc) * 2 + 1] = s1;
-    __syncthreads();
-    if (g == 0) {
-      for (int k = 1; k < G; ++k) { s0 += smem[(k * Cc + threadIdx.x) * 2]; s1 += smem[(k * Cc + threadIdx.x) * 2 + 1]; }
-      if (dbeta) dbeta[c] = s0;
-      if (dgamma) dgamma[c] = s1;
-      float gm = gamma ? gamma[c] : 1.f;
-      coef[c] = gm * invstd[c];                  // a
-      coef[C + c] = s0 * invM;                   // mean(dy)
-      coef[2 * C + c] = s1 * invM * invstd[c];   // mean(dy*xhat)*invstd, multiplies (x-mean)
-    }
+  for (int c = threadIdx.x; c < C; c += kBT) {
+    const float s0 = __ldcg(part + c), s1 = __ldcg(part + C + c);
+    part[c] = 0.f;
+    part[C + c] = 0.f;
+    if (dbeta) dbeta[c] = s0;
+    if (dgamma) dgamma[c] = s1;
+    const float gm = gamma ? gamma[c] : 1.f;
+    coef[c] = gm * invstd[c];                  // a
+    coef[C + c] = s0 * invM;                   // mean(dy)
+    coef[2 * C + c] = s1 * invM * invstd[c];   // mean(dy*xhat)*invstd, multiplies (x-mean)
   }
 }
 
@@ -285,9 +240,8 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __rest
 
 inline int reduce_grid(int64_t M, int C, int V) {
   int ty_n = kBT / (C / V);
-  int64_t g = (M + (int64_t)ty_n * 32 - 1) / ((int64_t)ty_n * 32);
+  int64_t g = (M + (int64_t)ty_n * 8 - 1) / ((int64_t)ty_n * 8);   // >= 8 rows per thread (one unrolled sweep)
   if (g > 4 * kNumSMs) g = 4 * kNumSMs;
-  if (g > 32768 / C) g = 32768 / C;   // bounds the serial final merge: <= 128 partial loads per thread
   if (g < 1) g = 1;
   return (int)g;
 }
@@ -302,9 +256,10 @@ inline bool shape_ok(int C, int V) { return C % V == 0 && (C / V) <= kBT && kBT 
 }  // namespace
 
 #define DETB200_BN_MAX_GRID (4 * 148)
+#define DETB200_BN_MAX_C 2048
 
-// Workspace (bytes) for one BatchNorm call: per-CTA partials [grid][2][C] floats + a ticket.
-DETB200_API int64_t detb200_bn_workspace_bytes(int C) { return (int64_t)DETB200_BN_MAX_GRID * 2 * C * 4 + 256; }
+// Workspace (bytes) for one BatchNorm call: global accumulators [2][C] floats + a ticket (all zero between calls).
+DETB200_API int64_t detb200_bn_workspace_bytes(int C) { return (int64_t)2 * C * 4 + 256; }
 
 // dtype 0 fp32 / 1 bf16.  x,y: [M, C] channels-last view.  gamma/beta/running_*/num_batches_tracked nullable.
 // mean, invstd, scale, shift: fp32 [C] outputs.  workspace must be zero-initialised once (ticket).
@@ -316,7 +271,7 @@ DETB200_API int detb200_bn_fwd_train(const void* x, void* y, int64_t M, int C, c
   if (M <= 0) return 0;
   if (!shape_ok(C, V)) { detb200_set_error("bn: C=%d unsupported for this dtype", C); return DETB200_ERR_UNSUPPORTED; }
   float* part = (float*)workspace;
-  unsigned int* ticket = (unsigned int*)((char*)workspace + (int64_t)DETB200_BN_MAX_GRID * 2 * C * 4);
+  unsigned int* ticket = (unsigned int*)((char*)workspace + (int64_t)2 * C * 4);
   BnParams p{gamma, beta, running_mean, running_var, num_batches_tracked, mean, invstd, scale, shift, momentum, eps};
   int rg = reduce_grid(M, C, V);
   size_t smem = (size_t)kBT * 2 * V * sizeof(float);
@@ -362,7 +317,7 @@ DETB200_API int detb200_bn_bwd(const void* dy, const void* x, void* dx, int64_t 
   if (M <= 0) return 0;
   if (!shape_ok(C, V)) { detb200_set_error("bn: C=%d unsupported for this dtype", C); return DETB200_ERR_UNSUPPORTED; }
   float* part = (float*)workspace;
-  unsigned int* ticket = (unsigned int*)((char*)workspace + (int64_t)DETB200_BN_MAX_GRID * 2 * C * 4);
+  unsigned int* ticket = (unsigned int*)((char*)workspace + (int64_t)2 * C * 4);
   int rg = reduce_grid(M, C, V);
   size_t smem = (size_t)kBT * 2 * V * sizeof(float);
   int64_t nvec = M * C / V;

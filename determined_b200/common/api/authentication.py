@@ -119,15 +119,24 @@ def login_with_cache(master: str, requested_user: Optional[str] = None, password
             return _session.Session(master, user, tok, cert)
     if password is None:
         password = env.get("DET_PASS")
-    if password is None and user == DEFAULT_USER:
-        password = ""
     if password is None:
-        password = getpass.getpass(f"Password for user '{user}': ")
-    sess = login(master, user, password, cert)
+        # default accounts ship with a blank password: try that before bothering the user
+        try:
+            sess = login(master, user, "", cert)
+        except errors.UnauthenticatedException:
+            import sys
+
+            if not sys.stdin or not sys.stdin.isatty():
+                raise
+            password = getpass.getpass(f"Password for user '{user}': ")
+            sess = login(master, user, password, cert)
+    else:
+        sess = login(master, user, password, cert)
     if store is not None:
         with contextlib.suppress(OSError):
             store.set_token(user, sess.token or "")
-            store.set_active(user)
+            if requested_user is None and store.get_active_user() is None:
+                store.set_active(user)     # `-u other` is a one-off; `det user login` switches
     return sess
 
 

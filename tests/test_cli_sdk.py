@@ -1,0 +1,158 @@
+"""CLI + SDK against an in-process master (no trial processes are launched)."""
+import io
+import json
+import os
+import pathlib
+import sys
+import contextlib
+
+import pytest
+import yaml
+
+from determined_b200.cli import cli
+from determined_b200.common import api
+from determined_b200.experimental import client as sdk
+from determined_b200.master import api as mapi
+from determined_b200.master import core
+
+FIX = pathlib.Path(__file__).parent / "fixtures" / "onevar_exp"
+CFG = {"name": "cli-exp", "entrypoint": "model_def:OneVarTrial", "searcher": {"name": "random", "metric": "val_loss", "max_length": 20, "max_trials": 3, "max_concurrent_trials": 2},
+       "hyperparameters": {"learning_rate": {"type": "double", "minval": 0.01, "maxval": 0.1}, "global_batch_size": 8}}
+
+
+@pytest.fixture()
+def cluster(tmp_path, monkeypatch):
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=8, launch=False, work_dir=str(tmp_path / "w"),
+                    cluster_defaults={"checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ck")}})
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    monkeypatch.setenv("DET_MASTER", m.url)
+    monkeypatch.delenv("DET_SESSION_TOKEN", raising=False)
+    yield m, tmp_path
+    m.stop()
+    srv.stop()
+
+
+def run(*argv):
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        rc = cli.main(list(argv))
+    return rc, buf.getvalue()
+
+
+def test_cli_experiment_lifecycle(cluster):
+    m, tmp = cluster
+    cfgf = tmp / "cfg.yaml"
+    cfgf.write_text(yaml.safe_dump(CFG))
+    rc, out = run("experiment", "create", str(cfgf), str(FIX), "--config", "searcher.max_trials=4", "--config", "description=from-cli")
+    assert rc == 0 and "Created experiment 1" in out
+    rc, out = run("e", "list", "--json")
+    rows = json.loads(out)
+    assert rows[0]["ID"] == 1 and rows[0]["State"] == "ACTIVE" and rows[0]["Name"] == "cli-exp"
+    rc, out = run("e", "describe", "1", "--json")
+    d = json.loads(out)[0]
+    assert d["config"]["searcher"]["max_trials"] == 4 and d["description"] == "from-cli" and len(d["trials"]) == 2
+    m.schedule_once()
+    rc, out = run("job", "list", "--json")
+    assert json.loads(out)[0]["Slots (acquired/needed)"] == "2/2"
+    rc, out = run("slot", "list", "--json")
+    assert sum(1 for s in json.loads(out) if s["Allocation ID"]) == 2
+    assert run("e", "pause", "1")[0] == 0
+    assert json.loads(run("e", "list", "--json")[1])[0]["State"] == "PAUSED"
+    assert run("e", "activate", "1")[0] == 0
+    assert run("e", "set", "priority", "1", "7")[0] == 0 and m.experiments[1].config["resources"]["priority"] == 7
+    assert run("e", "label", "add", "1", "blue")[0] == 0
+    assert "blue" in json.loads(run("e", "describe", "1", "--json")[1])[0]["labels"]
+    assert run("e", "kill", "1")[0] == 0
+    # launch=False: allocations never exit by themselves
+    for a in list(m.allocations.values()):
+        a.state = "TERMINATED"
+        a.exit_code = 137
+        m.on_allocation_exit(a)
+    assert json.loads(run("e", "list", "--json")[1])[0]["State"] == "CANCELED"
+    assert run("e", "archive", "1")[0] == 0
+    assert json.loads(run("e", "list", "--json")[1]) == []
+    assert run("e", "delete", "1", "--yes")[0] == 0
+    assert run("e", "describe", "1")[0] == 1
+
+
+def test_cli_misc_commands(cluster):
+    m, tmp = cluster
+    assert run("master", "info")[0] == 0
+    rc, out = run("agent", "list", "--json")
+    assert json.loads(out)[0]["Slots"] == 8
+    rc, out = run("resource-pool", "list", "--json")
+    assert json.loads(out)[0]["Scheduler"] == "FAIR_SHARE"
+    t = tmp / "t.yaml"
+    t.write_text("max_restarts: 0\nresources: {slots_per_trial: 2}\n")
+    assert run("template", "set", "small", str(t))[0] == 0
+    assert "max_restarts: 0" in run("template", "describe", "small")[1]
+    cfgf = tmp / "cfg.yaml"
+    cfgf.write_text(yaml.safe_dump(CFG))
+    assert run("e", "create", str(cfgf), str(FIX), "--template", "small", "--paused")[0] == 0
+    assert m.experiments[1].config["max_restarts"] == 0 and m.experiments[1].slots_per_trial() == 2
+    rc, out = run("preview-search", str(cfgf))
+    assert rc == 0 and "train 20" in out
+    assert run("user", "create", "alice")[0] == 1           # only admins may create users
+    assert run("-u", "admin", "user", "create", "alice")[0] == 0
+    assert any(u["Username"] == "alice" for u in json.loads(run("user", "list", "--json")[1]))
+    assert "determined" in run("user", "whoami")[1]
+    assert run("workspace", "create", "ws1")[0] == 0 and run("workspace", "create-project", "ws1", "p1")[0] == 0
+    assert json.loads(run("workspace", "list-projects", "ws1", "--json")[1])[0]["Name"] == "p1"
+    assert run("slot", "disable", m.agent_id, "3")[0] == 0
+    assert m.pool.agents[m.agent_id].slot_enabled[3] is False
+
+
+def test_sdk_checkpoints_and_models(cluster):
+    m, tmp = cluster
+    d = sdk.Determined(m.url)
+    exp = d.create_experiment(CFG, str(FIX))
+    assert exp.state == sdk.ExperimentState.ACTIVE and len(exp.list_trials()) == 2
+    t = exp.list_trials()[0]
+    sess = api.authentication.login(m.url, "determined", "")
+    # fake what a harness would report for trial t
+    ck_store = tmp / "ck"
+    for i, (steps, loss) in enumerate([(10, 0.5), (20, 0.2)]):
+        uuid = f"00000000-0000-0000-0000-00000000000{i}"
+        (ck_store / uuid).mkdir(parents=True)
+        (ck_store / uuid / "state_dict.pth").write_bytes(b"w" * 10)
+        sess.post(f"/api/v1/trials/{t.id}/metrics", json={"group": "validation", "metrics": {"trialId": t.id, "stepsCompleted": steps, "metrics": {"avgMetrics": {"val_loss": loss}}}})
+        sess.post("/api/v1/checkpoints", json={"uuid": uuid, "taskId": f"trial-{t.id}", "allocationId": "a", "state": "STATE_COMPLETED",
+                                                "resources": {"state_dict.pth": "10"}, "metadata": {"steps_completed": steps}})
+    best = exp.top_checkpoint()
+    assert best.uuid.endswith("1") and best.training["searcherMetric"] == 0.2
+    assert [c.uuid[-1] for c in exp.top_n_checkpoints(2)] == ["1", "0"]
+    assert t.select_checkpoint(latest=True).uuid.endswith("1")
+    assert t.top_checkpoint(sort_by="val_loss", smaller_is_better=False).uuid.endswith("0")
+    path = best.download(str(tmp / "dl"))
+    assert (pathlib.Path(path) / "state_dict.pth").exists() and json.loads((pathlib.Path(path) / "metadata.json").read_text())["steps_completed"] == 20
+    best.add_metadata({"note": "good"})
+    assert d.get_checkpoint(best.uuid).metadata["note"] == "good"
+    model = d.create_model("resnet", "desc", labels=["cv"])
+    v = model.register_version(best.uuid)
+    assert v.model_version == 1 and d.get_model("resnet").get_version().checkpoint.uuid == best.uuid
+    with pytest.raises(api.errors.APIException):
+        best.delete()                       # registered checkpoints are protected
+    other = d.get_checkpoint("00000000-0000-0000-0000-000000000000")
+    other.delete()
+    assert not (ck_store / other.uuid).exists()
+    assert list(t.iter_metrics("validation"))[1]["metrics"] == {"val_loss": 0.2}
+    rc, out = run("checkpoint", "describe", best.uuid, "--json")
+    assert json.loads(out)["metadata"]["note"] == "good"
+    rc, out = run("e", "list-checkpoints", str(exp.id), "--json")
+    assert len(json.loads(out)) == 2
+
+
+def test_local_test_mode_via_cli(tmp_path, monkeypatch):
+    cfgf = tmp_path / "cfg.yaml"
+    c = dict(CFG)
+    c["hyperparameters"] = {"learning_rate": 0.05, "global_batch_size": 8}
+    cfgf.write_text(yaml.safe_dump(c))
+    cwd = os.getcwd()
+    try:
+        rc, out = run("e", "create", str(cfgf), str(FIX), "--local", "--test")
+    finally:
+        os.chdir(cwd)
+        sys.path[:] = [p for p in sys.path if p != str(FIX)]
+        sys.modules.pop("model_def", None)
+    assert rc == 0 and "test succeeded" in out
