@@ -322,3 +322,84 @@ DETB200_API int detb200_scale_flat(float* x, int64_t n, const float* dyn_scale, 
   DETB200_LAUNCH_CHECK();
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// detb200_sumsq_noalloc — the same sum-of-squares reduction for callers that cannot obtain device
+// memory of their own for the scratch area.
+//
+// Who that is: a process that has already handed the whole HBM to a fixed pool or caching
+// allocator (a fresh cudaMalloc would fail or fragment the pool); a plain C caller that links this
+// library without any allocator of its own; and code on a latency-critical path that must not
+// pay cudaMalloc/cudaFree's device-wide synchronisation (it would stall the communication stream
+// that is overlapping backward).  For them the partial-sum area and the ticket live in a
+// file-scope __device__ array below, so the call needs nothing beyond its input and outputs.
+//
+// Costs and rules that come with that choice:
+//   * every GPU whose context loads this library carries the array (DETB200_SUMSQ_NOALLOC_SCRATCH_BYTES
+//     = 4864 bytes) until the process exits;
+//   * n must be <= DETB200_SUMSQ_NOALLOC_MAX_ELEMS (2^30 floats, 4 GiB): the array holds a fixed
+//     1184 fp32 partials and the variant is only validated up to that length; larger inputs are
+//     refused with DETB200_ERR_TOO_LARGE rather than silently losing accuracy;
+//   * the array is shared by every call on that device and keeps whatever the previous call left,
+//     so the ticket word is cleared on the caller's stream before each launch, and two calls that
+//     can overlap on the GPU (different streams, no ordering between them) race on it — order them;
+//   * the first call on a device looks the array's device address up (cudaGetSymbolAddress) with
+//     that device current; make that first call outside of any stream capture.
+// It never calls cudaMalloc, cudaFree or any allocating library routine.
+// ---------------------------------------------------------------------------------------------
+#define DETB200_SUMSQ_NOALLOC_MAX_ELEMS (1ll << 30)
+#define DETB200_SUMSQ_NOALLOC_SCRATCH_BYTES (((DETB200_SUMSQ_MAX_BLOCKS + 1) * 4 + 255) / 256 * 256)
+#define DETB200_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_sumsq_noalloc_scratch[DETB200_SUMSQ_NOALLOC_SCRATCH_BYTES];
+
+#include <mutex>
+
+namespace {
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[DETB200_NOALLOC_MAX_DEVICES] = {nullptr};
+
+// In host code `g_sumsq_noalloc_scratch` is only a handle for the runtime, not an address the GPU
+// can use; the real device address is per device and must be asked for with that device current.
+int noalloc_scratch_for_current_device(void** out) {
+  int dev = -1;
+  DETB200_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= DETB200_NOALLOC_MAX_DEVICES) {
+    detb200_set_error("sumsq_noalloc: device index %d outside [0,%d)", dev, DETB200_NOALLOC_MAX_DEVICES);
+    return DETB200_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    DETB200_CHECK(cudaGetSymbolAddress(&p, g_sumsq_noalloc_scratch));
+    if (p == nullptr) { detb200_set_error("sumsq_noalloc: cudaGetSymbolAddress returned NULL"); return DETB200_ERR_UNSUPPORTED; }
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+DETB200_API int64_t detb200_sumsq_noalloc_max_elems() { return DETB200_SUMSQ_NOALLOC_MAX_ELEMS; }
+
+DETB200_API int detb200_sumsq_noalloc(const float* x, int64_t n, float* out, int* nonfinite_flag, int accumulate,
+                                      cudaStream_t stream) {
+  if (!x || !out || n < 0) { detb200_set_error("sumsq_noalloc: bad argument"); return DETB200_ERR_BAD_ARG; }
+  if (((uintptr_t)x & 15) != 0) { detb200_set_error("sumsq_noalloc: x must be 16-byte aligned"); return DETB200_ERR_BAD_ARG; }
+  if (n > DETB200_SUMSQ_NOALLOC_MAX_ELEMS) {
+    detb200_set_error("sumsq_noalloc: n=%lld exceeds the built-in scratch limit of %lld elements; use detb200_sumsq with "
+                      "caller-provided scratch", (long long)n, (long long)DETB200_SUMSQ_NOALLOC_MAX_ELEMS);
+    return DETB200_ERR_TOO_LARGE;
+  }
+  void* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  float* partials = (float*)scratch;
+  unsigned int* ticket = (unsigned int*)(partials + DETB200_SUMSQ_MAX_BLOCKS);
+  // the array remembers the previous call: the ticket must read 0 when the kernel starts
+  DETB200_CHECK(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), stream));
+  int grid = grid_for(n, kThreads, kVec * 4, DETB200_SUMSQ_MAX_BLOCKS);
+  sumsq_kernel<<<grid, kThreads, 0, stream>>>(x, n, partials, ticket, out, nonfinite_flag, accumulate);
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}

@@ -60,6 +60,17 @@ int detb200_adadelta_flat(float* p, float* g, float* square_avg, float* acc_delt
 int64_t detb200_sumsq_scratch_bytes(void);
 int detb200_sumsq(const float* x, int64_t n, void* scratch, float* out, int* nonfinite_flag, int accumulate,
                   detb200_stream_t stream);
+/* Same reduction with the scratch built into the library (a file-scope __device__ array of 4864
+ * bytes per GPU, held until exit), for callers that have no device memory to give: processes whose
+ * HBM is entirely owned by a pool/caching allocator, C callers without an allocator, and hot paths
+ * that cannot afford cudaMalloc's device-wide sync.  No counterpart in the reference (it has no
+ * native code at all).  n <= detb200_sumsq_noalloc_max_elems() (2^30) or DETB200_ERR_TOO_LARGE.
+ * Allocates nothing.  Calls on one device share the array: order them on the GPU, overlapping
+ * calls race.  The first call on a device resolves the array's address; do it before any stream
+ * capture. */
+int64_t detb200_sumsq_noalloc_max_elems(void);
+int detb200_sumsq_noalloc(const float* x, int64_t n, float* out, int* nonfinite_flag /* nullable */, int accumulate,
+                          detb200_stream_t stream);
 /* coef = extra_scale * min(1, max_norm / (sqrt(sum(terms)) + 1e-6)); norm_out nullable. */
 int detb200_clip_coef(const float* sumsq_terms, int nterms, float max_norm, float extra_scale, float* coef_out,
                       float* norm_out, detb200_stream_t stream);
