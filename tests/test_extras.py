@@ -1,0 +1,234 @@
+"""Custom searcher (client side) against a live master, unmanaged core_v2, HF/Lightning callbacks,
+batch inference, and the legacy workload sequencer."""
+import json
+import pathlib
+import types
+import uuid
+
+import pytest
+import torch
+import yaml
+
+from determined_b200 import core, searcher, workload
+from determined_b200.common import api
+from determined_b200.master import api as mapi
+from determined_b200.master import core as mcore
+
+FIX = pathlib.Path(__file__).parent / "fixtures" / "onevar_exp"
+
+
+@pytest.fixture()
+def cluster(tmp_path, monkeypatch):
+    m = mcore.Master(db_path=str(tmp_path / "m.db"), num_slots=4, work_dir=str(tmp_path / "work"),
+                     cluster_defaults={"checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpt")}})
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    monkeypatch.setenv("DET_MASTER", m.url)
+    monkeypatch.delenv("DET_SESSION_TOKEN", raising=False)
+    sess = api.authentication.login(m.url, "determined", "")
+    yield m, sess, tmp_path
+    m.stop()
+    srv.stop()
+
+
+class TwoLRSearch(searcher.SearchMethod):
+    """Two trials with fixed learning rates, each trained 16 batches; closes both, then shuts down."""
+
+    def __init__(self):
+        self.lrs = [0.05, 0.2]
+        self.results = {}
+        self.closed = 0
+
+    def initial_operations(self, st):
+        ops = []
+        for lr in self.lrs:
+            rid = uuid.uuid4()
+            ops += [searcher.Create(rid, {"learning_rate": lr, "batch_size": 8, "global_batch_size": 8}, None), searcher.ValidateAfter(rid, 16)]
+        return ops
+
+    def on_trial_created(self, st, rid):
+        return []
+
+    def on_validation_completed(self, st, rid, metric, train_length):
+        self.results[str(rid)] = metric
+        return [searcher.Close(rid)]
+
+    def on_trial_closed(self, st, rid):
+        self.closed += 1
+        return [searcher.Shutdown()] if self.closed == len(self.lrs) else []
+
+    def on_trial_exited_early(self, st, rid, reason):
+        return [searcher.Shutdown(failure=True)]
+
+    def progress(self, st):
+        return self.closed / len(self.lrs)
+
+    def save_method_state(self, path):
+        (path / "m.json").write_text(json.dumps({"results": self.results, "closed": self.closed}))
+
+    def load_method_state(self, path):
+        d = json.loads((path / "m.json").read_text())
+        self.results, self.closed = d["results"], d["closed"]
+
+
+def test_local_search_runner_drives_custom_experiment(cluster):
+    m, sess, tmp = cluster
+    cfg = {"name": "custom", "entrypoint": "model_def:OneVarTrial", "searcher": {"name": "custom", "metric": "val_loss", "unit": "batches"},
+           "hyperparameters": {"learning_rate": 0.1, "batch_size": 8, "global_batch_size": 8}, "scheduling_unit": 8,
+           "resources": {"slots_per_trial": 1}, "max_restarts": 0}
+    method = TwoLRSearch()
+    runner = searcher.LocalSearchRunner(method, searcher_dir=tmp / "search", session=sess)
+    eid = runner.run(cfg, model_dir=str(FIX))
+    exp = sess.get(f"/api/v1/experiments/{eid}").json()["experiment"]
+    assert exp["state"] == "STATE_COMPLETED"
+    trials = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"]
+    assert len(trials) == 2 and all(t["state"] == "STATE_COMPLETED" for t in trials)
+    assert len(method.results) == 2 and all(isinstance(v, float) for v in method.results.values())
+    assert sorted(round(t["hparams"]["learning_rate"], 3) for t in trials) == [0.05, 0.2]
+    # state was checkpointed after every event batch and is loadable by a fresh method
+    m2 = TwoLRSearch()
+    st, got = m2.load(tmp / "search" / f"exp_{eid}")
+    assert got == eid and m2.closed == 2 and len(st.trials_closed) == 2 and len(st.trials_created) == 2
+
+
+def test_core_v2_unmanaged_trial_reports(cluster):
+    from determined_b200.experimental import core_v2
+
+    m, sess, tmp = cluster
+    core_v2.init(defaults=core_v2.DefaultConfig(name="unmanaged", hparams={"lr": 0.5}, searcher={"name": "single", "metric": "loss", "max_length": 3}),
+                 unmanaged=core_v2.UnmanagedConfig(external_experiment_id="ext-e", external_trial_id="ext-t"),
+                 checkpoint_storage=str(tmp / "ck2"))
+    try:
+        for i in range(3):
+            core_v2.train.report_training_metrics(steps_completed=i + 1, metrics={"loss": 1.0 / (i + 1)})
+        core_v2.train.report_validation_metrics(steps_completed=3, metrics={"loss": 0.25})
+        with core_v2.checkpoint.store_path({"steps_completed": 3}) as (p, uid):
+            (p / "w.bin").write_bytes(b"abc")
+        assert "/det/experiments/" in core_v2.url_reverse_webui_exp_view()
+    finally:
+        core_v2.close()
+    exps = sess.get("/api/v1/experiments").json()["experiments"]
+    e = [x for x in exps if x["name"] == "unmanaged"][0]
+    assert e["unmanaged"] is True
+    t = sess.get(f"/api/v1/experiments/{e['id']}/trials").json()["trials"][0]
+    vals = sess.get(f"/api/v1/trials/{t['id']}/metrics", params={"group": "validation"}).json()["metrics"]
+    assert vals[-1]["metrics"]["avgMetrics"]["loss"] == 0.25 and vals[-1]["totalBatches"] == 3
+    cks = sess.get(f"/api/v1/trials/{t['id']}/checkpoints").json()["checkpoints"]
+    assert len(cks) == 1 and "w.bin" in cks[0]["resources"]
+    # same external ids -> the same trial is continued, not duplicated
+    core_v2.init(defaults=core_v2.DefaultConfig(name="unmanaged"), unmanaged=core_v2.UnmanagedConfig(external_experiment_id="ext-e", external_trial_id="ext-t"),
+                 checkpoint_storage=str(tmp / "ck2"))
+    try:
+        assert core_v2.info.trial.trial_id == t["id"]
+        assert core_v2.info.latest_checkpoint == cks[0]["uuid"]
+    finally:
+        core_v2.close()
+
+
+class _FakeTrain:
+    def __init__(self):
+        self.training, self.validation, self.progress = [], [], []
+
+    def report_training_metrics(self, steps_completed, metrics):
+        self.training.append((steps_completed, metrics))
+
+    def report_validation_metrics(self, steps_completed, metrics):
+        self.validation.append((steps_completed, metrics))
+
+    def report_progress(self, p):
+        self.progress.append(p)
+
+
+def test_hf_det_callback_reports_and_stops(tmp_path):
+    from determined_b200 import transformers as det_tf
+
+    with core._dummy_init(checkpoint_storage=str(tmp_path / "ck"), searcher_length=6) as ctx:
+        args = types.SimpleNamespace(max_steps=6, num_train_epochs=1, eval_steps=3, save_steps=3, output_dir=str(tmp_path / "out"),
+                                     overwrite_output_dir=True, resume_from_checkpoint=None, deepspeed=None, logging_steps=1)
+        cb = det_tf.DetCallback(ctx, args)
+        state = types.SimpleNamespace(global_step=0, epoch=0.0, is_world_process_zero=True, max_steps=6, best_model_checkpoint=None)
+        control = types.SimpleNamespace(should_training_stop=False, should_save=False, should_evaluate=False)
+        seen = []
+        orig_t, orig_v = ctx.train.report_training_metrics, ctx.train.report_validation_metrics
+        ctx.train.report_training_metrics = lambda steps_completed, metrics: (seen.append(("t", steps_completed, metrics)), orig_t(steps_completed, metrics))
+        ctx.train.report_validation_metrics = lambda steps_completed, metrics: (seen.append(("v", steps_completed, metrics)), orig_v(steps_completed, metrics))
+        for step in range(1, 7):
+            state.global_step = step
+            cb.on_log(args, state, control, logs={"loss": 1.0 / step, "learning_rate": 1e-3})
+            if step % 3 == 0:
+                cb.on_log(args, state, control, logs={"eval_loss": 0.5 / step, "eval_runtime": 1.0})
+                out = pathlib.Path(args.output_dir) / f"checkpoint-{step}"
+                out.mkdir(parents=True, exist_ok=True)
+                (out / "model.bin").write_bytes(b"x")
+                cb.on_save(args, state, control)
+            cb.on_step_end(args, state, control)
+        kinds = [k for k, *_ in seen]
+        assert kinds.count("t") == 6 and kinds.count("v") == 2
+        assert control.should_training_stop          # the single searcher op (6 batches) is complete
+        assert det_tf.get_metric_type({"eval_loss": 1}) == "eval" and det_tf.get_metric_type({"loss": 1}) == "train_progress"
+
+
+def test_torch_batch_process(tmp_path):
+    from determined_b200.pytorch import experimental as px
+
+    seen = []
+
+    class Proc(px.TorchBatchProcessor):
+        def __init__(self, context):
+            self.context = context
+            self.model = context.prepare_model_for_inference(torch.nn.Linear(2, 1))
+            self.n = 0
+
+        def process_batch(self, batch, batch_idx):
+            x = self.context.to_device(batch)
+            with torch.no_grad():
+                self.model(x)
+            seen.append(batch_idx)
+            self.n += 1
+
+        def on_checkpoint_start(self):
+            seen.append("ckpt")
+
+        def on_finish(self):
+            seen.append("done")
+
+    ds = torch.utils.data.TensorDataset(torch.randn(20, 2))
+
+    class DS(torch.utils.data.Dataset):
+        def __len__(self):
+            return 20
+
+        def __getitem__(self, i):
+            return ds[i][0]
+
+    px.torch_batch_process(Proc, DS(), batch_size=4, checkpoint_interval=2, distributed_context=core.DummyDistributedContext())
+    assert [s for s in seen if isinstance(s, int)] == [0, 1, 2, 3, 4]
+    assert seen.count("ckpt") >= 2 and seen[-1] == "done"
+
+
+def test_workload_sequencer_orders_train_validate_checkpoint(tmp_path):
+    from determined_b200.layers import WorkloadSequencer
+
+    exp_conf = {"searcher": {"name": "single", "metric": "loss", "smaller_is_better": True, "max_length": {"batches": 8}},
+                "scheduling_unit": 2, "min_validation_period": {"batches": 4}, "min_checkpoint_period": {"batches": 4},
+                "checkpoint_policy": "best", "records_per_epoch": 0}
+    with core._dummy_init(checkpoint_storage=str(tmp_path / "ck"), searcher_length=8) as ctx:
+        ctx.searcher._units = core.Unit.BATCHES
+        seq = WorkloadSequencer(ctx, exp_conf, trial_id=1, exp_id=1, global_batch_size=4)
+        kinds = []
+        for wkld, respond in seq:
+            kinds.append((wkld.kind.name, wkld.num_batches, wkld.total_batches_processed))
+            if wkld.kind == workload.Workload.Kind.RUN_STEP:
+                respond({"metrics": {"avg_metrics": {"loss": 1.0}, "batch_metrics": [{"loss": 1.0}] * wkld.num_batches}, "stop_requested": False})
+            elif wkld.kind == workload.Workload.Kind.COMPUTE_VALIDATION_METRICS:
+                respond({"metrics": {"validation_metrics": {"loss": 1.0 / (1 + wkld.total_batches_processed)}}, "stop_requested": False})
+            else:
+                respond({"uuid": str(uuid.uuid4())})
+    names = [k for k, *_ in kinds]
+    assert names[:2] == ["RUN_STEP", "RUN_STEP"]
+    assert names.count("RUN_STEP") == 4 and names.count("COMPUTE_VALIDATION_METRICS") == 2
+    assert names.count("CHECKPOINT_MODEL") >= 2
+    i4 = names.index("COMPUTE_VALIDATION_METRICS")
+    assert kinds[i4][2] == 4
+    st = seq.get_state()
+    assert st["steps_completed"] == 8 if "steps_completed" in st else True
