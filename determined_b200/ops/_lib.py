@@ -82,9 +82,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_bn_apply", i, [p, p, i64, i, p, p, i, i, p])
     _sig(lib, "detb200_bn_bwd", i, [p, p, p, i64, i, p, p, p, p, p, p, p, i, p])
     # tcgen05 GEMM family (csrc/gemm_sm100.cu)
-    _sig(lib, "detb200_gemm_bf16", i, [p, p, p, p, i, i, i, i, i, p])
-    _sig(lib, "detb200_ag_gemm_bf16", i, [p, POINTER(c_void_p), p, p, i, i, i, i, i, i, p])
-    _sig(lib, "detb200_gemm_workspace_bytes", i64, [])
+    _sig(lib, "detb200_gemm_bf16", i, [p, p, p, p, p, i64, i64, i64, i64, i64, i64, i64, i, i, i, i, i, i, p])
     # attention (csrc/attention.cu)
     _sig(lib, "detb200_attn_fwd", i, [p, p, p, p, p, i, i, i, i, f, i, p])
     _sig(lib, "detb200_attn_bwd", i, [p, p, p, p, p, p, p, p, p, p, i, i, i, i, f, i, p])

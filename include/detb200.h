@@ -152,6 +152,23 @@ int detb200_xent_bwd(const void* logits, const int64_t* target, const float* lse
                      void* dlogits /* may alias logits */, int64_t rows, int vocab, int64_t ignore_index,
                      int dtype, detb200_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * bf16 GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed operands (csrc/gemm_sm100.cu).
+ * C[M,N] (+)= op(A) * op(B)^T with fp32 accumulation.  Reference: every nn.Linear / matmul the user's
+ * model runs under DDP or DeepSpeed (harness/determined/pytorch/_pytorch_context.py:296-299 wraps the
+ * model, the GEMMs themselves are library calls there).
+ *   a_mn_major = 0: A is [M,K] row-major (lda = row stride);  1: A is stored [K,M] (lda = stride of k)
+ *   b_mn_major = 0: B is [N,K] row-major (nn.Linear weight);  1: B is stored [K,N]
+ *   epilogue: 0 none, 1 GELU(erf), 2 GELU(tanh), 3 ReLU  -> `aux` (nullable) receives the pre-activation (bf16);
+ *             4/5/6: multiply by GELU'(erf) / GELU'(tanh) / ReLU' of the pre-activation read from `aux`.
+ *   out_fp32: C is fp32 (else bf16); accumulate: C += result (e.g. weight gradients straight into a flat fp32 buffer).
+ * All operand bases 16-byte aligned, all row strides multiples of 8 elements.
+ * ------------------------------------------------------------------------------------------- */
+int detb200_gemm_bf16(const void* A, const void* B, void* C, const void* bias /* nullable, [N] */, void* aux /* nullable */,
+                      int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t ldaux,
+                      int a_mn_major, int b_mn_major, int out_fp32, int bias_fp32, int epilogue, int accumulate,
+                      detb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
