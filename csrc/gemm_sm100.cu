@@ -43,6 +43,21 @@ struct GemmArgs {
   unsigned int ready_value;
   int rows_per_shard;
   int m_block_rotation;          // first m-block to work on (own shard first)
+  // optional fused reduce-scatter: tiles of row shard d are stored (bf16) into rank d's receive slot
+  int rs_world, rs_rank;
+  unsigned int rs_epoch;
+  unsigned int* rs_entered;            // my ctrl: entered[r] written by rank r at kernel start
+  unsigned int* rs_peer_count[8];      // rank d's counter for partials coming from me
+};
+
+struct TmapArray { CUtensorMap m[8]; };
+
+// Control block of the fused GEMM+collective kernels (one per rank, symmetric memory, zero-initialised).
+struct GemmCtrl {
+  unsigned int entered[16];     // entered[r]: rank r has started call number `epoch` (its earlier work is complete)
+  unsigned int a_ready[16];     // a_ready[s]: arrivals for gathered shard s (monotonic)
+  unsigned int rs_count[16];    // rs_count[s]: partial tiles received from rank s (monotonic)
+  unsigned int pad[16];
 };
 
 template <int kBlockN> struct Cfg {
@@ -68,16 +83,45 @@ __device__ __forceinline__ float dgelu_tanh(float x) {
   return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
 }
 
-__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
   unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// spin until *p - target >= 0 (wrap-safe), trapping after `ns`
+__device__ __forceinline__ void wait_counter_sys(const unsigned int* p, unsigned int target, const char* what, int idx) {
+  if ((int)(ld_acquire_sys_u32(p) - target) >= 0) return;
+  const uint64_t t0 = globaltimer_ns();
+  while ((int)(ld_acquire_sys_u32(p) - target) < 0) {
+    if (globaltimer_ns() - t0 > 20000000000ull) {
+      printf("detb200: timed out waiting for %s[%d] (have %u want %u) block %d\n", what, idx, ld_acquire_sys_u32(p), target, blockIdx.x);
+      __trap();
+    }
+    __nanosleep(100);
+  }
+}
 
-template <int kBlockN, bool kAMN, bool kBMN>
-__global__ void __launch_bounds__(kThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_aux, const GemmArgs args) {
+// Shard-major tile walk: t = (shard_idx * nt + n_blk) * mb_per_shard + m_local, shards rotated by `rotation` m-blocks.
+__device__ __forceinline__ void tile_coords(int t, int mt, int nt, int mb_per_shard, int rotation, int& m_blk, int& n_blk) {
+  const int tiles_per_shard = mb_per_shard * nt;
+  const int shard_idx = t / tiles_per_shard;
+  const int r = t - shard_idx * tiles_per_shard;
+  n_blk = r / mb_per_shard;
+  m_blk = shard_idx * mb_per_shard + (r - n_blk * mb_per_shard) + rotation;
+  if (m_blk >= mt) m_blk -= mt;
+}
+
+// kRS: the epilogue ships bf16 partial tiles to the rank owning the row shard instead of writing C.
+template <int kBlockN, bool kAMN, bool kBMN, bool kRS>
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_c,
+                                          const CUtensorMap& tmap_aux, const CUtensorMap* tmap_rs, const GemmArgs& args, const int cta,
+                                          const int ncta) {
   using C = Cfg<kBlockN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -96,6 +140,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int mt = (args.M + kBlockM - 1) / kBlockM, nt = (args.N + kBlockN - 1) / kBlockN;
   const int num_tiles = mt * nt;
   const int kb_count = (args.K + kBlockK - 1) / kBlockK;
+  // tiles are walked shard by shard (all column blocks of a row shard before the next shard) so that a fused
+  // collective can overlap: the plain GEMM is the one-shard case
+  const int mb_per_shard = (args.rows_per_shard > 0 && args.rows_per_shard < args.M) ? args.rows_per_shard / kBlockM : mt;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -125,25 +172,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        int m_blk = t % mt;
-        const int n_blk = t / mt;
-        if (args.m_block_rotation) m_blk = (m_blk + args.m_block_rotation) % mt;
+      for (int t = cta; t < num_tiles; t += ncta) {
+        int m_blk, n_blk;
+        tile_coords(t, mt, nt, mb_per_shard, args.m_block_rotation, m_blk, n_blk);
         if (args.a_ready != nullptr) {
           // rows of this tile may span two shards; wait for both
           const int s0 = (m_blk * kBlockM) / args.rows_per_shard;
           const int last_row = min(m_blk * kBlockM + kBlockM, args.M) - 1;
           const int s1 = last_row / args.rows_per_shard;
-          const uint64_t t0 = globaltimer_ns();
-          for (int s = s0; s <= s1; ++s) {
-            while (ld_acquire_gpu(args.a_ready + s) < args.ready_value) {
-              if (globaltimer_ns() - t0 > 10000000000ull) {
-                printf("detb200: gemm timed out waiting for A shard %d\n", s);
-                __trap();
-              }
-              __nanosleep(64);
-            }
-          }
+          for (int s = s0; s <= s1; ++s) wait_counter_sys(args.a_ready + s, args.ready_value, "a_ready", s);
           fence_proxy_async();   // generic-proxy writes of the gather -> async-proxy (TMA) reads
         }
         for (int kb = 0; kb < kb_count; ++kb) {
@@ -177,7 +214,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = cta; t < num_tiles; t += ncta) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kBlockN;
@@ -233,14 +270,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     };
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      int m_blk = t % mt;
-      const int n_blk = t / mt;
-      if (args.m_block_rotation) m_blk = (m_blk + args.m_block_rotation) % mt;
+    for (int t = cta; t < num_tiles; t += ncta) {
+      int m_blk, n_blk;
+      tile_coords(t, mt, nt, mb_per_shard, args.m_block_rotation, m_blk, n_blk);
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const int gm0 = m_blk * kBlockM + q * 32;          // first row of this warp's box
+      int gm0 = m_blk * kBlockM + q * 32;                // first row of this warp's box
       const int gm = m_blk * kBlockM + row_in_tile;
+      const CUtensorMap* tm_out = &tmap_c;
+      int shard = 0;
+      if (kRS) {
+        shard = (m_blk * kBlockM) / args.rows_per_shard;
+        tm_out = tmap_rs + shard;
+        gm0 -= shard * args.rows_per_shard;
+        // the owner must have left its previous reduction before its receive slots are overwritten
+        if (shard != args.rs_rank) wait_counter_sys(args.rs_entered + shard, args.rs_epoch, "entered", shard);
+      }
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kBlockN;
 #pragma unroll 1
       for (int c = 0; c < kBlockN; c += 64) {
@@ -312,14 +357,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
           }
         }
-        if (args.out_fp32) {
-          emit(&tmap_c, r, gn, gm0, args.accumulate != 0);
-          if (gn + 32 < args.N) emit(&tmap_c, r + 32, gn + 32, gm0, args.accumulate != 0);
+        if (!kRS && args.out_fp32) {
+          emit(tm_out, r, gn, gm0, args.accumulate != 0);
+          if (gn + 32 < args.N) emit(tm_out, r + 32, gn + 32, gm0, args.accumulate != 0);
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j) packed[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
-          emit(&tmap_c, packed, gn, gm0, args.accumulate != 0);
+          emit(tm_out, packed, gn, gm0, !kRS && args.accumulate != 0);
         }
+      }
+      if (kRS) {
+        // partial rows of this warp have fully landed at the owner -> count one arrival there
+        if (lane == 0) {
+          tma_store_wait<0>();
+          fence_proxy_async();
+          red_add_release_sys(args.rs_peer_count[shard], 1u);
+        }
+        __syncwarp();
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
@@ -331,6 +385,157 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+template <int kBlockN, bool kAMN, bool kBMN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_aux, const GemmArgs args) {
+  gemm_body<kBlockN, kAMN, kBMN, false>(tmap_a, tmap_b, tmap_c, tmap_aux, nullptr, args, blockIdx.x, gridDim.x);
+}
+
+// ---- all-gather fused GEMM --------------------------------------------------------------------------
+// CTAs [0, n_gemm) run the GEMM over the gathered A; the remaining CTAs push this rank's row shard of A
+// into every peer's copy of the gather buffer (posted NVLink stores) and count arrivals in the peer's
+// a_ready[rank].  The GEMM starts with its own shard and consumes remote shards in the order they are sent.
+struct AgArgs {
+  uint8_t* peer_a[16];         // base of the [T, lda] gather buffer on every rank (peer-mapped)
+  GemmCtrl* peer_ctrl[16];
+  int rank, world, n_gemm;
+  int rows_per_shard;
+  int64_t row_bytes, ld_bytes;
+  unsigned int epoch;
+};
+
+// One thread per pusher CTA drives a ring of bulk copies: global (local HBM) -> smem -> peer global over NVLink.
+// kPushBufs x 16 KiB in flight per CTA; no registers or generic-proxy traffic involved.
+constexpr int kPushBufs = 12;
+constexpr int kPushLookahead = 8;
+constexpr uint32_t kPushChunk = 16384;
+
+__device__ __forceinline__ void ag_pusher(const AgArgs& ag, const int c, const int nc) {
+  extern __shared__ uint8_t smem_raw[];
+  GemmCtrl* me = ag.peer_ctrl[ag.rank];
+  if (c == 0 && threadIdx.x < ag.world && (int)threadIdx.x != ag.rank)
+    st_release_sys_u32(&ag.peer_ctrl[threadIdx.x]->entered[ag.rank], ag.epoch);   // my shard is final, my old gather data is dead
+  if (threadIdx.x != 0) return;
+  red_add_release_sys(&me->a_ready[ag.rank], 1u);                                  // own shard needs no copy
+  const uint32_t buf0 = (smem_u32(smem_raw) + 127u) & ~127u;
+  const uint32_t bar0 = buf0 + kPushBufs * kPushChunk;
+  for (int b = 0; b < kPushBufs; ++b) mbar_init(bar0 + 8u * b, 1);
+  fence_mbar_init();
+  // the shard as a list of contiguous pieces: whole shard if rows are dense, else one piece per row
+  const bool dense = ag.ld_bytes == ag.row_bytes;
+  const int64_t piece_bytes = dense ? (int64_t)ag.rows_per_shard * ag.row_bytes : ag.row_bytes;
+  const int64_t n_pieces = dense ? 1 : ag.rows_per_shard;
+  const int64_t chunks_per_piece = (piece_bytes + kPushChunk - 1) / kPushChunk;
+  const int64_t n_chunks = n_pieces * chunks_per_piece;
+  const int64_t per = (n_chunks + nc - 1) / nc;
+  const int64_t lo = (int64_t)c * per, hi = (lo + per < n_chunks) ? lo + per : n_chunks;
+  const int64_t shard_off = (int64_t)ag.rank * ag.rows_per_shard * ag.ld_bytes;
+  auto locate = [&](int64_t ch, int64_t& off, uint32_t& bytes) {
+    const int64_t piece = ch / chunks_per_piece, k = ch - piece * chunks_per_piece;
+    const int64_t in_piece = k * kPushChunk;
+    off = shard_off + piece * ag.ld_bytes + in_piece;
+    const int64_t left = piece_bytes - in_piece;
+    bytes = (uint32_t)(left < (int64_t)kPushChunk ? left : (int64_t)kPushChunk);
+  };
+  uint32_t round = 0;                 // chunks issued so far (ring position / parity source), continues across peers
+  for (int i = 1; i < ag.world; ++i) {
+    const int p = (ag.rank - i + ag.world) % ag.world;         // peer p consumes my shard i-th
+    wait_counter_sys(&me->entered[p], ag.epoch, "entered", p);
+    const uint8_t* src = ag.peer_a[ag.rank];
+    uint8_t* dst = ag.peer_a[p];
+    const int64_t n = hi > lo ? hi - lo : 0;
+    for (int64_t j = 0; j < n + kPushLookahead; ++j) {
+      if (j < n) {
+        const uint32_t slot = (round + (uint32_t)j) % kPushBufs;
+        tma_store_wait_read<kPushBufs - kPushLookahead - 1>();            // the store that last used this slot has drained it
+        int64_t off; uint32_t bytes;
+        locate(lo + j, off, bytes);
+        mbar_expect_tx(bar0 + 8u * slot, bytes);
+        bulk_load(buf0 + slot * kPushChunk, src + off, bytes, bar0 + 8u * slot);
+      }
+      if (j >= kPushLookahead) {
+        const uint32_t seq = round + (uint32_t)(j - kPushLookahead);
+        const uint32_t slot = seq % kPushBufs;
+        mbar_wait(bar0 + 8u * slot, (seq / kPushBufs) & 1u);
+        int64_t off; uint32_t bytes;
+        locate(lo + j - kPushLookahead, off, bytes);
+        bulk_store(dst + off, buf0 + slot * kPushChunk, bytes);
+        tma_store_commit();
+      } else {
+        tma_store_commit();                                               // keep group numbering aligned with the ring
+      }
+    }
+    round += (uint32_t)n;
+    tma_store_wait<0>();                                                  // my slice has landed at peer p
+    __threadfence_system();
+    red_add_release_sys(&ag.peer_ctrl[p]->a_ready[ag.rank], 1u);
+  }
+}
+
+template <int kBlockN, bool kBMN>
+__global__ void __launch_bounds__(kThreads, 1)
+ag_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_aux, const GemmArgs args,
+                    const AgArgs ag) {
+  if ((int)blockIdx.x < ag.n_gemm) gemm_body<kBlockN, false, kBMN, false>(tmap_a, tmap_b, tmap_c, tmap_aux, nullptr, args, blockIdx.x, ag.n_gemm);
+  else ag_pusher(ag, blockIdx.x - ag.n_gemm, gridDim.x - ag.n_gemm);
+}
+
+// ---- GEMM fused reduce-scatter ------------------------------------------------------------------------
+// Every rank multiplies its K-slice; the bf16 partial tile of row shard d goes straight from the epilogue's
+// staging smem into rank d's receive slot [me] (TMA store over NVLink).  Once a rank has received all
+// partials of its shard (rs_count), all of its CTAs sum the W slots in fp32 (+bias) into the output.
+struct RsArgs {
+  const __nv_bfloat16* recv;       // my receive slots [world][rows_per_shard][N]
+  void* out;                       // [rows_per_shard, N]
+  const void* bias;
+  int64_t ldo;
+  int out_fp32, bias_fp32;
+  GemmCtrl* peer_ctrl[8];
+  unsigned int count_target;       // rs_count[s] value that means "all partials of this call from s are here"
+};
+
+template <int kBlockN, bool kAMN, bool kBMN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_rs_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ TmapArray tmap_rs, const GemmArgs args, const RsArgs rs) {
+  GemmCtrl* me = rs.peer_ctrl[args.rs_rank];
+  if (blockIdx.x == 0 && threadIdx.x < args.rs_world && (int)threadIdx.x != args.rs_rank)
+    st_release_sys_u32(&rs.peer_ctrl[threadIdx.x]->entered[args.rs_rank], args.rs_epoch);
+  gemm_body<kBlockN, kAMN, kBMN, true>(tmap_a, tmap_b, tmap_rs.m[0], tmap_rs.m[0], tmap_rs.m, args, blockIdx.x, gridDim.x);
+  // ---- reduction of my shard ----
+  if (threadIdx.x < args.rs_world) wait_counter_sys(&me->rs_count[threadIdx.x], rs.count_target, "rs_count", threadIdx.x);
+  __syncthreads();
+  const int N = args.N, rows = args.rows_per_shard;
+  const int64_t vec_per_row = N >> 3;
+  const int64_t total = (int64_t)rows * vec_per_row;
+  const int64_t slot = (int64_t)rows * N;
+  for (int64_t v = (int64_t)blockIdx.x * kThreads + threadIdx.x; v < total; v += (int64_t)gridDim.x * kThreads) {
+    const int64_t row = v / vec_per_row;
+    const int col = (int)(v % vec_per_row) * 8;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < args.rs_world; ++s) {
+      const uint4 u = ldg_stream_u4(reinterpret_cast<const uint4*>(rs.recv + s * slot + row * N + col));
+      acc[0] += bf16lo(u.x); acc[1] += bf16hi(u.x); acc[2] += bf16lo(u.y); acc[3] += bf16hi(u.y);
+      acc[4] += bf16lo(u.z); acc[5] += bf16hi(u.z); acc[6] += bf16lo(u.w); acc[7] += bf16hi(u.w);
+    }
+    if (rs.bias != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        acc[j] += rs.bias_fp32 ? reinterpret_cast<const float*>(rs.bias)[col + j] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rs.bias)[col + j]);
+    }
+    if (rs.out_fp32) {
+      float* o = reinterpret_cast<float*>(rs.out) + row * rs.ldo + col;
+      *reinterpret_cast<float4*>(o) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    } else {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(rs.out) + row * rs.ldo + col;
+      *reinterpret_cast<uint4*>(o) = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+    }
   }
 }
 
@@ -478,4 +683,152 @@ DETB200_API int detb200_gemm_bf16(const void* A, const void* B, void* C, const v
                                   int bias_fp32, int epilogue, int accumulate, cudaStream_t stream) {
   return detb200_gemm_bf16_impl(A, B, C, bias, aux, M, N, K, lda, ldb, ldc, ldaux, a_mn_major, b_mn_major, out_fp32, bias_fp32, epilogue,
                                 accumulate, nullptr, 0, 0, 0, 0, stream);
+}
+
+// ---- fused collectives: host entry points -----------------------------------------------------------
+DETB200_API int64_t detb200_gemm_ctrl_bytes(void) { return (int64_t)sizeof(GemmCtrl); }
+
+namespace {
+int sm_count(int* out) {
+  int dev = 0;
+  DETB200_CHECK(cudaGetDevice(&dev));
+  DETB200_CHECK(cudaDeviceGetAttribute(out, cudaDevAttrMultiProcessorCount, dev));
+  return 0;
+}
+}  // namespace
+
+DETB200_API int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl, int rank, int world, const void* B, void* C,
+                                     const void* bias, void* aux, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                     int64_t ldaux, int b_mn_major, int out_fp32, int bias_fp32, int epilogue, unsigned int epoch,
+                                     unsigned int ready_value, int n_push_ctas, cudaStream_t stream) {
+  if (world < 1 || world > 16 || rank < 0 || rank >= world || T % world != 0 || (T / world) % kBlockM != 0) {
+    detb200_set_error("ag_gemm: world %d rank %d T %lld: rows per rank must be a multiple of %d", world, rank, (long long)T, kBlockM);
+    return DETB200_ERR_BAD_ARG;
+  }
+  if (epilogue < 0 || epilogue > EPI_RELU) {
+    detb200_set_error("ag_gemm: only forward epilogues are supported");
+    return DETB200_ERR_BAD_ARG;
+  }
+  const int elem_c = out_fp32 ? 4 : 2;
+  const int bn = (N > 128) ? 256 : 128;
+  const int rows = (int)(T / world);
+  CUtensorMap ta, tb, tc, taux;
+  int rc = detb200_make_tmap_2d(&ta, 0, peer_a[rank], (uint64_t)K, (uint64_t)T, (uint64_t)lda * 2, kBlockK, kBlockM);
+  if (rc) return rc;
+  if (!b_mn_major) rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, kBlockK, bn);
+  else rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, kBlockK);
+  if (rc) return rc;
+  rc = detb200_make_tmap_2d(&tc, out_fp32, C, (uint64_t)N, (uint64_t)T, (uint64_t)ldc * elem_c, out_fp32 ? 32 : 64, 32);
+  if (rc) return rc;
+  if (aux != nullptr && epilogue != EPI_NONE) {
+    rc = detb200_make_tmap_2d(&taux, 0, aux, (uint64_t)N, (uint64_t)T, (uint64_t)ldaux * 2, 64, 32);
+    if (rc) return rc;
+  } else {
+    taux = tc;
+  }
+  int sms = kNumSMs;
+  if ((rc = sm_count(&sms))) return rc;
+  if (world == 1) n_push_ctas = 0;
+  else if (n_push_ctas <= 0) n_push_ctas = 4;
+  if (n_push_ctas >= sms) n_push_ctas = sms / 2;
+  GemmCtrl* me = reinterpret_cast<GemmCtrl*>(peer_ctrl[rank]);
+  GemmArgs g;
+  std::memset(&g, 0, sizeof(g));
+  g.C = C; g.bias = bias; g.aux = aux; g.M = (int)T; g.N = (int)N; g.K = (int)K; g.ldc = ldc; g.ldaux = ldaux;
+  g.out_fp32 = out_fp32; g.bias_fp32 = bias_fp32; g.epilogue = epilogue; g.accumulate = 0;
+  g.a_ready = world > 1 ? me->a_ready : nullptr; g.ready_value = ready_value; g.rows_per_shard = rows;
+  g.m_block_rotation = rank * (rows / kBlockM);
+  AgArgs ag;
+  std::memset(&ag, 0, sizeof(ag));
+  for (int r = 0; r < world; ++r) { ag.peer_a[r] = reinterpret_cast<uint8_t*>(peer_a[r]); ag.peer_ctrl[r] = reinterpret_cast<GemmCtrl*>(peer_ctrl[r]); }
+  ag.rank = rank; ag.world = world; ag.rows_per_shard = rows; ag.row_bytes = K * 2; ag.ld_bytes = lda * 2; ag.epoch = epoch;
+  const int mt = (int)((T + kBlockM - 1) / kBlockM), nt = (int)((N + bn - 1) / bn);
+  int n_gemm = sms - n_push_ctas;
+  if (mt * nt < n_gemm) n_gemm = mt * nt;
+  ag.n_gemm = n_gemm;
+  const int grid = n_gemm + n_push_ctas;
+#define DETB200_AG_LAUNCH(BN, BMN)                                                                                   \
+  do {                                                                                                               \
+    auto* kern = ag_gemm_bf16_kernel<BN, BMN>;                                                                       \
+    DETB200_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));     \
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, stream>>>(ta, tb, tc, taux, g, ag);                                  \
+  } while (0)
+  if (bn == 256) { if (b_mn_major) DETB200_AG_LAUNCH(256, true); else DETB200_AG_LAUNCH(256, false); }
+  else { if (b_mn_major) DETB200_AG_LAUNCH(128, true); else DETB200_AG_LAUNCH(128, false); }
+#undef DETB200_AG_LAUNCH
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+DETB200_API int detb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_recv, void* const* peer_ctrl, int rank, int world,
+                                     void* out, const void* bias, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldo,
+                                     int a_mn_major, int b_mn_major, int out_fp32, int bias_fp32, unsigned int epoch,
+                                     unsigned int count_base, cudaStream_t stream) {
+  if (world < 1 || world > 8 || rank < 0 || rank >= world || T % world != 0 || (T / world) % kBlockM != 0 || N % 8 != 0) {
+    detb200_set_error("gemm_rs: world %d (max 8) rank %d T %lld N %lld: rows per rank must be a multiple of %d and N of 8", world, rank,
+                      (long long)T, (long long)N, kBlockM);
+    return DETB200_ERR_BAD_ARG;
+  }
+  const int bn = (N > 128) ? 256 : 128;
+  const int rows = (int)(T / world);
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = detb200_make_tmap_2d(&ta, 0, A, (uint64_t)K, (uint64_t)T, (uint64_t)lda * 2, kBlockK, kBlockM);
+  else rc = detb200_make_tmap_2d(&ta, 0, A, (uint64_t)T, (uint64_t)K, (uint64_t)lda * 2, 64, kBlockK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, kBlockK, bn);
+  else rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, kBlockK);
+  if (rc) return rc;
+  TmapArray trs;
+  std::memset(&trs, 0, sizeof(trs));
+  for (int d = 0; d < world; ++d) {
+    uint8_t* base = reinterpret_cast<uint8_t*>(peer_recv[d]) + (int64_t)rank * rows * N * 2;     // slot [me] on rank d
+    rc = detb200_make_tmap_2d(&trs.m[d], 0, base, (uint64_t)N, (uint64_t)rows, (uint64_t)N * 2, 64, 32);
+    if (rc) return rc;
+  }
+  for (int d = world; d < 8; ++d) trs.m[d] = trs.m[0];
+  GemmArgs g;
+  std::memset(&g, 0, sizeof(g));
+  g.M = (int)T; g.N = (int)N; g.K = (int)K; g.rows_per_shard = rows;
+  g.m_block_rotation = ((rank + 1) % world) * (rows / kBlockM);      // remote shards first, own shard last
+  g.rs_world = world; g.rs_rank = rank; g.rs_epoch = epoch;
+  GemmCtrl* me = reinterpret_cast<GemmCtrl*>(peer_ctrl[rank]);
+  g.rs_entered = me->entered;
+  RsArgs rs;
+  std::memset(&rs, 0, sizeof(rs));
+  for (int d = 0; d < world; ++d) {
+    rs.peer_ctrl[d] = reinterpret_cast<GemmCtrl*>(peer_ctrl[d]);
+    g.rs_peer_count[d] = &rs.peer_ctrl[d]->rs_count[rank];
+  }
+  rs.recv = reinterpret_cast<const __nv_bfloat16*>(peer_recv[rank]);
+  rs.out = out; rs.bias = bias; rs.ldo = ldo; rs.out_fp32 = out_fp32; rs.bias_fp32 = bias_fp32;
+  const int mt = (int)(T / kBlockM), nt = (int)((N + bn - 1) / bn);
+  rs.count_target = count_base + (unsigned int)((rows / kBlockM) * nt * 4);
+  int sms = kNumSMs;
+  if ((rc = sm_count(&sms))) return rc;
+  const int grid = mt * nt < sms ? mt * nt : sms;
+#define DETB200_RS_LAUNCH(BN, AMN, BMN)                                                                              \
+  do {                                                                                                               \
+    auto* kern = gemm_rs_bf16_kernel<BN, AMN, BMN>;                                                                  \
+    DETB200_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));     \
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, stream>>>(ta, tb, trs, g, rs);                                       \
+  } while (0)
+#define DETB200_RS_DISPATCH(BN)                                                        \
+  do {                                                                                 \
+    if (!a_mn_major && !b_mn_major) DETB200_RS_LAUNCH(BN, false, false);               \
+    else if (!a_mn_major && b_mn_major) DETB200_RS_LAUNCH(BN, false, true);            \
+    else if (a_mn_major && !b_mn_major) DETB200_RS_LAUNCH(BN, true, false);            \
+    else DETB200_RS_LAUNCH(BN, true, true);                                            \
+  } while (0)
+  if (bn == 256) DETB200_RS_DISPATCH(256); else DETB200_RS_DISPATCH(128);
+#undef DETB200_RS_DISPATCH
+#undef DETB200_RS_LAUNCH
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+// arrivals one gemm_rs call adds to each rs_count entry of the shard owner (for the caller's running total)
+DETB200_API int detb200_gemm_rs_arrivals(int64_t T, int64_t N, int world) {
+  const int bn = (N > 128) ? 256 : 128;
+  return (int)((T / world / kBlockM) * ((N + bn - 1) / bn) * 4);
 }

@@ -83,6 +83,12 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_bn_bwd", i, [p, p, p, i64, i, p, p, p, p, p, p, p, i, p])
     # tcgen05 GEMM family (csrc/gemm_sm100.cu)
     _sig(lib, "detb200_gemm_bf16", i, [p, p, p, p, p, i64, i64, i64, i64, i64, i64, i64, i, i, i, i, i, i, p])
+    _sig(lib, "detb200_gemm_ctrl_bytes", i64, [])
+    _sig(lib, "detb200_gemm_rs_arrivals", i, [i64, i64, i])
+    _sig(lib, "detb200_ag_gemm_bf16", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, p, p, p, p, i64, i64, i64, i64, i64, i64, i64,
+                                         i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, i, p])
+    _sig(lib, "detb200_gemm_rs_bf16", i, [p, p, POINTER(c_void_p), POINTER(c_void_p), i, i, p, p, i64, i64, i64, i64, i64, i64,
+                                         i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, p])
     # attention (csrc/attention.cu)
     _sig(lib, "detb200_attn_fwd", i, [p, p, p, p, p, i, i, i, i, f, i, p])
     _sig(lib, "detb200_attn_bwd", i, [p, p, p, p, p, p, p, p, p, p, i, i, i, i, f, i, p])

@@ -169,6 +169,28 @@ int detb200_gemm_bf16(const void* A, const void* B, void* C, const void* bias /*
                       int a_mn_major, int b_mn_major, int out_fp32, int bias_fp32, int epilogue, int accumulate,
                       detb200_stream_t stream);
 
+/* GEMMs fused with their collective over NVLink peer memory (same file).  `peer_*` are host arrays of
+ * `world` device pointers (own pointer at [rank], peers' IPC-mapped pointers elsewhere); `peer_ctrl`
+ * points at detb200_gemm_ctrl_bytes() bytes of zero-initialised symmetric memory per rank.  `epoch` is the
+ * 1-based index of this fused call on this ctrl block (every rank issues the same sequence).
+ *   ag_gemm:  A is the [T, lda] gather buffer; this rank's rows [rank*T/world, ...) must be final in stream
+ *             order.  n_push_ctas CTAs push them to the peers while the others run the GEMM; `ready_value` is
+ *             the running total of n_push_ctas over all ag_gemm calls including this one.
+ *   gemm_rs:  out[T/world, N] = sum over ranks of (A_r * B_r^T) rows of this rank (+bias), partial tiles travel
+ *             as bf16; peer_recv[r] = [world][T/world][N] bf16 receive slots on rank r; `count_base` is the
+ *             running total of detb200_gemm_rs_arrivals() over earlier gemm_rs calls.  world <= 8.
+ * Reference: Megatron mpu all-gather / reduce-scatter around cuBLAS GEMMs in examples/deepspeed/gpt_neox. */
+int64_t detb200_gemm_ctrl_bytes(void);
+int detb200_gemm_rs_arrivals(int64_t T, int64_t N, int world);
+int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl, int rank, int world, const void* B, void* C, const void* bias,
+                         void* aux, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t ldaux,
+                         int b_mn_major, int out_fp32, int bias_fp32, int epilogue, unsigned int epoch, unsigned int ready_value,
+                         int n_push_ctas, detb200_stream_t stream);
+int detb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_recv, void* const* peer_ctrl, int rank, int world, void* out,
+                         const void* bias, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldo, int a_mn_major,
+                         int b_mn_major, int out_fp32, int bias_fp32, unsigned int epoch, unsigned int count_base,
+                         detb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -128,6 +128,124 @@ def check_resnet_matches_ddp(rank, world, dev):
         assert eng.kernel_launches > 0
 
 
+def check_gemm_comm(rank, world, dev):
+    """all-gather->GEMM and GEMM->reduce-scatter in one kernel each, vs NCCL collectives + fp32 matmul;
+    also timed against the unfused (NCCL + our GEMM) sequence."""
+    from determined_b200.ops import comm, gemm as G, gemm_comm
+
+    group = comm.PeerGroup.from_torch_distributed(dev)
+    tp = gemm_comm.TensorParallelGemm(group)
+    rows, K, N = 512, 1024, 1536
+    T = rows * world
+    for it in range(3):
+        torch.manual_seed(1000 + 10 * it + rank)
+        x_shard = torch.randn(rows, K, device=dev).to(torch.bfloat16)
+        w = (torch.randn(N, K, device=dev) * 0.05).to(torch.bfloat16)
+        bias = torch.randn(N, device=dev)
+        full, mine, _ = tp.gather_buffer(T, K)
+        mine.copy_(x_shard)
+        y = tp.all_gather_gemm(T, w, bias=bias, epilogue="gelu", out_dtype=torch.float32)
+        xs = [torch.empty_like(x_shard) for _ in range(world)]
+        dist.all_gather(xs, x_shard)
+        x_full = torch.cat(xs, 0)
+        want = torch.nn.functional.gelu(x_full.float() @ w.float().t() + bias)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(full, x_full)                       # the gather itself is bit exact
+        torch.testing.assert_close(y, want, rtol=3e-3, atol=3e-2)
+        # reduce-scatter: a [T, K] (this rank's K-slice), b [N, K]
+        a = torch.randn(T, K, device=dev).to(torch.bfloat16)
+        out = tp.gemm_reduce_scatter(a, w, bias=bias, out_dtype=torch.float32)
+        part = (a.float() @ w.float().t()).to(torch.bfloat16).float()     # partials travel as bf16
+        dist.all_reduce(part)
+        want_rs = part[rank * rows:(rank + 1) * rows] + bias
+        torch.cuda.synchronize()
+        torch.testing.assert_close(out, want_rs, rtol=1e-2, atol=0.25)
+    # autograd: column-parallel -> row-parallel block vs single-device math on gathered tensors
+    torch.manual_seed(7)
+    H, F4 = 1024, 2048                       # per-rank inner width F4
+    w1_all = (torch.randn(world, F4, H, device=dev) * 0.03)
+    w2_all = (torch.randn(world, H, F4, device=dev) * 0.03)
+    dist.broadcast(w1_all, 0)
+    dist.broadcast(w2_all, 0)
+    x_all = torch.randn(T, H, device=dev)
+    dist.broadcast(x_all, 0)
+    w1 = w1_all[rank].clone().requires_grad_(True)
+    w2 = w2_all[rank].clone().requires_grad_(True)
+    xs = x_all[rank * rows:(rank + 1) * rows].clone().to(torch.bfloat16).requires_grad_(True)
+    h = gemm_comm.column_parallel_linear(tp, xs, w1)
+    y = gemm_comm.row_parallel_linear(tp, torch.relu(h), w2)
+    y.float().sum().backward()
+    xr = x_all.to(torch.bfloat16).float().requires_grad_(True)
+    w1r = w1_all.to(torch.bfloat16).float().requires_grad_(True)
+    w2r = w2_all.to(torch.bfloat16).float().requires_grad_(True)
+    yr = sum(torch.relu(xr @ w1r[r].t()) @ w2r[r].t() for r in range(world))
+    yr.sum().backward()
+    torch.cuda.synchronize()
+
+    def rel(a, b):
+        return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-9))
+
+    assert rel(y, yr[rank * rows:(rank + 1) * rows]) < 2e-2, rel(y, yr[rank * rows:(rank + 1) * rows])
+    assert rel(w1.grad, w1r.grad[rank]) < 3e-2, rel(w1.grad, w1r.grad[rank])
+    assert rel(w2.grad, w2r.grad[rank]) < 3e-2, rel(w2.grad, w2r.grad[rank])
+    assert rel(xs.grad, xr.grad[rank * rows:(rank + 1) * rows]) < 3e-2
+    # ---- timing: fused kernels vs NCCL collective followed by the same GEMM (device time, max over ranks)
+    rows, K, N = 2048, 4096, 4096
+    T = rows * world
+    full, mine, _ = tp.gather_buffer(T, K)
+    w = (torch.randn(N, K, device=dev) * 0.02).to(torch.bfloat16)
+    x_shard = torch.randn(rows, K, device=dev).to(torch.bfloat16)
+    gathered = torch.empty(T, K, device=dev, dtype=torch.bfloat16)
+    a = torch.randn(T, K, device=dev).to(torch.bfloat16)
+    part = torch.empty(T, N, device=dev, dtype=torch.bfloat16)
+    rs_out = torch.empty(rows, N, device=dev, dtype=torch.bfloat16)
+
+    def fused_ag():
+        mine.copy_(x_shard)
+        tp.all_gather_gemm(T, w)
+
+    def fused_ag_n(n):
+        def f():
+            mine.copy_(x_shard)
+            tp.all_gather_gemm(T, w, push_ctas=n)
+        return f
+
+    def gemm_only():
+        G.gemm(gathered, w)
+
+    def nccl_ag():
+        dist.all_gather_into_tensor(gathered, x_shard)
+        G.gemm(gathered, w)
+
+    def fused_rs():
+        tp.gemm_reduce_scatter(a, w)
+
+    def nccl_rs():
+        G.gemm(a, w, out=part)
+        dist.reduce_scatter_tensor(rs_out, part)
+
+    res = {}
+    for name, fn in (("ag_gemm_fused", fused_ag), ("ag_gemm_fused_push2", fused_ag_n(2)), ("ag_gemm_fused_push8", fused_ag_n(8)),
+                     ("ag_gemm_fused_push16", fused_ag_n(16)), ("ag_gemm_nccl", nccl_ag), ("gemm_only_full_T", gemm_only),
+                     ("gemm_rs_fused", fused_rs), ("gemm_rs_nccl", nccl_rs)):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(10):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([s.elapsed_time(e) / 10], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res[name] = round(float(t.item()), 4)
+    if rank == 0:
+        import json
+        print("GEMM_COMM_TIMING", json.dumps({"world": world, "rows_per_rank": rows, "K": K, "N": N, "ms": res}), flush=True)
+
+
 def main():
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(local)
@@ -140,6 +258,8 @@ def main():
         check_engine(rank, world, dev)
     if which in ("all", "resnet"):
         check_resnet_matches_ddp(rank, world, dev)
+    if which in ("all", "gemm_comm"):
+        check_gemm_comm(rank, world, dev)
     dist.barrier()
     if rank == 0:
         print("DIST_CHECK_OK", which, flush=True)

@@ -25,7 +25,7 @@ def _ngpu() -> int:
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("which", ["allreduce", "engine", "resnet"])
+@pytest.mark.parametrize("which", ["allreduce", "engine", "resnet", "gemm_comm"])
 def test_two_ranks(which):
     _run(which, 2)
 
