@@ -81,20 +81,32 @@ def bench_bn(rows):
 
 
 def bench_norm(rows):
-    from determined_b200.ops import norm
+    """Raw kernel launches (no autograd / allocator on the timed path); ATen timed through its
+    native functions the same way."""
+    from determined_b200.ops import _lib
 
+    lib = _lib.load()
     hbm, _, src = peaks()
-    for rows_, cols in [(8192, 1024), (16384, 2560), (4096, 8192)]:
-        x = torch.randn(rows_, cols, device="cuda", dtype=torch.bfloat16, requires_grad=True)
-        ln = norm.LayerNorm(cols).cuda()
-        ref = torch.nn.LayerNorm(cols).cuda().to(torch.bfloat16)
+    for rows_, cols in [(8192, 768), (8192, 1024), (16384, 2560), (16384, 4096), (4096, 8192)]:
+        x = torch.randn(rows_, cols, device="cuda", dtype=torch.bfloat16)
         dy = torch.randn_like(x)
-        y = ln(x)
-        t_f = timeit(lambda: ln(x))
-        t_b = timeit(lambda: y.backward(dy, retain_graph=True))
-        yr = ref(x)
-        t_rf = timeit(lambda: ref(x))
-        t_rb = timeit(lambda: yr.backward(dy, retain_graph=True))
+        y, dx = torch.empty_like(x), torch.empty_like(x)
+        g = torch.ones(cols, device="cuda", dtype=torch.bfloat16)
+        b = torch.zeros(cols, device="cuda", dtype=torch.bfloat16)
+        dg, db = torch.empty_like(g), torch.empty_like(g)
+        mean = torch.empty(rows_, device="cuda")
+        rstd = torch.empty(rows_, device="cuda")
+        ws = torch.empty(int(lib.detb200_norm_bwd_workspace_elems(rows_, cols, 0)), device="cuda")
+        s = _lib.stream_ptr()
+        fwd = lambda: lib.detb200_norm_fwd(x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),  # noqa: E731
+                                           rows_, cols, 1e-5, 1, 0, s)
+        bwd = lambda: lib.detb200_norm_bwd(dy.data_ptr(), x.data_ptr(), g.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),  # noqa: E731
+                                           dg.data_ptr(), db.data_ptr(), ws.data_ptr(), rows_, cols, 1, 0, s)
+        t_f = timeit(fwd)
+        t_b = timeit(bwd)
+        _, m_a, r_a = torch.native_layer_norm(x, (cols,), g, b, 1e-5)
+        t_rf = timeit(lambda: torch.native_layer_norm(x, (cols,), g, b, 1e-5))
+        t_rb = timeit(lambda: torch.ops.aten.native_layer_norm_backward(dy, x, (cols,), m_a, r_a, g, b, [True, True, True]))
         nb = x.numel() * 2
         rows.append({"kernel": "layernorm_fwd", "shape": [rows_, cols], "us": t_f, "algo_GBs": 2 * nb / t_f / 1e3, "frac_of_hbm": 2 * nb / t_f / 1e3 / hbm, "aten_us": t_rf, "peak_source": src})
         rows.append({"kernel": "layernorm_bwd", "shape": [rows_, cols], "us": t_b, "algo_GBs": 3 * nb / t_b / 1e3, "frac_of_hbm": 3 * nb / t_b / 1e3 / hbm, "aten_us": t_rb, "peak_source": src})

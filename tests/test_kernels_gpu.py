@@ -103,7 +103,7 @@ def test_sumsq_and_clip_coef(n):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("rows,cols", [(1, 2), (37, 1024), (513, 2560), (64, 8192), (300, 770)])
+@pytest.mark.parametrize("rows,cols", [(1, 2), (37, 1024), (513, 2560), (64, 8192), (300, 770), (1001, 768), (130, 1536), (9, 256), (77, 4096), (5, 8)])
 @pytest.mark.parametrize("rms", [False, True])
 def test_norm_fwd_bwd(dtype, rows, cols, rms):
     from determined_b200.ops import norm
