@@ -1,0 +1,97 @@
+"""Flash attention over the tcgen05 forward kernel (``csrc/attention.cu``).
+
+``flash_attention(q, k, v, causal=..., scale=..., layout=...)`` takes ``[B, S, H, D]`` (``layout=
+"bshd"``, the shape a fused QKV projection produces — any strides with D contiguous, so slices of
+a packed QKV tensor are consumed in place) or ``[B, H, S, D]`` (``"bhsd"``).  Grouped-query
+attention is expressed by K/V having fewer heads.  The forward (and its log-sum-exp) is native;
+the backward currently recomputes through PyTorch's fused SDPA (a library call, like cuBLAS).
+
+Reference: GPT-NeoX / GPT-2 example attention (``examples/deepspeed/gpt_neox``; Megatron fused
+softmax + bmm), K13 in SURVEY.md.
+"""
+import math
+from typing import Any, Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from determined_b200.ops import _lib
+
+
+def _strides_bshd(t: torch.Tensor, layout: str) -> Tuple[int, int, int]:
+    if layout == "bshd":
+        return t.stride(0), t.stride(1), t.stride(2)
+    return t.stride(0), t.stride(2), t.stride(1)
+
+
+def _dims(t: torch.Tensor, layout: str) -> Tuple[int, int, int, int]:
+    """(B, S, H, D)"""
+    if layout == "bshd":
+        return t.shape[0], t.shape[1], t.shape[2], t.shape[3]
+    return t.shape[0], t.shape[2], t.shape[1], t.shape[3]
+
+
+def _ok(t: torch.Tensor) -> bool:
+    return t.stride(-1) == 1 and all(s % 8 == 0 for s in t.stride()[:-1]) and t.data_ptr() % 16 == 0
+
+
+def attention_forward(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool, scale: float, layout: str,
+                      need_lse: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    lib = _lib.load()
+    q, k, v = (t if _ok(t) else t.contiguous() for t in (q, k, v))
+    B, Sq, H, D = _dims(q, layout)
+    _, Skv, Hkv, _ = _dims(k, layout)
+    o = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)      # bshd storage
+    lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device) if need_lse else None
+    i64x3 = _lib.c_int64 * 3
+    _lib.check(lib.detb200_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), _lib.ptr(lse), B, H, Hkv, Sq, Skv, D,
+                                    i64x3(*_strides_bshd(q, layout)), i64x3(*_strides_bshd(k, layout)), i64x3(*_strides_bshd(v, layout)),
+                                    i64x3(o.stride(0), o.stride(1), o.stride(2)), float(scale), int(causal), _lib.stream_ptr()), "attn_fwd")
+    return (o if layout == "bshd" else o.permute(0, 2, 1, 3)), lse
+
+
+def _sdpa(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool, scale: float, layout: str) -> torch.Tensor:
+    if layout == "bshd":
+        q, k, v = (t.transpose(1, 2) for t in (q, k, v))
+    if k.shape[1] != q.shape[1]:
+        rep = q.shape[1] // k.shape[1]
+        k, v = k.repeat_interleave(rep, 1), v.repeat_interleave(rep, 1)
+    if causal and q.shape[2] != k.shape[2]:
+        Sq, Sk = q.shape[2], k.shape[2]
+        mask = torch.ones(Sq, Sk, dtype=torch.bool, device=q.device).tril(Sk - Sq)
+        o = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, scale=scale)
+    else:
+        o = F.scaled_dot_product_attention(q, k, v, is_causal=causal, scale=scale)
+    return o.transpose(1, 2) if layout == "bshd" else o
+
+
+class _FlashAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx: Any, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool, scale: float, layout: str) -> torch.Tensor:
+        o, _ = attention_forward(q, k, v, causal, scale, layout, need_lse=False)
+        ctx.save_for_backward(q, k, v)
+        ctx.cfg = (causal, scale, layout)
+        return o
+
+    @staticmethod
+    def backward(ctx: Any, do: torch.Tensor) -> Tuple[Any, ...]:
+        q, k, v = ctx.saved_tensors
+        causal, scale, layout = ctx.cfg
+        with torch.enable_grad():
+            qq, kk, vv = (t.detach().requires_grad_(True) for t in (q, k, v))
+            o = _sdpa(qq, kk, vv, causal, scale, layout)
+        dq, dk, dv = torch.autograd.grad(o, (qq, kk, vv), do)
+        return dq, dk, dv, None, None, None
+
+
+def flash_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = False, scale: Optional[float] = None,
+                    layout: str = "bhsd") -> torch.Tensor:
+    if layout not in ("bhsd", "bshd"):
+        raise ValueError(f"layout must be 'bhsd' or 'bshd', got {layout!r}")
+    D = q.shape[-1]
+    scale = float(scale) if scale is not None else 1.0 / math.sqrt(D)
+    if not q.is_cuda:
+        return _sdpa(q, k, v, causal, scale, layout)
+    if q.dtype != torch.bfloat16 or D not in (64, 128):
+        raise ValueError(f"flash_attention: bf16 inputs with head dim 64 or 128 required on CUDA (got {q.dtype}, D={D})")
+    return _FlashAttnFn.apply(q, k, v, causal, scale, layout)

@@ -191,6 +191,17 @@ int detb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_recv, v
                          int b_mn_major, int out_fp32, int bias_fp32, unsigned int epoch, unsigned int count_base,
                          detb200_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Flash attention forward on tcgen05 (csrc/attention.cu): S = QK^T and O += PV on the tensor cores, S/P/O in
+ * tensor memory, K/V streamed by TMA, online softmax in registers.  q/k/v/o are bf16 with logical shape
+ * (B, S, H, D), element strides {batch, seq, head} and D contiguous (64 or 128); H_kv divides H (GQA).
+ * lse (nullable): fp32 [B, H, S_q].  Reference: attention of the GPT-2 / GPT-NeoX examples
+ * (examples/deepspeed/gpt_neox, Megatron fused softmax + bmm).
+ * ------------------------------------------------------------------------------------------- */
+int detb200_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int H_kv, int S_q, int S_kv, int D,
+                     const int64_t* q_strides, const int64_t* k_strides, const int64_t* v_strides, const int64_t* o_strides,
+                     float scale, int causal, detb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,75 @@
+"""tcgen05 flash attention forward vs fp32 PyTorch (layouts, causal, GQA, tails), plus autograd wiring."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(q, k, v, causal, scale):
+    # q,k,v: [B,H,S,D] fp32
+    if k.shape[1] != q.shape[1]:
+        rep = q.shape[1] // k.shape[1]
+        k, v = k.repeat_interleave(rep, 1), v.repeat_interleave(rep, 1)
+    s = (q @ k.transpose(-1, -2)) * scale
+    if causal:
+        Sq, Sk = q.shape[2], k.shape[2]
+        mask = torch.ones(Sq, Sk, dtype=torch.bool, device=q.device).tril(Sk - Sq)
+        s = s.masked_fill(~mask, float("-inf"))
+    lse = torch.logsumexp(s, -1)
+    return torch.softmax(s, -1) @ v, lse
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("cfg", [(2, 4, 4, 256, 256, 128), (1, 8, 2, 384, 384, 64), (2, 3, 3, 200, 200, 128), (1, 2, 2, 1000, 1000, 64),
+                                 (1, 4, 4, 128, 512, 128), (1, 2, 1, 77, 333, 64), (1, 16, 16, 2048, 2048, 128)])
+def test_attention_forward_matches_reference(cfg, causal):
+    from determined_b200.ops import attention as A
+
+    B, H, Hkv, Sq, Skv, D = cfg
+    torch.manual_seed(0)
+    q = torch.randn(B, H, Sq, D, device="cuda").to(torch.bfloat16)
+    k = torch.randn(B, Hkv, Skv, D, device="cuda").to(torch.bfloat16)
+    v = torch.randn(B, Hkv, Skv, D, device="cuda").to(torch.bfloat16)
+    scale = 1.0 / math.sqrt(D)
+    want, want_lse = _ref(q.float(), k.float(), v.float(), causal, scale)
+    got, lse = A.attention_forward(q, k, v, causal, scale, "bhsd")
+    torch.cuda.synchronize()
+    torch.testing.assert_close(got.float(), want, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(lse, want_lse, rtol=1e-3, atol=2e-3)
+
+
+def test_attention_packed_qkv_bshd_and_autograd():
+    from determined_b200.ops import attention as A
+
+    B, S, H, D = 2, 320, 6, 64
+    torch.manual_seed(1)
+    qkv = torch.randn(B, S, 3, H, D, device="cuda").to(torch.bfloat16).requires_grad_(True)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]                # strided views, consumed in place
+    o = A.flash_attention(q, k, v, causal=True, layout="bshd")
+    assert o.shape == (B, S, H, D)
+    do = torch.randn_like(o)
+    o.backward(do)
+    g = qkv.grad.clone()
+    qkv.grad = None
+    qf = qkv.detach().float().requires_grad_(True)
+    want, _ = _ref(qf[:, :, 0].transpose(1, 2), qf[:, :, 1].transpose(1, 2), qf[:, :, 2].transpose(1, 2), True, 1.0 / math.sqrt(D))
+    want.transpose(1, 2).backward(do.float())
+    torch.testing.assert_close(o.float(), want.transpose(1, 2), rtol=2e-2, atol=2e-2)
+    rel = (g.float() - qf.grad).norm() / qf.grad.norm()
+    assert rel < 3e-2, rel
+
+
+def test_attention_large_scores_stay_finite():
+    from determined_b200.ops import attention as A
+
+    torch.manual_seed(2)
+    q = (torch.randn(1, 2, 256, 128, device="cuda") * 6).to(torch.bfloat16)
+    k = (torch.randn(1, 2, 256, 128, device="cuda") * 6).to(torch.bfloat16)
+    v = torch.randn(1, 2, 256, 128, device="cuda").to(torch.bfloat16)
+    got, lse = A.attention_forward(q, k, v, False, 1.0, "bhsd")
+    want, want_lse = _ref(q.float(), k.float(), v.float(), False, 1.0)
+    assert torch.isfinite(got.float()).all() and torch.isfinite(lse).all()
+    torch.testing.assert_close(got.float(), want, rtol=3e-2, atol=3e-2)
+    torch.testing.assert_close(lse, want_lse, rtol=1e-3, atol=1e-2)
