@@ -293,3 +293,376 @@ DETB200_API int detb200_attn_fwd(const void* q, const void* k, const void* v, vo
   a.scale_log2 = scale * 1.4426950408889634f; a.causal = causal;
   return D == 128 ? launch_fwd<128>(tq, tk, tv, a, stream) : launch_fwd<64>(tq, tk, tv, a, stream);
 }
+
+// =====================================================================================================
+// Backward.  One CTA owns a block of 128 keys of one (batch, head) and walks the query blocks (64 rows)
+// that attend to it.  All five GEMMs of a (key block, query block) pair run on tcgen05; the accumulators
+// dK, dV stay in tensor memory for the whole walk:
+//
+//   S^T  = K Q_i^T          dP^T = V dO_i^T                      (A, B from smem, K-major)
+//   P^T  = exp2(S^T*c - lse_i)      dS^T = P^T o (dP^T - delta_i) * scale       (8 compute warps, one key row per thread)
+//   dV  += P^T dO_i         dK  += dS^T Q_i                      (A = bf16 P^T / dS^T in TMEM, B = the same smem tiles read MN-major)
+//   dQ_i^T = K^T dS^T                                            (A = K read MN-major, B = dS^T staged in smem) -> fp32 atomics
+//
+// TMEM columns: S^T 64 | dP^T 64 | P^T 32 | dS^T 32 | dQ^T 64 | dV 128 | dK 128 = 512.
+// S^T/dP^T of block i+1 are issued as soon as the compute warps hold block i in registers.
+namespace {
+
+constexpr int kBwdKeys = 128;
+constexpr int kBwdQ = 64;
+constexpr int kBwdThreads = 320;            // warp 0 TMA, warp 1 MMA, warps 2..9 compute
+constexpr int kBwdCompute = 256;
+
+struct AttnBwdArgs {
+  const float* lse;       // [B, H, S]
+  const float* delta;     // [B, H, S]
+  float* dq_acc;          // [B, S, H, D] fp32, zero-initialised
+  __nv_bfloat16* dK;
+  __nv_bfloat16* dV;
+  int B, H, S;
+  int64_t dk_sb, dk_ss, dk_sh, dv_sb, dv_ss, dv_sh;
+  float scale, scale_log2;
+  int causal;
+};
+
+// D fixed at 128
+struct BCfg {
+  static constexpr int D = 128;
+  static constexpr int kKBytes = kBwdKeys * D * 2;          // 32 KiB (K or V)
+  static constexpr int kQBytes = kBwdQ * D * 2;             // 16 KiB (Q_i or dO_i)
+  static constexpr int kdSBytes = kBwdKeys * kBwdQ * 2;     // 16 KiB
+  static constexpr int kSmemBytes = 2 * kKBytes + 4 * kQBytes + kdSBytes + 1024 /*align*/ + 2 * 2 * kBwdQ * 4 /*lse, delta*/ + 256;
+  static constexpr int tS = 0, tdP = 64, tP = 128, tdS = 160, tdQ = 192, tdV = 256, tdK = 384;
+};
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+                const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do, const AttnBwdArgs args) {
+  using C = BCfg;
+  constexpr int D = C::D;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sK = smem_base, sV = sK + C::kKBytes;
+  const uint32_t sQ0 = sV + C::kKBytes;                       // Q stage s at sQ0 + s*2*kQBytes, dO right after it
+  const uint32_t sdS = sQ0 + 4 * C::kQBytes;
+  const uint32_t sStat = sdS + C::kdSBytes;                   // float lse2[2][64], delta[2][64]
+  const uint32_t bar_base = sStat + 2 * 2 * kBwdQ * 4;
+  const uint32_t kv_full = bar_base;
+  auto qdo_full = [&](int s) { return bar_base + 8u * (1 + s); };
+  auto qdo_empty = [&](int s) { return bar_base + 8u * (3 + s); };
+  const uint32_t sp_full = bar_base + 8u * 5, sp_empty = bar_base + 8u * 6, pds_full = bar_base + 8u * 7, mma_done = bar_base + 8u * 8,
+                 dq_empty = bar_base + 8u * 9;
+  const uint32_t tmem_slot = bar_base + 8u * 10;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  float* stat = reinterpret_cast<float*>(smem_gen + (sStat - smem_base));
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_blk = blockIdx.x, k0 = k_blk * kBwdKeys;
+  const int bh = blockIdx.y, b = bh / args.H, h = bh % args.H;
+  const int nq_total = (args.S + kBwdQ - 1) / kBwdQ;
+  const int i_min = args.causal ? (k0 / kBwdQ) : 0;            // first query block that can see these keys
+  const int n_it = nq_total - i_min;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v); prefetch_tmap(&tmap_do);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(qdo_full(s), 1); mbar_init(qdo_empty(s), 1); }
+    mbar_init(sp_full, 1);
+    mbar_init(sp_empty, kBwdCompute);
+    mbar_init(pds_full, kBwdCompute);
+    mbar_init(mma_done, 1);
+    mbar_init(dq_empty, kBwdCompute);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (n_it > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        mbar_expect_tx(kv_full, 2 * C::kKBytes);
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          tma_load_4d(sK + hh * (kBwdKeys * 128), &tmap_k, kv_full, hh * 64, h, k0, b);
+          tma_load_4d(sV + hh * (kBwdKeys * 128), &tmap_v, kv_full, hh * 64, h, k0, b);
+        }
+        for (int it = 0; it < n_it; ++it) {
+          const int st = it & 1, q0 = (i_min + it) * kBwdQ;
+          mbar_wait(qdo_empty(st), ((it >> 1) & 1) ^ 1u);
+          mbar_expect_tx(qdo_full(st), 2 * C::kQBytes);
+          const uint32_t sQ = sQ0 + st * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            tma_load_4d(sQ + hh * (kBwdQ * 128), &tmap_q, qdo_full(st), hh * 64, h, q0, b);
+            tma_load_4d(sdO + hh * (kBwdQ * 128), &tmap_do, qdo_full(st), hh * 64, h, q0, b);
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        constexpr uint32_t idesc_s = idesc_bf16_f32(128, kBwdQ, 0, 0);       // S^T, dP^T: [128 keys x 64 q]
+        constexpr uint32_t idesc_dkv = idesc_bf16_f32(128, D, 0, 1);         // dV, dK: A in TMEM, B MN-major
+        constexpr uint32_t idesc_dq = idesc_bf16_f32(128, kBwdQ, 1, 1);      // dQ^T: A = K MN-major, B = dS^T MN-major
+        auto issue_s_dp = [&](int it) {
+          const uint32_t sQ = sQ0 + (it & 1) * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
+#pragma unroll
+          for (int k = 0; k < D / 16; ++k) {
+            const uint64_t da = smem_desc_sw128(sK + (k / 4) * (kBwdKeys * 128) + (k % 4) * 32, 16, 1024);
+            const uint64_t db = smem_desc_sw128(sQ + (k / 4) * (kBwdQ * 128) + (k % 4) * 32, 16, 1024);
+            mma_f16_ss(tmem_base + C::tS, da, db, idesc_s, k != 0 ? 1u : 0u);
+          }
+#pragma unroll
+          for (int k = 0; k < D / 16; ++k) {
+            const uint64_t da = smem_desc_sw128(sV + (k / 4) * (kBwdKeys * 128) + (k % 4) * 32, 16, 1024);
+            const uint64_t db = smem_desc_sw128(sdO + (k / 4) * (kBwdQ * 128) + (k % 4) * 32, 16, 1024);
+            mma_f16_ss(tmem_base + C::tdP, da, db, idesc_s, k != 0 ? 1u : 0u);
+          }
+          tc_commit(sp_full);
+        };
+        mbar_wait(kv_full, 0);
+        mbar_wait(qdo_full(0), 0);
+        tc_fence_after();
+        issue_s_dp(0);
+        for (int it = 0; it < n_it; ++it) {
+          if (it + 1 < n_it) {
+            mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
+            mbar_wait(sp_empty, it & 1);
+            tc_fence_after();
+            issue_s_dp(it + 1);
+          }
+          mbar_wait(pds_full, it & 1);
+          tc_fence_after();
+          const uint32_t sQ = sQ0 + (it & 1) * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
+#pragma unroll
+          for (int k = 0; k < kBwdQ / 16; ++k) {       // reduction over the 64 queries
+            const uint64_t ddo = smem_desc_sw128(sdO + k * 2048, kBwdQ * 128, 1024);
+            mma_f16_ts(tmem_base + C::tdV, tmem_base + C::tP + k * 8, ddo, idesc_dkv, (it | k) != 0 ? 1u : 0u);
+          }
+#pragma unroll
+          for (int k = 0; k < kBwdQ / 16; ++k) {
+            const uint64_t dq = smem_desc_sw128(sQ + k * 2048, kBwdQ * 128, 1024);
+            mma_f16_ts(tmem_base + C::tdK, tmem_base + C::tdS + k * 8, dq, idesc_dkv, (it | k) != 0 ? 1u : 0u);
+          }
+          if (it > 0) {
+            mbar_wait(dq_empty, (it - 1) & 1);
+            tc_fence_after();
+          }
+#pragma unroll
+          for (int k = 0; k < kBwdKeys / 16; ++k) {    // reduction over the 128 keys
+            const uint64_t da = smem_desc_sw128(sK + k * 2048, kBwdKeys * 128, 1024);
+            const uint64_t db = smem_desc_sw128(sdS + k * 2048, kBwdKeys * 128, 1024);
+            mma_f16_ss(tmem_base + C::tdQ, da, db, idesc_dq, k != 0 ? 1u : 0u);
+          }
+          tc_commit(qdo_empty(it & 1));
+          tc_commit(mma_done);
+        }
+      }
+    } else {
+      const int cw = warp - 2;                    // 0..7
+      const int q = warp & 3;                     // TMEM lane quarter
+      const int half = cw >> 2;                   // which 32 of the 64 query columns
+      const int row = q * 32 + lane;              // key row inside the block / d index for dQ^T
+      const int key = k0 + row;
+      const int ct = threadIdx.x - 64;            // 0..255
+      const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+      const int64_t stat_base = ((int64_t)b * args.H + h) * args.S;
+      float* dq_base = args.dq_acc + ((int64_t)b * args.S * args.H + h) * D;     // + q * H * D + d
+
+      auto drain_dq = [&](int it) {               // dQ^T of block `it` -> global fp32 accumulator
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + C::tdQ + lane_off + half * 32, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(dq_empty);
+        const int q0 = (i_min + it) * kBwdQ + half * 32;
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+          if (q0 + c < args.S) atomicAdd(dq_base + (int64_t)(q0 + c) * args.H * D + row, __uint_as_float(r[c]));
+      };
+
+      for (int it = 0; it < n_it; ++it) {
+        const int q0 = (i_min + it) * kBwdQ;
+        float* st_l = stat + (it & 1) * 2 * kBwdQ;
+        if (ct < kBwdQ) st_l[ct] = (q0 + ct < args.S) ? args.lse[stat_base + q0 + ct] * 1.4426950408889634f : INFINITY;
+        else if (ct < 2 * kBwdQ) st_l[ct] = (q0 + ct - kBwdQ < args.S) ? args.delta[stat_base + q0 + ct - kBwdQ] : 0.f;
+        named_bar_sync(1, kBwdCompute);
+        mbar_wait(sp_full, it & 1);
+        tc_fence_after();
+        uint32_t rs[32], rp[32];
+        tmem_ld_32x32(tmem_base + C::tS + lane_off + half * 32, rs);
+        tmem_ld_32x32(tmem_base + C::tdP + lane_off + half * 32, rp);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(sp_empty);
+        uint32_t pP[16], pS[16];
+        const bool diag = args.causal && (q0 < k0 + kBwdKeys);          // some (key, query) pairs of this tile are masked
+#pragma unroll
+        for (int c = 0; c < 32; c += 2) {
+          float p[2], ds[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int qc = half * 32 + c + e;
+            float pv = exp2f(__uint_as_float(rs[c + e]) * args.scale_log2 - st_l[qc]);
+            if ((diag && key > q0 + qc) || key >= args.S) pv = 0.f;
+            p[e] = pv;
+            ds[e] = pv * (__uint_as_float(rp[c + e]) - st_l[kBwdQ + qc]) * args.scale;
+          }
+          pP[c >> 1] = pack_bf16(p[0], p[1]);
+          pS[c >> 1] = pack_bf16(ds[0], ds[1]);
+        }
+        if (it > 0) {
+          mbar_wait(mma_done, (it - 1) & 1);      // dV/dK/dQ of the previous block retired: P/dS buffers free, dQ^T ready
+          tc_fence_after();
+          drain_dq(it - 1);
+        }
+        tmem_st_32x16(tmem_base + C::tP + lane_off + half * 16, pP);
+        tmem_st_32x16(tmem_base + C::tdS + lane_off + half * 16, pS);
+        {
+          const uint32_t dst = sdS + (uint32_t)row * 128u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t a = dst + (uint32_t)(((half * 4 + j) ^ (row & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pS[4 * j]), "r"(pS[4 * j + 1]), "r"(pS[4 * j + 2]), "r"(pS[4 * j + 3]) : "memory");
+          }
+        }
+        tmem_st_wait();
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(pds_full);
+      }
+      mbar_wait(mma_done, (n_it - 1) & 1);
+      tc_fence_after();
+      drain_dq(n_it - 1);
+      // dV, dK: this thread owns key row `row`, columns [64*half, 64*half + 64)
+      const bool row_ok = key < args.S;
+#pragma unroll
+      for (int which = 0; which < 2; ++which) {
+        __nv_bfloat16* base = which == 0 ? args.dV + (int64_t)b * args.dv_sb + (int64_t)key * args.dv_ss + (int64_t)h * args.dv_sh
+                                         : args.dK + (int64_t)b * args.dk_sb + (int64_t)key * args.dk_ss + (int64_t)h * args.dk_sh;
+        const uint32_t tcol = tmem_base + (which == 0 ? C::tdV : C::tdK) + lane_off + half * 64;
+#pragma unroll
+        for (int c = 0; c < 64; c += 32) {
+          uint32_t r[32];
+          tmem_ld_32x32(tcol + c, r);
+          tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              uint4 u;
+              u.x = pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+              u.y = pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+              u.z = pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
+              u.w = pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
+              *reinterpret_cast<uint4*>(base + half * 64 + c + i) = u;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= 2) {
+    // keys nobody attends to (cannot happen with S_q == S_kv, kept for safety): zero gradients
+    const int row = (warp & 3) * 32 + lane, half = (warp - 2) >> 2, key = k0 + row;
+    if (key < args.S) {
+      for (int c = 0; c < 64; c += 8) {
+        *reinterpret_cast<uint4*>(args.dV + (int64_t)b * args.dv_sb + (int64_t)key * args.dv_ss + (int64_t)h * args.dv_sh + half * 64 + c) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(args.dK + (int64_t)b * args.dk_sb + (int64_t)key * args.dk_ss + (int64_t)h * args.dk_sh + half * 64 + c) = make_uint4(0, 0, 0, 0);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// delta[b,h,s] = sum_d O * dO   (one warp per row, D = 128: 4 elements per lane)
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S,
+                  int64_t o_sb, int64_t o_ss, int64_t o_sh, int64_t do_sb, int64_t do_ss, int64_t do_sh) {
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)B * H * S;
+  for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += (int64_t)gridDim.x * 8) {
+    const int s = (int)(r % S);
+    const int h = (int)((r / S) % H);
+    const int64_t b = r / ((int64_t)S * H);
+    const uint2 a = *reinterpret_cast<const uint2*>(o + b * o_sb + (int64_t)s * o_ss + (int64_t)h * o_sh + lane * 4);
+    const uint2 g = *reinterpret_cast<const uint2*>(d_o + b * do_sb + (int64_t)s * do_ss + (int64_t)h * do_sh + lane * 4);
+    float v = bf16lo(a.x) * bf16lo(g.x) + bf16hi(a.x) * bf16hi(g.x) + bf16lo(a.y) * bf16lo(g.y) + bf16hi(a.y) * bf16hi(g.y);
+    v = warp_sum(v);
+    if (lane == 0) delta[r] = v;          // r enumerates (b, h, s)
+  }
+}
+
+// dq (bf16, strided) = dq_acc (fp32 [B,S,H,D] contiguous)
+__global__ void __launch_bounds__(256)
+attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int64_t n8, int S, int H, int64_t sb, int64_t ss, int64_t sh) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < n8; v += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = ldg_stream(reinterpret_cast<const float4*>(acc) + 2 * v), c = ldg_stream(reinterpret_cast<const float4*>(acc) + 2 * v + 1);
+    const int d8 = (int)(v % 16);
+    int64_t t = v / 16;
+    const int h = (int)(t % H); t /= H;
+    const int s = (int)(t % S);
+    const int64_t b = t / S;
+    *reinterpret_cast<uint4*>(dq + b * sb + (int64_t)s * ss + (int64_t)h * sh + d8 * 8) =
+        make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(c.x, c.y), pack_bf16(c.z, c.w));
+  }
+}
+
+}  // namespace
+
+// Backward of detb200_attn_fwd for H_kv == H, S_q == S_kv, D == 128.  All tensors bf16 (B, S, H, D)-addressed with element
+// strides {batch, seq, head}.  `delta` (fp32 [B,H,S]) and `dq_acc` (fp32 [B,S,H,D]) are caller-provided scratch; dq_acc is
+// zeroed here.  dq/dk/dv may be slices of one packed buffer.
+DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, float* delta,
+                                 float* dq_acc, void* dq, void* dk, void* dv, int B, int H, int S, int D, const int64_t* q_st,
+                                 const int64_t* k_st, const int64_t* v_st, const int64_t* o_st, const int64_t* do_st, const int64_t* dq_st,
+                                 const int64_t* dk_st, const int64_t* dv_st, float scale, int causal, cudaStream_t stream) {
+  if (D != 128) {
+    detb200_set_error("attn_bwd: head dim %d unsupported (128)", D);
+    return DETB200_ERR_UNSUPPORTED;
+  }
+  for (const int64_t* st : {o_st, do_st, dq_st, dk_st, dv_st})
+    if ((st[0] & 7) || (st[1] & 7) || (st[2] & 7)) {
+      detb200_set_error("attn_bwd: strides must be multiples of 8 elements");
+      return DETB200_ERR_BAD_ARG;
+    }
+  CUtensorMap tq, tk, tv, tdo;
+  auto mk = [&](CUtensorMap* m, const void* base, const int64_t* st, uint32_t rows) {
+    const uint64_t dims[4] = {(uint64_t)D, (uint64_t)H, (uint64_t)S, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)st[2] * 2, (uint64_t)st[1] * 2, (uint64_t)st[0] * 2};
+    const uint32_t box[4] = {64, 1, rows, 1};
+    return detb200_make_tmap_4d_bf16(m, base, dims, strides, box);
+  };
+  int rc;
+  if ((rc = mk(&tq, q, q_st, kBwdQ))) return rc;
+  if ((rc = mk(&tdo, d_o, do_st, kBwdQ))) return rc;
+  if ((rc = mk(&tk, k, k_st, kBwdKeys))) return rc;
+  if ((rc = mk(&tv, v, v_st, kBwdKeys))) return rc;
+  const int64_t rows = (int64_t)B * H * S;
+  attn_delta_kernel<<<grid_for(rows, 8, 1, kNumSMs * 16), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(o), reinterpret_cast<const __nv_bfloat16*>(d_o),
+                                                                         delta, B, H, S, o_st[0], o_st[1], o_st[2], do_st[0], do_st[1], do_st[2]);
+  DETB200_LAUNCH_CHECK();
+  DETB200_CHECK(cudaMemsetAsync(dq_acc, 0, sizeof(float) * (size_t)rows * D, stream));
+  AttnBwdArgs a;
+  a.lse = lse; a.delta = delta; a.dq_acc = dq_acc; a.dK = reinterpret_cast<__nv_bfloat16*>(dk); a.dV = reinterpret_cast<__nv_bfloat16*>(dv);
+  a.B = B; a.H = H; a.S = S;
+  a.dk_sb = dk_st[0]; a.dk_ss = dk_st[1]; a.dk_sh = dk_st[2]; a.dv_sb = dv_st[0]; a.dv_ss = dv_st[1]; a.dv_sh = dv_st[2];
+  a.scale = scale; a.scale_log2 = scale * 1.4426950408889634f; a.causal = causal;
+  DETB200_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BCfg::kSmemBytes));
+  dim3 grid((S + kBwdKeys - 1) / kBwdKeys, B * H);
+  attn_bwd_kernel<<<grid, kBwdThreads, BCfg::kSmemBytes, stream>>>(tq, tk, tv, tdo, a);
+  DETB200_LAUNCH_CHECK();
+  const int64_t n8 = rows * D / 8;
+  attn_dq_convert_kernel<<<grid_for(n8, 256, 2, kNumSMs * 8), 256, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), n8, S, H, dq_st[0], dq_st[1], dq_st[2]);
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}

@@ -91,6 +91,12 @@ def load() -> ctypes.CDLL:
                                          i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, p])
     # attention (csrc/attention.cu)
     _sig(lib, "detb200_attn_fwd", i, [p, p, p, p, p, i, i, i, i, i, i, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), f, i, p])
+    P64 = POINTER(c_int64)
+    _sig(lib, "detb200_attn_bwd", i, [p, p, p, p, p, p, p, p, p, p, p, i, i, i, i, P64, P64, P64, P64, P64, P64, P64, P64, f, i, p])
+    _sig(lib, "detb200_rotary_qkv", i, [p, p, p, i64, i, i, i, i, i64, i64, i64, i64, i, p])
+    _sig(lib, "detb200_colsum_bf16", i, [p, p, i64, i, i64, i, p])
+    _sig(lib, "detb200_cast_bf16", i, [p, p, i64, p])
+    _sig(lib, "detb200_add_bf16", i, [p, p, p, p, i64, p])
     _lib = lib
     return lib
 

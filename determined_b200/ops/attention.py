@@ -15,7 +15,7 @@ from typing import Any, Optional, Tuple
 import torch
 import torch.nn.functional as F
 
-from determined_b200.ops import _lib
+from determined_b200.ops import _lib, fused
 
 
 def _strides_bshd(t: torch.Tensor, layout: str) -> Tuple[int, int, int]:
@@ -95,3 +95,78 @@ def flash_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: b
     if q.dtype != torch.bfloat16 or D not in (64, 128):
         raise ValueError(f"flash_attention: bf16 inputs with head dim 64 or 128 required on CUDA (got {q.dtype}, D={D})")
     return _FlashAttnFn.apply(q, k, v, causal, scale, layout)
+
+
+class _QKVPackedFn(torch.autograd.Function):
+    """Attention over a packed ``[B, S, 3, H, D]`` projection: rotary is applied to Q/K *in place* (the
+    projection output is private to this op), the forward kernel reads the three strided slices, and the
+    backward produces one packed ``dqkv`` (no per-slice zero-fill + scatter through autograd)."""
+
+    @staticmethod
+    def forward(ctx: Any, qkv: torch.Tensor, cos: Optional[torch.Tensor], sin: Optional[torch.Tensor], rot: int, causal: bool,
+                scale: float) -> torch.Tensor:
+        qkv = qkv.data              # same storage, detached from the producer's version counter: we own this buffer
+        if rot:
+            fused.rotary_qkv_(qkv, cos, sin, rot)
+        q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+        if qkv.is_cuda:
+            o, lse = attention_forward(q, k, v, causal, scale, "bshd", need_lse=True)
+        else:
+            o, lse = _sdpa(q, k, v, causal, scale, "bshd").contiguous(), None
+        ctx.save_for_backward(qkv, o, lse, cos, sin)
+        ctx.cfg = (rot, causal, scale)
+        return o
+
+    @staticmethod
+    def backward(ctx: Any, do: torch.Tensor) -> Tuple[Any, ...]:
+        qkv, o, lse, cos, sin = ctx.saved_tensors
+        rot, causal, scale = ctx.cfg
+        dqkv = torch.empty_like(qkv)
+        if qkv.is_cuda and qkv.shape[-1] == 128 and _native_bwd_available():
+            attention_backward_packed(qkv, o, lse, do, dqkv, causal, scale)
+        else:
+            with torch.enable_grad():
+                qq, kk, vv = (qkv[:, :, i].detach().requires_grad_(True) for i in range(3))
+                oo = _sdpa(qq, kk, vv, causal, scale, "bshd")
+            dq, dk, dv = torch.autograd.grad(oo, (qq, kk, vv), do)
+            dqkv[:, :, 0].copy_(dq)
+            dqkv[:, :, 1].copy_(dk)
+            dqkv[:, :, 2].copy_(dv)
+        if rot:
+            fused.rotary_qkv_(dqkv, cos, sin, rot, conj=True)
+        return dqkv, None, None, None, None, None
+
+
+def _native_bwd_available() -> bool:
+    return hasattr(_lib.load(), "detb200_attn_bwd")
+
+
+def attention_backward_packed(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Tensor, do: torch.Tensor, dqkv: torch.Tensor, causal: bool,
+                              scale: float) -> None:
+    lib = _lib.load()
+    B, S, _, H, D = qkv.shape
+    do = do if (_ok(do) and do.stride(-1) == 1) else do.contiguous()
+    i64x3 = _lib.c_int64 * 3
+    dq_acc = torch.zeros((B, S, H, D), dtype=torch.float32, device=qkv.device)
+    delta = torch.empty((B, H, S), dtype=torch.float32, device=qkv.device)
+
+    def st(t: torch.Tensor) -> Any:
+        return i64x3(t.stride(0), t.stride(1), t.stride(2))
+
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    dq, dk, dv = dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2]
+    _lib.check(lib.detb200_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(), delta.data_ptr(),
+                                    dq_acc.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, H, S, D, st(q), st(k), st(v), st(o), st(do),
+                                    st(dq), st(dk), st(dv), float(scale), int(causal), _lib.stream_ptr()), "attn_bwd")
+
+
+def attention_qkvpacked(qkv: torch.Tensor, rope: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, rot: int = 0, causal: bool = True,
+                        scale: Optional[float] = None) -> torch.Tensor:
+    """``qkv``: ``[B, S, 3, H, D]`` (consumed: rotary is applied in place).  ``rope``: fp32 ``(cos, sin)`` of shape
+    ``[S, rot/2]``.  Returns ``[B, S, H, D]``."""
+    D = qkv.shape[-1]
+    scale = float(scale) if scale is not None else 1.0 / math.sqrt(D)
+    cos, sin = (rope if (rope is not None and rot) else (None, None))
+    if qkv.is_cuda and (qkv.dtype != torch.bfloat16 or D not in (64, 128)):
+        raise ValueError(f"attention_qkvpacked: bf16 with head dim 64 or 128 required on CUDA (got {qkv.dtype}, D={D})")
+    return _QKVPackedFn.apply(qkv, cos, sin, rot if cos is not None else 0, causal, scale)

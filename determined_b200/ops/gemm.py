@@ -14,7 +14,7 @@ from typing import Any, Optional, Tuple
 import torch
 import torch.nn.functional as F
 
-from determined_b200.ops import _lib
+from determined_b200.ops import _lib, fused
 
 EPILOGUES = {"none": 0, "gelu": 1, "gelu_erf": 1, "gelu_tanh": 2, "relu": 3, "dgelu": 4, "dgelu_erf": 4, "dgelu_tanh": 5, "drelu": 6}
 _BWD_OF = {1: 4, 2: 5, 3: 6}
@@ -141,7 +141,7 @@ class _LinearFn(torch.autograd.Function):
             if dw.dtype != ctx.w_dtype:
                 dw = dw.to(ctx.w_dtype)
         if ctx.b_dtype is not None and ctx.needs_input_grad[2]:
-            db = dy2.float().sum(0).to(ctx.b_dtype)
+            db = fused.colsum(dy2).to(ctx.b_dtype)
         return dx, dw, db, None
 
 
@@ -177,10 +177,10 @@ class _MLPFn(torch.autograd.Function):
             return g if g.dtype == dt else g.to(dt)
 
         dw2 = wgrad(dy2, h, d2) if ctx.needs_input_grad[3] else None
-        db2 = dy2.float().sum(0).to(db2t) if db2t is not None and ctx.needs_input_grad[4] else None
+        db2 = fused.colsum(dy2).to(db2t) if db2t is not None and ctx.needs_input_grad[4] else None
         dpre = gemm(dy2, w2b, b_mn_major=True, epilogue={1: "dgelu", 2: "dgelu_tanh", 3: "drelu"}[ctx.epi], aux=pre)
         dw1 = wgrad(dpre, x2, d1) if ctx.needs_input_grad[1] else None
-        db1 = dpre.float().sum(0).to(db1t) if db1t is not None and ctx.needs_input_grad[2] else None
+        db1 = fused.colsum(dpre).to(db1t) if db1t is not None and ctx.needs_input_grad[2] else None
         dx = gemm(dpre, w1b, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         return dx, dw1, db1, dw2, db2, None
 

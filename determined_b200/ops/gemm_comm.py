@@ -20,7 +20,7 @@ from typing import Any, Optional, Tuple
 
 import torch
 
-from determined_b200.ops import _lib, comm
+from determined_b200.ops import _lib, comm, fused
 from determined_b200.ops import gemm as G
 
 PUSH_CTAS = 0          # 0 = pick 2 * world pusher CTAs (measured: 16 hide the gather completely at world 8)
@@ -129,7 +129,7 @@ class _ColumnParallelFn(torch.autograd.Function):
         dy2 = G._as_bf16_2d(dy)
         dx = ctx.tp.gemm_reduce_scatter(dy2, w, b_mn_major=True)                     # [T, N/W] x [N/W, K] -> rows of [T, K]
         dw = G.gemm(dy2, x_full, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else torch.bfloat16)
-        db = dy2.float().sum(0).to(ctx.b_dtype) if ctx.b_dtype is not None else None
+        db = fused.colsum(dy2).to(ctx.b_dtype) if ctx.b_dtype is not None else None
         return None, dx, dw.to(ctx.w_dtype), db
 
 
@@ -155,7 +155,7 @@ class _RowParallelFn(torch.autograd.Function):
         mine.copy_(dy_shard)
         dx = tp.all_gather_gemm(T, w, b_mn_major=True)                                # [T, N] x [N, K/W]
         dw = G.gemm(full, x2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else torch.bfloat16)
-        db = dy_shard.float().sum(0).to(ctx.b_dtype) if ctx.b_dtype is not None else None
+        db = fused.colsum(G._as_bf16_2d(dy_shard)).to(ctx.b_dtype) if ctx.b_dtype is not None else None
         return None, dx, dw.to(ctx.w_dtype), db
 
 

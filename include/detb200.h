@@ -202,6 +202,25 @@ int detb200_attn_fwd(const void* q, const void* k, const void* v, void* o, float
                      const int64_t* q_strides, const int64_t* k_strides, const int64_t* v_strides, const int64_t* o_strides,
                      float scale, int causal, detb200_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Transformer glue (csrc/elementwise.cu).  Reference: the ATen elementwise / cat / reduce kernels the
+ * GPT-2 / GPT-NeoX examples launch around attention and the linear layers.
+ * ------------------------------------------------------------------------------------------- */
+int detb200_rotary_qkv(void* qkv, const float* cos_t, const float* sin_t, int64_t B, int S, int H, int D, int rot, int64_t sb, int64_t ss,
+                       int64_t sw, int64_t sh, int conj, detb200_stream_t stream);
+int detb200_colsum_bf16(const void* x, float* out, int64_t M, int N, int64_t ld, int accumulate, detb200_stream_t stream);
+int detb200_cast_bf16(const float* x, void* y, int64_t n, detb200_stream_t stream);
+int detb200_add_bf16(const void* a, const void* b, const void* c /* nullable */, void* y, int64_t n, detb200_stream_t stream);
+
+/* Backward of detb200_attn_fwd on tcgen05 (H_kv == H, S_q == S_kv, D == 128): five GEMMs per (key block, query block)
+ * pair, dK/dV accumulated in tensor memory, dQ through fp32 atomics into `dq_acc` ([B,S,H,D], zeroed here) and converted
+ * to bf16.  `delta`: fp32 [B,H,S] scratch.  dq/dk/dv may be the three slices of one packed [B,S,3,H,D] buffer. */
+int detb200_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, float* delta,
+                     float* dq_acc, void* dq, void* dk, void* dv, int B, int H, int S, int D, const int64_t* q_strides,
+                     const int64_t* k_strides, const int64_t* v_strides, const int64_t* o_strides, const int64_t* do_strides,
+                     const int64_t* dq_strides, const int64_t* dk_strides, const int64_t* dv_strides, float scale, int causal,
+                     detb200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
