@@ -45,8 +45,21 @@ def main():
             t_ours = timeit(lambda: A.attention_forward(q, k, v, causal, scale, "bhsd"), flush)
             t_ref = timeit(lambda: F.scaled_dot_product_attention(q, k, v, is_causal=causal), flush)
             fl = 4.0 * B * H * S * S * D * (0.5 if causal else 1.0)
-            rows.append({"B": B, "H": H, "S": S, "D": D, "causal": causal, "ours_ms": t_ours, "sdpa_ms": t_ref, "ours_tflops": fl / t_ours / 1e9,
-                         "sdpa_tflops": fl / t_ref / 1e9, "ours_frac_of_measured_peak": fl / t_ours / 1e9 / peak})
+            row = {"B": B, "H": H, "S": S, "D": D, "causal": causal, "ours_ms": t_ours, "sdpa_ms": t_ref, "ours_tflops": fl / t_ours / 1e9,
+                   "sdpa_tflops": fl / t_ref / 1e9, "ours_frac_of_measured_peak": fl / t_ours / 1e9 / peak}
+            if D == 128:
+                # backward only (2.5x the forward FLOPs): packed QKV through our kernel vs SDPA's backward
+                qkv = torch.randn(B, S, 3, H, D, device="cuda").to(torch.bfloat16)
+                o, lse = A.attention_forward(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal, scale, "bshd")
+                do = torch.randn_like(o)
+                dqkv = torch.empty_like(qkv)
+                t_b = timeit(lambda: A.attention_backward_packed(qkv, o, lse, do, dqkv, causal, scale), flush)
+                qr, kr, vr = (t.clone().requires_grad_(True) for t in (q, k, v))
+                out_r = F.scaled_dot_product_attention(qr, kr, vr, is_causal=causal)
+                do_r = torch.randn_like(out_r)
+                t_rb = timeit(lambda: torch.autograd.grad(out_r, (qr, kr, vr), do_r, retain_graph=True), flush)
+                row.update({"ours_bwd_ms": t_b, "sdpa_bwd_ms": t_rb, "ours_bwd_tflops": 2.5 * fl / t_b / 1e9, "sdpa_bwd_tflops": 2.5 * fl / t_rb / 1e9})
+            rows.append(row)
             print(json.dumps(rows[-1]))
     if args.json:
         pathlib.Path(args.json).write_text(json.dumps({"peak_tflops": peak, "rows": rows}, indent=1))
