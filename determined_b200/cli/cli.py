@@ -512,6 +512,71 @@ def workspace_cmd(args: argparse.Namespace) -> int:
     return 0
 
 
+def ntsc_cmd(args: argparse.Namespace) -> int:
+    """``det cmd|shell|notebook|tensorboard ...`` (reference ``harness/determined/cli/{command,shell,notebook,tensorboard}.py``)."""
+    sess = _session(args)
+    kind, plural = args.kind, args.kind + "s"
+    if args.action in ("run", "start"):
+        cfg: Dict[str, Any] = {}
+        if getattr(args, "config_file", None):
+            cfg = yaml.safe_load(pathlib.Path(args.config_file).read_text()) or {}
+        for kv in getattr(args, "config", None) or []:
+            k, v = kv.split("=", 1)
+            cur = cfg
+            parts = k.split(".")
+            for part in parts[:-1]:
+                cur = cur.setdefault(part, {})
+            cur[parts[-1]] = yaml.safe_load(v)
+        body: Dict[str, Any] = {"config": cfg}
+        if kind == "command":
+            if not args.entrypoint:
+                raise SystemExit("det cmd run: a command is required")
+            cfg["entrypoint"] = [x for i, x in enumerate(args.entrypoint) if not (i == 0 and x == "--")]
+        if kind == "tensorboard":
+            body["experimentIds"] = [int(x) for x in (args.experiment_ids or [])]
+            body["trialIds"] = [int(x) for x in (args.trial_ids or [])]
+        if getattr(args, "slots", None) is not None:
+            cfg.setdefault("resources", {})["slots"] = args.slots
+        if getattr(args, "template", None):
+            body["templateName"] = args.template
+        t = sess.post(f"/api/v1/{plural}", json=body).json()[kind]
+        print(f"Launched {kind} (id: {t['id']}).")
+        if getattr(args, "detach", True) is False:
+            return _follow_task_logs(sess, t["id"], plural, kind)
+        return 0
+    if args.action == "list":
+        ts = sess.get(f"/api/v1/{plural}").json()[plural]
+        _table([[t["id"], t["username"], t["description"], t["state"].replace("STATE_", ""), t["exitStatus"], t["resourcePool"]] for t in ts],
+               ["ID", "Owner", "Description", "State", "Exit Status", "Resource Pool"], args.json)
+        return 0
+    if args.action == "kill":
+        for tid in args.ids:
+            sess.post(f"/api/v1/{plural}/{tid}/kill")
+            print(f"Killed {kind} {tid}")
+        return 0
+    if args.action == "logs":
+        return _follow_task_logs(sess, args.id, plural, kind, follow=args.follow)
+    if args.action == "describe":
+        print(json.dumps(sess.get(f"/api/v1/{plural}/{args.id}").json()[kind], indent=2))
+        return 0
+    return 2
+
+
+def _follow_task_logs(sess: api.Session, task_id: str, plural: str, kind: str, follow: bool = True) -> int:
+    last = 0
+    while True:
+        logs = sess.get(f"/api/v1/tasks/{task_id}/logs", params={"offset": last}).json()["logs"]
+        for l in logs:
+            sys.stdout.write(l["log"])
+            last = max(last, int(l["id"]))
+        t = sess.get(f"/api/v1/{plural}/{task_id}").json()[kind]
+        if t["state"] == "STATE_TERMINATED" and not logs:
+            return int(t["exitStatus"] or 0)
+        if not follow and not logs:
+            return 0
+        time.sleep(0.3)
+
+
 def deploy_local(args: argparse.Namespace) -> int:
     """``det deploy local cluster-up``: start the single-box master in the foreground or detached
     (reference ``harness/determined/deploy/local``: docker-compose master+db+agent)."""
@@ -768,6 +833,34 @@ def make_parser() -> argparse.ArgumentParser:
             a.add_argument("project")
         outfmt(a)
         a.set_defaults(fn=workspace_cmd, action=name)
+
+    for kind, aliases in (("command", ["cmd"]), ("shell", []), ("notebook", []), ("tensorboard", [])):
+        cp = sub.add_parser(kind, aliases=aliases).add_subparsers(dest="sub")
+        start = cp.add_parser("run" if kind == "command" else "start")
+        start.add_argument("--config-file")
+        start.add_argument("--config", action="append")
+        start.add_argument("--template")
+        start.add_argument("--slots", type=int)
+        start.add_argument("-d", "--detach", action="store_true", default=(kind != "command"))
+        if kind == "command":
+            start.add_argument("entrypoint", nargs=argparse.REMAINDER)
+        if kind == "tensorboard":
+            start.add_argument("experiment_ids", nargs="*")
+            start.add_argument("-t", "--trial-ids", nargs="*")
+        start.set_defaults(fn=ntsc_cmd, kind=kind, action="run" if kind == "command" else "start")
+        a = cp.add_parser("list")
+        outfmt(a)
+        a.set_defaults(fn=ntsc_cmd, kind=kind, action="list")
+        a = cp.add_parser("kill")
+        a.add_argument("ids", nargs="+")
+        a.set_defaults(fn=ntsc_cmd, kind=kind, action="kill")
+        a = cp.add_parser("logs")
+        a.add_argument("id")
+        a.add_argument("-f", "--follow", action="store_true")
+        a.set_defaults(fn=ntsc_cmd, kind=kind, action="logs")
+        a = cp.add_parser("describe")
+        a.add_argument("id")
+        a.set_defaults(fn=ntsc_cmd, kind=kind, action="describe")
 
     dp = sub.add_parser("deploy").add_subparsers(dest="sub")
     lo = dp.add_parser("local")

@@ -1301,6 +1301,145 @@ def list_tasks(ctx: Ctx) -> Any:
                                              "state": a.state, "resources": [{"agentDevices": {ctx.m.agent_id: {"devices": a.slot_ids}}}]} for a in ctx.m.allocations.values()}}
 
 
+# ---------------------------------------------------------------------------------------------
+# commands / shells / notebooks / tensorboards (reference api_command.go, api_shell.go, api_notebook.go, api_tensorboard.go)
+# ---------------------------------------------------------------------------------------------
+def _ntsc_routes(kind: str, plural: str) -> None:
+    key = kind
+
+    @route("POST", f"/api/v1/{plural}")
+    def launch(ctx: Ctx) -> Any:
+        b = ctx.body or {}
+        cfg = b.get("config") or {}
+        if isinstance(cfg, str):
+            import yaml as _yaml
+            cfg = _yaml.safe_load(cfg) or {}
+        if b.get("templateName"):
+            row = ctx.m.db.one("SELECT config FROM templates WHERE name=?", (b["templateName"],))
+            if row is None:
+                raise HTTPError(404, f"template {b['templateName']} not found")
+            from determined_b200.master import expconf as _expconf
+            cfg = _expconf.merge(cfg, dbmod.U(row["config"], {}))
+        try:
+            t = ctx.m.commands.launch(kind, cfg, ctx.user["id"], ctx.user["username"], b)
+        except ValueError as e:
+            raise HTTPError(400, str(e))
+        return {key: t.to_json(), "config": cfg}
+
+    @route("GET", f"/api/v1/{plural}")
+    def list_(ctx: Ctx) -> Any:
+        return {plural: [t.to_json() for t in ctx.m.commands.list(kind)]}
+
+    @route("GET", f"/api/v1/{plural}/{{task_id}}")
+    def get(ctx: Ctx, task_id: str) -> Any:
+        try:
+            return {key: ctx.m.commands.get(task_id, kind).to_json()}
+        except KeyError:
+            raise HTTPError(404, f"{kind} {task_id} not found")
+
+    @route("POST", f"/api/v1/{plural}/{{task_id}}/kill")
+    def kill(ctx: Ctx, task_id: str) -> Any:
+        try:
+            t = ctx.m.commands.get(task_id, kind)
+        except KeyError:
+            raise HTTPError(404, f"{kind} {task_id} not found")
+        t.kill()
+        return {key: t.to_json()}
+
+    @route("POST", f"/api/v1/{plural}/{{task_id}}/set_priority")
+    def prio(ctx: Ctx, task_id: str) -> Any:
+        try:
+            t = ctx.m.commands.get(task_id, kind)
+        except KeyError:
+            raise HTTPError(404, f"{kind} {task_id} not found")
+        t.config.setdefault("resources", {})["priority"] = int((ctx.body or {}).get("priority", 42))
+        return {key: t.to_json()}
+
+
+for _k, _p in (("command", "commands"), ("shell", "shells"), ("notebook", "notebooks"), ("tensorboard", "tensorboards")):
+    _ntsc_routes(_k, _p)
+
+
+# ---------------------------------------------------------------------------------------------
+# streaming updates (reference master/internal/stream/*: websocket publisher for projects / models / model versions;
+# here the same startup / sync / upsert / delete messages over a long-poll POST)
+# ---------------------------------------------------------------------------------------------
+class _StreamState:
+    """seq numbers per (kind, id), bumped when the row's content changes (detected lazily at poll time)."""
+    lock = threading.Lock()
+    seq = 0
+    rows: Dict[Tuple[str, int], Tuple[int, str]] = {}
+
+
+def _stream_scan(ctx: Ctx) -> Dict[str, Dict[int, Dict[str, Any]]]:
+    db = ctx.m.db
+    cur: Dict[str, Dict[int, Dict[str, Any]]] = {"projects": {}, "models": {}, "model_versions": {}}
+    for r in db.all("SELECT * FROM projects", ()):
+        cur["projects"][r["id"]] = {"id": r["id"], "name": r["name"], "description": r["description"] or "", "archived": bool(r["archived"]) if "archived" in r.keys() else False,
+                                    "workspace_id": r["workspace_id"], "user_id": r["user_id"] if "user_id" in r.keys() else None, "state": "UNSPECIFIED"}
+    for r in db.all("SELECT * FROM models", ()):
+        cur["models"][r["id"]] = {"id": r["id"], "name": r["name"], "description": r["description"] or "", "archived": bool(r["archived"]) if "archived" in r.keys() else False,
+                                  "labels": dbmod.U(r["labels"], []) if "labels" in r.keys() else [], "workspace_id": r["workspace_id"] if "workspace_id" in r.keys() else 1,
+                                  "user_id": r["user_id"] if "user_id" in r.keys() else None}
+    for r in db.all("SELECT * FROM model_versions", ()):
+        cur["model_versions"][r["id"]] = {"id": r["id"], "name": r["name"] if "name" in r.keys() else "", "version": r["version"], "checkpoint_uuid": r["checkpoint_uuid"],
+                                          "model_id": r["model_id"], "comment": r["comment"] if "comment" in r.keys() else "", "labels": [],
+                                          "user_id": r["user_id"] if "user_id" in r.keys() else None}
+    with _StreamState.lock:
+        for kind, rows in cur.items():
+            for i, row in rows.items():
+                h = json.dumps(row, sort_keys=True, default=str)
+                old = _StreamState.rows.get((kind, i))
+                if old is None or old[1] != h:
+                    _StreamState.seq += 1
+                    _StreamState.rows[(kind, i)] = (_StreamState.seq, h)
+                row["seq"] = _StreamState.rows[(kind, i)][0]
+        for key in [k for k in _StreamState.rows if k[1] not in cur[k[0]]]:
+            del _StreamState.rows[key]
+    return cur
+
+
+def _stream_match(kind: str, row: Dict[str, Any], spec: Dict[str, Any]) -> bool:
+    def hit(field: str, key: str) -> bool:
+        ids = spec.get(key)
+        return bool(ids) and row.get(field) in ids
+    if kind == "projects":
+        return hit("workspace_id", "workspace_ids") or hit("id", "project_ids")
+    if kind == "models":
+        return hit("workspace_id", "workspace_ids") or hit("id", "model_ids") or hit("user_id", "user_ids")
+    return hit("model_id", "model_ids") or hit("id", "model_version_ids") or hit("user_id", "user_ids")
+
+
+@route("POST", "/stream")
+def stream(ctx: Ctx) -> Any:
+    from determined_b200.common.streams import _util as su
+
+    b = ctx.body or {}
+    sub = b.get("subscribe") or {}
+    cur = _stream_scan(ctx)
+    wire_name = {"projects": "project", "models": "model", "model_versions": "modelversion"}
+    msgs: List[Dict[str, Any]] = []
+    polling = "poll_since" in b
+    if not polling:
+        msgs.append({"sync_msg": {"sync_id": b.get("sync_id"), "complete": False}})
+    for kind, spec in sub.items():
+        if kind not in cur:
+            continue
+        since = int(b["poll_since"]) if polling else int(spec.get("since") or 0)
+        known = set(su.range_encoded_keys((b.get("known") or {}).get(kind, ""))) if not polling else set()
+        visible = {i: r for i, r in cur[kind].items() if _stream_match(kind, r, spec)}
+        if not polling:
+            gone = known - set(visible)
+            if gone:
+                msgs.append({kind + "_deleted": su.encode_keys(gone)})
+        for i, r in sorted(visible.items()):
+            if r["seq"] > since or (not polling and i not in known):
+                msgs.append({wire_name[kind]: r})
+    if not polling:
+        msgs.append({"sync_msg": {"sync_id": b.get("sync_id"), "complete": True}})
+    return {"messages": msgs, "seq": _StreamState.seq}
+
+
 @route("GET", "/metrics", auth_required=False)
 @route("GET", "/prom/det-state-metrics", auth_required=False)
 def prometheus(ctx: Ctx) -> Any:

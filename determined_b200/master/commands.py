@@ -1,0 +1,204 @@
+"""Generic tasks: commands, shells, notebooks, tensorboards ("NTSC").
+
+Parity: reference ``master/internal/command/*`` (command actors, ``CommandService``) and the
+``api_command.go`` / ``api_shell.go`` / ``api_notebook.go`` / ``api_tensorboard.go`` handlers:
+a task is a config (``entrypoint``, ``resources.slots``, ``environment.environment_variables``,
+``description``) scheduled through the same resource pool as trials (non-preemptible), launched
+with the task env contract, its output shipped to task logs, killable.
+
+Single-box differences: the process runs directly on the host (no container), so shells have no
+sshd to attach to and notebooks need ``jupyterlab`` importable; both are still scheduled, logged
+and killable like commands.  Tensorboards serve the experiments' tfevents through
+``determined_b200.exec.tensorboard``.
+"""
+import json
+import logging
+import os
+import pathlib
+import secrets
+import shlex
+import signal
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+import uuid
+from typing import Any, Dict, List, Optional
+
+from determined_b200.master import scheduler
+
+logger = logging.getLogger("determined.master.commands")
+
+TYPES = {"command": "COMMAND", "shell": "SHELL", "notebook": "NOTEBOOK", "tensorboard": "TENSORBOARD"}
+
+
+def default_entrypoint(kind: str, body: Dict[str, Any]) -> List[str]:
+    if kind == "NOTEBOOK":
+        return [sys.executable, "-m", "jupyterlab", "--no-browser", "--ip=127.0.0.1", "--ServerApp.token="]
+    if kind == "SHELL":
+        # no sshd on a single box: keep a login shell alive so the slot reservation, logs and kill path behave
+        return ["/bin/bash", "-lc", "echo shell task ready on $(hostname); exec sleep infinity"]
+    if kind == "TENSORBOARD":
+        ids = [str(i) for i in body.get("experimentIds") or []]
+        tids = [str(i) for i in body.get("trialIds") or []]
+        return [sys.executable, "-m", "determined_b200.exec.tensorboard", "--experiments", ",".join(ids), "--trials", ",".join(tids)]
+    raise ValueError("a command needs an entrypoint")
+
+
+class CommandTask:
+    def __init__(self, mgr: "CommandManager", kind: str, config: Dict[str, Any], owner_id: int, owner_name: str, body: Dict[str, Any]) -> None:
+        self.mgr, self.kind, self.config = mgr, kind, config
+        self.id = str(uuid.uuid4())
+        self.owner_id, self.owner_name = owner_id, owner_name
+        self.state = "QUEUED"
+        self.start_time = time.time()
+        self.end_time: Optional[float] = None
+        self.exit_code: Optional[int] = None
+        self.slots = int((config.get("resources") or {}).get("slots", 0) or 0)
+        self.description = config.get("description") or f"{kind.lower()} ({owner_name})"
+        self.proc: Optional[subprocess.Popen] = None
+        self.slot_ids: List[int] = []
+        self.token = secrets.token_hex(16)
+        self.killed = False
+        self.context: Optional[bytes] = body.get("_context")
+        ep = config.get("entrypoint")
+        if not ep:
+            ep = default_entrypoint(kind, body)
+        self.argv: List[str] = ep if isinstance(ep, list) else ["/bin/bash", "-lc", str(ep)]
+        self.run_dir: Optional[str] = None
+
+    @property
+    def pool_key(self) -> str:
+        return f"cmd-{self.id}"
+
+    def to_json(self) -> Dict[str, Any]:
+        return {"id": self.id, "description": self.description, "state": "STATE_" + self.state, "startTime": self.start_time, "endTime": self.end_time,
+                "username": self.owner_name, "userId": self.owner_id, "resourcePool": self.mgr.master.pool.name, "exitStatus": self.exit_code,
+                "jobId": self.id, "type": self.kind, "slots": self.slots, "slotIds": self.slot_ids, "config": self.config}
+
+    def start(self, slot_ids: List[int]) -> None:
+        m = self.mgr.master
+        self.slot_ids = slot_ids
+        self.run_dir = tempfile.mkdtemp(prefix=f"detb200-{self.kind.lower()}-{self.id[:8]}-", dir=m.work_dir)
+        if self.context:
+            from determined_b200.common import context as det_context
+
+            det_context.extract_tarball(self.context, self.run_dir) if hasattr(det_context, "extract_tarball") else None
+        env = dict(os.environ)
+        for kv in ((self.config.get("environment") or {}).get("environment_variables") or []):
+            if isinstance(kv, str) and "=" in kv:
+                k, v = kv.split("=", 1)
+                env[k] = v
+        env.update({"DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port), "DET_CLUSTER_ID": m.cluster_id,
+                    "DET_AGENT_ID": m.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids), "DET_TASK_ID": self.id, "DET_ALLOCATION_ID": self.id + ".1",
+                    "DET_SESSION_TOKEN": self.token, "DET_TASK_TYPE": self.kind, "DET_USER": self.owner_name, "PYTHONUNBUFFERED": "1",
+                    "DET_RUN_DIR": self.run_dir})
+        if slot_ids:
+            env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in slot_ids)
+        elif m.num_gpus:
+            env["CUDA_VISIBLE_DEVICES"] = ""
+        root = str(pathlib.Path(__file__).resolve().parents[2])
+        env["PYTHONPATH"] = os.pathsep.join([root] + ([env["PYTHONPATH"]] if env.get("PYTHONPATH") else []))
+        m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)", (self.token, self.owner_id, time.time() + 14 * 86400, self.id))
+        self.state = "RUNNING"
+        m.db.exec("UPDATE tasks SET state=? WHERE id=?", (self.state, self.id))
+        logger.info("starting %s %s: %s", self.kind, self.id, " ".join(shlex.quote(a) for a in self.argv))
+        self.proc = subprocess.Popen(self.argv, cwd=self.run_dir, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, start_new_session=True,
+                                     text=True, bufsize=1, errors="replace")
+        threading.Thread(target=self._pump, daemon=True, name=f"cmdlogs-{self.id[:8]}").start()
+
+    def _pump(self) -> None:
+        assert self.proc is not None and self.proc.stdout is not None
+        m = self.mgr.master
+        batch: List[Any] = []
+        last = time.time()
+        for line in self.proc.stdout:
+            batch.append((self.id, self.id + ".1", time.time(), "INFO", None, "stdout", "task", line if line.endswith("\n") else line + "\n"))
+            if len(batch) >= 100 or time.time() - last > 0.3:
+                m.db.add_logs(batch)
+                batch, last = [], time.time()
+        if batch:
+            m.db.add_logs(batch)
+        code = self.proc.wait()
+        self.finish(code)
+
+    def finish(self, code: Optional[int]) -> None:
+        m = self.mgr.master
+        self.exit_code, self.end_time, self.state = code, time.time(), "TERMINATED"
+        m.db.exec("UPDATE tasks SET state=?, end_time=? WHERE id=?", (self.state, self.end_time, self.id))
+        m.db.exec("DELETE FROM sessions WHERE token=?", (self.token,))
+        with m.lock:
+            m.pool.release(self.pool_key)
+        m.kick()
+
+    def kill(self) -> None:
+        self.killed = True
+        if self.proc is not None and self.proc.poll() is None:
+            try:
+                os.killpg(self.proc.pid, signal.SIGTERM)
+            except ProcessLookupError:
+                pass
+
+            def hard(p: subprocess.Popen = self.proc) -> None:
+                time.sleep(5)
+                if p.poll() is None:
+                    try:
+                        os.killpg(p.pid, signal.SIGKILL)
+                    except ProcessLookupError:
+                        pass
+
+            threading.Thread(target=hard, daemon=True).start()
+        elif self.state == "QUEUED":
+            self.finish(None)
+
+
+class CommandManager:
+    def __init__(self, master: Any) -> None:
+        self.master = master
+        self.tasks: Dict[str, CommandTask] = {}
+
+    def launch(self, kind: str, config: Dict[str, Any], owner_id: int, owner_name: str, body: Dict[str, Any]) -> CommandTask:
+        t = CommandTask(self, TYPES[kind], config, owner_id, owner_name, body)
+        m = self.master
+        with m.lock:
+            self.tasks[t.id] = t
+            m.db.exec("INSERT INTO tasks(id,type,start_time,job_id,config,state,owner_id) VALUES(?,?,?,?,?,?,?)",
+                      (t.id, t.kind, t.start_time, t.id, json.dumps(config), t.state, owner_id))
+            res = config.get("resources") or {}
+            m.pool.allocate(scheduler.AllocateRequest(t.pool_key, t.id, t.slots, priority=res.get("priority"), weight=float(res.get("weight", 1) or 1),
+                                                      preemptible=False, name=t.description, submit_time=time.time()))
+        m.kick()
+        return t
+
+    def on_assigned(self, pool_key: str, slot_ids: List[int]) -> bool:
+        """Called by the scheduler loop for requests whose id starts with ``cmd-``."""
+        t = self.tasks.get(pool_key[4:])
+        if t is None or t.state != "QUEUED":
+            return False
+        if not self.master.launch_enabled:
+            t.slot_ids, t.state = slot_ids, "RUNNING"
+            return True
+        try:
+            t.start(slot_ids)
+        except Exception as e:
+            logger.exception("failed to start %s %s", t.kind, t.id)
+            self.master.db.add_logs([(t.id, t.id + ".1", time.time(), "ERROR", None, "stdout", "master", f"failed to start: {e}\n")])
+            t.exit_code, t.end_time, t.state = 127, time.time(), "TERMINATED"
+            self.master.db.exec("UPDATE tasks SET state=?, end_time=? WHERE id=?", (t.state, t.end_time, t.id))
+            return False
+        return True
+
+    def get(self, task_id: str, kind: Optional[str] = None) -> CommandTask:
+        t = self.tasks.get(task_id)
+        if t is None or (kind is not None and t.kind != TYPES[kind]):
+            raise KeyError(task_id)
+        return t
+
+    def list(self, kind: str) -> List[CommandTask]:
+        return sorted((t for t in self.tasks.values() if t.kind == TYPES[kind]), key=lambda t: t.start_time)
+
+    def stop_all(self) -> None:
+        for t in list(self.tasks.values()):
+            if t.state != "TERMINATED":
+                t.kill()

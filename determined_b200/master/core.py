@@ -532,6 +532,9 @@ class Master:
         self._stop = threading.Event()
         self._sched_thread: Optional[threading.Thread] = None
         self.start_time = time.time()
+        from determined_b200.master import commands as _commands
+
+        self.commands = _commands.CommandManager(self)
         self._restore()
 
     @property
@@ -546,6 +549,7 @@ class Master:
     def stop(self) -> None:
         self._stop.set()
         self._kick.set()
+        self.commands.stop_all()
         with self.lock:
             for a in list(self.allocations.values()):
                 a.kill()
@@ -681,6 +685,10 @@ class Master:
                         self.pool.release(rid)
             d = self.pool.tick()
             for req, asg in d.to_allocate:
+                if req.allocation_id.startswith("cmd-"):          # command / shell / notebook / tensorboard task
+                    if not self.commands.on_assigned(req.allocation_id, sorted(s for slots in asg.values() for s in slots)):
+                        self.pool.release(req.allocation_id)
+                    continue
                 tid = int(req.allocation_id.split("-")[1])
                 t = self.trials.get(tid)
                 if t is None or not t.wants_resources():

@@ -232,3 +232,131 @@ def test_workload_sequencer_orders_train_validate_checkpoint(tmp_path):
     assert kinds[i4][2] == 4
     st = seq.get_state()
     assert st["steps_completed"] == 8 if "steps_completed" in st else True
+
+
+def test_commands_run_through_scheduler_logs_and_kill(cluster, capsys):
+    """NTSC: `det cmd run` schedules a generic task on slots, ships its output, reports the exit code;
+    a long-running shell task holds its slots until killed."""
+    import time
+
+    from determined_b200.cli import cli
+
+    m, sess, tmp = cluster
+    rc = cli.main(["cmd", "run", "--slots", "1", "--", "python", "-c", "import os; print('hello from', os.environ['DET_TASK_TYPE'], os.environ['DET_SLOT_IDS'])"])
+    out = capsys.readouterr().out
+    assert rc == 0 and "hello from COMMAND [" in out and "Launched command" in out
+    failing = sess.post("/api/v1/commands", json={"config": {"entrypoint": "exit 3"}}).json()["command"]
+    deadline = time.time() + 30
+    while time.time() < deadline:
+        c = sess.get(f"/api/v1/commands/{failing['id']}").json()["command"]
+        if c["state"] == "STATE_TERMINATED":
+            break
+        time.sleep(0.2)
+    assert c["exitStatus"] == 3
+    sh = sess.post("/api/v1/shells", json={"config": {"resources": {"slots": 2}}}).json()["shell"]
+    deadline = time.time() + 30
+    while time.time() < deadline and sess.get(f"/api/v1/shells/{sh['id']}").json()["shell"]["state"] != "STATE_RUNNING":
+        time.sleep(0.2)
+    used = [s for a in sess.get("/api/v1/agents").json()["agents"] for s in a["slots"].values() if s.get("container")]
+    assert len(used) == 2
+    assert [x["id"] for x in sess.get("/api/v1/shells").json()["shells"]] == [sh["id"]]
+    assert cli.main(["shell", "kill", sh["id"]]) == 0
+    deadline = time.time() + 30
+    while time.time() < deadline and sess.get(f"/api/v1/shells/{sh['id']}").json()["shell"]["state"] != "STATE_TERMINATED":
+        time.sleep(0.2)
+    assert sess.get(f"/api/v1/shells/{sh['id']}").json()["shell"]["state"] == "STATE_TERMINATED"
+    m.schedule_once()
+    used = [s for a in sess.get("/api/v1/agents").json()["agents"] for s in a["slots"].values() if s.get("container")]
+    assert used == []
+
+
+def test_streams_subscribe_sync_upsert_delete(cluster):
+    from determined_b200.common import streams
+
+    m, sess, tmp = cluster
+    w = sess.post("/api/v1/workspaces", json={"name": "ws-stream"}).json()["workspace"]
+    p1 = sess.post(f"/api/v1/workspaces/{w['id']}/projects", json={"name": "p1", "description": "d"}).json()["project"]
+    st = streams.Stream(streams.PollingStreamTransport(sess, poll_interval=0.1))
+    st.subscribe(sync_id="a", projects=streams.ProjectSpec(workspace_id=w["id"]))
+    assert next(st) == streams.Sync("a", False)
+    first = next(st)
+    assert isinstance(first, streams.wire.ProjectMsg) and first.id == p1["id"] and first.name == "p1"
+    assert next(st) == streams.Sync("a", True)
+    # online event: a new project in the subscribed workspace shows up without resubscribing
+    p2 = sess.post(f"/api/v1/workspaces/{w['id']}/projects", json={"name": "p2", "description": ""}).json()["project"]
+    ev = next(st)
+    assert isinstance(ev, streams.wire.ProjectMsg) and ev.id == p2["id"]
+    # resubscribe after a deletion: the cache's known keys produce a deletion message
+    sess.delete(f"/api/v1/projects/{p1['id']}")
+    st.subscribe(sync_id="b", projects=streams.ProjectSpec(workspace_id=w["id"]))
+    got = [next(st) for _ in range(3)]
+    assert got[0] == streams.Sync("b", False) and got[-1] == streams.Sync("b", True)
+    assert isinstance(got[1], streams.wire.ProjectsDeleted) and got[1].keys == str(p1["id"])
+    assert streams.encode_keys({1, 2, 3, 7}) == "1-3,7" and list(streams.range_encoded_keys("1-3,7")) == [1, 2, 3, 7]
+
+
+def test_model_hub_base_transformer_trial_native_gpt(tmp_path):
+    """model_hub's BaseTransformerTrial drives the native GPT through PyTorchTrial / Trainer on CPU."""
+    from determined_b200 import pytorch
+    from determined_b200.model_hub import huggingface as hf, utils as mh_utils
+
+    class LMTrial(hf.BaseTransformerTrial):
+        def _loader(self):
+            g = torch.Generator().manual_seed(0)
+            data = torch.randint(0, 512, (64, 33), generator=g)
+
+            class DS(torch.utils.data.Dataset):
+                def __len__(self):
+                    return 64
+
+                def __getitem__(self, i):
+                    return {"input_ids": data[i]}
+
+            return pytorch.DataLoader(DS(), batch_size=self.context.get_per_slot_batch_size())
+
+        def build_training_data_loader(self):
+            return self._loader()
+
+        def build_validation_data_loader(self):
+            return self._loader()
+
+        def evaluate_batch(self, batch, batch_idx):
+            ids = batch["input_ids"]
+            _, loss = self.model(ids[:, :-1], ids[:, 1:])
+            return {"val_loss": loss}
+
+    hparams = {"model_mode": "native-gpt", "gpt_preset": "tiny", "use_apex_amp": False, "use_pretrained_weights": False, "global_batch_size": 8,
+               "learning_rate": 3e-3, "weight_decay": 0.01, "num_warmup_steps": 2, "max_grad_norm": 1.0}
+    exp_conf = {"searcher": {"name": "single", "metric": "val_loss", "max_length": {"batches": 12}}, "hyperparameters": hparams,
+                "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ck")}}
+    with pytorch.init(hparams=hparams, exp_conf=exp_conf) as ctx:
+        trial = LMTrial(ctx)
+        assert trial.hparams.num_training_steps == 12
+        pytorch.Trainer(trial, ctx).fit(max_length=pytorch.Batch(12), validation_period=pytorch.Batch(6), reporting_period=pytorch.Batch(6))
+    groups = hf.group_parameters_for_optimizer(trial.model, 0.1)
+    assert groups[0]["weight_decay"] == 0.1 and groups[1]["weight_decay"] == 0.0 and len(groups[1]["params"]) > 0
+    assert mh_utils.compute_num_training_steps({"searcher": {"max_length": {"epochs": 2}}, "records_per_epoch": 80}, 8) == 20
+    d = mh_utils.AttrDict({"a": {"b": 1}})
+    assert d.a.b == 1
+    opt_kw, sched_kw = hf.default_parse_optimizer_lr_scheduler_kwargs({"learning_rate": 0.1, "num_training_steps": 5, "lr_scheduler_type": "cosine"})
+    assert opt_kw.learning_rate == 0.1 and sched_kw.lr_scheduler_type == "cosine"
+
+
+def test_execution_helpers(tmp_path):
+    from determined_b200 import _execution as ex
+
+    hp = ex._generate_random_hparam_values({"lr": {"type": "double", "minval": 0.1, "maxval": 0.2}, "n": {"type": "int", "minval": 1, "maxval": 3},
+                                            "c": {"type": "categorical", "vals": ["a", "b"]}, "k": {"type": "const", "val": 7}, "lg": {"type": "log", "base": 10, "minval": -3, "maxval": -1},
+                                            "nested": {"x": {"type": "const", "val": 1}}, "plain": 5})
+    assert 0.1 <= hp["lr"] <= 0.2 and hp["n"] in (1, 2, 3) and hp["c"] in ("a", "b") and hp["k"] == 7 and 1e-3 <= hp["lg"] <= 1e-1
+    assert hp["nested"] == {"x": 1} and hp["plain"] == 5
+    t = ex._make_test_experiment_config({"searcher": {"name": "adaptive_asha", "metric": "m", "max_trials": 9}, "hyperparameters": {"k": {"type": "const", "val": 2}}})
+    assert t["searcher"] == {"name": "single", "metric": "m", "max_length": {"batches": 1}} and t["max_restarts"] == 0 and t["hyperparameters"] == {"k": 2}
+    cfg = ex._make_local_execution_exp_config({"resources": {"slots_per_trial": 8}, "name": "x"}, str(tmp_path), managed_training=False, test_mode=True)
+    assert cfg["resources"] == {"slots_per_trial": 1, "native_parallel": False} and cfg["checkpoint_storage"]["host_path"] == str(tmp_path)
+    ctx, cfg2, hp2 = ex._make_local_execution_env(False, True, {"hyperparameters": {"k": {"type": "const", "val": 3}}}, str(tmp_path))
+    with ctx:
+        assert hp2 == {"k": 3}
+    with pytest.raises(BaseException, match="SystemExit"):
+        with ex._local_execution_manager(tmp_path):
+            raise SystemExit(1)
