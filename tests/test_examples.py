@@ -1,0 +1,58 @@
+"""The shipped examples run (CPU, local mode): a user of the reference finds working counterparts."""
+import importlib.util
+import os
+import pathlib
+import subprocess
+import sys
+
+import pytest
+import yaml
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+EX = ROOT / "examples"
+
+
+def _local_test(example_dir: pathlib.Path, cfg: str) -> None:
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    r = subprocess.run([sys.executable, "-m", "determined_b200.cli", "experiment", "create", cfg, ".", "--local", "--test"], cwd=example_dir, env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "Model training test succeeded." in r.stdout, r.stdout[-3000:]
+
+
+def test_mnist_tutorial_local_test_mode():
+    _local_test(EX / "tutorials" / "mnist_pytorch", "const.yaml")
+
+
+def test_all_example_configs_validate():
+    from determined_b200.master import expconf
+
+    n = 0
+    for f in EX.rglob("*.yaml"):
+        cfg = yaml.safe_load(f.read_text())
+        full = expconf.finalize(cfg, {"checkpoint_storage": {"type": "shared_fs", "host_path": "/tmp/ck"}})
+        assert full["searcher"]["name"] in ("single", "adaptive_asha", "custom"), f
+        n += 1
+    assert n >= 7
+
+
+def test_gpt_neox_deepspeed_example_trains_tiny_model(tmp_path, monkeypatch):
+    from determined_b200 import pytorch
+    from determined_b200.pytorch import deepspeed as det_ds
+
+    spec = importlib.util.spec_from_file_location("gpt2_trial", EX / "deepspeed" / "gpt_neox" / "gpt2_trial.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    monkeypatch.chdir(tmp_path)
+    hp = {"model": "tiny", "seq_length": 32, "model_overrides": {"rotary_pct": 0.25, "parallel_residual": True, "tie_embeddings": False},
+          "deepspeed_config": str(EX / "deepspeed" / "gpt_neox" / "ds_config.json"),
+          "overwrite_deepspeed_args": {"gradient_accumulation_steps": 2, "bf16": {"enabled": False}, "optimizer": {"params": {"lr": 3e-3}}}}
+    with det_ds.init(hparams=hp, exp_conf={"checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ck")}}, require_gpu=False) as ctx:
+        trial = mod.GPT2Trial(ctx)
+        det_ds.Trainer(trial, ctx).fit(max_length=pytorch.Batch(6), validation_period=pytorch.Batch(6))
+    assert trial.engine.global_steps == 6 and trial.engine.micro_steps == 12
+
+
+def test_core_api_example_runs_off_cluster():
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    r = subprocess.run([sys.executable, "train.py"], cwd=EX / "tutorials" / "core_api", env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-2000:]
