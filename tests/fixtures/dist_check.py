@@ -246,6 +246,52 @@ def check_gemm_comm(rank, world, dev):
         print("GEMM_COMM_TIMING", json.dumps({"world": world, "rows_per_rank": rows, "K": K, "N": N, "ms": res}), flush=True)
 
 
+def check_gpt_tp(rank, world, dev):
+    """Tensor+sequence-parallel GPT over the fused GEMM+collective kernels == the unsharded native GPT."""
+    from determined_b200.models import gpt, gpt_tp
+    from determined_b200.ops import comm, gemm_comm
+
+    group = comm.PeerGroup.from_torch_distributed(dev)
+    tp = gemm_comm.TensorParallelGemm(group)
+    for kw in ({}, {"rotary_pct": 0.25, "parallel_residual": True, "tie_embeddings": False}):
+        torch.manual_seed(11)
+        cfg = gpt.GPTConfig(n_layer=2, n_head=4 * world // 2 if world > 2 else 4, n_embd=128 * (4 * world // 2 if world > 2 else 4), block_size=256, vocab_size=1024, **kw)
+        full = gpt.GPT(cfg).to(dev)
+        for p in full.parameters():
+            dist.broadcast(p.data, 0)
+        model = gpt_tp.TPGPT(cfg, tp).to(dev)
+        model.load_from_full(full)
+        B, S = 2 * world, 256
+        idx = torch.randint(0, 1024, (B, S + 1), device=dev)
+        dist.broadcast(idx, 0)
+        _, want = full(idx[:, :-1], idx[:, 1:])
+        want.backward()
+        got = model(idx[:, :-1], idx[:, 1:])
+        got.backward()
+        model.sync_replicated_grads()
+        tot = got.detach().clone()
+        dist.all_reduce(tot)
+        assert abs(float(tot) - float(want)) < 2e-2, (float(tot), float(want))
+
+        def rel(a, b):
+            return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-9))
+
+        E, D, H = cfg.n_embd, cfg.head_dim, cfg.n_head
+        hl = H // world
+        for mine, theirs in zip(model.blocks, full.blocks):
+            g = theirs.qkv.weight.grad.view(3, H, D, E)[:, rank * hl:(rank + 1) * hl].reshape(-1, E)
+            assert rel(mine.qkv_w.grad, g) < 5e-2, ("qkv_w", rel(mine.qkv_w.grad, g))
+            assert rel(mine.proj_w.grad, theirs.proj.weight.grad[:, rank * hl * D:(rank + 1) * hl * D]) < 5e-2
+            F4 = mine.fc1_w.shape[0]
+            assert rel(mine.fc1_w.grad, theirs.mlp.fc1.weight.grad[rank * F4:(rank + 1) * F4]) < 5e-2
+            assert rel(mine.fc2_w.grad, theirs.mlp.fc2.weight.grad[:, rank * F4:(rank + 1) * F4]) < 5e-2
+            assert rel(mine.fc2_b.grad, theirs.mlp.fc2.bias.grad) < 5e-2
+            assert rel(mine.ln1.weight.grad, theirs.ln1.weight.grad) < 5e-2
+        assert rel(model.wte.weight.grad, full.wte.weight.grad) < 5e-2
+        assert rel(model.ln_f.weight.grad, full.ln_f.weight.grad) < 5e-2
+    dist.barrier()
+
+
 def main():
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(local)
@@ -260,6 +306,8 @@ def main():
         check_resnet_matches_ddp(rank, world, dev)
     if which in ("all", "gemm_comm"):
         check_gemm_comm(rank, world, dev)
+    if which in ("all", "gpt_tp"):
+        check_gpt_tp(rank, world, dev)
     dist.barrier()
     if rank == 0:
         print("DIST_CHECK_OK", which, flush=True)
