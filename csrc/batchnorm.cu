@@ -156,10 +156,10 @@ bn_stats_kernel(const T* __restrict__ x, int64_t M, int C, float* __restrict__ p
   if (threadIdx.x == 0 && p.num_batches_tracked) *p.num_batches_tracked += 1;
 }
 
-template <typename T, bool kRelu>
+template <typename T, bool kRelu, bool kAdd = false>
 __global__ void __launch_bounds__(kBT)
 bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t nvec, int C,
-                const float* __restrict__ scale, const float* __restrict__ shift) {
+                const float* __restrict__ scale, const float* __restrict__ shift, const T* __restrict__ res = nullptr) {
   constexpr int V = Vec<T>::N;
   const int cthreads = C / V;
   const int64_t tid = (int64_t)blockIdx.x * kBT + threadIdx.x;
@@ -169,20 +169,22 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t nvec, int C,
   for (int j = 0; j < V; ++j) { sc[j] = scale[c0 + j]; sh[j] = shift[c0 + j]; }
   const int64_t stride = (int64_t)gridDim.x * kBT;
   for (int64_t i = tid; i < nvec; i += stride) {
-    float v[V];
+    float v[V], rr[V];
     Vec<T>::ld(x + i * V, v);
+    if (kAdd) Vec<T>::ld(res + i * V, rr);
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       v[j] = fmaf(v[j], sc[j], sh[j]);
+      if (kAdd) v[j] += rr[j];
       if (kRelu) v[j] = fmaxf(v[j], 0.f);
     }
     Vec<T>::st(y + i * V, v);
   }
 }
 
-template <typename T>
+template <typename T, bool kMask = false>
 __global__ void __launch_bounds__(kBT)
-bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t M, int C,
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ yout, int64_t M, int C,
                      const float* __restrict__ mean, const float* __restrict__ invstd,
                      const float* __restrict__ gamma, float* __restrict__ part,
                      unsigned int* __restrict__ ticket, float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -192,13 +194,19 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
   float mu[V], is[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) { mu[j] = mean[cg * V + j]; is[j] = invstd[cg * V + j]; }
-  bool last = column_reduce<T, 2, 2>(M, C, part, ticket,
-      [&](int64_t r, int c0, float (*regs)[V]) { Vec<T>::ld(dy + r * C + c0, regs[0]); Vec<T>::ld(x + r * C + c0, regs[1]); },
+  // kMask: the forward fused a ReLU after the affine (+ residual); its gradient gate is (output > 0)
+  bool last = column_reduce<T, 2, kMask ? 3 : 2>(M, C, part, ticket,
+      [&](int64_t r, int c0, float (*regs)[V]) {
+        Vec<T>::ld(dy + r * C + c0, regs[0]);
+        Vec<T>::ld(x + r * C + c0, regs[1]);
+        if (kMask) Vec<T>::ld(yout + r * C + c0, regs[2]);
+      },
       [&](float (*regs)[V], float (*acc)[V]) {
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-          acc[0][j] += regs[0][j];
-          acc[1][j] = fmaf(regs[0][j], (regs[1][j] - mu[j]) * is[j], acc[1][j]);
+          const float g = (kMask && !(regs[kMask ? 2 : 0][j] > 0.f)) ? 0.f : regs[0][j];
+          acc[0][j] += g;
+          acc[1][j] = fmaf(g, (regs[1][j] - mu[j]) * is[j], acc[1][j]);
         }
       });
   if (!last) return;
@@ -216,10 +224,11 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
   }
 }
 
-template <typename T>
+template <typename T, bool kMask = false>
 __global__ void __launch_bounds__(kBT)
 bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t nvec, int C,
-                    const float* __restrict__ mean, const float* __restrict__ coef) {
+                    const float* __restrict__ mean, const float* __restrict__ coef, const T* __restrict__ yout = nullptr,
+                    T* __restrict__ dres = nullptr) {
   constexpr int V = Vec<T>::N;
   const int cthreads = C / V;
   const int64_t tid = (int64_t)blockIdx.x * kBT + threadIdx.x;
@@ -232,6 +241,13 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __rest
     float g[V], v[V];
     Vec<T>::ld(dy + i * V, g);
     Vec<T>::ld(x + i * V, v);
+    if (kMask) {
+      float yo[V];
+      Vec<T>::ld(yout + i * V, yo);
+#pragma unroll
+      for (int j = 0; j < V; ++j) if (!(yo[j] > 0.f)) g[j] = 0.f;
+      if (dres != nullptr) Vec<T>::st(dres + i * V, g);     // gradient of the residual branch = gated dy
+    }
 #pragma unroll
     for (int j = 0; j < V; ++j) g[j] = a[j] * (g[j] - b[j] - (v[j] - mu[j]) * k[j]);
     Vec<T>::st(dx + i * V, g);
@@ -323,11 +339,67 @@ DETB200_API int detb200_bn_bwd(const void* dy, const void* x, void* dx, int64_t 
   int64_t nvec = M * C / V;
   int ag = apply_grid(nvec);
   if (dtype == 1) {
-    bn_bwd_reduce_kernel<__nv_bfloat16><<<rg, kBT, smem, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, M, C, mean, invstd, gamma, part, ticket, dgamma, dbeta, coef);
+    bn_bwd_reduce_kernel<__nv_bfloat16><<<rg, kBT, smem, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, nullptr, M, C, mean, invstd, gamma, part, ticket, dgamma, dbeta, coef);
     bn_bwd_apply_kernel<__nv_bfloat16><<<ag, kBT, 0, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, nvec, C, mean, coef);
   } else {
-    bn_bwd_reduce_kernel<float><<<rg, kBT, smem, stream>>>((const float*)dy, (const float*)x, M, C, mean, invstd, gamma, part, ticket, dgamma, dbeta, coef);
+    bn_bwd_reduce_kernel<float><<<rg, kBT, smem, stream>>>((const float*)dy, (const float*)x, nullptr, M, C, mean, invstd, gamma, part, ticket, dgamma, dbeta, coef);
     bn_bwd_apply_kernel<float><<<ag, kBT, 0, stream>>>((const float*)dy, (const float*)x, (float*)dx, nvec, C, mean, coef);
+  }
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+// Fused variants.  Forward: y = relu?(bn(x) + residual?).  Backward: `y` (the forward output) gates dy by (y > 0) when
+// the forward applied a ReLU; `dres` (nullable) receives the gated dy = gradient of the residual branch.
+DETB200_API int detb200_bn_fwd_train_fused(const void* x, const void* residual, void* y, int64_t M, int C, const float* gamma,
+                                           const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+                                           float* mean, float* invstd, float* scale, float* shift, float momentum, float eps, int relu,
+                                           void* workspace, int dtype, cudaStream_t stream) {
+  if (residual == nullptr)
+    return detb200_bn_fwd_train(x, y, M, C, gamma, beta, running_mean, running_var, num_batches_tracked, mean, invstd, scale, shift, momentum,
+                                eps, relu, workspace, dtype, stream);
+  const int V = dtype == 1 ? 8 : 4;
+  if (M <= 0) return 0;
+  if (!shape_ok(C, V)) { detb200_set_error("bn: C=%d unsupported for this dtype", C); return DETB200_ERR_UNSUPPORTED; }
+  float* part = (float*)workspace;
+  unsigned int* ticket = (unsigned int*)((char*)workspace + (int64_t)2 * C * 4);
+  BnParams p{gamma, beta, running_mean, running_var, num_batches_tracked, mean, invstd, scale, shift, momentum, eps};
+  const int rg = reduce_grid(M, C, V);
+  const size_t smem = (size_t)kBT * 2 * V * sizeof(float);
+  const int64_t nvec = M * C / V;
+  const int ag = apply_grid(nvec);
+  if (dtype == 1) {
+    bn_stats_kernel<__nv_bfloat16><<<rg, kBT, smem, stream>>>((const __nv_bfloat16*)x, M, C, part, ticket, p);
+    if (relu) bn_apply_kernel<__nv_bfloat16, true, true><<<ag, kBT, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, nvec, C, scale, shift, (const __nv_bfloat16*)residual);
+    else bn_apply_kernel<__nv_bfloat16, false, true><<<ag, kBT, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, nvec, C, scale, shift, (const __nv_bfloat16*)residual);
+  } else {
+    bn_stats_kernel<float><<<rg, kBT, smem, stream>>>((const float*)x, M, C, part, ticket, p);
+    if (relu) bn_apply_kernel<float, true, true><<<ag, kBT, 0, stream>>>((const float*)x, (float*)y, nvec, C, scale, shift, (const float*)residual);
+    else bn_apply_kernel<float, false, true><<<ag, kBT, 0, stream>>>((const float*)x, (float*)y, nvec, C, scale, shift, (const float*)residual);
+  }
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+DETB200_API int detb200_bn_bwd_fused(const void* dy, const void* x, const void* y, void* dx, void* dres, int64_t M, int C, const float* gamma,
+                                     const float* mean, const float* invstd, float* dgamma, float* dbeta, float* coef, void* workspace,
+                                     int dtype, cudaStream_t stream) {
+  if (y == nullptr) return detb200_bn_bwd(dy, x, dx, M, C, gamma, mean, invstd, dgamma, dbeta, coef, workspace, dtype, stream);
+  const int V = dtype == 1 ? 8 : 4;
+  if (M <= 0) return 0;
+  if (!shape_ok(C, V)) { detb200_set_error("bn: C=%d unsupported for this dtype", C); return DETB200_ERR_UNSUPPORTED; }
+  float* part = (float*)workspace;
+  unsigned int* ticket = (unsigned int*)((char*)workspace + (int64_t)2 * C * 4);
+  const int rg = reduce_grid(M, C, V);
+  const size_t smem = (size_t)kBT * 2 * V * sizeof(float);
+  const int64_t nvec = M * C / V;
+  const int ag = apply_grid(nvec);
+  if (dtype == 1) {
+    bn_bwd_reduce_kernel<__nv_bfloat16, true><<<rg, kBT, smem, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, C, mean, invstd, gamma, part, ticket, dgamma, dbeta, coef);
+    bn_bwd_apply_kernel<__nv_bfloat16, true><<<ag, kBT, 0, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, nvec, C, mean, coef, (const __nv_bfloat16*)y, (__nv_bfloat16*)dres);
+  } else {
+    bn_bwd_reduce_kernel<float, true><<<rg, kBT, smem, stream>>>((const float*)dy, (const float*)x, (const float*)y, M, C, mean, invstd, gamma, part, ticket, dgamma, dbeta, coef);
+    bn_bwd_apply_kernel<float, true><<<ag, kBT, 0, stream>>>((const float*)dy, (const float*)x, (float*)dx, nvec, C, mean, coef, (const float*)y, (float*)dres);
   }
   DETB200_LAUNCH_CHECK();
   return 0;

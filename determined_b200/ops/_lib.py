@@ -80,6 +80,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_bn_workspace_bytes", i64, [i])
     _sig(lib, "detb200_bn_fwd_train", i, [p, p, i64, i, p, p, p, p, p, p, p, p, p, f, f, i, p, i, p])
     _sig(lib, "detb200_bn_apply", i, [p, p, i64, i, p, p, i, i, p])
+    _sig(lib, "detb200_bn_fwd_train_fused", i, [p, p, p, i64, i, p, p, p, p, p, p, p, p, p, f, f, i, p, i, p])
+    _sig(lib, "detb200_bn_bwd_fused", i, [p, p, p, p, p, i64, i, p, p, p, p, p, p, p, i, p])
     _sig(lib, "detb200_bn_bwd", i, [p, p, p, i64, i, p, p, p, p, p, p, p, i, p])
     # tcgen05 GEMM family (csrc/gemm_sm100.cu)
     _sig(lib, "detb200_gemm_bf16", i, [p, p, p, p, p, i64, i64, i64, i64, i64, i64, i64, i, i, i, i, i, i, p])
@@ -101,7 +103,17 @@ def load() -> ctypes.CDLL:
     return lib
 
 
+# kernels launched per native entry point (for the launch accounting bench.py reports); default 1
+KERNELS_PER_CALL = {"bn_fwd_train": 2, "bn_bwd": 2, "norm_bwd": 3, "attn_bwd": 3, "optimizer_step": 2, "sumsq": 2}
+LAUNCHES = [0]
+
+
+def count_launches(n: int) -> None:
+    LAUNCHES[0] += n
+
+
 def check(rc: int, what: str = "") -> None:
+    LAUNCHES[0] += KERNELS_PER_CALL.get(what, 1)
     if rc != 0:
         lib = load()
         msg = lib.detb200_last_error()

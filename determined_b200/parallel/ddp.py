@@ -158,6 +158,13 @@ class GenericGradEngine(GradEngineBase):
 class FusedGradEngine(GradEngineBase):
     fused = True
 
+    @property
+    def kernel_launches(self) -> int:
+        """Native kernels launched by this process so far (every entry point of the library counts itself)."""
+        from determined_b200.ops import _lib as _l
+
+        return _l.LAUNCHES[0]
+
     def __init__(self, dist_ctx: Any, device: torch.device, aggregation_frequency: int,
                  bucket_cap_mb: float = 25.0, timeout_s: float = 120.0) -> None:
         super().__init__(dist_ctx, device, aggregation_frequency)
@@ -167,7 +174,6 @@ class FusedGradEngine(GradEngineBase):
         self.bucket_cap = int(bucket_cap_mb * (1 << 20))
         self.timeout_s = timeout_s
         self.comm_stream = torch.cuda.Stream(device=device) if dist_ctx.size > 1 else None
-        self.kernel_launches = 0
 
     # ------------------------------------------------------------------ set-up
     def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool) -> torch.optim.Optimizer:
@@ -243,7 +249,6 @@ class FusedGradEngine(GradEngineBase):
             scale /= self.agg
         comm.allreduce_fused(rec.group, rec.peer_bufs, b.offset, b.numel, scale, stream=self.comm_stream,
                              timeout_s=self.timeout_s)
-        self.kernel_launches += 1
         b.launched = True
 
     def _launch_ready(self, rec: _OptRecord) -> None:
@@ -294,12 +299,10 @@ class FusedGradEngine(GradEngineBase):
                 grad_scale = optim.clip_coef(terms, clip_grads.max_norm, rec.scratch)
             else:
                 optim.sumsq(lay.flat_grad, rec.scratch)
-                self.kernel_launches += 1
                 # the norm is of the *averaged* gradient: fold static_scale^2 in through extra handling
                 if static_scale != 1.0:
                     rec.scratch.sumsq.mul_(static_scale * static_scale)
                 grad_scale = optim.clip_coef(rec.scratch.sumsq, clip_grads.max_norm, rec.scratch)
-            self.kernel_launches += 1
             clip_grads.last_norm = rec.scratch.norm
         elif clip_grads is not None:
             if static_scale != 1.0:
@@ -311,7 +314,6 @@ class FusedGradEngine(GradEngineBase):
 
         if use_fused_step:
             optimizer.step(grad_scale=grad_scale, static_scale=static_scale, zero_grad=auto_zero_grads)
-            self.kernel_launches += 2 * len(optimizer.param_groups)
         else:
             if static_scale != 1.0:
                 lay.flat_grad.mul_(static_scale)

@@ -221,7 +221,9 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
 
             n = batchnorm.convert_batchnorm_(model)
             if n:
-                logger.info("fused engine: %d BatchNorm2d modules now run the native channels-last kernels", n)
+                nb = batchnorm.fuse_residual_blocks_(model)
+                logger.info("fused engine: %d BatchNorm2d modules now run the native channels-last kernels "
+                            "(%d residual blocks with ReLU / add folded into them)", n, nb)
         if self.experimental._auto_amp:
             model = self.autocast_forward_pass(model)
         self.models.append(model)

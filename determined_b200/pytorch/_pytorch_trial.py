@@ -579,9 +579,9 @@ class _PyTorchTrialController:
             if sync is not None:
                 sync()
         gs.graph.replay()
-        eng = self.context._get_engine()
-        if hasattr(eng, "kernel_launches"):
-            eng.kernel_launches += gs.launches
+        from determined_b200.ops import _lib as _native_lib
+
+        _native_lib.count_launches(gs.launches)          # kernels recorded in the graph ran once more
         return _graph_outputs(gs.static_out)
 
     def _needs_more_warmup(self, boundary: bool) -> bool:
@@ -596,15 +596,16 @@ class _PyTorchTrialController:
             if sync is not None:
                 sync()
         g = torch.cuda.CUDAGraph()
-        eng = self.context._get_engine()
-        n0 = getattr(eng, "kernel_launches", 0)
+        from determined_b200.ops import _lib as _native_lib
+
+        n0 = _native_lib.LAUNCHES[0]
         with torch.cuda.graph(g):
             out = self.trial.train_batch(batch=gs.static_in, epoch_idx=epoch_idx, batch_idx=batch_idx)
             if isinstance(out, torch.Tensor):
                 out = {"loss": out}
             gs.static_out = {k: (v.detach() if isinstance(v, torch.Tensor) else v) for k, v in out.items()}
         gs.graph = g
-        gs.launches = getattr(eng, "kernel_launches", 0) - n0
+        gs.launches = _native_lib.LAUNCHES[0] - n0       # counted once at capture = the single replay below
         # capture does not execute: replay once so this batch is actually trained on
         g.replay()
         return _graph_outputs(gs.static_out)

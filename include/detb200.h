@@ -141,6 +141,16 @@ int detb200_bn_apply(const void* x, void* y, int64_t M, int C, const float* scal
 int detb200_bn_bwd(const void* dy, const void* x, void* dx /* may alias dy */, int64_t M, int C, const float* gamma,
                    const float* mean, const float* invstd, float* dgamma, float* dbeta, float* coef /* 3*C */,
                    void* workspace, int dtype, detb200_stream_t stream);
+/* Fused variants: y = relu?(bn(x) + residual?); the backward gates dy by (y > 0) when `y` is given and writes the gated dy
+ * (gradient of the residual branch) to `dres` when non-null.  Replaces the separate add / ReLU / threshold_backward kernels
+ * of a ResNet basic block. */
+int detb200_bn_fwd_train_fused(const void* x, const void* residual /* nullable */, void* y, int64_t M, int C, const float* gamma,
+                               const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+                               float* mean, float* invstd, float* scale, float* shift, float momentum, float eps, int relu,
+                               void* workspace, int dtype, detb200_stream_t stream);
+int detb200_bn_bwd_fused(const void* dy, const void* x, const void* y /* nullable */, void* dx, void* dres /* nullable */, int64_t M, int C,
+                         const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta, float* coef,
+                         void* workspace, int dtype, detb200_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Softmax cross-entropy (csrc/xent.cu).  Reference: log_softmax + nll_loss in

@@ -254,3 +254,75 @@ def test_batchnorm_train_fwd_bwd(dtype, shape):
     # eval mode goes through the stock path and must agree exactly
     mine.eval(); ref.eval()
     torch.testing.assert_close(mine(x.detach().float()), ref(x.detach().float()), rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_batchnorm_fused_relu_and_residual(dtype):
+    from determined_b200.ops import batchnorm
+
+    torch.manual_seed(3)
+    dev = torch.device("cuda")
+    N, C, H, W = 16, 64, 8, 8
+    x = torch.randn(N, C, H, W, device=dev, dtype=dtype).contiguous(memory_format=torch.channels_last).requires_grad_()
+    res = torch.randn(N, C, H, W, device=dev, dtype=dtype).contiguous(memory_format=torch.channels_last).requires_grad_()
+    dy = torch.randn(N, C, H, W, device=dev, dtype=dtype).contiguous(memory_format=torch.channels_last)
+    for use_res in (False, True):
+        bn = batchnorm.FusedBatchNorm2d(C).to(dev)
+        ref = torch.nn.BatchNorm2d(C).to(dev)
+        with torch.no_grad():
+            bn.weight.uniform_(0.5, 1.5)
+            bn.bias.uniform_(-0.5, 0.5)
+            ref.load_state_dict(bn.state_dict())
+        y = bn.forward_fused(x, res if use_res else None, True)
+        y.backward(dy)
+        gx, gr = x.grad.clone(), (res.grad.clone() if use_res else None)
+        gw, gb = bn.weight.grad.clone(), bn.bias.grad.clone()
+        x.grad = None
+        res.grad = None
+        xr, rr = x.detach().float().requires_grad_(), res.detach().float().requires_grad_()
+        z = ref(xr)
+        yr = torch.relu(z + rr) if use_res else torch.relu(z)
+        yr.backward(dy.float())
+        tol = dict(rtol=3e-2, atol=3e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+        torch.testing.assert_close(y.float(), yr, **tol)
+        # entries within rounding of the ReLU kink may be gated differently in bf16: compare in norm
+        rel = lambda a, b: float((a.float() - b.float()).norm() / (b.float().norm() + 1e-9))  # noqa: E731
+        lim = 3e-2 if dtype == torch.bfloat16 else 1e-4
+        assert rel(gx, xr.grad) < lim and rel(gw, ref.weight.grad) < lim and rel(gb, ref.bias.grad) < lim
+        if use_res:
+            assert rel(gr, rr.grad) < lim
+        torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-2, atol=1e-3)
+
+
+def test_residual_block_fusion_is_verified_and_matches():
+    from determined_b200.models.resnet_cifar import BasicBlock, resnet18_cifar
+    from determined_b200.ops import batchnorm
+
+    torch.manual_seed(4)
+    dev = torch.device("cuda")
+    model = resnet18_cifar().to(dev).to(memory_format=torch.channels_last)
+    ref = resnet18_cifar().to(dev).to(memory_format=torch.channels_last)
+    ref.load_state_dict(model.state_dict())
+    assert batchnorm.convert_batchnorm_(model) == 20
+    assert batchnorm.fuse_residual_blocks_(model) == 8
+
+    class Odd(BasicBlock):                 # same children, different math: must not be patched
+        def forward(self, x):
+            return super().forward(x) * 2.0
+
+    odd = Odd(64, 64).to(dev)
+    batchnorm.convert_batchnorm_(odd)
+    assert batchnorm.fuse_residual_blocks_(odd) == 0
+    x = torch.randn(32, 3, 32, 32, device=dev).contiguous(memory_format=torch.channels_last)
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        out, out_ref = model(x), ref(x)
+        torch.testing.assert_close(out, out_ref, rtol=1e-3, atol=1e-3)
+        out.square().mean().backward()
+        out_ref.square().mean().backward()
+        for (n, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+            rel = float((a.grad - b.grad).norm() / (b.grad.norm() + 1e-9))
+            assert rel < 5e-3, (n, rel)
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
