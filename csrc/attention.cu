@@ -325,20 +325,20 @@ struct AttnBwdArgs {
   int causal;
 };
 
-// D fixed at 128
-struct BCfg {
-  static constexpr int D = 128;
+template <int kD> struct BCfg {
+  static constexpr int D = kD;
   static constexpr int kKBytes = kBwdKeys * D * 2;          // 32 KiB (K or V)
   static constexpr int kQBytes = kBwdQ * D * 2;             // 16 KiB (Q_i or dO_i)
   static constexpr int kdSBytes = kBwdKeys * kBwdQ * 2;     // 16 KiB
   static constexpr int kSmemBytes = 2 * kKBytes + 4 * kQBytes + kdSBytes + 1024 /*align*/ + 2 * 2 * kBwdQ * 4 /*lse, delta*/ + 256;
-  static constexpr int tS = 0, tdP = 64, tP = 128, tdS = 160, tdQ = 192, tdV = 256, tdK = 384;
+  static constexpr int tS = 0, tdP = 64, tP = 128, tdS = 160, tdQ = 192, tdV = 256, tdK = 256 + kD;
 };
 
+template <int kD>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                 const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do, const AttnBwdArgs args) {
-  using C = BCfg;
+  using C = BCfg<kD>;
   constexpr int D = C::D;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -388,7 +388,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       if (lane == 0) {
         mbar_expect_tx(kv_full, 2 * C::kKBytes);
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
+        for (int hh = 0; hh < D / 64; ++hh) {
           tma_load_4d(sK + hh * (kBwdKeys * 128), &tmap_k, kv_full, hh * 64, h, k0, b);
           tma_load_4d(sV + hh * (kBwdKeys * 128), &tmap_v, kv_full, hh * 64, h, k0, b);
         }
@@ -398,7 +398,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           mbar_expect_tx(qdo_full(st), 2 * C::kQBytes);
           const uint32_t sQ = sQ0 + st * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
 #pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
+          for (int hh = 0; hh < D / 64; ++hh) {
             tma_load_4d(sQ + hh * (kBwdQ * 128), &tmap_q, qdo_full(st), hh * 64, h, q0, b);
             tma_load_4d(sdO + hh * (kBwdQ * 128), &tmap_do, qdo_full(st), hh * 64, h, q0, b);
           }
@@ -455,7 +455,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           }
 #pragma unroll
           for (int k = 0; k < kBwdKeys / 16; ++k) {    // reduction over the 128 keys
-            const uint64_t da = smem_desc_sw128(sK + k * 2048, kBwdKeys * 128, 1024);
+            const uint64_t da = smem_desc_sw128(sK + k * 2048, D == 128 ? kBwdKeys * 128 : 0, 1024);
             const uint64_t db = smem_desc_sw128(sdS + k * 2048, kBwdKeys * 128, 1024);
             mma_f16_ss(tmem_base + C::tdQ, da, db, idesc_dq, k != 0 ? 1u : 0u);
           }
@@ -481,9 +481,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         tc_fence_before();
         mbar_arrive(dq_empty);
         const int q0 = (i_min + it) * kBwdQ + half * 32;
+        if (row < D) {                          // D == 64: TMEM lanes 64..127 hold duplicates of the padded MMA rows
 #pragma unroll
-        for (int c = 0; c < 32; ++c)
-          if (q0 + c < args.S) atomicAdd(dq_base + (int64_t)(q0 + c) * args.H * D + row, __uint_as_float(r[c]));
+          for (int c = 0; c < 32; ++c)
+            if (q0 + c < args.S) atomicAdd(dq_base + (int64_t)(q0 + c) * args.H * D + row, __uint_as_float(r[c]));
+        }
       };
 
       for (int it = 0; it < n_it; ++it) {
@@ -539,15 +541,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       mbar_wait(mma_done, (n_it - 1) & 1);
       tc_fence_after();
       drain_dq(n_it - 1);
-      // dV, dK: this thread owns key row `row`, columns [64*half, 64*half + 64)
+      // dV, dK: this thread owns key row `row`, columns [D/2 * half, D/2 * half + D/2)
       const bool row_ok = key < args.S;
 #pragma unroll
       for (int which = 0; which < 2; ++which) {
         __nv_bfloat16* base = which == 0 ? args.dV + (int64_t)b * args.dv_sb + (int64_t)key * args.dv_ss + (int64_t)h * args.dv_sh
                                          : args.dK + (int64_t)b * args.dk_sb + (int64_t)key * args.dk_ss + (int64_t)h * args.dk_sh;
-        const uint32_t tcol = tmem_base + (which == 0 ? C::tdV : C::tdK) + lane_off + half * 64;
+        const uint32_t tcol = tmem_base + (which == 0 ? C::tdV : C::tdK) + lane_off + half * (D / 2);
 #pragma unroll
-        for (int c = 0; c < 64; c += 32) {
+        for (int c = 0; c < D / 2; c += 32) {
           uint32_t r[32];
           tmem_ld_32x32(tcol + c, r);
           tmem_ld_wait();
@@ -559,7 +561,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
               u.y = pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
               u.z = pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
               u.w = pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
-              *reinterpret_cast<uint4*>(base + half * 64 + c + i) = u;
+              *reinterpret_cast<uint4*>(base + half * (D / 2) + c + i) = u;
             }
           }
         }
@@ -569,9 +571,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     // keys nobody attends to (cannot happen with S_q == S_kv, kept for safety): zero gradients
     const int row = (warp & 3) * 32 + lane, half = (warp - 2) >> 2, key = k0 + row;
     if (key < args.S) {
-      for (int c = 0; c < 64; c += 8) {
-        *reinterpret_cast<uint4*>(args.dV + (int64_t)b * args.dv_sb + (int64_t)key * args.dv_ss + (int64_t)h * args.dv_sh + half * 64 + c) = make_uint4(0, 0, 0, 0);
-        *reinterpret_cast<uint4*>(args.dK + (int64_t)b * args.dk_sb + (int64_t)key * args.dk_ss + (int64_t)h * args.dk_sh + half * 64 + c) = make_uint4(0, 0, 0, 0);
+      for (int c = 0; c < kD / 2; c += 8) {
+        *reinterpret_cast<uint4*>(args.dV + (int64_t)b * args.dv_sb + (int64_t)key * args.dv_ss + (int64_t)h * args.dv_sh + half * (kD / 2) + c) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(args.dK + (int64_t)b * args.dk_sb + (int64_t)key * args.dk_ss + (int64_t)h * args.dk_sh + half * (kD / 2) + c) = make_uint4(0, 0, 0, 0);
       }
     }
   }
@@ -584,9 +586,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   }
 }
 
-// delta[b,h,s] = sum_d O * dO   (one warp per row, D = 128: 4 elements per lane)
+// delta[b,h,s] = sum_d O * dO   (one warp per row; lanes cover D in 4-element pieces)
 __global__ void __launch_bounds__(256)
-attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S,
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S, int D,
                   int64_t o_sb, int64_t o_ss, int64_t o_sh, int64_t do_sb, int64_t do_ss, int64_t do_sh) {
   const int lane = threadIdx.x & 31;
   const int64_t rows = (int64_t)B * H * S;
@@ -594,9 +596,12 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
     const int s = (int)(r % S);
     const int h = (int)((r / S) % H);
     const int64_t b = r / ((int64_t)S * H);
-    const uint2 a = *reinterpret_cast<const uint2*>(o + b * o_sb + (int64_t)s * o_ss + (int64_t)h * o_sh + lane * 4);
-    const uint2 g = *reinterpret_cast<const uint2*>(d_o + b * do_sb + (int64_t)s * do_ss + (int64_t)h * do_sh + lane * 4);
-    float v = bf16lo(a.x) * bf16lo(g.x) + bf16hi(a.x) * bf16hi(g.x) + bf16lo(a.y) * bf16lo(g.y) + bf16hi(a.y) * bf16hi(g.y);
+    float v = 0.f;
+    if (lane * 4 < D) {
+      const uint2 a = *reinterpret_cast<const uint2*>(o + b * o_sb + (int64_t)s * o_ss + (int64_t)h * o_sh + lane * 4);
+      const uint2 g = *reinterpret_cast<const uint2*>(d_o + b * do_sb + (int64_t)s * do_ss + (int64_t)h * do_sh + lane * 4);
+      v = bf16lo(a.x) * bf16lo(g.x) + bf16hi(a.x) * bf16hi(g.x) + bf16lo(a.y) * bf16lo(g.y) + bf16hi(a.y) * bf16hi(g.y);
+    }
     v = warp_sum(v);
     if (lane == 0) delta[r] = v;          // r enumerates (b, h, s)
   }
@@ -604,11 +609,11 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
 
 // dq (bf16, strided) = dq_acc (fp32 [B,S,H,D] contiguous)
 __global__ void __launch_bounds__(256)
-attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int64_t n8, int S, int H, int64_t sb, int64_t ss, int64_t sh) {
+attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int64_t n8, int S, int H, int D, int64_t sb, int64_t ss, int64_t sh) {
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < n8; v += (int64_t)gridDim.x * blockDim.x) {
     const float4 a = ldg_stream(reinterpret_cast<const float4*>(acc) + 2 * v), c = ldg_stream(reinterpret_cast<const float4*>(acc) + 2 * v + 1);
-    const int d8 = (int)(v % 16);
-    int64_t t = v / 16;
+    const int d8 = (int)(v % (D / 8));
+    int64_t t = v / (D / 8);
     const int h = (int)(t % H); t /= H;
     const int s = (int)(t % S);
     const int64_t b = t / S;
@@ -619,15 +624,15 @@ attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict_
 
 }  // namespace
 
-// Backward of detb200_attn_fwd for H_kv == H, S_q == S_kv, D == 128.  All tensors bf16 (B, S, H, D)-addressed with element
+// Backward of detb200_attn_fwd for H_kv == H, S_q == S_kv, D in {64, 128}.  All tensors bf16 (B, S, H, D)-addressed with element
 // strides {batch, seq, head}.  `delta` (fp32 [B,H,S]) and `dq_acc` (fp32 [B,S,H,D]) are caller-provided scratch; dq_acc is
 // zeroed here.  dq/dk/dv may be slices of one packed buffer.
 DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, float* delta,
                                  float* dq_acc, void* dq, void* dk, void* dv, int B, int H, int S, int D, const int64_t* q_st,
                                  const int64_t* k_st, const int64_t* v_st, const int64_t* o_st, const int64_t* do_st, const int64_t* dq_st,
                                  const int64_t* dk_st, const int64_t* dv_st, float scale, int causal, cudaStream_t stream) {
-  if (D != 128) {
-    detb200_set_error("attn_bwd: head dim %d unsupported (128)", D);
+  if (D != 128 && D != 64) {
+    detb200_set_error("attn_bwd: head dim %d unsupported (64 or 128)", D);
     return DETB200_ERR_UNSUPPORTED;
   }
   for (const int64_t* st : {o_st, do_st, dq_st, dk_st, dv_st})
@@ -649,7 +654,7 @@ DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, co
   if ((rc = mk(&tv, v, v_st, kBwdKeys))) return rc;
   const int64_t rows = (int64_t)B * H * S;
   attn_delta_kernel<<<grid_for(rows, 8, 1, kNumSMs * 16), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(o), reinterpret_cast<const __nv_bfloat16*>(d_o),
-                                                                         delta, B, H, S, o_st[0], o_st[1], o_st[2], do_st[0], do_st[1], do_st[2]);
+                                                                         delta, B, H, S, D, o_st[0], o_st[1], o_st[2], do_st[0], do_st[1], do_st[2]);
   DETB200_LAUNCH_CHECK();
   DETB200_CHECK(cudaMemsetAsync(dq_acc, 0, sizeof(float) * (size_t)rows * D, stream));
   AttnBwdArgs a;
@@ -657,12 +662,17 @@ DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, co
   a.B = B; a.H = H; a.S = S;
   a.dk_sb = dk_st[0]; a.dk_ss = dk_st[1]; a.dk_sh = dk_st[2]; a.dv_sb = dv_st[0]; a.dv_ss = dv_st[1]; a.dv_sh = dv_st[2];
   a.scale = scale; a.scale_log2 = scale * 1.4426950408889634f; a.causal = causal;
-  DETB200_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BCfg::kSmemBytes));
   dim3 grid((S + kBwdKeys - 1) / kBwdKeys, B * H);
-  attn_bwd_kernel<<<grid, kBwdThreads, BCfg::kSmemBytes, stream>>>(tq, tk, tv, tdo, a);
+  if (D == 128) {
+    DETB200_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, BCfg<128>::kSmemBytes));
+    attn_bwd_kernel<128><<<grid, kBwdThreads, BCfg<128>::kSmemBytes, stream>>>(tq, tk, tv, tdo, a);
+  } else {
+    DETB200_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, BCfg<64>::kSmemBytes));
+    attn_bwd_kernel<64><<<grid, kBwdThreads, BCfg<64>::kSmemBytes, stream>>>(tq, tk, tv, tdo, a);
+  }
   DETB200_LAUNCH_CHECK();
   const int64_t n8 = rows * D / 8;
-  attn_dq_convert_kernel<<<grid_for(n8, 256, 2, kNumSMs * 8), 256, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), n8, S, H, dq_st[0], dq_st[1], dq_st[2]);
+  attn_dq_convert_kernel<<<grid_for(n8, 256, 2, kNumSMs * 8), 256, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), n8, S, H, D, dq_st[0], dq_st[1], dq_st[2]);
   DETB200_LAUNCH_CHECK();
   return 0;
 }

@@ -42,30 +42,39 @@ rotary_qkv_kernel(__nv_bfloat16* __restrict__ qkv, const float* __restrict__ cos
   }
 }
 
-// grid (ceil(N/64), row_chunks); 8 warps per CTA, lane = 2 columns
+// grid (ceil(N/128), row_chunks); 8 warps per CTA, lane = 4 columns (8-byte loads), 4 rows in flight per warp
 __global__ void __launch_bounds__(256)
 colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int64_t M, int N, int64_t ld) {
-  __shared__ float2 sm[8][32];
+  __shared__ float4 sm[8][32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int col = blockIdx.x * 64 + lane * 2;
+  const int col = blockIdx.x * 128 + lane * 4;
   const int64_t rows_per = (M + gridDim.y - 1) / gridDim.y;
   const int64_t r0 = (int64_t)blockIdx.y * rows_per, r1 = (r0 + rows_per < M) ? r0 + rows_per : M;
-  float2 acc = make_float2(0.f, 0.f);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (col < N) {
-    for (int64_t r = r0 + w; r < r1; r += 8) {
-      const uint32_t u = *reinterpret_cast<const uint32_t*>(x + r * ld + col);
-      acc.x += bf16lo(u);
-      acc.y += bf16hi(u);
+    int64_t r = r0 + w;
+    for (; r + 24 < r1; r += 32) {
+      uint2 u[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) u[k] = *reinterpret_cast<const uint2*>(x + (r + 8 * k) * ld + col);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { acc.x += bf16lo(u[k].x); acc.y += bf16hi(u[k].x); acc.z += bf16lo(u[k].y); acc.w += bf16hi(u[k].y); }
+    }
+    for (; r < r1; r += 8) {
+      const uint2 u = *reinterpret_cast<const uint2*>(x + r * ld + col);
+      acc.x += bf16lo(u.x); acc.y += bf16hi(u.x); acc.z += bf16lo(u.y); acc.w += bf16hi(u.y);
     }
   }
   sm[w][lane] = acc;
   __syncthreads();
   if (w == 0 && col < N) {
-    float2 t = make_float2(0.f, 0.f);
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { t.x += sm[i][lane].x; t.y += sm[i][lane].y; }
+    for (int i = 0; i < 8; ++i) { t.x += sm[i][lane].x; t.y += sm[i][lane].y; t.z += sm[i][lane].z; t.w += sm[i][lane].w; }
     atomicAdd(out + col, t.x);
-    if (col + 1 < N) atomicAdd(out + col + 1, t.y);
+    atomicAdd(out + col + 1, t.y);
+    atomicAdd(out + col + 2, t.z);
+    atomicAdd(out + col + 3, t.w);
   }
 }
 
@@ -114,17 +123,17 @@ DETB200_API int detb200_rotary_qkv(void* qkv, const float* cos_t, const float* s
   return 0;
 }
 
-// out (fp32 [N]) = (accumulate ? out : 0) + column sums of x (bf16 [M, N], row stride ld elements, N even).
+// out (fp32 [N]) = (accumulate ? out : 0) + column sums of x (bf16 [M, N], row stride ld elements, N % 4 == 0).
 DETB200_API int detb200_colsum_bf16(const void* x, float* out, int64_t M, int N, int64_t ld, int accumulate, cudaStream_t stream) {
   if (N <= 0) return 0;
-  if ((N & 1) || (ld & 1)) {
-    detb200_set_error("colsum_bf16: N and ld must be even");
+  if ((N & 3) || (ld & 3) || (reinterpret_cast<uintptr_t>(x) & 7u)) {
+    detb200_set_error("colsum_bf16: N and ld must be multiples of 4 and x 8-byte aligned");
     return DETB200_ERR_UNSUPPORTED;
   }
   if (!accumulate) DETB200_CHECK(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)N, stream));
   if (M <= 0) return 0;
-  const int gx = (N + 63) / 64;
-  int gy = (kNumSMs * 4 + gx - 1) / gx;
+  const int gx = (N + 127) / 128;
+  int gy = (kNumSMs * 6 + gx - 1) / gx;
   if (gy > (M + 63) / 64) gy = (int)((M + 63) / 64);
   if (gy < 1) gy = 1;
   colsum_bf16_kernel<<<dim3(gx, gy), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), out, M, N, ld);

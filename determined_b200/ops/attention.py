@@ -4,7 +4,8 @@
 "bshd"``, the shape a fused QKV projection produces — any strides with D contiguous, so slices of
 a packed QKV tensor are consumed in place) or ``[B, H, S, D]`` (``"bhsd"``).  Grouped-query
 attention is expressed by K/V having fewer heads.  The forward (and its log-sum-exp) is native;
-the backward currently recomputes through PyTorch's fused SDPA (a library call, like cuBLAS).
+the packed-QKV path (`attention_qkvpacked`, used by the GPT models) has a native tcgen05 backward too;
+the generic `flash_attention` backward recomputes through PyTorch's fused SDPA (a library call).
 
 Reference: GPT-NeoX / GPT-2 example attention (``examples/deepspeed/gpt_neox``; Megatron fused
 softmax + bmm), K13 in SURVEY.md.
@@ -122,7 +123,7 @@ class _QKVPackedFn(torch.autograd.Function):
         qkv, o, lse, cos, sin = ctx.saved_tensors
         rot, causal, scale = ctx.cfg
         dqkv = torch.empty_like(qkv)
-        if qkv.is_cuda and qkv.shape[-1] == 128 and _native_bwd_available():
+        if qkv.is_cuda and qkv.shape[-1] in (64, 128) and _native_bwd_available():
             attention_backward_packed(qkv, o, lse, do, dqkv, causal, scale)
         else:
             with torch.enable_grad():

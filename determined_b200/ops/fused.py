@@ -9,7 +9,7 @@ from determined_b200.ops import _lib
 def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
     """fp32 column sums of a bf16 ``[M, N]`` matrix (bias gradients)."""
     M, N = x.shape
-    if not x.is_cuda or x.dtype != torch.bfloat16 or N % 2 or x.stride(1) != 1 or x.stride(0) % 2:
+    if not x.is_cuda or x.dtype != torch.bfloat16 or N % 4 or x.stride(1) != 1 or x.stride(0) % 4 or x.data_ptr() % 8:
         r = x.float().sum(0)
         if out is None:
             return r

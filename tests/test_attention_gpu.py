@@ -76,7 +76,8 @@ def test_attention_large_scores_stay_finite():
 
 
 @pytest.mark.parametrize("causal", [True, False])
-@pytest.mark.parametrize("cfg", [(2, 256, 2, 128, 0), (1, 384, 3, 128, 32), (2, 200, 2, 128, 64), (1, 1024, 4, 128, 0)])
+@pytest.mark.parametrize("cfg", [(2, 256, 2, 128, 0), (1, 384, 3, 128, 32), (2, 200, 2, 128, 64), (1, 1024, 4, 128, 0),
+                                 (2, 256, 3, 64, 0), (1, 333, 2, 64, 16), (1, 1024, 12, 64, 0)])
 def test_attention_qkvpacked_native_backward(cfg, causal):
     """Packed QKV + in-place rotary + tcgen05 forward and backward vs fp32 math on the same inputs."""
     from determined_b200.models import gpt as G

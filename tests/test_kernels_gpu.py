@@ -326,3 +326,18 @@ def test_residual_block_fusion_is_verified_and_matches():
             assert rel < 5e-3, (n, rel)
     finally:
         torch.backends.cudnn.allow_tf32 = tf32
+
+
+def test_fused_glue_kernels():
+    from determined_b200.ops import fused
+
+    torch.manual_seed(6)
+    x = torch.randn(3001, 520, device="cuda").to(torch.bfloat16)
+    torch.testing.assert_close(fused.colsum(x), x.float().sum(0), rtol=1e-3, atol=5e-2)
+    view = torch.randn(777, 1024, device="cuda").to(torch.bfloat16)[:, 128:128 + 260]
+    out = torch.ones(260, device="cuda")
+    fused.colsum(view, out=out, accumulate=True)
+    torch.testing.assert_close(out, 1 + view.float().sum(0), rtol=1e-3, atol=5e-2)
+    a, b, c = (torch.randn(4, 100, 64, device="cuda").to(torch.bfloat16) for _ in range(3))
+    torch.testing.assert_close(fused.add(a, b, c).float(), a.float() + b.float() + c.float(), rtol=1e-2, atol=3e-2)
+    torch.testing.assert_close(fused.add(a, b), a + b)
