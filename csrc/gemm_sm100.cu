@@ -17,6 +17,7 @@
 #include <unordered_map>
 #include <string>
 #include <cstring>
+#include <cstdlib>
 
 using namespace sm100;
 
@@ -60,11 +61,12 @@ struct GemmCtrl {
   unsigned int pad[16];
 };
 
-template <int kBlockN> struct Cfg {
+template <int kBlockN, bool kTwoCta = false> struct Cfg {
+  static constexpr int kBRows = kTwoCta ? kBlockN / 2 : kBlockN;      // rows of B this CTA stages (a CTA pair splits N)
   static constexpr int kABytes = kBlockM * kBlockK * 2;
-  static constexpr int kBBytes = kBlockN * kBlockK * 2;
+  static constexpr int kBBytes = kBRows * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (kBlockN == 256) ? 4 : 6;
+  static constexpr int kStages = (kStageBytes > 32768) ? 4 : 6;
   static constexpr int kTmemCols = 2 * kBlockN;                    // two accumulator stages
   static constexpr int kSmemBytes = kStages * kStageBytes + 4 * 2 * kStageBufBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
@@ -118,11 +120,13 @@ __device__ __forceinline__ void tile_coords(int t, int mt, int nt, int mb_per_sh
 }
 
 // kRS: the epilogue ships bf16 partial tiles to the rank owning the row shard instead of writing C.
-template <int kBlockN, bool kAMN, bool kBMN, bool kRS>
+template <int kBlockN, bool kAMN, bool kBMN, bool kRS, bool kTwoCta = false>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_c,
                                           const CUtensorMap& tmap_aux, const CUtensorMap* tmap_rs, const GemmArgs& args, const int cta,
                                           const int ncta) {
-  using C = Cfg<kBlockN>;
+  using C = Cfg<kBlockN, kTwoCta>;
+  const uint32_t cta_rank = kTwoCta ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t stage_base = smem_base + C::kStages * C::kStageBytes;     // epilogue staging: 4 warps x 2 x 4 KiB
@@ -137,12 +141,14 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_aligned + C::kStages * C::kStageBytes + 4 * 2 * kStageBufBytes + 8 * (2 * C::kStages + 4));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int mt = (args.M + kBlockM - 1) / kBlockM, nt = (args.N + kBlockN - 1) / kBlockN;
+  // a CTA pair walks 256-row tiles; each CTA of the pair owns 128 of the rows
+  constexpr int kTileM = kTwoCta ? 2 * kBlockM : kBlockM;
+  const int mt = (args.M + kTileM - 1) / kTileM, nt = (args.N + kBlockN - 1) / kBlockN;
   const int num_tiles = mt * nt;
   const int kb_count = (args.K + kBlockK - 1) / kBlockK;
   // tiles are walked shard by shard (all column blocks of a row shard before the next shard) so that a fused
   // collective can overlap: the plain GEMM is the one-shard case
-  const int mb_per_shard = (args.rows_per_shard > 0 && args.rows_per_shard < args.M) ? args.rows_per_shard / kBlockM : mt;
+  const int mb_per_shard = (!kTwoCta && args.rows_per_shard > 0 && args.rows_per_shard < args.M) ? args.rows_per_shard / kBlockM : mt;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -157,13 +163,17 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), kEpiThreads);
+      mbar_init(tempty_bar(s), kTwoCta ? 2 * kEpiThreads : kEpiThreads);     // the leader's copy collects both CTAs' epilogues
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, C::kTmemCols);
+  if (warp == 1) {
+    if (kTwoCta) tmem_alloc_2sm(tmem_slot, C::kTmemCols);
+    else tmem_alloc(tmem_slot, C::kTmemCols);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (kTwoCta) cluster_sync();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -175,6 +185,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
       for (int t = cta; t < num_tiles; t += ncta) {
         int m_blk, n_blk;
         tile_coords(t, mt, nt, mb_per_shard, args.m_block_rotation, m_blk, n_blk);
+        if (kTwoCta) m_blk = 2 * m_blk + (int)cta_rank;
         if (args.a_ready != nullptr) {
           // rows of this tile may span two shards; wait for both
           const int s0 = (m_blk * kBlockM) / args.rows_per_shard;
@@ -185,22 +196,26 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
         }
         for (int kb = 0; kb < kb_count; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          mbar_expect_tx(full_bar(stage), C::kStageBytes);
+          // pair mode: both CTAs' loads are credited to the leader's barrier, which expects the bytes of both
+          if (!kTwoCta || leader) mbar_expect_tx(full_bar(stage), C::kStageBytes * (kTwoCta ? 2 : 1));
           const uint32_t sa = smem_base + stage * C::kStageBytes;
           const uint32_t sb = sa + C::kABytes;
+          const int b_row0 = n_blk * kBlockN + (int)cta_rank * C::kBRows;
+          auto load = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1) {
+            if (kTwoCta) tma_load_2d_2sm(dst, tm, full_bar(stage), c0, c1);
+            else tma_load_2d(dst, tm, full_bar(stage), c0, c1);
+          };
           if (!kAMN) {
-            tma_load_2d(sa, &tmap_a, full_bar(stage), kb * kBlockK, m_blk * kBlockM);
+            load(sa, &tmap_a, kb * kBlockK, m_blk * kBlockM);
           } else {
 #pragma unroll
-            for (int j = 0; j < kBlockM / 64; ++j)
-              tma_load_2d(sa + j * (64 * kBlockK * 2), &tmap_a, full_bar(stage), m_blk * kBlockM + j * 64, kb * kBlockK);
+            for (int j = 0; j < kBlockM / 64; ++j) load(sa + j * (64 * kBlockK * 2), &tmap_a, m_blk * kBlockM + j * 64, kb * kBlockK);
           }
           if (!kBMN) {
-            tma_load_2d(sb, &tmap_b, full_bar(stage), kb * kBlockK, n_blk * kBlockN);
+            load(sb, &tmap_b, kb * kBlockK, b_row0);
           } else {
 #pragma unroll
-            for (int j = 0; j < kBlockN / 64; ++j)
-              tma_load_2d(sb + j * (64 * kBlockK * 2), &tmap_b, full_bar(stage), n_blk * kBlockN + j * 64, kb * kBlockK);
+            for (int j = 0; j < C::kBRows / 64; ++j) load(sb + j * (64 * kBlockK * 2), &tmap_b, b_row0 + j * 64, kb * kBlockK);
           }
           if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
         }
@@ -208,8 +223,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
-      constexpr uint32_t idesc = idesc_bf16_f32(kBlockM, kBlockN, kAMN ? 1 : 0, kBMN ? 1 : 0);
+    if (lane == 0 && (!kTwoCta || leader)) {
+      constexpr uint32_t idesc = idesc_bf16_f32(kTileM, kBlockN, kAMN ? 1 : 0, kBMN ? 1 : 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -229,10 +244,16 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
             // MN-major: advance two 8-row k-groups (2 KiB); LBO = one 64-wide MN box (64 k-rows * 128 B).
             const uint64_t da = kAMN ? smem_desc_sw128(sa + k * 2048, 64 * kBlockK * 2, 1024) : smem_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = kBMN ? smem_desc_sw128(sb + k * 2048, 64 * kBlockK * 2, 1024) : smem_desc_sw128(sb + k * 32, 16, 1024);
-            mma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (kTwoCta) mma_f16_ss_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            else mma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          tc_commit(empty_bar(stage));                     // smem slot reusable once these MMAs retire
-          if (kb == kb_count - 1) tc_commit(tfull_bar(acc));  // accumulator complete
+          if (kTwoCta) {
+            tc_commit_2sm(empty_bar(stage), 3);                       // frees the slot in both CTAs
+            if (kb == kb_count - 1) tc_commit_2sm(tfull_bar(acc), 3);  // both epilogues may read their half
+          } else {
+            tc_commit(empty_bar(stage));                     // smem slot reusable once these MMAs retire
+            if (kb == kb_count - 1) tc_commit(tfull_bar(acc));  // accumulator complete
+          }
           if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
@@ -273,6 +294,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
     for (int t = cta; t < num_tiles; t += ncta) {
       int m_blk, n_blk;
       tile_coords(t, mt, nt, mb_per_shard, args.m_block_rotation, m_blk, n_blk);
+      if (kTwoCta) m_blk = 2 * m_blk + (int)cta_rank;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       int gm0 = m_blk * kBlockM + q * 32;                // first row of this warp's box
@@ -297,7 +319,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
         tmem_ld_wait();
         if (c + 64 >= kBlockN || gn + 64 >= args.N) {     // last chunk of the tile: accumulator drained
           tc_fence_before();
-          mbar_arrive(tempty_bar(acc));
+          if (kTwoCta) mbar_arrive_cluster(tempty_bar(acc), 0);
+          else mbar_arrive(tempty_bar(acc));
         }
         float* v = reinterpret_cast<float*>(r);
         if (args.bias != nullptr) {
@@ -381,11 +404,22 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (kTwoCta) cluster_sync();
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C::kTmemCols);
+    if (kTwoCta) tmem_dealloc_2sm(tmem_base, C::kTmemCols);
+    else tmem_dealloc(tmem_base, C::kTmemCols);
   }
+}
+
+// CTA-pair variant: two SMs of a TPC share one 256x256 tile (cta_group::2); each stages half of A's rows and half of B's,
+// which cuts shared-memory traffic per SM by a third and leaves room for six pipeline stages.
+template <bool kAMN, bool kBMN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_aux, const GemmArgs args) {
+  gemm_body<256, kAMN, kBMN, false, true>(tmap_a, tmap_b, tmap_c, tmap_aux, nullptr, args, blockIdx.x >> 1, gridDim.x >> 1);
 }
 
 template <int kBlockN, bool kAMN, bool kBMN>
@@ -579,6 +613,29 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, 
   return 0;
 }
 
+template <bool kAMN, bool kBMN>
+int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& taux, const GemmArgs& a, int sms,
+            cudaStream_t stream) {
+  using C = Cfg<256, true>;
+  auto* kern = gemm2_bf16_kernel<kAMN, kBMN>;
+  DETB200_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+  const int mt2 = (a.M + 2 * kBlockM - 1) / (2 * kBlockM), nt = (a.N + 255) / 256;
+  int pairs = sms / 2;
+  if (mt2 * nt < pairs) pairs = mt2 * nt;
+  kern<<<2 * pairs, kThreads, C::kSmemBytes, stream>>>(ta, tb, tc, taux, a);
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+bool two_cta_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DETB200_GEMM_2CTA");
+    v = (e == nullptr || e[0] != '0') ? 1 : 0;
+  }
+  return v == 1;
+}
+
 }  // namespace
 
 int detb200_make_tmap_2d(CUtensorMap* out, int fp32, const void* base, uint64_t inner, uint64_t outer, uint64_t row_stride_bytes,
@@ -662,12 +719,15 @@ int detb200_gemm_bf16_impl(const void* A, const void* B, void* C, const void* bi
     return DETB200_ERR_BAD_ARG;
   }
   const int bn = (N > 128) ? 256 : 128;
+  // CTA pairs (cta_group::2) for anything with at least one full 256x256 tile; the plain kernel otherwise and for the
+  // shard-ordered (gather-fused) walks
+  const bool two_cta = bn == 256 && M > kBlockM && a_ready == nullptr && m_block_rotation == 0 && max_ctas <= 0 && two_cta_enabled();
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn_major) rc = detb200_make_tmap_2d(&ta, 0, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, kBlockK, kBlockM);
   else rc = detb200_make_tmap_2d(&ta, 0, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 64, kBlockK);
   if (rc) return rc;
-  if (!b_mn_major) rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, kBlockK, bn);
+  if (!b_mn_major) rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, kBlockK, two_cta ? bn / 2 : bn);
   else rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, kBlockK);
   if (rc) return rc;
   // output boxes: 32 rows x 128 bytes (64 bf16 or 32 fp32 columns)
@@ -689,6 +749,12 @@ int detb200_gemm_bf16_impl(const void* A, const void* B, void* C, const void* bi
   DETB200_CHECK(cudaGetDevice(&dev));
   DETB200_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   if (max_ctas > 0 && max_ctas < sms) sms = max_ctas;
+  if (two_cta) {
+    if (!a_mn_major && !b_mn_major) return launch2<false, false>(ta, tb, tc, taux, g, sms, stream);
+    if (!a_mn_major && b_mn_major) return launch2<false, true>(ta, tb, tc, taux, g, sms, stream);
+    if (a_mn_major && !b_mn_major) return launch2<true, false>(ta, tb, tc, taux, g, sms, stream);
+    return launch2<true, true>(ta, tb, tc, taux, g, sms, stream);
+  }
 #define DETB200_GEMM_DISPATCH(BN)                                                                         \
   do {                                                                                                    \
     if (!a_mn_major && !b_mn_major) return launch<BN, false, false>(ta, tb, tc, taux, g, sms, stream);              \
