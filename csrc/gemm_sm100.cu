@@ -43,7 +43,9 @@ struct GemmArgs {
   const unsigned int* a_ready;   // [n_shards] monotonically increasing counters (device memory)
   unsigned int ready_value;
   int rows_per_shard;
-  int m_block_rotation;          // first m-block to work on (own shard first)
+  int m_block_rotation;          // first block (of the sharded dimension) to work on: own shard first
+  int gather_mode;               // which dimension the readiness counters shard: 0 = rows of A (M), 1 = rows of a K-major B (N),
+                                 // 2 = rows of an MN-major B (K: the k-loop is rotated instead of the tile walk)
   // optional fused reduce-scatter: tiles of row shard d are stored (bf16) into rank d's receive slot
   int rs_world, rs_rank;
   unsigned int rs_epoch;
@@ -148,7 +150,14 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
   const int kb_count = (args.K + kBlockK - 1) / kBlockK;
   // tiles are walked shard by shard (all column blocks of a row shard before the next shard) so that a fused
   // collective can overlap: the plain GEMM is the one-shard case
-  const int mb_per_shard = (!kTwoCta && args.rows_per_shard > 0 && args.rows_per_shard < args.M) ? args.rows_per_shard / kBlockM : mt;
+  const bool sharded = !kTwoCta && args.rows_per_shard > 0;
+  const int mb_per_shard = (sharded && args.gather_mode == 0 && args.rows_per_shard < args.M) ? args.rows_per_shard / kBlockM : mt;
+  const int nb_per_shard = (sharded && args.gather_mode == 1 && args.rows_per_shard < args.N) ? args.rows_per_shard / kBlockN : nt;
+  const int kb_per_shard = (sharded && args.gather_mode == 2 && args.rows_per_shard < args.K) ? args.rows_per_shard / kBlockK : kb_count;
+  auto coords = [&](int t, int& m_blk, int& n_blk) {
+    if (sharded && args.gather_mode == 1) tile_coords(t, nt, mt, nb_per_shard, args.m_block_rotation, n_blk, m_blk);   // walk N shard by shard
+    else tile_coords(t, mt, nt, mb_per_shard, args.gather_mode == 0 ? args.m_block_rotation : 0, m_blk, n_blk);
+  };
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -184,17 +193,26 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
       uint32_t phase = 0;
       for (int t = cta; t < num_tiles; t += ncta) {
         int m_blk, n_blk;
-        tile_coords(t, mt, nt, mb_per_shard, args.m_block_rotation, m_blk, n_blk);
+        coords(t, m_blk, n_blk);
         if (kTwoCta) m_blk = 2 * m_blk + (int)cta_rank;
-        if (args.a_ready != nullptr) {
+        if (args.a_ready != nullptr && args.gather_mode != 2) {
           // rows of this tile may span two shards; wait for both
-          const int s0 = (m_blk * kBlockM) / args.rows_per_shard;
-          const int last_row = min(m_blk * kBlockM + kBlockM, args.M) - 1;
-          const int s1 = last_row / args.rows_per_shard;
-          for (int s = s0; s <= s1; ++s) wait_counter_sys(args.a_ready + s, args.ready_value, "a_ready", s);
-          fence_proxy_async();   // generic-proxy writes of the gather -> async-proxy (TMA) reads
+          const int first = args.gather_mode == 0 ? m_blk * kBlockM : n_blk * kBlockN;
+          const int last = (args.gather_mode == 0 ? min(first + kBlockM, args.M) : min(first + kBlockN, args.N)) - 1;
+          for (int s = first / args.rows_per_shard; s <= last / args.rows_per_shard; ++s) wait_counter_sys(args.a_ready + s, args.ready_value, "a_ready", s);
+          fence_proxy_async();   // async-proxy writes of the gather (remote) -> async-proxy (TMA) reads after the acquire
         }
-        for (int kb = 0; kb < kb_count; ++kb) {
+        for (int kb_i = 0; kb_i < kb_count; ++kb_i) {
+          int kb = kb_i;
+          if (args.gather_mode == 2 && args.a_ready != nullptr) {
+            // K-sharded operand: start the reduction at the own shard and take remote k-ranges as they arrive
+            kb = kb_i + args.m_block_rotation;
+            if (kb >= kb_count) kb -= kb_count;
+            if (kb_i == 0 || kb % kb_per_shard == 0) {
+              wait_counter_sys(args.a_ready + kb / kb_per_shard, args.ready_value, "a_ready(k)", kb / kb_per_shard);
+              fence_proxy_async();
+            }
+          }
           mbar_wait(empty_bar(stage), phase ^ 1u);
           // pair mode: both CTAs' loads are credited to the leader's barrier, which expects the bytes of both
           if (!kTwoCta || leader) mbar_expect_tx(full_bar(stage), C::kStageBytes * (kTwoCta ? 2 : 1));
@@ -293,7 +311,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmap_a, const CUten
     uint32_t acc_phase = 0;
     for (int t = cta; t < num_tiles; t += ncta) {
       int m_blk, n_blk;
-      tile_coords(t, mt, nt, mb_per_shard, args.m_block_rotation, m_blk, n_blk);
+      coords(t, m_blk, n_blk);
       if (kTwoCta) m_blk = 2 * m_blk + (int)cta_rank;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
@@ -786,31 +804,47 @@ int sm_count(int* out) {
 }
 }  // namespace
 
-DETB200_API int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl, int rank, int world, const void* B, void* C,
-                                     const void* bias, void* aux, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
-                                     int64_t ldaux, int b_mn_major, int out_fp32, int bias_fp32, int epilogue, unsigned int epoch,
-                                     unsigned int ready_value, int n_push_ctas, cudaStream_t stream) {
-  if (world < 1 || world > 16 || rank < 0 || rank >= world || T % world != 0 || (T / world) % kBlockM != 0) {
-    detb200_set_error("ag_gemm: world %d rank %d T %lld: rows per rank must be a multiple of %d", world, rank, (long long)T, kBlockM);
+// Gather-fused GEMM.  `peer_g[r]` is rank r's copy of the *gathered* operand's buffer (row-sharded: rank r owns rows
+// [r*rows/world, ...)); `other` is the local operand.
+//   gather_b = 0: the gathered operand is A ([T, ld_g], K-major): sequence-parallel activations.   other = B.
+//   gather_b = 1: the gathered operand is B: ZeRO-3 style weight shards.  gathered_mn_major = 0: B is [N, K] sharded over N
+//                 (forward, Y = X W^T); 1: B is stored [K, N] and sharded over its rows = the reduction dimension (dX = dY W):
+//                 the k-loop then starts at the own shard.  other = A ([M, K], K-major).
+DETB200_API int detb200_ag_gemm_bf16_ex(void* const* peer_g, void* const* peer_ctrl, int rank, int world, const void* other, void* C,
+                                        const void* bias, void* aux, int64_t M, int64_t N, int64_t K, int64_t ld_g, int64_t ld_other,
+                                        int64_t ldc, int64_t ldaux, int gather_b, int gathered_mn_major, int other_mn_major, int out_fp32,
+                                        int bias_fp32, int epilogue, unsigned int epoch, unsigned int ready_value, int n_push_ctas,
+                                        cudaStream_t stream) {
+  const int bn = (N > 128) ? 256 : 128;
+  const int mode = !gather_b ? 0 : (gathered_mn_major ? 2 : 1);
+  const int64_t g_rows = mode == 0 ? M : mode == 1 ? N : K;                   // rows of the gathered operand's storage
+  const int64_t g_cols = mode == 2 ? N : K;                                   // its contiguous dimension
+  const int align = mode == 0 ? kBlockM : mode == 1 ? bn : kBlockK;
+  if (world < 1 || world > 16 || rank < 0 || rank >= world || g_rows % world != 0 || (g_rows / world) % align != 0) {
+    detb200_set_error("ag_gemm: world %d rank %d: the gathered operand has %lld rows; rows per rank must be a multiple of %d", world, rank,
+                      (long long)g_rows, align);
     return DETB200_ERR_BAD_ARG;
   }
-  if (epilogue < 0 || epilogue > EPI_RELU) {
-    detb200_set_error("ag_gemm: only forward epilogues are supported");
+  if (epilogue < 0 || epilogue > EPI_RELU || (gather_b && other_mn_major) || (!gather_b && gathered_mn_major)) {
+    detb200_set_error("ag_gemm: unsupported combination (forward epilogues only; the A operand must be K-major)");
     return DETB200_ERR_BAD_ARG;
   }
   const int elem_c = out_fp32 ? 4 : 2;
-  const int bn = (N > 128) ? 256 : 128;
-  const int rows = (int)(T / world);
+  const int rows = (int)(g_rows / world);
+  const void* A = gather_b ? other : peer_g[rank];
+  const void* B = gather_b ? peer_g[rank] : other;
+  const int64_t lda = gather_b ? ld_other : ld_g, ldb = gather_b ? ld_g : ld_other;
+  const int b_mn = gather_b ? gathered_mn_major : other_mn_major;
   CUtensorMap ta, tb, tc, taux;
-  int rc = detb200_make_tmap_2d(&ta, 0, peer_a[rank], (uint64_t)K, (uint64_t)T, (uint64_t)lda * 2, kBlockK, kBlockM);
+  int rc = detb200_make_tmap_2d(&ta, 0, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, kBlockK, kBlockM);
   if (rc) return rc;
-  if (!b_mn_major) rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, kBlockK, bn);
+  if (!b_mn) rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, kBlockK, bn);
   else rc = detb200_make_tmap_2d(&tb, 0, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, kBlockK);
   if (rc) return rc;
-  rc = detb200_make_tmap_2d(&tc, out_fp32, C, (uint64_t)N, (uint64_t)T, (uint64_t)ldc * elem_c, out_fp32 ? 32 : 64, 32);
+  rc = detb200_make_tmap_2d(&tc, out_fp32, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * elem_c, out_fp32 ? 32 : 64, 32);
   if (rc) return rc;
   if (aux != nullptr && epilogue != EPI_NONE) {
-    rc = detb200_make_tmap_2d(&taux, 0, aux, (uint64_t)N, (uint64_t)T, (uint64_t)ldaux * 2, 64, 32);
+    rc = detb200_make_tmap_2d(&taux, 0, aux, (uint64_t)N, (uint64_t)M, (uint64_t)ldaux * 2, 64, 32);
     if (rc) return rc;
   } else {
     taux = tc;
@@ -823,15 +857,16 @@ DETB200_API int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl
   GemmCtrl* me = reinterpret_cast<GemmCtrl*>(peer_ctrl[rank]);
   GemmArgs g;
   std::memset(&g, 0, sizeof(g));
-  g.C = C; g.bias = bias; g.aux = aux; g.M = (int)T; g.N = (int)N; g.K = (int)K; g.ldc = ldc; g.ldaux = ldaux;
+  g.C = C; g.bias = bias; g.aux = aux; g.M = (int)M; g.N = (int)N; g.K = (int)K; g.ldc = ldc; g.ldaux = ldaux;
   g.out_fp32 = out_fp32; g.bias_fp32 = bias_fp32; g.epilogue = epilogue; g.accumulate = 0;
   g.a_ready = world > 1 ? me->a_ready : nullptr; g.ready_value = ready_value; g.rows_per_shard = rows;
-  g.m_block_rotation = rank * (rows / kBlockM);
+  g.gather_mode = mode;
+  g.m_block_rotation = rank * (rows / align);
   AgArgs ag;
   std::memset(&ag, 0, sizeof(ag));
-  for (int r = 0; r < world; ++r) { ag.peer_a[r] = reinterpret_cast<uint8_t*>(peer_a[r]); ag.peer_ctrl[r] = reinterpret_cast<GemmCtrl*>(peer_ctrl[r]); }
-  ag.rank = rank; ag.world = world; ag.rows_per_shard = rows; ag.row_bytes = K * 2; ag.ld_bytes = lda * 2; ag.epoch = epoch;
-  const int mt = (int)((T + kBlockM - 1) / kBlockM), nt = (int)((N + bn - 1) / bn);
+  for (int r = 0; r < world; ++r) { ag.peer_a[r] = reinterpret_cast<uint8_t*>(peer_g[r]); ag.peer_ctrl[r] = reinterpret_cast<GemmCtrl*>(peer_ctrl[r]); }
+  ag.rank = rank; ag.world = world; ag.rows_per_shard = rows; ag.row_bytes = g_cols * 2; ag.ld_bytes = ld_g * 2; ag.epoch = epoch;
+  const int mt = (int)((M + kBlockM - 1) / kBlockM), nt = (int)((N + bn - 1) / bn);
   int n_gemm = sms - n_push_ctas;
   if (mt * nt < n_gemm) n_gemm = mt * nt;
   ag.n_gemm = n_gemm;
@@ -842,11 +877,19 @@ DETB200_API int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl
     DETB200_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));     \
     kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, stream>>>(ta, tb, tc, taux, g, ag);                                  \
   } while (0)
-  if (bn == 256) { if (b_mn_major) DETB200_AG_LAUNCH(256, true); else DETB200_AG_LAUNCH(256, false); }
-  else { if (b_mn_major) DETB200_AG_LAUNCH(128, true); else DETB200_AG_LAUNCH(128, false); }
+  if (bn == 256) { if (b_mn) DETB200_AG_LAUNCH(256, true); else DETB200_AG_LAUNCH(256, false); }
+  else { if (b_mn) DETB200_AG_LAUNCH(128, true); else DETB200_AG_LAUNCH(128, false); }
 #undef DETB200_AG_LAUNCH
   DETB200_LAUNCH_CHECK();
   return 0;
+}
+
+DETB200_API int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl, int rank, int world, const void* B, void* C,
+                                     const void* bias, void* aux, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                     int64_t ldaux, int b_mn_major, int out_fp32, int bias_fp32, int epilogue, unsigned int epoch,
+                                     unsigned int ready_value, int n_push_ctas, cudaStream_t stream) {
+  return detb200_ag_gemm_bf16_ex(peer_a, peer_ctrl, rank, world, B, C, bias, aux, T, N, K, lda, ldb, ldc, ldaux, 0, 0, b_mn_major, out_fp32,
+                                 bias_fp32, epilogue, epoch, ready_value, n_push_ctas, stream);
 }
 
 DETB200_API int detb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_recv, void* const* peer_ctrl, int rank, int world,

@@ -89,6 +89,8 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_gemm_rs_arrivals", i, [i64, i64, i])
     _sig(lib, "detb200_ag_gemm_bf16", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, p, p, p, p, i64, i64, i64, i64, i64, i64, i64,
                                          i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, i, p])
+    _sig(lib, "detb200_ag_gemm_bf16_ex", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, p, p, p, p, i64, i64, i64, i64, i64, i64, i64,
+                                            i, i, i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, i, p])
     _sig(lib, "detb200_gemm_rs_bf16", i, [p, p, POINTER(c_void_p), POINTER(c_void_p), i, i, p, p, i64, i64, i64, i64, i64, i64,
                                          i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, p])
     # attention (csrc/attention.cu)

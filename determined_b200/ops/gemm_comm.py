@@ -23,7 +23,7 @@ import torch
 from determined_b200.ops import _lib, comm, fused
 from determined_b200.ops import gemm as G
 
-PUSH_CTAS = 0          # 0 = pick 2 * world pusher CTAs (measured: 16 hide the gather completely at world 8)
+PUSH_CTAS = 16         # pusher CTAs of the gather-fused kernels (measured best at world 2 and 8; each drives ~40 GB/s of NVLink)
 
 
 class TensorParallelGemm:
@@ -74,13 +74,37 @@ class TensorParallelGemm:
             out = torch.empty((T, N), dtype=out_dtype, device=full.device)
         lib = _lib.load()
         self.epoch += 1
-        npush = (push_ctas or 2 * self.world) if self.world > 1 else 0
+        npush = (push_ctas or 16) if self.world > 1 else 0
         self._ready += npush
         _lib.check(lib.detb200_ag_gemm_bf16(ptrs, self.ctrl_ptrs, self.rank, self.world, weight.data_ptr(), out.data_ptr(), _lib.ptr(bias),
                                             _lib.ptr(aux), T, N, K, full.stride(0), weight.stride(0), out.stride(0),
                                             aux.stride(0) if aux is not None else 0, int(b_mn_major), int(out.dtype == torch.float32),
                                             int(bias is not None and bias.dtype == torch.float32), G.EPILOGUES[epilogue], self.epoch,
                                             self._ready, npush, _lib.stream_ptr()), "ag_gemm_bf16")
+        return out
+
+    def gather_weight_gemm(self, x: torch.Tensor, rows_total: int, cols: int, *, transposed: bool = False, bias: Optional[torch.Tensor] = None,
+                           out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, push_ctas: int = PUSH_CTAS) -> torch.Tensor:
+        """ZeRO-3 style: the *weight* ``W [rows_total, cols]`` is row-sharded over the ranks inside ``gather_buffer(rows_total,
+        cols)`` (this rank's rows already written).  ``transposed=False``: ``x [T, cols] @ W^T -> [T, rows_total]`` (forward; W's
+        shards arrive as column blocks of the output).  ``transposed=True``: ``x [T, rows_total] @ W -> [T, cols]`` (input
+        gradient; W's shards are ranges of the reduction, which starts at the own shard)."""
+        G._check_operand(x, "x")
+        full, _, ptrs = self.gather_buffer(rows_total, cols)
+        T = x.shape[0]
+        N, K = (cols, rows_total) if transposed else (rows_total, cols)
+        if x.shape[1] != K:
+            raise ValueError(f"gather_weight_gemm: x has {x.shape[1]} columns, expected {K}")
+        if out is None:
+            out = torch.empty((T, N), dtype=out_dtype, device=x.device)
+        lib = _lib.load()
+        self.epoch += 1
+        npush = (push_ctas or 16) if self.world > 1 else 0
+        self._ready += npush
+        _lib.check(lib.detb200_ag_gemm_bf16_ex(ptrs, self.ctrl_ptrs, self.rank, self.world, x.data_ptr(), out.data_ptr(), _lib.ptr(bias), None, T, N, K,
+                                               full.stride(0), x.stride(0), out.stride(0), 0, 1, int(transposed), 0, int(out.dtype == torch.float32),
+                                               int(bias is not None and bias.dtype == torch.float32), 0, self.epoch, self._ready, npush,
+                                               _lib.stream_ptr()), "ag_gemm_bf16")
         return out
 
     def gemm_reduce_scatter(self, a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
@@ -165,3 +189,74 @@ def column_parallel_linear(tp: TensorParallelGemm, x_shard: torch.Tensor, weight
 
 def row_parallel_linear(tp: TensorParallelGemm, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
     return _RowParallelFn.apply(tp, x, weight, bias)
+
+
+class _Zero3LinearFn(torch.autograd.Function):
+    """Linear layer whose weight is partitioned by output rows across data-parallel ranks (ZeRO stage 3):
+
+        forward   y  = x W^T       weight shards gathered *inside* the GEMM (they arrive as column blocks of y)
+        backward  dx = dy W        gathered again inside the dgrad GEMM (as ranges of its reduction)
+                  dW_shard = reduce_scatter_r(dy_r^T x_r)   the wgrad GEMM ships partial tiles to the owning rank
+
+    so the full weight never exists outside the transient gather buffer shared by all layers of that shape, and
+    neither collective runs as a separate kernel.  Gradients are averaged over the ranks (DDP convention)."""
+
+    @staticmethod
+    def forward(ctx: Any, tp: TensorParallelGemm, x: torch.Tensor, w_shard: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+        x2 = G._as_bf16_2d(x)
+        rows, K = w_shard.shape
+        N = rows * tp.world
+        _, mine, _ = tp.gather_buffer(N, K)
+        mine.copy_(w_shard)                                    # fp32 master shard -> bf16 slot of the gather buffer
+        y = tp.gather_weight_gemm(x2, N, K, bias=bias)
+        ctx.tp, ctx.shape, ctx.x_shape = tp, (N, K), x.shape
+        ctx.save_for_backward(x2, w_shard)
+        ctx.w_dtype, ctx.b_dtype = w_shard.dtype, bias.dtype if bias is not None else None
+        return y.reshape(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx: Any, dy: torch.Tensor) -> Tuple[Any, ...]:
+        x2, w_shard = ctx.saved_tensors
+        tp = ctx.tp
+        N, K = ctx.shape
+        dy2 = G._as_bf16_2d(dy)
+        _, mine, _ = tp.gather_buffer(N, K)
+        mine.copy_(w_shard)                                    # another layer of the same shape may have used the buffer since
+        dx = tp.gather_weight_gemm(dy2, N, K, transposed=True).reshape(ctx.x_shape)
+        dw = tp.gemm_reduce_scatter(dy2, x2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32)     # rows of dW owned by this rank
+        dw = dw.mul_(1.0 / tp.world).to(ctx.w_dtype)
+        db = None
+        if ctx.b_dtype is not None:
+            db = fused.colsum(dy2)
+            if tp.world > 1:
+                import torch.distributed as dist
+
+                dist.all_reduce(db)
+                db.mul_(1.0 / tp.world)
+            db = db.to(ctx.b_dtype)
+        return None, dx, dw, db
+
+
+def zero3_linear(tp: TensorParallelGemm, x: torch.Tensor, w_shard: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    return _Zero3LinearFn.apply(tp, x, w_shard, bias)
+
+
+class Zero3Linear(torch.nn.Module):
+    """``nn.Linear`` holding only this rank's ``out_features / world`` rows of the weight (fp32 master)."""
+
+    def __init__(self, tp: TensorParallelGemm, in_features: int, out_features: int, bias: bool = True) -> None:
+        super().__init__()
+        if out_features % tp.world or (out_features // tp.world) % 256:
+            raise ValueError("Zero3Linear: out_features / world must be a multiple of 256")
+        self.tp, self.in_features, self.out_features = tp, in_features, out_features
+        self.weight_shard = torch.nn.Parameter(torch.empty(out_features // tp.world, in_features))
+        self.bias = torch.nn.Parameter(torch.zeros(out_features)) if bias else None
+        torch.nn.init.normal_(self.weight_shard, std=0.02)
+
+    @torch.no_grad()
+    def load_full_weight(self, w: torch.Tensor) -> None:
+        rows = self.out_features // self.tp.world
+        self.weight_shard.copy_(w[self.tp.rank * rows:(self.tp.rank + 1) * rows])
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return zero3_linear(self.tp, x, self.weight_shard, self.bias)

@@ -196,6 +196,13 @@ int detb200_ag_gemm_bf16(void* const* peer_a, void* const* peer_ctrl, int rank, 
                          void* aux, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t ldaux,
                          int b_mn_major, int out_fp32, int bias_fp32, int epilogue, unsigned int epoch, unsigned int ready_value,
                          int n_push_ctas, detb200_stream_t stream);
+/* Generalised gather-fused GEMM: gather_b = 0 gathers A (as above); gather_b = 1 gathers B, the ZeRO-3 weight case:
+ * gathered_mn_major = 0 -> B is [N, K] sharded over N (forward), 1 -> B is stored [K, N], sharded over the reduction (dgrad).
+ * `other` is the local operand (A must be K-major). */
+int detb200_ag_gemm_bf16_ex(void* const* peer_g, void* const* peer_ctrl, int rank, int world, const void* other, void* C, const void* bias,
+                            void* aux, int64_t M, int64_t N, int64_t K, int64_t ld_g, int64_t ld_other, int64_t ldc, int64_t ldaux,
+                            int gather_b, int gathered_mn_major, int other_mn_major, int out_fp32, int bias_fp32, int epilogue,
+                            unsigned int epoch, unsigned int ready_value, int n_push_ctas, detb200_stream_t stream);
 int detb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_recv, void* const* peer_ctrl, int rank, int world, void* out,
                          const void* bias, int64_t T, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldo, int a_mn_major,
                          int b_mn_major, int out_fp32, int bias_fp32, unsigned int epoch, unsigned int count_base,

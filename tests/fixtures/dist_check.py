@@ -292,6 +292,47 @@ def check_gpt_tp(rank, world, dev):
     dist.barrier()
 
 
+def check_zero3_linear(rank, world, dev):
+    """ZeRO-3 linear: weight shards gathered inside the fwd and dgrad GEMMs, wgrad reduce-scattered by its epilogue."""
+    from determined_b200.ops import comm, gemm_comm
+
+    group = comm.PeerGroup.from_torch_distributed(dev)
+    tp = gemm_comm.TensorParallelGemm(group)
+    K, N, T = 1024, 512 * world, 768
+    for it in range(3):
+        torch.manual_seed(50 + it)
+        w_full = (torch.randn(N, K, device=dev) * 0.05)
+        bias = torch.randn(N, device=dev)
+        dist.broadcast(w_full, 0)
+        dist.broadcast(bias, 0)
+        lin = gemm_comm.Zero3Linear(tp, K, N).to(dev)
+        lin.load_full_weight(w_full)
+        with torch.no_grad():
+            lin.bias.copy_(bias)
+        torch.manual_seed(1000 * it + rank)                      # every rank has its own data
+        x = torch.randn(T, K, device=dev).to(torch.bfloat16).requires_grad_(True)
+        dy = torch.randn(T, N, device=dev).to(torch.bfloat16)
+        y = lin(x)
+        y.backward(dy)
+        wb = w_full.to(torch.bfloat16).float()
+        want_y = x.detach().float() @ wb.t() + bias
+        torch.testing.assert_close(y.float(), want_y, rtol=2e-2, atol=5e-2)
+        want_dx = dy.float() @ wb
+        rel = float((x.grad.float() - want_dx).norm() / want_dx.norm())
+        assert rel < 2e-2, ("dx", rel)
+        dw_full = dy.float().t() @ x.detach().float()
+        dist.all_reduce(dw_full)
+        dw_full /= world
+        rows = N // world
+        want_dw = dw_full[rank * rows:(rank + 1) * rows]
+        rel = float((lin.weight_shard.grad - want_dw).norm() / want_dw.norm())
+        assert rel < 2e-2, ("dw", rel)
+        db = dy.float().sum(0)
+        dist.all_reduce(db)
+        torch.testing.assert_close(lin.bias.grad, db / world, rtol=2e-2, atol=0.5)
+    dist.barrier()
+
+
 def main():
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(local)
@@ -308,6 +349,8 @@ def main():
         check_gemm_comm(rank, world, dev)
     if which in ("all", "gpt_tp"):
         check_gpt_tp(rank, world, dev)
+    if which in ("all", "zero3"):
+        check_zero3_linear(rank, world, dev)
     dist.barrier()
     if rank == 0:
         print("DIST_CHECK_OK", which, flush=True)
