@@ -512,6 +512,62 @@ def workspace_cmd(args: argparse.Namespace) -> int:
     return 0
 
 
+def rbac_cmd(args: argparse.Namespace) -> int:
+    """``det user-group ...`` / ``det rbac ...`` (reference ``harness/determined/cli/{user_groups,rbac}.py``)."""
+    sess = _session(args)
+
+    def uid(name: str) -> int:
+        for u in sess.get("/api/v1/users").json()["users"]:
+            if u["username"] == name:
+                return int(u["id"])
+        raise SystemExit(f"user {name} not found")
+
+    def gid(name: str) -> int:
+        for g in sess.get("/api/v1/groups").json()["groups"]:
+            if g["group"]["name"] == name:
+                return int(g["group"]["groupId"])
+        raise SystemExit(f"group {name} not found")
+
+    def rid(name: str) -> int:
+        for r in sess.get("/api/v1/roles").json()["roles"]:
+            if r["name"] == name:
+                return int(r["roleId"])
+        raise SystemExit(f"role {name} not found")
+
+    a = args.action
+    if a == "group-create":
+        g = sess.post("/api/v1/groups", json={"name": args.name, "addUsers": [uid(u) for u in args.add_user or []]}).json()["group"]
+        print(f"Created group {g['name']} (id {g['groupId']})")
+    elif a == "group-list":
+        gs = sess.get("/api/v1/groups").json()["groups"]
+        _table([[g["group"]["groupId"], g["group"]["name"], g["numMembers"]] for g in gs], ["ID", "Name", "# Members"], args.json)
+    elif a == "group-describe":
+        g = sess.get(f"/api/v1/groups/{gid(args.name)}").json()["group"]
+        _table([[u["id"], u["username"]] for u in g["users"]], ["User ID", "Username"], args.json)
+    elif a in ("group-add-user", "group-remove-user"):
+        key = "addUsers" if a == "group-add-user" else "removeUsers"
+        sess.put(f"/api/v1/groups/{gid(args.name)}", json={key: [uid(u) for u in args.users]})
+        print("ok")
+    elif a == "group-delete":
+        sess.delete(f"/api/v1/groups/{gid(args.name)}")
+        print(f"Deleted group {args.name}")
+    elif a == "list-roles":
+        _table([[r["roleId"], r["name"]] for r in sess.get("/api/v1/roles").json()["roles"]], ["ID", "Role"], args.json)
+    elif a in ("assign-role", "unassign-role"):
+        ra = {"role": {"roleId": rid(args.role)}, "scopeWorkspaceId": args.workspace_id}
+        body: Dict[str, Any] = {"userRoleAssignments": [], "groupRoleAssignments": []}
+        if args.username:
+            body["userRoleAssignments"].append({"userId": uid(args.username), "roleAssignment": ra})
+        if args.group_name:
+            body["groupRoleAssignments"].append({"groupId": gid(args.group_name), "roleAssignment": ra})
+        sess.post("/api/v1/roles/" + ("add-assignments" if a == "assign-role" else "remove-assignments"), json=body)
+        print("ok")
+    elif a == "list-users-roles":
+        rs = sess.get(f"/api/v1/roles/search/by-user/{uid(args.username)}").json()["roles"]
+        _table([[r["role"]["name"], r["scopeWorkspaceId"], r["groupId"]] for r in rs], ["Role", "Workspace", "Via group"], args.json)
+    return 0
+
+
 def ntsc_cmd(args: argparse.Namespace) -> int:
     """``det cmd|shell|notebook|tensorboard ...`` (reference ``harness/determined/cli/{command,shell,notebook,tensorboard}.py``)."""
     sess = _session(args)
@@ -861,6 +917,34 @@ def make_parser() -> argparse.ArgumentParser:
         a = cp.add_parser("describe")
         a.add_argument("id")
         a.set_defaults(fn=ntsc_cmd, kind=kind, action="describe")
+
+    ug = sub.add_parser("user-group").add_subparsers(dest="sub")
+    for name, act in (("create", "group-create"), ("list", "group-list"), ("describe", "group-describe"), ("add-user", "group-add-user"),
+                      ("remove-user", "group-remove-user"), ("delete", "group-delete")):
+        a = ug.add_parser(name)
+        if act != "group-list":
+            a.add_argument("name")
+        if act == "group-create":
+            a.add_argument("--add-user", action="append")
+        if act in ("group-add-user", "group-remove-user"):
+            a.add_argument("users", nargs="+")
+        outfmt(a)
+        a.set_defaults(fn=rbac_cmd, action=act)
+    rb = sub.add_parser("rbac").add_subparsers(dest="sub")
+    a = rb.add_parser("list-roles")
+    outfmt(a)
+    a.set_defaults(fn=rbac_cmd, action="list-roles")
+    for name in ("assign-role", "unassign-role"):
+        a = rb.add_parser(name)
+        a.add_argument("role")
+        a.add_argument("-u", "--username")
+        a.add_argument("-g", "--group-name")
+        a.add_argument("-w", "--workspace-id", type=int)
+        a.set_defaults(fn=rbac_cmd, action=name)
+    a = rb.add_parser("list-users-roles")
+    a.add_argument("username")
+    outfmt(a)
+    a.set_defaults(fn=rbac_cmd, action="list-users-roles")
 
     dp = sub.add_parser("deploy").add_subparsers(dest="sub")
     lo = dp.add_parser("local")

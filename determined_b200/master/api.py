@@ -237,6 +237,128 @@ def set_password(ctx: Ctx, uid: str) -> Any:
 
 
 # ---------------------------------------------------------------------------------------------
+# groups and role assignments (reference master/internal/usergroup, master/internal/rbac; the OSS edition ships the
+# same API with a fixed role catalogue).  Roles gate nothing beyond admin-only mutations here: single-tenant box.
+# ---------------------------------------------------------------------------------------------
+ROLES = [{"roleId": 1, "name": "ClusterAdmin"}, {"roleId": 2, "name": "WorkspaceAdmin"}, {"roleId": 4, "name": "WorkspaceCreator"},
+         {"roleId": 5, "name": "Viewer"}, {"roleId": 6, "name": "Editor"}, {"roleId": 7, "name": "ModelRegistryViewer"}]
+
+
+def _group_json(ctx: Ctx, row: Any) -> Dict[str, Any]:
+    members = ctx.m.db.all("SELECT u.* FROM users u JOIN group_members g ON g.user_id=u.id WHERE g.group_id=?", (row["id"],))
+    return {"groupId": row["id"], "name": row["name"], "users": [user_json(u) for u in members]}
+
+
+@route("POST", "/api/v1/groups")
+def create_group(ctx: Ctx) -> Any:
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    b = ctx.body or {}
+    try:
+        gid = ctx.m.db.exec("INSERT INTO groups(name) VALUES(?)", (b.get("name"),))
+    except Exception as e:
+        raise HTTPError(409, f"cannot create group: {e}")
+    for uid in b.get("addUsers") or []:
+        ctx.m.db.exec("INSERT OR IGNORE INTO group_members(group_id,user_id) VALUES(?,?)", (gid, int(uid)))
+    return {"group": _group_json(ctx, ctx.m.db.one("SELECT * FROM groups WHERE id=?", (gid,)))}
+
+
+@route("POST", "/api/v1/groups/search")
+@route("GET", "/api/v1/groups")
+def list_groups(ctx: Ctx) -> Any:
+    rows = ctx.m.db.all("SELECT * FROM groups ORDER BY id", ())
+    uid = (ctx.body or {}).get("userId") if isinstance(ctx.body, dict) else None
+    out = [_group_json(ctx, r) for r in rows]
+    if uid:
+        out = [g for g in out if any(u["id"] == int(uid) for u in g["users"])]
+    return {"groups": [{"group": g, "numMembers": len(g["users"])} for g in out]}
+
+
+@route("GET", "/api/v1/groups/{gid}")
+def get_group(ctx: Ctx, gid: str) -> Any:
+    row = ctx.m.db.one("SELECT * FROM groups WHERE id=?", (int(gid),))
+    if row is None:
+        raise HTTPError(404, f"group {gid} not found")
+    return {"group": _group_json(ctx, row)}
+
+
+@route("PUT", "/api/v1/groups/{gid}")
+def update_group(ctx: Ctx, gid: str) -> Any:
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    b = ctx.body or {}
+    if ctx.m.db.one("SELECT id FROM groups WHERE id=?", (int(gid),)) is None:
+        raise HTTPError(404, f"group {gid} not found")
+    if b.get("name"):
+        ctx.m.db.exec("UPDATE groups SET name=? WHERE id=?", (b["name"], int(gid)))
+    for uid in b.get("addUsers") or []:
+        ctx.m.db.exec("INSERT OR IGNORE INTO group_members(group_id,user_id) VALUES(?,?)", (int(gid), int(uid)))
+    for uid in b.get("removeUsers") or []:
+        ctx.m.db.exec("DELETE FROM group_members WHERE group_id=? AND user_id=?", (int(gid), int(uid)))
+    return {"group": _group_json(ctx, ctx.m.db.one("SELECT * FROM groups WHERE id=?", (int(gid),)))}
+
+
+@route("DELETE", "/api/v1/groups/{gid}")
+def delete_group(ctx: Ctx, gid: str) -> Any:
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    ctx.m.db.exec("DELETE FROM group_members WHERE group_id=?", (int(gid),))
+    ctx.m.db.exec("DELETE FROM role_assignments WHERE group_id=?", (int(gid),))
+    ctx.m.db.exec("DELETE FROM groups WHERE id=?", (int(gid),))
+    return {}
+
+
+@route("POST", "/api/v1/roles/search")
+@route("GET", "/api/v1/roles")
+def list_roles(ctx: Ctx) -> Any:
+    return {"roles": ROLES}
+
+
+@route("POST", "/api/v1/roles/add-assignments")
+def assign_roles(ctx: Ctx) -> Any:
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    b = ctx.body or {}
+    names = {r["roleId"]: r["name"] for r in ROLES}
+    for a in b.get("userRoleAssignments") or []:
+        ra = a.get("roleAssignment") or {}
+        ctx.m.db.exec("INSERT INTO role_assignments(role,user_id,group_id,workspace_id) VALUES(?,?,?,?)",
+                      (names.get(int((ra.get("role") or {}).get("roleId", 0)), "Viewer"), int(a["userId"]), None, ra.get("scopeWorkspaceId")))
+    for a in b.get("groupRoleAssignments") or []:
+        ra = a.get("roleAssignment") or {}
+        ctx.m.db.exec("INSERT INTO role_assignments(role,user_id,group_id,workspace_id) VALUES(?,?,?,?)",
+                      (names.get(int((ra.get("role") or {}).get("roleId", 0)), "Viewer"), None, int(a["groupId"]), ra.get("scopeWorkspaceId")))
+    return {}
+
+
+@route("POST", "/api/v1/roles/remove-assignments")
+def remove_roles(ctx: Ctx) -> Any:
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    b = ctx.body or {}
+    names = {r["roleId"]: r["name"] for r in ROLES}
+    for a in b.get("userRoleAssignments") or []:
+        ra = a.get("roleAssignment") or {}
+        ctx.m.db.exec("DELETE FROM role_assignments WHERE role=? AND user_id=? AND workspace_id IS ?",
+                      (names.get(int((ra.get("role") or {}).get("roleId", 0))), int(a["userId"]), ra.get("scopeWorkspaceId")))
+    for a in b.get("groupRoleAssignments") or []:
+        ra = a.get("roleAssignment") or {}
+        ctx.m.db.exec("DELETE FROM role_assignments WHERE role=? AND group_id=? AND workspace_id IS ?",
+                      (names.get(int((ra.get("role") or {}).get("roleId", 0))), int(a["groupId"]), ra.get("scopeWorkspaceId")))
+    return {}
+
+
+@route("GET", "/api/v1/roles/search/by-user/{uid}")
+def roles_of_user(ctx: Ctx, uid: str) -> Any:
+    direct = ctx.m.db.all("SELECT * FROM role_assignments WHERE user_id=?", (int(uid),))
+    via = ctx.m.db.all("SELECT r.* FROM role_assignments r JOIN group_members g ON g.group_id=r.group_id WHERE g.user_id=?", (int(uid),))
+    ids = {r["name"]: r["roleId"] for r in ROLES}
+    def fmt(r: Any) -> Dict[str, Any]:
+        return {"role": {"roleId": ids.get(r["role"]), "name": r["role"]}, "scopeWorkspaceId": r["workspace_id"], "groupId": r["group_id"]}
+    return {"roles": [fmt(r) for r in list(direct) + list(via)]}
+
+
+# ---------------------------------------------------------------------------------------------
 # experiments
 # ---------------------------------------------------------------------------------------------
 @route("POST", "/api/v1/experiments")

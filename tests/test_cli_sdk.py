@@ -156,3 +156,24 @@ def test_local_test_mode_via_cli(tmp_path, monkeypatch):
         sys.path[:] = [p for p in sys.path if p != str(FIX)]
         sys.modules.pop("model_def", None)
     assert rc == 0 and "test succeeded" in out
+
+
+def test_groups_and_role_assignments(cluster):
+    m, tmp = cluster
+    assert run("-u", "admin", "user", "create", "alice")[0] == 0
+    rc, out = run("-u", "admin", "user-group", "create", "research", "--add-user", "alice")
+    assert rc == 0 and "Created group research" in out
+    rc, out = run("user-group", "describe", "research", "--json")
+    assert [r["Username"] for r in json.loads(out)] == ["alice"]
+    assert run("-u", "admin", "rbac", "assign-role", "Editor", "-g", "research", "-w", "1")[0] == 0
+    assert run("-u", "admin", "rbac", "assign-role", "Viewer", "-u", "alice")[0] == 0
+    rc, out = run("rbac", "list-users-roles", "alice", "--json")
+    roles = sorted(r["Role"] for r in json.loads(out))
+    assert roles == ["Editor", "Viewer"]
+    assert run("-u", "admin", "rbac", "unassign-role", "Viewer", "-u", "alice")[0] == 0
+    rc, out = run("rbac", "list-users-roles", "alice", "--json")
+    assert [r["Role"] for r in json.loads(out)] == ["Editor"]
+    assert run("-u", "admin", "user-group", "remove-user", "research", "alice")[0] == 0
+    rc, out = run("user-group", "list", "--json")
+    assert json.loads(out)[0]["# Members"] == 0
+    assert run("-u", "admin", "user-group", "delete", "research")[0] == 0
