@@ -34,5 +34,25 @@ def run() -> None:
     h = torch.randn(64, 1024, device=dev, dtype=torch.bfloat16, requires_grad=True)
     ln = norm.LayerNorm(1024).to(dev)
     ln(h).float().sum().backward()
+    # the transformer path: tcgen05 GEMMs (incl. the CTA-pair kernel and fused MLP epilogues), tcgen05 flash attention
+    # forward + backward on a packed QKV projection with in-place rotary, LayerNorm, fused cross-entropy
+    from determined_b200.models import gpt
+    from determined_b200.ops import _lib
+
+    n0 = _lib.LAUNCHES[0]
+    torch.manual_seed(0)
+    m = gpt.GPT(gpt.GPTConfig(n_layer=2, n_head=2, n_embd=256, block_size=256, vocab_size=1024, rotary_pct=0.25, parallel_residual=True,
+                              tie_embeddings=False)).to(dev)
+    o = torch.optim.AdamW(m.parameters(), lr=3e-3)
+    idx = torch.randint(0, 1024, (4, 257), device=dev)
+    gl = []
+    for _ in range(3):
+        _, l = m(idx[:, :-1], idx[:, 1:])
+        o.zero_grad()
+        l.backward()
+        o.step()
+        gl.append(float(l))
+    assert all(v == v for v in gl) and gl[-1] < gl[0], f"GPT smoke loss did not decrease: {gl}"
     torch.cuda.synchronize()
-    print(f"smoke ok: losses={['%.4f' % l for l in losses]}")
+    print(f"smoke ok: resnet losses={['%.4f' % l for l in losses]} gpt losses={['%.4f' % l for l in gl]} "
+          f"native kernel launches in the GPT part: {_lib.LAUNCHES[0] - n0}")
