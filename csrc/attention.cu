@@ -5,7 +5,8 @@
 //   warp 1      MMA issuer     QK(j+1) is issued as soon as the softmax has *read* S(j), so it overlaps the
 //                              exponentials; PV(j) follows when P(j) has been written to TMEM
 //   warps 2..5  softmax        one thread per query row: tcgen05.ld S -> running max / sum (lazy rescale of O
-//                              only when the max moved by > 2^8) -> P as packed bf16 -> tcgen05.st
+//                              only when the max moved by > 2^8) -> P as packed bf16 -> tcgen05.st into one of two P
+//                              buffers, so P(j) is produced while PV(j-1) is still running
 //
 // Two CTAs are resident per SM (96 KiB smem, 256 TMEM columns each) so one CTA's softmax overlaps the other's
 // MMAs.  Layout-agnostic: Q/K/V/O are addressed as (batch, seq, head, dim) with arbitrary strides (dim contiguous),
@@ -55,8 +56,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   auto kv_full = [&](int s) { return bar_base + 8u * (1 + s); };
   auto kv_empty = [&](int s) { return bar_base + 8u * (1 + kStagesKV + s); };
   const uint32_t s_full = bar_base + 8u * (1 + 2 * kStagesKV);
-  const uint32_t s_empty = s_full + 8u, p_full = s_full + 16u, o_done = s_full + 24u;
-  const uint32_t tmem_slot = s_full + 32u;
+  const uint32_t s_empty = s_full + 8u, p_full = s_full + 16u, o_done = s_full + 24u;   // o_done: two barriers, PV(j) commits to [j & 1]
+  const uint32_t tmem_slot = s_full + 40u;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -85,6 +86,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     mbar_init(s_empty, 128);
     mbar_init(p_full, 128);
     mbar_init(o_done, 1);
+    mbar_init(o_done + 8u, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::kTmemCols);
@@ -143,10 +145,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         for (int k = 0; k < kBN / 16; ++k) {
           // V block is [keys, D] with D contiguous: MN-major B; 64-wide d groups are kBN*128 B apart
           const uint64_t dv = smem_desc_sw128(sV + k * 2048, kBN * 128, 1024);
-          mma_f16_ts(tO, tP + k * 8, dv, idesc_pv, (j | k) != 0 ? 1u : 0u);
+          mma_f16_ts(tO, tP + (j & 1) * (kBN / 2) + k * 8, dv, idesc_pv, (j | k) != 0 ? 1u : 0u);
         }
         tc_commit(kv_empty(j % kStagesKV));
-        tc_commit(o_done);
+        tc_commit(o_done + 8u * (j & 1));
       }
     }
   } else {
@@ -155,6 +157,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     const int qi = q0 + row;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     float m_used = -INFINITY, l = 0.f;
+    // PV(i) commits to o_done[i & 1]; each of the two barriers is consumed strictly in order, and neither can run two
+    // phases ahead of a thread (PV(i+2) needs this thread's P(i+2), written only after PV(i) was observed), so the
+    // parity test is never ambiguous.
+    int o_seen0 = 0, o_seen1 = 0;
+    auto wait_pv = [&](int n) {                       // all of PV(0..n-1) have retired
+      while (o_seen0 < (n + 1) / 2) { mbar_wait(o_done, o_seen0 & 1); ++o_seen0; }
+      while (o_seen1 < n / 2) { mbar_wait(o_done + 8u, o_seen1 & 1); ++o_seen1; }
+      tc_fence_after();
+    };
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
@@ -178,10 +189,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const float m_new = fmaxf(m_used, mx * args.scale_log2);
       const bool need = m_new > m_used + kRescaleThreshold;       // also true for the first finite block
       const bool any = __any_sync(0xffffffffu, need);
-      if (j > 0) {
-        mbar_wait(o_done, (j - 1) & 1);                           // PV(j-1) retired: P reusable, O stable
-        tc_fence_after();
-      }
+      // P is double-buffered: P(j) may be written while PV(j-1) still runs; only PV(j-2), the previous user of this
+      // buffer, must have retired.  Rescaling O additionally needs PV(j-1) to be done with it.
+      wait_pv(any ? j : j - 1);
       if (any) {
         const float alpha = need ? exp2f(m_used - m_new) : 1.f;   // exp2(-inf) = 0 on the first block
         if (need) { m_used = m_new; l *= alpha; }
@@ -207,13 +217,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         pk[c >> 1] = pack_bf16(p0, p1);
       }
       l += sum;
-      tmem_st_32x32(tP + lane_off, pk);
+      tmem_st_32x32(tP + (j & 1) * (kBN / 2) + lane_off, pk);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_full);
     }
-    mbar_wait(o_done, (n_kv - 1) & 1);
-    tc_fence_after();
+    wait_pv(n_kv);
     const float inv_l = l > 0.f ? 1.f / l : 0.f;
     const bool row_ok = qi < args.S_q;
     __nv_bfloat16* op = args.O + (int64_t)b * args.o_sb + (int64_t)qi * args.o_ss + (int64_t)h * args.o_sh;
