@@ -13,6 +13,7 @@
 // which covers [B,H,S,D], [B,S,H,D] and packed QKV.  GQA via h_kv = h / (H / H_kv).
 // Replaces: the attention of the GPT-2 / GPT-NeoX examples (K13; Megatron softmax+bmm or flash-attn there).
 #include "sm100.cuh"
+#include <cstdlib>
 
 using namespace sm100;
 
@@ -31,6 +32,7 @@ struct AttnArgs {
   int64_t o_sb, o_ss, o_sh;        // element strides of O
   float scale_log2;                // softmax scale * log2(e)
   int causal;
+  long long* prof;                 // debug (DETB200_ATTN_PROF=1): cycle stamps of CTA (0,0)'s first softmax warp
 };
 
 template <int D> struct ACfg {
@@ -166,9 +168,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       while (o_seen1 < n / 2) { mbar_wait(o_done + 8u, o_seen1 & 1); ++o_seen1; }
       tc_fence_after();
     };
+    const bool prof = args.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
     for (int j = 0; j < n_kv; ++j) {
+      if (prof && j < 16) args.prof[j * 4 + 0] = clock64();
       mbar_wait(s_full, j & 1);
       tc_fence_after();
+      if (prof && j < 16) args.prof[j * 4 + 1] = clock64();
       uint32_t r[64];
       tmem_ld_32x32(tS + lane_off, r);
       tmem_ld_32x32(tS + lane_off + 32, r + 32);
@@ -191,6 +196,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const bool any = __any_sync(0xffffffffu, need);
       // P is double-buffered: P(j) may be written while PV(j-1) still runs; only PV(j-2), the previous user of this
       // buffer, must have retired.  Rescaling O additionally needs PV(j-1) to be done with it.
+      if (prof && j < 16) args.prof[j * 4 + 2] = clock64();
       wait_pv(any ? j : j - 1);
       if (any) {
         const float alpha = need ? exp2f(m_used - m_new) : 1.f;   // exp2(-inf) = 0 on the first block
@@ -221,6 +227,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_full);
+      if (prof && j < 16) args.prof[j * 4 + 3] = clock64();
     }
     wait_pv(n_kv);
     const float inv_l = l > 0.f ? 1.f / l : 0.f;
@@ -300,6 +307,22 @@ DETB200_API int detb200_attn_fwd(const void* q, const void* k, const void* v, vo
   a.O = reinterpret_cast<__nv_bfloat16*>(o); a.lse = lse; a.B = B; a.H = H; a.H_kv = H_kv; a.S_q = S_q; a.S_kv = S_kv;
   a.o_sb = o_strides[0]; a.o_ss = o_strides[1]; a.o_sh = o_strides[2];
   a.scale_log2 = scale * 1.4426950408889634f; a.causal = causal;
+  a.prof = nullptr;
+  static const bool want_prof = getenv("DETB200_ATTN_PROF") != nullptr;
+  if (want_prof) {
+    static long long* dbuf = nullptr;
+    if (dbuf == nullptr) DETB200_CHECK(cudaMalloc(&dbuf, 64 * sizeof(long long)));
+    DETB200_CHECK(cudaMemsetAsync(dbuf, 0, 64 * sizeof(long long), stream));
+    a.prof = dbuf;
+    rc = D == 128 ? launch_fwd<128>(tq, tk, tv, a, stream) : launch_fwd<64>(tq, tk, tv, a, stream);
+    long long h[64];
+    DETB200_CHECK(cudaMemcpyAsync(h, dbuf, sizeof(h), cudaMemcpyDeviceToHost, stream));
+    DETB200_CHECK(cudaStreamSynchronize(stream));
+    for (int j = 0; j < 16 && h[j * 4 + 3] != 0; ++j)
+      fprintf(stderr, "attn_prof j=%d wait_s=%lld ld+max=%lld wait_pv+exp+st=%lld loop=%lld\n", j, h[j * 4 + 1] - h[j * 4], h[j * 4 + 2] - h[j * 4 + 1],
+              h[j * 4 + 3] - h[j * 4 + 2], j ? h[j * 4] - h[(j - 1) * 4] : 0);
+    return rc;
+  }
   return D == 128 ? launch_fwd<128>(tq, tk, tv, a, stream) : launch_fwd<64>(tq, tk, tv, a, stream);
 }
 
