@@ -35,11 +35,24 @@ struct AttnArgs {
   long long* prof;                 // debug (DETB200_ATTN_PROF=1): cycle stamps of CTA (0,0)'s first softmax warp
 };
 
+// 2^x on the FMA / integer pipes (no MUFU): round-to-nearest split x = n + f with the 1.5*2^23 trick, cubic for 2^f on
+// [-0.5, 0.5] (relative error 6e-4, below bf16 resolution), n added straight into the exponent field.
+__device__ __forceinline__ float exp2_fma(float x) {
+  x = fmaxf(x, -125.f);
+  const float t = x + 12582912.f;
+  const float f = x - (t - 12582912.f);
+  float p = fmaf(f, 0.0555041087f, 0.2402265070f);
+  p = fmaf(p, f, 0.6931471806f);
+  p = fmaf(p, f, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+constexpr int kPolyOf4 = 0;      // of every 4 exponentials, this many take the FMA path (MUFU.EX2 is 16/clk/SM on B200)
+
 template <int D> struct ACfg {
   static constexpr int kQBytes = kBM * D * 2;
   static constexpr int kKVBytes = kBN * D * 2;           // one of K or V
   static constexpr int kStageBytes = 2 * kKVBytes;
-  static constexpr int kSmemBytes = kQBytes + kStagesKV * kStageBytes + 1024 + 128;
+  static constexpr int kSmemBytes = kQBytes + kStagesKV * kStageBytes + 1024 + 256;
   static constexpr int kColS = 0, kColP = kBN, kColO = 128;
   static constexpr int kTmemCols = 256;
 };
@@ -55,9 +68,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   const uint32_t sKV = smem_base + C::kQBytes;
   const uint32_t bar_base = sKV + kStagesKV * C::kStageBytes;
   const uint32_t q_full = bar_base;
-  auto kv_full = [&](int s) { return bar_base + 8u * (1 + s); };
-  auto kv_empty = [&](int s) { return bar_base + 8u * (1 + kStagesKV + s); };
-  const uint32_t s_full = bar_base + 8u * (1 + 2 * kStagesKV);
+  // K and V have their own full/empty barriers: a K slot is free as soon as its QK MMA retired (one block earlier than
+  // the V slot), so K(j+2) is in flight while block j is still in the softmax
+  auto k_full = [&](int s) { return bar_base + 8u * (1 + s); };
+  auto k_empty = [&](int s) { return bar_base + 8u * (1 + kStagesKV + s); };
+  auto v_full = [&](int s) { return bar_base + 8u * (1 + 2 * kStagesKV + s); };
+  auto v_empty = [&](int s) { return bar_base + 8u * (1 + 3 * kStagesKV + s); };
+  const uint32_t s_full = bar_base + 8u * (1 + 4 * kStagesKV);
   const uint32_t s_empty = s_full + 8u, p_full = s_full + 16u, o_done = s_full + 24u;   // o_done: two barriers, PV(j) commits to [j & 1]
   const uint32_t tmem_slot = s_full + 40u;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
@@ -83,7 +100,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
-    for (int s = 0; s < kStagesKV; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 1); }
+    for (int s = 0; s < kStagesKV; ++s) { mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1); }
     mbar_init(s_full, 1);
     mbar_init(s_empty, 128);
     mbar_init(p_full, 128);
@@ -103,16 +120,27 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       mbar_expect_tx(q_full, C::kQBytes);
 #pragma unroll
       for (int hh = 0; hh < D / 64; ++hh) tma_load_4d(sQ + hh * (kBM * 128), &tmap_q, q_full, hh * 64, h, q0, b);
-      for (int j = 0; j < n_kv; ++j) {
+      auto load_k = [&](int j) {
         const int st = j % kStagesKV;
-        mbar_wait(kv_empty(st), ((j / kStagesKV) & 1) ^ 1u);
-        mbar_expect_tx(kv_full(st), C::kStageBytes);
-        const uint32_t sK = sKV + st * C::kStageBytes, sV = sK + C::kKVBytes;
+        mbar_wait(k_empty(st), ((j / kStagesKV) & 1) ^ 1u);
+        mbar_expect_tx(k_full(st), C::kKVBytes);
+        const uint32_t sK = sKV + st * C::kStageBytes;
 #pragma unroll
-        for (int hh = 0; hh < D / 64; ++hh) {
-          tma_load_4d(sK + hh * (kBN * 128), &tmap_k, kv_full(st), hh * 64, h_kv, j * kBN, b);
-          tma_load_4d(sV + hh * (kBN * 128), &tmap_v, kv_full(st), hh * 64, h_kv, j * kBN, b);
-        }
+        for (int hh = 0; hh < D / 64; ++hh) tma_load_4d(sK + hh * (kBN * 128), &tmap_k, k_full(st), hh * 64, h_kv, j * kBN, b);
+      };
+      auto load_v = [&](int j) {
+        const int st = j % kStagesKV;
+        mbar_wait(v_empty(st), ((j / kStagesKV) & 1) ^ 1u);
+        mbar_expect_tx(v_full(st), C::kKVBytes);
+        const uint32_t sV = sKV + st * C::kStageBytes + C::kKVBytes;
+#pragma unroll
+        for (int hh = 0; hh < D / 64; ++hh) tma_load_4d(sV + hh * (kBN * 128), &tmap_v, v_full(st), hh * 64, h_kv, j * kBN, b);
+      };
+      // K runs one block ahead of V: K(j+1) only waits for QK(j-1), V(j) for PV(j-2); neither wait blocks the other
+      load_k(0);
+      for (int j = 0; j < n_kv; ++j) {
+        if (j + 1 < n_kv) load_k(j + 1);
+        load_v(j);
       }
     }
   } else if (warp == 1) {
@@ -130,16 +158,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         tc_commit(s_full);
       };
       mbar_wait(q_full, 0);
-      mbar_wait(kv_full(0), 0);
+      mbar_wait(k_full(0), 0);
       tc_fence_after();
       issue_qk(0);
+      tc_commit(k_empty(0));
       for (int j = 0; j < n_kv; ++j) {
         if (j + 1 < n_kv) {
-          mbar_wait(kv_full((j + 1) % kStagesKV), ((j + 1) / kStagesKV) & 1);
+          mbar_wait(k_full((j + 1) % kStagesKV), ((j + 1) / kStagesKV) & 1);
           mbar_wait(s_empty, j & 1);                  // softmax(j) holds S(j) in registers
           tc_fence_after();
           issue_qk(j + 1);
+          tc_commit(k_empty((j + 1) % kStagesKV));
         }
+        mbar_wait(v_full(j % kStagesKV), (j / kStagesKV) & 1);
         mbar_wait(p_full, j & 1);
         tc_fence_after();
         const uint32_t sV = sKV + (j % kStagesKV) * C::kStageBytes + C::kKVBytes;
@@ -149,7 +180,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           const uint64_t dv = smem_desc_sw128(sV + k * 2048, kBN * 128, 1024);
           mma_f16_ts(tO, tP + (j & 1) * (kBN / 2) + k * 8, dv, idesc_pv, (j | k) != 0 ? 1u : 0u);
         }
-        tc_commit(kv_empty(j % kStagesKV));
+        tc_commit(v_empty(j % kStagesKV));
         tc_commit(o_done + 8u * (j & 1));
       }
     }
@@ -159,21 +190,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     const int qi = q0 + row;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     float m_used = -INFINITY, l = 0.f;
-    // PV(i) commits to o_done[i & 1]; each of the two barriers is consumed strictly in order, and neither can run two
-    // phases ahead of a thread (PV(i+2) needs this thread's P(i+2), written only after PV(i) was observed), so the
-    // parity test is never ambiguous.
-    int o_seen0 = 0, o_seen1 = 0;
-    auto wait_pv = [&](int n) {                       // all of PV(0..n-1) have retired
-      while (o_seen0 < (n + 1) / 2) { mbar_wait(o_done, o_seen0 & 1); ++o_seen0; }
-      while (o_seen1 < n / 2) { mbar_wait(o_done + 8u, o_seen1 & 1); ++o_seen1; }
+    // PV(i) commits to o_done[i & 1].  A tcgen05.commit covers every MMA issued before it, and QK(j) is issued after
+    // PV(j-2): once S(j) has been observed, PV(j-2) has retired and the P buffer (j & 1) is free without any further wait.
+    // Only a rescale of O needs PV(j-1); its barrier cannot be more than one phase ahead (PV(j+1) needs this thread's
+    // P(j+1)), so a direct parity wait is unambiguous.
+    auto wait_pv_done = [&](int i) {
+      mbar_wait(o_done + 8u * (i & 1), (i >> 1) & 1);
       tc_fence_after();
     };
     const bool prof = args.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
     for (int j = 0; j < n_kv; ++j) {
-      if (prof && j < 16) args.prof[j * 4 + 0] = clock64();
+      if (prof && j < 8) args.prof[j * 8 + 0] = clock64();
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      if (prof && j < 16) args.prof[j * 4 + 1] = clock64();
+      if (prof && j < 8) args.prof[j * 8 + 1] = clock64();
       uint32_t r[64];
       tmem_ld_32x32(tS + lane_off, r);
       tmem_ld_32x32(tS + lane_off + 32, r + 32);
@@ -196,8 +226,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const bool any = __any_sync(0xffffffffu, need);
       // P is double-buffered: P(j) may be written while PV(j-1) still runs; only PV(j-2), the previous user of this
       // buffer, must have retired.  Rescaling O additionally needs PV(j-1) to be done with it.
-      if (prof && j < 16) args.prof[j * 4 + 2] = clock64();
-      wait_pv(any ? j : j - 1);
+      if (prof && j < 8) args.prof[j * 8 + 2] = clock64();
+      if (any && j > 0) wait_pv_done(j - 1);
+      if (prof && j < 8) args.prof[j * 8 + 4] = clock64();
       if (any) {
         const float alpha = need ? exp2f(m_used - m_new) : 1.f;   // exp2(-inf) = 0 on the first block
         if (need) { m_used = m_new; l *= alpha; }
@@ -218,18 +249,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const float mm = (m_used == -INFINITY) ? 0.f : m_used;       // fully masked row so far: p = exp2(-inf) = 0
 #pragma unroll
       for (int c = 0; c < 64; c += 2) {
-        const float p0 = exp2f(s[c] * args.scale_log2 - mm), p1 = exp2f(s[c + 1] * args.scale_log2 - mm);
+        const float x0 = s[c] * args.scale_log2 - mm, x1 = s[c + 1] * args.scale_log2 - mm;
+        const float p0 = ((c & 3) < kPolyOf4) ? exp2_fma(x0) : exp2f(x0);
+        const float p1 = (((c + 1) & 3) < kPolyOf4) ? exp2_fma(x1) : exp2f(x1);
         sum += p0 + p1;
         pk[c >> 1] = pack_bf16(p0, p1);
       }
       l += sum;
+      if (prof && j < 8) args.prof[j * 8 + 5] = clock64() + (long long)(sum == 12345.f);
       tmem_st_32x32(tP + (j & 1) * (kBN / 2) + lane_off, pk);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_full);
-      if (prof && j < 16) args.prof[j * 4 + 3] = clock64();
+      if (prof && j < 8) args.prof[j * 8 + 3] = clock64();
     }
-    wait_pv(n_kv);
+    wait_pv_done(n_kv - 1);
     const float inv_l = l > 0.f ? 1.f / l : 0.f;
     const bool row_ok = qi < args.S_q;
     __nv_bfloat16* op = args.O + (int64_t)b * args.o_sb + (int64_t)qi * args.o_ss + (int64_t)h * args.o_sh;
@@ -318,9 +352,10 @@ DETB200_API int detb200_attn_fwd(const void* q, const void* k, const void* v, vo
     long long h[64];
     DETB200_CHECK(cudaMemcpyAsync(h, dbuf, sizeof(h), cudaMemcpyDeviceToHost, stream));
     DETB200_CHECK(cudaStreamSynchronize(stream));
-    for (int j = 0; j < 16 && h[j * 4 + 3] != 0; ++j)
-      fprintf(stderr, "attn_prof j=%d wait_s=%lld ld+max=%lld wait_pv+exp+st=%lld loop=%lld\n", j, h[j * 4 + 1] - h[j * 4], h[j * 4 + 2] - h[j * 4 + 1],
-              h[j * 4 + 3] - h[j * 4 + 2], j ? h[j * 4] - h[(j - 1) * 4] : 0);
+    for (int j = 0; j < 8 && h[j * 8 + 3] != 0; ++j)
+      fprintf(stderr, "attn_prof j=%d wait_s=%lld ld+max=%lld wait_pv=%lld rescale+exp=%lld st+arrive=%lld loop=%lld\n", j, h[j * 8 + 1] - h[j * 8],
+              h[j * 8 + 2] - h[j * 8 + 1], h[j * 8 + 4] - h[j * 8 + 2], h[j * 8 + 5] - h[j * 8 + 4], h[j * 8 + 3] - h[j * 8 + 5],
+              j ? h[j * 8] - h[(j - 1) * 8] : 0);
     return rc;
   }
   return D == 128 ? launch_fwd<128>(tq, tk, tv, a, stream) : launch_fwd<64>(tq, tk, tv, a, stream);
