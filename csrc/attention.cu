@@ -46,7 +46,6 @@ __device__ __forceinline__ float exp2_fma(float x) {
   p = fmaf(p, f, 1.0f);
   return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
-constexpr int kPolyOf4 = 0;      // of every 4 exponentials, this many take the FMA path (MUFU.EX2 is 16/clk/SM on B200)
 
 template <int D> struct ACfg {
   static constexpr int kQBytes = kBM * D * 2;
@@ -57,7 +56,8 @@ template <int D> struct ACfg {
   static constexpr int kTmemCols = 256;
 };
 
-template <int D>
+// kPolyOf4: of every 4 exponentials, this many take the FMA path (MUFU.EX2 is 16/clk/SM on B200)
+template <int D, int kPolyOf4>
 __global__ void __launch_bounds__(kAThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                 const __grid_constant__ CUtensorMap tmap_v, const AttnArgs args) {
@@ -296,15 +296,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   }
 }
 
-template <int D>
-int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnArgs& a, cudaStream_t stream) {
+template <int D, int kPoly>
+int launch_fwd_p(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnArgs& a, cudaStream_t stream) {
   using C = ACfg<D>;
-  auto* kern = attn_fwd_kernel<D>;
+  auto* kern = attn_fwd_kernel<D, kPoly>;
   DETB200_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
   dim3 grid((a.S_q + kBM - 1) / kBM, a.B * a.H);
   kern<<<grid, kAThreads, C::kSmemBytes, stream>>>(tq, tk, tv, a);
   DETB200_LAUNCH_CHECK();
   return 0;
+}
+
+template <int D>
+int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnArgs& a, cudaStream_t stream) {
+  static const int poly = [] { const char* e = getenv("DETB200_ATTN_POLY"); return e ? atoi(e) : 0; }();
+  if (poly == 1) return launch_fwd_p<D, 1>(tq, tk, tv, a, stream);
+  if (poly == 2) return launch_fwd_p<D, 2>(tq, tk, tv, a, stream);
+  return launch_fwd_p<D, 0>(tq, tk, tv, a, stream);
 }
 
 }  // namespace
