@@ -147,12 +147,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     if (lane == 0) {
       constexpr uint32_t idesc_qk = idesc_bf16_f32(kBM, kBN, 0, 0);
       constexpr uint32_t idesc_pv = idesc_bf16_f32(kBM, D, 0, 1);
+      const uint64_t dq_base = smem_desc_sw128(sQ, 16, 1024);
+      const uint64_t dk_base0 = smem_desc_sw128(sKV, 16, 1024);
+      const uint64_t dv_base0 = smem_desc_sw128(sKV + C::kKVBytes, kBN * 128, 1024);      // MN-major: LBO = one 64-wide d group
       auto issue_qk = [&](int j) {
-        const uint32_t sK = sKV + (j % kStagesKV) * C::kStageBytes;
+        // descriptors differ from their base only by a compile-time constant in the (16-byte granular) address field: one
+        // add per MMA keeps the single issuing thread far ahead of the tensor pipe
+        const uint64_t db0 = dk_base0 + (uint64_t)((j % kStagesKV) * (C::kStageBytes >> 4));
 #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
-          const uint64_t da = smem_desc_sw128(sQ + (k / 4) * (kBM * 128) + (k % 4) * 32, 16, 1024);
-          const uint64_t db = smem_desc_sw128(sK + (k / 4) * (kBN * 128) + (k % 4) * 32, 16, 1024);
+          const uint64_t da = dq_base + (uint64_t)(((k / 4) * (kBM * 128) + (k % 4) * 32) >> 4);
+          const uint64_t db = db0 + (uint64_t)(((k / 4) * (kBN * 128) + (k % 4) * 32) >> 4);
           mma_f16_ss(tS, da, db, idesc_qk, k != 0 ? 1u : 0u);
         }
         tc_commit(s_full);
@@ -173,11 +178,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         mbar_wait(v_full(j % kStagesKV), (j / kStagesKV) & 1);
         mbar_wait(p_full, j & 1);
         tc_fence_after();
-        const uint32_t sV = sKV + (j % kStagesKV) * C::kStageBytes + C::kKVBytes;
+        const uint64_t dv0 = dv_base0 + (uint64_t)((j % kStagesKV) * (C::kStageBytes >> 4));
 #pragma unroll
         for (int k = 0; k < kBN / 16; ++k) {
           // V block is [keys, D] with D contiguous: MN-major B; 64-wide d groups are kBN*128 B apart
-          const uint64_t dv = smem_desc_sw128(sV + k * 2048, kBN * 128, 1024);
+          const uint64_t dv = dv0 + (uint64_t)((k * 2048) >> 4);
           mma_f16_ts(tO, tP + (j & 1) * (kBN / 2) + k * 8, dv, idesc_pv, (j | k) != 0 ? 1u : 0u);
         }
         tc_commit(v_empty(j % kStagesKV));
@@ -387,6 +392,7 @@ constexpr int kBwdKeys = 128;
 constexpr int kBwdQ = 64;
 constexpr int kBwdThreads = 320;            // warp 0 TMA, warp 1 MMA, warps 2..9 compute
 constexpr int kBwdCompute = 256;
+constexpr int kBwdQStages = 3;              // (Q_i, dO_i) ring: a slot is refilled only after dQ(i) retired, so two slots expose the load latency
 
 struct AttnBwdArgs {
   const float* lse;       // [B, H, S]
@@ -398,6 +404,7 @@ struct AttnBwdArgs {
   int64_t dk_sb, dk_ss, dk_sh, dv_sb, dv_ss, dv_sh;
   float scale, scale_log2;
   int causal;
+  long long* prof;        // debug (DETB200_ATTN_PROF=1): cycle stamps of CTA (0,0)'s first compute warp
 };
 
 template <int kD> struct BCfg {
@@ -405,29 +412,34 @@ template <int kD> struct BCfg {
   static constexpr int kKBytes = kBwdKeys * D * 2;          // 32 KiB (K or V)
   static constexpr int kQBytes = kBwdQ * D * 2;             // 16 KiB (Q_i or dO_i)
   static constexpr int kdSBytes = kBwdKeys * kBwdQ * 2;     // 16 KiB
-  static constexpr int kSmemBytes = 2 * kKBytes + 4 * kQBytes + kdSBytes + 1024 /*align*/ + 2 * 2 * kBwdQ * 4 /*lse, delta*/ + 256;
+  static constexpr int kdQBytes = kBwdQ * kD * 4;           // fp32 dQ tile staged for the TMA reduce-add
+  static constexpr int kSmemBytes = 2 * kKBytes + 2 * kBwdQStages * kQBytes + kdSBytes + kdQBytes + 1024 /*align*/ + kBwdQStages * 2 * kBwdQ * 4 /*lse2, delta per ring slot*/ + 256;
   static constexpr int tS = 0, tdP = 64, tP = 128, tdS = 160, tdQ = 192, tdV = 256, tdK = 256 + kD;
 };
 
 template <int kD>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
-                const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do, const AttnBwdArgs args) {
+                const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
+                const __grid_constant__ CUtensorMap tmap_dq, const __grid_constant__ CUtensorMap tmap_lse2,
+                const __grid_constant__ CUtensorMap tmap_delta, const AttnBwdArgs args) {
   using C = BCfg<kD>;
   constexpr int D = C::D;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sK = smem_base, sV = sK + C::kKBytes;
   const uint32_t sQ0 = sV + C::kKBytes;                       // Q stage s at sQ0 + s*2*kQBytes, dO right after it
-  const uint32_t sdS = sQ0 + 4 * C::kQBytes;
-  const uint32_t sStat = sdS + C::kdSBytes;                   // float lse2[2][64], delta[2][64]
-  const uint32_t bar_base = sStat + 2 * 2 * kBwdQ * 4;
+  const uint32_t sdS = sQ0 + 2 * kBwdQStages * C::kQBytes;
+  const uint32_t sdQ = sdS + C::kdSBytes;                     // [64 q][D] fp32, dense
+  const uint32_t sStat = sdQ + C::kdQBytes;                   // per ring slot: float lse2[64], delta[64] (TMA-loaded with Q / dO)
+  const uint32_t bar_base = sStat + kBwdQStages * 2 * kBwdQ * 4;
   const uint32_t kv_full = bar_base;
   auto qdo_full = [&](int s) { return bar_base + 8u * (1 + s); };
-  auto qdo_empty = [&](int s) { return bar_base + 8u * (3 + s); };
-  const uint32_t sp_full = bar_base + 8u * 5, sp_empty = bar_base + 8u * 6, pds_full = bar_base + 8u * 7, mma_done = bar_base + 8u * 8,
-                 dq_empty = bar_base + 8u * 9;
-  const uint32_t tmem_slot = bar_base + 8u * 10;
+  auto qdo_empty = [&](int s) { return bar_base + 8u * (1 + kBwdQStages + s); };
+  constexpr uint32_t kB0 = 1 + 2 * kBwdQStages;
+  const uint32_t sp_full = bar_base + 8u * kB0, sp_empty = bar_base + 8u * (kB0 + 1), pds_full = bar_base + 8u * (kB0 + 2),
+                 mma_done = bar_base + 8u * (kB0 + 3), dq_empty = bar_base + 8u * (kB0 + 4);
+  const uint32_t tmem_slot = bar_base + 8u * (kB0 + 5);
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   float* stat = reinterpret_cast<float*>(smem_gen + (sStat - smem_base));
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
@@ -440,11 +452,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   const int n_it = nq_total - i_min;
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v); prefetch_tmap(&tmap_do);
+    prefetch_tmap(&tmap_q); prefetch_tmap(&tmap_k); prefetch_tmap(&tmap_v); prefetch_tmap(&tmap_do); prefetch_tmap(&tmap_dq); prefetch_tmap(&tmap_lse2); prefetch_tmap(&tmap_delta);
   }
   if (warp == 1 && lane == 0) {
     mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(qdo_full(s), 1); mbar_init(qdo_empty(s), 1); }
+    for (int s = 0; s < kBwdQStages; ++s) { mbar_init(qdo_full(s), 1); mbar_init(qdo_empty(s), 1); }
     mbar_init(sp_full, 1);
     mbar_init(sp_empty, kBwdCompute);
     mbar_init(pds_full, kBwdCompute);
@@ -468,10 +480,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           tma_load_4d(sV + hh * (kBwdKeys * 128), &tmap_v, kv_full, hh * 64, h, k0, b);
         }
         for (int it = 0; it < n_it; ++it) {
-          const int st = it & 1, q0 = (i_min + it) * kBwdQ;
-          mbar_wait(qdo_empty(st), ((it >> 1) & 1) ^ 1u);
-          mbar_expect_tx(qdo_full(st), 2 * C::kQBytes);
+          const int st = it % kBwdQStages, q0 = (i_min + it) * kBwdQ;
+          mbar_wait(qdo_empty(st), ((it / kBwdQStages) & 1) ^ 1u);
+          mbar_expect_tx(qdo_full(st), 2 * C::kQBytes + 2 * kBwdQ * 4);
           const uint32_t sQ = sQ0 + st * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
+          // the block's softmax statistics ride along (rows beyond S are zero-filled, which makes their dS vanish)
+          tma_load_4d(sStat + st * (2 * kBwdQ * 4), &tmap_lse2, qdo_full(st), q0, bh, 0, 0);
+          tma_load_4d(sStat + st * (2 * kBwdQ * 4) + kBwdQ * 4, &tmap_delta, qdo_full(st), q0, bh, 0, 0);
 #pragma unroll
           for (int hh = 0; hh < D / 64; ++hh) {
             tma_load_4d(sQ + hh * (kBwdQ * 128), &tmap_q, qdo_full(st), hh * 64, h, q0, b);
@@ -484,44 +499,56 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         constexpr uint32_t idesc_s = idesc_bf16_f32(128, kBwdQ, 0, 0);       // S^T, dP^T: [128 keys x 64 q]
         constexpr uint32_t idesc_dkv = idesc_bf16_f32(128, D, 0, 1);         // dV, dK: A in TMEM, B MN-major
         constexpr uint32_t idesc_dq = idesc_bf16_f32(128, kBwdQ, 1, 1);      // dQ^T: A = K MN-major, B = dS^T MN-major
+        // base descriptors; every MMA adds a compile-time constant to the address field (see the forward kernel)
+        const uint64_t dK_k = smem_desc_sw128(sK, 16, 1024), dV_k = smem_desc_sw128(sV, 16, 1024);                  // K-major A
+        const uint64_t dK_mn = smem_desc_sw128(sK, D == 128 ? kBwdKeys * 128 : 0, 1024);                          // MN-major A (M = d)
+        const uint64_t ddS_mn = smem_desc_sw128(sdS, kBwdKeys * 128, 1024);
+        const uint64_t dQ_k0 = smem_desc_sw128(sQ0, 16, 1024), ddO_k0 = smem_desc_sw128(sQ0 + C::kQBytes, 16, 1024);
+        const uint64_t dQ_mn0 = smem_desc_sw128(sQ0, kBwdQ * 128, 1024), ddO_mn0 = smem_desc_sw128(sQ0 + C::kQBytes, kBwdQ * 128, 1024);
+        constexpr uint32_t kSlot16 = (2 * C::kQBytes) >> 4;                                   // ring slot pitch in descriptor units
         auto issue_s_dp = [&](int it) {
-          const uint32_t sQ = sQ0 + (it & 1) * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
+          const uint64_t slot = (uint64_t)((it % kBwdQStages) * kSlot16);
+          const uint64_t q0d = dQ_k0 + slot, do0d = ddO_k0 + slot;
 #pragma unroll
           for (int k = 0; k < D / 16; ++k) {
-            const uint64_t da = smem_desc_sw128(sK + (k / 4) * (kBwdKeys * 128) + (k % 4) * 32, 16, 1024);
-            const uint64_t db = smem_desc_sw128(sQ + (k / 4) * (kBwdQ * 128) + (k % 4) * 32, 16, 1024);
+            const uint64_t da = dK_k + (uint64_t)(((k / 4) * (kBwdKeys * 128) + (k % 4) * 32) >> 4);
+            const uint64_t db = q0d + (uint64_t)(((k / 4) * (kBwdQ * 128) + (k % 4) * 32) >> 4);
             mma_f16_ss(tmem_base + C::tS, da, db, idesc_s, k != 0 ? 1u : 0u);
           }
 #pragma unroll
           for (int k = 0; k < D / 16; ++k) {
-            const uint64_t da = smem_desc_sw128(sV + (k / 4) * (kBwdKeys * 128) + (k % 4) * 32, 16, 1024);
-            const uint64_t db = smem_desc_sw128(sdO + (k / 4) * (kBwdQ * 128) + (k % 4) * 32, 16, 1024);
+            const uint64_t da = dV_k + (uint64_t)(((k / 4) * (kBwdKeys * 128) + (k % 4) * 32) >> 4);
+            const uint64_t db = do0d + (uint64_t)(((k / 4) * (kBwdQ * 128) + (k % 4) * 32) >> 4);
             mma_f16_ss(tmem_base + C::tdP, da, db, idesc_s, k != 0 ? 1u : 0u);
           }
           tc_commit(sp_full);
         };
+        const bool mprof = args.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
         mbar_wait(kv_full, 0);
         mbar_wait(qdo_full(0), 0);
         tc_fence_after();
         issue_s_dp(0);
         for (int it = 0; it < n_it; ++it) {
           if (it + 1 < n_it) {
-            mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
+            mbar_wait(qdo_full((it + 1) % kBwdQStages), ((it + 1) / kBwdQStages) & 1);
             mbar_wait(sp_empty, it & 1);
             tc_fence_after();
+            if (mprof && it < 4) args.prof[64 + it * 4 + 0] = clock64();
             issue_s_dp(it + 1);
+            if (mprof && it < 4) args.prof[64 + it * 4 + 1] = clock64();
           }
           mbar_wait(pds_full, it & 1);
           tc_fence_after();
-          const uint32_t sQ = sQ0 + (it & 1) * 2 * C::kQBytes, sdO = sQ + C::kQBytes;
+          if (mprof && it < 4) args.prof[64 + it * 4 + 2] = clock64();
+          const uint64_t slot_mn = (uint64_t)((it % kBwdQStages) * kSlot16);
 #pragma unroll
           for (int k = 0; k < kBwdQ / 16; ++k) {       // reduction over the 64 queries
-            const uint64_t ddo = smem_desc_sw128(sdO + k * 2048, kBwdQ * 128, 1024);
+            const uint64_t ddo = ddO_mn0 + slot_mn + (uint64_t)((k * 2048) >> 4);
             mma_f16_ts(tmem_base + C::tdV, tmem_base + C::tP + k * 8, ddo, idesc_dkv, (it | k) != 0 ? 1u : 0u);
           }
 #pragma unroll
           for (int k = 0; k < kBwdQ / 16; ++k) {
-            const uint64_t dq = smem_desc_sw128(sQ + k * 2048, kBwdQ * 128, 1024);
+            const uint64_t dq = dQ_mn0 + slot_mn + (uint64_t)((k * 2048) >> 4);
             mma_f16_ts(tmem_base + C::tdK, tmem_base + C::tdS + k * 8, dq, idesc_dkv, (it | k) != 0 ? 1u : 0u);
           }
           if (it > 0) {
@@ -530,12 +557,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           }
 #pragma unroll
           for (int k = 0; k < kBwdKeys / 16; ++k) {    // reduction over the 128 keys
-            const uint64_t da = smem_desc_sw128(sK + k * 2048, D == 128 ? kBwdKeys * 128 : 0, 1024);
-            const uint64_t db = smem_desc_sw128(sdS + k * 2048, kBwdKeys * 128, 1024);
+            const uint64_t da = dK_mn + (uint64_t)((k * 2048) >> 4);
+            const uint64_t db = ddS_mn + (uint64_t)((k * 2048) >> 4);
             mma_f16_ss(tmem_base + C::tdQ, da, db, idesc_dq, k != 0 ? 1u : 0u);
           }
-          tc_commit(qdo_empty(it & 1));
+          tc_commit(qdo_empty(it % kBwdQStages));
           tc_commit(mma_done);
+          if (mprof && it < 4) args.prof[64 + it * 4 + 3] = clock64();
         }
       }
     } else {
@@ -546,31 +574,40 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const int key = k0 + row;
       const int ct = threadIdx.x - 64;            // 0..255
       const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-      const int64_t stat_base = ((int64_t)b * args.H + h) * args.S;
-      float* dq_base = args.dq_acc + ((int64_t)b * args.S * args.H + h) * D;     // + q * H * D + d
 
-      auto drain_dq = [&](int it) {               // dQ^T of block `it` -> global fp32 accumulator
+      // dQ^T of block `it`: TMEM -> registers -> transposed into a dense [q][d] fp32 tile in smem -> one asynchronous TMA
+      // reduce-add into the global fp32 accumulator (the L2 does the atomics; the compute threads do not wait for them)
+      auto drain_dq = [&](int it) {
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + C::tdQ + lane_off + half * 32, r);
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(dq_empty);
-        const int q0 = (i_min + it) * kBwdQ + half * 32;
-        if (row < D) {                          // D == 64: TMEM lanes 64..127 hold duplicates of the padded MMA rows
+        if (ct == 0) tma_store_wait_read<0>();          // the previous reduce has read the staging tile
+        named_bar_sync(2, kBwdCompute);
+        if (row < D) {                                  // D == 64: TMEM lanes 64..127 hold duplicates of the padded MMA rows
+          const uint32_t dst = sdQ + (uint32_t)((half * 32) * D + row) * 4u;
 #pragma unroll
-          for (int c = 0; c < 32; ++c)
-            if (q0 + c < args.S) atomicAdd(dq_base + (int64_t)(q0 + c) * args.H * D + row, __uint_as_float(r[c]));
+          for (int c = 0; c < 32; ++c) asm volatile("st.shared.b32 [%0], %1;" ::"r"(dst + (uint32_t)(c * D * 4)), "r"(r[c]) : "memory");
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(2, kBwdCompute);
+        if (ct == 0) {
+          tma_reduce_add_4d(&tmap_dq, sdQ, 0, h, (i_min + it) * kBwdQ, b);
+          tma_store_commit();
         }
       };
 
+      const bool prof = args.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && warp == 2 && lane == 0;
       for (int it = 0; it < n_it; ++it) {
+        if (prof && it < 8) args.prof[it * 8 + 0] = clock64();
         const int q0 = (i_min + it) * kBwdQ;
-        float* st_l = stat + (it & 1) * 2 * kBwdQ;
-        if (ct < kBwdQ) st_l[ct] = (q0 + ct < args.S) ? args.lse[stat_base + q0 + ct] * 1.4426950408889634f : INFINITY;
-        else if (ct < 2 * kBwdQ) st_l[ct] = (q0 + ct - kBwdQ < args.S) ? args.delta[stat_base + q0 + ct - kBwdQ] : 0.f;
-        named_bar_sync(1, kBwdCompute);
+        const float* st_l = stat + (it % kBwdQStages) * 2 * kBwdQ;
+        if (prof && it < 8) args.prof[it * 8 + 1] = clock64();
         mbar_wait(sp_full, it & 1);
+        mbar_wait(qdo_full(it % kBwdQStages), (it / kBwdQStages) & 1);   // already complete (S(it) consumed this slot); orders the stats reads
         tc_fence_after();
+        if (prof && it < 8) args.prof[it * 8 + 2] = clock64();
         uint32_t rs[32], rp[32];
         tmem_ld_32x32(tmem_base + C::tS + lane_off + half * 32, rs);
         tmem_ld_32x32(tmem_base + C::tdP + lane_off + half * 32, rp);
@@ -578,26 +615,36 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         tc_fence_before();
         mbar_arrive(sp_empty);
         uint32_t pP[16], pS[16];
-        const bool diag = args.causal && (q0 < k0 + kBwdKeys);          // some (key, query) pairs of this tile are masked
+        // Rows of keys beyond S need no mask: their K and V rows were zero-filled by TMA, so whatever P they get multiplies zeros
+        // in dQ and lands in dK/dV rows that are never stored.  Only tiles crossing the causal diagonal mask, per element.
+        const bool diag = args.causal && (q0 < k0 + kBwdKeys);
+        const float4* l4 = reinterpret_cast<const float4*>(st_l + half * 32);
+        const float4* d4 = reinterpret_cast<const float4*>(st_l + kBwdQ + half * 32);
 #pragma unroll
-        for (int c = 0; c < 32; c += 2) {
-          float p[2], ds[2];
+        for (int c = 0; c < 32; c += 4) {
+          const float4 L = l4[c >> 2], Dl = d4[c >> 2];
+          const float lv[4] = {L.x, L.y, L.z, L.w}, dv[4] = {Dl.x, Dl.y, Dl.z, Dl.w};
+          float pq[4], dq[4];
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int qc = half * 32 + c + e;
-            float pv = exp2f(__uint_as_float(rs[c + e]) * args.scale_log2 - st_l[qc]);
-            if ((diag && key > q0 + qc) || key >= args.S) pv = 0.f;
-            p[e] = pv;
-            ds[e] = pv * (__uint_as_float(rp[c + e]) - st_l[kBwdQ + qc]) * args.scale;
+          for (int e = 0; e < 4; ++e) {
+            float pv = exp2f(__uint_as_float(rs[c + e]) * args.scale_log2 - lv[e]);
+            if (diag && key > q0 + half * 32 + c + e) pv = 0.f;
+            pq[e] = pv;
+            dq[e] = pv * (__uint_as_float(rp[c + e]) - dv[e]) * args.scale;
           }
-          pP[c >> 1] = pack_bf16(p[0], p[1]);
-          pS[c >> 1] = pack_bf16(ds[0], ds[1]);
+          pP[c >> 1] = pack_bf16(pq[0], pq[1]);
+          pP[(c >> 1) + 1] = pack_bf16(pq[2], pq[3]);
+          pS[c >> 1] = pack_bf16(dq[0], dq[1]);
+          pS[(c >> 1) + 1] = pack_bf16(dq[2], dq[3]);
         }
+        if (prof && it < 8) args.prof[it * 8 + 3] = clock64() + (long long)(pP[0] == 0x12345678u && pS[3] == 77u);
         if (it > 0) {
           mbar_wait(mma_done, (it - 1) & 1);      // dV/dK/dQ of the previous block retired: P/dS buffers free, dQ^T ready
           tc_fence_after();
+          if (prof && it < 8) args.prof[it * 8 + 4] = clock64();
           drain_dq(it - 1);
         }
+        if (prof && it < 8) args.prof[it * 8 + 5] = clock64();
         tmem_st_32x16(tmem_base + C::tP + lane_off + half * 16, pP);
         tmem_st_32x16(tmem_base + C::tdS + lane_off + half * 16, pS);
         {
@@ -612,10 +659,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive(pds_full);
+        if (prof && it < 8) args.prof[it * 8 + 6] = clock64();
       }
       mbar_wait(mma_done, (n_it - 1) & 1);
       tc_fence_after();
       drain_dq(n_it - 1);
+      if (ct == 0) tma_store_wait<0>();
       // dV, dK: this thread owns key row `row`, columns [D/2 * half, D/2 * half + D/2)
       const bool row_ok = key < args.S;
 #pragma unroll
@@ -663,7 +712,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
 
 // delta[b,h,s] = sum_d O * dO   (one warp per row; lanes cover D in 4-element pieces)
 __global__ void __launch_bounds__(256)
-attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S, int D,
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o, const float* __restrict__ lse, float* __restrict__ delta,
+                  float* __restrict__ lse2, int B, int H, int S, int S_pad, int D,
                   int64_t o_sb, int64_t o_ss, int64_t o_sh, int64_t do_sb, int64_t do_ss, int64_t do_sh) {
   const int lane = threadIdx.x & 31;
   const int64_t rows = (int64_t)B * H * S;
@@ -678,7 +728,11 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
       v = bf16lo(a.x) * bf16lo(g.x) + bf16hi(a.x) * bf16hi(g.x) + bf16lo(a.y) * bf16lo(g.y) + bf16hi(a.y) * bf16hi(g.y);
     }
     v = warp_sum(v);
-    if (lane == 0) delta[r] = v;          // r enumerates (b, h, s)
+    if (lane == 0) {                      // r enumerates (b, h, s); the statistics rows are padded to S_pad
+      const int64_t w = (r / S) * S_pad + s;
+      delta[w] = v;
+      lse2[w] = lse[r] * 1.4426950408889634f;
+    }
   }
 }
 
@@ -700,7 +754,7 @@ attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict_
 }  // namespace
 
 // Backward of detb200_attn_fwd for H_kv == H, S_q == S_kv, D in {64, 128}.  All tensors bf16 (B, S, H, D)-addressed with element
-// strides {batch, seq, head}.  `delta` (fp32 [B,H,S]) and `dq_acc` (fp32 [B,S,H,D]) are caller-provided scratch; dq_acc is
+// strides {batch, seq, head}.  `delta` (fp32 [2,B,H,ceil64(S)]: row-dot(O,dO) and lse*log2e) and `dq_acc` (fp32 [B,S,H,D]) are caller-provided scratch; dq_acc is
 // zeroed here.  dq/dk/dv may be slices of one packed buffer.
 DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, float* delta,
                                  float* dq_acc, void* dq, void* dk, void* dv, int B, int H, int S, int D, const int64_t* q_st,
@@ -727,9 +781,26 @@ DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, co
   if ((rc = mk(&tdo, d_o, do_st, kBwdQ))) return rc;
   if ((rc = mk(&tk, k, k_st, kBwdKeys))) return rc;
   if ((rc = mk(&tv, v, v_st, kBwdKeys))) return rc;
+  CUtensorMap tdq;
+  {
+    const uint64_t dims[4] = {(uint64_t)D, (uint64_t)H, (uint64_t)S, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)D * 4, (uint64_t)H * D * 4, (uint64_t)S * H * D * 4};
+    const uint32_t box[4] = {(uint32_t)D, 1, kBwdQ, 1};
+    if ((rc = detb200_make_tmap_4d_f32_plain(&tdq, dq_acc, dims, strides, box))) return rc;
+  }
   const int64_t rows = (int64_t)B * H * S;
+  const int S_pad = (S + 63) / 64 * 64;                          // row pitch of the statistics (TMA needs 16-byte multiples)
+  const int64_t stat_elems = (int64_t)B * H * S_pad;
+  CUtensorMap tl2, tdl;
+  {
+    const uint64_t dims[4] = {(uint64_t)S, (uint64_t)B * H, 1, 1};
+    const uint64_t strides[3] = {(uint64_t)S_pad * 4, (uint64_t)stat_elems * 4, (uint64_t)stat_elems * 4};
+    const uint32_t box[4] = {kBwdQ, 1, 1, 1};
+    if ((rc = detb200_make_tmap_4d_f32_plain(&tdl, delta, dims, strides, box))) return rc;
+    if ((rc = detb200_make_tmap_4d_f32_plain(&tl2, delta + stat_elems, dims, strides, box))) return rc;
+  }
   attn_delta_kernel<<<grid_for(rows, 8, 1, kNumSMs * 16), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(o), reinterpret_cast<const __nv_bfloat16*>(d_o),
-                                                                         delta, B, H, S, D, o_st[0], o_st[1], o_st[2], do_st[0], do_st[1], do_st[2]);
+                                                                         lse, delta, delta + stat_elems, B, H, S, S_pad, D, o_st[0], o_st[1], o_st[2], do_st[0], do_st[1], do_st[2]);
   DETB200_LAUNCH_CHECK();
   DETB200_CHECK(cudaMemsetAsync(dq_acc, 0, sizeof(float) * (size_t)rows * D, stream));
   AttnBwdArgs a;
@@ -737,15 +808,37 @@ DETB200_API int detb200_attn_bwd(const void* q, const void* k, const void* v, co
   a.B = B; a.H = H; a.S = S;
   a.dk_sb = dk_st[0]; a.dk_ss = dk_st[1]; a.dk_sh = dk_st[2]; a.dv_sb = dv_st[0]; a.dv_ss = dv_st[1]; a.dv_sh = dv_st[2];
   a.scale = scale; a.scale_log2 = scale * 1.4426950408889634f; a.causal = causal;
+  a.prof = nullptr;
+  static const bool want_prof = getenv("DETB200_ATTN_PROF") != nullptr;
+  static long long* dbuf = nullptr;
+  if (want_prof) {
+    if (dbuf == nullptr) DETB200_CHECK(cudaMalloc(&dbuf, 96 * sizeof(long long)));
+    DETB200_CHECK(cudaMemsetAsync(dbuf, 0, 96 * sizeof(long long), stream));
+    a.prof = dbuf;
+  }
   dim3 grid((S + kBwdKeys - 1) / kBwdKeys, B * H);
   if (D == 128) {
     DETB200_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, BCfg<128>::kSmemBytes));
-    attn_bwd_kernel<128><<<grid, kBwdThreads, BCfg<128>::kSmemBytes, stream>>>(tq, tk, tv, tdo, a);
+    attn_bwd_kernel<128><<<grid, kBwdThreads, BCfg<128>::kSmemBytes, stream>>>(tq, tk, tv, tdo, tdq, tl2, tdl, a);
   } else {
     DETB200_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, BCfg<64>::kSmemBytes));
-    attn_bwd_kernel<64><<<grid, kBwdThreads, BCfg<64>::kSmemBytes, stream>>>(tq, tk, tv, tdo, a);
+    attn_bwd_kernel<64><<<grid, kBwdThreads, BCfg<64>::kSmemBytes, stream>>>(tq, tk, tv, tdo, tdq, tl2, tdl, a);
   }
   DETB200_LAUNCH_CHECK();
+  if (want_prof) {
+    long long hbuf[96];
+    DETB200_CHECK(cudaMemcpyAsync(hbuf, dbuf, sizeof(hbuf), cudaMemcpyDeviceToHost, stream));
+    DETB200_CHECK(cudaStreamSynchronize(stream));
+    const long long t0 = hbuf[0];
+    for (int j = 1; j < 4; ++j)
+      fprintf(stderr, "attn_bwd_abs it=%d compute: top=%lld sp_seen=%lld math_done=%lld mma_seen=%lld drained=%lld pds_arrive=%lld | mma: issue_sdp(it+1)=%lld..%lld pds_seen=%lld issued_all=%lld\n",
+              j, hbuf[j * 8] - t0, hbuf[j * 8 + 2] - t0, hbuf[j * 8 + 3] - t0, hbuf[j * 8 + 4] - t0, hbuf[j * 8 + 5] - t0, hbuf[j * 8 + 6] - t0,
+              hbuf[64 + j * 4] - t0, hbuf[64 + j * 4 + 1] - t0, hbuf[64 + j * 4 + 2] - t0, hbuf[64 + j * 4 + 3] - t0);
+    for (int j = 0; j < 8 && hbuf[j * 8 + 6] != 0; ++j)
+      fprintf(stderr, "attn_bwd_prof it=%d stage+bar=%lld wait_sp=%lld ld+math=%lld wait_mma=%lld drain_dq=%lld st+arrive=%lld loop=%lld\n", j,
+              hbuf[j * 8 + 1] - hbuf[j * 8], hbuf[j * 8 + 2] - hbuf[j * 8 + 1], hbuf[j * 8 + 3] - hbuf[j * 8 + 2], j ? hbuf[j * 8 + 4] - hbuf[j * 8 + 3] : 0,
+              j ? hbuf[j * 8 + 5] - hbuf[j * 8 + 4] : 0, hbuf[j * 8 + 6] - hbuf[j * 8 + 5], j ? hbuf[j * 8] - hbuf[(j - 1) * 8] : 0);
+  }
   const int64_t n8 = rows * D / 8;
   attn_dq_convert_kernel<<<grid_for(n8, 256, 2, kNumSMs * 8), 256, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), n8, S, H, D, dq_st[0], dq_st[1], dq_st[2]);
   DETB200_LAUNCH_CHECK();

@@ -717,6 +717,26 @@ int detb200_make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t
   return 0;
 }
 
+// fp32, no swizzle (dense [box3][box2][box1][box0] image in smem): used for TMA reduce-add into fp32 accumulators
+int detb200_make_tmap_4d_f32_plain(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides[3], const uint32_t box[4]) {
+  std::call_once(g_encode_once, resolve_encode);
+  if (g_encode == nullptr) {
+    detb200_set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return DETB200_ERR_UNSUPPORTED;
+  }
+  const cuuint64_t d[4] = {dims[0], dims[1], dims[2], dims[3]};
+  const cuuint64_t st[3] = {strides[0], strides[1], strides[2]};
+  const cuuint32_t bx[4] = {box[0], box[1], box[2], box[3]};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), d, st, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    detb200_set_error("cuTensorMapEncodeTiled(4d f32) failed with CUresult %d", (int)r);
+    return DETB200_ERR_BAD_ARG;
+  }
+  return 0;
+}
+
 // Shared by the plain and the gather-fused entry points.
 int detb200_gemm_bf16_impl(const void* A, const void* B, void* C, const void* bias, void* aux, int64_t M, int64_t N, int64_t K, int64_t lda,
                            int64_t ldb, int64_t ldc, int64_t ldaux, int a_mn_major, int b_mn_major, int out_fp32, int bias_fp32,

@@ -149,7 +149,7 @@ def attention_backward_packed(qkv: torch.Tensor, o: torch.Tensor, lse: torch.Ten
     do = do if (_ok(do) and do.stride(-1) == 1) else do.contiguous()
     i64x3 = _lib.c_int64 * 3
     dq_acc = torch.zeros((B, S, H, D), dtype=torch.float32, device=qkv.device)
-    delta = torch.empty((B, H, S), dtype=torch.float32, device=qkv.device)
+    delta = torch.empty((2, B, H, (S + 63) // 64 * 64), dtype=torch.float32, device=qkv.device)   # row-dot(O, dO) and lse * log2(e), padded rows
 
     def st(t: torch.Tensor) -> Any:
         return i64x3(t.stride(0), t.stride(1), t.stride(2))

@@ -231,7 +231,7 @@ int detb200_add_bf16(const void* a, const void* b, const void* c /* nullable */,
 
 /* Backward of detb200_attn_fwd on tcgen05 (H_kv == H, S_q == S_kv, D == 128): five GEMMs per (key block, query block)
  * pair, dK/dV accumulated in tensor memory, dQ through fp32 atomics into `dq_acc` ([B,S,H,D], zeroed here) and converted
- * to bf16.  `delta`: fp32 [B,H,S] scratch.  dq/dk/dv may be the three slices of one packed [B,S,3,H,D] buffer. */
+ * to bf16.  `delta`: fp32 [2,B,H,ceil64(S)] scratch.  dq/dk/dv may be the three slices of one packed [B,S,3,H,D] buffer. */
 int detb200_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse, float* delta,
                      float* dq_acc, void* dq, void* dk, void* dv, int B, int H, int S, int D, const int64_t* q_strides,
                      const int64_t* k_strides, const int64_t* v_strides, const int64_t* o_strides, const int64_t* do_strides,
