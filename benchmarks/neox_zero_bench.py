@@ -42,6 +42,7 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--stage", type=int, default=1)
+    ap.add_argument("--vocab", type=int, default=50304, help="51200 also lets the LM head split over 8 ranks under stage 3")
     ap.add_argument("--json")
     a = ap.parse_args()
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
@@ -49,10 +50,11 @@ def main() -> None:
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl")
     out = {"model": a.model, "world": world, "micro_batch": a.batch, "seq": a.seq, "zero_stage": a.stage}
-    pool = [torch.randint(0, 50304, (a.batch, a.seq + 1), device=dev) for _ in range(4)]
+    pool = [torch.randint(0, a.vocab, (a.batch, a.seq + 1), device=dev) for _ in range(4)]
     # ---- native: our model + ZeRO engine
     torch.manual_seed(0)
-    model = gpt.build(a.model, block_size=a.seq)
+    model = gpt.build(a.model, block_size=a.seq, vocab_size=a.vocab)
+    flops_tok = model.flops_per_token(a.seq)            # before stage 3 cuts the weights into shards
     cfg = {"train_micro_batch_size_per_gpu": a.batch, "gradient_accumulation_steps": 1, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
            "optimizer": {"type": "AdamW", "params": {"lr": 1e-4, "weight_decay": 0.1, "betas": [0.9, 0.95]}}, "zero_optimization": {"stage": a.stage}}
     engine, _, _, _ = zero.initialize(model=model, config=cfg)
@@ -63,29 +65,52 @@ def main() -> None:
         engine.backward(loss)
         engine.step()
 
+    torch.cuda.reset_peak_memory_stats()
     ms = timed(native_step, a.steps, a.warmup, dev)
     tok = world * a.batch * a.seq / ms * 1e3
-    out["native"] = {"ms_per_step": ms, "tokens_per_s": tok, "model_tflops_per_gpu": tok / world * model.flops_per_token(a.seq) / 1e12}
-    del engine, model
+    out["native"] = {"ms_per_step": ms, "tokens_per_s": tok, "model_tflops_per_gpu": tok / world * flops_tok / 1e12,
+                     "peak_mem_gb": torch.cuda.max_memory_allocated() / 2**30, "partitioned_weights": engine.partitioned,
+                     "optimizer_kernel_launches_total": engine.kernel_launches}
+    del engine, model, native_step
     torch.cuda.empty_cache()
     # ---- library arm: stock torch modules, DDP, fused AdamW, bf16 autocast
     torch.manual_seed(0)
-    ref = gpt.build(a.model, native=False, block_size=a.seq).to(dev)
-    ddp = torch.nn.parallel.DistributedDataParallel(ref, device_ids=[local], gradient_as_bucket_view=True)
-    opt = torch.optim.AdamW(ref.parameters(), lr=1e-4, weight_decay=0.1, betas=(0.9, 0.95), fused=True)
+    ref = gpt.build(a.model, native=False, block_size=a.seq, vocab_size=a.vocab).to(dev)
+    arm = "torch_ddp"
+    ddp = None
+    if a.stage >= 3:
+        # the library equivalent of ZeRO-3: FSDP full sharding per transformer block, bf16 compute, NCCL all-gather / reduce-scatter
+        try:
+            from torch.distributed.fsdp import FullyShardedDataParallel as FSDP
+            from torch.distributed.fsdp import MixedPrecision
+            from torch.distributed.fsdp.wrap import ModuleWrapPolicy
+
+            ddp = FSDP(ref, auto_wrap_policy=ModuleWrapPolicy({gpt.Block}), device_id=local, use_orig_params=True,
+                       mixed_precision=MixedPrecision(param_dtype=torch.bfloat16, reduce_dtype=torch.float32))
+            arm = "torch_fsdp"
+        except Exception as e:  # noqa: BLE001
+            out["fsdp_error"] = repr(e)[:300]
+            ddp = None
+    if ddp is None:
+        ddp = torch.nn.parallel.DistributedDataParallel(ref, device_ids=[local], gradient_as_bucket_view=True)
+    opt = torch.optim.AdamW(ddp.parameters(), lr=1e-4, weight_decay=0.1, betas=(0.9, 0.95), fused=True)
 
     def torch_step(i):
         idx = pool[i % 4]
         with torch.autocast("cuda", dtype=torch.bfloat16):
             _, loss = ddp(idx[:, :-1], idx[:, 1:])
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+        if arm == "torch_fsdp":
+            ddp.clip_grad_norm_(1.0)
+        else:
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
         opt.step()
         opt.zero_grad(set_to_none=True)
 
+    torch.cuda.reset_peak_memory_stats()
     ms2 = timed(torch_step, a.steps, a.warmup, dev)
     tok2 = world * a.batch * a.seq / ms2 * 1e3
-    out["torch_ddp"] = {"ms_per_step": ms2, "tokens_per_s": tok2}
+    out[arm] = {"ms_per_step": ms2, "tokens_per_s": tok2, "peak_mem_gb": torch.cuda.max_memory_allocated() / 2**30}
     out["speedup"] = ms2 / ms
     if rank == 0:
         print("NEOX_ZERO_BENCH", json.dumps(out), flush=True)

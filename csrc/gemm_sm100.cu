@@ -448,9 +448,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 }
 
 // ---- all-gather fused GEMM --------------------------------------------------------------------------
-// CTAs [0, n_gemm) run the GEMM over the gathered A; the remaining CTAs push this rank's row shard of A
-// into every peer's copy of the gather buffer (posted NVLink stores) and count arrivals in the peer's
-// a_ready[rank].  The GEMM starts with its own shard and consumes remote shards in the order they are sent.
+// The first n_push CTAs push this rank's row shard of A into every peer's copy of the gather buffer (posted NVLink
+// stores) and count arrivals in the peer's a_ready[rank]; the other n_gemm CTAs run the GEMM over the gathered A,
+// starting with the own shard and consuming remote shards in the order they are sent.
 struct AgArgs {
   uint8_t* peer_a[16];         // base of the [T, lda] gather buffer on every rank (peer-mapped)
   GemmCtrl* peer_ctrl[16];
@@ -533,8 +533,12 @@ __global__ void __launch_bounds__(kThreads, 1)
 ag_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_aux, const GemmArgs args,
                     const AgArgs ag) {
-  if ((int)blockIdx.x < ag.n_gemm) gemm_body<kBlockN, false, kBMN, false>(tmap_a, tmap_b, tmap_c, tmap_aux, nullptr, args, blockIdx.x, ag.n_gemm);
-  else ag_pusher(ag, blockIdx.x - ag.n_gemm, gridDim.x - ag.n_gemm);
+  // Pushers take the lowest block indices: they are what the *peers* wait for, so they must be resident even when something
+  // else (an NCCL kernel on another stream) holds a few SMs and part of this grid has to queue.  A GEMM CTA that queues
+  // only delays its own tiles.
+  const int n_push = (int)gridDim.x - ag.n_gemm;
+  if ((int)blockIdx.x < n_push) ag_pusher(ag, blockIdx.x, n_push);
+  else gemm_body<kBlockN, false, kBMN, false>(tmap_a, tmap_b, tmap_c, tmap_aux, nullptr, args, blockIdx.x - n_push, ag.n_gemm);
 }
 
 // ---- GEMM fused reduce-scatter ------------------------------------------------------------------------
@@ -845,8 +849,9 @@ DETB200_API int detb200_ag_gemm_bf16_ex(void* const* peer_g, void* const* peer_c
                       (long long)g_rows, align);
     return DETB200_ERR_BAD_ARG;
   }
-  if (epilogue < 0 || epilogue > EPI_RELU || (gather_b && other_mn_major) || (!gather_b && gathered_mn_major)) {
-    detb200_set_error("ag_gemm: unsupported combination (forward epilogues only; the A operand must be K-major)");
+  if (epilogue < 0 || epilogue > EPI_DRELU || (epilogue > EPI_RELU && aux == nullptr) || (gather_b && other_mn_major) ||
+      (!gather_b && gathered_mn_major)) {
+    detb200_set_error("ag_gemm: unsupported combination (derivative epilogues need aux; the A operand must be K-major)");
     return DETB200_ERR_BAD_ARG;
   }
   const int elem_c = out_fp32 ? 4 : 2;
@@ -863,7 +868,7 @@ DETB200_API int detb200_ag_gemm_bf16_ex(void* const* peer_g, void* const* peer_c
   if (rc) return rc;
   rc = detb200_make_tmap_2d(&tc, out_fp32, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * elem_c, out_fp32 ? 32 : 64, 32);
   if (rc) return rc;
-  if (aux != nullptr && epilogue != EPI_NONE) {
+  if (aux != nullptr && epilogue >= EPI_GELU_ERF && epilogue <= EPI_RELU) {
     rc = detb200_make_tmap_2d(&taux, 0, aux, (uint64_t)N, (uint64_t)M, (uint64_t)ldaux * 2, 64, 32);
     if (rc) return rc;
   } else {

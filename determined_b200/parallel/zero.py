@@ -18,10 +18,18 @@ kernel per bucket (``detb200_rs_adam_ag``): read slice r of all peers' gradient 
 NVLink, sum*scale, AdamW on the owned moment shard, and push the fresh weights into every peer's
 parameter buffer — reduce-scatter, optimizer and all-gather fused, no NCCL, no gradient shard
 round trip.  With ``gradient_clipping`` the kernel runs in two phases around a device-side clip
-coefficient (global norm needs all shards first).  ZeRO stage 3's per-layer parameter
-all-gather is unnecessary in this plan (weights stay gathered — they fit); the stage number is
-accepted and reported, and a true parameter-sharded linear is available as
-``determined_b200.ops.gemm.ShardedLinear`` (all-gather fused into the tcgen05 GEMM).
+coefficient (global norm needs all shards first).
+
+Stage 3 (``zero_optimization.stage: 3``) additionally **partitions the weights**: every linear
+layer the kernels can split (``ops/gemm_comm.partition_linears_``, the role of
+``deepspeed.zero.Init``) keeps only its ``out_features / world`` rows as fp32 master, with
+matching gradient and moment shards.  The parameter all-gather is fused into the tcgen05 GEMMs
+that consume the weights (forward and dgrad: ``detb200_ag_gemm_bf16_ex``) and the wgrad GEMM
+reduce-scatters straight into the owner's shard (``detb200_gemm_rs_bf16``), so those weights need
+no collective at step time: one local fused AdamW over the shard buffer.  Small / tied /
+indivisible parameters (embeddings, norms, biases, an LM head whose vocabulary does not split)
+stay replicated on the stage-1/2 path above.  ``stage3_param_persistence_threshold`` is the
+size below which a weight is left replicated, as in DeepSpeed.
 
 On CPU (tests) the same API runs on ``torch.distributed`` all-reduce + ``torch.optim.AdamW``.
 """
@@ -99,6 +107,12 @@ class ZeroEngine:
             device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
         self.device = device
         self.module.to(device)
+        self._tp: Any = None
+        self.partitioned = 0
+        if self._stage >= 3 and isinstance(zo, dict) and zo.get("partition_parameters", device.type == "cuda"):
+            self._partition_stage3(zo)
+            if self.partitioned:
+                model_parameters = None        # the caller's list predates the partitioning pass
         self.micro_steps = 0
         self.global_steps = 0
         self.global_samples = 0
@@ -110,7 +124,8 @@ class ZeroEngine:
             g0 = optimizer.param_groups[0]
             self._hp = {"lr": float(g0.get("lr", 1e-3)), "betas": tuple(g0.get("betas", (0.9, 0.999))), "eps": float(g0.get("eps", 1e-8)),
                         "weight_decay": float(g0.get("weight_decay", 0.0))}
-            params = [p for g in optimizer.param_groups for p in g["params"] if p.requires_grad]
+            if not self.partitioned:
+                params = [p for g in optimizer.param_groups for p in g["params"] if p.requires_grad]
         else:
             typ = str(ocfg.get("type", "AdamW")).lower()
             if typ not in ("adam", "adamw", "fusedadam"):
@@ -119,6 +134,8 @@ class ZeroEngine:
                         "weight_decay": float(op.get("weight_decay", 0.01 if typ == "adamw" else 0.0))}
         self._params = params
         self._native = device.type == "cuda"
+        self._sharded = [p for p in params if getattr(p, "_zero3_shard", False)]
+        self._replicated = [p for p in params if not getattr(p, "_zero3_shard", False)]
         self.param_groups = [{"params": params, **{k: v for k, v in self._hp.items()}}]   # optimizer-like for LR schedulers
         if self._native:
             self._setup_native()
@@ -130,8 +147,32 @@ class ZeroEngine:
         self.training = True
 
     # ------------------------------------------------------------------ set-up
+    def _partition_stage3(self, zo: Dict[str, Any]) -> None:
+        from determined_b200.ops import gemm_comm
+
+        if self.world > 1:
+            with torch.no_grad():          # shards must be cut from identical weights
+                for t in list(self.module.parameters()) + list(self.module.buffers()):
+                    dist.broadcast(t.data, src=0)
+        thresh = zo.get("stage3_param_persistence_threshold", 1 << 20)
+        thresh = (1 << 20) if thresh in (None, "auto") else int(float(thresh))
+        if self.device.type == "cuda":
+            from determined_b200.ops import _lib, comm
+
+            _lib.load()
+            with torch.cuda.device(self.device):
+                self.group = comm.PeerGroup.from_torch_distributed(self.device)
+                self._tp = gemm_comm.TensorParallelGemm(self.group)
+        else:
+            self._tp = gemm_comm.HostTensorParallel()      # CPU tests: same layers over gloo collectives
+        self._tp.external_bias_reduce = True       # biases are replicated parameters: the bucketed path reduces them
+        self.partitioned = gemm_comm.partition_linears_(self.module, self._tp, min_params=thresh)
+        if self.partitioned and self.device.type == "cuda":
+            torch.cuda.empty_cache()
+        logger.info("ZeRO-3: partitioned %d weight matrices over %d ranks", self.partitioned, self.world)
+
     def _setup_native(self) -> None:
-        from determined_b200.ops import _lib, comm
+        from determined_b200.ops import _lib, comm, optim
 
         _lib.load()
         world = self.world
@@ -146,9 +187,16 @@ class ZeroEngine:
             return alloc
 
         with torch.cuda.device(self.device):
-            self.layout = FlatLayout(self.param_groups, self.device, align=align, segment_align=align,
+            self.layout = FlatLayout([{"params": self._replicated}], self.device, align=align, segment_align=align,
                                      grad_alloc=symm("grad"), param_alloc=symm("param"))
-            self.group = comm.PeerGroup.from_torch_distributed(self.device)
+            if getattr(self, "group", None) is None:
+                self.group = comm.PeerGroup.from_torch_distributed(self.device)
+            self.shard_layout: Optional[FlatLayout] = None
+            if self._sharded:
+                self.shard_layout = FlatLayout([{"params": self._sharded}], self.device, align=4, segment_align=4)
+                self.shard_m = torch.zeros(self.shard_layout.total, dtype=torch.float32, device=self.device)
+                self.shard_v = torch.zeros(self.shard_layout.total, dtype=torch.float32, device=self.device)
+                self._norm_scratch = optim.NormScratch(self.device) if self._clip > 0 else None
             self.peer_grads = self.group.map(self._bufs["grad"])
             self.peer_params = self.group.map(self._bufs["param"])
             total = self.layout.total
@@ -176,13 +224,15 @@ class ZeroEngine:
         self.kernel_launches = 0
 
     def _setup_fallback(self) -> None:
+        self.shard_layout = None
         self._torch_opt = torch.optim.AdamW(self._params, lr=self._hp["lr"], betas=self._hp["betas"], eps=self._hp["eps"],
                                             weight_decay=self._hp["weight_decay"])
         self.param_groups = self._torch_opt.param_groups
         if self.world > 1:
             with torch.no_grad():
                 for p in self.module.parameters():
-                    dist.broadcast(p.data, src=0)
+                    if not getattr(p, "_zero3_shard", False):      # weight shards differ per rank by construction
+                        dist.broadcast(p.data, src=0)
 
     def _build_scheduler(self) -> None:
         sc = self.config.get("scheduler")
@@ -242,10 +292,33 @@ class ZeroEngine:
         return self.module.state_dict()
 
     def load_state_dict(self, sd: Dict[str, Any], strict: bool = True) -> Any:
-        out = self.module.load_state_dict(sd, strict=strict)
+        out = self.module.load_state_dict(dict(sd), strict=strict)
+        self._rebind()
+        return out
+
+    def _rebind(self) -> None:
         if self._native:
             self.layout.rebind()
-        return out
+            if self.shard_layout is not None:
+                self.shard_layout.rebind()
+
+    def consolidated_state_dict(self) -> Optional[Dict[str, Any]]:
+        """State dict of the *unpartitioned* model on the CPU (rank 0; other ranks get None).  With stage-3 partitioning this
+        all-gathers one weight at a time — every rank must call it (DeepSpeed: ``stage3_gather_16bit_weights_on_model_save``)."""
+        if not self.partitioned:
+            return {k: v.detach().cpu() for k, v in self.module.state_dict().items()} if self.rank == 0 else None
+        from determined_b200.ops.gemm_comm import Zero3Linear
+
+        sd: Dict[str, Any] = {k: v.detach().cpu() for k, v in self.module.state_dict().items()} if self.rank == 0 else {}
+        for name, m in self.module.named_modules():
+            if isinstance(m, Zero3Linear):
+                full = m.full_weight()
+                if self.rank == 0:
+                    prefix = name + "." if name else ""
+                    sd.pop(prefix + "weight_shard", None)
+                    sd[prefix + "weight"] = full.cpu()
+                del full
+        return sd if self.rank == 0 else None
 
     def __call__(self, *args: Any, **kwargs: Any) -> Any:
         return self.forward(*args, **kwargs)
@@ -288,7 +361,7 @@ class ZeroEngine:
 
     def _fallback_step(self) -> None:
         if self.world > 1:
-            grads = [p.grad for p in self._params if p.grad is not None]
+            grads = [p.grad for p in self._replicated if p.grad is not None]
             if grads:
                 flat = torch._utils._flatten_dense_tensors(grads)
                 dist.all_reduce(flat)
@@ -296,7 +369,15 @@ class ZeroEngine:
                 for g, r in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
                     g.copy_(r)
         if self._clip > 0:
-            torch.nn.utils.clip_grad_norm_(self._params, self._clip)
+            sq = sum((p.grad.float().pow(2).sum() for p in self._replicated if p.grad is not None), torch.zeros(()))
+            mine = sum((p.grad.float().pow(2).sum() for p in self._sharded if p.grad is not None), torch.zeros(()))
+            if self.world > 1 and self._sharded:
+                dist.all_reduce(mine)
+            coef = min(1.0, self._clip / (float((sq + mine).sqrt()) + 1e-6))
+            if coef < 1.0:
+                for p in self._params:
+                    if p.grad is not None:
+                        p.grad.mul_(coef)
         self._torch_opt.step()
         self._torch_opt.zero_grad(set_to_none=False)
 
@@ -332,13 +413,32 @@ class ZeroEngine:
                     self.kernel_launches += 1
                     soff += shard
 
+            def shard_update(grad_scale_ptr: Any) -> None:
+                # partitioned weights: their gradient shards are already reduced (wgrad GEMM epilogue), so the update is local
+                lay = self.shard_layout
+                _lib.check(lib.detb200_adam_flat(lay.flat_param.data_ptr(), lay.flat_grad.data_ptr(), self.shard_m.data_ptr(),
+                                                 self.shard_v.data_ptr(), None, lay.total, self.lr_dev.data_ptr(), self.step_dev.data_ptr(),
+                                                 grad_scale_ptr, None, float(hp["betas"][0]), float(hp["betas"][1]), float(hp["eps"]),
+                                                 float(hp["weight_decay"]), 1, 1.0, 1, 0, sp), "adam_flat")
+                self.kernel_launches += 1
+
             if self._clip > 0:
                 run(1, None)
                 terms = self.group.stats_tensor()[0, :world]
-                _lib.check(lib.detb200_clip_coef(terms.data_ptr(), world, self._clip, 1.0, self.coef.data_ptr(), self.norm.data_ptr(), sp), "clip")
+                if self.shard_layout is not None:
+                    # global norm = replicated part (per-rank slices, exchanged by the kernel) + every rank's weight shards
+                    mine = optim.sumsq(self.shard_layout.flat_grad, self._norm_scratch)
+                    if world > 1:
+                        dist.all_reduce(mine)
+                    terms = torch.cat([terms, mine])
+                _lib.check(lib.detb200_clip_coef(terms.data_ptr(), terms.numel(), self._clip, 1.0, self.coef.data_ptr(), self.norm.data_ptr(), sp), "clip")
                 run(2, self.coef.data_ptr())
+                if self.shard_layout is not None:
+                    shard_update(self.coef.data_ptr())
             else:
                 run(0, None)
+                if self.shard_layout is not None:
+                    shard_update(None)
             # every peer finished reading our gradients (end barrier of the last bucket): clear them
             self.layout.flat_grad.zero_()
         cur.wait_stream(st)
@@ -363,14 +463,17 @@ class ZeroEngine:
         tag = tag or f"global_step{self.global_steps}"
         d = pathlib.Path(save_dir) / str(tag)
         d.mkdir(parents=True, exist_ok=True)
+        module_sd = self.consolidated_state_dict() if self.partitioned else self.module.state_dict()
         if self.rank == 0:
-            torch.save({"module": self.module.state_dict(), "global_steps": self.global_steps, "micro_steps": self.micro_steps,
+            torch.save({"module": module_sd, "global_steps": self.global_steps, "micro_steps": self.micro_steps,
                         "global_samples": self.global_samples, "dp_world_size": self.world, "lr": float(self.param_groups[0]["lr"]),
                         "client_state": client_state or {}, "ds_config": self.config}, d / "mp_rank_00_model_states.pt")
             if save_latest:
                 (pathlib.Path(save_dir) / "latest").write_text(str(tag))
         if self._native:
             opt = {"m": self.m.cpu(), "v": self.v.cpu(), "step": int(self.step_dev.item()), "buckets": self.buckets, "world": self.world}
+            if self.shard_layout is not None:
+                opt.update(shard_m=self.shard_m.cpu(), shard_v=self.shard_v.cpu(), shard_total=self.shard_layout.total)
         else:
             opt = {"torch_opt": self._torch_opt.state_dict()}
         torch.save(opt, d / f"zero_pp_rank_{self.rank}_mp_rank_00_optim_states.pt")
@@ -388,9 +491,8 @@ class ZeroEngine:
             tag = latest.read_text().strip()
         d = load_dir / str(tag)
         ms = torch.load(d / "mp_rank_00_model_states.pt", map_location="cpu", weights_only=False)
-        self.module.load_state_dict(ms["module"], strict=load_module_strict)
-        if self._native:
-            self.layout.rebind()
+        self.module.load_state_dict(dict(ms["module"]), strict=load_module_strict)
+        self._rebind()
         self.global_steps, self.micro_steps = int(ms["global_steps"]), int(ms["micro_steps"])
         self.global_samples = int(ms.get("global_samples", 0))
         self.param_groups[0]["lr"] = float(ms.get("lr", self.param_groups[0]["lr"]))
@@ -403,6 +505,11 @@ class ZeroEngine:
                                        "re-sharding is not supported yet")
                 self.m.copy_(opt["m"])
                 self.v.copy_(opt["v"])
+                if self.shard_layout is not None and "shard_m" in opt:
+                    if int(opt.get("shard_total", -1)) != self.shard_layout.total:
+                        raise RuntimeError("weight-shard optimizer state was saved for a different partitioning")
+                    self.shard_m.copy_(opt["shard_m"])
+                    self.shard_v.copy_(opt["shard_v"])
                 self.step_dev.fill_(int(opt["step"]))
             elif not self._native and "torch_opt" in opt:
                 self._torch_opt.load_state_dict(opt["torch_opt"])

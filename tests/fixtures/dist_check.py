@@ -333,6 +333,65 @@ def check_zero3_linear(rank, world, dev):
     dist.barrier()
 
 
+def check_zero3_engine(rank, world, dev):
+    """GPT under the ZeRO engine: stage 3 (partitioned weights, gather / reduce-scatter inside the GEMMs) follows the same
+    loss curve as stage 1 (replicated weights) and consolidates to the same checkpoint keys."""
+    import tempfile
+
+    from determined_b200.models import gpt
+    from determined_b200.ops import gemm_comm
+    from determined_b200.parallel import zero
+
+    def run(stage):
+        torch.manual_seed(0)
+        E = 512 if world <= 2 else 256 * world             # every projection must split into 256-row shards
+        model = gpt.build("tiny", native=True, n_embd=E, n_head=E // 128, n_layer=2, vocab_size=1024, block_size=256, rotary_pct=0.25,
+                          parallel_residual=True, tie_embeddings=False)
+        cfg = {"train_micro_batch_size_per_gpu": 4, "gradient_accumulation_steps": 2, "gradient_clipping": 1.0, "bf16": {"enabled": True},
+               "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.1}},
+               "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 1000}}
+        eng, _, _, _ = zero.initialize(model=model, config=cfg)
+        g = torch.Generator().manual_seed(100 + rank)
+        losses = []
+        for _ in range(8):
+            idx = torch.randint(0, 1024, (4, 256), generator=g).to(dev)
+            _, loss = eng(idx, idx)
+            eng.backward(loss)
+            eng.step()
+            losses.append(loss.detach().float())
+        t = torch.stack(losses)
+        dist.all_reduce(t)
+        return eng, (t / world).tolist()
+
+    e1, l1 = run(1)
+    e3, l3 = run(3)
+    if world <= 2:
+        assert e3.partitioned == 9, e3.partitioned           # qkv, proj, fc1, fc2 of both blocks + the LM head
+        assert isinstance(e3.module.blocks[0].mlp, gemm_comm.Zero3MLP)
+    else:
+        assert e3.partitioned >= 5, e3.partitioned
+    assert l3[-1] < l3[0], l3
+    for a, b in zip(l1, l3):
+        assert abs(a - b) < 3e-2 * abs(a), (l1, l3)
+    sd1, sd3 = e1.consolidated_state_dict(), e3.consolidated_state_dict()
+    if rank == 0:
+        assert set(sd1) == set(sd3)
+        for k in sd1:
+            assert sd1[k].shape == sd3[k].shape, k
+        w1, w3 = sd1["blocks.0.mlp.fc1.weight"], sd3["blocks.0.mlp.fc1.weight"]
+        assert "blocks.0.mlp.fc1.weight_shard" not in sd3
+        assert float((w1 - w3).abs().max()) < 2e-2, float((w1 - w3).abs().max())
+    d = [tempfile.mkdtemp() if rank == 0 else None]
+    dist.broadcast_object_list(d, 0)
+    e3.save_checkpoint(d[0], tag="z3")
+    e3b, _ = run(3)
+    e3b.load_checkpoint(d[0])
+    for (n, a), (_, b) in zip(e3.module.named_parameters(), e3b.module.named_parameters()):
+        assert torch.equal(a, b), n
+    assert torch.equal(e3.shard_m, e3b.shard_m)
+    dist.barrier()
+
+
 def main():
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(local)
@@ -351,6 +410,8 @@ def main():
         check_gpt_tp(rank, world, dev)
     if which in ("all", "zero3"):
         check_zero3_linear(rank, world, dev)
+    if which in ("all", "zero3_engine"):
+        check_zero3_engine(rank, world, dev)
     dist.barrier()
     if rank == 0:
         print("DIST_CHECK_OK", which, flush=True)
