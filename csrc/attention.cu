@@ -33,7 +33,10 @@ struct AttnArgs {
   float scale_log2;                // softmax scale * log2(e)
   int causal;
   long long* prof;                 // debug (DETB200_ATTN_PROF=1): cycle stamps of CTA (0,0)'s first softmax warp
+  int delay_v_ns;                  // test hook (detb200_attn_debug_delay_v): hold every V tile back, as a congested HBM/NVLink would
 };
+
+int g_delay_v_ns = 0;
 
 // 2^x on the FMA / integer pipes (no MUFU): round-to-nearest split x = n + f with the 1.5*2^23 trick, cubic for 2^f on
 // [-0.5, 0.5] (relative error 6e-4, below bf16 resolution), n added straight into the exponent field.
@@ -75,8 +78,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   auto v_full = [&](int s) { return bar_base + 8u * (1 + 2 * kStagesKV + s); };
   auto v_empty = [&](int s) { return bar_base + 8u * (1 + 3 * kStagesKV + s); };
   const uint32_t s_full = bar_base + 8u * (1 + 4 * kStagesKV);
-  const uint32_t s_empty = s_full + 8u, p_full = s_full + 16u, o_done = s_full + 24u;   // o_done: two barriers, PV(j) commits to [j & 1]
-  const uint32_t tmem_slot = s_full + 40u;
+  // p_full and o_done are barrier PAIRS indexed by j & 1.  With one p_full barrier the softmax can complete P(j) and P(j+1)
+  // (S(j+1) is issued before the MMA thread waits for P(j)) while the MMA thread still waits for V(j) to land: two phases
+  // ahead of a parity wait is indistinguishable from none, and the kernel hangs -- seen under NVLink/HBM contention only.
+  const uint32_t s_empty = s_full + 8u, p_full = s_full + 16u, o_done = s_full + 32u;
+  const uint32_t tmem_slot = s_full + 48u;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -104,6 +110,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     mbar_init(s_full, 1);
     mbar_init(s_empty, 128);
     mbar_init(p_full, 128);
+    mbar_init(p_full + 8u, 128);
     mbar_init(o_done, 1);
     mbar_init(o_done + 8u, 1);
     fence_mbar_init();
@@ -131,6 +138,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       auto load_v = [&](int j) {
         const int st = j % kStagesKV;
         mbar_wait(v_empty(st), ((j / kStagesKV) & 1) ^ 1u);
+        if (args.delay_v_ns > 0) {
+          const uint64_t t0 = globaltimer_ns();
+          while (globaltimer_ns() - t0 < (uint64_t)args.delay_v_ns) __nanosleep(200);
+        }
         mbar_expect_tx(v_full(st), C::kKVBytes);
         const uint32_t sV = sKV + st * C::kStageBytes + C::kKVBytes;
 #pragma unroll
@@ -176,7 +187,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           tc_commit(k_empty((j + 1) % kStagesKV));
         }
         mbar_wait(v_full(j % kStagesKV), (j / kStagesKV) & 1);
-        mbar_wait(p_full, j & 1);
+        mbar_wait(p_full + 8u * (j & 1), (j >> 1) & 1);
         tc_fence_after();
         const uint64_t dv0 = dv_base0 + (uint64_t)((j % kStagesKV) * (C::kStageBytes >> 4));
 #pragma unroll
@@ -265,7 +276,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       tmem_st_32x32(tP + (j & 1) * (kBN / 2) + lane_off, pk);
       tmem_st_wait();
       tc_fence_before();
-      mbar_arrive(p_full);
+      mbar_arrive(p_full + 8u * (j & 1));
       if (prof && j < 8) args.prof[j * 8 + 3] = clock64();
     }
     wait_pv_done(n_kv - 1);
@@ -322,6 +333,13 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
 
 }  // namespace
 
+// Test hook: delay every V tile of the forward kernel by `ns` nanoseconds (0 = off).  Reorders the pipeline the way a
+// congested memory system does; tests/test_attention_gpu.py uses it to pin the barrier protocol.
+DETB200_API int detb200_attn_debug_delay_v(int ns) {
+  g_delay_v_ns = ns < 0 ? 0 : ns;
+  return 0;
+}
+
 // q/k/v/o: bf16, logical shape (B, S, H, D) with element strides (sb, ss, sh) and D contiguous.
 // lse (nullable): fp32 [B, H, S_q], natural-log sum-exp of the scaled scores (needed by the backward).
 DETB200_API int detb200_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int H_kv, int S_q,
@@ -355,6 +373,7 @@ DETB200_API int detb200_attn_fwd(const void* q, const void* k, const void* v, vo
   a.o_sb = o_strides[0]; a.o_ss = o_strides[1]; a.o_sh = o_strides[2];
   a.scale_log2 = scale * 1.4426950408889634f; a.causal = causal;
   a.prof = nullptr;
+  a.delay_v_ns = g_delay_v_ns;
   static const bool want_prof = getenv("DETB200_ATTN_PROF") != nullptr;
   if (want_prof) {
     static long long* dbuf = nullptr;

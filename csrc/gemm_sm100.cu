@@ -103,7 +103,7 @@ __device__ __forceinline__ void wait_counter_sys(const unsigned int* p, unsigned
   if ((int)(ld_acquire_sys_u32(p) - target) >= 0) return;
   const uint64_t t0 = globaltimer_ns();
   while ((int)(ld_acquire_sys_u32(p) - target) < 0) {
-    if (globaltimer_ns() - t0 > 20000000000ull) {
+    if (globaltimer_ns() - t0 > 10000000000ull) {
       printf("detb200: timed out waiting for %s[%d] (have %u want %u) block %d\n", what, idx, ld_acquire_sys_u32(p), target, blockIdx.x);
       __trap();
     }

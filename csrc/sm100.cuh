@@ -44,7 +44,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   const uint64_t t0 = globaltimer_ns();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > 4000000000ull) {
+    if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > 30000000000ull) {
       printf("detb200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
       __trap();
     }

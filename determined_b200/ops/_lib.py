@@ -94,6 +94,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_gemm_rs_bf16", i, [p, p, POINTER(c_void_p), POINTER(c_void_p), i, i, p, p, i64, i64, i64, i64, i64, i64,
                                          i, i, i, i, ctypes.c_uint32, ctypes.c_uint32, p])
     # attention (csrc/attention.cu)
+    _sig(lib, "detb200_attn_debug_delay_v", i, [i])
     _sig(lib, "detb200_attn_fwd", i, [p, p, p, p, p, i, i, i, i, i, i, POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), f, i, p])
     P64 = POINTER(c_int64)
     _sig(lib, "detb200_attn_bwd", i, [p, p, p, p, p, p, p, p, p, p, p, i, i, i, i, P64, P64, P64, P64, P64, P64, P64, P64, f, i, p])

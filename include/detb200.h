@@ -215,6 +215,7 @@ int detb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_recv, v
  * lse (nullable): fp32 [B, H, S_q].  Reference: attention of the GPT-2 / GPT-NeoX examples
  * (examples/deepspeed/gpt_neox, Megatron fused softmax + bmm).
  * ------------------------------------------------------------------------------------------- */
+int detb200_attn_debug_delay_v(int ns);   /* test hook: hold back every V tile of the forward kernel (0 = off) */
 int detb200_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int H_kv, int S_q, int S_kv, int D,
                      const int64_t* q_strides, const int64_t* k_strides, const int64_t* v_strides, const int64_t* o_strides,
                      float scale, int causal, detb200_stream_t stream);

@@ -3,6 +3,7 @@ import math
 
 import pytest
 import torch
+import torch.nn.functional as F
 
 pytestmark = pytest.mark.gpu
 
@@ -108,3 +109,54 @@ def test_attention_qkvpacked_native_backward(cfg, causal):
         g, w = got[:, :, i], xr.grad[:, :, i]
         rel = float((g - w).norm() / (w.norm() + 1e-9))
         assert rel < 2.5e-2, (name, rel)
+
+
+@pytest.mark.parametrize("D", [64, 128])
+def test_forward_survives_late_v_tiles(D):
+    """Regression: the softmax may finish P(j) and P(j+1) before V(j) lands (S(j+1) only needs K(j+1)).  With a single
+    "P ready" barrier that put the producer two phases ahead of the MMA thread's parity wait and the kernel hung; seen on
+    8-GPU runs where peers' NVLink pushes slow the V loads.  The debug hook holds every V tile back to force that order."""
+    from determined_b200.ops import _lib
+    from determined_b200.ops import attention as A
+
+    lib = _lib.load()
+    torch.manual_seed(0)
+    B, S, H = 2, 1024, 4
+    q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
+    want = F.scaled_dot_product_attention(q.transpose(1, 2).float(), k.transpose(1, 2).float(), v.transpose(1, 2).float(),
+                                          is_causal=True).transpose(1, 2)
+    try:
+        for ns in (3000, 20000):
+            lib.detb200_attn_debug_delay_v(ns)
+            o = A.flash_attention(q, k, v, causal=True, layout="bshd")
+            torch.cuda.synchronize()
+            torch.testing.assert_close(o.float(), want, rtol=2e-2, atol=2e-2)
+    finally:
+        lib.detb200_attn_debug_delay_v(0)
+
+
+def test_large_and_growing_logits():
+    """Row maxima that keep jumping (the lazy-rescale path) and logits far outside the unit range; non-finite inputs must
+    not hang either."""
+    from determined_b200.ops import attention as A
+
+    torch.manual_seed(1)
+    B, S, H, D = 1, 1024, 4, 128
+    for scale, ramp in [(12.0, 0.0), (3.0, 20.0)]:
+        q = torch.randn(B, S, H, D, device="cuda") * scale
+        k = torch.randn(B, S, H, D, device="cuda") * scale
+        if ramp:
+            k = k + (torch.arange(S, device="cuda").float() / S * ramp)[None, :, None, None] * torch.sign(q.mean(1, keepdim=True))
+        v = torch.randn(B, S, H, D, device="cuda")
+        q, k, v = (t.to(torch.bfloat16) for t in (q, k, v))
+        for causal in (True, False):
+            o = A.flash_attention(q, k, v, causal=causal, layout="bshd")
+            want = F.scaled_dot_product_attention(q.transpose(1, 2).float(), k.transpose(1, 2).float(), v.transpose(1, 2).float(),
+                                                  is_causal=causal).transpose(1, 2)
+            torch.testing.assert_close(o.float(), want, rtol=3e-2, atol=4e-2)
+    q = torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16)
+    q[0, 100, 0, 0] = float("nan")
+    k = torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16)
+    k[0, 7, 3, 5] = float("inf")
+    A.flash_attention(q, k, torch.randn_like(q), causal=True, layout="bshd")
+    torch.cuda.synchronize()
