@@ -1,0 +1,292 @@
+"""The agent daemon: offers this host's slots to a master and runs the tasks it is handed.
+
+Parity: reference ``agent/internal/agent.go`` (connect, announce devices, reconnect with the list
+of surviving containers), ``agent/internal/containers/manager.go`` + ``container/container.go``
+(start / monitor / kill, log forwarding, state persisted for re-attachment after a restart) and
+``agent/internal/detect`` (slot detection).  What is different: tasks are process groups, not
+Docker containers (``ProcessRuntime`` below is the one "container runtime" of this build — the
+reference has docker / podman / singularity drivers behind the same three verbs), and the link to
+the master is a REST long-poll instead of a websocket (``master/agents.py``).
+
+``python -m determined_b200.agent --master-url http://127.0.0.1:8080 --agent-id gpu-box-2``
+"""
+import base64
+import io
+import json
+import logging
+import os
+import pathlib
+import shutil
+import signal
+import socket
+import subprocess
+import sys
+import tarfile
+import tempfile
+import threading
+import time
+from typing import Any, Dict, List, Optional
+
+import requests
+
+from determined_b200 import __version__, gpu
+
+logger = logging.getLogger("determined.agent")
+
+PYTHON_PLACEHOLDER = "{python}"
+KILL_GRACE_S = 10.0
+
+
+def detect_slots(limit: Optional[int] = None, slot_type: str = "auto") -> List[Dict[str, Any]]:
+    """One entry per schedulable device: the visible NVIDIA GPUs (``nvidia-smi --query-gpu=index,name,uuid``, reference
+    ``detect/nvidia.go:19-117``), else CPU slots (``slot_type: cpu`` gives ``limit`` of them; reference ``detect/cpu.go``)."""
+    gpus, _ = gpu.get_gpus() if slot_type in ("auto", "cuda", "gpu") else ([], "")
+    if gpus:
+        out = [{"type": "DEVICE_TYPE_CUDA", "brand": g.name, "uuid": g.uuid, "index": g.id} for g in gpus]
+    else:
+        out = [{"type": "DEVICE_TYPE_CPU", "brand": "cpu", "uuid": f"cpu-{i}", "index": i} for i in range(limit if limit is not None else 1)]
+    return out[:limit] if limit is not None else out
+
+
+class _Task:
+    def __init__(self, cid: str, proc: Optional[subprocess.Popen], run_dir: Optional[str], pid: int) -> None:
+        self.cid, self.proc, self.run_dir, self.pid = cid, proc, run_dir, pid
+        self.kill_sent: Optional[float] = None
+
+
+class ProcessRuntime:
+    """start / kill / wait for process groups; survives agent restarts through a small state file."""
+
+    def __init__(self, work_dir: str, emit: Any) -> None:
+        self.work_dir = work_dir
+        self.emit = emit                         # emit(event dict): queued for the next poll
+        self.tasks: Dict[str, _Task] = {}
+        self.lock = threading.Lock()
+        self.state_path = os.path.join(work_dir, "tasks.json")
+
+    # -- persistence (re-attachment) -----------------------------------------------------------------
+    def _save(self) -> None:
+        with self.lock:
+            data = {cid: {"pid": t.pid, "run_dir": t.run_dir} for cid, t in self.tasks.items()}
+        tmp = self.state_path + ".tmp"
+        with open(tmp, "w") as f:
+            json.dump(data, f)
+        os.replace(tmp, self.state_path)
+
+    def reattach(self) -> List[str]:
+        """Tasks of a previous agent life that are still alive.  Their pipes are gone with the old agent, so their
+        remaining output is lost; exits are detected by polling the process group leader."""
+        try:
+            with open(self.state_path) as f:
+                old = json.load(f)
+        except (OSError, ValueError):
+            return []
+        alive = []
+        for cid, rec in old.items():
+            pid = int(rec.get("pid", 0))
+            if pid > 0 and _alive(pid):
+                t = _Task(cid, None, rec.get("run_dir"), pid)
+                self.tasks[cid] = t
+                threading.Thread(target=self._watch_pid, args=(t,), daemon=True, name=f"watch-{cid[:8]}").start()
+                alive.append(cid)
+        self._save()
+        return alive
+
+    def _watch_pid(self, t: _Task) -> None:
+        while _alive(t.pid):
+            time.sleep(0.5)
+        self._done(t, None)
+
+    # -- verbs ---------------------------------------------------------------------------------------
+    def start(self, action: Dict[str, Any], agent_id: str) -> None:
+        cid = str(action["container_id"])
+        try:
+            run_dir = tempfile.mkdtemp(prefix=f"task-{cid[:12]}-", dir=self.work_dir)
+            model_dir = os.path.join(run_dir, "model")
+            info_dir = os.path.join(run_dir, "info")
+            os.makedirs(model_dir, exist_ok=True)
+            os.makedirs(info_dir, exist_ok=True)
+            if action.get("archive"):
+                with tarfile.open(fileobj=io.BytesIO(base64.b64decode(action["archive"])), mode="r:*") as tf:
+                    tf.extractall(model_dir, filter="data")
+            env = dict(os.environ)
+            env.pop("DET_LATEST_CHECKPOINT", None)
+            env.update({str(k): str(v) for k, v in (action.get("env") or {}).items()})
+            slot_ids = [int(s) for s in action.get("slot_ids") or []]
+            env.update({"DET_AGENT_ID": agent_id, "DET_RUN_DIR": run_dir, "DET_INFO_DIR": info_dir, "DET_MODEL_DIR": model_dir,
+                        "DET_SLOT_IDS": json.dumps(slot_ids)})
+            env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in slot_ids)
+            root = str(pathlib.Path(__file__).resolve().parents[2])
+            env["PYTHONPATH"] = os.pathsep.join([model_dir, root] + ([env["PYTHONPATH"]] if env.get("PYTHONPATH") else []))
+            argv = [sys.executable if a == PYTHON_PLACEHOLDER else str(a) for a in action["argv"]]
+            cwd = os.path.join(run_dir, action.get("workdir") or "")
+            proc = subprocess.Popen(argv, cwd=cwd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, start_new_session=True,
+                                    text=True, bufsize=1, errors="replace")
+        except Exception as e:  # noqa: BLE001
+            logger.exception("could not start task %s", cid)
+            self.emit({"type": "start_failed", "container_id": cid, "error": repr(e)})
+            return
+        t = _Task(cid, proc, run_dir, proc.pid)
+        with self.lock:
+            self.tasks[cid] = t
+        self._save()
+        logger.info("task %s started: pid %d, slots %s", cid, proc.pid, slot_ids)
+        threading.Thread(target=self._pump, args=(t,), daemon=True, name=f"task-{cid[:8]}").start()
+
+    def _pump(self, t: _Task) -> None:
+        assert t.proc is not None and t.proc.stdout is not None
+        batch: List[str] = []
+        last = time.time()
+        for line in t.proc.stdout:
+            batch.append(line.rstrip("\n"))
+            if len(batch) >= 100 or time.time() - last > 0.3:
+                self.emit({"type": "log", "container_id": t.cid, "lines": batch})
+                batch, last = [], time.time()
+        if batch:
+            self.emit({"type": "log", "container_id": t.cid, "lines": batch})
+        self._done(t, t.proc.wait())
+
+    def _done(self, t: _Task, code: Optional[int]) -> None:
+        with self.lock:
+            self.tasks.pop(t.cid, None)
+        self._save()
+        if t.run_dir and not os.environ.get("DET_KEEP_RUN_DIRS"):
+            shutil.rmtree(t.run_dir, ignore_errors=True)
+        logger.info("task %s exited with %s", t.cid, code)
+        self.emit({"type": "exit", "container_id": t.cid, "exit_code": code})
+
+    def kill(self, cid: str, sig: str = "TERM") -> None:
+        with self.lock:
+            t = self.tasks.get(cid)
+        if t is None:
+            return
+        _signal_group(t.pid, signal.SIGKILL if sig == "KILL" else signal.SIGTERM)
+        if sig != "KILL" and t.kill_sent is None:
+            t.kill_sent = time.time()
+
+            def hard() -> None:
+                time.sleep(KILL_GRACE_S)
+                if _alive(t.pid):
+                    _signal_group(t.pid, signal.SIGKILL)
+            threading.Thread(target=hard, daemon=True).start()
+
+    def kill_all(self) -> None:
+        for cid in list(self.tasks):
+            self.kill(cid, "KILL")
+
+    def running(self) -> List[str]:
+        with self.lock:
+            return sorted(self.tasks)
+
+
+def _alive(pid: int) -> bool:
+    try:
+        os.kill(pid, 0)
+    except ProcessLookupError:
+        return False
+    except PermissionError:
+        return True
+    # a zombie child of ours still answers signal 0: reap it if it is ours
+    try:
+        done, _ = os.waitpid(pid, os.WNOHANG)
+        return done == 0
+    except ChildProcessError:
+        return True
+
+
+def _signal_group(pid: int, sig: int) -> None:
+    try:
+        os.killpg(pid, sig)
+    except (ProcessLookupError, PermissionError):
+        pass
+
+
+class Agent:
+    def __init__(self, master_url: str, agent_id: Optional[str] = None, slots: Optional[int] = None, slot_type: str = "auto",
+                 resource_pool: str = "default", work_dir: Optional[str] = None, token: Optional[str] = None) -> None:
+        self.master_url = master_url.rstrip("/")
+        self.id = agent_id or socket.gethostname()
+        self.slots = detect_slots(slots, slot_type)
+        self.resource_pool = resource_pool
+        self.token = token or os.environ.get("DET_AGENT_TOKEN")
+        self.work_dir = work_dir or tempfile.mkdtemp(prefix=f"detb200-agent-{self.id}-")
+        os.makedirs(self.work_dir, exist_ok=True)
+        self._events: List[Dict[str, Any]] = []
+        self._ev_lock = threading.Lock()
+        self._stop = threading.Event()
+        self.runtime = ProcessRuntime(self.work_dir, self._emit)
+        self.http = requests.Session()
+        self.poll_timeout = 10.0
+        self.registered = False
+
+    def _emit(self, ev: Dict[str, Any]) -> None:
+        with self._ev_lock:
+            self._events.append(ev)
+
+    def _post(self, path: str, body: Dict[str, Any], timeout: float) -> Dict[str, Any]:
+        if self.token:
+            body = {**body, "token": self.token}
+        r = self.http.post(self.master_url + path, json=body, timeout=timeout)
+        if r.status_code >= 400:
+            raise RuntimeError(f"{path}: HTTP {r.status_code}: {r.text[:200]}")
+        return r.json()
+
+    def register(self) -> Dict[str, Any]:
+        body = {"id": self.id, "slots": self.slots, "resourcePool": self.resource_pool, "version": __version__,
+                "addresses": [_my_address()], "containers": self.runtime.running()}
+        resp = self._post("/api/v1/agents/register", body, 15)
+        self.poll_timeout = float(resp.get("pollTimeoutSeconds", 10))
+        self.registered = True
+        logger.info("registered with %s as %s (%d slots, re-attached: %s)", self.master_url, self.id, len(self.slots), resp.get("reattached"))
+        return resp
+
+    def step(self) -> None:
+        """One poll: ship pending events, execute the actions that come back."""
+        with self._ev_lock:
+            events, self._events = self._events, []
+        try:
+            resp = self._post(f"/api/v1/agents/{self.id}/poll", {"events": events, "timeoutSeconds": 0 if events else self.poll_timeout},
+                              self.poll_timeout + 15)
+        except Exception:
+            with self._ev_lock:                      # keep them for the next attempt
+                self._events = events + self._events
+            raise
+        if resp.get("reregister"):
+            with self._ev_lock:
+                self._events = events + self._events
+            self.register()
+            return
+        for act in resp.get("actions") or []:
+            if act.get("type") == "start":
+                self.runtime.start(act, self.id)
+            elif act.get("type") == "kill":
+                self.runtime.kill(str(act.get("container_id")), str(act.get("signal") or "TERM"))
+
+    def run(self) -> None:
+        self.runtime.reattach()
+        backoff = 0.5
+        while not self._stop.is_set():
+            try:
+                if not self.registered:
+                    self.register()
+                self.step()
+                backoff = 0.5
+            except Exception as e:  # noqa: BLE001
+                if self._stop.is_set():
+                    break
+                logger.warning("master unreachable (%s); retrying in %.1fs", e, backoff)
+                self.registered = False
+                self._stop.wait(backoff)
+                backoff = min(backoff * 2, 10.0)
+
+    def stop(self, kill_tasks: bool = True) -> None:
+        self._stop.set()
+        if kill_tasks:
+            self.runtime.kill_all()
+
+
+def _my_address() -> str:
+    try:
+        return socket.gethostbyname(socket.gethostname())
+    except OSError:
+        return "127.0.0.1"

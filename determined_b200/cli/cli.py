@@ -634,34 +634,30 @@ def _follow_task_logs(sess: api.Session, task_id: str, plural: str, kind: str, f
 
 
 def deploy_local(args: argparse.Namespace) -> int:
-    """``det deploy local cluster-up``: start the single-box master in the foreground or detached
-    (reference ``harness/determined/deploy/local``: docker-compose master+db+agent)."""
-    import subprocess
+    """``det deploy local cluster-up | cluster-down | master-up | master-down | agent-up | agent-down | logs`` (reference
+    ``harness/determined/deploy/local``: docker-compose master+db+agent; here plain daemons with pid files)."""
+    from determined_b200.deploy import local
 
-    cmd = [sys.executable, "-m", "determined_b200.master", "--port", str(args.master_port)]
-    if args.slots is not None:
-        cmd += ["--slots", str(args.slots)]
-    if args.scheduler:
-        cmd += ["--scheduler", args.scheduler]
-    if args.action == "cluster-up":
-        if args.no_detach:
-            return subprocess.call(cmd)
-        log = open(os.path.expanduser("~/.detb200-master.log"), "ab")
-        p = subprocess.Popen(cmd, stdout=log, stderr=log, start_new_session=True)
-        pathlib.Path(os.path.expanduser("~/.detb200-master.pid")).write_text(str(p.pid))
-        print(f"master started (pid {p.pid}) on http://127.0.0.1:{args.master_port}; logs in ~/.detb200-master.log")
+    if args.action in ("cluster-up", "master-up"):
+        pid = local.master_up(port=args.master_port, cluster_name=args.cluster_name, slots=args.slots, scheduler=args.scheduler,
+                              detach=not args.no_detach)
+        if not args.no_detach:
+            print(f"master started (pid {pid}) on http://127.0.0.1:{args.master_port}; `det deploy local logs` shows its output")
         return 0
-    if args.action == "cluster-down":
-        import signal
-
-        pf = pathlib.Path(os.path.expanduser("~/.detb200-master.pid"))
-        if pf.exists():
-            try:
-                os.kill(int(pf.read_text()), signal.SIGTERM)
-                print("master stopped")
-            except ProcessLookupError:
-                print("master was not running")
-            pf.unlink()
+    if args.action in ("cluster-down", "master-down"):
+        print("master stopped" if local.master_down(args.cluster_name, delete_db=args.delete_db) else "master was not running")
+        return 0
+    if args.action == "agent-up":
+        pid = local.agent_up(master_url=args.master or f"http://127.0.0.1:{args.master_port}", agent_name=args.agent_name, slots=args.slots,
+                             slot_type=args.slot_type, detach=not args.no_detach)
+        if not args.no_detach:
+            print(f"agent {args.agent_name} started (pid {pid})")
+        return 0
+    if args.action == "agent-down":
+        print("agent stopped" if local.agent_down(args.agent_name) else "agent was not running")
+        return 0
+    if args.action == "logs":
+        local.logs(args.cluster_name, follow=args.follow)
         return 0
     return 2
 
@@ -948,11 +944,16 @@ def make_parser() -> argparse.ArgumentParser:
 
     dp = sub.add_parser("deploy").add_subparsers(dest="sub")
     lo = dp.add_parser("local")
-    lo.add_argument("action", choices=["cluster-up", "cluster-down"])
+    lo.add_argument("action", choices=["cluster-up", "cluster-down", "master-up", "master-down", "agent-up", "agent-down", "logs"])
     lo.add_argument("--master-port", type=int, default=8080)
-    lo.add_argument("--slots", type=int)
+    lo.add_argument("--cluster-name", default="determined")
+    lo.add_argument("--agent-name", default="determined-agent")
+    lo.add_argument("--slots", type=int, help="master: slots it drives itself (0 = agents only); agent: slots it offers")
+    lo.add_argument("--slot-type", choices=["auto", "cuda", "cpu"], default="auto")
     lo.add_argument("--scheduler", choices=["fair_share", "priority", "round_robin"])
     lo.add_argument("--no-detach", action="store_true")
+    lo.add_argument("--delete-db", action="store_true")
+    lo.add_argument("--follow", "-f", action="store_true")
     lo.set_defaults(fn=deploy_local)
 
     a = sub.add_parser("version")

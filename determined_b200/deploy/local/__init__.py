@@ -1,7 +1,8 @@
 """``det deploy local``: the reference (``harness/determined/deploy/local/cluster_utils.py``) starts
 master + Postgres + agent containers with docker; here the "cluster" is one master process that owns
-the box's GPUs, so cluster-up/master-up start it (detached, pid file under ``~/.local/share``) and
-agent-up/agent-down are accepted no-ops (the master *is* the agent)."""
+the box's GPUs, so cluster-up/master-up start it (detached, pid file under ``~/.local/share``).
+``agent-up`` starts an extra agent daemon (``python -m determined_b200.agent``) that offers more
+slots to a master — ``master-up --slots 0`` plus agents is the reference's master/agent split."""
 import os
 import pathlib
 import signal
@@ -64,12 +65,33 @@ def cluster_down(cluster_name: str = "determined", delete_db: bool = False) -> b
     return master_down(cluster_name, delete_db)
 
 
-def agent_up(*_, **__) -> None:
-    """The single-box master schedules its own GPUs; nothing to start."""
+def agent_up(master_url: str = "http://127.0.0.1:8080", agent_name: str = "determined-agent", slots: Optional[int] = None,
+             slot_type: str = "auto", resource_pool: str = "default", detach: bool = True) -> Optional[int]:
+    """Start an agent daemon (reference ``det deploy local agent-up MASTER_HOST``)."""
+    STATE_DIR.mkdir(parents=True, exist_ok=True)
+    cmd = [sys.executable, "-m", "determined_b200.agent", "--master-url", master_url, "--agent-id", agent_name, "--slot-type", slot_type,
+           "--resource-pool", resource_pool, "--work-dir", str(STATE_DIR / f"agent-{agent_name}")]
+    if slots is not None:
+        cmd += ["--slots", str(slots)]
+    if not detach:
+        return subprocess.call(cmd)
+    log = open(STATE_DIR / f"agent-{agent_name}.log", "ab")
+    p = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, start_new_session=True)
+    _pid_file(f"agent-{agent_name}").write_text(str(p.pid))
+    return p.pid
 
 
-def agent_down(*_, **__) -> None:
-    pass
+def agent_down(agent_name: str = "determined-agent") -> bool:
+    """SIGINT: the agent kills its tasks and exits (SIGTERM would leave them running for re-attachment)."""
+    pf = _pid_file(f"agent-{agent_name}")
+    if not pf.exists():
+        return False
+    try:
+        os.kill(int(pf.read_text()), signal.SIGINT)
+    except ProcessLookupError:
+        pass
+    pf.unlink(missing_ok=True)
+    return True
 
 
 def logs(cluster_name: str = "determined", follow: bool = False) -> None:

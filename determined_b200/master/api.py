@@ -1076,25 +1076,65 @@ def _agent_json(m: core.Master) -> Dict[str, Any]:
             "draining": False, "addresses": ["127.0.0.1"], "version": __version__, "label": ag.label}
 
 
+def _any_agent_json(m: core.Master, agent_id: str) -> Dict[str, Any]:
+    if agent_id == m.agent_id:
+        return _agent_json(m)
+    ra = m.agents.get(agent_id)
+    if ra is None:
+        raise HTTPError(404, "agent not found")
+    j = ra.to_json(m.pool.agents.get(agent_id))
+    j["registeredTime"] = _ts(ra.registered)
+    return j
+
+
 @route("GET", "/api/v1/agents")
 def agents(ctx: Ctx) -> Any:
-    return {"agents": [_agent_json(ctx.m)], "pagination": {"total": 1}}
+    m = ctx.m
+    out = [_agent_json(m)] if m.pool.agents[m.agent_id].num_slots or not m.agents.agents else []
+    out += [_any_agent_json(m, a) for a in sorted(m.agents.agents)]
+    return {"agents": out, "pagination": {"total": len(out)}}
 
 
 @route("GET", "/api/v1/agents/{agent_id}")
 def get_agent(ctx: Ctx, agent_id: str) -> Any:
-    if agent_id != ctx.m.agent_id:
-        raise HTTPError(404, "agent not found")
-    return {"agent": _agent_json(ctx.m)}
+    return {"agent": _any_agent_json(ctx.m, agent_id)}
 
 
 @route("GET", "/api/v1/agents/{agent_id}/slots")
 def get_slots(ctx: Ctx, agent_id: str) -> Any:
-    return {"slots": list(_agent_json(ctx.m)["slots"].values())}
+    return {"slots": list(_any_agent_json(ctx.m, agent_id)["slots"].values())}
+
+
+def _agent_auth(ctx: Ctx) -> None:
+    """Agents are part of the cluster, not users: they present the cluster's agent token if one is configured
+    (``DET_AGENT_TOKEN`` / ``--agent-token``), like the reference's internal agent endpoint they need no login."""
+    import os
+
+    want = getattr(ctx.m, "agent_token", None) or os.environ.get("DET_AGENT_TOKEN")
+    if want and (ctx.body or {}).get("token") != want:
+        raise HTTPError(403, "bad agent token")
+
+
+@route("POST", "/api/v1/agents/register", auth_required=False)
+def agent_register(ctx: Ctx) -> Any:
+    """Agent protocol (reference ``aproto.AgentStarted`` over the agent websocket): announce slots and the tasks still running."""
+    _agent_auth(ctx)
+    try:
+        return ctx.m.agents.register(ctx.body or {})
+    except ValueError as e:
+        raise HTTPError(400, str(e))
+
+
+@route("POST", "/api/v1/agents/{agent_id}/poll", auth_required=False)
+def agent_poll(ctx: Ctx, agent_id: str) -> Any:
+    """Events up (task logs, exits), actions down (start / kill); held open up to ``timeoutSeconds`` when idle."""
+    _agent_auth(ctx)
+    b = ctx.body or {}
+    return ctx.m.agents.poll(agent_id, b, float(b.get("timeoutSeconds", 10)))
 
 
 def _set_enabled(ctx: Ctx, agent_id: str, slot: Optional[str], enabled: bool) -> Any:
-    if agent_id != ctx.m.agent_id:
+    if agent_id not in ctx.m.pool.agents:
         raise HTTPError(404, "agent not found")
     with ctx.m.lock:
         ag = ctx.m.pool.agents[agent_id]
@@ -1118,8 +1158,9 @@ route("POST", "/api/v1/agents/{agent_id}/slots/{slot}/disable")(lambda ctx, agen
 def resource_pools(ctx: Ctx) -> Any:
     p = ctx.m.pool
     ag = p.agents[ctx.m.agent_id]
-    return {"resourcePools": [{"name": p.name, "description": "one 8xB200 node", "type": "RESOURCE_POOL_TYPE_STATIC", "numAgents": 1,
-                               "slotsAvailable": ag.num_slots, "slotsUsed": ag.num_used(), "slotType": "DEVICE_TYPE_CUDA" if ctx.m.num_gpus else "DEVICE_TYPE_CPU",
+    live = [a for a in p.agents.values() if a.enabled and a.num_slots]
+    return {"resourcePools": [{"name": p.name, "description": "one 8xB200 node", "type": "RESOURCE_POOL_TYPE_STATIC", "numAgents": max(len(live), 1),
+                               "slotsAvailable": sum(a.num_slots for a in live), "slotsUsed": sum(a.num_used() for a in p.agents.values()), "slotType": "DEVICE_TYPE_CUDA" if ctx.m.num_gpus else "DEVICE_TYPE_CPU",
                                "defaultComputePool": True, "defaultAuxPool": True, "preemptible": p.preemption, "schedulerType": "SCHEDULER_TYPE_" + p.scheduler.upper(),
                                "schedulerFittingPolicy": "FITTING_POLICY_" + p.policy.upper(), "slotsPerAgent": ag.num_slots, "location": "on-prem", "auxContainerCapacity": 100,
                                "auxContainersRunning": len(ag.zero_slot_tasks)}], "pagination": {"total": 1}}

@@ -77,23 +77,36 @@ class CommandTask:
                 "username": self.owner_name, "userId": self.owner_id, "resourcePool": self.mgr.master.pool.name, "exitStatus": self.exit_code,
                 "jobId": self.id, "type": self.kind, "slots": self.slots, "slotIds": self.slot_ids, "config": self.config}
 
-    def start(self, slot_ids: List[int]) -> None:
+    def start(self, slot_ids: List[int], agent_id: Optional[str] = None) -> None:
         m = self.mgr.master
         self.slot_ids = slot_ids
+        self.agent_id = agent_id or m.agent_id
+        task_env: Dict[str, str] = {}
+        for kv in ((self.config.get("environment") or {}).get("environment_variables") or []):
+            if isinstance(kv, str) and "=" in kv:
+                k, v = kv.split("=", 1)
+                task_env[k] = v
+        task_env.update({"DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port), "DET_CLUSTER_ID": m.cluster_id,
+                         "DET_AGENT_ID": self.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids), "DET_TASK_ID": self.id,
+                         "DET_ALLOCATION_ID": self.id + ".1", "DET_SESSION_TOKEN": self.token, "DET_TASK_TYPE": self.kind,
+                         "DET_USER": self.owner_name, "PYTHONUNBUFFERED": "1"})
+        if m.agents.is_remote(agent_id):
+            from determined_b200.master import agents as agents_mod
+
+            m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)", (self.token, self.owner_id, time.time() + 14 * 86400, self.id))
+            self.state = "RUNNING"
+            m.db.exec("UPDATE tasks SET state=? WHERE id=?", (self.state, self.id))
+            argv = [agents_mod.PYTHON_PLACEHOLDER if a == sys.executable else a for a in self.argv]
+            m.agents.start(self.agent_id, self.id, self, argv, task_env, slot_ids, archive=self.context, workdir="model")
+            return
         self.run_dir = tempfile.mkdtemp(prefix=f"detb200-{self.kind.lower()}-{self.id[:8]}-", dir=m.work_dir)
         if self.context:
             from determined_b200.common import context as det_context
 
             det_context.extract_tarball(self.context, self.run_dir) if hasattr(det_context, "extract_tarball") else None
         env = dict(os.environ)
-        for kv in ((self.config.get("environment") or {}).get("environment_variables") or []):
-            if isinstance(kv, str) and "=" in kv:
-                k, v = kv.split("=", 1)
-                env[k] = v
-        env.update({"DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port), "DET_CLUSTER_ID": m.cluster_id,
-                    "DET_AGENT_ID": m.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids), "DET_TASK_ID": self.id, "DET_ALLOCATION_ID": self.id + ".1",
-                    "DET_SESSION_TOKEN": self.token, "DET_TASK_TYPE": self.kind, "DET_USER": self.owner_name, "PYTHONUNBUFFERED": "1",
-                    "DET_RUN_DIR": self.run_dir})
+        env.update(task_env)
+        env["DET_RUN_DIR"] = self.run_dir
         if slot_ids:
             env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in slot_ids)
         elif m.num_gpus:
@@ -123,6 +136,15 @@ class CommandTask:
         code = self.proc.wait()
         self.finish(code)
 
+    # sink interface of master/agents.py (task running under a remote agent)
+    def on_logs(self, lines: List[str]) -> None:
+        now = time.time()
+        self.mgr.master.db.add_logs([(self.id, self.id + ".1", now, "INFO", None, "stdout", "task", ln if ln.endswith("\n") else ln + "\n") for ln in lines])
+
+    def on_exit(self, code: Optional[int]) -> None:
+        if self.state != "TERMINATED":
+            self.finish(code)
+
     def finish(self, code: Optional[int]) -> None:
         m = self.mgr.master
         self.exit_code, self.end_time, self.state = code, time.time(), "TERMINATED"
@@ -134,6 +156,10 @@ class CommandTask:
 
     def kill(self) -> None:
         self.killed = True
+        m = self.mgr.master
+        if m.agents.is_remote(getattr(self, "agent_id", None)) and self.state == "RUNNING":
+            m.agents.kill(self.agent_id, self.id)
+            return
         if self.proc is not None and self.proc.poll() is None:
             try:
                 os.killpg(self.proc.pid, signal.SIGTERM)
@@ -171,7 +197,7 @@ class CommandManager:
         m.kick()
         return t
 
-    def on_assigned(self, pool_key: str, slot_ids: List[int]) -> bool:
+    def on_assigned(self, pool_key: str, slot_ids: List[int], agent_id: Optional[str] = None) -> bool:
         """Called by the scheduler loop for requests whose id starts with ``cmd-``."""
         t = self.tasks.get(pool_key[4:])
         if t is None or t.state != "QUEUED":
@@ -180,7 +206,7 @@ class CommandManager:
             t.slot_ids, t.state = slot_ids, "RUNNING"
             return True
         try:
-            t.start(slot_ids)
+            t.start(slot_ids, agent_id)
         except Exception as e:
             logger.exception("failed to start %s %s", t.kind, t.id)
             self.master.db.add_logs([(t.id, t.id + ".1", time.time(), "ERROR", None, "stdout", "master", f"failed to start: {e}\n")])

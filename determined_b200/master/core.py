@@ -36,6 +36,7 @@ from typing import Any, Callable, Dict, List, Optional, Tuple
 
 from determined_b200 import constants, gpu, util
 from determined_b200.master import db as dbmod
+from determined_b200.master import agents as agents_mod
 from determined_b200.master import expconf, scheduler
 from determined_b200.master import searcher as S
 
@@ -81,11 +82,37 @@ class Allocation:
         self._threads: List[threading.Thread] = []
 
     # -- lifecycle ---------------------------------------------------------------------------------
-    def start(self, slot_ids: List[int]) -> None:
+    def start(self, slot_ids: List[int], agent_id: Optional[str] = None) -> None:
         m, t = self.master, self.trial
         self.slot_ids = slot_ids
+        self.agent_id = agent_id or m.agent_id
         self.state = "RUNNING"
         exp = t.experiment
+        remote = m.agents.is_remote(agent_id)
+        # what the master decides; the host running the task (this process, or an agent) layers it over its own environment
+        task_env: Dict[str, str] = dict(exp.environment_variables())
+        task_env.update({
+            "DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port),
+            "DET_CLUSTER_ID": m.cluster_id, "DET_AGENT_ID": self.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids),
+            "DET_TASK_ID": t.task_id, "DET_ALLOCATION_ID": self.id, "DET_SESSION_TOKEN": self.token,
+            "DET_TASK_TYPE": "TRIAL", "DET_TRIAL_ID": str(t.id), "DET_EXPERIMENT_ID": str(exp.id),
+            "DET_TRIAL_SEED": str(t.seed), "DET_HPARAMS": util.json_encode(t.hparams),
+            "DET_EXPERIMENT_CONFIG": util.json_encode(exp.config), "DET_STEPS_COMPLETED": str(t.total_batches),
+            "DET_TRIAL_RUN_ID": str(t.run_id), "DET_RESOURCES_ID": f"{self.id}-box", "DET_CONTAINER_ID": self.id,
+            "DET_USER": exp.owner_name, "PYTHONUNBUFFERED": "1",
+        })
+        ckpt = t.latest_checkpoint or t.warm_start_checkpoint
+        if ckpt:
+            task_env["DET_LATEST_CHECKPOINT"] = ckpt
+        m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)",
+                  (self.token, exp.owner_id, time.time() + 14 * 86400, t.task_id))
+        m.db.exec("INSERT INTO allocations(id,task_id,trial_id,state,slots,slot_ids,start_time,resource_pool) VALUES(?,?,?,?,?,?,?,?)",
+                  (self.id, t.task_id, t.id, "RUNNING", self.slots, json.dumps(slot_ids), time.time(), m.pool.name))
+        if remote:
+            row = m.db.one("SELECT model_definition FROM experiments WHERE id=?", (exp.id,))
+            m.agents.start(self.agent_id, self.id, self, [agents_mod.PYTHON_PLACEHOLDER, "-m", "determined_b200.exec.launch"], task_env, slot_ids,
+                           archive=row["model_definition"] if row is not None else None, workdir="model")
+            return
         self.run_dir = tempfile.mkdtemp(prefix=f"detb200-alloc-{self.id[:8]}-", dir=m.work_dir)
         model_dir = os.path.join(self.run_dir, "model")
         os.makedirs(model_dir, exist_ok=True)
@@ -93,33 +120,15 @@ class Allocation:
         info_dir = os.path.join(self.run_dir, "info")
         os.makedirs(info_dir, exist_ok=True)
         env = dict(os.environ)
-        env.update(exp.environment_variables())
-        env.update({
-            "DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port),
-            "DET_CLUSTER_ID": m.cluster_id, "DET_AGENT_ID": m.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids),
-            "DET_TASK_ID": t.task_id, "DET_ALLOCATION_ID": self.id, "DET_SESSION_TOKEN": self.token,
-            "DET_TASK_TYPE": "TRIAL", "DET_TRIAL_ID": str(t.id), "DET_EXPERIMENT_ID": str(exp.id),
-            "DET_TRIAL_SEED": str(t.seed), "DET_HPARAMS": util.json_encode(t.hparams),
-            "DET_EXPERIMENT_CONFIG": util.json_encode(exp.config), "DET_STEPS_COMPLETED": str(t.total_batches),
-            "DET_TRIAL_RUN_ID": str(t.run_id), "DET_RESOURCES_ID": f"{self.id}-box", "DET_CONTAINER_ID": self.id,
-            "DET_RUN_DIR": self.run_dir, "DET_INFO_DIR": info_dir, "DET_MODEL_DIR": model_dir,
-            "DET_USER": exp.owner_name, "PYTHONUNBUFFERED": "1",
-        })
-        ckpt = t.latest_checkpoint or t.warm_start_checkpoint
-        if ckpt:
-            env["DET_LATEST_CHECKPOINT"] = ckpt
-        else:
-            env.pop("DET_LATEST_CHECKPOINT", None)
+        env.pop("DET_LATEST_CHECKPOINT", None)
+        env.update(task_env)
+        env.update({"DET_RUN_DIR": self.run_dir, "DET_INFO_DIR": info_dir, "DET_MODEL_DIR": model_dir})
         if slot_ids:
             env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in slot_ids)
         elif m.num_gpus:
             env["CUDA_VISIBLE_DEVICES"] = ""
         root = str(pathlib.Path(__file__).resolve().parents[2])
         env["PYTHONPATH"] = os.pathsep.join([model_dir, root] + ([env["PYTHONPATH"]] if env.get("PYTHONPATH") else []))
-        m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)",
-                  (self.token, exp.owner_id, time.time() + 14 * 86400, t.task_id))
-        m.db.exec("INSERT INTO allocations(id,task_id,trial_id,state,slots,slot_ids,start_time,resource_pool) VALUES(?,?,?,?,?,?,?,?)",
-                  (self.id, t.task_id, t.id, "RUNNING", self.slots, json.dumps(slot_ids), time.time(), m.pool.name))
         cmd = [sys.executable, "-m", "determined_b200.exec.launch"]
         self.proc = subprocess.Popen(cmd, cwd=model_dir, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                                      start_new_session=True, text=True, bufsize=1, errors="replace")
@@ -130,11 +139,9 @@ class Allocation:
         th.start()
         self._threads.append(th)
 
-    def _pump_logs(self) -> None:
-        assert self.proc is not None and self.proc.stdout is not None
-        batch: List[Tuple[Any, ...]] = []
-        last = time.time()
-        for line in self.proc.stdout:
+    def _log_rows(self, lines: List[str]) -> List[Tuple[Any, ...]]:
+        rows: List[Tuple[Any, ...]] = []
+        for line in lines:
             rank = None
             txt = line.rstrip("\n")
             if txt.startswith("[rank="):
@@ -149,8 +156,16 @@ class Allocation:
                 if txt.startswith(lv + ":"):
                     level = lv
                     break
-            batch.append((self.trial.task_id, self.id, time.time(), level, rank, "stdout", "task", txt + "\n"))
+            rows.append((self.trial.task_id, self.id, time.time(), level, rank, "stdout", "task", txt + "\n"))
             self.master.log_policies(self.trial, txt)
+        return rows
+
+    def _pump_logs(self) -> None:
+        assert self.proc is not None and self.proc.stdout is not None
+        batch: List[Tuple[Any, ...]] = []
+        last = time.time()
+        for line in self.proc.stdout:
+            batch.extend(self._log_rows([line]))
             if len(batch) >= 200 or time.time() - last > 0.5:
                 self.master.db.add_logs(batch)
                 batch, last = [], time.time()
@@ -162,6 +177,19 @@ class Allocation:
         code = self.proc.wait()
         for th in self._threads[:1]:
             th.join(timeout=5)
+        self._finish(code)
+
+    # sink interface of master/agents.py: the same two things, reported by a remote agent
+    def on_logs(self, lines: List[str]) -> None:
+        rows = self._log_rows(lines)
+        if rows:
+            self.master.db.add_logs(rows)
+
+    def on_exit(self, code: Optional[int]) -> None:
+        if self.state != "TERMINATED":
+            self._finish(code if code is not None else 137)
+
+    def _finish(self, code: int) -> None:
         self.exit_code = code
         self.state = "TERMINATED"
         self.master.db.exec("UPDATE allocations SET state='TERMINATED', end_time=?, exit_code=?, exit_reason=? WHERE id=?",
@@ -184,6 +212,10 @@ class Allocation:
 
     def kill(self) -> None:
         self.killed = True
+        if self.master.agents.is_remote(getattr(self, "agent_id", None)):
+            if self.state == "RUNNING":
+                self.master.agents.kill(self.agent_id, self.id)        # the agent escalates to SIGKILL itself
+            return
         if self.proc is not None and self.proc.poll() is None:
             try:
                 os.killpg(self.proc.pid, signal.SIGTERM)
@@ -519,7 +551,8 @@ class Master:
         n = num_slots if num_slots is not None else (len(gpus) or 1)
         self.slot_type = "cuda" if (self.num_gpus and num_slots is None) else "cpu"
         self.pool = scheduler.ResourcePool("default", scheduler_type, fitting_policy, preemption)
-        self.pool.add_agent(scheduler.Agent(self.agent_id, n))
+        self.pool.add_agent(scheduler.Agent(self.agent_id, n))      # num_slots=0: every slot comes from remote agents
+        self.agents = agents_mod.AgentRegistry(self)
         self.work_dir = work_dir or tempfile.mkdtemp(prefix="detb200-master-")
         os.makedirs(self.work_dir, exist_ok=True)
         self.cluster_defaults = cluster_defaults or {}
@@ -606,9 +639,9 @@ class Master:
         if (cfg.get("reproducibility") or {}).get("experiment_seed") is None:
             cfg.setdefault("reproducibility", {})["experiment_seed"] = int(time.time()) & 0x7FFFFFFF
         slots = int((cfg.get("resources") or {}).get("slots_per_trial", 1))
-        cap = sum(a.num_slots for a in self.pool.agents.values())
-        if slots > cap:
-            raise expconf.ConfigError([f"<config>.resources.slots_per_trial: {slots} exceeds the {cap} slots of this box"])
+        cap = max((a.num_slots for a in self.pool.agents.values()), default=0)      # a trial runs on one agent
+        if cap and slots > cap:           # no slots at all yet (agents still connecting): queue it
+            raise expconf.ConfigError([f"<config>.resources.slots_per_trial: {slots} exceeds the {cap} slots of the largest agent"])
         S.new_search_method(cfg["searcher"])     # fail early on impossible searcher configs
         if validate_only:
             return None, cfg
@@ -683,10 +716,18 @@ class Master:
                                 submit_time=time.time()))
                     elif rid in self.pool.pending:
                         self.pool.release(rid)
+            self.agents.reap()
             d = self.pool.tick()
             for req, asg in d.to_allocate:
+                # a task runs on one host: the (single-node) launch layer has no cross-agent rendezvous
+                hosts = [a for a, sl in asg.items() if sl] or list(asg)[:1]
+                agent_id = hosts[0] if hosts else self.agent_id
+                if len(hosts) > 1:
+                    logger.error("request %s was spread over agents %s; only single-agent placements can run", req.allocation_id, hosts)
+                    self.pool.release(req.allocation_id)
+                    continue
                 if req.allocation_id.startswith("cmd-"):          # command / shell / notebook / tensorboard task
-                    if not self.commands.on_assigned(req.allocation_id, sorted(s for slots in asg.values() for s in slots)):
+                    if not self.commands.on_assigned(req.allocation_id, sorted(s for slots in asg.values() for s in slots), agent_id):
                         self.pool.release(req.allocation_id)
                     continue
                 tid = int(req.allocation_id.split("-")[1])
@@ -701,7 +742,7 @@ class Master:
                 slot_ids = sorted(s for slots in asg.values() for s in slots)
                 if self.launch_enabled:
                     try:
-                        alloc.start(slot_ids)
+                        alloc.start(slot_ids, agent_id)
                     except Exception:
                         logger.exception("failed to start allocation %s", alloc.id)
                         alloc.exit_code = 1
