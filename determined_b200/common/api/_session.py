@@ -47,6 +47,11 @@ class BaseSession:
         h = {"Content-Type": "application/json"}
         if self.token:
             h["Authorization"] = f"Bearer {self.token}"
+        from determined_b200.common import tracing
+
+        tp = tracing.current_traceparent()
+        if tp:
+            h["traceparent"] = tp       # the master's span for this request becomes a child of the caller's
         if extra:
             h.update(extra)
         return h

@@ -21,6 +21,8 @@ def main(argv=None) -> int:
     ap.add_argument("--scheduler", choices=["fair_share", "priority", "round_robin"], default=None)
     ap.add_argument("--fitting-policy", choices=["best", "worst"], default=None)
     ap.add_argument("--slots", type=int, default=None, help="override detected slot count (CPU testing)")
+    ap.add_argument("--agent-token", default=None, help="shared secret agents must present (default: $DET_AGENT_TOKEN, none)")
+    ap.add_argument("--otel-endpoint", default=None, help="OTLP/HTTP collector (or file://path) for request traces; config: telemetry.otel_endpoint")
     ap.add_argument("--log-level", default="INFO")
     args = ap.parse_args(argv)
     logging.basicConfig(level=getattr(logging, args.log_level.upper()), format="%(asctime)s %(levelname)s: %(name)s: %(message)s")
@@ -40,6 +42,13 @@ def main(argv=None) -> int:
                     fitting_policy=args.fitting_policy or sch.get("fitting_policy", "best"),
                     preemption=bool((sch.get("preemption") or {}).get("enabled", True)), num_slots=args.slots,
                     cluster_defaults=defaults)
+    m.agent_token = args.agent_token or (cfg.get("security") or {}).get("agent_token")
+    tel = cfg.get("telemetry") or {}
+    otel = args.otel_endpoint or (tel.get("otel_endpoint") if tel.get("otel_enabled", True) else None)
+    if otel:
+        from determined_b200.common import tracing
+
+        tracing.configure("determined-master", otel)
     srv = api.APIServer(m, host, port).start()
     m.start()
     logging.getLogger("determined.master").info("master %s listening on %s (%d slots, scheduler=%s)", m.cluster_id, m.url,

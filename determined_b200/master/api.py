@@ -23,6 +23,7 @@ from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 from typing import Any, Callable, Dict, List, Optional, Tuple
 
 from determined_b200 import __version__
+from determined_b200.common import tracing
 from determined_b200.common.api import authentication as auth
 from determined_b200.master import core, db as dbmod, expconf
 from determined_b200.master import searcher as S
@@ -1664,6 +1665,9 @@ class Handler(BaseHTTPRequestHandler):
                 body = json.loads(raw)
             except ValueError:
                 body = raw.decode(errors="replace")
+        if path.startswith("/proxy/"):
+            self._proxy(method, path, u.query, raw)
+            return
         for meth, rx, fn, need_auth in ROUTES:
             if meth != method:
                 continue
@@ -1676,7 +1680,8 @@ class Handler(BaseHTTPRequestHandler):
                 return
             ctx = Ctx(self.master, user, urllib.parse.parse_qs(u.query), body, raw)
             try:
-                out = fn(ctx, **{k: urllib.parse.unquote(v) for k, v in mt.groupdict().items()})
+                with tracing.span(f"{method} {rx.pattern[1:-3]}", traceparent=self.headers.get("traceparent"), **{"http.method": method, "http.target": path}):
+                    out = fn(ctx, **{k: urllib.parse.unquote(v) for k, v in mt.groupdict().items()})
                 if isinstance(out, tuple):
                     self._send(200, out[1], out[0])
                 else:
@@ -1692,6 +1697,51 @@ class Handler(BaseHTTPRequestHandler):
                 self._send(500, {"error": {"code": 13, "message": f"{type(e).__name__}: {e}"}, "message": f"{type(e).__name__}: {e}"})
             return
         self._send(404, {"error": {"code": 5, "message": f"no route for {method} {path}"}, "message": f"no route for {method} {path}"})
+
+    def _proxy(self, method: str, path: str, query: str, raw: bytes) -> None:
+        """``/proxy/<task id>/<rest>``: reverse proxy to the HTTP service of a running task (tensorboard, notebook, a command
+        with ``proxy_ports``) at the port the master's registry gave it.  Reference ``master/internal/proxy``: there the
+        task registers its address; here the master chose host and port itself, so there is nothing to trust.  Plain HTTP
+        request/response only (no websocket upgrade)."""
+        import http.client
+
+        parts = path.split("/", 3)
+        task_id = parts[2] if len(parts) > 2 else ""
+        rest = "/" + (parts[3] if len(parts) > 3 else "")
+        qs = urllib.parse.parse_qs(query)
+        user = self._user()
+        if user is None and qs.get("token"):
+            r = self.master.db.one("SELECT user_id FROM sessions WHERE token=? AND expiry>?", (qs["token"][0], time.time()))
+            user = {"id": r["user_id"]} if r is not None else None
+        if user is None:
+            self._send(401, {"message": "unauthenticated"})
+            return
+        t = self.master.commands.tasks.get(task_id)
+        if t is None or t.state != "RUNNING" or not t.service_port:
+            self._send(404, {"message": f"task {task_id} has no running service"})
+            return
+        fwd_q = urllib.parse.urlencode([(k, v) for k, vs in qs.items() if k != "token" for v in vs])
+        hdrs = {k: v for k, v in self.headers.items() if k.lower() not in ("host", "authorization", "connection", "content-length")}
+        hdrs["X-Forwarded-Prefix"] = f"/proxy/{task_id}"
+        try:
+            conn = http.client.HTTPConnection(t.service_host, t.service_port, timeout=30)
+            conn.request(method, rest + ("?" + fwd_q if fwd_q else ""), body=raw or None, headers=hdrs)
+            resp = conn.getresponse()
+            data = resp.read()
+        except OSError as e:
+            self._send(502, {"message": f"service of task {task_id} is not answering: {e}"})
+            return
+        self.send_response(resp.status)
+        for k, v in resp.getheaders():
+            if k.lower() not in ("transfer-encoding", "connection", "content-length"):
+                self.send_header(k, v)
+        self.send_header("Content-Length", str(len(data)))
+        self.end_headers()
+        try:
+            self.wfile.write(data)
+        except (BrokenPipeError, ConnectionResetError):
+            pass
+        conn.close()
 
     def do_GET(self) -> None:
         self._dispatch("GET")

@@ -67,6 +67,9 @@ class CommandTask:
             ep = default_entrypoint(kind, body)
         self.argv: List[str] = ep if isinstance(ep, list) else ["/bin/bash", "-lc", str(ep)]
         self.run_dir: Optional[str] = None
+        # tasks that serve HTTP get a port from the master's registry and are reachable through /proxy/<task id>/
+        self.service_port: Optional[int] = None
+        self.service_host = "127.0.0.1"
 
     @property
     def pool_key(self) -> str:
@@ -75,13 +78,22 @@ class CommandTask:
     def to_json(self) -> Dict[str, Any]:
         return {"id": self.id, "description": self.description, "state": "STATE_" + self.state, "startTime": self.start_time, "endTime": self.end_time,
                 "username": self.owner_name, "userId": self.owner_id, "resourcePool": self.mgr.master.pool.name, "exitStatus": self.exit_code,
-                "jobId": self.id, "type": self.kind, "slots": self.slots, "slotIds": self.slot_ids, "config": self.config}
+                "jobId": self.id, "type": self.kind, "slots": self.slots, "slotIds": self.slot_ids, "config": self.config,
+                "serviceAddress": f"/proxy/{self.id}/" if self.service_port else None}
 
     def start(self, slot_ids: List[int], agent_id: Optional[str] = None) -> None:
         m = self.mgr.master
         self.slot_ids = slot_ids
         self.agent_id = agent_id or m.agent_id
         task_env: Dict[str, str] = {}
+        if self.kind in ("TENSORBOARD", "NOTEBOOK") or (self.config.get("proxy_ports") or self.config.get("service")):
+            self.service_port = m.ports.acquire()
+            ra = m.agents.get(self.agent_id)
+            if ra is not None and ra.addresses:
+                self.service_host = ra.addresses[0]
+            task_env["DET_SERVICE_PORT"] = str(self.service_port)
+            if self.kind == "TENSORBOARD" and "--port" not in self.argv:
+                self.argv = self.argv + ["--port", str(self.service_port)]
         for kv in ((self.config.get("environment") or {}).get("environment_variables") or []):
             if isinstance(kv, str) and "=" in kv:
                 k, v = kv.split("=", 1)
@@ -150,6 +162,7 @@ class CommandTask:
         self.exit_code, self.end_time, self.state = code, time.time(), "TERMINATED"
         m.db.exec("UPDATE tasks SET state=?, end_time=? WHERE id=?", (self.state, self.end_time, self.id))
         m.db.exec("DELETE FROM sessions WHERE token=?", (self.token,))
+        m.ports.release(self.service_port)
         with m.lock:
             m.pool.release(self.pool_key)
         m.kick()

@@ -553,6 +553,9 @@ class Master:
         self.pool = scheduler.ResourcePool("default", scheduler_type, fitting_policy, preemption)
         self.pool.add_agent(scheduler.Agent(self.agent_id, n))      # num_slots=0: every slot comes from remote agents
         self.agents = agents_mod.AgentRegistry(self)
+        from determined_b200.master import portregistry
+
+        self.ports = portregistry.PortRegistry()
         self.work_dir = work_dir or tempfile.mkdtemp(prefix="detb200-master-")
         os.makedirs(self.work_dir, exist_ok=True)
         self.cluster_defaults = cluster_defaults or {}

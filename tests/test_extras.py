@@ -2,6 +2,8 @@
 batch inference, and the legacy workload sequencer."""
 import json
 import pathlib
+import sys
+import time
 import types
 import uuid
 
@@ -360,3 +362,69 @@ def test_execution_helpers(tmp_path):
     with pytest.raises(BaseException, match="SystemExit"):
         with ex._local_execution_manager(tmp_path):
             raise SystemExit(1)
+
+
+def test_task_proxy_and_port_registry(cluster):
+    """A task that serves HTTP gets a port from the registry and is reachable through /proxy/<task id>/ (reference
+    master/internal/proxy + portregistry)."""
+    import requests as rq
+
+    from determined_b200.master import portregistry
+
+    reg = portregistry.PortRegistry(23500, 23510)
+    a, b = reg.acquire(), reg.acquire()
+    assert a != b and reg.in_use() == {a, b}
+    reg.release(a)
+    assert reg.in_use() == {b}
+
+    m, sess = cluster[0], cluster[1]
+    (pathlib.Path(m.work_dir)).mkdir(parents=True, exist_ok=True)
+    serve = "import http.server,os;os.makedirs('pub',exist_ok=True);open('pub/hello.txt','w').write('hi from task');os.chdir('pub');" \
+            "http.server.ThreadingHTTPServer(('127.0.0.1',int(os.environ['DET_SERVICE_PORT'])),http.server.SimpleHTTPRequestHandler).serve_forever()"
+    cmd = sess.post("/api/v1/commands", json={"config": {"entrypoint": [sys.executable, "-c", serve], "proxy_ports": True}}).json()["command"]
+    url = None
+    for _ in range(100):
+        c = sess.get(f"/api/v1/commands/{cmd['id']}").json()["command"]
+        if c["state"] == "STATE_RUNNING" and c.get("serviceAddress"):
+            url = m.url + c["serviceAddress"]
+            r = rq.get(url + "hello.txt", headers={"Authorization": f"Bearer {sess.token}"}, timeout=5)
+            if r.status_code == 200:
+                break
+        time.sleep(0.2)
+    assert url is not None and r.status_code == 200 and r.text == "hi from task", (r.status_code, r.text)
+    assert rq.get(url + "hello.txt", timeout=5).status_code == 401                      # the proxy is behind the master's auth
+    assert rq.get(url + "hello.txt", params={"token": sess.token}, timeout=5).status_code == 200
+    assert rq.get(m.url + "/proxy/nope/x", headers={"Authorization": f"Bearer {sess.token}"}, timeout=5).status_code == 404
+    sess.post(f"/api/v1/commands/{cmd['id']}/kill")
+    for _ in range(100):
+        if sess.get(f"/api/v1/commands/{cmd['id']}").json()["command"]["state"] == "STATE_TERMINATED":
+            break
+        time.sleep(0.1)
+    assert m.ports.in_use() == set()
+
+
+def test_tracing_spans_nest_and_export_otlp(cluster, tmp_path):
+    """Request spans of the master are children of the caller's span (W3C traceparent) and land in an OTLP JSON export."""
+    from determined_b200.common import tracing
+
+    out = tmp_path / "traces.jsonl"
+    assert not tracing.enabled()
+    with tracing.span("noop") as s0:          # disabled: no-op
+        assert s0 is None
+    tr = tracing.configure("test-service", f"file://{out}", flush_s=60)
+    try:
+        m, sess = cluster[0], cluster[1]
+        with tracing.span("client.list", purpose="test") as root:
+            sess.get("/api/v1/experiments")
+            with pytest.raises(ValueError):
+                with tracing.span("failing"):
+                    raise ValueError("boom")
+        tr.flush()
+    finally:
+        tracing.shutdown()
+    spans = [s for line in out.read_text().splitlines() for rs in json.loads(line)["resourceSpans"] for ss in rs["scopeSpans"] for s in ss["spans"]]
+    by = {s["name"]: s for s in spans}
+    assert {"client.list", "failing", "GET /api/v1/experiments"} <= set(by)
+    assert by["GET /api/v1/experiments"]["traceId"] == root.trace_id and by["GET /api/v1/experiments"]["parentSpanId"] == root.span_id
+    assert by["failing"]["status"]["code"] == 2 and by["failing"]["parentSpanId"] == root.span_id
+    assert {"key": "purpose", "value": {"stringValue": "test"}} in by["client.list"]["attributes"]
