@@ -1619,6 +1619,15 @@ def prometheus(ctx: Ctx) -> Any:
 # ---------------------------------------------------------------------------------------------
 # server
 # ---------------------------------------------------------------------------------------------
+@route("GET", "/api/v1/openapi.json", auth_required=False)
+@route("GET", "/api/v1/swagger.json", auth_required=False)
+def openapi_doc(ctx: Ctx) -> Any:
+    """Machine-readable description of every route (feeds the binding generator)."""
+    from determined_b200.master import openapi
+
+    return openapi.build(ROUTES)
+
+
 class Handler(BaseHTTPRequestHandler):
     protocol_version = "HTTP/1.1"
     master: core.Master = None  # type: ignore

@@ -177,3 +177,18 @@ def test_groups_and_role_assignments(cluster):
     rc, out = run("user-group", "list", "--json")
     assert json.loads(out)[0]["# Members"] == 0
     assert run("-u", "admin", "user-group", "delete", "research")[0] == 0
+
+
+def test_generated_bindings_are_fresh_and_work(cluster):
+    """The committed bindings match the route table, and calling through them hits the master."""
+    from determined_b200.common.api import bindings, generate_bindings
+
+    assert generate_bindings.main(["--check"]) == 0
+    from determined_b200.common import api
+
+    sess = api.authentication.login(cluster[0].url, "determined", "")
+    doc = bindings.get_openapi_json(sess)
+    assert "/api/v1/experiments/{eid}" in doc["paths"] or any(p.startswith("/api/v1/experiments/{") for p in doc["paths"])
+    assert "agents" in bindings.get_agents(sess)
+    w = bindings.post_workspaces(sess, body={"name": "bindings-ws"})["workspace"]
+    assert bindings.get_workspaces_by_wid(sess, wid=w["id"])["workspace"]["name"] == "bindings-ws"
