@@ -1619,6 +1619,16 @@ def prometheus(ctx: Ctx) -> Any:
 # ---------------------------------------------------------------------------------------------
 # server
 # ---------------------------------------------------------------------------------------------
+@route("GET", "/", auth_required=False)
+@route("GET", "/det", auth_required=False)
+@route("GET", "/index.html", auth_required=False)
+def webui(ctx: Ctx) -> Any:
+    """The dashboard: one static page that talks to this API (reference ``webui/react``)."""
+    import pathlib
+
+    return "text/html; charset=utf-8", (pathlib.Path(__file__).parent / "static" / "index.html").read_bytes()
+
+
 @route("GET", "/api/v1/openapi.json", auth_required=False)
 @route("GET", "/api/v1/swagger.json", auth_required=False)
 def openapi_doc(ctx: Ctx) -> Any:

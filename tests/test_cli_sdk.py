@@ -192,3 +192,22 @@ def test_generated_bindings_are_fresh_and_work(cluster):
     assert "agents" in bindings.get_agents(sess)
     w = bindings.post_workspaces(sess, body={"name": "bindings-ws"})["workspace"]
     assert bindings.get_workspaces_by_wid(sess, wid=w["id"])["workspace"]["name"] == "bindings-ws"
+
+
+def test_webui_is_served_and_its_api_calls_exist(cluster):
+    """The dashboard page is served at / and every API path it fetches is a real route."""
+    import re
+
+    import requests
+
+    from determined_b200.master import api as mapi_
+
+    m = cluster[0]
+    r = requests.get(m.url + "/", timeout=5)
+    assert r.status_code == 200 and "text/html" in r.headers["Content-Type"] and "determined_b200" in r.text
+    paths = set(re.findall(r"[\"`](/api/v1/[A-Za-z0-9_\-/${}.]*)", r.text))
+    assert len(paths) >= 12
+    for p in paths:
+        concrete = p.replace("${kind}", "commands").replace("${b.dataset.k}", "commands").replace("${b.dataset.a}", "pause")
+        concrete = re.sub(r"\$\{[^}]*\}", "1", concrete).split("?")[0]
+        assert any(rx.match(concrete) for _, rx, _, _ in mapi_.ROUTES), p
