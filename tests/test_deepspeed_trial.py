@@ -137,3 +137,65 @@ def test_mpu_from_pipeline_grid():
     assert (mid.should_build_data_loader, mid.should_report_metrics) == (False, False)
     assert (last.should_build_data_loader, last.should_report_metrics) == (True, True)
     assert last.data_parallel_world_size == 2
+
+
+class Stage3Trial(LinearDSTrial):
+    """Same trial surface, a model with one weight the stage-3 pass partitions (host twin of the fused kernels on CPU)."""
+
+    def __init__(self, context):
+        from determined_b200.ops import gemm as G
+
+        self.context = context
+        cfg = {"train_micro_batch_size_per_gpu": 4, "gradient_accumulation_steps": 1,
+               "optimizer": {"type": "AdamW", "params": {"lr": 0.01, "weight_decay": 0.0}},
+               "zero_optimization": {"stage": 3, "partition_parameters": True, "stage3_param_persistence_threshold": 1}}
+        torch.manual_seed(3)
+
+        class Float(torch.nn.Module):          # the fused layer computes in bf16; the plain layers around it are fp32 on CPU
+            def forward(self, x):
+                return x.float()
+
+        model = torch.nn.Sequential(torch.nn.Linear(1, 64), G.FusedLinear(64, 256, activation="relu"), Float(), torch.nn.Linear(256, 1))
+        engine, _, _, _ = zero.initialize(model=model, config=cfg)
+        self.engine = context.wrap_model_engine(engine)
+        self.calls = 0
+
+    def train_batch(self, it, epoch_idx, batch_idx):
+        x, y = self.context.to_device(next(it))
+        loss = torch.nn.functional.mse_loss(self.engine(x).float(), y)
+        self.engine.backward(loss)
+        self.engine.step()
+        self.calls += 1
+        return {"loss": loss}
+
+    def evaluate_batch(self, it, batch_idx):
+        x, y = self.context.to_device(next(it))
+        return {"val_loss": torch.nn.functional.mse_loss(self.engine(x).float(), y)}
+
+
+def test_deepspeed_trial_stage3_checkpoint_holds_full_weights_and_resumes(tmp_path, monkeypatch):
+    from determined_b200.ops import gemm_comm
+
+    monkeypatch.chdir(tmp_path)
+    store = tmp_path / "ck"
+    store.mkdir()
+
+    def run(max_batches, latest=None):
+        with det_ds.init(hparams={}, exp_conf={}, require_gpu=False) as ctx:
+            from determined_b200.common import storage
+
+            ctx._core.checkpoint._storage_manager = storage.SharedFSStorageManager(str(store))
+            trial = Stage3Trial(ctx)
+            det_ds.Trainer(trial, ctx).fit(max_length=pytorch.Batch(max_batches), checkpoint_policy="all", latest_checkpoint=latest)
+            return trial
+
+    t = run(3)
+    assert t.engine.partitioned == 1 and isinstance(t.engine.module[1], gemm_comm.Zero3Linear)
+    ck = sorted(store.iterdir(), key=lambda p: p.stat().st_mtime)[-1]
+    ms = torch.load(ck / "model0" / "mp_rank_00_model_states.pt", weights_only=False)
+    assert ms["module"]["1.weight"].shape == (256, 64) and "1.weight_shard" not in ms["module"]      # the unpartitioned state dict
+    t2 = run(5, latest=ck.name)
+    ref = run(5)
+    assert t2.engine.global_steps == 5
+    for a, b in zip(t2.engine.module.parameters(), ref.engine.module.parameters()):
+        torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
