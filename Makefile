@@ -1,0 +1,31 @@
+# Developer entry points (reference: top-level Makefile + tools/devcluster + .circleci).
+PY ?= python
+
+.PHONY: build test test-gpu bench bindings check devcluster clean
+
+build:            ## compile the native library for sm_100a (nvcc cross-compiles without a GPU)
+	$(PY) -c "import __graft_entry__ as g; g.build()"
+
+test:             ## CPU suite (multi-process paths run over gloo)
+	$(PY) -m pytest tests/ -x -q -m "not gpu"
+
+test-gpu:         ## needs a B200
+	$(PY) -m pytest tests/ -x -q -m gpu
+
+bench:            ## headline benchmark, one GPU
+	$(PY) bench.py --gpus 1 --steps 100 --warmup 10
+
+bindings:         ## regenerate common/api/bindings.py from the master's route table
+	$(PY) -m determined_b200.common.api.generate_bindings
+
+check: bindings   ## what CI runs before the tests
+	git diff --exit-code determined_b200/common/api/bindings.py
+	$(PY) -m compileall -q determined_b200 tests benchmarks examples bench.py __graft_entry__.py
+
+devcluster:       ## a master without own slots plus one agent, in the foreground of two background daemons
+	$(PY) -m determined_b200.cli deploy local master-up --slots 0
+	$(PY) -m determined_b200.cli deploy local agent-up
+	@echo "dashboard: http://127.0.0.1:8080/   stop with: det deploy local agent-down && det deploy local master-down"
+
+clean:
+	rm -rf build determined_b200/_native/*.so determined_b200/_native/*.o .pytest_cache
