@@ -1608,11 +1608,24 @@ def stream(ctx: Ctx) -> Any:
 @route("GET", "/prom/det-state-metrics", auth_required=False)
 def prometheus(ctx: Ctx) -> Any:
     """Prometheus text exposition (reference ``master/internal/prom``)."""
-    ag = ctx.m.pool.agents[ctx.m.agent_id]
-    lines = ["# TYPE det_slots_total gauge", f"det_slots_total {ag.num_slots}", "# TYPE det_slots_used gauge", f"det_slots_used {ag.num_used()}",
-             "# TYPE det_allocations_running gauge", f"det_allocations_running {len(ctx.m.allocations)}",
-             "# TYPE det_experiments_active gauge", f"det_experiments_active {sum(1 for e in ctx.m.experiments.values() if e.state == core.ACTIVE)}",
-             "# TYPE det_pending_requests gauge", f"det_pending_requests {len(ctx.m.pool.pending)}"]
+    m = ctx.m
+    lines = ["# TYPE det_slots_total gauge", "# TYPE det_slots_used gauge", "# TYPE det_agent_connected gauge"]
+    for aid, ag in sorted(m.pool.agents.items()):
+        if aid == m.agent_id and not ag.num_slots:
+            continue
+        ra = m.agents.get(aid)
+        lines += [f'det_slots_total{{agent="{aid}"}} {ag.num_slots}', f'det_slots_used{{agent="{aid}"}} {ag.num_used()}',
+                  f'det_agent_connected{{agent="{aid}"}} {int(ra.connected) if ra is not None else 1}']
+    lines += ["# TYPE det_allocations_running gauge", f"det_allocations_running {len(m.allocations)}",
+              "# TYPE det_pending_requests gauge", f"det_pending_requests {len(m.pool.pending)}", "# TYPE det_experiments gauge"]
+    by_state: Dict[str, int] = {}
+    for e in m.experiments.values():
+        by_state[e.state] = by_state.get(e.state, 0) + 1
+    by_state.setdefault(core.ACTIVE, 0)
+    lines += [f'det_experiments{{state="{k}"}} {v}' for k, v in sorted(by_state.items())]
+    lines += ["# TYPE det_experiments_active gauge", f"det_experiments_active {by_state[core.ACTIVE]}",
+              "# TYPE det_tasks_running gauge", f"det_tasks_running {sum(1 for t in m.commands.tasks.values() if t.state == 'RUNNING')}",
+              "# TYPE det_master_uptime_seconds counter", f"det_master_uptime_seconds {time.time() - m.start_time:.0f}"]
     return ("text/plain; version=0.0.4", "\n".join(lines) + "\n")
 
 

@@ -211,3 +211,11 @@ def test_webui_is_served_and_its_api_calls_exist(cluster):
         concrete = p.replace("${kind}", "commands").replace("${b.dataset.k}", "commands").replace("${b.dataset.a}", "pause")
         concrete = re.sub(r"\$\{[^}]*\}", "1", concrete).split("?")[0]
         assert any(rx.match(concrete) for _, rx, _, _ in mapi_.ROUTES), p
+
+
+def test_prometheus_endpoint(cluster):
+    import requests
+
+    m = cluster[0]
+    txt = requests.get(m.url + "/prom/det-state-metrics", timeout=5).text
+    assert f'det_slots_total{{agent="{m.agent_id}"}} 8' in txt and "det_experiments_active 0" in txt and "det_master_uptime_seconds" in txt
