@@ -25,6 +25,8 @@ def _run_pytorch_trial(trial_class: Type[Any], info: det.ClusterInfo) -> int:
             logging.getLogger().setLevel(logging.WARNING)
         if (cfg.get("optimizations") or {}).get("cuda_graphs"):
             ctx.experimental.enable_cuda_graphs(True)
+        if (cfg.get("optimizations") or {}).get("async_checkpoint"):
+            ctx.experimental.enable_async_checkpoint(True)
         trial = trial_class(ctx)
         gbs = ctx._global_batch_size
         def unit(d: Any) -> pytorch.TrainUnit:

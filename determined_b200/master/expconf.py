@@ -88,7 +88,7 @@ OPTIMIZATIONS: Spec = {
     "mixed_precision": F(str, "O0", enum=["O0", "O1", "O2", "O3"]), "tensor_fusion_cycle_time": F(int, 1, min=0),
     "tensor_fusion_threshold": F(int, 64, min=0),
     # B200 engine extensions (ignored by the reference)
-    "fused_engine": F(bool, None), "cuda_graphs": F(bool, False), "bucket_cap_mb": F(_NUM, 25),
+    "fused_engine": F(bool, None), "cuda_graphs": F(bool, False), "bucket_cap_mb": F(_NUM, 25), "async_checkpoint": F(bool, False),
 }
 PROFILING: Spec = {"enabled": F(bool, False), "begin_on_batch": F(int, 0, min=0), "end_after_batch": F(int, None, min=0),
                    "sync_timings": F(bool, True)}

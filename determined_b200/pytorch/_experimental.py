@@ -20,6 +20,7 @@ class PyTorchExperimentalContext:
         self._cuda_graphs = False
         self._bucket_cap_mb = 25.0
         self._wire_dtype: Optional[torch.dtype] = None
+        self._async_checkpoint = False
 
     def use_amp(self, dtype: Optional[torch.dtype] = None) -> None:
         """Automatic mixed precision: ``train_batch``/``evaluate_batch`` forward passes run under
@@ -52,6 +53,15 @@ class PyTorchExperimentalContext:
         self._fused_engine = enabled
         self._bucket_cap_mb = bucket_cap_mb
         self._wire_dtype = wire_dtype
+
+    def enable_async_checkpoint(self, enabled: bool = True) -> None:
+        """Checkpoint fast path: at a checkpoint boundary the chief snapshots models / optimizers / schedulers into pinned host
+        memory with non-blocking copies on the training stream and a writer thread serialises, uploads and reports the
+        checkpoint while training continues (``pytorch/_async_checkpoint.py``).  The files are identical to the synchronous
+        path.  ``on_checkpoint_write_end`` / ``on_checkpoint_end`` then run on the writer thread and
+        ``on_checkpoint_upload_end`` is delivered at the next checkpoint or at exit; checkpoints taken while exiting
+        (preemption, end of training) are always synchronous."""
+        self._async_checkpoint = enabled
 
     def enable_cuda_graphs(self, enabled: bool = True) -> None:
         """Capture ``train_batch`` (forward + backward + fused all-reduce + optimizer) into CUDA

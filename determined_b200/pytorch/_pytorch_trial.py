@@ -20,6 +20,7 @@ B200-first changes in the hot loop:
 import abc
 import collections.abc as col_abc
 import contextlib
+import copy
 import enum
 import json
 import logging
@@ -221,6 +222,7 @@ class _PyTorchTrialController:
         self._graphs: Dict[bool, _GraphedStep] = {}
         self._graph_warmup_left = 3
         self._graphs_failed = False
+        self._pending_upload_cbs: List[str] = []
         self.step_timer = core.StepTimer()
         self._metric_writer: Any = None
         self._batch_hooks = [cb for cb in self.callbacks.values()
@@ -346,6 +348,7 @@ class _PyTorchTrialController:
                 stack.callback(self.core_context.profiler.off)
             for cb in self.callbacks.values():
                 cb.on_training_start()
+            stack.callback(self._close_checkpoint_writer)      # runs before on_trial_shutdown: nothing is left in flight
             self._run()
 
     def _run(self) -> None:
@@ -807,11 +810,20 @@ class _PyTorchTrialController:
                     "framework": f"torch-{torch.__version__}",
                     "format": "pickle",
                 }
-                with self.core_context.checkpoint.store_path(md) as (path, uuid):
-                    self._save(pathlib.Path(path))
+                if self.context.experimental._async_checkpoint and not already_exiting:
+                    uuid = self._save_behind(md)
+                else:
+                    self._drain_checkpoints()
+                    with self.core_context.checkpoint.store_path(md) as (path, uuid):
+                        self._save(pathlib.Path(path))
+            elif not (self.context.experimental._async_checkpoint and not already_exiting):
+                self._drain_checkpoints()
             uuid = self.context.distributed.broadcast(uuid)
-            for cb in self.callbacks.values():
-                cb.on_checkpoint_upload_end(uuid=uuid)
+            if self._ckpt_writer is not None and not already_exiting and self.context.experimental._async_checkpoint:
+                self._pending_upload_cbs.append(uuid)          # delivered once the writer is done (next checkpoint / exit)
+            else:
+                for cb in self.callbacks.values():
+                    cb.on_checkpoint_upload_end(uuid=uuid)
         except errors.InvalidHP:
             if not already_exiting:
                 self.core_context.train.report_early_exit(core.EarlyExitReason.INVALID_HP)
@@ -820,13 +832,68 @@ class _PyTorchTrialController:
         if not already_exiting:
             self._stop_requested()
 
+    # -- checkpoint fast path (pytorch/_async_checkpoint.py) ----------------------------------------
+    _ckpt_writer: Any = None
+    _ckpt_pool: Any = None
+
+    def _save_behind(self, md: Dict[str, Any]) -> str:
+        """Chief only: snapshot now (non-blocking D2H on the training stream), write and report from the writer thread.
+        Returns the storage id as soon as the writer has opened the checkpoint."""
+        import queue as _queue
+
+        from determined_b200.pytorch import _async_checkpoint as ac
+
+        if self._ckpt_writer is None:
+            self._ckpt_writer, self._ckpt_pool = ac.CheckpointWriter(max_pending=1), ac.PinnedPool()
+        self._drain_checkpoints()                 # at most one in flight; also delivers its upload callbacks
+        checkpoint, state_vars, load_data = self._collect()
+        snap = ac.snapshot(checkpoint, self._ckpt_pool)
+        ident: "_queue.Queue[Any]" = _queue.Queue(1)
+
+        def job() -> None:
+            try:
+                with self.core_context.checkpoint.store_path(md) as (path, uuid):
+                    ident.put(uuid)
+                    self._write(pathlib.Path(path), snap.wait(), state_vars, load_data)
+            except BaseException as e:  # noqa: BLE001
+                ident.put(e)               # harmless if the id was already delivered (queue of one, nobody reads twice)
+                raise
+            finally:
+                self._ckpt_pool.give(snap.bufs)
+
+        self._ckpt_writer.submit(job)
+        got = ident.get()
+        if isinstance(got, BaseException):
+            raise got
+        return str(got)
+
+    def _drain_checkpoints(self) -> None:
+        """Wait for the checkpoint in flight (if any), surface its failure, deliver the deferred upload callbacks."""
+        if self._ckpt_writer is not None:
+            self._ckpt_writer.join()
+        pending, self._pending_upload_cbs = self._pending_upload_cbs, []
+        for uuid in pending:
+            for cb in self.callbacks.values():
+                cb.on_checkpoint_upload_end(uuid=uuid)
+
+    def _close_checkpoint_writer(self) -> None:
+        try:
+            self._drain_checkpoints()
+        finally:
+            if self._ckpt_writer is not None:
+                w, self._ckpt_writer = self._ckpt_writer, None
+                w.close()
+
     def _save(self, path: pathlib.Path) -> None:
         """Write the reference checkpoint layout: ``state_dict.pth``, ``trial_state.pkl``,
         ``load_data.json``, ``code/`` (``metadata.json`` is added by the CheckpointContext)."""
+        checkpoint, state_vars, load_data = self._collect()
+        self._write(path, checkpoint, state_vars, load_data)
+
+    def _collect(self) -> Tuple[Dict[str, Any], Dict[str, Any], Dict[str, Any]]:
+        """Everything a checkpoint holds, referencing live tensors (main thread, at a step boundary)."""
         assert self.state is not None
         ctx = self.context
-        path.mkdir(parents=True, exist_ok=True)
-        util.write_user_code(path, not self.local_training)
         rng_state = {"cpu_rng_state": torch.random.get_rng_state(), "np_rng_state": np.random.get_state(),
                      "random_rng_state": random.getstate()}
         if torch.cuda.is_available() and ctx.device.type == "cuda":
@@ -842,14 +909,20 @@ class _PyTorchTrialController:
             checkpoint["scaler_state_dict"] = ctx._scaler.state_dict()
         for cb in self.callbacks.values():
             cb.on_checkpoint_save_start(checkpoint)
-        torch.save(checkpoint, str(path / "state_dict.pth"))
-        with (path / "trial_state.pkl").open("wb") as f:
-            pickle.dump(vars(self.state), f)
         trial_cls = type(self.trial)
         load_data: Dict[str, Any] = {"trial_type": "PyTorchTrial", "experiment_config": ctx._exp_conf,
                                      "hparams": ctx._hparams,
                                      "trial_cls_spec": f"{trial_cls.__module__}:{trial_cls.__qualname__}",
                                      "is_trainer": True}
+        return checkpoint, copy.deepcopy(vars(self.state)), load_data
+
+    def _write(self, path: pathlib.Path, checkpoint: Dict[str, Any], state_vars: Dict[str, Any], load_data: Dict[str, Any]) -> None:
+        """Serialise one checkpoint (any thread; ``checkpoint`` must not alias live training state when called off-thread)."""
+        path.mkdir(parents=True, exist_ok=True)
+        util.write_user_code(path, not self.local_training)
+        torch.save(checkpoint, str(path / "state_dict.pth"))
+        with (path / "trial_state.pkl").open("wb") as f:
+            pickle.dump(state_vars, f)
         (path / "load_data.json").write_text(util.json_encode(load_data))
         for cb in self.callbacks.values():
             if util.is_overridden(cb.on_checkpoint_end, _callback.PyTorchCallback):

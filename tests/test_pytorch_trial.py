@@ -109,3 +109,69 @@ def test_load_trial_from_checkpoint(tmp_path, monkeypatch):
     ck = sorted((tmp_path / "ckpt").iterdir(), key=lambda p: p.stat().st_mtime)[-1]
     loaded = pytorch.load_trial_from_checkpoint_path(str(ck), trial_class=onevar.OneVarTrial)
     assert abs(float(loaded.model.weight) - t1.weights[-1]) < 1e-7
+
+
+def test_async_checkpoint_writes_the_same_files_behind_training(tmp_path, monkeypatch):
+    """Checkpoint fast path: mid-training checkpoints are snapshotted and written by a background thread; the files match the
+    synchronous path, the snapshot is taken at the boundary (later steps do not leak into it), callbacks are delivered, and the
+    trial resumes from one of them."""
+    from determined_b200.pytorch import _async_checkpoint as ac
+
+    monkeypatch.chdir(tmp_path)
+    hp = {"learning_rate": 0.1, "batch_size": 4, "dataset_len": 32}
+    events = []
+
+    class Spy(pytorch.PyTorchCallback):
+        def on_checkpoint_write_end(self, checkpoint_dir):
+            events.append(("write", pathlib.Path(checkpoint_dir).name))
+
+        def on_checkpoint_upload_end(self, uuid):
+            events.append(("upload", uuid))
+
+    def run(root, enable, latest=None, upto=12):
+        exp_conf = {"checkpoint_storage": {"type": "shared_fs", "host_path": str(root)}}
+        root.mkdir(exist_ok=True)
+        with pytorch.init(hparams=hp, exp_conf=exp_conf) as ctx:
+            ctx._core.checkpoint._storage_manager = __import__("determined_b200").common.storage.SharedFSStorageManager(str(root))
+            ctx.experimental.enable_async_checkpoint(enable)
+            trial = onevar.OneVarTrial(ctx)
+            trial.build_callbacks = lambda: {"spy": Spy()}
+            pytorch.Trainer(trial, ctx).fit(max_length=pytorch.Batch(upto), checkpoint_period=pytorch.Batch(4), checkpoint_policy="none",
+                                            latest_checkpoint=latest)
+            return trial
+
+    run(tmp_path / "sync", False)
+    sync_events, events[:] = list(events), []
+    t = run(tmp_path / "async", True)
+    assert sorted(e for e in events if e[0] == "write") and len([e for e in events if e[0] == "upload"]) == len([e for e in sync_events if e[0] == "upload"])
+
+    def by_step(root):
+        out = {}
+        for d in root.iterdir():
+            md = json.loads((d / "metadata.json").read_text())
+            out[md["steps_completed"]] = d
+        return out
+
+    a, s = by_step(tmp_path / "async"), by_step(tmp_path / "sync")
+    assert set(a) == set(s) == {4, 8, 12}
+    for step in (4, 8, 12):
+        assert {p.name for p in a[step].iterdir()} == {p.name for p in s[step].iterdir()}
+        sa, ss = torch.load(a[step] / "state_dict.pth", weights_only=False), torch.load(s[step] / "state_dict.pth", weights_only=False)
+        for ma, ms in zip(sa["models_state_dict"], ss["models_state_dict"]):
+            for k in ms:
+                assert torch.equal(ma[k], ms[k]), (step, k)
+        assert pickle.loads((a[step] / "trial_state.pkl").read_bytes()) == pickle.loads((s[step] / "trial_state.pkl").read_bytes())
+    t2 = run(tmp_path / "async", True, latest=a[8].name, upto=16)
+    exp = onevar.expected_weights(0.0, 0.1, _batches(32, 4, 16))
+    np.testing.assert_allclose(t2.weights, exp[8:], rtol=1e-5, atol=1e-6)
+
+    # the building blocks: snapshots are deep and writer failures surface at join
+    live = {"w": torch.ones(3), "nested": [torch.zeros(2), {"k": 1}], "t": (torch.ones(1), "s")}
+    snap = ac.snapshot(live).wait()
+    live["w"].add_(1)
+    assert torch.equal(snap["w"], torch.ones(3)) and snap["nested"][1] == {"k": 1} and isinstance(snap["t"], tuple)
+    w = ac.CheckpointWriter()
+    w.submit(lambda: (_ for _ in ()).throw(OSError("disk full")))
+    with pytest.raises(RuntimeError, match="background checkpoint failed"):
+        w.join()
+    w.close()
