@@ -19,6 +19,7 @@ CSRC = ROOT / "csrc"
 OBJ = HERE / "obj"
 LIB = HERE / "libdetb200.so"
 LAUNCHER = HERE / "detb200-launch"
+HOSTLIB = HERE / "libdetb200_host.so"
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--use_fast_math", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-I", str(ROOT / "include"),
@@ -83,6 +84,17 @@ def build(verbose: bool = False) -> pathlib.Path:
             r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
             if r.returncode != 0:
                 raise RuntimeError(f"launcher build failed\n{r.stdout}")
+    # host-only runtime pieces (no CUDA): shared-memory object collectives; sources under csrc/host/
+    hdir = CSRC / "host"
+    if hdir.is_dir():
+        srcs = sorted(hdir.glob("*.cpp"))
+        if srcs and (not HOSTLIB.exists() or any(s.stat().st_mtime > HOSTLIB.stat().st_mtime for s in srcs)):
+            cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-pthread", "-fvisibility=hidden", "-o", str(HOSTLIB), *map(str, srcs), "-lrt"]
+            if verbose:
+                print(" ".join(cmd), flush=True)
+            r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(f"host library build failed\n{r.stdout}")
     return LIB
 
 

@@ -204,8 +204,19 @@ class DistributedContext:
         kind = _transport
         if kind is None:
             kind = "torch" if _torch_dist_ready(size) else "socket"
+            if kind == "socket" and cross_size == 1 and not force_tcp and os.environ.get("DET_SHM_COLLECTIVES", "1") != "0":
+                from determined_b200.core import _shm_transport
+
+                if _shm_transport.available():
+                    kind = "shm"
         if kind == "torch":
             self._transport = _TorchTransport()
+        elif kind == "shm":
+            # all ranks on this box: one shared-memory segment instead of a socket star through the chief
+            from determined_b200.core import _shm_transport
+
+            tag = os.environ.get("DET_ALLOCATION_ID", "") or str(os.getppid())
+            self._transport = _shm_transport.ShmTransport(rank, size, f"{tag}-{pub_port + port_offset}")  # type: ignore[assignment]
         else:
             if chief_ip is None:
                 raise ValueError("chief_ip is required when size > 1 and torch.distributed is not initialized")
