@@ -512,6 +512,106 @@ def workspace_cmd(args: argparse.Namespace) -> int:
     return 0
 
 
+def project_cmd(args: argparse.Namespace) -> int:
+    """``det project list|create|describe|delete|list-experiments WORKSPACE [PROJECT]`` (reference ``cli/project.py``)."""
+    sess = _session(args)
+    ws = [w for w in sess.get("/api/v1/workspaces", params={"name": args.workspace}).json()["workspaces"] if w["name"] == args.workspace]
+    if not ws:
+        raise SystemExit(f"workspace {args.workspace!r} not found")
+    wid = ws[0]["id"]
+    projects = sess.get(f"/api/v1/workspaces/{wid}/projects").json()["projects"]
+    if args.action == "list":
+        _table([[p["id"], p["name"], p["description"], p["numExperiments"]] for p in projects], ["ID", "Name", "Description", "# Experiments"], args.json)
+        return 0
+    if args.action == "create":
+        p = sess.post(f"/api/v1/workspaces/{wid}/projects", json={"name": args.project, "description": args.description or ""}).json()["project"]
+        print(f"Created project {p['name']} (id {p['id']}) in workspace {args.workspace}")
+        return 0
+    match = [p for p in projects if p["name"] == args.project]
+    if not match:
+        raise SystemExit(f"project {args.project!r} not found in workspace {args.workspace!r}")
+    pid = match[0]["id"]
+    if args.action == "describe":
+        p = sess.get(f"/api/v1/projects/{pid}").json()["project"]
+        if args.json:
+            print(json.dumps(p, indent=2))
+        else:
+            _table([[p["id"], p["name"], p.get("description", ""), p.get("numExperiments", 0), p.get("workspaceId", wid)]],
+                   ["ID", "Name", "Description", "# Experiments", "Workspace"], False)
+    elif args.action == "list-experiments":
+        es = sess.get("/api/v1/experiments", params={"projectId": pid, "limit": 500}).json()["experiments"]
+        _table([[e["id"], e["name"], e["state"].replace("STATE_", ""), f"{100 * (e.get('progress') or 0):.0f}%", e.get("username", "")] for e in es],
+               ["ID", "Name", "State", "Progress", "Owner"], args.json)
+    elif args.action == "delete":
+        sess.delete(f"/api/v1/projects/{pid}")
+        print(f"Deleted project {args.project}")
+    return 0
+
+
+def task_cmd(args: argparse.Namespace) -> int:
+    """``det task list | logs TASK_ID [-f] | kill TASK_ID`` over every kind of task (reference ``cli/task.py``)."""
+    sess = _session(args)
+    if args.action == "list":
+        rows = []
+        for aid, a in sess.get("/api/v1/tasks").json()["allocationIdToSummary"].items():
+            devs = [f"{ag}:{','.join(str(d) for d in v['devices'])}" for r in a.get("resources", []) for ag, v in r.get("agentDevices", {}).items()]
+            rows.append([a["taskId"], aid, a["name"], a["slotsNeeded"], a["state"], " ".join(devs)])
+        _table(rows, ["Task ID", "Allocation ID", "Name", "Slots", "State", "Devices"], args.json)
+        return 0
+    if args.action == "logs":
+        last = 0
+        while True:
+            logs = sess.get(f"/api/v1/tasks/{args.task_id}/logs", params={"offset": last}).json()["logs"]
+            for ln in logs:
+                sys.stdout.write(ln["log"])
+                last = max(last, int(ln["id"]))
+            running = any(a["taskId"] == args.task_id for a in sess.get("/api/v1/tasks").json()["allocationIdToSummary"].values())
+            if not logs and (not args.follow or not running):
+                return 0
+            time.sleep(0.3)
+    if args.action == "kill":
+        for plural in ("commands", "shells", "notebooks", "tensorboards"):
+            try:
+                sess.post(f"/api/v1/{plural}/{args.task_id}/kill")
+                print(f"Killed {plural[:-1]} {args.task_id}")
+                return 0
+            except api.errors.APIException:
+                continue
+        raise SystemExit(f"task {args.task_id} is not a command / shell / notebook / tensorboard (kill trials through their experiment)")
+    return 2
+
+
+def dev_cmd(args: argparse.Namespace) -> int:
+    """``det dev curl PATH`` / ``det dev bindings list|call`` (reference ``cli/dev.py``): raw authenticated API access."""
+    sess = _session(args)
+    if args.action == "curl":
+        body = json.loads(args.data) if args.data else None
+        r = getattr(sess, args.request.lower())(args.path, **({"json": body} if body is not None else {}))
+        try:
+            print(json.dumps(r.json(), indent=2))
+        except ValueError:
+            print(r.text)
+        return 0
+    from determined_b200.common.api import bindings
+
+    names = sorted(n for n in dir(bindings) if n.split("_")[0] in ("get", "post", "put", "patch", "delete") and callable(getattr(bindings, n)))
+    if args.action == "list":
+        for n in names:
+            print(f"{n:60s} {(getattr(bindings, n).__doc__ or '').strip()}")
+        return 0
+    if args.name not in names:
+        raise SystemExit(f"no binding named {args.name!r}; see `det dev bindings list`")
+    kw: Dict[str, Any] = {}
+    for item in args.args:
+        k, _, v = item.partition("=")
+        try:
+            kw[k] = json.loads(v)
+        except ValueError:
+            kw[k] = v
+    print(json.dumps(getattr(bindings, args.name)(sess, **kw), indent=2))
+    return 0
+
+
 def rbac_cmd(args: argparse.Namespace) -> int:
     """``det user-group ...`` / ``det rbac ...`` (reference ``harness/determined/cli/{user_groups,rbac}.py``)."""
     sess = _session(args)
@@ -885,6 +985,43 @@ def make_parser() -> argparse.ArgumentParser:
             a.add_argument("project")
         outfmt(a)
         a.set_defaults(fn=workspace_cmd, action=name)
+
+    pj = sub.add_parser("project", aliases=["p"]).add_subparsers(dest="sub")
+    for name in ("list", "create", "describe", "delete", "list-experiments"):
+        a = pj.add_parser(name)
+        a.add_argument("workspace")
+        if name != "list":
+            a.add_argument("project")
+        if name == "create":
+            a.add_argument("--description")
+        outfmt(a)
+        a.set_defaults(fn=project_cmd, action=name)
+
+    tk = sub.add_parser("task").add_subparsers(dest="sub")
+    a = tk.add_parser("list", aliases=["ls"])
+    outfmt(a)
+    a.set_defaults(fn=task_cmd, action="list")
+    a = tk.add_parser("logs")
+    a.add_argument("task_id")
+    a.add_argument("-f", "--follow", action="store_true")
+    a.set_defaults(fn=task_cmd, action="logs")
+    a = tk.add_parser("kill")
+    a.add_argument("task_id")
+    a.set_defaults(fn=task_cmd, action="kill")
+
+    dv = sub.add_parser("dev").add_subparsers(dest="sub")
+    a = dv.add_parser("curl")
+    a.add_argument("path")
+    a.add_argument("-X", "--request", default="GET", choices=["GET", "POST", "PUT", "PATCH", "DELETE"])
+    a.add_argument("-d", "--data", help="JSON request body")
+    a.set_defaults(fn=dev_cmd, action="curl")
+    bd = dv.add_parser("bindings").add_subparsers(dest="bsub")
+    a = bd.add_parser("list")
+    a.set_defaults(fn=dev_cmd, action="list")
+    a = bd.add_parser("call")
+    a.add_argument("name")
+    a.add_argument("args", nargs="*", help="key=value (values are parsed as JSON when possible; body={...} for the payload)")
+    a.set_defaults(fn=dev_cmd, action="call")
 
     for kind, aliases in (("command", ["cmd"]), ("shell", []), ("notebook", []), ("tensorboard", [])):
         cp = sub.add_parser(kind, aliases=aliases).add_subparsers(dest="sub")

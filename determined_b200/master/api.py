@@ -1461,8 +1461,15 @@ def delete_webhook(ctx: Ctx, wid: str) -> Any:
 
 @route("GET", "/api/v1/tasks")
 def list_tasks(ctx: Ctx) -> Any:
-    return {"allocationIdToSummary": {a.id: {"taskId": a.trial.task_id, "allocationId": a.id, "name": f"trial {a.trial.id}", "slotsNeeded": a.slots,
-                                             "state": a.state, "resources": [{"agentDevices": {ctx.m.agent_id: {"devices": a.slot_ids}}}]} for a in ctx.m.allocations.values()}}
+    """Every running allocation: trials and command / shell / notebook / tensorboard tasks."""
+    m = ctx.m
+    out = {a.id: {"taskId": a.trial.task_id, "allocationId": a.id, "name": f"trial {a.trial.id}", "slotsNeeded": a.slots, "state": a.state,
+                  "resources": [{"agentDevices": {getattr(a, "agent_id", m.agent_id): {"devices": a.slot_ids}}}]} for a in m.allocations.values()}
+    for t in m.commands.tasks.values():
+        if t.state in ("QUEUED", "RUNNING"):
+            out[t.id + ".1"] = {"taskId": t.id, "allocationId": t.id + ".1", "name": t.description, "slotsNeeded": t.slots, "state": t.state,
+                                "resources": [{"agentDevices": {getattr(t, "agent_id", m.agent_id): {"devices": t.slot_ids}}}]}
+    return {"allocationIdToSummary": out}
 
 
 # ---------------------------------------------------------------------------------------------

@@ -219,3 +219,26 @@ def test_prometheus_endpoint(cluster):
     m = cluster[0]
     txt = requests.get(m.url + "/prom/det-state-metrics", timeout=5).text
     assert f'det_slots_total{{agent="{m.agent_id}"}} 8' in txt and "det_experiments_active 0" in txt and "det_master_uptime_seconds" in txt
+
+
+def test_cli_project_task_dev(cluster):
+    def run(*argv):
+        rc, out = globals()["run"](*argv)
+        assert rc == 0, out
+        return out
+
+    out = run("workspace", "create", "ws1")
+    assert "Created workspace ws1" in out
+    assert "Created project p1" in run("project", "create", "ws1", "p1", "--description", "first")
+    assert "p1" in run("project", "list", "ws1") and "first" in run("project", "describe", "ws1", "p1")
+    assert "ID" in run("project", "list-experiments", "ws1", "p1")
+    assert "Deleted project p1" in run("project", "delete", "ws1", "p1")
+    assert "p1" not in run("project", "list", "ws1")
+    assert "Task ID" in run("task", "list")
+    got = json.loads(run("dev", "curl", "/api/v1/master"))
+    assert "clusterId" in got or "version" in got
+    assert "get_agents" in run("dev", "bindings", "list")
+    ws = json.loads(run("dev", "bindings", "call", "post_workspaces", 'body={"name": "via-bindings"}'))
+    assert ws["workspace"]["name"] == "via-bindings"
+    one = json.loads(run("dev", "bindings", "call", "get_workspaces_by_wid", f"wid={ws['workspace']['id']}"))
+    assert one["workspace"]["name"] == "via-bindings"
