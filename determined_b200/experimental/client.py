@@ -391,6 +391,105 @@ class Model:
         self._session.delete(f"/api/v1/models/{self.name}")
 
 
+class User:
+    """Reference ``common/experimental/user.py``."""
+
+    def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
+        self._session = session
+        self._hydrate(data)
+
+    def _hydrate(self, d: Dict[str, Any]) -> None:
+        self.user_id, self.username = d["id"], d["username"]
+        self.admin, self.active, self.display_name = bool(d.get("admin")), bool(d.get("active", True)), d.get("displayName")
+
+    def _patch(self, **fields: Any) -> None:
+        self._hydrate(self._session.patch(f"/api/v1/users/{self.user_id}", json={"user": fields}).json()["user"])
+
+    def rename(self, new_username: str) -> None:
+        self._patch(username=new_username)
+
+    def activate(self) -> None:
+        self._patch(active=True)
+
+    def deactivate(self) -> None:
+        self._patch(active=False)
+
+    def change_display_name(self, display_name: str) -> None:
+        self._patch(displayName=display_name)
+
+    def change_password(self, new_password: str) -> None:
+        self._patch(password=api.authentication.salt_and_hash(new_password), isHashed=True)
+
+    def reload(self) -> None:
+        for u in self._session.get("/api/v1/users").json()["users"]:
+            if u["id"] == self.user_id:
+                self._hydrate(u)
+
+    def __repr__(self) -> str:
+        return f"User(id={self.user_id}, username={self.username!r})"
+
+
+class Project:
+    """Reference ``common/experimental/project.py``."""
+
+    def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
+        self._session = session
+        self.id, self.name, self.description = data["id"], data["name"], data.get("description", "")
+        self.workspace_id, self.n_experiments = data.get("workspaceId"), data.get("numExperiments", 0)
+        self.archived, self.notes = bool(data.get("archived")), data.get("notes") or []
+
+    def list_experiments(self) -> List["Experiment"]:
+        r = self._session.get("/api/v1/experiments", params={"projectId": self.id, "limit": 1000}).json()
+        return [Experiment(self._session, e["id"], e) for e in r["experiments"]]
+
+    def delete(self) -> None:
+        self._session.delete(f"/api/v1/projects/{self.id}")
+
+    def __repr__(self) -> str:
+        return f"Project(id={self.id}, name={self.name!r})"
+
+
+class Workspace:
+    """Reference ``common/experimental/workspace.py``."""
+
+    def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
+        self._session = session
+        self.id, self.name = data["id"], data["name"]
+        self.archived, self.immutable, self.n_projects = bool(data.get("archived")), bool(data.get("immutable")), data.get("numProjects", 0)
+
+    def create_project(self, name: str, description: str = "") -> Project:
+        r = self._session.post(f"/api/v1/workspaces/{self.id}/projects", json={"name": name, "description": description}).json()
+        return Project(self._session, r["project"])
+
+    def list_projects(self) -> List[Project]:
+        return [Project(self._session, p) for p in self._session.get(f"/api/v1/workspaces/{self.id}/projects").json()["projects"]]
+
+    def get_project(self, project_name: str) -> Project:
+        for p in self.list_projects():
+            if p.name == project_name:
+                return p
+        raise ValueError(f"workspace {self.name!r} has no project named {project_name!r}")
+
+    def delete(self) -> None:
+        self._session.delete(f"/api/v1/workspaces/{self.id}")
+
+    def __repr__(self) -> str:
+        return f"Workspace(id={self.id}, name={self.name!r})"
+
+
+class ResourcePool:
+    """Reference ``common/experimental/resource_pool.py``."""
+
+    def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
+        self._session = session
+        self.name = data["name"]
+        self.slots_available, self.slots_used, self.num_agents = data.get("slotsAvailable", 0), data.get("slotsUsed", 0), data.get("numAgents", 0)
+        self.scheduler_type, self.fitting_policy = data.get("schedulerType"), data.get("schedulerFittingPolicy")
+
+    def __repr__(self) -> str:
+        return f"ResourcePool(name={self.name!r}, slots={self.slots_used}/{self.slots_available})"
+
+
 class Determined:
     """Entry point of the SDK.  ``master`` defaults to ``$DET_MASTER`` or localhost:8080."""
 
@@ -449,11 +548,82 @@ class Determined:
 
     list_models = get_models
 
+    def get_model_by_id(self, model_id: int) -> Model:
+        for m in self.get_models():
+            if getattr(m, "model_id", getattr(m, "id", None)) == model_id:
+                return m
+        raise ValueError(f"no model with id {model_id}")
+
+    def get_model_labels(self) -> List[str]:
+        return sorted({label for m in self._session.get("/api/v1/models").json()["models"] for label in (m.get("labels") or [])})
+
     def get_master_info(self) -> Dict[str, Any]:
         return self._session.get("/api/v1/master").json()
 
     def whoami(self) -> Dict[str, Any]:
         return self._session.get("/api/v1/me").json()["user"]
+
+    # -- users ---------------------------------------------------------------------------------
+    def create_user(self, username: str, admin: bool = False, password: Optional[str] = None, active: bool = True) -> User:
+        body: Dict[str, Any] = {"user": {"username": username, "admin": admin, "active": active}}
+        if password is not None:
+            body.update(password=api.authentication.salt_and_hash(password), isHashed=True)
+        return User(self._session, self._session.post("/api/v1/users", json=body).json()["user"])
+
+    def list_users(self, active: Optional[bool] = None) -> List[User]:
+        users = [User(self._session, u) for u in self._session.get("/api/v1/users", params={"limit": 10000}).json()["users"]]
+        return [u for u in users if active is None or u.active == active]
+
+    def get_user_by_id(self, user_id: int) -> User:
+        for u in self.list_users():
+            if u.user_id == user_id:
+                return u
+        raise ValueError(f"no user with id {user_id}")
+
+    def get_user_by_name(self, user_name: str) -> User:
+        for u in self.list_users():
+            if u.username == user_name:
+                return u
+        raise ValueError(f"no user named {user_name!r}")
+
+    def get_session_username(self) -> str:
+        return str(self.whoami()["username"])
+
+    # -- workspaces / projects / pools -------------------------------------------------------------
+    def list_workspaces(self) -> List[Workspace]:
+        return [Workspace(self._session, w) for w in self._session.get("/api/v1/workspaces", params={"limit": 10000}).json()["workspaces"]]
+
+    def get_workspace(self, name: str) -> Workspace:
+        for w in self.list_workspaces():
+            if w.name == name:
+                return w
+        raise ValueError(f"no workspace named {name!r}")
+
+    def create_workspace(self, name: str) -> Workspace:
+        return Workspace(self._session, self._session.post("/api/v1/workspaces", json={"name": name}).json()["workspace"])
+
+    def delete_workspace(self, name: str) -> None:
+        self.get_workspace(name).delete()
+
+    def list_resource_pools(self) -> List[ResourcePool]:
+        return [ResourcePool(self._session, p) for p in self._session.get("/api/v1/resource-pools").json()["resourcePools"]]
+
+    # -- metrics across trials ---------------------------------------------------------------------
+    def iter_trials_metrics(self, trial_ids: List[int], group: str) -> Iterator[Dict[str, Any]]:
+        """Metrics of several trials in one call (reference ``Determined.iter_trials_metrics``)."""
+        r = self._session.get("/api/v1/trials/metrics/trial_metrics", params={"trialIds": list(trial_ids), "group": group}).json()
+        for m in r["metrics"]:
+            yield {"trial_id": m["trialId"], "group": m["group"], "steps_completed": m["totalBatches"], "metrics": m["metrics"]["avgMetrics"],
+                   "batch_metrics": m["metrics"].get("batchMetrics"), "end_time": m["endTime"]}
+
+    def stream_trials_metrics(self, trial_ids: List[int], group: str) -> Iterator[Dict[str, Any]]:
+        return self.iter_trials_metrics(trial_ids, group)
+
+    def stream_trials_training_metrics(self, trial_ids: List[int]) -> Iterator[Dict[str, Any]]:
+        return self.iter_trials_metrics(trial_ids, "training")
+
+    def stream_trials_validation_metrics(self, trial_ids: List[int]) -> Iterator[Dict[str, Any]]:
+        return self.iter_trials_metrics(trial_ids, "validation")
 
     def preview_search(self, config: Union[str, Dict[str, Any]], seed: int = 0) -> Dict[str, Any]:
         text = yaml.safe_dump(config) if isinstance(config, dict) else config

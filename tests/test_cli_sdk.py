@@ -242,3 +242,31 @@ def test_cli_project_task_dev(cluster):
     assert ws["workspace"]["name"] == "via-bindings"
     one = json.loads(run("dev", "bindings", "call", "get_workspaces_by_wid", f"wid={ws['workspace']['id']}"))
     assert one["workspace"]["name"] == "via-bindings"
+
+
+def test_sdk_users_workspaces_projects_pools(cluster):
+    from determined_b200.experimental import client
+
+    d = client.Determined(cluster[0].url, "admin", "")
+    u = d.create_user("alice", password="pw1")
+    assert u.username == "alice" and not u.admin and u.active
+    u.change_display_name("Alice A.")
+    u.deactivate()
+    assert d.get_user_by_name("alice").active is False and d.get_user_by_id(u.user_id).display_name == "Alice A."
+    assert [x.username for x in d.list_users(active=False)] == ["alice"]
+    u.activate()
+    u.rename("alice2")
+    assert d.get_user_by_name("alice2").user_id == u.user_id and d.get_session_username() == "admin"
+    client.Determined(cluster[0].url, "alice2", "pw1")                 # the password set at creation works
+    ws = d.create_workspace("research")
+    p = ws.create_project("vision", "cv models")
+    assert [x.name for x in ws.list_projects()] == ["vision"] and ws.get_project("vision").description == "cv models"
+    assert "research" in [w.name for w in d.list_workspaces()] and p.list_experiments() == []
+    p.delete()
+    d.delete_workspace("research")
+    assert "research" not in [w.name for w in d.list_workspaces()]
+    pools = d.list_resource_pools()
+    assert pools[0].name == "default" and pools[0].slots_available == 8
+    m = d.create_model("m1", labels=["a", "b"])
+    assert d.get_model_labels() == ["a", "b"] and d.get_model_by_id(getattr(m, "model_id", getattr(m, "id", None))).name == "m1"
+    assert list(d.iter_trials_metrics([], "training")) == []
