@@ -428,3 +428,20 @@ def test_tracing_spans_nest_and_export_otlp(cluster, tmp_path):
     assert by["GET /api/v1/experiments"]["traceId"] == root.trace_id and by["GET /api/v1/experiments"]["parentSpanId"] == root.span_id
     assert by["failing"]["status"]["code"] == 2 and by["failing"]["parentSpanId"] == root.span_id
     assert {"key": "purpose", "value": {"stringValue": "test"}} in by["client.list"]["attributes"]
+
+
+def test_top_level_trial_context_and_bases():
+    import determined_b200 as det
+
+    c = det.TrialContext.from_config({"hyperparameters": {"lr": {"type": "const", "val": 0.1}, "global_batch_size": 32}, "data": {"path": "/x"}})
+    assert c.get_hparam("lr") == 0.1 and c.get_global_batch_size() == 32 and c.get_per_slot_batch_size() == 32
+    assert c.get_data_config() == {"path": "/x"} and c.get_trial_id() == 0 and not c.get_stop_requested()
+    c.set_stop_requested(True)
+    assert c.get_stop_requested()
+    with pytest.raises(ValueError, match="Could not find name"):
+        c.get_hparam("missing")
+    with pytest.raises(TypeError):
+        det.LegacyTrial(c)                   # abstract
+    with pytest.raises(TypeError):
+        det.TrialController(c)
+    assert det.EnvContext().managed_training is True
