@@ -56,3 +56,66 @@ def test_core_api_example_runs_off_cluster():
     env = dict(os.environ, PYTHONPATH=str(ROOT))
     r = subprocess.run([sys.executable, "train.py"], cwd=EX / "tutorials" / "core_api", env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
     assert r.returncode == 0, r.stdout[-2000:]
+
+
+def test_batch_inference_example_runs_off_cluster(tmp_path):
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    r = subprocess.run([sys.executable, str(EX / "features" / "torch_batch_process" / "batch_inference.py")], cwd=tmp_path, env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0 and "wrote 200 embeddings" in r.stdout, r.stdout[-2000:]
+
+
+def test_unmanaged_example_reports_to_a_master(tmp_path):
+    from determined_b200.common import api
+    from determined_b200.master import api as mapi
+    from determined_b200.master import core
+
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=1, launch=False, work_dir=str(tmp_path / "w"))
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    try:
+        env = dict(os.environ, PYTHONPATH=str(ROOT), DET_MASTER=m.url, HOME=str(tmp_path))
+        r = subprocess.run([sys.executable, str(EX / "features" / "unmanaged" / "1_singleton.py")], cwd=tmp_path, env=env,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert r.returncode == 0 and "experiment page:" in r.stdout, r.stdout[-2000:]
+        sess = api.authentication.login(m.url, "determined", "")
+        exps = sess.get("/api/v1/experiments").json()["experiments"]
+        assert [e["name"] for e in exps] == ["unmanaged-1-singleton"]
+        tid = sess.get(f"/api/v1/experiments/{exps[0]['id']}/trials").json()["trials"][0]["id"]
+        mets = sess.get(f"/api/v1/trials/{tid}/metrics").json()["metrics"]
+        assert len([x for x in mets if x["group"] == "training"]) == 10 and len([x for x in mets if x["group"] == "validation"]) == 2
+    finally:
+        m.stop()
+        srv.stop()
+
+
+def test_ports_example_config_launches_a_proxied_service(tmp_path):
+    import time
+
+    import requests
+
+    from determined_b200.common import api
+    from determined_b200.master import api as mapi
+    from determined_b200.master import core
+
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=1, work_dir=str(tmp_path / "w"))
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    try:
+        sess = api.authentication.login(m.url, "determined", "")
+        cfg = yaml.safe_load((EX / "features" / "ports" / "server.yml").read_text())
+        cmd = sess.post("/api/v1/commands", json={"config": cfg}).json()["command"]
+        ok = False
+        for _ in range(100):
+            c = sess.get(f"/api/v1/commands/{cmd['id']}").json()["command"]
+            if c.get("serviceAddress") and c["state"] == "STATE_RUNNING":
+                r = requests.get(m.url + c["serviceAddress"], params={"token": sess.token}, timeout=5)
+                if r.status_code == 200 and "Directory listing" in r.text:
+                    ok = True
+                    break
+            time.sleep(0.2)
+        assert ok
+        sess.post(f"/api/v1/commands/{cmd['id']}/kill")
+    finally:
+        m.stop()
+        srv.stop()
