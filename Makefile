@@ -1,7 +1,7 @@
 # Developer entry points (reference: top-level Makefile + tools/devcluster + .circleci).
 PY ?= python
 
-.PHONY: build test test-gpu bench bindings check devcluster clean
+.PHONY: build test test-gpu bench bindings check tsan devcluster clean
 
 build:            ## compile the native library for sm_100a (nvcc cross-compiles without a GPU)
 	$(PY) -c "import __graft_entry__ as g; g.build()"
@@ -21,6 +21,10 @@ bindings:         ## regenerate common/api/bindings.py from the master's route t
 check: bindings   ## what CI runs before the tests
 	git diff --exit-code determined_b200/common/api/bindings.py
 	$(PY) -m compileall -q determined_b200 tests benchmarks examples bench.py __graft_entry__.py
+
+tsan:             ## race check of the C++ host runtime (shared-memory collectives) under ThreadSanitizer
+	g++ -std=c++17 -O1 -g -fsanitize=thread -pthread csrc/host/shm_collective.cpp csrc/host/shm_collective_test.cpp -lrt -o /tmp/detb200_shm_tsan
+	TSAN_OPTIONS=exitcode=66 /tmp/detb200_shm_tsan 4 500
 
 devcluster:       ## a master without own slots plus one agent, in the foreground of two background daemons
 	$(PY) -m determined_b200.cli deploy local master-up --slots 0

@@ -269,3 +269,18 @@ DETB200_HOST_API int detb200_shm_barrier(void* handle, double timeout_s) {
   if (h->world > 1024) return fail(-1, "world too large");
   return round_trip(h, nullptr, 0, 0, nullptr, chunk, total, timeout_s);
 }
+
+// Test hook: another rank's handle on the SAME mapping as `handle` (threads of one process).  ThreadSanitizer tracks
+// virtual addresses, so only with a shared mapping can it see the protocol's data accesses and check that the
+// arrive / depart release-acquire pairs really order them (csrc/host/shm_collective_test.cpp).
+DETB200_HOST_API void* detb200_shm_clone_for_rank(void* handle, int rank) {
+  auto* h0 = static_cast<Handle*>(handle);
+  if (h0 == nullptr || rank < 0 || rank >= h0->world) return nullptr;
+  auto* h = new Handle(*h0);
+  h->rank = rank;
+  h->round = 0;
+  h->owner = false;
+  return h;
+}
+
+DETB200_HOST_API void detb200_shm_free_clone(void* handle) { delete static_cast<Handle*>(handle); }

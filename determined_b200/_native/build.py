@@ -87,7 +87,7 @@ def build(verbose: bool = False) -> pathlib.Path:
     # host-only runtime pieces (no CUDA): shared-memory object collectives; sources under csrc/host/
     hdir = CSRC / "host"
     if hdir.is_dir():
-        srcs = sorted(hdir.glob("*.cpp"))
+        srcs = sorted(p for p in hdir.glob("*.cpp") if not p.name.endswith("_test.cpp"))
         if srcs and (not HOSTLIB.exists() or any(s.stat().st_mtime > HOSTLIB.stat().st_mtime for s in srcs)):
             cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-pthread", "-fvisibility=hidden", "-o", str(HOSTLIB), *map(str, srcs), "-lrt"]
             if verbose:

@@ -113,3 +113,34 @@ def test_distributed_context_uses_it_on_one_node():
     [t.start() for t in th]
     [t.join(60) for t in th]
     assert out[0] == ([0, 10], "cfg", [0, 1], [0, 1]) and out[1] == ([0, 10], "cfg", None, [0, 1])
+
+
+def test_protocol_is_race_free_under_thread_sanitizer(tmp_path):
+    """Builds the collective with -fsanitize=thread and runs 4 ranks as threads on one mapping; also proves the check has teeth:
+    the same run with the arrive store weakened to relaxed must be reported."""
+    import pathlib
+    import subprocess
+
+    src = pathlib.Path(__file__).resolve().parent.parent / "csrc" / "host"
+
+    def build(lib_src, out):
+        r = subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-pthread", str(lib_src), str(src / "shm_collective_test.cpp"), "-lrt", "-o", str(out)],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        return r
+
+    good = tmp_path / "shm_tsan"
+    r = build(src / "shm_collective.cpp", good)
+    if r.returncode != 0:
+        pytest.skip("no ThreadSanitizer runtime: " + r.stdout[-200:])
+    env = dict(os.environ, TSAN_OPTIONS="exitcode=66")
+    r = subprocess.run([str(good), "4", "200"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0 and "ThreadSanitizer" not in r.stdout, r.stdout[-3000:]
+    broken_src = tmp_path / "broken.cpp"
+    text = (src / "shm_collective.cpp").read_text()
+    weak = text.replace("h->arrive()[h->rank].v.store(s, std::memory_order_release)", "h->arrive()[h->rank].v.store(s, std::memory_order_relaxed)")
+    assert weak != text
+    broken_src.write_text(weak)
+    bad = tmp_path / "shm_broken"
+    assert build(broken_src, bad).returncode == 0
+    r = subprocess.run([str(bad), "4", "50"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert "ThreadSanitizer: data race" in r.stdout
