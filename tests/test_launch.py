@@ -1,0 +1,80 @@
+"""Launch layer: the C++ launcher (rank contract, [rank=N] prefixes, kill-a-rank watchdog), the torch_distributed launch module
+with a real gloo rendezvous, argument parsing of the launch modules."""
+import json
+import os
+import pathlib
+import subprocess
+import sys
+import time
+
+import pytest
+
+from determined_b200.launch import _common, deepspeed, horovod, torch_distributed
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+LAUNCHER = _common.NATIVE_LAUNCHER
+needs_launcher = pytest.mark.skipif(not LAUNCHER.exists(), reason="native launcher not built")
+
+
+def _free_port():
+    import socket
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@needs_launcher
+def test_native_launcher_rank_contract_and_prefixes():
+    code = "import os; print('R', os.environ['RANK'], os.environ['LOCAL_RANK'], os.environ['WORLD_SIZE'], os.environ['LOCAL_WORLD_SIZE'], os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'])"
+    port = _free_port()
+    r = subprocess.run([str(LAUNCHER), "--nproc", "3", "--master-addr", "127.0.0.1", "--master-port", str(port), "--", sys.executable, "-c", code],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout
+    lines = sorted(l for l in r.stdout.splitlines() if " R " in l or l.startswith("[rank="))
+    assert lines == [f"[rank={i}] R {i} {i} 3 3 127.0.0.1 {port}" for i in range(3)], r.stdout
+
+
+@needs_launcher
+def test_native_launcher_kills_the_job_when_a_rank_dies():
+    """Kill-a-rank: rank 1 fails, the survivors (sleeping for a minute) are torn down within the grace period and the job exits
+    non-zero — the allocation then restarts from its checkpoint under max_restarts (reference pid_server / WorkerError)."""
+    code = "import os, sys, time\nif os.environ['RANK'] == '1':\n    time.sleep(0.5); sys.exit(3)\ntime.sleep(60)"
+    t0 = time.time()
+    r = subprocess.run([str(LAUNCHER), "--nproc", "3", "--grace", "2", "--master-port", str(_free_port()), "--", sys.executable, "-c", code],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=50)
+    assert r.returncode != 0 and time.time() - t0 < 20, (r.returncode, time.time() - t0, r.stdout)
+
+
+def test_torch_distributed_launch_module_runs_a_gloo_job(tmp_path):
+    script = tmp_path / "job.py"
+    script.write_text(
+        "import os, torch, torch.distributed as dist\n"
+        "dist.init_process_group('gloo')\n"
+        "t = torch.tensor([float(dist.get_rank() + 1)])\n"
+        "dist.all_reduce(t)\n"
+        "open(os.path.join(os.environ['OUT'], f\"r{dist.get_rank()}\"), 'w').write(str(float(t)))\n"
+        "dist.destroy_process_group()\n")
+    env = dict(os.environ, PYTHONPATH=str(ROOT), DET_SLOT_IDS=json.dumps([0, 1]), OUT=str(tmp_path), C10D_PORT=str(_free_port()), CUDA_VISIBLE_DEVICES="")
+    env.pop("DET_MASTER", None)
+    r = subprocess.run([sys.executable, "-m", "determined_b200.launch.torch_distributed", "--", sys.executable, str(script)], env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180)
+    assert r.returncode == 0, r.stdout[-2000:]
+    assert (tmp_path / "r0").read_text() == "3.0" and (tmp_path / "r1").read_text() == "3.0"
+
+
+def test_launch_argument_parsing():
+    ov, script = torch_distributed.parse_args(["--rdzv_conf", "x=1", "--", "python3", "train.py", "--lr", "1"])
+    assert ov == ["--rdzv_conf", "x=1"] and script == ["python3", "train.py", "--lr", "1"]
+    ov, script = torch_distributed.parse_args(["--trial", "model_def:MyTrial"])
+    assert ov == [] and "model_def:MyTrial" in " ".join(script)
+    with pytest.raises(SystemExit):
+        torch_distributed.parse_args([])
+    assert _common.split_args(["a", "b"]) == ([], ["a", "b"])
+    cmd = _common.torchrun_cmd(4, ["python3", "t.py"], ["--foo"], port=1234)
+    assert cmd[cmd.index("--nproc_per_node") + 1] == "4" and "--max_restarts" in cmd and cmd[-2:] == ["python3", "t.py"] and "--foo" in cmd
+    assert _common.pid_server_wrap(2, ["x"], "/tmp/sock")[-4:] == ["/tmp/sock", "2", "--", "x"]
+    for mod in (deepspeed, horovod):
+        assert hasattr(mod, "main")
