@@ -78,3 +78,30 @@ def test_launch_argument_parsing():
     assert _common.pid_server_wrap(2, ["x"], "/tmp/sock")[-4:] == ["/tmp/sock", "2", "--", "x"]
     for mod in (deepspeed, horovod):
         assert hasattr(mod, "main")
+
+
+def _pid_server(tmp_path, worker_codes):
+    """pid_server supervising one launcher process that starts len(worker_codes) workers under pid_client."""
+    addr = str(tmp_path / "pid.sock")
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    workers = " & ".join(f"{sys.executable} -m determined_b200.exec.pid_client {addr} -- {sys.executable} -c \"{code}\"" for code in worker_codes)
+    cmd = [sys.executable, "-m", "determined_b200.exec.pid_server", "--on-fail", "SIGTERM", "--on-exit", "WAIT", "--grace-period", "2", "--signal-children", addr,
+           str(len(worker_codes)), "--", "/bin/bash", "-c", workers + " & wait"]
+    t0 = time.time()
+    with open(tmp_path / "out.log", "w") as out:          # a file, not a pipe: an orphaned worker must not keep the test waiting for EOF
+        r = subprocess.run(cmd, env=env, stdout=out, stderr=subprocess.STDOUT, timeout=120)
+    r.stdout = (tmp_path / "out.log").read_text()
+    return r, time.time() - t0
+
+
+def test_pid_server_passes_when_all_workers_exit_cleanly(tmp_path):
+    r, _ = _pid_server(tmp_path, ["print('a')", "print('b')"])
+    assert r.returncode == 0, r.stdout[-2000:]
+
+
+def test_pid_server_fails_fast_when_a_worker_dies(tmp_path):
+    """Reference ipc.py:409-502: a worker that vanishes without the graceful-exit byte is a WorkerError; the launcher (and the
+    worker still sleeping) are signalled after the grace period."""
+    r, dt = _pid_server(tmp_path, ["import time; time.sleep(60)", "import sys, time; time.sleep(0.5); sys.exit(7)"])
+    assert r.returncode != 0 and dt < 30, (r.returncode, dt, r.stdout[-2000:])
+    assert "died without a graceful exit" in r.stdout
