@@ -8,6 +8,7 @@ activate, cancel, kill, logs, download, set, archive, delete, label — ``cli/ex
 ``workspace``/``project``, ``preview-search``, ``deploy local``, ``version``.
 """
 import argparse
+import base64
 import json
 import os
 import pathlib
@@ -128,6 +129,42 @@ def experiment_create(args: argparse.Namespace) -> int:
         pass
     if args.follow_first_trial and not args.paused:
         return _follow_trial_logs(sess, eid)
+    return 0
+
+
+def experiment_continue(args: argparse.Namespace) -> int:
+    """``det experiment continue ID [--config-file f] [--config k=v]`` (reference ``cli/experiment.py`` ``continue``)."""
+    cfg: Dict[str, Any] = {}
+    if args.config_file:
+        cfg = yaml.safe_load(pathlib.Path(args.config_file).read_text()) or {}
+    _parse_config_overrides(cfg, args.config)
+    sess = _session(args)
+    sess.post("/api/v1/experiments/continue", json={"id": args.experiment_id, "overrideConfig": yaml.safe_dump(cfg) if cfg else None})
+    print(f"Continued experiment {args.experiment_id}")
+    if args.follow_first_trial:
+        return _follow_trial_logs(sess, args.experiment_id)
+    return 0
+
+
+def experiment_move(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    ws = [w for w in sess.get("/api/v1/workspaces", params={"name": args.workspace}).json()["workspaces"] if w["name"] == args.workspace]
+    if not ws:
+        raise SystemExit(f"workspace {args.workspace!r} not found")
+    pj = [p for p in sess.get(f"/api/v1/workspaces/{ws[0]['id']}/projects").json()["projects"] if p["name"] == args.project]
+    if not pj:
+        raise SystemExit(f"project {args.project!r} not found in workspace {args.workspace!r}")
+    sess.post(f"/api/v1/experiments/{args.experiment_id}/move", json={"destinationProjectId": pj[0]["id"]})
+    print(f"Moved experiment {args.experiment_id} to project {args.project}")
+    return 0
+
+
+def experiment_download_model_def(args: argparse.Namespace) -> int:
+    sess = _session(args)
+    blob = base64.b64decode(sess.get(f"/api/v1/experiments/{args.experiment_id}/model_def").json()["b64Tgz"])
+    out = pathlib.Path(args.output_dir) / f"experiment_{args.experiment_id}_model_def.tgz"
+    out.write_bytes(blob)
+    print(f"Wrote {out} ({len(blob)} bytes)")
     return 0
 
 
@@ -841,6 +878,21 @@ def make_parser() -> argparse.ArgumentParser:
     a = e.add_parser("config")
     a.add_argument("experiment_id", type=int)
     a.set_defaults(fn=experiment_config)
+    a = e.add_parser("continue")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("--config-file")
+    a.add_argument("--config", action="append")
+    a.add_argument("-f", "--follow-first-trial", action="store_true")
+    a.set_defaults(fn=experiment_continue)
+    a = e.add_parser("move")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("workspace")
+    a.add_argument("project")
+    a.set_defaults(fn=experiment_move)
+    a = e.add_parser("download-model-def")
+    a.add_argument("experiment_id", type=int)
+    a.add_argument("--output-dir", default=".")
+    a.set_defaults(fn=experiment_download_model_def)
     a = e.add_parser("wait")
     a.add_argument("experiment_id", type=int)
     a.add_argument("--polling-interval", type=float, default=5)

@@ -522,6 +522,12 @@ class Determined:
                                                             "projectId": project_id, "template": template}).json()
         return Experiment(self._session, r["experiment"]["id"], r["experiment"])
 
+    def continue_experiment(self, experiment_id: int, config: Union[str, Dict[str, Any], None] = None) -> Experiment:
+        """Re-open a finished single-trial experiment; ``config`` holds overrides such as a larger ``searcher.max_length``."""
+        text = yaml.safe_dump(config) if isinstance(config, dict) else config
+        r = self._session.post("/api/v1/experiments/continue", json={"id": experiment_id, "overrideConfig": text}).json()
+        return Experiment(self._session, experiment_id, r["experiment"])
+
     def get_experiment(self, experiment_id: int) -> Experiment:
         return Experiment(self._session, experiment_id, self._session.get(f"/api/v1/experiments/{experiment_id}").json()["experiment"])
 

@@ -457,6 +457,25 @@ route("POST", "/api/v1/experiments/{eid}/cancel")(_exp_action("cancel"))
 route("POST", "/api/v1/experiments/{eid}/kill")(_exp_action("kill"))
 
 
+@route("POST", "/api/v1/experiments/continue")
+def continue_experiment(ctx: Ctx) -> Any:
+    """Re-open a finished single-trial experiment, optionally with config overrides (``overrideConfig``: YAML text or object)."""
+    b = ctx.body or {}
+    try:
+        exp = ctx.m.continue_experiment(int(b.get("id")), b.get("overrideConfig") or None)
+    except core.Conflict as e:
+        raise HTTPError(409, str(e))
+    row = ctx.m.db.one("SELECT * FROM experiments WHERE id=?", (exp.id,))
+    return {"experiment": exp_json(ctx.m, row), "warnings": []}
+
+
+@route("POST", "/api/v1/experiments/{eid}/move")
+def move_experiment(ctx: Ctx, eid: str) -> Any:
+    """Move an experiment to another project (``destinationProjectId``)."""
+    ctx.m.move_experiment(int(eid), int((ctx.body or {}).get("destinationProjectId")))
+    return {}
+
+
 @route("POST", "/api/v1/experiments/{eid}/archive")
 def archive_experiment(ctx: Ctx, eid: str) -> Any:
     row = _exp_row(ctx, eid)

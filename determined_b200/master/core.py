@@ -663,6 +663,75 @@ class Master:
                 exp.start()
         return exp, cfg
 
+    def continue_experiment(self, eid: int, override: Any = None) -> Experiment:
+        """Re-open a finished single-trial experiment (reference ``api_experiment.go`` ``ContinueExperiment``): the same trial
+        trains on from its latest checkpoint, typically with a larger ``searcher.max_length`` from ``override``.  A completed
+        experiment must ask for more training than it has done; an errored / cancelled one may simply be retried."""
+        from determined_b200.master.searcher import methods as S_methods
+
+        with self.lock:
+            live = self.experiments.get(eid)
+            if live is not None and live.state not in TERMINAL:
+                raise Conflict(f"experiment {eid} is {live.state}; only finished experiments can be continued")
+            row = self.db.one("SELECT * FROM experiments WHERE id=?", (eid,))
+            if row is None:
+                raise NotFound(f"experiment {eid} not found")
+            if row["state"] not in TERMINAL:
+                raise Conflict(f"experiment {eid} is {row['state']}; only finished experiments can be continued")
+            cfg = dbmod.U(row["config"], {})
+            if override:
+                cfg = expconf.merge(expconf.parse(override), cfg)
+                expconf.validate_sanity(cfg)
+                expconf.validate_complete(cfg)
+            if cfg["searcher"]["name"] != "single":
+                raise expconf.ConfigError([f"<config>.searcher.name: only single-trial experiments can be continued, not {cfg['searcher']['name']}"])
+            prev_state = row["state"]
+            self.db.exec("UPDATE experiments SET state=?, config=?, end_time=NULL WHERE id=?", (ACTIVE, dbmod.J(cfg), eid))
+            exp = self._hydrate(self.db.one("SELECT * FROM experiments WHERE id=?", (eid,)))
+            if len(exp.trials) != 1:
+                self.db.exec("UPDATE experiments SET state=?, config=? WHERE id=?", (prev_state, row["config"], eid))
+                raise Conflict(f"experiment {eid} has {len(exp.trials)} trials; exactly one is needed to continue")
+            t = next(iter(exp.trials.values()))
+            method = exp.searcher.method
+            assert isinstance(method, S_methods.RandomSearch)
+            if prev_state == COMPLETED and t.completed_units >= method.max_length:
+                self.db.exec("UPDATE experiments SET state=?, config=? WHERE id=?", (prev_state, row["config"], eid))
+                raise Conflict(f"experiment {eid} already trained {t.completed_units} units; raise searcher.max_length above that to continue")
+            # a fresh single-trial search that has already created this trial and still waits for its one operation
+            seed = int((cfg.get("reproducibility") or {}).get("experiment_seed") or 0)
+            exp.searcher = S.Searcher(seed, method, cfg.get("hyperparameters") or {})
+            method.s.update(created_trials=1, pending_trials=1)
+            exp.searcher.trials_requested = 1
+            exp.searcher.trials_created[t.request_id] = True
+            exp.searcher.trial_progress[t.request_id] = float(t.completed_units)
+            exp.shutdown_requested = False
+            exp.state = ACTIVE
+            t.state, t.restarts, t.early_exit_reason, t.cancel_retries = ACTIVE, 0, None, False
+            t.target = max(method.max_length, t.completed_units)
+            t.ops = [t.target] if t.target > t.completed_units else []
+            t.close_requested = True
+            self.db.exec("UPDATE trials SET end_time=NULL WHERE id=?", (t.id,))
+            self.db.exec("UPDATE tasks SET state='ACTIVE', end_time=NULL WHERE id=?", (t.task_id,))
+            t.persist()
+            self.experiments[eid] = exp
+            self.trials[t.id] = t
+            if not t.ops:                         # nothing left to train (an errored run that had in fact finished): close it again
+                exp.process_operations([])
+                queue: List[Any] = []
+                exp._maybe_finish_trial(t, queue)
+                exp.process_operations(queue)
+            exp.persist()
+            logger.info("experiment %d continued: trial %d trains on from %d to %d", eid, t.id, t.completed_units, t.target)
+        self.kick()
+        return exp
+
+    def move_experiment(self, eid: int, project_id: int) -> None:
+        if self.db.one("SELECT id FROM projects WHERE id=?", (project_id,)) is None:
+            raise NotFound(f"project {project_id} not found")
+        if self.db.one("SELECT id FROM experiments WHERE id=?", (eid,)) is None:
+            raise NotFound(f"experiment {eid} not found")
+        self.db.exec("UPDATE experiments SET project_id=? WHERE id=?", (project_id, eid))
+
     def get_experiment(self, eid: int) -> Experiment:
         with self.lock:
             exp = self.experiments.get(eid)

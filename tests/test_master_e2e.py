@@ -216,3 +216,27 @@ def test_master_restart_restores_experiments(tmp_path):
     assert e2.searcher.trials_requested == 3
     m2.schedule_once()
     assert len(m2.allocations) == 2          # re-queued after restart
+
+
+def test_continue_extends_a_finished_experiment_and_move_changes_project(cluster):
+    m, sess, tmp = cluster
+    eid = create(sess, BASE)
+    assert wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR"}) == "STATE_COMPLETED", dump_logs(sess, eid)
+    tid = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"][0]["id"]
+    # same length again: refused
+    with pytest.raises(api.errors.APIException):
+        sess.post("/api/v1/experiments/continue", json={"id": eid})
+    out = sess.post("/api/v1/experiments/continue", json={"id": eid, "overrideConfig": yaml.safe_dump({"searcher": {"max_length": {"batches": 40}}})}).json()
+    assert out["experiment"]["state"] in ("STATE_ACTIVE", "STATE_RUNNING", "STATE_QUEUED")
+    assert wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR"}) == "STATE_COMPLETED", dump_logs(sess, eid)
+    trials = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"]
+    assert len(trials) == 1 and trials[0]["id"] == tid and trials[0]["totalBatchesProcessed"] == 40 and trials[0]["state"] == "STATE_COMPLETED"
+    logs = "".join(l["log"] for l in sess.get(f"/api/v1/trials/{tid}/logs").json()["logs"])
+    assert "Restoring trial from checkpoint" in logs, "the continued run must resume, not start over"
+    val = [x["totalBatches"] for x in sess.get(f"/api/v1/trials/{tid}/metrics").json()["metrics"] if x["group"] == "validation"]
+    assert val[-1] == 40 and 24 in val
+    ws = sess.post("/api/v1/workspaces", json={"name": "w2"}).json()["workspace"]
+    pj = sess.post(f"/api/v1/workspaces/{ws['id']}/projects", json={"name": "p2"}).json()["project"]
+    sess.post(f"/api/v1/experiments/{eid}/move", json={"destinationProjectId": pj["id"]})
+    assert sess.get(f"/api/v1/experiments/{eid}").json()["experiment"]["projectId"] == pj["id"]
+    assert [e["id"] for e in sess.get("/api/v1/experiments", params={"projectId": pj["id"]}).json()["experiments"]] == [eid]
