@@ -324,6 +324,23 @@ def trial_kill(args: argparse.Namespace) -> int:
     return 0
 
 
+def trial_download(args: argparse.Namespace) -> int:
+    """``det trial download ID [--latest | --best | --uuid U] [-o DIR]``: fetch one of the trial's checkpoints."""
+    t = _sdk(args).get_trial(args.trial_id)
+    ck = t.select_checkpoint(uuid=args.uuid) if args.uuid else t.select_checkpoint(best=True) if args.best else t.select_checkpoint(latest=True)
+    if ck is None:
+        raise SystemExit(f"trial {args.trial_id} has no matching checkpoint")
+    path = ck.download(args.output_dir)
+    print(f"Local checkpoint path: {path}")
+    return 0
+
+
+def agent_enable(args: argparse.Namespace) -> int:
+    _session(args).post(f"/api/v1/agents/{args.agent_id}/{'enable' if args.enable else 'disable'}")
+    print(f"{'Enabled' if args.enable else 'Disabled'} agent {args.agent_id}")
+    return 0
+
+
 def checkpoint_describe(args: argparse.Namespace) -> int:
     c = _session(args).get(f"/api/v1/checkpoints/{args.uuid}").json()["checkpoint"]
     if args.json:
@@ -470,6 +487,9 @@ def model_cmd(args: argparse.Namespace) -> int:
         _table([[m.model_id, m.name, m.description, json.dumps(m.metadata)]], ["ID", "Name", "Description", "Metadata"])
         print()
         _table([[v.model_version, v.checkpoint.uuid if v.checkpoint else None, v.name, v.comment] for v in m.list_versions()], ["Version", "Checkpoint", "Name", "Comment"])
+    elif args.action == "list-versions":
+        _table([[v.model_version, v.checkpoint.uuid if v.checkpoint else None, v.name, v.comment] for v in d.get_model(args.name).list_versions()],
+               ["Version", "Checkpoint", "Name", "Comment"], args.json)
     elif args.action == "register-version":
         v = d.get_model(args.name).register_version(args.uuid)
         print(f"Registered version {v.model_version} of model {args.name}")
@@ -511,6 +531,12 @@ def user_cmd(args: argparse.Namespace) -> int:
         if not us:
             raise SystemExit(f"user {args.username} not found")
         sess.patch(f"/api/v1/users/{us[0]['id']}", json={"user": {"active": args.action == "activate"}})
+    elif args.action == "rename":
+        us = [u for u in sess.get("/api/v1/users").json()["users"] if u["username"] == args.username]
+        if not us:
+            raise SystemExit(f"user {args.username} not found")
+        sess.patch(f"/api/v1/users/{us[0]['id']}", json={"user": {"username": args.new_username}})
+        print(f"Renamed user {args.username} to {args.new_username}")
     elif args.action == "change-password":
         import getpass
 
@@ -925,6 +951,14 @@ def make_parser() -> argparse.ArgumentParser:
     a = t.add_parser("kill")
     a.add_argument("trial_id", type=int)
     a.set_defaults(fn=trial_kill)
+    a = t.add_parser("download")
+    a.add_argument("trial_id", type=int)
+    g = a.add_mutually_exclusive_group()
+    g.add_argument("--latest", action="store_true", default=True)
+    g.add_argument("--best", action="store_true")
+    g.add_argument("--uuid")
+    a.add_argument("-o", "--output-dir")
+    a.set_defaults(fn=trial_download)
 
     # checkpoint
     c = sub.add_parser("checkpoint", aliases=["c"], help="manage checkpoints").add_subparsers(dest="sub")
@@ -967,6 +1001,10 @@ def make_parser() -> argparse.ArgumentParser:
     a = ag.add_parser("list", aliases=["ls"])
     outfmt(a)
     a.set_defaults(fn=agent_list)
+    for name, en in (("enable", True), ("disable", False)):
+        a = ag.add_parser(name)
+        a.add_argument("agent_id")
+        a.set_defaults(fn=agent_enable, enable=en)
     sl = sub.add_parser("slot", aliases=["s"]).add_subparsers(dest="sub")
     a = sl.add_parser("list", aliases=["ls"])
     outfmt(a)
@@ -1001,7 +1039,7 @@ def make_parser() -> argparse.ArgumentParser:
         a.set_defaults(fn=template_cmd, action=name)
 
     md = sub.add_parser("model").add_subparsers(dest="sub")
-    for name in ("list", "create", "describe", "register-version", "delete"):
+    for name in ("list", "create", "describe", "list-versions", "register-version", "delete"):
         a = md.add_parser(name)
         if name != "list":
             a.add_argument("name")
@@ -1013,10 +1051,12 @@ def make_parser() -> argparse.ArgumentParser:
         a.set_defaults(fn=model_cmd, action=name)
 
     us = sub.add_parser("user", aliases=["u"]).add_subparsers(dest="sub")
-    for name in ("login", "logout", "whoami", "list", "create", "activate", "deactivate", "change-password"):
+    for name in ("login", "logout", "whoami", "list", "create", "activate", "deactivate", "rename", "change-password"):
         a = us.add_parser(name)
-        if name in ("login", "create", "activate", "deactivate"):
+        if name in ("login", "create", "activate", "deactivate", "rename"):
             a.add_argument("username")
+        if name == "rename":
+            a.add_argument("new_username")
         if name == "create":
             a.add_argument("--admin", action="store_true")
         outfmt(a)

@@ -270,3 +270,20 @@ def test_sdk_users_workspaces_projects_pools(cluster):
     m = d.create_model("m1", labels=["a", "b"])
     assert d.get_model_labels() == ["a", "b"] and d.get_model_by_id(getattr(m, "model_id", getattr(m, "id", None))).name == "m1"
     assert list(d.iter_trials_metrics([], "training")) == []
+
+
+def test_cli_agent_user_model_additions(cluster):
+    def ok(*argv):
+        rc, out = run(*argv)
+        assert rc == 0, out
+        return out
+
+    m = cluster[0]
+    assert "Disabled agent" in ok("agent", "disable", m.agent_id)
+    assert not m.pool.agents[m.agent_id].enabled
+    assert "Enabled agent" in ok("agent", "enable", m.agent_id)
+    ok("-u", "admin", "user", "create", "bob")
+    assert "Renamed user bob to robert" in ok("-u", "admin", "user", "rename", "bob", "robert")
+    assert "robert" in ok("user", "list")
+    ok("model", "create", "mm", "--description", "d")
+    assert "Version" in ok("model", "list-versions", "mm")
