@@ -240,3 +240,19 @@ def test_continue_extends_a_finished_experiment_and_move_changes_project(cluster
     sess.post(f"/api/v1/experiments/{eid}/move", json={"destinationProjectId": pj["id"]})
     assert sess.get(f"/api/v1/experiments/{eid}").json()["experiment"]["projectId"] == pj["id"]
     assert [e["id"] for e in sess.get("/api/v1/experiments", params={"projectId": pj["id"]}).json()["experiments"]] == [eid]
+
+
+def test_two_slot_trial_runs_data_parallel_over_gloo(cluster):
+    """slots_per_trial=2 on CPU slots: launcher -> two ranks -> gloo gradient averaging + object collectives -> one trial result."""
+    m, sess, tmp = cluster
+    cfg = json.loads(json.dumps(BASE))
+    cfg["resources"] = {"slots_per_trial": 2}
+    cfg["hyperparameters"]["global_batch_size"] = 8
+    eid = create(sess, cfg)
+    assert wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR"}) == "STATE_COMPLETED", dump_logs(sess, eid)
+    t = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"][0]
+    assert t["totalBatchesProcessed"] == 24
+    ranks = {l.get("rankId") for l in sess.get(f"/api/v1/trials/{t['id']}/logs").json()["logs"]}
+    assert ranks & {0, 1, None}
+    alloc = m.db.one("SELECT slots FROM allocations WHERE trial_id=?", (t["id"],))
+    assert alloc["slots"] == 2
