@@ -41,7 +41,7 @@ def main(argv=None) -> int:
     m = core.Master(db_path=dbp, host=host, port=port, scheduler_type=args.scheduler or sch.get("type", "fair_share"),
                     fitting_policy=args.fitting_policy or sch.get("fitting_policy", "best"),
                     preemption=bool((sch.get("preemption") or {}).get("enabled", True)), num_slots=args.slots,
-                    cluster_defaults=defaults)
+                    cluster_defaults=defaults, resource_pools=cfg.get("resource_pools") or None)
     m.agent_token = args.agent_token or (cfg.get("security") or {}).get("agent_token")
     tel = cfg.get("telemetry") or {}
     otel = args.otel_endpoint or (tel.get("otel_endpoint") if tel.get("otel_enabled", True) else None)

@@ -89,8 +89,12 @@ class AgentRegistry:
         with m.lock, self.lock:
             old = self.agents.get(agent_id)
             ag = RemoteAgent(agent_id, body)
-            if ag.resource_pool != m.pool.name:
-                raise ValueError(f"unknown resource pool {ag.resource_pool!r}")
+            pool = m.pools.get(ag.resource_pool)
+            if pool is None:
+                raise ValueError(f"unknown resource pool {ag.resource_pool!r} (have: {', '.join(sorted(m.pools))})")
+            elsewhere = m.pool_of_agent(agent_id)
+            if elsewhere is not None and elsewhere is not pool:
+                raise ValueError(f"agent {agent_id} is already registered in pool {elsewhere.name!r}")
             if old is not None:
                 # reconnect: keep the tasks the agent still runs, fail the ones it lost
                 for cid, sink in old.containers.items():
@@ -100,10 +104,10 @@ class AgentRegistry:
                         self._lost(sink, cid, "agent restarted without this task")
             orphans = [c for c in running if c not in ag.containers]
             self.agents[agent_id] = ag
-            pa = m.pool.agents.get(agent_id)
+            pa = pool.agents.get(agent_id)
             if pa is None or pa.num_slots != len(ag.slots):
                 pa = scheduler.Agent(agent_id, len(ag.slots))
-                m.pool.add_agent(pa)
+                pool.add_agent(pa)
             pa.enabled = True
             for cid in orphans:                       # tasks of a previous master life: nobody waits for them
                 ag.push({"type": "kill", "container_id": cid, "signal": "KILL"})
@@ -190,7 +194,8 @@ class AgentRegistry:
             if ag is None:
                 return
             ag.connected = False
-            pa = m.pool.agents.get(agent_id)
+            owner = m.pool_of_agent(agent_id)
+            pa = owner.agents.get(agent_id) if owner is not None else None
             if pa is not None:
                 pa.enabled = False
             lost = list(ag.containers.items())

@@ -185,6 +185,9 @@ def master_info(ctx: Ctx) -> Any:
 def master_config(ctx: Ctx) -> Any:
     return {"config": {"resource_manager": {"type": "agent", "scheduler": {"type": ctx.m.pool.scheduler, "fitting_policy": ctx.m.pool.policy,
                                                                             "preemption": {"enabled": ctx.m.pool.preemption}}},
+                       "resource_pools": [{"pool_name": pl.name, "description": ctx.m.pool_descriptions.get(pl.name, ""),
+                                           "scheduler": {"type": pl.scheduler, "fitting_policy": pl.policy, "preemption": {"enabled": pl.preemption}}}
+                                          for pl in ctx.m.pools.values()],
                        "checkpoint_storage": ctx.m.cluster_defaults.get("checkpoint_storage")}}
 
 
@@ -536,7 +539,13 @@ def patch_experiment(ctx: Ctx, eid: str) -> Any:
     res = b.get("resources") or {}
     with ctx.m.lock:
         live = ctx.m.experiments.get(int(eid))
-        for key, setter in (("priority", ctx.m.pool.set_priority), ("weight", ctx.m.pool.set_weight), ("maxSlots", ctx.m.pool.set_max_slots)):
+        def on_all_pools(name: str) -> Callable[[str, Any], None]:
+            def apply(job_id: str, value: Any) -> None:
+                for pl in ctx.m.pools.values():
+                    getattr(pl, name)(job_id, value)
+            return apply
+
+        for key, setter in (("priority", on_all_pools("set_priority")), ("weight", on_all_pools("set_weight")), ("maxSlots", on_all_pools("set_max_slots"))):
             if res.get(key) is not None:
                 ck = {"maxSlots": "max_slots"}.get(key, key)
                 cfg.setdefault("resources", {})[ck] = res[key]
@@ -1102,7 +1111,8 @@ def _any_agent_json(m: core.Master, agent_id: str) -> Dict[str, Any]:
     ra = m.agents.get(agent_id)
     if ra is None:
         raise HTTPError(404, "agent not found")
-    j = ra.to_json(m.pool.agents.get(agent_id))
+    owner = m.pool_of_agent(agent_id)
+    j = ra.to_json(owner.agents.get(agent_id) if owner is not None else None)
     j["registeredTime"] = _ts(ra.registered)
     return j
 
@@ -1154,10 +1164,11 @@ def agent_poll(ctx: Ctx, agent_id: str) -> Any:
 
 
 def _set_enabled(ctx: Ctx, agent_id: str, slot: Optional[str], enabled: bool) -> Any:
-    if agent_id not in ctx.m.pool.agents:
+    owner = ctx.m.pool_of_agent(agent_id)
+    if owner is None:
         raise HTTPError(404, "agent not found")
     with ctx.m.lock:
-        ag = ctx.m.pool.agents[agent_id]
+        ag = owner.agents[agent_id]
         if slot is None:
             ag.enabled = enabled
         else:
@@ -1165,7 +1176,7 @@ def _set_enabled(ctx: Ctx, agent_id: str, slot: Optional[str], enabled: bool) ->
                 ag.slot_enabled = [True] * ag.num_slots
             ag.slot_enabled[int(slot)] = enabled
     ctx.m.kick()
-    return {"agent": _agent_json(ctx.m)}
+    return {"agent": _any_agent_json(ctx.m, agent_id)}
 
 
 route("POST", "/api/v1/agents/{agent_id}/enable")(lambda ctx, agent_id: _set_enabled(ctx, agent_id, None, True))
@@ -1176,30 +1187,36 @@ route("POST", "/api/v1/agents/{agent_id}/slots/{slot}/disable")(lambda ctx, agen
 
 @route("GET", "/api/v1/resource-pools")
 def resource_pools(ctx: Ctx) -> Any:
-    p = ctx.m.pool
-    ag = p.agents[ctx.m.agent_id]
-    live = [a for a in p.agents.values() if a.enabled and a.num_slots]
-    return {"resourcePools": [{"name": p.name, "description": "one 8xB200 node", "type": "RESOURCE_POOL_TYPE_STATIC", "numAgents": max(len(live), 1),
-                               "slotsAvailable": sum(a.num_slots for a in live), "slotsUsed": sum(a.num_used() for a in p.agents.values()), "slotType": "DEVICE_TYPE_CUDA" if ctx.m.num_gpus else "DEVICE_TYPE_CPU",
-                               "defaultComputePool": True, "defaultAuxPool": True, "preemptible": p.preemption, "schedulerType": "SCHEDULER_TYPE_" + p.scheduler.upper(),
-                               "schedulerFittingPolicy": "FITTING_POLICY_" + p.policy.upper(), "slotsPerAgent": ag.num_slots, "location": "on-prem", "auxContainerCapacity": 100,
-                               "auxContainersRunning": len(ag.zero_slot_tasks)}], "pagination": {"total": 1}}
+    out = []
+    for p in ctx.m.pools.values():
+        live = [a for a in p.agents.values() if a.enabled and a.num_slots]
+        out.append({"name": p.name, "description": ctx.m.pool_descriptions.get(p.name, ""), "type": "RESOURCE_POOL_TYPE_STATIC", "numAgents": len(live),
+                    "slotsAvailable": sum(a.num_slots for a in live), "slotsUsed": sum(a.num_used() for a in p.agents.values()),
+                    "slotType": "DEVICE_TYPE_CUDA" if ctx.m.num_gpus else "DEVICE_TYPE_CPU", "defaultComputePool": p.name == "default",
+                    "defaultAuxPool": p.name == "default", "preemptible": p.preemption, "schedulerType": "SCHEDULER_TYPE_" + p.scheduler.upper(),
+                    "schedulerFittingPolicy": "FITTING_POLICY_" + p.policy.upper(), "slotsPerAgent": max((a.num_slots for a in p.agents.values()), default=0),
+                    "location": "on-prem", "auxContainerCapacity": 100 * max(len(p.agents), 1),
+                    "auxContainersRunning": sum(len(a.zero_slot_tasks) for a in p.agents.values())})
+    return {"resourcePools": out, "pagination": {"total": len(out)}}
 
 
 @route("GET", "/api/v1/job-queues-v2")
 @route("GET", "/api/v1/job-queues")
 def job_queue(ctx: Ctx) -> Any:
-    with ctx.m.lock:
-        rows = ctx.m.pool.job_queue()
+    """Jobs of one pool (``resourcePool=``) or of all pools."""
+    want = ctx.q("resourcePool")
     jobs: Dict[str, Dict[str, Any]] = {}
-    for r in rows:
-        j = jobs.setdefault(r["job_id"], {"jobId": r["job_id"], "type": "TYPE_EXPERIMENT", "entityId": r["job_id"].replace("exp-", ""), "priority": r["priority"],
-                                          "weight": r["weight"], "allocatedSlots": 0, "requestedSlots": 0, "resourcePool": ctx.m.pool.name, "name": r["name"],
-                                          "summary": {"state": "STATE_QUEUED", "jobsAhead": 0}})
-        j["requestedSlots"] += r["slots"]
-        if r["state"] == "SCHEDULED":
-            j["allocatedSlots"] += r["slots"]
-            j["summary"]["state"] = "STATE_SCHEDULED"
+    with ctx.m.lock:
+        per_pool = [(p.name, p.job_queue()) for p in ctx.m.pools.values() if not want or p.name == want]
+    for pname, rows in per_pool:
+        for r in rows:
+            j = jobs.setdefault(r["job_id"], {"jobId": r["job_id"], "type": "TYPE_EXPERIMENT", "entityId": r["job_id"].replace("exp-", ""), "priority": r["priority"],
+                                              "weight": r["weight"], "allocatedSlots": 0, "requestedSlots": 0, "resourcePool": pname, "name": r["name"],
+                                              "summary": {"state": "STATE_QUEUED", "jobsAhead": 0}})
+            j["requestedSlots"] += r["slots"]
+            if r["state"] == "SCHEDULED":
+                j["allocatedSlots"] += r["slots"]
+                j["summary"]["state"] = "STATE_SCHEDULED"
     return {"jobs": list(jobs.values()), "pagination": {"total": len(jobs)}}
 
 
@@ -1208,10 +1225,11 @@ def update_job_queue(ctx: Ctx) -> Any:
     with ctx.m.lock:
         for u in (ctx.body or {}).get("updates", []):
             jid = u.get("jobId")
-            if u.get("priority") is not None:
-                ctx.m.pool.set_priority(jid, int(u["priority"]))
-            if u.get("weight") is not None:
-                ctx.m.pool.set_weight(jid, float(u["weight"]))
+            for p in ctx.m.pools.values():
+                if u.get("priority") is not None:
+                    p.set_priority(jid, int(u["priority"]))
+                if u.get("weight") is not None:
+                    p.set_weight(jid, float(u["weight"]))
             for exp in ctx.m.experiments.values():
                 if exp.job_id == jid:
                     if u.get("priority") is not None:
@@ -1636,14 +1654,14 @@ def prometheus(ctx: Ctx) -> Any:
     """Prometheus text exposition (reference ``master/internal/prom``)."""
     m = ctx.m
     lines = ["# TYPE det_slots_total gauge", "# TYPE det_slots_used gauge", "# TYPE det_agent_connected gauge"]
-    for aid, ag in sorted(m.pool.agents.items()):
+    for aid, ag in sorted((a, g) for pl in m.pools.values() for a, g in pl.agents.items()):
         if aid == m.agent_id and not ag.num_slots:
             continue
         ra = m.agents.get(aid)
         lines += [f'det_slots_total{{agent="{aid}"}} {ag.num_slots}', f'det_slots_used{{agent="{aid}"}} {ag.num_used()}',
                   f'det_agent_connected{{agent="{aid}"}} {int(ra.connected) if ra is not None else 1}']
     lines += ["# TYPE det_allocations_running gauge", f"det_allocations_running {len(m.allocations)}",
-              "# TYPE det_pending_requests gauge", f"det_pending_requests {len(m.pool.pending)}", "# TYPE det_experiments gauge"]
+              "# TYPE det_pending_requests gauge", f"det_pending_requests {sum(len(pl.pending) for pl in m.pools.values())}", "# TYPE det_experiments gauge"]
     by_state: Dict[str, int] = {}
     for e in m.experiments.values():
         by_state[e.state] = by_state.get(e.state, 0) + 1

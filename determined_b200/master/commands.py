@@ -77,7 +77,7 @@ class CommandTask:
 
     def to_json(self) -> Dict[str, Any]:
         return {"id": self.id, "description": self.description, "state": "STATE_" + self.state, "startTime": self.start_time, "endTime": self.end_time,
-                "username": self.owner_name, "userId": self.owner_id, "resourcePool": self.mgr.master.pool.name, "exitStatus": self.exit_code,
+                "username": self.owner_name, "userId": self.owner_id, "resourcePool": (self.config.get("resources") or {}).get("resource_pool") or "default", "exitStatus": self.exit_code,
                 "jobId": self.id, "type": self.kind, "slots": self.slots, "slotIds": self.slot_ids, "config": self.config,
                 "serviceAddress": f"/proxy/{self.id}/" if self.service_port else None}
 
@@ -164,7 +164,7 @@ class CommandTask:
         m.db.exec("DELETE FROM sessions WHERE token=?", (self.token,))
         m.ports.release(self.service_port)
         with m.lock:
-            m.pool.release(self.pool_key)
+            m.release_request(self.pool_key)
         m.kick()
 
     def kill(self) -> None:
@@ -200,12 +200,13 @@ class CommandManager:
     def launch(self, kind: str, config: Dict[str, Any], owner_id: int, owner_name: str, body: Dict[str, Any]) -> CommandTask:
         t = CommandTask(self, TYPES[kind], config, owner_id, owner_name, body)
         m = self.master
+        res = config.get("resources") or {}
+        pool = m.pool_for(res)                   # unknown pool: refused before anything is recorded
         with m.lock:
             self.tasks[t.id] = t
             m.db.exec("INSERT INTO tasks(id,type,start_time,job_id,config,state,owner_id) VALUES(?,?,?,?,?,?,?)",
                       (t.id, t.kind, t.start_time, t.id, json.dumps(config), t.state, owner_id))
-            res = config.get("resources") or {}
-            m.pool.allocate(scheduler.AllocateRequest(t.pool_key, t.id, t.slots, priority=res.get("priority"), weight=float(res.get("weight", 1) or 1),
+            pool.allocate(scheduler.AllocateRequest(t.pool_key, t.id, t.slots, priority=res.get("priority"), weight=float(res.get("weight", 1) or 1),
                                                       preemptible=False, name=t.description, submit_time=time.time()))
         m.kick()
         return t

@@ -107,7 +107,7 @@ class Allocation:
         m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)",
                   (self.token, exp.owner_id, time.time() + 14 * 86400, t.task_id))
         m.db.exec("INSERT INTO allocations(id,task_id,trial_id,state,slots,slot_ids,start_time,resource_pool) VALUES(?,?,?,?,?,?,?,?)",
-                  (self.id, t.task_id, t.id, "RUNNING", self.slots, json.dumps(slot_ids), time.time(), m.pool.name))
+                  (self.id, t.task_id, t.id, "RUNNING", self.slots, json.dumps(slot_ids), time.time(), getattr(self, "pool_name", "default")))
         if remote:
             row = m.db.one("SELECT model_definition FROM experiments WHERE id=?", (exp.id,))
             m.agents.start(self.agent_id, self.id, self, [agents_mod.PYTHON_PLACEHOLDER, "-m", "determined_b200.exec.launch"], task_env, slot_ids,
@@ -538,7 +538,8 @@ class Master:
     def __init__(self, db_path: str = ":memory:", host: str = "127.0.0.1", port: int = 8080,
                  scheduler_type: str = "fair_share", fitting_policy: str = "best", preemption: bool = True,
                  num_slots: Optional[int] = None, work_dir: Optional[str] = None,
-                 cluster_defaults: Optional[Dict[str, Any]] = None, launch: bool = True) -> None:
+                 cluster_defaults: Optional[Dict[str, Any]] = None, launch: bool = True,
+                 resource_pools: Optional[List[Dict[str, Any]]] = None) -> None:
         self.db = dbmod.DB(db_path)
         self.host, self.port = host, port
         self.lock = threading.RLock()
@@ -550,8 +551,19 @@ class Master:
         self.num_gpus = len(gpus)
         n = num_slots if num_slots is not None else (len(gpus) or 1)
         self.slot_type = "cuda" if (self.num_gpus and num_slots is None) else "cpu"
-        self.pool = scheduler.ResourcePool("default", scheduler_type, fitting_policy, preemption)
-        self.pool.add_agent(scheduler.Agent(self.agent_id, n))      # num_slots=0: every slot comes from remote agents
+        # Resource pools (reference master.yaml ``resource_pools``): "default" always exists and owns this box's slots; more
+        # pools come from the config and are filled by agents that register into them.  Each pool runs its own scheduler.
+        self.pools: Dict[str, scheduler.ResourcePool] = {"default": scheduler.ResourcePool("default", scheduler_type, fitting_policy, preemption)}
+        self.pool_descriptions: Dict[str, str] = {"default": "this box"}
+        for rp in resource_pools or []:
+            name = str(rp.get("pool_name") or rp.get("name") or "")
+            if not name:
+                raise ValueError("resource_pools entries need a pool_name")
+            sch = rp.get("scheduler") or {}
+            pre = (sch.get("preemption") or {}).get("enabled", preemption) if isinstance(sch.get("preemption"), dict) else preemption
+            self.pools[name] = scheduler.ResourcePool(name, sch.get("type", scheduler_type), sch.get("fitting_policy", fitting_policy), bool(pre))
+            self.pool_descriptions[name] = str(rp.get("description") or "")
+        self.pools["default"].add_agent(scheduler.Agent(self.agent_id, n))      # num_slots=0: every slot comes from remote agents
         self.agents = agents_mod.AgentRegistry(self)
         from determined_b200.master import portregistry
 
@@ -576,6 +588,28 @@ class Master:
     @property
     def url(self) -> str:
         return f"http://{self.host}:{self.port}"
+
+    @property
+    def pool(self) -> scheduler.ResourcePool:
+        """The default pool (what every caller meant while there was only one)."""
+        return self.pools["default"]
+
+    def pool_for(self, resources: Optional[Dict[str, Any]]) -> scheduler.ResourcePool:
+        name = (resources or {}).get("resource_pool") or "default"
+        if name not in self.pools:
+            raise expconf.ConfigError([f"<config>.resources.resource_pool: unknown resource pool {name!r} (have: {', '.join(sorted(self.pools))})"])
+        return self.pools[name]
+
+    def pool_of_agent(self, agent_id: str) -> Optional[scheduler.ResourcePool]:
+        for p in self.pools.values():
+            if agent_id in p.agents:
+                return p
+        return None
+
+    def release_request(self, key: str) -> None:
+        """Drop a request / allocation from whichever pool holds it (release is idempotent)."""
+        for p in self.pools.values():
+            p.release(key)
 
     # -- boot / shutdown -----------------------------------------------------------------------------
     def start(self) -> None:
@@ -642,7 +676,7 @@ class Master:
         if (cfg.get("reproducibility") or {}).get("experiment_seed") is None:
             cfg.setdefault("reproducibility", {})["experiment_seed"] = int(time.time()) & 0x7FFFFFFF
         slots = int((cfg.get("resources") or {}).get("slots_per_trial", 1))
-        cap = max((a.num_slots for a in self.pool.agents.values()), default=0)      # a trial runs on one agent
+        cap = max((a.num_slots for a in self.pool_for(cfg.get("resources")).agents.values()), default=0)      # a trial runs on one agent
         if cap and slots > cap:           # no slots at all yet (agents still connecting): queue it
             raise expconf.ConfigError([f"<config>.resources.slots_per_trial: {slots} exceeds the {cap} slots of the largest agent"])
         S.new_search_method(cfg["searcher"])     # fail early on impossible searcher configs
@@ -777,53 +811,28 @@ class Master:
             # submit / withdraw requests
             for exp in list(self.experiments.values()):
                 res = exp.config.get("resources") or {}
+                try:
+                    pool = self.pool_for(res)
+                except expconf.ConfigError:
+                    pool = self.pool                 # the pool went away with a config change: fall back rather than strand the trial
                 for t in exp.trials.values():
                     rid = f"req-{t.id}-{t.run_id}"
                     if t.wants_resources():
-                        if rid not in self.pool.pending and not any(a.trial is t for a in self.allocations.values()):
-                            self.pool.allocate(scheduler.AllocateRequest(
+                        if rid not in pool.pending and not any(a.trial is t for a in self.allocations.values()):
+                            pool.allocate(scheduler.AllocateRequest(
                                 rid, exp.job_id, exp.slots_per_trial(), priority=res.get("priority"),
                                 weight=float(res.get("weight", 1) or 1), max_slots=res.get("max_slots"),
                                 preemptible=True, name=f"exp {exp.id} trial {t.id}",
                                 submit_time=time.time()))
-                    elif rid in self.pool.pending:
-                        self.pool.release(rid)
+                    elif rid in pool.pending:
+                        pool.release(rid)
             self.agents.reap()
-            d = self.pool.tick()
-            for req, asg in d.to_allocate:
-                # a task runs on one host: the (single-node) launch layer has no cross-agent rendezvous
-                hosts = [a for a, sl in asg.items() if sl] or list(asg)[:1]
-                agent_id = hosts[0] if hosts else self.agent_id
-                if len(hosts) > 1:
-                    logger.error("request %s was spread over agents %s; only single-agent placements can run", req.allocation_id, hosts)
-                    self.pool.release(req.allocation_id)
-                    continue
-                if req.allocation_id.startswith("cmd-"):          # command / shell / notebook / tensorboard task
-                    if not self.commands.on_assigned(req.allocation_id, sorted(s for slots in asg.values() for s in slots), agent_id):
-                        self.pool.release(req.allocation_id)
-                    continue
-                tid = int(req.allocation_id.split("-")[1])
-                t = self.trials.get(tid)
-                if t is None or not t.wants_resources():
-                    self.pool.release(req.allocation_id)
-                    continue
-                alloc = Allocation(self, t, req.allocation_id + "-" + uuid.uuid4().hex[:8], req.slots_needed)
-                alloc.pool_key = req.allocation_id
-                t.allocation = alloc
-                self.allocations[alloc.id] = alloc
-                slot_ids = sorted(s for slots in asg.values() for s in slots)
-                if self.launch_enabled:
-                    try:
-                        alloc.start(slot_ids, agent_id)
-                    except Exception:
-                        logger.exception("failed to start allocation %s", alloc.id)
-                        alloc.exit_code = 1
-                        alloc.state = "TERMINATED"
-                        self.on_allocation_exit(alloc)
-                else:
-                    alloc.slot_ids = slot_ids
-                    alloc.state = "RUNNING"
-            for rid in d.to_release:
+            to_release: List[str] = []
+            for pool in self.pools.values():
+                d = pool.tick()
+                to_release += list(d.to_release)
+                self._start_assigned(pool, d.to_allocate)
+            for rid in to_release:
                 for a in self.allocations.values():
                     if getattr(a, "pool_key", None) == rid:
                         logger.info("preempting allocation %s (scheduler)", a.id)
@@ -834,10 +843,46 @@ class Master:
                     logger.warning("allocation %s ignored preemption for %.0fs; killing", a.id, PREEMPT_KILL_DEADLINE_S)
                     a.kill()
 
+    def _start_assigned(self, pool: scheduler.ResourcePool, assigned: Any) -> None:
+        for req, asg in assigned:
+            # a task runs on one host: the (single-node) launch layer has no cross-agent rendezvous
+            hosts = [a for a, sl in asg.items() if sl] or list(asg)[:1]
+            agent_id = hosts[0] if hosts else self.agent_id
+            if len(hosts) > 1:
+                logger.error("request %s was spread over agents %s; only single-agent placements can run", req.allocation_id, hosts)
+                pool.release(req.allocation_id)
+                continue
+            if req.allocation_id.startswith("cmd-"):          # command / shell / notebook / tensorboard task
+                if not self.commands.on_assigned(req.allocation_id, sorted(s for slots in asg.values() for s in slots), agent_id):
+                    pool.release(req.allocation_id)
+                continue
+            tid = int(req.allocation_id.split("-")[1])
+            t = self.trials.get(tid)
+            if t is None or not t.wants_resources():
+                pool.release(req.allocation_id)
+                continue
+            alloc = Allocation(self, t, req.allocation_id + "-" + uuid.uuid4().hex[:8], req.slots_needed)
+            alloc.pool_key = req.allocation_id
+            alloc.pool_name = pool.name
+            t.allocation = alloc
+            self.allocations[alloc.id] = alloc
+            slot_ids = sorted(s for slots in asg.values() for s in slots)
+            if self.launch_enabled:
+                try:
+                    alloc.start(slot_ids, agent_id)
+                except Exception:
+                    logger.exception("failed to start allocation %s", alloc.id)
+                    alloc.exit_code = 1
+                    alloc.state = "TERMINATED"
+                    self.on_allocation_exit(alloc)
+            else:
+                alloc.slot_ids = slot_ids
+                alloc.state = "RUNNING"
+
     def on_allocation_exit(self, alloc: Allocation) -> None:
         with self.lock:
             self.allocations.pop(alloc.id, None)
-            self.pool.release(getattr(alloc, "pool_key", alloc.id))
+            self.release_request(getattr(alloc, "pool_key", alloc.id))
             alloc.trial.experiment.allocation_exited(alloc.trial, alloc)
         self.kick()
 

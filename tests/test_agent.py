@@ -116,3 +116,42 @@ def test_agent_restart_reattaches_and_disconnect_fails_tasks(cluster, monkeypatc
     _wait(lambda: sess.get(f"/api/v1/commands/{cid}").json()["command"]["state"] == "STATE_TERMINATED", 30, "task failed after disconnect")
     assert not sess.get("/api/v1/agents/agent-1").json()["agent"]["connected"]
     os.kill(pid, signal.SIGKILL)
+
+
+def test_resource_pools_route_work_to_the_agents_registered_in_them(tmp_path):
+    """master.yaml `resource_pools`: a second pool with its own scheduler; an agent joins it; `resources.resource_pool` sends an
+    experiment and a command there; unknown pools are refused."""
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=1, work_dir=str(tmp_path / "work"),
+                    cluster_defaults={"checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpt")}},
+                    resource_pools=[{"pool_name": "aux", "description": "extra box", "scheduler": {"type": "priority", "fitting_policy": "worst"}}])
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    a = Agent(m.url, "aux-1", slots=2, slot_type="cpu", resource_pool="aux", work_dir=str(tmp_path / "aux-1"))
+    th = threading.Thread(target=a.run, daemon=True)
+    th.start()
+    try:
+        sess = api.authentication.login(m.url, "determined", "")
+        _wait(lambda: any(x["id"] == "aux-1" for x in sess.get("/api/v1/agents").json()["agents"]), what="agent registration")
+        pools = {p["name"]: p for p in sess.get("/api/v1/resource-pools").json()["resourcePools"]}
+        assert set(pools) == {"default", "aux"} and pools["aux"]["slotsAvailable"] == 2 and pools["default"]["slotsAvailable"] == 1
+        assert pools["aux"]["schedulerType"] == "SCHEDULER_TYPE_PRIORITY" and pools["aux"]["schedulerFittingPolicy"] == "FITTING_POLICY_WORST"
+        assert sess.get("/api/v1/agents/aux-1").json()["agent"]["resourcePools"] == ["aux"]
+        cfg = dict(BASE, resources={"slots_per_trial": 2, "resource_pool": "aux"})          # 2 slots: only the aux agent can hold it
+        eid = create(sess, cfg)
+        assert wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR"}) == "STATE_COMPLETED", dump_logs(sess, eid)
+        row = m.db.one("SELECT resource_pool FROM allocations WHERE trial_id IN (SELECT id FROM trials WHERE experiment_id=?)", (eid,))
+        assert row["resource_pool"] == "aux"
+        r = sess.post("/api/v1/commands", json={"config": {"entrypoint": ["/bin/sh", "-c", "echo on=$DET_AGENT_ID"], "resources": {"slots": 0, "resource_pool": "aux"}}}).json()
+        cid = r["command"]["id"]
+        assert r["command"]["resourcePool"] == "aux"
+        _wait(lambda: sess.get(f"/api/v1/commands/{cid}").json()["command"]["state"] == "STATE_TERMINATED", 30, "command exit")
+        assert "on=aux-1" in "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{cid}/logs").json()["logs"])
+        with pytest.raises(api.errors.APIException, match="unknown resource pool"):
+            create(sess, dict(BASE, resources={"slots_per_trial": 1, "resource_pool": "nope"}))
+        with pytest.raises(api.errors.APIException):
+            sess.post("/api/v1/commands", json={"config": {"entrypoint": "true", "resources": {"resource_pool": "nope"}}})
+        assert {p["pool_name"] for p in sess.get("/api/v1/master/config").json()["config"]["resource_pools"]} == {"default", "aux"}
+    finally:
+        a.stop()
+        m.stop()
+        srv.stop()
