@@ -105,3 +105,19 @@ def test_pid_server_fails_fast_when_a_worker_dies(tmp_path):
     r, dt = _pid_server(tmp_path, ["import time; time.sleep(60)", "import sys, time; time.sleep(0.5); sys.exit(7)"])
     assert r.returncode != 0 and dt < 30, (r.returncode, dt, r.stdout[-2000:])
     assert "died without a graceful exit" in r.stdout
+
+
+@pytest.mark.parametrize("module,flag", [("deepspeed", "USE_DEEPSPEED"), ("horovod", None)])
+def test_deepspeed_and_horovod_launch_modules_start_local_ranks(tmp_path, module, flag):
+    """Both accept the reference's command lines and start one process per slot with the torch rank contract."""
+    script = tmp_path / "job.py"
+    script.write_text("import os\nopen(os.path.join(os.environ['OUT'], 'r' + os.environ['RANK']), 'w').write(os.environ['WORLD_SIZE'] + ' ' + os.environ.get('USE_DEEPSPEED', '-'))\n")
+    env = dict(os.environ, PYTHONPATH=str(ROOT), DET_SLOT_IDS=json.dumps([0, 1, 2]), OUT=str(tmp_path), C10D_PORT=str(_free_port()), CUDA_VISIBLE_DEVICES="")
+    env.pop("DET_MASTER", None)
+    r = subprocess.run([sys.executable, "-m", f"determined_b200.launch.{module}", "--", sys.executable, str(script)], env=env,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-2000:]
+    got = sorted((p.name, p.read_text()) for p in tmp_path.glob("r[0-9]"))
+    assert [g[0] for g in got] == ["r0", "r1", "r2"] and all(g[1].startswith("3 ") for g in got)
+    if flag:
+        assert all(g[1].endswith(" 1") for g in got)
