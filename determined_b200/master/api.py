@@ -1796,6 +1796,7 @@ class Handler(BaseHTTPRequestHandler):
         if t is None or t.state != "RUNNING" or not t.service_port:
             self._send(404, {"message": f"task {task_id} has no running service"})
             return
+        t.last_activity = time.time()
         fwd_q = urllib.parse.urlencode([(k, v) for k, vs in qs.items() if k != "token" for v in vs])
         hdrs = {k: v for k, v in self.headers.items() if k.lower() not in ("host", "authorization", "connection", "content-length")}
         hdrs["X-Forwarded-Prefix"] = f"/proxy/{task_id}"

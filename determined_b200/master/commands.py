@@ -46,6 +46,21 @@ def default_entrypoint(kind: str, body: Dict[str, Any]) -> List[str]:
     raise ValueError("a command needs an entrypoint")
 
 
+def parse_duration(v: Any) -> Optional[float]:
+    """``90`` / ``"90s"`` / ``"30m"`` / ``"1h30m"`` -> seconds; None / empty -> None (Go duration strings of the reference configs)."""
+    if v in (None, "", 0):
+        return None
+    if isinstance(v, (int, float)):
+        return float(v)
+    import re
+
+    parts = re.findall(r"(\d+(?:\.\d+)?)(ms|s|m|h|d)?", str(v).strip())
+    if not parts or "".join(a + b for a, b in parts) != str(v).strip():
+        raise ValueError(f"cannot parse duration {v!r}")
+    unit = {"ms": 1e-3, "s": 1.0, "m": 60.0, "h": 3600.0, "d": 86400.0, "": 1.0}
+    return sum(float(a) * unit[b] for a, b in parts)
+
+
 class CommandTask:
     def __init__(self, mgr: "CommandManager", kind: str, config: Dict[str, Any], owner_id: int, owner_name: str, body: Dict[str, Any]) -> None:
         self.mgr, self.kind, self.config = mgr, kind, config
@@ -70,6 +85,9 @@ class CommandTask:
         # tasks that serve HTTP get a port from the master's registry and are reachable through /proxy/<task id>/
         self.service_port: Optional[int] = None
         self.service_host = "127.0.0.1"
+        # reference notebook / tensorboard configs: ``idle_timeout`` kills a service nobody has talked to for that long
+        self.idle_timeout: Optional[float] = parse_duration(config.get("idle_timeout"))
+        self.last_activity = time.time()
 
     @property
     def pool_key(self) -> str:
@@ -106,7 +124,7 @@ class CommandTask:
             from determined_b200.master import agents as agents_mod
 
             m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)", (self.token, self.owner_id, time.time() + 14 * 86400, self.id))
-            self.state = "RUNNING"
+            self.state, self.last_activity = "RUNNING", time.time()
             m.db.exec("UPDATE tasks SET state=? WHERE id=?", (self.state, self.id))
             argv = [agents_mod.PYTHON_PLACEHOLDER if a == sys.executable else a for a in self.argv]
             m.agents.start(self.agent_id, self.id, self, argv, task_env, slot_ids, archive=self.context, workdir="model")
@@ -126,7 +144,7 @@ class CommandTask:
         root = str(pathlib.Path(__file__).resolve().parents[2])
         env["PYTHONPATH"] = os.pathsep.join([root] + ([env["PYTHONPATH"]] if env.get("PYTHONPATH") else []))
         m.db.exec("INSERT INTO sessions(token,user_id,expiry,task_id) VALUES(?,?,?,?)", (self.token, self.owner_id, time.time() + 14 * 86400, self.id))
-        self.state = "RUNNING"
+        self.state, self.last_activity = "RUNNING", time.time()
         m.db.exec("UPDATE tasks SET state=? WHERE id=?", (self.state, self.id))
         logger.info("starting %s %s: %s", self.kind, self.id, " ".join(shlex.quote(a) for a in self.argv))
         self.proc = subprocess.Popen(self.argv, cwd=self.run_dir, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, start_new_session=True,
@@ -237,6 +255,18 @@ class CommandManager:
 
     def list(self, kind: str) -> List[CommandTask]:
         return sorted((t for t in self.tasks.values() if t.kind == TYPES[kind]), key=lambda t: t.start_time)
+
+    def reap_idle(self, now: Optional[float] = None) -> List[str]:
+        """Kill running tasks whose ``idle_timeout`` has passed without proxy traffic; called from the scheduler loop."""
+        now = now if now is not None else time.time()
+        killed = []
+        for t in list(self.tasks.values()):
+            if t.state == "RUNNING" and t.idle_timeout and now - t.last_activity > t.idle_timeout:
+                logger.info("%s %s idle for %.0fs (timeout %.0fs): killing", t.kind, t.id, now - t.last_activity, t.idle_timeout)
+                self.master.db.add_logs([(t.id, t.id + ".1", now, "INFO", None, "stdout", "master", f"idle for more than {t.idle_timeout:.0f}s: terminating\n")])
+                t.kill()
+                killed.append(t.id)
+        return killed
 
     def stop_all(self) -> None:
         for t in list(self.tasks.values()):

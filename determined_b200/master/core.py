@@ -827,6 +827,7 @@ class Master:
                     elif rid in pool.pending:
                         pool.release(rid)
             self.agents.reap()
+            self.commands.reap_idle()
             to_release: List[str] = []
             for pool in self.pools.values():
                 d = pool.tick()

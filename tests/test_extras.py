@@ -445,3 +445,36 @@ def test_top_level_trial_context_and_bases():
     with pytest.raises(TypeError):
         det.TrialController(c)
     assert det.EnvContext().managed_training is True
+
+
+def test_idle_timeout_kills_a_quiet_service_and_proxy_traffic_keeps_it_alive(cluster):
+    import requests as rq
+
+    from determined_b200.master import commands
+
+    assert commands.parse_duration("1h30m") == 5400 and commands.parse_duration(45) == 45 and commands.parse_duration("500ms") == 0.5
+    assert commands.parse_duration(None) is None
+    with pytest.raises(ValueError):
+        commands.parse_duration("soon")
+    m, sess = cluster[0], cluster[1]
+    serve = "import http.server,os;http.server.ThreadingHTTPServer(('127.0.0.1',int(os.environ['DET_SERVICE_PORT'])),http.server.SimpleHTTPRequestHandler).serve_forever()"
+    cmd = sess.post("/api/v1/commands", json={"config": {"entrypoint": [sys.executable, "-c", serve], "proxy_ports": True, "idle_timeout": "3s"}}).json()["command"]
+    t = m.commands.tasks[cmd["id"]]
+    for _ in range(100):
+        if t.state == "RUNNING":
+            break
+        time.sleep(0.1)
+    assert t.state == "RUNNING" and t.idle_timeout == 3.0
+    # traffic through the proxy counts as activity
+    for _ in range(4):
+        time.sleep(1.0)
+        rq.get(m.url + f"/proxy/{t.id}/", headers={"Authorization": f"Bearer {sess.token}"}, timeout=5)
+        m.commands.reap_idle()
+    assert t.state == "RUNNING", "a service in use must not be reaped"
+    for _ in range(100):                       # then silence
+        m.commands.reap_idle()
+        if t.state == "TERMINATED":
+            break
+        time.sleep(0.2)
+    assert t.state == "TERMINATED" and t.killed
+    assert "idle for more than 3s" in "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{t.id}/logs").json()["logs"])
