@@ -445,6 +445,10 @@ def job_update(args: argparse.Namespace) -> int:
         upd["priority"] = args.priority
     if args.weight is not None:
         upd["weight"] = args.weight
+    if getattr(args, "ahead_of", None):
+        upd["aheadOf"] = args.ahead_of
+    if getattr(args, "behind_of", None):
+        upd["behindOf"] = args.behind_of
     _session(args).post("/api/v1/job-queues", json={"updates": [upd]})
     print(f"Updated job {args.job_id}")
     return 0
@@ -1023,6 +1027,8 @@ def make_parser() -> argparse.ArgumentParser:
     a.add_argument("job_id")
     a.add_argument("--priority", type=int)
     a.add_argument("--weight", type=float)
+    a.add_argument("--ahead-of", help="job id to queue just before")
+    a.add_argument("--behind-of", help="job id to queue just after")
     a.set_defaults(fn=job_update)
     rp = sub.add_parser("resource-pool", aliases=["rp"]).add_subparsers(dest="sub")
     a = rp.add_parser("list", aliases=["ls"])

@@ -1230,6 +1230,19 @@ def update_job_queue(ctx: Ctx) -> Any:
                     p.set_priority(jid, int(u["priority"]))
                 if u.get("weight") is not None:
                     p.set_weight(jid, float(u["weight"]))
+            ahead, behind = u.get("aheadOf") or (u.get("queuePosition") or {}).get("aheadOf"), u.get("behindOf") or (u.get("queuePosition") or {}).get("behindOf")
+            if ahead or behind:
+                moved = False
+                for p in ctx.m.pools.values():
+                    try:
+                        p.move_job(jid, ahead_of=ahead, behind_of=behind)
+                        moved = True
+                    except KeyError:
+                        continue
+                    except ValueError as e:
+                        raise HTTPError(400, str(e))
+                if not moved:
+                    raise HTTPError(404, f"job {jid} and its anchor share no resource pool queue")
             for exp in ctx.m.experiments.values():
                 if exp.job_id == jid:
                     if u.get("priority") is not None:

@@ -384,11 +384,14 @@ class ResourcePool:
         self.running: Dict[str, AllocateRequest] = {}
         self.assignments: Dict[str, Assignment] = {}
         self.releasing: Set[str] = set()
+        self.job_positions: Dict[str, float] = {}      # job id -> queue position set by move_job (0 = submit order)
 
     def add_agent(self, agent: Agent) -> None:
         self.agents[agent.id] = agent
 
     def allocate(self, req: AllocateRequest) -> None:
+        if req.job_id in self.job_positions:
+            req.queue_position = self.job_positions[req.job_id]       # later requests of a moved job keep its place
         self.pending[req.allocation_id] = req
 
     def release(self, allocation_id: str) -> None:
@@ -408,6 +411,38 @@ class ResourcePool:
         for r in list(self.pending.values()) + list(self.running.values()):
             if r.job_id == job_id:
                 r.weight = weight
+
+    def move_job(self, job_id: str, ahead_of: Optional[str] = None, behind_of: Optional[str] = None) -> None:
+        """``det job update JOB --ahead-of OTHER`` / ``--behind-of OTHER`` (reference ``job queue`` position updates): the job takes
+        the anchor's priority and a queue position just before / after it; within one priority the queue is ordered by position,
+        then submit time."""
+        anchor = ahead_of or behind_of
+        if anchor is None or anchor == job_id:
+            raise ValueError("move_job needs another job as anchor")
+        reqs = list(self.pending.values()) + list(self.running.values())
+        mine = [r for r in reqs if r.job_id == job_id]
+        theirs = [r for r in reqs if r.job_id == anchor]
+        if not mine or not theirs:
+            raise KeyError(f"job {job_id if not mine else anchor} has no request in pool {self.name}")
+        # positions are compared before submit times, so give every job that never moved its submit time as position first
+        for r in reqs:
+            if r.job_id not in self.job_positions:
+                self.job_positions[r.job_id] = min(x.submit_time for x in reqs if x.job_id == r.job_id)
+        for r in reqs:
+            r.queue_position = self.job_positions[r.job_id]
+        ordered = sorted({r.job_id: self.job_positions[r.job_id] for r in reqs if r.job_id != job_id}.items(), key=lambda kv: kv[1])
+        idx = [j for j, _ in ordered].index(anchor)
+        apos = ordered[idx][1]
+        if ahead_of:
+            prev = ordered[idx - 1][1] if idx > 0 else apos - 2.0
+            pos = (prev + apos) / 2.0
+        else:
+            nxt = ordered[idx + 1][1] if idx + 1 < len(ordered) else apos + 2.0
+            pos = (apos + nxt) / 2.0
+        self.job_positions[job_id] = pos
+        prio = theirs[0].priority
+        for r in mine:
+            r.queue_position, r.priority = pos, prio
 
     def set_max_slots(self, job_id: str, max_slots: Optional[int]) -> None:
         for r in list(self.pending.values()) + list(self.running.values()):

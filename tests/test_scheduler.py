@@ -150,3 +150,28 @@ def test_disabled_slots_are_not_used():
     assert rp.tick().to_allocate == []
     rp.allocate(AllocateRequest("y", "j", 4))
     assert ids(rp.tick()) == ["y"]
+
+
+def test_move_job_ahead_and_behind_reorders_the_queue():
+    rp = pool("priority", n=2)
+    for i, j in enumerate(["a", "b", "c", "d"]):
+        rp.allocate(AllocateRequest(f"r{j}", f"job-{j}", 2, submit_time=100.0 + i))
+    d = rp.tick()
+    assert ids(d) == ["ra"]                                        # the box is full: b, c, d queue in submit order
+    order = lambda: [r["job_id"] for r in rp.job_queue() if r["state"] == "QUEUED"]   # noqa: E731
+    assert order() == ["job-b", "job-c", "job-d"]
+    rp.move_job("job-d", ahead_of="job-b")
+    assert order() == ["job-d", "job-b", "job-c"]
+    rp.move_job("job-b", behind_of="job-c")
+    assert order() == ["job-d", "job-c", "job-b"]
+    rp.release("ra")
+    assert ids(rp.tick()) == ["rd"]                                # the moved job really runs first
+    rp.allocate(AllocateRequest("rd2", "job-d", 2, submit_time=500.0))   # a later request of a moved job keeps its place
+    assert order()[0] == "job-d"
+    rp.allocate(AllocateRequest("rlow", "job-low", 2, priority=90, submit_time=50.0))
+    rp.move_job("job-low", ahead_of="job-c")                      # crossing a priority lane adopts the anchor's priority
+    assert [r for r in rp.job_queue() if r["job_id"] == "job-low"][0]["priority"] == 42
+    with pytest.raises(KeyError):
+        rp.move_job("job-x", ahead_of="job-c")
+    with pytest.raises(ValueError):
+        rp.move_job("job-c", ahead_of="job-c")
