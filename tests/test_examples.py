@@ -119,3 +119,26 @@ def test_ports_example_config_launches_a_proxied_service(tmp_path):
     finally:
         m.stop()
         srv.stop()
+
+
+def test_dsat_torchvision_examples(tmp_path, monkeypatch):
+    """The DeepSpeedTrial variant trains a few batches on CPU with an overlaid engine config (what DSAT does per trial); the
+    Core API variant runs off-cluster and reports its profile."""
+    from determined_b200 import pytorch
+    from determined_b200.pytorch import deepspeed as det_ds
+
+    d = EX / "deepspeed_autotune" / "torchvision"
+    spec = importlib.util.spec_from_file_location("dsat_vision_model_def", d / "deepspeed_trial" / "model_def.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    monkeypatch.chdir(tmp_path)
+    hp = {"model_name": "resnet18", "image_size": 32, "dataset_len": 16, "deepspeed_config": str(d / "deepspeed_trial" / "ds_config.json"),
+          "overwrite_deepspeed_args": {"train_micro_batch_size_per_gpu": 4, "bf16": {"enabled": False}, "zero_optimization": {"stage": 2}}}
+    with det_ds.init(hparams=hp, exp_conf={"checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ck")}}, require_gpu=False) as ctx:
+        trial = mod.VisionTrial(ctx)
+        assert trial.engine.train_micro_batch_size_per_gpu() == 4 and trial.engine.zero_optimization_stage() == 2
+        det_ds.Trainer(trial, ctx).fit(max_length=pytorch.Batch(3), validation_period=pytorch.Batch(3))
+    assert trial.engine.global_steps == 3
+    env = dict(os.environ, PYTHONPATH=str(ROOT), CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, "script.py"], cwd=d / "core_api", env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:]
