@@ -117,16 +117,37 @@ def experiment_create(args: argparse.Namespace) -> int:
     if args.local:
         return _run_local(cfg, args.model_def, args.test)
     sess = _session(args)
+    if args.test:
+        # on-cluster test mode: the same model and config squeezed into a one-batch single-trial experiment that exercises
+        # train / validate / checkpoint on real slots, then report how it ended
+        s = cfg.get("searcher") or {}
+        cfg["searcher"] = {"name": "single", "metric": s.get("metric", "loss"), "smaller_is_better": s.get("smaller_is_better", True),
+                           "max_length": {"batches": 1}}
+        cfg["min_validation_period"] = {"batches": 1}
+        cfg["min_checkpoint_period"] = {"batches": 1}
+        cfg["description"] = "[test mode] " + str(cfg.get("description") or cfg.get("name") or "")
+        for v in (cfg.get("hyperparameters") or {}).values():
+            if isinstance(v, dict) and v.get("type") in ("int", "double", "log", "categorical") and "count" in v:
+                v.pop("count")
     files = det_context.read_v1_context(pathlib.Path(args.model_def)) if args.model_def else []
     for inc in args.include or []:
         files += det_context.read_v1_context(pathlib.Path(inc))
     body = {"config": yaml.safe_dump(cfg), "modelDefinition": files, "activate": not args.paused, "template": args.template,
-            "projectId": args.project_id, "validateOnly": bool(args.test and not args.local and False)}
+            "projectId": args.project_id}
     r = sess.post("/api/v1/experiments", json=body).json()
     eid = r["experiment"]["id"]
     print(f"Created experiment {eid}")
-    if args.publish:
-        pass
+    if args.test and not args.paused:
+        rc = _follow_trial_logs(sess, eid)
+        state = sess.get(f"/api/v1/experiments/{eid}").json()["experiment"]["state"]
+        for _ in range(600):
+            if state in ("STATE_COMPLETED", "STATE_ERROR", "STATE_CANCELED"):
+                break
+            time.sleep(0.5)
+            state = sess.get(f"/api/v1/experiments/{eid}").json()["experiment"]["state"]
+        ok = state == "STATE_COMPLETED"
+        print("Model training test succeeded." if ok else f"Model training test failed: experiment {eid} ended as {state}.")
+        return 0 if ok else (rc or 1)
     if args.follow_first_trial and not args.paused:
         return _follow_trial_logs(sess, eid)
     return 0

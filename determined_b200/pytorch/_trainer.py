@@ -67,8 +67,6 @@ class Trainer:
             smaller_is_better, searcher_metric_name = True, None
             steps_completed = 0
             global_batch_size = None
-            if checkpoint_policy == "best":
-                checkpoint_policy = "all" if False else "best"
         else:
             if test_mode:
                 raise ValueError("test_mode is only supported in local training mode.")

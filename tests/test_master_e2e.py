@@ -256,3 +256,20 @@ def test_two_slot_trial_runs_data_parallel_over_gloo(cluster):
     assert ranks & {0, 1, None}
     alloc = m.db.one("SELECT slots FROM allocations WHERE trial_id=?", (t["id"],))
     assert alloc["slots"] == 2
+
+
+def test_cli_on_cluster_test_mode(cluster, capsys, monkeypatch):
+    """`det experiment create --test` on a cluster: a one-batch copy of the experiment runs on real slots and reports success."""
+    from determined_b200.cli import cli
+
+    m, sess, tmp = cluster
+    monkeypatch.setenv("DET_MASTER", m.url)
+    cfg_path = tmp / "cfg.yaml"
+    cfg_path.write_text(yaml.safe_dump(dict(BASE, searcher={"name": "adaptive_asha", "metric": "val_loss", "max_trials": 4, "max_length": {"batches": 64}})))
+    rc = cli.main(["experiment", "create", str(cfg_path), str(FIX), "--test"])
+    out = capsys.readouterr().out
+    assert rc == 0 and "Model training test succeeded." in out, out[-2000:]
+    exps = sess.get("/api/v1/experiments").json()["experiments"]
+    assert len(exps) == 1 and exps[0]["description"].startswith("[test mode]")
+    t = sess.get(f"/api/v1/experiments/{exps[0]['id']}/trials").json()["trials"]
+    assert len(t) == 1 and t[0]["totalBatchesProcessed"] == 1
