@@ -583,6 +583,15 @@ class Master:
         from determined_b200.master import commands as _commands
 
         self.commands = _commands.CommandManager(self)
+        # pools backed by a workload manager instead of agents (reference dispatcher RM): master/slurm.py
+        self.backends: Dict[str, Any] = {}
+        for rp in resource_pools or []:
+            prov = rp.get("provider") or {}
+            if str(prov.get("type", "")).lower() == "slurm":
+                from determined_b200.master import slurm
+
+                name = str(rp.get("pool_name") or rp.get("name"))
+                self.backends[name] = slurm.SlurmBackend(self, name, prov)
         self._restore()
 
     @property
@@ -623,6 +632,8 @@ class Master:
         with self.lock:
             for a in list(self.allocations.values()):
                 a.kill()
+        for b in self.backends.values():
+            b.stop()
 
     def _restore(self) -> None:
         """Re-hydrate non-terminal experiments (reference ``core.go:821-873``, ``restore.go``).
