@@ -1499,14 +1499,40 @@ def list_webhooks(ctx: Ctx) -> Any:
 @route("POST", "/api/v1/webhooks")
 def create_webhook(ctx: Ctx) -> Any:
     b = ctx.body or {}
+    if not str(b.get("url") or "").startswith(("http://", "https://")):
+        raise HTTPError(400, "webhook url must be http(s)")
     wid = ctx.m.db.exec("INSERT INTO webhooks(url,webhook_type,triggers) VALUES(?,?,?)", (b.get("url"), b.get("webhookType", "WEBHOOK_TYPE_DEFAULT"), dbmod.J(b.get("triggers") or [])))
+    ctx.m.webhooks_changed()
     return {"webhook": {"id": wid, "url": b.get("url"), "webhookType": b.get("webhookType", "WEBHOOK_TYPE_DEFAULT"), "triggers": b.get("triggers") or []}}
 
 
 @route("DELETE", "/api/v1/webhooks/{wid}")
 def delete_webhook(ctx: Ctx, wid: str) -> Any:
     ctx.m.db.exec("DELETE FROM webhooks WHERE id=?", (int(wid),))
+    ctx.m.webhooks_changed()
     return {}
+
+
+@route("POST", "/api/v1/webhooks/{wid}/test")
+def test_webhook(ctx: Ctx, wid: str) -> Any:
+    """Deliver a sample event to one webhook (reference ``TestWebhook``)."""
+    r = ctx.m.db.one("SELECT * FROM webhooks WHERE id=?", (int(wid),))
+    if r is None:
+        raise HTTPError(404, "webhook not found")
+    ctx.m._post_webhook(dict(r), "EXPERIMENT_STATE_CHANGE", {"experiment_id": 0, "state": "COMPLETED", "test": True})
+    return {"completed": True}
+
+
+@route("GET", "/api/v1/master/webhook_signing_key")
+def webhook_signing_key(ctx: Ctx) -> Any:
+    """The key receivers use to verify ``X-Determined-AuthSignature`` (admins only)."""
+    if not ctx.user["admin"]:
+        raise HTTPError(403, "admin only")
+    key = ctx.m.db.get_meta("webhook_signing_key")
+    if not key:
+        key = secrets.token_hex(16)
+        ctx.m.db.set_meta("webhook_signing_key", key)
+    return {"key": key}
 
 
 @route("GET", "/api/v1/tasks")

@@ -158,6 +158,7 @@ class Allocation:
                     break
             rows.append((self.trial.task_id, self.id, time.time(), level, rank, "stdout", "task", txt + "\n"))
             self.master.log_policies(self.trial, txt)
+            self.master.webhook_log_line(self.trial.task_id, txt)
         return rows
 
     def _pump_logs(self) -> None:
@@ -914,23 +915,85 @@ class Master:
                 if action == "cancel_retries":
                     trial.cancel_retries = True
 
-    def fire_webhooks(self, trigger: str, payload: Dict[str, Any]) -> None:
-        rows = self.db.all("SELECT * FROM webhooks")
-        if not rows:
-            return
+    # webhook task-log triggers: compiled regexes cached per webhook row (rebuilt when the set of webhooks changes)
+    _log_hooks: Optional[List[Tuple[Any, Any]]] = None
 
-        def post(url: str, body: Dict[str, Any]) -> None:
+    def _task_log_hooks(self) -> List[Tuple[Any, Any]]:
+        if self._log_hooks is None:
+            import re
+
+            hooks = []
+            for r in self.db.all("SELECT * FROM webhooks"):
+                for t in dbmod.U(r["triggers"], []):
+                    if str(t.get("triggerType", "")).endswith("TASK_LOG"):
+                        rx = (t.get("condition") or {}).get("regex")
+                        if rx:
+                            try:
+                                hooks.append((re.compile(rx), dict(r)))
+                            except re.error:
+                                logger.warning("webhook %s: bad regex %r", r["id"], rx)
+            self._log_hooks = hooks
+        return self._log_hooks
+
+    def webhooks_changed(self) -> None:
+        self._log_hooks = None
+
+    def webhook_log_line(self, task_id: str, line: str) -> None:
+        """``TRIGGER_TYPE_TASK_LOG`` (reference ``internal/webhooks`` + ``logpattern``): post when a task's output matches."""
+        for rx, row in self._task_log_hooks():
+            if rx.search(line):
+                self._post_webhook(row, "TASK_LOG", {"task_id": task_id, "log": line, "regex": rx.pattern})
+
+    def _post_webhook(self, row: Dict[str, Any], trigger: str, payload: Dict[str, Any]) -> None:
+        """One delivery: the default JSON event, or a Slack message for ``WEBHOOK_TYPE_SLACK``; signed with the cluster's
+        webhook key (``X-Determined-AuthSignature`` = HMAC-SHA256 over ``timestamp,body``) like the reference."""
+        import hashlib
+        import hmac
+
+        ts = int(time.time())
+        if str(row.get("webhook_type", "")).endswith("SLACK"):
+            what = ", ".join(f"{k} {v}" for k, v in payload.items())
+            body = {"text": f"Determined: {trigger.replace('_', ' ').lower()} — {what}",
+                    "blocks": [{"type": "section", "text": {"type": "mrkdwn", "text": f"*{trigger.replace('_', ' ').title()}*\n{what}"}}]}
+        else:
+            body = {"event_id": uuid.uuid4().hex, "event_type": trigger, "timestamp": ts, "data": payload, "condition": row.get("_condition")}
+        raw = json.dumps(body).encode()
+        key = (self.db.get_meta("webhook_signing_key") or "").encode()
+        if not key:
+            key = secrets.token_hex(16).encode()
+            self.db.set_meta("webhook_signing_key", key.decode())
+        sig = hmac.new(key, f"{ts},".encode() + raw, hashlib.sha256).hexdigest()
+        url = row["url"]
+
+        def post() -> None:
             try:
                 import requests
 
-                requests.post(url, json=body, timeout=5)
+                requests.post(url, data=raw, timeout=5, headers={"Content-Type": "application/json", "X-Determined-AuthTimestamp": str(ts),
+                                                                 "X-Determined-AuthSignature": sig})
             except Exception as e:
                 logger.debug("webhook %s failed: %s", url, e)
 
+        threading.Thread(target=post, daemon=True).start()
+
+    def fire_webhooks(self, trigger: str, payload: Dict[str, Any]) -> None:
+        """State-change triggers.  A trigger may carry ``condition: {state: COMPLETED}`` (or a list of states); without one every
+        change is delivered."""
+        rows = self.db.all("SELECT * FROM webhooks")
         for r in rows:
             trig = dbmod.U(r["triggers"], [])
-            if any(t.get("triggerType", "").endswith(trigger) for t in trig) or not trig:
-                threading.Thread(target=post, args=(r["url"], {"event_type": trigger, "data": payload, "timestamp": time.time()}), daemon=True).start()
+            for t in trig or [{}]:
+                if trig and not str(t.get("triggerType", "")).endswith(trigger):
+                    continue
+                want = (t.get("condition") or {}).get("state")
+                if want:
+                    states = [want] if isinstance(want, str) else list(want)
+                    if str(payload.get("state", "")).replace("STATE_", "") not in [str(x).replace("STATE_", "") for x in states]:
+                        continue
+                row = dict(r)
+                row["_condition"] = t.get("condition")
+                self._post_webhook(row, trigger, payload)
+                break
 
     def schedule_gc(self, exp: Experiment) -> None:
         threading.Thread(target=self.run_checkpoint_gc, args=(exp.id,), daemon=True, name=f"gc-{exp.id}").start()

@@ -273,3 +273,61 @@ def test_cli_on_cluster_test_mode(cluster, capsys, monkeypatch):
     assert len(exps) == 1 and exps[0]["description"].startswith("[test mode]")
     t = sess.get(f"/api/v1/experiments/{exps[0]['id']}/trials").json()["trials"]
     assert len(t) == 1 and t[0]["totalBatchesProcessed"] == 1
+
+
+def test_webhooks_state_conditions_log_triggers_slack_and_signatures(cluster):
+    import hashlib
+    import hmac
+    import http.server
+    import threading
+
+    m, sess, tmp = cluster
+    got = []
+
+    class H(http.server.BaseHTTPRequestHandler):
+        def do_POST(self):
+            n = int(self.headers.get("Content-Length") or 0)
+            got.append((self.path, dict(self.headers), self.rfile.read(n)))
+            self.send_response(200)
+            self.send_header("Content-Length", "0")
+            self.end_headers()
+
+        def log_message(self, *a):
+            pass
+
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), H)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    base = f"http://127.0.0.1:{srv.server_address[1]}"
+    try:
+        mk = lambda path, typ, trig: sess.post("/api/v1/webhooks", json={"url": base + path, "webhookType": typ, "triggers": trig}).json()["webhook"]  # noqa: E731
+        w1 = mk("/done", "WEBHOOK_TYPE_DEFAULT", [{"triggerType": "TRIGGER_TYPE_EXPERIMENT_STATE_CHANGE", "condition": {"state": "COMPLETED"}}])
+        mk("/slack", "WEBHOOK_TYPE_SLACK", [{"triggerType": "TRIGGER_TYPE_EXPERIMENT_STATE_CHANGE", "condition": {"state": ["COMPLETED", "ERROR"]}}])
+        mk("/log", "WEBHOOK_TYPE_DEFAULT", [{"triggerType": "TRIGGER_TYPE_TASK_LOG", "condition": {"regex": "Restoring trial|validat"}}])
+        with pytest.raises(api.errors.APIException):
+            sess.post("/api/v1/webhooks", json={"url": "file:///etc/passwd"})
+        eid = create(sess, BASE)
+        assert wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR"}) == "STATE_COMPLETED", dump_logs(sess, eid)
+        t0 = time.time()
+        while time.time() - t0 < 10 and not ({p for p, _, _ in got} >= {"/done", "/slack"}):
+            time.sleep(0.1)
+        done = [(h, b) for p, h, b in got if p == "/done"]
+        assert len(done) == 1, "only the COMPLETED transition matches the condition"
+        body = json.loads(done[0][1])
+        assert body["event_type"] == "EXPERIMENT_STATE_CHANGE" and body["data"]["state"] == "COMPLETED" and body["data"]["experiment_id"] == eid
+        admin = api.authentication.login(m.url, "admin", "")
+        key = admin.get("/api/v1/master/webhook_signing_key").json()["key"].encode()
+        h = {k.lower(): v for k, v in done[0][0].items()}
+        want = hmac.new(key, h["x-determined-authtimestamp"].encode() + b"," + done[0][1], hashlib.sha256).hexdigest()
+        assert h["x-determined-authsignature"] == want
+        logs = [json.loads(b) for p, _, b in got if p == "/log"]
+        assert logs and logs[0]["event_type"] == "TASK_LOG" and logs[0]["data"]["task_id"].startswith("trial-"), dump_logs(sess, eid)
+        slack = json.loads([b for p, _, b in got if p == "/slack"][0])
+        assert "text" in slack and "blocks" in slack and "COMPLETED" in slack["text"]
+        got.clear()
+        sess.post(f"/api/v1/webhooks/{w1['id']}/test")
+        t0 = time.time()
+        while time.time() - t0 < 5 and not got:
+            time.sleep(0.05)
+        assert got and json.loads(got[0][2])["data"]["test"] is True
+    finally:
+        srv.shutdown()
