@@ -640,6 +640,117 @@ def preview_search(ctx: Ctx) -> Any:
     return {"simulation": {"config": cfg, "seed": int(b.get("seed", 0)), "trials": trials, "unit": unit}}
 
 
+# -- hyperparameter visualisation (reference api_experiment.go: MetricNames, TrialsSnapshot, TrialsSample; api_trials.go: Summarize / Compare)
+def _flat_hparams(hp: Any, prefix: str = "") -> Dict[str, Any]:
+    out: Dict[str, Any] = {}
+    for k, v in (hp or {}).items():
+        if isinstance(v, dict):
+            out.update(_flat_hparams(v, f"{prefix}{k}."))
+        else:
+            out[f"{prefix}{k}"] = v
+    return out
+
+
+@route("GET", "/api/v1/experiments/{eid}/metric-names")
+@route("GET", "/api/v1/experiments/metrics-stream/metric-names")      # registered first (decorators apply bottom-up): the literal path wins
+def metric_names(ctx: Ctx, eid: Optional[str] = None) -> Any:
+    """Names of every training / validation metric the experiment(s) reported, plus the searcher metric."""
+    ids = [int(eid)] if eid else [int(x) for x in ctx.query.get("ids", [])]
+    out = []
+    for i in ids:
+        row = _exp_row(ctx, str(i))
+        names: Dict[str, set] = {"training": set(), "validation": set()}
+        for r in ctx.m.db.all("SELECT DISTINCT grp, metrics FROM metrics WHERE trial_id IN (SELECT id FROM trials WHERE experiment_id=?)", (i,)):
+            if r["grp"] in names:
+                names[r["grp"]].update(k for k, v in dbmod.U(r["metrics"], {}).items() if isinstance(v, (int, float)))
+        cfg = dbmod.U(row["config"], {})
+        out.append({"experimentId": i, "searcherMetric": (cfg.get("searcher") or {}).get("metric"), "trainingMetrics": sorted(names["training"]),
+                    "validationMetrics": sorted(names["validation"]),
+                    "metricNames": [{"group": g, "name": n} for g in ("training", "validation") for n in sorted(names[g])]})
+    return out[0] if eid else {"results": out}
+
+
+def _metric_points(ctx: Ctx, eid: str, name: str, group: str) -> Dict[int, List[Tuple[int, float]]]:
+    pts: Dict[int, List[Tuple[int, float]]] = {}
+    for r in ctx.m.db.all("SELECT trial_id, steps_completed, metrics FROM metrics WHERE grp=? AND trial_id IN (SELECT id FROM trials WHERE experiment_id=?) "
+                          "ORDER BY steps_completed, id", (group, int(eid))):
+        v = dbmod.U(r["metrics"], {}).get(name)
+        if isinstance(v, (int, float)):
+            pts.setdefault(r["trial_id"], []).append((r["steps_completed"], float(v)))
+    return pts
+
+
+@route("GET", "/api/v1/experiments/{eid}/metrics-stream/trials-snapshot")
+@route("GET", "/api/v1/experiments/{eid}/trials-snapshot")
+def trials_snapshot(ctx: Ctx, eid: str) -> Any:
+    """One point per trial: its hyperparameters and the value of ``metricName`` at ``batchesProcessed`` (default: each trial's
+    latest report) — the data behind the parallel-coordinates / scatter / heat-map views."""
+    _exp_row(ctx, eid)
+    name, group = ctx.q("metricName"), ctx.q("group") or {"METRIC_TYPE_TRAINING": "training"}.get(ctx.q("metricType", ""), "validation")
+    if not name:
+        raise HTTPError(400, "metricName is required")
+    at = ctx.q("batchesProcessed")
+    trials = []
+    hp_of = {r["id"]: _flat_hparams(dbmod.U(r["hparams"], {})) for r in ctx.m.db.all("SELECT id, hparams FROM trials WHERE experiment_id=?", (int(eid),))}
+    for tid, series in sorted(_metric_points(ctx, eid, name, group).items()):
+        pick = [p for p in series if at is None or p[0] <= int(at)]
+        if pick:
+            trials.append({"trialId": tid, "hparams": hp_of.get(tid, {}), "metric": pick[-1][1], "batchesProcessed": pick[-1][0]})
+    return {"trials": trials}
+
+
+@route("GET", "/api/v1/experiments/{eid}/metrics-stream/trials-sample")
+@route("GET", "/api/v1/experiments/{eid}/trials-sample")
+def trials_sample(ctx: Ctx, eid: str) -> Any:
+    """Learning curves of up to ``maxTrials`` trials (the best by final value first), each thinned to ``maxDatapoints`` points."""
+    row = _exp_row(ctx, eid)
+    name, group = ctx.q("metricName"), ctx.q("group") or {"METRIC_TYPE_TRAINING": "training"}.get(ctx.q("metricType", ""), "validation")
+    if not name:
+        raise HTTPError(400, "metricName is required")
+    smaller = bool((dbmod.U(row["config"], {}).get("searcher") or {}).get("smaller_is_better", True))
+    max_trials, max_pts = ctx.qi("maxTrials", 25), max(ctx.qi("maxDatapoints", 1000), 2)
+    series = _metric_points(ctx, eid, name, group)
+    order = sorted(series, key=lambda t: series[t][-1][1], reverse=not smaller)[:max_trials]
+    hp_of = {r["id"]: _flat_hparams(dbmod.U(r["hparams"], {})) for r in ctx.m.db.all("SELECT id, hparams FROM trials WHERE experiment_id=?", (int(eid),))}
+    trials = []
+    for tid in order:
+        pts = series[tid]
+        if len(pts) > max_pts:
+            step = (len(pts) - 1) / (max_pts - 1)
+            pts = [pts[round(i * step)] for i in range(max_pts)]
+        trials.append({"trialId": tid, "hparams": hp_of.get(tid, {}), "data": [{"batches": b, "value": v} for b, v in pts]})
+    return {"trials": trials, "promotedTrials": [], "demotedTrials": []}
+
+
+@route("GET", "/api/v1/trials/{tid}/summarize")
+def summarize_trial(ctx: Ctx, tid: str) -> Any:
+    """A trial with its metric series thinned to ``maxDatapoints`` per metric (reference ``SummarizeTrial``)."""
+    row = _trial_row(ctx, tid)
+    want, max_pts = set(ctx.query.get("metricNames", [])), max(ctx.qi("maxDatapoints", 1000), 2)
+    series: Dict[Tuple[str, str], List[Dict[str, Any]]] = {}
+    for r in ctx.m.db.all("SELECT grp, steps_completed, metrics, report_time FROM metrics WHERE trial_id=? ORDER BY steps_completed, id", (int(tid),)):
+        for k, v in dbmod.U(r["metrics"], {}).items():
+            if isinstance(v, (int, float)) and (not want or k in want):
+                series.setdefault((r["grp"], k), []).append({"batches": r["steps_completed"], "value": float(v), "time": _ts(r["report_time"])})
+    out = []
+    for (g, k), pts in sorted(series.items()):
+        if len(pts) > max_pts:
+            step = (len(pts) - 1) / (max_pts - 1)
+            pts = [pts[round(i * step)] for i in range(max_pts)]
+        out.append({"name": k, "type": "METRIC_TYPE_TRAINING" if g == "training" else "METRIC_TYPE_VALIDATION", "group": g, "data": pts})
+    return {"trial": trial_json(ctx.m, row), "metrics": out}
+
+
+@route("GET", "/api/v1/trials/compare")
+def compare_trials(ctx: Ctx) -> Any:
+    """``summarize`` for several trials at once (``trialIds=1&trialIds=2``)."""
+    out = []
+    for t in ctx.query.get("trialIds", []):
+        s_ = summarize_trial(ctx, t)
+        out.append({"trial": s_["trial"], "metrics": s_["metrics"]})
+    return {"trials": out}
+
+
 # -- custom searcher events ------------------------------------------------------------------------
 @route("GET", "/api/v1/experiments/{eid}/searcher_events")
 def searcher_events(ctx: Ctx, eid: str) -> Any:

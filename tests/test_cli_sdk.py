@@ -287,3 +287,30 @@ def test_cli_agent_user_model_additions(cluster):
     assert "robert" in ok("user", "list")
     ok("model", "create", "mm", "--description", "d")
     assert "Version" in ok("model", "list-versions", "mm")
+
+
+def test_hp_visualisation_endpoints(cluster):
+    """metric-names / trials-snapshot / trials-sample / summarize / compare over metrics reported for two trials."""
+    m, tmp = cluster
+    d = sdk.Determined(m.url)
+    exp = d.create_experiment(CFG, str(FIX))
+    sess = api.authentication.login(m.url, "determined", "")
+    trials = exp.list_trials()
+    for k, t in enumerate(trials):
+        for steps in (10, 20, 30):
+            sess.post(f"/api/v1/trials/{t.id}/metrics", json={"group": "validation", "metrics": {"stepsCompleted": steps, "trialId": t.id, "trialRunId": 0,
+                                                                                                 "metrics": {"avgMetrics": {"val_loss": 1.0 / steps + k, "acc": 0.5}}}})
+            sess.post(f"/api/v1/trials/{t.id}/metrics", json={"group": "training", "metrics": {"stepsCompleted": steps, "trialId": t.id, "trialRunId": 0,
+                                                                                               "metrics": {"avgMetrics": {"loss": 2.0 / steps}}}})
+    names = sess.get(f"/api/v1/experiments/{exp.id}/metric-names").json()
+    assert names["validationMetrics"] == ["acc", "val_loss"] and names["trainingMetrics"] == ["loss"] and names["searcherMetric"] == "val_loss"
+    multi = sess.get("/api/v1/experiments/metrics-stream/metric-names", params={"ids": [exp.id]}).json()["results"]
+    assert multi[0]["experimentId"] == exp.id
+    snap = sess.get(f"/api/v1/experiments/{exp.id}/trials-snapshot", params={"metricName": "val_loss", "batchesProcessed": 20}).json()["trials"]
+    assert [round(x["metric"], 4) for x in snap] == [0.05, 1.05] and all(x["batchesProcessed"] == 20 and "hparams" in x for x in snap)
+    sample = sess.get(f"/api/v1/experiments/{exp.id}/trials-sample", params={"metricName": "val_loss", "maxTrials": 1, "maxDatapoints": 2}).json()["trials"]
+    assert len(sample) == 1 and sample[0]["trialId"] == trials[0].id and [p["batches"] for p in sample[0]["data"]] == [10, 30]
+    summ = sess.get(f"/api/v1/trials/{trials[0].id}/summarize", params={"metricNames": ["loss"]}).json()
+    assert [x["name"] for x in summ["metrics"]] == ["loss"] and len(summ["metrics"][0]["data"]) == 3 and summ["trial"]["id"] == trials[0].id
+    cmp_ = sess.get("/api/v1/trials/compare", params={"trialIds": [t.id for t in trials]}).json()["trials"]
+    assert len(cmp_) == 2 and {x["name"] for x in cmp_[1]["metrics"]} == {"acc", "loss", "val_loss"}
