@@ -467,7 +467,7 @@ class _PyTorchTrialController:
             self.context._current_batch_idx = batch_idx
             if in_epoch == 0:
                 for cb in self.callbacks.values():
-                    cb.on_training_epoch_start(epoch_idx)
+                    self._epoch_start(cb, epoch_idx)
             num_inputs += self.trial.get_batch_length(batch)
             for cb in self._batch_hooks:
                 cb.on_training_batch_start(batch_idx)
@@ -831,6 +831,22 @@ class _PyTorchTrialController:
             raise
         if not already_exiting:
             self._stop_requested()
+
+    _legacy_epoch_cbs: Optional[set] = None
+
+    def _epoch_start(self, cb: Any, epoch_idx: int) -> None:
+        """Callbacks written before ``on_training_epoch_start`` took the epoch index still work (reference
+        ``_pytorch_trial.py:368-378`` keeps them alive with a deprecation warning); the arity is looked up once per callback."""
+        if self._legacy_epoch_cbs is None:
+            import inspect
+
+            self._legacy_epoch_cbs = {id(c) for c in self.callbacks.values() if not inspect.signature(c.on_training_epoch_start).parameters}
+            if self._legacy_epoch_cbs:
+                logger.warning("on_training_epoch_start() without an epoch_idx parameter is deprecated; please add it")
+        if id(cb) in self._legacy_epoch_cbs:
+            cb.on_training_epoch_start()
+        else:
+            cb.on_training_epoch_start(epoch_idx)
 
     # -- checkpoint fast path (pytorch/_async_checkpoint.py) ----------------------------------------
     _ckpt_writer: Any = None

@@ -1,0 +1,36 @@
+"""Unmodified user code of the reference runs on this harness: the trial classes of the reference's own test fixtures
+(``/root/reference/harness/tests/experiment/fixtures``) are imported as they are, with ``import determined`` aliased to this
+package by ``determined_b200.install_alias()``, and trained through ``pytorch.init`` + ``Trainer.fit``.  Skipped where the
+reference checkout is not present."""
+import json
+import pathlib
+import subprocess
+import sys
+
+import pytest
+
+REF = pathlib.Path("/root/reference/harness")
+RUNNER = pathlib.Path(__file__).parent / "fixtures" / "run_reference_trial.py"
+pytestmark = pytest.mark.skipif(not (REF / "tests" / "experiment" / "fixtures" / "pytorch_onevar_model.py").exists(), reason="reference checkout not available")
+
+CASES = [
+    ("pytorch_onevar_model", "OneVarTrial", 8, {}),                              # custom reducers (class + function), callbacks, analytic checks inside train_batch
+    ("pytorch_onevar_model", "OneVarTrialWithMultiValidation", 8, {}),
+    ("pytorch_onevar_model", "OneVarTrialWithTrainingMetrics", 8, {}),
+    ("pytorch_onevar_model", "OneVarTrialCustomEval", 8, {}),                    # evaluate_full_dataset
+    ("pytorch_onevar_model", "OneVarTrialGradClipping", 8, {}),                  # clip_grads callables
+    ("pytorch_onevar_model", "OneVarTrialWithNonScalarValidation", 8, {}),
+    ("pytorch_onevar_model", "OneVarTrialWithLRScheduler", 8, {"lr_scheduler_step_mode": 1}),
+    ("pytorch_onevar_model", "OneVarTrialAccessContext", 1, {"lr_scheduler_step_mode": 1}),      # two models / optimizers / schedulers on one context
+    ("pytorch_onevar_model", "OneVarTrialCallbacks", 8, {}),                     # includes a callback with the pre-0.17.8 epoch-start signature
+    ("pytorch_onevar_model", "OneVarAutoAMPTrial", 4, {}),
+    ("pytorch_onevar_model", "OneVarManualAMPTrial", 4, {}),
+]
+
+
+def test_reference_fixture_trials_run_unmodified(tmp_path):
+    r = subprocess.run([sys.executable, str(RUNNER), str(REF), "--cases", json.dumps(CASES)], cwd=tmp_path,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    for _, cls, _, _ in CASES:
+        assert f"REFERENCE_TRIAL_OK {cls}" in r.stdout, f"{cls} failed:\n" + r.stdout[-4000:]
+    assert r.returncode == 0, r.stdout[-3000:]
