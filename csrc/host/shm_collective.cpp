@@ -189,6 +189,16 @@ DETB200_HOST_API void* detb200_shm_open(const char* name, int rank, int world, s
   return h;
 }
 
+// Remove the name (rank 0, once every rank has attached): the mapping lives on until the last rank unmaps it, and close()
+// then needs no cross-rank coordination.
+DETB200_HOST_API void detb200_shm_unlink(void* handle) {
+  auto* h = static_cast<Handle*>(handle);
+  if (h != nullptr && h->owner) {
+    shm_unlink(h->name.c_str());
+    h->owner = false;
+  }
+}
+
 DETB200_HOST_API void detb200_shm_close(void* handle) {
   auto* h = static_cast<Handle*>(handle);
   if (h == nullptr) return;

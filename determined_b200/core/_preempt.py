@@ -145,6 +145,8 @@ class DummyPreemptContext(PreemptContext):
         self._force = True
 
     def should_preempt(self, auto_ack: bool = True) -> bool:
+        if not self._started:
+            raise RuntimeError("cannot call .should_preempt() before .start(); use the PreemptContext as a context manager")
         if self._dist.rank == 0:
             out = self._force
             if self._preempt_mode == PreemptMode.WorkersAskChief:

@@ -21,6 +21,7 @@ def load() -> Optional[ctypes.CDLL]:
         lib.detb200_shm_open.restype = ctypes.c_void_p
         lib.detb200_shm_open.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_double]
         lib.detb200_shm_close.argtypes = [ctypes.c_void_p]
+        lib.detb200_shm_unlink.argtypes = [ctypes.c_void_p]
         lib.detb200_shm_exchange_sizes.argtypes = [ctypes.c_void_p, ctypes.c_uint64, u64p, ctypes.c_double]
         lib.detb200_shm_allgatherv.argtypes = [ctypes.c_void_p, ctypes.c_char_p, u64p, u64p, ctypes.c_void_p, ctypes.c_double]
         lib.detb200_shm_barrier.argtypes = [ctypes.c_void_p, ctypes.c_double]
@@ -45,6 +46,12 @@ class ShmTransport:
         self._h = lib.detb200_shm_open(self._name, rank, size, slot_bytes, min(timeout_s, 120.0))
         if not self._h:
             raise RuntimeError(f"shared-memory transport: {lib.detb200_shm_last_error().decode()}")
+        if size > 1:
+            # everyone is attached after this barrier; rank 0 then drops the name, so close() is a plain unmap and ranks may
+            # close in any order (or not at all, if the process is killed) without leaving a segment behind
+            self.barrier()
+            if rank == 0:
+                lib.detb200_shm_unlink(self._h)
 
     def _check(self, rc: int) -> None:
         if rc != 0:
@@ -81,10 +88,5 @@ class ShmTransport:
 
     def close(self) -> None:
         if self._h:
-            if self.size > 1:
-                try:
-                    self.barrier()          # nobody unmaps (and rank 0 does not unlink) while a peer still reads
-                except RuntimeError:
-                    pass
             self._lib.detb200_shm_close(self._h)
             self._h = None

@@ -299,6 +299,10 @@ class PIDServer:
         self.sel.unregister(conn)
         conn.close()
         del self.conns[conn]
+        if pid not in self.graceful_shutdowns:
+            # the connection is gone without the goodbye byte: the worker crashed (its pid may linger a moment as a zombie,
+            # so do not leave this to the pid poll, which stops once every connection has closed)
+            raise errors.WorkerError(f"Detected that worker process (pid {pid}) exited without a graceful exit")
 
     def check_pids(self) -> None:
         for pid in self.pids:
@@ -320,11 +324,13 @@ class PIDServer:
             if health_check is not None:
                 health_check()
 
-    def run_subprocess(self, cmd: List[str], on_fail: Optional[signal.Signals] = signal.SIGTERM,
+    def run_subprocess(self, cmd: List[str], on_fail: Optional[signal.Signals] = None,
                        on_exit: Optional[signal.Signals] = None, grace_period: int = 3,
                        signal_children: bool = False, env: Optional[Dict[str, str]] = None) -> int:
-        """Run ``cmd`` (the launcher) while watching the workers.  Return its exit code, or 80-83
-        on watchdog-detected failures (same codes as the reference ``ipc.py:455-502``)."""
+        """Run ``cmd`` (the launcher) while watching the workers and return an exit code with the reference's meaning
+        (``ipc.py:451-502``): the launcher's own code if it ends first (77 if that was 0: it must outlive its workers); after
+        a worker failure the launcher is given ``grace_period`` seconds, then ``on_fail`` (78 if it then exits 0), else
+        waited for (79 if it exits 0); after a clean run ``on_exit`` is delivered the same way."""
         from determined_b200 import util
 
         p = subprocess.Popen(cmd, env=env)
@@ -338,42 +344,39 @@ class PIDServer:
             if ret is not None:
                 raise HealthCheckFail(ret)
 
-        def kill(sig: signal.Signals) -> None:
+        def send(sig: signal.Signals) -> None:
             if signal_children:
                 util.signal_process_tree(p, sig)
-            else:
+            with contextlib.suppress(ProcessLookupError):
                 p.send_signal(sig)
+
+        def deliver(sig: signal.Signals, zero_means: int) -> Optional[int]:
+            time.sleep(grace_period)            # let things finish logging and exit on their own first
+            send(sig)
+            if sig != signal.SIGKILL:
+                try:
+                    return p.wait(timeout=10) or zero_means
+                except subprocess.TimeoutExpired:
+                    logger.error("launcher ignored %s; sending SIGKILL", sig.name)
+                    send(signal.SIGKILL)
+            return None
 
         with util.forward_signals(p):
             try:
                 self.run(health_check)
             except HealthCheckFail as e:
-                # launcher exited on its own; non-zero passes through, zero with missing
-                # graceful-exit handshakes is still a failure.
-                if e.code:
-                    return e.code
-                done = len(self.pids) >= self.num_clients and len(self.graceful_shutdowns) >= len(self.pids)
-                return 0 if done else 79
+                return e.code or 77
             except errors.WorkerError as e:
                 logger.error("%s", e)
                 if on_fail is not None:
-                    kill(on_fail)
-                    try:
-                        return p.wait(timeout=grace_period) or 80
-                    except subprocess.TimeoutExpired:
-                        logger.error("launcher ignored %s; sending SIGKILL", on_fail.name)
-                        kill(signal.SIGKILL)
-                        return p.wait() or 81
-                return p.wait() or 82
-            # all workers exited gracefully
+                    rc = deliver(on_fail, 78)
+                    if rc is not None:
+                        return rc
+                return p.wait() or 79
             if on_exit is not None:
-                kill(on_exit)
-                try:
-                    return p.wait(timeout=grace_period)
-                except subprocess.TimeoutExpired:
-                    kill(signal.SIGKILL)
-                    p.wait()
-                    return 83
+                rc = deliver(on_exit, 0)
+                if rc is not None:
+                    return rc
             return p.wait()
 
 

@@ -256,14 +256,16 @@ def calculate_batch_sizes(hparams: Dict[str, Any], slots_per_trial: int, trialna
     slots = max(int(slots_per_trial), 1)
     if "global_batch_size" not in hparams:
         raise errors.InvalidExperimentException(
-            f"`global_batch_size` hyperparameter is required for {trialname}-based training")
+            f"Please specify an integer `global_batch_size` hyperparameter in your experiment config: "
+            f"`global_batch_size` is a required hyperparameter for running experiments with {trialname}-based training.")
     gbs = hparams["global_batch_size"]
     if not isinstance(gbs, int) or isinstance(gbs, bool):
         raise errors.InvalidExperimentException(
-            f"`global_batch_size` must be an integer, not {type(gbs).__name__}")
+            f"`global_batch_size` hyperparameter must be an integer value, not {type(gbs).__name__}. Use int or const types.")
     if gbs < slots:
         raise errors.InvalidExperimentException(
-            f"`global_batch_size` ({gbs}) must be >= slots_per_trial ({slots})")
+            f"Please set the `global_batch_size` hyperparameter to be greater or equal to the number of slots. "
+            f"Current batch_size: {gbs}, slots_per_trial: {slots}.")
     per_slot = gbs // slots
     eff = per_slot * slots
     if eff != gbs:

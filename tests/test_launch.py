@@ -104,7 +104,7 @@ def test_pid_server_fails_fast_when_a_worker_dies(tmp_path):
     worker still sleeping) are signalled after the grace period."""
     r, dt = _pid_server(tmp_path, ["import time; time.sleep(60)", "import sys, time; time.sleep(0.5); sys.exit(7)"])
     assert r.returncode != 0 and dt < 30, (r.returncode, dt, r.stdout[-2000:])
-    assert "died without a graceful exit" in r.stdout
+    assert "without a graceful exit" in r.stdout
 
 
 @pytest.mark.parametrize("module,flag", [("deepspeed", "USE_DEEPSPEED"), ("horovod", None)])

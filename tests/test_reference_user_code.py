@@ -34,3 +34,24 @@ def test_reference_fixture_trials_run_unmodified(tmp_path):
     for _, cls, _, _ in CASES:
         assert f"REFERENCE_TRIAL_OK {cls}" in r.stdout, f"{cls} failed:\n" + r.stdout[-4000:]
     assert r.returncode == 0, r.stdout[-3000:]
+
+
+REF_TESTS = [
+    # (file, -k expression, minimum number of tests that must pass)
+    ("tests/core/test_searcher.py", "", 5),
+    ("tests/core/test_preempt.py", "", 14),
+    ("tests/test_util.py", "", 11),
+    ("tests/test_ipc.py", "PIDServer or distributed_context", 14),      # the one left out drives ZeroMQ classes directly
+]
+
+
+@pytest.mark.parametrize("path,expr,n", REF_TESTS, ids=[t[0].split("/")[-1] for t in REF_TESTS])
+def test_reference_unit_tests_pass_against_this_package(path, expr, n, tmp_path):
+    """The reference's own unit tests of the searcher / preemption contexts, utilities, DistributedContext and the PID
+    watchdog, run as they are against ``determined_b200`` under the ``determined`` alias."""
+    import re
+
+    args = [sys.executable, str(RUNNER.with_name("run_reference_tests.py")), str(REF), path] + (["-k", expr] if expr else [])
+    r = subprocess.run(args, cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    m = re.search(r"(\d+) passed", r.stdout)
+    assert r.returncode == 0 and m and int(m.group(1)) >= n and " failed" not in r.stdout.splitlines()[-1], r.stdout[-3000:]
