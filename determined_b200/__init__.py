@@ -31,7 +31,9 @@ def install_alias(name: str = "determined") -> None:
                 mod = importlib.import_module(real)
             except ImportError:
                 return None
-            sys.modules[fullname] = mod
+            # Do NOT put the module into sys.modules here: importlib's _find_spec would then take the module's own spec (real name,
+            # source loader) instead of ours and execute the package a second time under its real name -> duplicate classes.
+            # _load_unlocked registers sys.modules[fullname] itself, with the object create_module hands back.
             return importlib.util.spec_from_loader(fullname, loader=_Loader(mod))
 
     class _Loader:

@@ -158,9 +158,11 @@ def from_string(shortcut: str) -> StorageManager:
         raise ValueError(f'Malformed checkpoint_storage string "{shortcut}"')
     scheme = u.scheme.lower()
     if scheme in ("", "file"):
-        return storage.SharedFSStorageManager(os.path.abspath(u.path))
+        if u.netloc:
+            raise ValueError(f'Malformed checkpoint_storage string "{shortcut}": a file path cannot name a host')
+        return storage.SharedFSStorageManager(base_path=u.path if scheme else shortcut)
     if scheme == "s3":
-        return storage.S3StorageManager(bucket=u.netloc, prefix=u.path.lstrip("/"), temp_dir=tempfile.gettempdir())
+        return storage.S3StorageManager(bucket=u.netloc, prefix=u.path.lstrip("/"))
     if scheme == "gs":
-        return storage.GCSStorageManager(bucket=u.netloc, prefix=u.path.lstrip("/"), temp_dir=tempfile.gettempdir())
-    raise NotImplementedError("only shared_fs, s3, and gs storage shortcuts are supported")
+        return storage.GCSStorageManager(bucket=u.netloc, prefix=u.path.lstrip("/"))
+    raise ValueError(f'Unsupported checkpoint_storage string "{shortcut}": only absolute paths, file://, s3:// and gs:// are understood')

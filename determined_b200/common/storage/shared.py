@@ -75,8 +75,9 @@ class SharedFSStorageManager(base.StorageManager):
         extra = set(config) - allowed
         if extra:
             raise TypeError(f"unexpected shared_fs keys: {sorted(extra)}")
-        # Single box, no containers: the host path *is* the path we see.
-        return cls(full_storage_path(config["host_path"], config.get("storage_path"), None))
+        # Tasks here are host processes, so callers pass container_path=None and the host path is the path we see; a caller
+        # that does run inside a mount (the reference's containers bind host_path at container_path) may still say so.
+        return cls(full_storage_path(config["host_path"], config.get("storage_path"), container_path))
 
     def post_store_path(self, src: Union[str, os.PathLike], dst: str) -> None:
         # direct access: nothing to do.

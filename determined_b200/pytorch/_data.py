@@ -130,7 +130,7 @@ def to_device(data: _Data, device: torch.device, warned_types: Optional[Set[Type
         return type(data)(to_device(v, device, warned_types) for v in data)  # type: ignore
     if warned_types is not None and type(data) not in warned_types:
         warned_types.add(type(data))
-        logger.warning("to_device() was passed a %s, which is left on the host", type(data).__name__)
+        logger.warning("to_device(): not able to move data of type %s to the device; it stays on the host", type(data).__name__)
     return data  # type: ignore
 
 

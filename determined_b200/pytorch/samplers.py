@@ -77,7 +77,7 @@ class SkipBatchSampler(BatchSampler):
         self.batch_sampler, self.skip = batch_sampler, skip
 
     def __len__(self) -> int:
-        return max(len(self.batch_sampler) - self.skip, 0)
+        return len(self.batch_sampler)          # the length of an epoch does not change, only where the first one starts
 
     def __iter__(self) -> Iterator[List[int]]:
         it = iter(self.batch_sampler)
@@ -87,6 +87,44 @@ class SkipBatchSampler(BatchSampler):
             except StopIteration:
                 return
         yield from it
+
+
+class SkipSampler(Sampler):
+    """Record-level twin of :class:`SkipBatchSampler`: drops the first ``skip`` indices, keeps the epoch length."""
+
+    def __init__(self, sampler: Sampler, skip: int) -> None:
+        self.sampler, self.skip = sampler, skip
+
+    def __len__(self) -> int:
+        return len(self.sampler)  # type: ignore[arg-type]
+
+    def __iter__(self) -> Iterator[int]:
+        it = iter(self.sampler)
+        for _ in range(self.skip):
+            try:
+                next(it)
+            except StopIteration:
+                return
+        yield from it
+
+
+class RepeatSampler(Sampler):
+    """Cycles through ``sampler`` forever (every pass re-iterates it, so a shuffling sampler reshuffles)."""
+
+    def __init__(self, sampler: Sampler) -> None:
+        self.sampler = sampler
+
+    def __len__(self) -> int:
+        return len(self.sampler)  # type: ignore[arg-type]
+
+    def __iter__(self) -> Iterator[int]:
+        while True:
+            n = 0
+            for i in self.sampler:
+                n += 1
+                yield i
+            if n == 0:
+                return
 
 
 class ReproducibleShuffleSampler(Sampler):

@@ -478,3 +478,30 @@ def test_idle_timeout_kills_a_quiet_service_and_proxy_traffic_keeps_it_alive(clu
         time.sleep(0.2)
     assert t.state == "TERMINATED" and t.killed
     assert "idle for more than 3s" in "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{t.id}/logs").json()["logs"])
+
+
+def test_install_alias_never_executes_a_module_twice(tmp_path):
+    """`import determined.x` must hand back the very module object of `determined_b200.x` (a second execution of a package
+    under its real name would duplicate every class: isinstance checks and mock.patch targets would silently miss)."""
+    import subprocess
+
+    code = (
+        "import sys, determined_b200\n"
+        "import determined_b200.pytorch as rp, determined_b200.common as rc\n"
+        "determined_b200.install_alias()\n"
+        "import determined.pytorch as p, determined.common as c\n"
+        "from determined.common import storage, api\n"
+        "from determined import core\n"
+        "assert p is rp and c is rc and sys.modules['determined_b200.common'] is rc and sys.modules['determined_b200.pytorch'] is rp\n"
+        "assert p.PyTorchTrial is rp.PyTorchTrial and core is determined_b200.core\n"
+        "import determined.common.storage as s2\n"
+        "assert s2 is storage and s2 is sys.modules['determined_b200.common.storage']\n"
+        "from unittest import mock\n"
+        "for _ in range(2):\n"
+        "    with mock.patch('determined.common.storage.SharedFSStorageManager') as m:\n"
+        "        storage.from_string('/tmp/x')\n"
+        "    m.assert_called_once_with(base_path='/tmp/x')\n"
+        "print('ALIAS_OK')\n")
+    r = subprocess.run([sys.executable, "-c", code], cwd=tmp_path, env=dict(__import__("os").environ, PYTHONPATH=str(pathlib.Path(__file__).resolve().parents[1])),
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert "ALIAS_OK" in r.stdout, r.stdout[-2000:]

@@ -42,6 +42,10 @@ REF_TESTS = [
     ("tests/core/test_preempt.py", "", 14),
     ("tests/test_util.py", "", 11),
     ("tests/test_ipc.py", "PIDServer or distributed_context", 14),      # the one left out drives ZeroMQ classes directly
+    ("tests/experiment/pytorch/test_pytorch_data.py", "", 24),          # samplers, adapt_batch_sampler, to_device
+    ("tests/experiment/pytorch/test_reducer.py", "", 5),
+    ("tests/storage/test_storage_base.py", "not shared_fs_shortcut_dict", 21),   # the one left out calls a private helper of core._context
+    ("tests/common/test_yaml.py", "", 4),
 ]
 
 

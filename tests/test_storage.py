@@ -63,7 +63,7 @@ def test_build_and_shortcuts(tmp_path):
     assert isinstance(storage.from_string(str(tmp_path)), storage.SharedFSStorageManager)
     assert isinstance(storage.from_string("s3://bucket/prefix"), storage.S3StorageManager)
     assert isinstance(storage.from_string("gs://bucket/p"), storage.GCSStorageManager)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(ValueError):
         storage.from_string("ftp://x/y")
     with pytest.raises(ValueError):
         storage.build({"type": "azure", "container": "c"}, None)
