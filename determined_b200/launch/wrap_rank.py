@@ -13,10 +13,30 @@ from typing import IO, List, Optional
 
 
 def forward(src: IO[bytes], dst: IO[bytes], prefix: bytes) -> None:
-    for line in iter(src.readline, b""):
-        if not line.endswith(b"\n"):
-            line += b"\n"
-        dst.write(prefix + line)
+    """Copy ``src`` to ``dst`` line by line with ``prefix``; a carriage return ends a line too (progress bars redraw with
+    ``\r`` and would otherwise sit in the buffer until the next newline), and every emitted line ends with ``\n``."""
+    fd = src.fileno()
+    pending = b""
+    while True:
+        chunk = os.read(fd, 65536)
+        if not chunk:
+            break
+        pending += chunk
+        out = []
+        while True:
+            cut = min((i for i in (pending.find(b"\n"), pending.find(b"\r")) if i >= 0), default=-1)
+            if cut < 0:
+                break
+            was_cr = pending[cut:cut + 1] == b"\r"
+            line, pending = pending[:cut], pending[cut + 1:]
+            if was_cr and pending[:1] == b"\n":
+                pending = pending[1:]           # \r\n is one line end
+            out.append(prefix + line + b"\n")
+        if out:
+            dst.write(b"".join(out))
+            dst.flush()
+    if pending:
+        dst.write(prefix + pending + b"\n")
         dst.flush()
 
 
@@ -32,6 +52,9 @@ def main(argv: Optional[List[str]] = None) -> int:
         p.error("a command is required")
     rank = None
     for name in a.rank_var_name.split(","):
+        if name.isdigit():                      # a literal rank instead of a variable name
+            rank = name
+            break
         if name in os.environ:
             rank = os.environ[name]
             break
@@ -41,7 +64,11 @@ def main(argv: Optional[List[str]] = None) -> int:
           threading.Thread(target=forward, args=(proc.stderr, sys.stderr.buffer, prefix), daemon=True)]
     for t in ts:
         t.start()
-    from determined_b200 import util
+    try:
+        from determined_b200 import util
+    except ImportError:                         # run as a plain script file (python .../wrap_rank.py): find the package next to it
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+        from determined_b200 import util
 
     with util.forward_signals(proc):
         rc = proc.wait()

@@ -46,6 +46,7 @@ REF_TESTS = [
     ("tests/experiment/pytorch/test_reducer.py", "", 5),
     ("tests/storage/test_storage_base.py", "not shared_fs_shortcut_dict", 21),   # the one left out calls a private helper of core._context
     ("tests/common/test_yaml.py", "", 4),
+    ("tests/launch/test_wrap_rank.py", "", 1),
 ]
 
 
