@@ -51,6 +51,34 @@ class CheckpointState(enum.Enum):
     PARTIALLY_DELETED = "STATE_PARTIALLY_DELETED"
 
 
+class OrderBy(enum.Enum):
+    """Ascending or descending order of a sorted listing."""
+
+    ASCENDING = "ORDER_BY_ASC"
+    ASC = "ORDER_BY_ASC"
+    DESCENDING = "ORDER_BY_DESC"
+    DESC = "ORDER_BY_DESC"
+
+
+TrialOrderBy = ModelOrderBy = CheckpointOrderBy = OrderBy          # deprecated names of the same enum
+
+
+class TrialSortBy(enum.Enum):
+    """Field a listing of trials is sorted on."""
+
+    ID = "SORT_BY_ID"
+    START_TIME = "SORT_BY_START_TIME"
+    END_TIME = "SORT_BY_END_TIME"
+    STATE = "SORT_BY_STATE"
+    BEST_VALIDATION_METRIC = "SORT_BY_BEST_VALIDATION_METRIC"
+    LATEST_VALIDATION_METRIC = "SORT_BY_LATEST_VALIDATION_METRIC"
+    BATCHES_PROCESSED = "SORT_BY_BATCHES_PROCESSED"
+    DURATION = "SORT_BY_DURATION"
+    RESTARTS = "SORT_BY_RESTARTS"
+    CHECKPOINT_SIZE = "SORT_BY_CHECKPOINT_SIZE"
+    LOG_RETENTION_DAYS = "SORT_BY_LOG_RETENTION_DAYS"
+
+
 class ModelSortBy(enum.Enum):
     NAME = "SORT_BY_NAME"
     CREATION_TIME = "SORT_BY_CREATION_TIME"
@@ -275,9 +303,30 @@ class Experiment:
             raise ValueError(f"project {project_name!r} not found")
         self._session.post(f"/api/v1/experiments/{self.id}/move", json={"destinationProjectId": pr[0]["id"]})
 
-    def list_trials(self) -> List[Trial]:
-        r = self._session.get(f"/api/v1/experiments/{self.id}/trials").json()
-        return [Trial(self._session, t["id"], t) for t in r["trials"]]
+    def list_trials(self, sort_by: TrialSortBy = TrialSortBy.ID, order_by: OrderBy = OrderBy.ASCENDING) -> List[Trial]:
+        r = self._session.get(f"/api/v1/experiments/{self.id}/trials", params={"limit": 10000}).json()
+        rows = r["trials"]
+
+        def metric(d: Optional[Dict[str, Any]]) -> Any:
+            m = ((d or {}).get("metrics") or {})
+            m = m.get("avgMetrics", m)
+            name = ((self.config or {}).get("searcher") or {}).get("metric")
+            return m.get(name) if isinstance(m, dict) else None
+
+        keys = {
+            TrialSortBy.ID: lambda t: t["id"], TrialSortBy.START_TIME: lambda t: t.get("startTime") or "",
+            TrialSortBy.END_TIME: lambda t: t.get("endTime") or "", TrialSortBy.STATE: lambda t: t.get("state") or "",
+            TrialSortBy.BEST_VALIDATION_METRIC: lambda t: metric(t.get("bestValidation")),
+            TrialSortBy.LATEST_VALIDATION_METRIC: lambda t: metric(t.get("latestValidation")),
+            TrialSortBy.BATCHES_PROCESSED: lambda t: t.get("totalBatchesProcessed") or 0, TrialSortBy.RESTARTS: lambda t: t.get("restarts") or 0,
+            TrialSortBy.DURATION: lambda t: (t.get("endTime") or "") > "" and (t.get("endTime"), t.get("startTime")) or ("", ""),
+            TrialSortBy.CHECKPOINT_SIZE: lambda t: int(t.get("totalCheckpointSize") or 0), TrialSortBy.LOG_RETENTION_DAYS: lambda t: t.get("logRetentionDays") or 0,
+        }
+        key = keys[TrialSortBy(sort_by)]
+        have = [t for t in rows if key(t) is not None]
+        rest = [t for t in rows if key(t) is None]                        # trials without the value go last in either order
+        have.sort(key=key, reverse=OrderBy(order_by) in (OrderBy.DESCENDING, OrderBy.DESC))
+        return [Trial(self._session, t["id"], t) for t in have + rest]
 
     get_trials = list_trials
 

@@ -314,3 +314,14 @@ def test_hp_visualisation_endpoints(cluster):
     assert [x["name"] for x in summ["metrics"]] == ["loss"] and len(summ["metrics"][0]["data"]) == 3 and summ["trial"]["id"] == trials[0].id
     cmp_ = sess.get("/api/v1/trials/compare", params={"trialIds": [t.id for t in trials]}).json()["trials"]
     assert len(cmp_) == 2 and {x["name"] for x in cmp_[1]["metrics"]} == {"acc", "loss", "val_loss"}
+
+
+def test_sdk_list_trials_sorting(cluster):
+    m, tmp = cluster
+    d = sdk.Determined(m.url)
+    exp = d.create_experiment(CFG, str(FIX))
+    ids = [t.id for t in exp.list_trials()]
+    assert ids == sorted(ids) and len(ids) == 2
+    assert [t.id for t in exp.list_trials(sort_by=sdk.TrialSortBy.ID, order_by=sdk.OrderBy.DESC)] == sorted(ids, reverse=True)
+    assert sdk.OrderBy.ASC is sdk.OrderBy.ASCENDING and sdk.TrialOrderBy is sdk.OrderBy
+    assert len(exp.list_trials(sort_by=sdk.TrialSortBy.BEST_VALIDATION_METRIC)) == 2        # no validations yet: still listed
