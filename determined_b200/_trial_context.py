@@ -16,6 +16,8 @@ class EnvContext:
     """What a launched trial process knows about its surroundings (filled from ``det.get_cluster_info()``)."""
 
     master_url: str = ""
+    master_cert_file: Optional[str] = None
+    master_cert_name: Optional[str] = None
     experiment_config: Dict[str, Any] = dataclasses.field(default_factory=dict)
     hparams: Dict[str, Any] = dataclasses.field(default_factory=dict)
     latest_checkpoint: Optional[str] = None
@@ -31,6 +33,9 @@ class EnvContext:
     test_mode: bool = False
     on_cluster: bool = False
     slot_ids: List[int] = dataclasses.field(default_factory=list)
+    use_gpu: bool = False
+    container_gpus: List[str] = dataclasses.field(default_factory=list)
+    debug: bool = False
 
     @classmethod
     def from_cluster_info(cls, info: Any) -> "EnvContext":

@@ -15,6 +15,7 @@ import threading
 from typing import Any, Callable, Dict, List, Optional, Tuple
 
 from determined_b200.common import storage
+from determined_b200.tensorboard import util  # noqa: E402
 
 logger = logging.getLogger("determined.tensorboard")
 
@@ -38,18 +39,16 @@ def get_base_path(checkpoint_config: Dict[str, Any]) -> pathlib.Path:
 
 
 def get_rank_aware_path(path: pathlib.Path, rank: int) -> pathlib.Path:
-    """``events.out.tfevents.123`` stays; other files get ``#<rank>`` inserted before the suffix."""
-    if rank == 0 or "tfevents" in path.name:
-        return path
-    stem, suffix = path.stem, path.suffix
-    return path.with_name(f"{stem}#{rank}{suffix}")
+    """Name under which a non-chief rank's file is uploaded (``tensorboard/util.py`` has the rules); rank 0 and event files keep theirs."""
+    if rank == 0 or "tfevents" in pathlib.Path(path).name:
+        return pathlib.Path(path)
+    return util.get_rank_aware_path(pathlib.Path(path), rank)
 
 
 class TensorboardManager:
     def __init__(self, base_path: pathlib.Path, sync_path: pathlib.Path, async_upload: bool = True) -> None:
         self.base_path = pathlib.Path(base_path)
-        self.sync_path = pathlib.Path(sync_path)
-        self.base_path.mkdir(parents=True, exist_ok=True)
+        self.sync_path = pathlib.Path(sync_path)        # (the directory is created by build(), not here: a manager may point anywhere)
         self._seen: Dict[pathlib.Path, float] = {}
         self._q: "queue.Queue[Any]" = queue.Queue()
         self._thread: Optional[threading.Thread] = None
@@ -68,6 +67,22 @@ class TensorboardManager:
                     continue
                 self._seen[p] = mt
                 out.append(p)
+        return out
+
+    def list_tb_files(self, rank: int, selector: Callable[[pathlib.Path], bool] = lambda _: True) -> List[pathlib.Path]:
+        """Files under ``base_path`` a sync would consider: every rank's event files are theirs alone, so the chief takes all
+        files and the other ranks everything except event files (those stay per-rank on the chief's side)."""
+        if not self.base_path.exists():
+            logger.warning("%s directory does not exist.", self.base_path)
+            return []
+        out = []
+        for root, _, files in os.walk(self.base_path):
+            for f in files:
+                p = pathlib.Path(root, f)
+                if rank != 0 and "tfevents" in f:
+                    continue
+                if selector(p):
+                    out.append(p)
         return out
 
     def _upload(self, pairs: List[Tuple[pathlib.Path, pathlib.Path]]) -> None:
@@ -153,6 +168,7 @@ def build(cluster_id: str, experiment_id: Any, trial_id: Any, checkpoint_config:
           container_path: Optional[str] = None, async_upload: bool = True) -> TensorboardManager:
     kind = checkpoint_config.get("type")
     base = get_base_path(checkpoint_config)
+    base.mkdir(parents=True, exist_ok=True)
     sync = get_sync_path(cluster_id, experiment_id, trial_id)
     if kind in ("shared_fs", "directory"):
         mgr = storage.build(checkpoint_config, container_path)
