@@ -97,7 +97,8 @@ def apply_globs_to_resources(resources: Dict[str, int], prefix: str, globs: List
 class StorageManager(metaclass=abc.ABCMeta):
     """Abstract persistent store addressed by ``storage_id`` (a checkpoint uuid)."""
 
-    def __init__(self, base_path: str) -> None:
+    def __init__(self, base_path: Union[str, os.PathLike]) -> None:
+        base_path = os.fspath(base_path) if isinstance(base_path, os.PathLike) else base_path
         if not isinstance(base_path, str) or not base_path:
             raise ValueError("base_path must be a non-empty string")
         self._base_path = base_path

@@ -166,17 +166,21 @@ class StorageTensorboardManager(TensorboardManager):
 
 def build(cluster_id: str, experiment_id: Any, trial_id: Any, checkpoint_config: Dict[str, Any],
           container_path: Optional[str] = None, async_upload: bool = True) -> TensorboardManager:
-    kind = checkpoint_config.get("type")
+    if "type" not in checkpoint_config:
+        raise TypeError("Missing 'type' parameter of storage configuration")
+    kind = checkpoint_config["type"]
+    if not isinstance(kind, str):
+        raise TypeError("`type` parameter of storage configuration must be a string")
+    if kind not in ("shared_fs", "directory", "s3", "gcs", "azure"):
+        raise TypeError(f"Unknown storage type: {kind}")
     base = get_base_path(checkpoint_config)
     base.mkdir(parents=True, exist_ok=True)
     sync = get_sync_path(cluster_id, experiment_id, trial_id)
+    storage_config = {k: v for k, v in checkpoint_config.items() if k != "base_path"}      # base_path is ours, not the storage manager's
+    mgr = storage.build(storage_config, container_path)
     if kind in ("shared_fs", "directory"):
-        mgr = storage.build(checkpoint_config, container_path)
         return SharedFSTensorboardManager(mgr._base_path, base, sync, async_upload=async_upload)
-    if kind in ("s3", "gcs", "azure"):
-        return StorageTensorboardManager(storage.build(checkpoint_config, container_path), base, sync,
-                                         async_upload=async_upload)
-    raise TypeError(f"Unknown storage type for tensorboard: {kind}")
+    return StorageTensorboardManager(mgr, base, sync, async_upload=async_upload)
 
 
 def get_metric_writer() -> Any:

@@ -48,6 +48,7 @@ REF_TESTS = [
     ("tests/common/test_yaml.py", "", 4),
     ("tests/launch/test_wrap_rank.py", "", 1),
     ("tests/tensorboard/test_util.py", "not nonexistent_directory", 9),        # that one needs a path that does not exist on the test machine
+    ("tests/tensorboard/test_base.py", "not upload_thread", 7),                # that one constructs a private upload-thread class
     ("tests/core/test_checkpoint.py", "not test_checkpoint_context", 16),      # the one left out asserts on private call sites (mocks)
 ]
 
