@@ -17,13 +17,21 @@ DEFAULT_MAX_RETRIES = 5
 
 
 def canonicalize_master_url(url: str) -> str:
-    if "://" not in url:
-        url = "http://" + url
-    scheme, rest = url.split("://", 1)
-    host = rest.rstrip("/")
-    if ":" not in host.split("/")[0]:
-        host = host + (":443" if scheme == "https" else ":8080")
-    return f"{scheme}://{host}"
+    """``host`` -> ``http://host:8080``; explicit schemes get their own default port (80 / 443); a path is kept without its
+    trailing slash; credentials, queries and fragments are refused, as is an empty host."""
+    import urllib.parse
+
+    bare = "://" not in url
+    u = urllib.parse.urlparse(("http://" + url) if bare else url)
+    if u.username or u.password or u.query or u.fragment or u.params:
+        raise ValueError(f"master url must not contain username, password, query, or fragment: {url!r}")
+    if not u.hostname:
+        raise ValueError(f"master url must contain a nonempty hostname: {url!r}")
+    if u.scheme not in ("http", "https"):
+        raise ValueError(f"master url must be http or https: {url!r}")
+    port = u.port or (8080 if bare else 443 if u.scheme == "https" else 80)
+    host = f"[{u.hostname}]" if ":" in u.hostname else u.hostname
+    return f"{u.scheme}://{host}:{port}{u.path.rstrip('/')}"
 
 
 class BaseSession:

@@ -46,6 +46,7 @@ REF_TESTS = [
     ("tests/experiment/pytorch/test_reducer.py", "", 5),
     ("tests/storage/test_storage_base.py", "not shared_fs_shortcut_dict", 21),   # the one left out calls a private helper of core._context
     ("tests/common/test_yaml.py", "", 4),
+    ("tests/common/test_api.py", "", 15),                                       # master URL canonicalisation
     ("tests/launch/test_wrap_rank.py", "", 1),
     ("tests/tensorboard/test_util.py", "not nonexistent_directory", 9),        # that one needs a path that does not exist on the test machine
     ("tests/tensorboard/test_base.py", "not upload_thread", 7),                # that one constructs a private upload-thread class
