@@ -12,6 +12,7 @@ import shutil
 import tempfile
 from typing import Any, Dict, Iterator, List, Optional, Union
 
+from determined_b200 import errors
 from determined_b200.common.storage import base
 
 
@@ -96,7 +97,7 @@ class S3StorageManager(CloudStorageManager):
             os.makedirs(os.path.dirname(target), exist_ok=True)
             self._b().download_file(obj.key, target)
         if not found:
-            raise FileNotFoundError(f"no objects under s3://{self.bucket_name}/{pfx}")
+            raise errors.CheckpointNotFound(f"no objects under s3://{self.bucket_name}/{pfx}")
 
     def delete(self, tgt: str, globs: List[str]) -> Dict[str, int]:
         pfx = self._key(tgt) + "/"
@@ -150,7 +151,7 @@ class GCSStorageManager(CloudStorageManager):
             os.makedirs(os.path.dirname(target), exist_ok=True)
             blob.download_to_filename(target)
         if not found:
-            raise FileNotFoundError(f"no objects under gs://{self.bucket_name}/{pfx}")
+            raise errors.CheckpointNotFound(f"no objects under gs://{self.bucket_name}/{pfx}")
 
     def delete(self, tgt: str, globs: List[str]) -> Dict[str, int]:
         pfx = self._key(tgt) + "/"
@@ -204,7 +205,7 @@ class AzureStorageManager(CloudStorageManager):
             with open(target, "wb") as f:
                 self._c().download_blob(b["name"]).readinto(f)
         if not found:
-            raise FileNotFoundError(f"no blobs under {self.container}/{pfx}")
+            raise errors.CheckpointNotFound(f"no blobs under {self.container}/{pfx}")
 
     def delete(self, tgt: str, globs: List[str]) -> Dict[str, int]:
         pfx = f"{tgt}/"

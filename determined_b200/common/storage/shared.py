@@ -12,6 +12,7 @@ import pathlib
 import shutil
 from typing import Any, Dict, Iterator, List, Optional, Union
 
+from determined_b200 import errors
 from determined_b200 import util
 from determined_b200.common.storage import base
 
@@ -91,7 +92,7 @@ class SharedFSStorageManager(base.StorageManager):
         # Zero-copy: hand out the real directory.  (selector is irrelevant: nothing is copied.)
         d = os.path.join(self._base_path, src)
         if not os.path.isdir(d):
-            raise FileNotFoundError(f"checkpoint directory not found: {d}")
+            raise errors.CheckpointNotFound(f"checkpoint directory not found: {d}")
         yield pathlib.Path(d)
 
     def delete(self, tgt: str, globs: List[str]) -> Dict[str, int]:
@@ -132,5 +133,5 @@ class SharedFSStorageManager(base.StorageManager):
     def download(self, src: str, dst: Union[str, os.PathLike], selector: Optional[base.Selector] = None) -> None:
         source = os.path.join(self._base_path, src)
         if not os.path.isdir(source):
-            raise FileNotFoundError(f"checkpoint directory not found: {source}")
+            raise errors.CheckpointNotFound(f"checkpoint directory not found: {source}")
         copytree(source, os.fspath(dst), selector=selector)

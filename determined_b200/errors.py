@@ -35,6 +35,11 @@ class InvalidCheckpointException(Exception):
         super().__init__("Invalid checkpoint." if why is None else f"Invalid checkpoint: {why}")
 
 
+class CheckpointNotFound(FileNotFoundError):
+    """The storage backend holds nothing under the requested checkpoint id (also a ``FileNotFoundError``, so callers that
+    predate this class keep working)."""
+
+
 class StopLoadingImplementation(Exception):
     """Used to interrupt the import of user code (``det.load``)."""
 

@@ -45,6 +45,7 @@ REF_TESTS = [
     ("tests/experiment/pytorch/test_pytorch_data.py", "", 24),          # samplers, adapt_batch_sampler, to_device
     ("tests/experiment/pytorch/test_reducer.py", "", 5),
     ("tests/storage/test_storage_base.py", "not shared_fs_shortcut_dict", 21),   # the one left out calls a private helper of core._context
+    ("tests/storage/test_shared_fs.py", "tensorboard_fetcher", 1),                 # incremental TensorBoard fetcher over a shared filesystem
     ("tests/common/test_yaml.py", "", 4),
     ("tests/common/test_api.py", "", 15),                                       # master URL canonicalisation
     ("tests/launch/test_wrap_rank.py", "", 1),
