@@ -90,8 +90,9 @@ def test_command_runs_on_remote_agent(cluster):
     r = sess.post("/api/v1/commands", json={"config": {"entrypoint": ["/bin/sh", "-c", "echo agent=$DET_AGENT_ID; echo done"], "resources": {"slots": 0}}}).json()
     cid = r["command"]["id"]
     _wait(lambda: sess.get(f"/api/v1/commands/{cid}").json()["command"]["state"] == "STATE_TERMINATED", 30, "command exit")
-    logs = "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{cid}/logs").json()["logs"])
-    assert "agent=agent-1" in logs and "done" in logs
+    get_logs = lambda: "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{cid}/logs").json()["logs"])  # noqa: E731
+    _wait(lambda: "done" in get_logs(), 10, "the command's output in the task log")
+    assert "agent=agent-1" in get_logs()
 
 
 def test_agent_restart_reattaches_and_disconnect_fails_tasks(cluster, monkeypatch):
@@ -145,7 +146,7 @@ def test_resource_pools_route_work_to_the_agents_registered_in_them(tmp_path):
         cid = r["command"]["id"]
         assert r["command"]["resourcePool"] == "aux"
         _wait(lambda: sess.get(f"/api/v1/commands/{cid}").json()["command"]["state"] == "STATE_TERMINATED", 30, "command exit")
-        assert "on=aux-1" in "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{cid}/logs").json()["logs"])
+        _wait(lambda: "on=aux-1" in "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{cid}/logs").json()["logs"]), 10, "command output")
         with pytest.raises(api.errors.APIException, match="unknown resource pool"):
             create(sess, dict(BASE, resources={"slots_per_trial": 1, "resource_pool": "nope"}))
         with pytest.raises(api.errors.APIException):
