@@ -138,6 +138,54 @@ class Bracket:
         return float(t.item())
 
 
+def allreduce_self_check(world: int) -> str:
+    """At N > 1, before anything is timed: the in-kernel all-reduce (whichever transport the engine will pick on this box:
+    NVSwitch in-switch reduction, else two-shot peer-to-peer) against ``torch.distributed.all_reduce`` on rank-seeded data,
+    and the propagation of a non-finite value from one rank to every rank's found_inf flag.  Raises on mismatch."""
+    import torch
+    import torch.distributed as dist
+
+    from determined_b200.ops import comm
+
+    dev = torch.device("cuda", torch.cuda.current_device())
+    group = comm.PeerGroup.from_torch_distributed(dev)
+    n = 4 * world * 300_000
+    buf = group.alloc(4 * n)
+    peers = group.map(buf)
+    mc = group.multicast(buf)
+    t = buf.tensor(torch.float32, n)
+    transports = [("nvls", mc)] if mc else []
+    transports.append(("p2p", None))
+    for name, m in transports:
+        torch.manual_seed(1000 + group.rank)
+        t.copy_(torch.randn(n, device=dev))
+        ref = t.clone()
+        dist.all_reduce(ref)
+        ref.mul_(1.0 / world)
+        group.begin_step()
+        group.found_inf.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce_fused(group, peers, 0, n, 1.0 / world, found_inf=group.found_inf, timeout_s=30, mc_ptr=m)
+        torch.cuda.synchronize()
+        err = float((t - ref).abs().max())
+        if not err <= 1e-5 or int(group.found_inf.item()) != 0:
+            raise RuntimeError(f"allreduce self-check failed ({name}): max abs error {err}, found_inf {int(group.found_inf.item())}")
+        t.zero_()
+        if group.rank == world - 1:
+            t[3] = float("inf")
+        group.begin_step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce_fused(group, peers, 0, n, 1.0, found_inf=group.found_inf, timeout_s=30, mc_ptr=m)
+        torch.cuda.synchronize()
+        if int(group.found_inf.item()) != 1:
+            raise RuntimeError(f"allreduce self-check failed ({name}): a non-finite value on one rank was not reported on rank {group.rank}")
+    dist.barrier()
+    group.close()
+    return "ok (" + "+".join(n for n, _ in transports) + ", max abs err <= 1e-5 vs NCCL, found_inf propagates)"
+
+
 def run_ours(args, on_device: bool, sampler):
     import torch
 
@@ -150,6 +198,8 @@ def run_ours(args, on_device: bool, sampler):
 
     class BenchCallback(pytorch.PyTorchCallback):
         def on_training_batch_start(self, batch_idx: int) -> None:
+            if batch_idx == 0 and args.world > 1 and not getattr(args, "_checked", None):
+                args._checked = allreduce_self_check(args.world)      # fails the run before anything is timed
             if batch_idx == bracket.first:
                 eng = counters["ctx"]._get_engine()
                 counters["launch0"] = getattr(eng, "kernel_launches", 0)
@@ -180,9 +230,14 @@ def run_ours(args, on_device: bool, sampler):
             ms = bracket.max_over_ranks_ms()
             launches = counters.get("launch1", 0) - counters.get("launch0", 0)
             fused = type(trial.opt).__name__
+            eng = ctx._get_engine()
+            rec = next(iter(eng.records.values()))
+            info = {"optimizer": fused, "buckets": len(rec.buckets),
+                    "transport": ("nvls" if rec.mc_ptr else "p2p") if args.world > 1 else "none"}
+            info["allreduce_check"] = getattr(args, "_checked", None)
     finally:
         os.chdir(cwd)
-    return ms, launches, fused
+    return ms, launches, info
 
 
 def run_reference(args, sampler):
@@ -257,6 +312,7 @@ def main() -> None:
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"),
                os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
+    requested_warmup = args.warmup
     args.warmup = max(args.warmup, 4)
     args.warmup += args.warmup % AGG_FREQ          # start the bracket on an aggregation boundary
     args.steps += args.steps % AGG_FREQ
@@ -286,13 +342,15 @@ def main() -> None:
                               "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                               "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                               "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                              "config": dict(config, harness="reference determined 0.31.1-dev0, torch DDP/NCCL, eager"),
+                              "warmup_requested": requested_warmup, "config": config,
+                              "harness": "reference determined 0.31.1-dev0 (baseline/_ref, unmodified), torch DDP/NCCL, eager; "
+                                         "host-fed: value == e2e (the reference has no device-resident input mode)",
                               "e2e": {"value": v, "unit": "samples/s",
                                       "h2d_bytes_per_step": PER_SLOT_BATCH * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 4},
                               "clocks": clocks}))
         return
 
-    ms, launches, fused = run_ours(args, on_device=True, sampler=sampler)
+    ms, launches, info = run_ours(args, on_device=True, sampler=sampler)
     clocks = sampler.stop() if sampler is not None else None
     e2e = None
     if not args.skip_e2e:
@@ -306,8 +364,12 @@ def main() -> None:
                           "higher_is_better": True, "scaling": "weak",
                           "vs_baseline": (v / BASELINE_PUBLISHED) if BASELINE_PUBLISHED else None,
                           "dtype": "bf16", "data": "synthetic",
-                          "config": dict(config, harness=f"determined_b200 fused engine ({fused}), "
-                                         f"{'eager' if args.no_graphs else 'CUDA-graph replay'}"),
+                          "warmup_requested": requested_warmup, "config": config,
+                          "harness": f"determined_b200 fused engine ({info['optimizer']}, {info['buckets']} buckets, "
+                                     f"all-reduce transport {info['transport']}), "
+                                     f"{'eager' if args.no_graphs else 'CUDA-graph replay'}; value = device-resident input "
+                                     "pool, e2e = host-fed through pytorch.init + Trainer.fit (compare e2e with the reference)",
+                          "allreduce_check": info.get("allreduce_check"),
                           "e2e": e2e, "gpu_launches": launches, "clocks": clocks}))
 
 

@@ -55,17 +55,6 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ float4 ld_peer(const float4* p) {
-  float4 r;
-  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
-  return r;
-}
-__device__ __forceinline__ void st_peer(float4* p, const float4& v) {
-  asm volatile("st.volatile.global.v4.f32 [%0], {%1,%2,%3,%4};"
-               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
-
 // Spin with a deadline: a peer that never arrives (crashed rank, diverged control flow) must not
 // hang the GPU forever.  On timeout the kernel records it and traps; the host sees a launch
 // failure and the trial restarts from its last checkpoint (SURVEY 5.3 "new build").
@@ -81,98 +70,118 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
   }
 }
 
-// phase bits: 1 = start barrier, 2 = reduce+scatter my slice, 4 = end barrier.  All bits set is the
-// normal multi-GPU launch.  Single-GPU tests emulate W ranks by launching phase 2 once per
-// emulated rank (kernels that spin on each other must not share a GPU).
-__global__ void __launch_bounds__(kCommThreads)
-allreduce_fused_kernel(Peers peers, int rank, int world, int64_t off, int64_t n, float scale,
-                       const float* __restrict__ inv_loss_scale, int* __restrict__ found_inf,
-                       int first_of_step, int phases, long long timeout_cycles) {
-  __shared__ float red[32];
-  __shared__ uint32_t s_epoch;
-  __shared__ bool s_last;
-  Ctrl* me = peers.ctrl[rank];
-  if (threadIdx.x == 0) s_epoch = me->epoch + 1;
-  __syncthreads();
-  const uint32_t epoch = s_epoch;
+// ---- data movement primitives -------------------------------------------------------------------------------------------
+// Peer data is read with weak, L1-bypassing loads: the start barrier (ld.acquire.sys by the polling threads, then
+// bar.sync) orders them after the peers' writes, and L1 holds nothing of these addresses at that point.
+__device__ __forceinline__ float4 ld_weak(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_weak(float4* p, const float4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_weak_u4(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_weak_u4(uint4* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// NVSwitch in-network reduction (NVLS): `p` is an address inside the mapping of a multicast object to which every
+// rank bound its buffer.  ld_reduce returns the fp32 sum over all ranks' copies, computed in the switch; st writes all
+// copies.  One request each per 16 bytes instead of W loads and W stores.
+__device__ __forceinline__ float4 mc_ld_reduce(const float4* p) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void mc_st(float4* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// bf16 wire format: eight bf16 per request, accumulated in fp32 inside the switch
+__device__ __forceinline__ uint4 mc_ld_reduce_bf16(const uint4* p) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void mc_st_u4(uint4* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 
+// ---- the barrier protocol, shared by every collective ------------------------------------------------------------------
+// One "participant" is (rank, bid of nblk): on a real run bid/nblk are blockIdx.x/gridDim.x; the single-GPU emulation
+// packs the CTAs of all ranks into one cooperative grid.
+struct Part {
+  int rank, world, bid, nblk;
+  long long timeout;
+};
+
+// Epoch of this collective + start barrier: nobody touches peer memory before every rank has entered the collective
+// (i.e. finished producing the data that is about to be read, and finished consuming what is about to be overwritten).
+__device__ __forceinline__ uint32_t comm_enter(const Peers& peers, const Part& pt, int phases, uint32_t* s_epoch) {
+  Ctrl* me = peers.ctrl[pt.rank];
+  if (threadIdx.x == 0) *s_epoch = me->epoch + 1;
+  __syncthreads();
+  const uint32_t epoch = *s_epoch;
   if (phases & 1) {
-    if (threadIdx.x < world && threadIdx.x != rank) {
-      if (blockIdx.x == 0) st_release_sys(&peers.ctrl[threadIdx.x]->start[rank], epoch);
-      wait_flag(&me->start[threadIdx.x], epoch, me, timeout_cycles);
+    if (threadIdx.x < pt.world && threadIdx.x != pt.rank) {
+      if (pt.bid == 0) st_release_sys(&peers.ctrl[threadIdx.x]->start[pt.rank], epoch);
+      wait_flag(&me->start[threadIdx.x], epoch, me, pt.timeout);
     }
     __syncthreads();
   }
+  return epoch;
+}
 
-  float sq = 0.f;
-  int bad = 0;
-  if (phases & 2) {
-    const float s = scale * (inv_loss_scale ? *inv_loss_scale : 1.f);
-    // slice boundaries in float4 units; the bucket is padded to a multiple of 4*world elements
-    const int64_t nvec = n >> 2;
-    const int64_t per = (nvec + world - 1) / world;
-    const int64_t v0 = per * rank;
-    const int64_t v1 = (v0 + per < nvec) ? v0 + per : nvec;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += stride) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      // issue all peer loads before consuming them: W independent NVLink requests in flight
-      float4 v[DETB200_MAX_RANKS];
-#pragma unroll
-      for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-        if (r < world) v[r] = ld_peer(reinterpret_cast<const float4*>(peers.buf[(rank + r) % world] + off) + i);
-#pragma unroll
-      for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-        if (r < world) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
-      acc.x *= s; acc.y *= s; acc.z *= s; acc.w *= s;
-      float q = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
-      bad |= !isfinite(q);
-      sq += q;
-#pragma unroll
-      for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-        if (r < world) st_peer(reinterpret_cast<float4*>(peers.buf[(rank + r) % world] + off) + i, acc);
-    }
-    float tot = block_sum(sq, red);
-    int anybad = __syncthreads_or(bad);
-    if (threadIdx.x == 0) {
-      atomicAdd(&me->acc[0], tot);
-      if (anybad) atomicAdd(&me->acc[1], 1.f);
-    }
-  }
-
-  // ---- completion: last block publishes stats + "done", then waits for every peer's "done"
+// Completion: the last CTA of this rank publishes the statistics (unless `publish_stats` is false) and "done", waits for
+// every peer's "done" (all remote writes into OUR memory have landed), then advances the epoch.
+__device__ __forceinline__ void comm_exit(const Peers& peers, const Part& pt, uint32_t epoch, int phases, bool publish_stats,
+                                          int first_of_step, int* found_inf, bool* s_last) {
+  Ctrl* me = peers.ctrl[pt.rank];
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
     uint32_t t = atomicAdd(&me->blocks_done, 1u);
-    s_last = (t == gridDim.x - 1);
+    *s_last = (t == (uint32_t)pt.nblk - 1);
   }
   __syncthreads();
-  if (!s_last) return;
+  if (!*s_last) return;
   __threadfence_system();
   if (phases & 4) {
     const float a0 = __ldcg(&me->acc[0]);
     const float a1 = __ldcg(&me->acc[1]);
     // read my running totals BEFORE any thread overwrites them (thread `rank` writes to `me`)
-    const float base0 = first_of_step ? 0.f : __ldcg(&me->stats[rank]);
-    const float base1 = first_of_step ? 0.f : __ldcg(&me->stats[DETB200_MAX_RANKS + rank]);
+    const float base0 = first_of_step ? 0.f : __ldcg(&me->stats[pt.rank]);
+    const float base1 = first_of_step ? 0.f : __ldcg(&me->stats[DETB200_MAX_RANKS + pt.rank]);
     __syncthreads();
-    if (threadIdx.x < world) {
+    if (threadIdx.x < pt.world) {
       Ctrl* pc = peers.ctrl[threadIdx.x];
-      // running totals for this step: overwrite my slot on every peer
-      float* slot = &pc->stats[rank];
-      asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(slot), "f"(base0 + a0) : "memory");
-      asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(slot + DETB200_MAX_RANKS), "f"(base1 + a1) : "memory");
-      __threadfence_system();
-      if (threadIdx.x != rank) {
-        st_release_sys(&pc->done[rank], epoch);
-        wait_flag(&me->done[threadIdx.x], epoch, me, timeout_cycles);
+      if (publish_stats) {
+        // running totals for this step: overwrite my slot on every peer
+        float* slot = &pc->stats[pt.rank];
+        asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(slot), "f"(base0 + a0) : "memory");
+        asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(slot + DETB200_MAX_RANKS), "f"(base1 + a1) : "memory");
+        __threadfence_system();
+      }
+      if (threadIdx.x != pt.rank) {
+        st_release_sys(&pc->done[pt.rank], epoch);
+        wait_flag(&me->done[threadIdx.x], epoch, me, pt.timeout);
       }
     }
     __syncthreads();
     if (found_inf != nullptr && threadIdx.x == 0) {
       float nbad = 0.f;
-      for (int r = 0; r < world; ++r) nbad += me->stats[DETB200_MAX_RANKS + r];
+      for (int r = 0; r < pt.world; ++r) nbad += me->stats[DETB200_MAX_RANKS + r];
       if (nbad > 0.f) *found_inf = 1;
     }
     if (threadIdx.x == 0) {
@@ -182,8 +191,213 @@ allreduce_fused_kernel(Peers peers, int rank, int world, int64_t off, int64_t n,
       me->epoch = epoch;
     }
   } else if (threadIdx.x == 0) {
-    // emulation mode: keep acc for inspection by the host test, re-arm the ticket only
+    // emulation of one phase at a time: keep acc for inspection by the host test, re-arm the ticket only
     me->blocks_done = 0u;
+  }
+}
+
+// Sum of slice element `i` (float4 index) over all ranks, peer-to-peer: kU vectors per thread per trip so that kU*W
+// independent 16-byte NVLink loads are in flight per thread whatever the world size.
+template <int W>
+struct Unroll { static constexpr int kU = (W == 0) ? 1 : ((W <= 4) ? 4 : 2); };
+
+template <int W, int kU>
+__device__ __forceinline__ void p2p_gather_sum(const Peers& peers, int rank, int world, int64_t off, int64_t i, int64_t stride,
+                                               int64_t v1, float4 (&acc)[kU]) {
+  constexpr int kW = (W == 0) ? DETB200_MAX_RANKS : W;
+  float4 v[kU][kW];
+#pragma unroll
+  for (int j = 0; j < kU; ++j)
+#pragma unroll
+    for (int r = 0; r < kW; ++r)
+      if (r < world && i + j * stride < v1) {
+        int src = rank + r; if (src >= world) src -= world;
+        v[j][r] = ld_weak(reinterpret_cast<const float4*>(peers.buf[src] + off) + i + j * stride);
+      }
+#pragma unroll
+  for (int j = 0; j < kU; ++j) {
+    acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < kW; ++r)
+      if (r < world && i + j * stride < v1) { acc[j].x += v[j][r].x; acc[j].y += v[j][r].y; acc[j].z += v[j][r].z; acc[j].w += v[j][r].w; }
+  }
+}
+
+// phase bits: 1 = start barrier, 2 = reduce+scatter my slice, 4 = end barrier.  All bits set is the normal multi-GPU
+// launch.  W: compile-time world for the peer-to-peer path (0 = run-time).  kNvls: in-switch reduction through `mc`.
+template <int W, bool kNvls>
+__device__ __forceinline__ void allreduce_body(const Peers& peers, float* mc, const Part& pt, int64_t off, int64_t n, float scale,
+                                               const float* __restrict__ inv_loss_scale, int* __restrict__ found_inf,
+                                               int first_of_step, int phases) {
+  __shared__ float red[32];
+  __shared__ uint32_t s_epoch;
+  __shared__ bool s_last;
+  Ctrl* me = peers.ctrl[pt.rank];
+  const uint32_t epoch = comm_enter(peers, pt, phases, &s_epoch);
+  const int rank = pt.rank, world = pt.world;
+  float sq = 0.f;
+  int bad = 0;
+  if (phases & 2) {
+    const float s = scale * (inv_loss_scale ? *inv_loss_scale : 1.f);
+    // slice boundaries in float4 units; the bucket is padded to a multiple of 4*world elements
+    const int64_t nvec = n >> 2;
+    const int64_t per = (nvec + world - 1) / world;
+    const int64_t v0 = per * rank;
+    const int64_t v1 = (v0 + per < nvec) ? v0 + per : nvec;
+    const int64_t stride = (int64_t)pt.nblk * blockDim.x;
+    constexpr int kU = kNvls ? 4 : Unroll<W>::kU;
+    for (int64_t i = v0 + (int64_t)pt.bid * blockDim.x + threadIdx.x; i < v1; i += stride * kU) {
+      float4 acc[kU];
+      if (kNvls) {
+#pragma unroll
+        for (int j = 0; j < kU; ++j)
+          if (i + j * stride < v1) acc[j] = mc_ld_reduce(reinterpret_cast<const float4*>(mc + off) + i + j * stride);
+      } else {
+        p2p_gather_sum<W, kU>(peers, rank, world, off, i, stride, v1, acc);
+      }
+#pragma unroll
+      for (int j = 0; j < kU; ++j) {
+        if (i + j * stride >= v1) continue;
+        float4 a = acc[j];
+        a.x *= s; a.y *= s; a.z *= s; a.w *= s;
+        float q = a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+        bad |= !isfinite(q);
+        sq += q;
+        if (kNvls) {
+          mc_st(reinterpret_cast<float4*>(mc + off) + i + j * stride, a);
+        } else {
+          constexpr int kW = (W == 0) ? DETB200_MAX_RANKS : W;
+#pragma unroll
+          for (int r = 0; r < kW; ++r)
+            if (r < world) {
+              int dst = rank + r; if (dst >= world) dst -= world;
+              st_weak(reinterpret_cast<float4*>(peers.buf[dst] + off) + i + j * stride, a);
+            }
+        }
+      }
+    }
+    float tot = block_sum(sq, red);
+    int anybad = __syncthreads_or(bad);
+    if (threadIdx.x == 0) {
+      atomicAdd(&me->acc[0], tot);
+      if (anybad) atomicAdd(&me->acc[1], 1.f);
+    }
+  }
+  comm_exit(peers, pt, epoch, phases, true, first_of_step, found_inf, &s_last);
+}
+
+template <int W, bool kNvls>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_fused_kernel(Peers peers, float* mc, int rank, int world, int64_t off, int64_t n, float scale,
+                       const float* __restrict__ inv_loss_scale, int* __restrict__ found_inf,
+                       int first_of_step, int phases, long long timeout_cycles) {
+  Part pt{rank, world, (int)blockIdx.x, (int)gridDim.x, timeout_cycles};
+  allreduce_body<W, kNvls>(peers, mc, pt, off, n, scale, inv_loss_scale, found_inf, first_of_step, phases);
+}
+
+// All ranks of a `world`-rank job in ONE cooperative grid on one GPU: CTA b plays CTA (b % cpr) of rank (b / cpr).  The
+// buffers are `world` separate allocations of the same GPU.  Same code, flags, epochs and barriers as the real launch;
+// co-residency (which the barriers need) is what the cooperative launch guarantees.  Test-only.
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_emulated_kernel(Peers peers, int world, int cpr, int64_t off, int64_t n, float scale,
+                          const float* __restrict__ inv_loss_scale, int* __restrict__ found_inf /* [world] */,
+                          int first_of_step, long long timeout_cycles) {
+  const int rank = blockIdx.x / cpr;
+  Part pt{rank, world, (int)blockIdx.x % cpr, cpr, timeout_cycles};
+  allreduce_body<0, false>(peers, nullptr, pt, off, n, scale, inv_loss_scale, found_inf ? found_inf + rank : nullptr,
+                           first_of_step, 7);
+}
+
+// ---- 16-bit wire format (reference: hvd.Compression.fp16, _pytorch_context.py:367; expconf optimizations.gradient_compression)
+// Every rank first rounds its fp32 gradients to bf16 into a symmetric staging buffer (a separate local kernel).  This
+// kernel reduces slice r of all ranks' staging buffers (bf16 over the wire, fp32 accumulation), scales, takes the
+// statistics from the fp32 values and writes the bf16 result back into every rank's staging buffer; a local kernel then
+// widens it into the fp32 gradient buffer.  Half the NVLink bytes of the fp32 kernel in both directions.
+template <bool kNvls>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_bf16_kernel(Peers peers /* buf = staging, bf16 */, void* mc, int rank, int world, int64_t off, int64_t n, float scale,
+                      const float* __restrict__ inv_loss_scale, int* __restrict__ found_inf, int first_of_step, int phases,
+                      long long timeout_cycles) {
+  __shared__ float red[32];
+  __shared__ uint32_t s_epoch;
+  __shared__ bool s_last;
+  Part pt{rank, world, (int)blockIdx.x, (int)gridDim.x, timeout_cycles};
+  Ctrl* me = peers.ctrl[rank];
+  const uint32_t epoch = comm_enter(peers, pt, phases, &s_epoch);
+  float sq = 0.f;
+  int bad = 0;
+  if (phases & 2) {
+    const float s = scale * (inv_loss_scale ? *inv_loss_scale : 1.f);
+    const int64_t nvec = n >> 3;                 // 8 bf16 per 16-byte vector
+    const int64_t per = (nvec + world - 1) / world;
+    const int64_t v0 = per * rank;
+    const int64_t v1 = (v0 + per < nvec) ? v0 + per : nvec;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += stride) {
+      float a[8];
+      if (kNvls) {
+        uint4 u = mc_ld_reduce_bf16(reinterpret_cast<const uint4*>((const __nv_bfloat16*)mc + off) + i);
+        a[0] = bf16lo(u.x); a[1] = bf16hi(u.x); a[2] = bf16lo(u.y); a[3] = bf16hi(u.y);
+        a[4] = bf16lo(u.z); a[5] = bf16hi(u.z); a[6] = bf16lo(u.w); a[7] = bf16hi(u.w);
+      } else {
+        uint4 v[DETB200_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < DETB200_MAX_RANKS; ++r)
+          if (r < world) {
+            int src = rank + r; if (src >= world) src -= world;
+            v[r] = ld_weak_u4(reinterpret_cast<const uint4*>((const __nv_bfloat16*)peers.buf[src] + off) + i);
+          }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = 0.f;
+#pragma unroll
+        for (int r = 0; r < DETB200_MAX_RANKS; ++r)
+          if (r < world) {
+            a[0] += bf16lo(v[r].x); a[1] += bf16hi(v[r].x); a[2] += bf16lo(v[r].y); a[3] += bf16hi(v[r].y);
+            a[4] += bf16lo(v[r].z); a[5] += bf16hi(v[r].z); a[6] += bf16lo(v[r].w); a[7] += bf16hi(v[r].w);
+          }
+      }
+      float q = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { a[k] *= s; q = fmaf(a[k], a[k], q); }
+      bad |= !isfinite(q);
+      sq += q;
+      uint4 o = make_uint4(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]), pack_bf16(a[4], a[5]), pack_bf16(a[6], a[7]));
+      if (kNvls) {
+        mc_st_u4(reinterpret_cast<uint4*>((__nv_bfloat16*)mc + off) + i, o);
+      } else {
+#pragma unroll
+        for (int r = 0; r < DETB200_MAX_RANKS; ++r)
+          if (r < world) {
+            int dst = rank + r; if (dst >= world) dst -= world;
+            st_weak_u4(reinterpret_cast<uint4*>((__nv_bfloat16*)peers.buf[dst] + off) + i, o);
+          }
+      }
+    }
+    float tot = block_sum(sq, red);
+    int anybad = __syncthreads_or(bad);
+    if (threadIdx.x == 0) {
+      atomicAdd(&me->acc[0], tot);
+      if (anybad) atomicAdd(&me->acc[1], 1.f);
+    }
+  }
+  comm_exit(peers, pt, epoch, phases, true, first_of_step, found_inf, &s_last);
+}
+
+__global__ void __launch_bounds__(256) widen_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, int64_t n8) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    uint4 u = ldg_stream_u4(reinterpret_cast<const uint4*>(x) + i);
+    stg_stream(reinterpret_cast<float4*>(y) + 2 * i, make_float4(bf16lo(u.x), bf16hi(u.x), bf16lo(u.y), bf16hi(u.y)));
+    stg_stream(reinterpret_cast<float4*>(y) + 2 * i + 1, make_float4(bf16lo(u.z), bf16hi(u.z), bf16lo(u.w), bf16hi(u.w)));
+  }
+}
+__global__ void __launch_bounds__(256) narrow_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n8) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float4 a = ldg_stream(reinterpret_cast<const float4*>(x) + 2 * i);
+    float4 b = ldg_stream(reinterpret_cast<const float4*>(x) + 2 * i + 1);
+    uint4 o = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
+    reinterpret_cast<uint4*>(y)[i] = o;
   }
 }
 
@@ -194,33 +408,27 @@ allreduce_fused_kernel(Peers peers, int rank, int world, int64_t off, int64_t n,
 // -> write the updated weights (bf16 and/or fp32) into EVERY peer's parameter buffer.  The reduced
 // gradient shard never goes back to HBM.  With clipping enabled the caller runs it as two phases
 // (mode 1: reduce + sum-of-squares into `gshard`; mode 2: Adam from `gshard` + push weights).
+// mode 1 may *accumulate* into gshard (gradient accumulation over micro-batches with partitioned gradients: ZeRO-2).
+// With kNvls the reduction is one multimem.ld_reduce per vector and the push one multimem.st.
 // ------------------------------------------------------------------------------------------
 struct ParamPeers {
   void* p_full[DETB200_MAX_RANKS];  // each peer's full (gathered) parameter buffer: bf16 or fp32
 };
 
-template <bool kLowp>
+template <bool kLowp, bool kNvls>
 __global__ void __launch_bounds__(kCommThreads)
-rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, int rank, int world, int64_t off, int64_t n,
-                  float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, float* mc_grad, void* mc_param, int rank, int world, int64_t off, int64_t poff,
+                  int64_t n, float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
                   float* __restrict__ gshard, float scale, const float* __restrict__ lr_p,
                   const int* __restrict__ step_p, const float* __restrict__ grad_scale_p,
-                  const int* __restrict__ skip_p, float beta1, float beta2, float eps, float wd, int mode,
+                  const int* __restrict__ skip_p, float beta1, float beta2, float eps, float wd, int mode, int accumulate,
                   int first_of_step, int phases, long long timeout_cycles) {
   __shared__ float red[32];
   __shared__ uint32_t s_epoch;
   __shared__ bool s_last;
+  Part pt{rank, world, (int)blockIdx.x, (int)gridDim.x, timeout_cycles};
   Ctrl* me = peers.ctrl[rank];
-  if (threadIdx.x == 0) s_epoch = me->epoch + 1;
-  __syncthreads();
-  const uint32_t epoch = s_epoch;
-  if (phases & 1) {
-    if (threadIdx.x < world && threadIdx.x != rank) {
-      if (blockIdx.x == 0) st_release_sys(&peers.ctrl[threadIdx.x]->start[rank], epoch);
-      wait_flag(&me->start[threadIdx.x], epoch, me, timeout_cycles);
-    }
-    __syncthreads();
-  }
+  const uint32_t epoch = comm_enter(peers, pt, phases, &s_epoch);
   float sq = 0.f;
   int bad = 0;
   if (phases & 2) {
@@ -230,8 +438,9 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, int rank, int world, int64_t o
     const float lr = lr_p ? *lr_p : 0.f;
     const int step = step_p ? *step_p : 1;
     const float gs = grad_scale_p ? *grad_scale_p : 1.f;
-    const float bc1 = 1.f - __powf(beta1, (float)step);
-    const float bc2 = 1.f - __powf(beta2, (float)step);
+    // per-thread scalars: double pow (the build's fast-math powf has ~1e-4 relative error in 1-beta2^step early on)
+    const float bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+    const float bc2 = (float)(1.0 - pow((double)beta2, (double)step));
     const float step_size = lr / bc1;
     const float inv_sqrt_bc2 = rsqrtf(bc2);
     const int64_t nvec = n >> 2;
@@ -243,19 +452,33 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, int rank, int world, int64_t o
       const int64_t li = i - v0;  // index into the owned shard
       float4 g;
       if (do_reduce) {
-        float4 vv[DETB200_MAX_RANKS];
+        if (kNvls) {
+          g = mc_ld_reduce(reinterpret_cast<const float4*>(mc_grad + off) + i);
+        } else {
+          float4 vv[DETB200_MAX_RANKS];
 #pragma unroll
-        for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-          if (r < world) vv[r] = ld_peer(reinterpret_cast<const float4*>(peers.buf[(rank + r) % world] + off) + i);
-        g = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int r = 0; r < DETB200_MAX_RANKS; ++r)
+            if (r < world) {
+              int src = rank + r; if (src >= world) src -= world;
+              vv[r] = ld_weak(reinterpret_cast<const float4*>(peers.buf[src] + off) + i);
+            }
+          g = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-          if (r < world) { g.x += vv[r].x; g.y += vv[r].y; g.z += vv[r].z; g.w += vv[r].w; }
+          for (int r = 0; r < DETB200_MAX_RANKS; ++r)
+            if (r < world) { g.x += vv[r].x; g.y += vv[r].y; g.z += vv[r].z; g.w += vv[r].w; }
+        }
         g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
+        if (mode == 1) {
+          if (accumulate) {
+            float4 o = reinterpret_cast<const float4*>(gshard)[li];
+            g.x += o.x; g.y += o.y; g.z += o.z; g.w += o.w;
+          }
+          reinterpret_cast<float4*>(gshard)[li] = g;
+        }
+        // statistics of what the optimizer will see (the accumulated shard when accumulating)
         float q = g.x * g.x + g.y * g.y + g.z * g.z + g.w * g.w;
         bad |= !isfinite(q);
         sq += q;
-        if (mode == 1) reinterpret_cast<float4*>(gshard)[li] = g;
       } else {
         g = reinterpret_cast<const float4*>(gshard)[li];
       }
@@ -270,7 +493,7 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, int rank, int world, int64_t o
           float pk = pp[k] * (1.f - lr * wd);
           float mk = fmaf(beta1, mm[k], (1.f - beta1) * gk);
           float vk = fmaf(beta2, vq[k], (1.f - beta2) * gk * gk);
-          pk -= step_size * __fdividef(mk, sqrtf(vk) * inv_sqrt_bc2 + eps);
+          pk -= step_size * (mk / (sqrtf(vk) * inv_sqrt_bc2 + eps));
           pp[k] = pk; mm[k] = mk; vq[k] = vk;
         }
         reinterpret_cast<float4*>(master)[li] = pv;
@@ -279,16 +502,27 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, int rank, int world, int64_t o
         // all-gather fused into the epilogue: push the fresh weights to every peer
         if (kLowp) {
           uint2 o = make_uint2(pack_bf16(pv.x, pv.y), pack_bf16(pv.z, pv.w));
+          if (kNvls) {
+            uint2* dst = reinterpret_cast<uint2*>((__nv_bfloat16*)mc_param + poff) + i;
+            asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" :: "l"(dst), "r"(o.x), "r"(o.y) : "memory");
+          } else {
 #pragma unroll
-          for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-            if (r < world) {
-              uint2* dst = reinterpret_cast<uint2*>((__nv_bfloat16*)ppeers.p_full[(rank + r) % world] + off) + i;
-              asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" :: "l"(dst), "r"(o.x), "r"(o.y) : "memory");
-            }
+            for (int r = 0; r < DETB200_MAX_RANKS; ++r)
+              if (r < world) {
+                int d = rank + r; if (d >= world) d -= world;
+                uint2* dst = reinterpret_cast<uint2*>((__nv_bfloat16*)ppeers.p_full[d] + poff) + i;
+                asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" :: "l"(dst), "r"(o.x), "r"(o.y) : "memory");
+              }
+          }
+        } else if (kNvls) {
+          mc_st(reinterpret_cast<float4*>((float*)mc_param + poff) + i, pv);
         } else {
 #pragma unroll
           for (int r = 0; r < DETB200_MAX_RANKS; ++r)
-            if (r < world) st_peer(reinterpret_cast<float4*>((float*)ppeers.p_full[(rank + r) % world] + off) + i, pv);
+            if (r < world) {
+              int d = rank + r; if (d >= world) d -= world;
+              st_weak(reinterpret_cast<float4*>((float*)ppeers.p_full[d] + poff) + i, pv);
+            }
         }
       }
     }
@@ -299,44 +533,7 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, int rank, int world, int64_t o
       if (anybad) atomicAdd(&me->acc[1], 1.f);
     }
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence_system();
-    uint32_t t = atomicAdd(&me->blocks_done, 1u);
-    s_last = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence_system();
-  if (phases & 4) {
-    const float a0 = __ldcg(&me->acc[0]);
-    const float a1 = __ldcg(&me->acc[1]);
-    const float base0 = first_of_step ? 0.f : __ldcg(&me->stats[rank]);
-    const float base1 = first_of_step ? 0.f : __ldcg(&me->stats[DETB200_MAX_RANKS + rank]);
-    __syncthreads();
-    if (threadIdx.x < world) {
-      Ctrl* pc = peers.ctrl[threadIdx.x];
-      if (mode != 2) {
-        float* slot = &pc->stats[rank];
-        asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(slot), "f"(base0 + a0) : "memory");
-        asm volatile("st.volatile.global.f32 [%0], %1;" :: "l"(slot + DETB200_MAX_RANKS), "f"(base1 + a1) : "memory");
-        __threadfence_system();
-      }
-      if (threadIdx.x != rank) {
-        st_release_sys(&pc->done[rank], epoch);
-        wait_flag(&me->done[threadIdx.x], epoch, me, timeout_cycles);
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      me->acc[0] = 0.f; me->acc[1] = 0.f;
-      me->blocks_done = 0u;
-      __threadfence();
-      me->epoch = epoch;
-    }
-  } else if (threadIdx.x == 0) {
-    me->blocks_done = 0u;
-  }
+  comm_exit(peers, pt, epoch, phases, mode != 2, first_of_step, nullptr, &s_last);
 }
 
 // Broadcast rank `root`'s buffer to all peers (parameter sync at start; reference
@@ -347,24 +544,17 @@ broadcast_kernel(Peers peers, int rank, int world, int root, int64_t off, int64_
                  long long timeout_cycles) {
   __shared__ uint32_t s_epoch;
   __shared__ bool s_last;
-  Ctrl* me = peers.ctrl[rank];
-  if (threadIdx.x == 0) s_epoch = me->epoch + 1;
-  __syncthreads();
-  const uint32_t epoch = s_epoch;
-  if (phases & 1) {
-    if (threadIdx.x < world && threadIdx.x != rank) {
-      if (blockIdx.x == 0) st_release_sys(&peers.ctrl[threadIdx.x]->start[rank], epoch);
-      wait_flag(&me->start[threadIdx.x], epoch, me, timeout_cycles);
-    }
-    __syncthreads();
-  }
+  Part pt{rank, world, (int)blockIdx.x, (int)gridDim.x, timeout_cycles};
+  const uint32_t epoch = comm_enter(peers, pt, phases, &s_epoch);
   if ((phases & 2) && rank != root) {
     const int64_t nvec = n >> 2;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const float4* src = reinterpret_cast<const float4*>(peers.buf[root] + off);
     float4* dst = reinterpret_cast<float4*>(peers.buf[rank] + off);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) dst[i] = ld_peer(src + i);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) dst[i] = ld_weak(src + i);
   }
+  // no statistics; acc stays untouched
+  Ctrl* me = peers.ctrl[rank];
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
@@ -400,10 +590,14 @@ int fill_peers(Peers* P, void* const* bufs, void* const* ctrls, int world) {
   return 0;
 }
 
-inline int comm_grid(int64_t n, int world) {
-  int64_t per = (n / 4 + world - 1) / world;
-  int g = grid_for(per, kCommThreads, 2, kNumSMs);
-  return g;
+// CTAs for a collective over `n_vec` 16-byte vectors per rank.  A handful of CTAs saturates NVLink (each thread keeps up
+// to 16 requests in flight); the rest of the GPU belongs to the backward pass this kernel is hiding behind.  `max_ctas`
+// <= 0 means the default budget.
+constexpr int kDefaultCommCtas = 32;
+inline int comm_grid(int64_t n_vec_per_rank, int per_thread, int max_ctas) {
+  int cap = max_ctas > 0 ? max_ctas : kDefaultCommCtas;
+  if (cap > kNumSMs) cap = kNumSMs;
+  return grid_for(n_vec_per_rank, kCommThreads, per_thread, cap);
 }
 
 }  // namespace
@@ -466,10 +660,19 @@ DETB200_API int detb200_comm_read_stats(const void* ctrl, int world, float* stat
 // detb200_clip_coef without a host round trip.
 DETB200_API void* detb200_comm_stats_ptr(void* ctrl) { return (void*)((Ctrl*)ctrl)->stats; }
 
-DETB200_API int detb200_allreduce_fused(void* const* peer_bufs, void* const* peer_ctrls, int rank, int world,
-                                        int64_t offset_elems, int64_t n_elems, float scale,
-                                        const float* inv_loss_scale, int* found_inf, int first_of_step,
-                                        int phases, double timeout_s, cudaStream_t stream) {
+template <int W>
+static void launch_allreduce_p2p(int grid, cudaStream_t stream, const Peers& P, int rank, int world, int64_t off, int64_t n,
+                                 float scale, const float* ils, int* found_inf, int first, int phases, long long cycles) {
+  allreduce_fused_kernel<W, false><<<grid, kCommThreads, 0, stream>>>(P, nullptr, rank, world, off, n, scale, ils, found_inf,
+                                                                      first, phases, cycles);
+}
+
+// mc_buf: this rank's mapping of the multicast object bound to all peer_bufs (NULL = peer-to-peer loads/stores).
+// max_ctas <= 0: default CTA budget.
+DETB200_API int detb200_allreduce_fused_ex(void* const* peer_bufs, void* const* peer_ctrls, void* mc_buf, int rank, int world,
+                                           int64_t offset_elems, int64_t n_elems, float scale,
+                                           const float* inv_loss_scale, int* found_inf, int first_of_step,
+                                           int phases, int max_ctas, double timeout_s, cudaStream_t stream) {
   Peers P;
   int rc = fill_peers(&P, peer_bufs, peer_ctrls, world);
   if (rc) return rc;
@@ -479,8 +682,135 @@ DETB200_API int detb200_allreduce_fused(void* const* peer_bufs, void* const* pee
   }
   if (n_elems == 0) return 0;
   long long cycles = (long long)(timeout_s * 1.9e9);
-  allreduce_fused_kernel<<<comm_grid(n_elems, world), kCommThreads, 0, stream>>>(
-      P, rank, world, offset_elems, n_elems, scale, inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  const int64_t per = (n_elems / 4 + world - 1) / world;
+  if (mc_buf != nullptr) {
+    allreduce_fused_kernel<0, true><<<comm_grid(per, 4, max_ctas), kCommThreads, 0, stream>>>(
+        P, (float*)mc_buf, rank, world, offset_elems, n_elems, scale, inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  } else if (world == 2) {
+    launch_allreduce_p2p<2>(comm_grid(per, Unroll<2>::kU, max_ctas), stream, P, rank, world, offset_elems, n_elems, scale,
+                            inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  } else if (world == 4) {
+    launch_allreduce_p2p<4>(comm_grid(per, Unroll<4>::kU, max_ctas), stream, P, rank, world, offset_elems, n_elems, scale,
+                            inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  } else if (world == 8) {
+    launch_allreduce_p2p<8>(comm_grid(per, Unroll<8>::kU, max_ctas), stream, P, rank, world, offset_elems, n_elems, scale,
+                            inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  } else {
+    launch_allreduce_p2p<0>(comm_grid(per, 1, max_ctas), stream, P, rank, world, offset_elems, n_elems, scale,
+                            inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  }
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+DETB200_API int detb200_allreduce_fused(void* const* peer_bufs, void* const* peer_ctrls, int rank, int world,
+                                        int64_t offset_elems, int64_t n_elems, float scale,
+                                        const float* inv_loss_scale, int* found_inf, int first_of_step,
+                                        int phases, double timeout_s, cudaStream_t stream) {
+  return detb200_allreduce_fused_ex(peer_bufs, peer_ctrls, nullptr, rank, world, offset_elems, n_elems, scale, inv_loss_scale,
+                                    found_inf, first_of_step, phases, 0, timeout_s, stream);
+}
+
+// Test entry point: every rank of a `world`-rank all-reduce in one cooperative launch on the current GPU (see
+// allreduce_emulated_kernel).  bufs/ctrls are `world` allocations of this GPU; found_inf is int[world] or NULL.
+DETB200_API int detb200_allreduce_fused_emulated(void* const* bufs, void* const* ctrls, int world, int64_t offset_elems,
+                                                 int64_t n_elems, float scale, const float* inv_loss_scale, int* found_inf,
+                                                 int first_of_step, int ctas_per_rank, double timeout_s, cudaStream_t stream) {
+  Peers P;
+  int rc = fill_peers(&P, bufs, ctrls, world);
+  if (rc) return rc;
+  if (n_elems % 4 != 0 || offset_elems % 4 != 0 || ctas_per_rank < 1) {
+    detb200_set_error("allreduce_fused_emulated: bad argument"); return DETB200_ERR_BAD_ARG;
+  }
+  int dev = 0, coop = 0, per_sm = 0, sms = 0;
+  DETB200_CHECK(cudaGetDevice(&dev));
+  DETB200_CHECK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+  DETB200_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  DETB200_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, allreduce_emulated_kernel, kCommThreads, 0));
+  if (!coop || world * ctas_per_rank > per_sm * sms) {
+    detb200_set_error("allreduce_fused_emulated: %d CTAs cannot be co-resident", world * ctas_per_rank);
+    return DETB200_ERR_UNSUPPORTED;
+  }
+  long long cycles = (long long)(timeout_s * 1.9e9);
+  void* args[] = {&P, &world, &ctas_per_rank, &offset_elems, &n_elems, &scale, &inv_loss_scale, &found_inf, &first_of_step, &cycles};
+  DETB200_CHECK(cudaLaunchCooperativeKernel((void*)allreduce_emulated_kernel, dim3(world * ctas_per_rank), dim3(kCommThreads),
+                                            args, 0, stream));
+  return 0;
+}
+
+// bf16 wire format.  peer_stage: every rank's bf16 staging buffer (symmetric); mc_stage: multicast mapping of it or NULL.
+// The three steps are separate entry points so that the caller can place them on streams as it likes:
+//   detb200_narrow_bf16 (local)  ->  detb200_allreduce_bf16 (collective)  ->  detb200_widen_bf16 (local).
+DETB200_API int detb200_narrow_bf16(const float* x, void* y_bf16, int64_t n, cudaStream_t stream) {
+  if (n % 8 != 0) { detb200_set_error("narrow_bf16: length must be a multiple of 8"); return DETB200_ERR_BAD_ARG; }
+  if (n == 0) return 0;
+  narrow_bf16_kernel<<<grid_for(n / 8, 256, 4, kNumSMs * 4), 256, 0, stream>>>(x, (__nv_bfloat16*)y_bf16, n / 8);
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+DETB200_API int detb200_widen_bf16(const void* x_bf16, float* y, int64_t n, cudaStream_t stream) {
+  if (n % 8 != 0) { detb200_set_error("widen_bf16: length must be a multiple of 8"); return DETB200_ERR_BAD_ARG; }
+  if (n == 0) return 0;
+  widen_bf16_kernel<<<grid_for(n / 8, 256, 4, kNumSMs * 4), 256, 0, stream>>>((const __nv_bfloat16*)x_bf16, y, n / 8);
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+DETB200_API int detb200_allreduce_bf16(void* const* peer_stage, void* const* peer_ctrls, void* mc_stage, int rank, int world,
+                                       int64_t offset_elems, int64_t n_elems, float scale, const float* inv_loss_scale,
+                                       int* found_inf, int first_of_step, int phases, int max_ctas, double timeout_s,
+                                       cudaStream_t stream) {
+  Peers P;
+  int rc = fill_peers(&P, peer_stage, peer_ctrls, world);
+  if (rc) return rc;
+  if (rank < 0 || rank >= world) { detb200_set_error("bad rank %d", rank); return DETB200_ERR_BAD_ARG; }
+  if (n_elems % 8 != 0 || offset_elems % 8 != 0) {
+    detb200_set_error("allreduce_bf16: offset/length must be multiples of 8 elements"); return DETB200_ERR_BAD_ARG;
+  }
+  if (n_elems == 0) return 0;
+  long long cycles = (long long)(timeout_s * 1.9e9);
+  const int64_t per = (n_elems / 8 + world - 1) / world;
+  int grid = comm_grid(per, 2, max_ctas);
+  if (mc_stage)
+    allreduce_bf16_kernel<true><<<grid, kCommThreads, 0, stream>>>(P, mc_stage, rank, world, offset_elems, n_elems, scale,
+                                                                   inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  else
+    allreduce_bf16_kernel<false><<<grid, kCommThreads, 0, stream>>>(P, nullptr, rank, world, offset_elems, n_elems, scale,
+                                                                    inv_loss_scale, found_inf, first_of_step, phases, cycles);
+  DETB200_LAUNCH_CHECK();
+  return 0;
+}
+
+// grad and param offsets may differ (ZeRO-2 reduces out of a small landing buffer into the shard of a full-size bucket).
+// mc_grad / mc_param: multicast mappings of the gradient / parameter buffers, both or neither.
+DETB200_API int detb200_rs_adam_ag_ex(void* const* peer_grad_bufs, void* const* peer_ctrls, void* const* peer_param_bufs,
+                                      void* mc_grad, void* mc_param, int param_is_bf16, int rank, int world,
+                                      int64_t grad_offset_elems, int64_t param_offset_elems, int64_t n_elems,
+                                      float* master_shard, float* m_shard, float* v_shard, float* grad_shard,
+                                      float scale, const float* lr, const int* step, const float* grad_scale,
+                                      const int* skip, float beta1, float beta2, float eps, float weight_decay,
+                                      int mode, int accumulate, int first_of_step, int phases, int max_ctas, double timeout_s,
+                                      cudaStream_t stream) {
+  Peers P;
+  int rc = fill_peers(&P, peer_grad_bufs, peer_ctrls, world);
+  if (rc) return rc;
+  ParamPeers PP;
+  for (int r = 0; r < world; ++r) PP.p_full[r] = peer_param_bufs ? peer_param_bufs[r] : nullptr;
+  if (n_elems % (4 * world) != 0 || grad_offset_elems % 4 != 0 || param_offset_elems % 4 != 0) {
+    detb200_set_error("rs_adam_ag: bucket length must be a multiple of 4*world floats"); return DETB200_ERR_BAD_ARG;
+  }
+  if ((mode == 1 || mode == 2) && !grad_shard) { detb200_set_error("rs_adam_ag: two-phase mode needs grad_shard"); return DETB200_ERR_BAD_ARG; }
+  if (mode != 1 && !peer_param_bufs) { detb200_set_error("rs_adam_ag: parameter buffers required unless mode 1"); return DETB200_ERR_BAD_ARG; }
+  if (n_elems == 0) return 0;
+  long long cycles = (long long)(timeout_s * 1.9e9);
+  int grid = comm_grid(n_elems / 4 / world, 2, max_ctas);
+  const bool nvls = mc_grad != nullptr && (mode == 1 || mc_param != nullptr) && world > 1;
+#define DETB200_RS_LAUNCH(LOWP, NVLS)                                                                                      \
+  rs_adam_ag_kernel<LOWP, NVLS><<<grid, kCommThreads, 0, stream>>>(P, PP, (float*)mc_grad, mc_param, rank, world,          \
+      grad_offset_elems, param_offset_elems, n_elems, master_shard, m_shard, v_shard, grad_shard, scale, lr, step,        \
+      grad_scale, skip, beta1, beta2, eps, weight_decay, mode, accumulate, first_of_step, phases, cycles)
+  if (param_is_bf16) { if (nvls) DETB200_RS_LAUNCH(true, true); else DETB200_RS_LAUNCH(true, false); }
+  else { if (nvls) DETB200_RS_LAUNCH(false, true); else DETB200_RS_LAUNCH(false, false); }
+#undef DETB200_RS_LAUNCH
   DETB200_LAUNCH_CHECK();
   return 0;
 }
@@ -491,28 +821,10 @@ DETB200_API int detb200_rs_adam_ag(void* const* peer_grad_bufs, void* const* pee
                                    float scale, const float* lr, const int* step, const float* grad_scale,
                                    const int* skip, float beta1, float beta2, float eps, float weight_decay,
                                    int mode, int first_of_step, int phases, double timeout_s, cudaStream_t stream) {
-  Peers P;
-  int rc = fill_peers(&P, peer_grad_bufs, peer_ctrls, world);
-  if (rc) return rc;
-  ParamPeers PP;
-  for (int r = 0; r < world; ++r) PP.p_full[r] = peer_param_bufs[r];
-  if (n_elems % (4 * world) != 0 || offset_elems % 4 != 0) {
-    detb200_set_error("rs_adam_ag: bucket length must be a multiple of 4*world floats"); return DETB200_ERR_BAD_ARG;
-  }
-  if ((mode == 1 || mode == 2) && !grad_shard) { detb200_set_error("rs_adam_ag: two-phase mode needs grad_shard"); return DETB200_ERR_BAD_ARG; }
-  if (n_elems == 0) return 0;
-  long long cycles = (long long)(timeout_s * 1.9e9);
-  int grid = comm_grid(n_elems, world);
-  if (param_is_bf16)
-    rs_adam_ag_kernel<true><<<grid, kCommThreads, 0, stream>>>(P, PP, rank, world, offset_elems, n_elems, master_shard,
-        m_shard, v_shard, grad_shard, scale, lr, step, grad_scale, skip, beta1, beta2, eps, weight_decay, mode,
-        first_of_step, phases, cycles);
-  else
-    rs_adam_ag_kernel<false><<<grid, kCommThreads, 0, stream>>>(P, PP, rank, world, offset_elems, n_elems, master_shard,
-        m_shard, v_shard, grad_shard, scale, lr, step, grad_scale, skip, beta1, beta2, eps, weight_decay, mode,
-        first_of_step, phases, cycles);
-  DETB200_LAUNCH_CHECK();
-  return 0;
+  return detb200_rs_adam_ag_ex(peer_grad_bufs, peer_ctrls, peer_param_bufs, nullptr, nullptr, param_is_bf16, rank, world,
+                               offset_elems, offset_elems, n_elems, master_shard, m_shard, v_shard, grad_shard, scale, lr, step,
+                               grad_scale, skip, beta1, beta2, eps, weight_decay, mode, 0, first_of_step, phases, 0, timeout_s,
+                               stream);
 }
 
 DETB200_API int detb200_broadcast(void* const* peer_bufs, void* const* peer_ctrls, int rank, int world, int root,

@@ -35,8 +35,10 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
   const float lr = *dyn.lr;
   const int step = *dyn.step;
   const float gs = static_scale * (dyn.grad_scale ? *dyn.grad_scale : 1.f) * (maximize ? -1.f : 1.f);
-  const float bc1 = 1.f - __powf(beta1, (float)step);
-  const float bc2 = 1.f - __powf(beta2, (float)step);
+  // per-thread scalars in double: the fast-math powf has ~1e-4 relative error in 1-beta2^step over the first steps,
+  // which made the fused Adam drift from torch.optim.Adam beyond fp32 rounding
+  const float bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+  const float bc2 = (float)(1.0 - pow((double)beta2, (double)step));
   const float step_size = lr / bc1;
   const float inv_sqrt_bc2 = rsqrtf(bc2);
   const int64_t nvec = n / kVec;
@@ -390,6 +392,20 @@ DETB200_API int detb200_sumsq_noalloc(const float* x, int64_t n, float* out, int
     detb200_set_error("sumsq_noalloc: n=%lld exceeds the built-in scratch limit of %lld elements; use detb200_sumsq with "
                       "caller-provided scratch", (long long)n, (long long)DETB200_SUMSQ_NOALLOC_MAX_ELEMS);
     return DETB200_ERR_TOO_LARGE;
+  }
+  // The scratch address belongs to the CURRENT device; a stream of another device would make the launch fail with a
+  // generic error (or, with peer access enabled, reduce into the wrong GPU's array).  Refuse that up front.
+  {
+    int cur = -1, sdev = -1;
+    if (cudaGetDevice(&cur) == cudaSuccess && cudaStreamGetDevice(stream, &sdev) == cudaSuccess) {
+      if (sdev != cur) {
+        detb200_set_error("sumsq_noalloc: stream belongs to device %d but device %d is current; make the stream's device "
+                          "current before the call", sdev, cur);
+        return DETB200_ERR_BAD_ARG;
+      }
+    } else {
+      cudaGetLastError();  // the query is advisory: fall through to the launch, which reports real problems
+    }
   }
   void* scratch = nullptr;
   int rc = noalloc_scratch_for_current_device(&scratch);

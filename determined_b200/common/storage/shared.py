@@ -70,6 +70,15 @@ def full_storage_path(host_path: str, storage_path: Optional[str] = None,
 
 
 class SharedFSStorageManager(base.StorageManager):
+    def _confined(self, storage_id: str) -> str:
+        """Resolve ``storage_id`` under the base path and refuse anything that normalises to the base itself or to a
+        location outside it (``../x``, absolute paths): these ids name directories that get copied from and rmtree'd."""
+        base_dir = os.path.normpath(self._base_path)
+        d = os.path.normpath(os.path.join(base_dir, storage_id))
+        if d == base_dir or os.path.commonpath([base_dir, d]) != base_dir:
+            raise ValueError(f"storage id {storage_id!r} escapes the checkpoint storage root")
+        return d
+
     @classmethod
     def from_config(cls, config: Dict[str, Any], container_path: Optional[str]) -> "SharedFSStorageManager":
         allowed = {"host_path", "storage_path", "container_path", "propagation"}
@@ -90,13 +99,13 @@ class SharedFSStorageManager(base.StorageManager):
     @contextlib.contextmanager
     def restore_path(self, src: str, selector: Optional[base.Selector] = None) -> Iterator[pathlib.Path]:
         # Zero-copy: hand out the real directory.  (selector is irrelevant: nothing is copied.)
-        d = os.path.join(self._base_path, src)
+        d = self._confined(src)
         if not os.path.isdir(d):
             raise errors.CheckpointNotFound(f"checkpoint directory not found: {d}")
         yield pathlib.Path(d)
 
     def delete(self, tgt: str, globs: List[str]) -> Dict[str, int]:
-        d = os.path.join(self._base_path, tgt)
+        d = self._confined(tgt)
         if not os.path.exists(d):
             logger.info("storage directory does not exist: %s", d)
             return {}
@@ -125,13 +134,13 @@ class SharedFSStorageManager(base.StorageManager):
 
     def upload(self, src: Union[str, os.PathLike], dst: str, paths: Optional[base.Paths] = None) -> None:
         src = os.fspath(src)
-        target = os.path.join(self._base_path, dst)
+        target = self._confined(dst)
         if os.path.realpath(src) == os.path.realpath(target):
             return
         copytree(src, target, paths=paths)
 
     def download(self, src: str, dst: Union[str, os.PathLike], selector: Optional[base.Selector] = None) -> None:
-        source = os.path.join(self._base_path, src)
+        source = self._confined(src)
         if not os.path.isdir(source):
             raise errors.CheckpointNotFound(f"checkpoint directory not found: {source}")
         copytree(source, os.fspath(dst), selector=selector)

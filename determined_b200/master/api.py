@@ -19,6 +19,7 @@ import secrets
 import threading
 import time
 import urllib.parse
+import uuid as uuid_mod
 from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 from typing import Any, Callable, Dict, List, Optional, Tuple
 
@@ -218,16 +219,30 @@ def create_user(ctx: Ctx) -> Any:
 
 @route("PATCH", "/api/v1/users/{uid}")
 def patch_user(ctx: Ctx, uid: str) -> Any:
-    if not ctx.user["admin"] and int(uid) != ctx.user["id"]:
+    """Reference api_user.go:429-466: ``admin`` / ``active`` / ``username`` may only be changed by an admin
+    (CanSetUsersAdmin / CanSetUsersActive / CanSetUsersUsername); a non-admin may change its own display name and
+    password and nothing else."""
+    is_admin = bool(ctx.user["admin"])
+    if not is_admin and int(uid) != ctx.user["id"]:
         raise HTTPError(403, "forbidden")
     b = ctx.body or {}
     u = b.get("user", b)
+    if not isinstance(u, dict):
+        raise HTTPError(400, "user patch must be an object")
+    if not is_admin and any(u.get(k) is not None for k in ("admin", "active", "username", "remote")):
+        raise HTTPError(403, "only admin privileged users can update users")
+    if ctx.m.db.one("SELECT id FROM users WHERE id=?", (int(uid),)) is None:
+        raise HTTPError(404, f"user {uid} not found")
     for col, key in (("active", "active"), ("admin", "admin"), ("display_name", "displayName"), ("username", "username")):
         if key in u and u[key] is not None:
             ctx.m.db.exec(f"UPDATE users SET {col}=?, modified_at=? WHERE id=?", (int(u[key]) if isinstance(u[key], bool) else u[key], time.time(), int(uid)))
-    if u.get("password") is not None:
-        pw = u["password"] if u.get("isHashed") else auth.salt_and_hash(u["password"])
-        ctx.m.db.exec("UPDATE users SET password_hash=? WHERE id=?", (pw, int(uid)))
+    pw = u.get("password")
+    if pw is None and isinstance(b, dict) and b is not u:
+        pw = b.get("password")
+    if pw is not None:
+        hashed = bool(u.get("isHashed") or (isinstance(b, dict) and b.get("isHashed")))
+        ctx.m.db.exec("UPDATE users SET password_hash=?, modified_at=? WHERE id=?",
+                      (pw if hashed else auth.salt_and_hash(str(pw)), time.time(), int(uid)))
     return {"user": user_json(ctx.m.db.one("SELECT * FROM users WHERE id=?", (int(uid),)))}
 
 
@@ -1034,6 +1049,12 @@ def report_checkpoint(ctx: Ctx) -> Any:
     uuid_ = ck.get("uuid")
     if not uuid_:
         raise HTTPError(400, "checkpoint uuid required")
+    # the id becomes a directory name under checkpoint storage (GC and DELETE rmtree it): only real UUIDs, as in the
+    # reference's uuid-typed column (master/internal/api_checkpoint.go, checkpoints_v2.uuid)
+    try:
+        uuid_ = str(uuid_mod.UUID(str(uuid_)))
+    except (ValueError, AttributeError, TypeError):
+        raise HTTPError(400, f"checkpoint uuid {uuid_!r} is not a UUID")
     md = ck.get("metadata") or {}
     res = {k: int(v) for k, v in (ck.get("resources") or {}).items()}
     t = ctx.m.db.one("SELECT id FROM trials WHERE task_id=?", (ck.get("taskId"),))

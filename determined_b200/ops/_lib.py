@@ -71,6 +71,27 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_allreduce_fused", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, i64, i64, f, p, p, i, i, d, p])
     _sig(lib, "detb200_rs_adam_ag", i, [POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), i, i, i, i64, i64,
                                         p, p, p, p, f, p, p, p, p, f, f, f, f, i, i, i, d, p])
+    PV = POINTER(c_void_p)
+    _sig(lib, "detb200_allreduce_fused_ex", i, [PV, PV, p, i, i, i64, i64, f, p, p, i, i, i, d, p])
+    _sig(lib, "detb200_allreduce_fused_emulated", i, [PV, PV, i, i64, i64, f, p, p, i, i, d, p])
+    _sig(lib, "detb200_narrow_bf16", i, [p, p, i64, p])
+    _sig(lib, "detb200_widen_bf16", i, [p, p, i64, p])
+    _sig(lib, "detb200_allreduce_bf16", i, [PV, PV, p, i, i, i64, i64, f, p, p, i, i, i, d, p])
+    _sig(lib, "detb200_rs_adam_ag_ex", i, [PV, PV, PV, p, p, i, i, i, i64, i64, i64, p, p, p, p, f, p, p, p, p, f, f, f, f,
+                                           i, i, i, i, i, d, p])
+    # VMM symmetric memory + multicast objects (csrc/symm.cpp)
+    _sig(lib, "detb200_vmm_query", i, [POINTER(c_int)])
+    _sig(lib, "detb200_vmm_granularity", i, [i, POINTER(c_int64)])
+    _sig(lib, "detb200_vmm_alloc", i, [i64, PV, POINTER(c_int)])
+    _sig(lib, "detb200_vmm_import", i, [i, i64, PV])
+    _sig(lib, "detb200_vmm_free", i, [p])
+    _sig(lib, "detb200_mc_create", i, [i, i64, POINTER(c_int64), POINTER(c_int)])
+    _sig(lib, "detb200_mc_import", i, [i, POINTER(c_int64)])
+    _sig(lib, "detb200_mc_add_device", i, [i64])
+    _sig(lib, "detb200_mc_bind", i, [i64, p, i64])
+    _sig(lib, "detb200_mc_map", i, [i64, i64, PV])
+    _sig(lib, "detb200_mc_free", i, [i64, p, i64])
+    _sig(lib, "detb200_close_fd", i, [i])
     _sig(lib, "detb200_broadcast", i, [POINTER(c_void_p), POINTER(c_void_p), i, i, i, i64, i64, i, d, p])
     _sig(lib, "detb200_norm_fwd", i, [p, p, p, p, p, p, i64, i, f, i, i, p])
     _sig(lib, "detb200_norm_bwd_workspace_elems", i64, [i64, i, i])
@@ -120,6 +141,13 @@ def check(rc: int, what: str = "") -> None:
     if rc != 0:
         lib = load()
         msg = lib.detb200_last_error()
+        raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg.decode() if msg else ''}")
+
+
+def check0(rc: int, what: str = "") -> None:
+    """``check`` for entry points that launch no kernel (set-up calls): nothing is added to the launch count."""
+    if rc != 0:
+        msg = load().detb200_last_error()
         raise NativeError(f"{what or 'native call'} failed (rc={rc}): {msg.decode() if msg else ''}")
 
 

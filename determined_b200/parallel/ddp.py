@@ -59,6 +59,18 @@ class _OptRecord:
         self.average_aggregated_gradients = True
         self.scratch: Any = None
         self.hooks: List[Any] = []
+        self.mc_ptr: Optional[int] = None      # multicast mapping of the gradient buffer (NVLS) or None
+        self.backward_passes = 1               # communicate on the last of this many backward passes (hvd semantics)
+        self.passes_seen = 0
+        self.stats_stale = False               # a bucket was reduced twice this step: the running norm counts it twice
+        self.wire_bf16 = False                 # 16-bit wire format (fp16_compression / gradient_compression)
+        self.stage_buf: Any = None
+        self.stage: Optional[torch.Tensor] = None
+        self.peer_stage: Any = None
+        self.mc_stage: Optional[int] = None
+        self.inv_scale: Optional[torch.Tensor] = None   # 1/loss_scale of the wrapped GradScaler, device
+        self.found_inf: Optional[torch.Tensor] = None   # int32[1], device
+        self.unscaled_in_flight = False        # this step's buckets were unscaled + inf-checked by the all-reduce
 
 
 class GradEngineBase:
@@ -71,10 +83,11 @@ class GradEngineBase:
         self.records: Dict[int, _OptRecord] = {}
         self._communicating = True
 
-    def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool) -> torch.optim.Optimizer:
+    def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool,
+                      backward_passes_per_step: int = 1, fp16_compression: bool = False) -> torch.optim.Optimizer:
         raise NotImplementedError
 
-    def backward_begin(self, communicate: bool) -> None:
+    def backward_begin(self, communicate: bool, scaler: Any = None) -> None:
         self._communicating = communicate
 
     def backward_end(self) -> None:
@@ -94,17 +107,32 @@ class GradEngineBase:
         if not (dist.is_available() and dist.is_initialized()):
             return
         with torch.no_grad():
-            for m in models:
-                tensors = [p.data for p in m.parameters()] + [b.data for b in m.buffers()]
-                for t in tensors:
-                    dist.broadcast(t, src=0)
+            tensors = [t for m in models for t in ([p.data for p in m.parameters()] + [b.data for b in m.buffers()])]
+            self._broadcast_tensors(tensors)
+
+    def _broadcast_tensors(self, tensors: List[torch.Tensor]) -> None:
+        """One collective per dtype instead of one per tensor (ResNet-18: 122 tensors)."""
+        import torch.distributed as dist
+
+        by_dtype: Dict[Any, List[torch.Tensor]] = {}
+        for t in tensors:
+            by_dtype.setdefault((t.dtype, t.device), []).append(t)
+        for group in by_dtype.values():
+            flat = torch.cat([t.reshape(-1) for t in group])
+            dist.broadcast(flat, src=0)
+            off = 0
+            for t in group:
+                n = t.numel()
+                t.copy_(flat[off:off + n].view_as(t))
+                off += n
 
     def close(self) -> None:
         pass
 
 
 class GenericGradEngine(GradEngineBase):
-    def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool) -> torch.optim.Optimizer:
+    def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool,
+                      backward_passes_per_step: int = 1, fp16_compression: bool = False) -> torch.optim.Optimizer:
         rec = _OptRecord()
         rec.optimizer = optimizer
         rec.average_aggregated_gradients = average_aggregated_gradients
@@ -166,63 +194,109 @@ class FusedGradEngine(GradEngineBase):
         return _l.LAUNCHES[0]
 
     def __init__(self, dist_ctx: Any, device: torch.device, aggregation_frequency: int,
-                 bucket_cap_mb: float = 25.0, timeout_s: float = 120.0) -> None:
+                 bucket_cap_mb: float = 25.0, timeout_s: float = 120.0, tail_bucket_mb: float = 1.0) -> None:
         super().__init__(dist_ctx, device, aggregation_frequency)
         from determined_b200.ops import _lib
 
         _lib.load()
         self.bucket_cap = int(bucket_cap_mb * (1 << 20))
+        self.tail_cap = int(tail_bucket_mb * (1 << 20))
         self.timeout_s = timeout_s
-        self.comm_stream = torch.cuda.Stream(device=device) if dist_ctx.size > 1 else None
+        # highest priority: a bucket's CTAs should get the first SM slots that free up, not queue behind backward
+        self.comm_stream = None
+        if dist_ctx.size > 1:
+            _, hi = torch.cuda.Stream.priority_range()
+            self.comm_stream = torch.cuda.Stream(device=device, priority=hi)
 
     # ------------------------------------------------------------------ set-up
-    def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool) -> torch.optim.Optimizer:
+    def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool,
+                      backward_passes_per_step: int = 1, fp16_compression: bool = False) -> torch.optim.Optimizer:
         from determined_b200.ops import comm, optim
 
         world = self.dist.size
         rec = _OptRecord()
         rec.optimizer = optimizer
         rec.average_aggregated_gradients = average_aggregated_gradients
-        align = 4 * world
+        rec.backward_passes = max(1, int(backward_passes_per_step))
+        rec.wire_bf16 = bool(fp16_compression) and world > 1
+        align = (8 if rec.wire_bf16 else 4) * world
         grad_alloc = None
-        if world > 1:
-            def grad_alloc(n: int) -> torch.Tensor:  # noqa: E306
-                rec.grad_buf = comm.SymmetricBuffer(4 * n, self.device)
-                return rec.grad_buf.tensor(torch.float32, n)
         with torch.cuda.device(self.device):
+            if world > 1:
+                rec.group = comm.PeerGroup.from_torch_distributed(self.device)
+
+                def grad_alloc(n: int) -> torch.Tensor:  # noqa: E306
+                    rec.grad_buf = rec.group.alloc(4 * n)
+                    return rec.grad_buf.tensor(torch.float32, n)
             rec.layout = FlatLayout(optimizer.param_groups, self.device, align=align, segment_align=align,
                                     grad_alloc=grad_alloc)
             rec.fused_step = optim.fuse_optimizer_(optimizer, rec.layout)
             rec.scratch = optim.NormScratch(self.device)
+            rec.found_inf = torch.zeros(1, dtype=torch.int32, device=self.device)
+            rec.found_inf_f = torch.zeros(1, dtype=torch.float32, device=self.device)
+            rec.inv_scale = torch.ones(1, dtype=torch.float32, device=self.device)
             if world > 1:
-                rec.group = comm.PeerGroup.from_torch_distributed(self.device)
                 rec.peer_bufs = rec.group.map(rec.grad_buf)
-                rec.buckets = rec.layout.make_buckets(self.bucket_cap, align)
+                rec.mc_ptr = rec.group.multicast(rec.grad_buf)
+                if rec.wire_bf16:
+                    rec.stage_buf = rec.group.alloc(2 * rec.layout.total)
+                    rec.stage = rec.stage_buf.tensor(torch.bfloat16, rec.layout.total)
+                    rec.peer_stage = rec.group.map(rec.stage_buf)
+                    rec.mc_stage = rec.group.multicast(rec.stage_buf)
+                rec.buckets = rec.layout.make_buckets(self.bucket_cap, align, tail_cap_bytes=self.tail_cap)
                 for b in rec.buckets:
                     for s in b.owned:
                         rec.bucket_of[id(s.param)] = b
                 for s in rec.layout.slots:
                     rec.hooks.append(s.param.register_post_accumulate_grad_hook(self._make_hook(rec)))
                 self._arm(rec)
+                logger.info("fused gradient engine: %d params in %d buckets, %s%s", len(rec.layout.slots), len(rec.buckets),
+                            "NVLS in-switch reduction" if rec.mc_ptr else "peer-to-peer two-shot",
+                            ", bf16 wire format" if rec.wire_bf16 else "")
         if not rec.fused_step:
             logger.info("optimizer %s is not fusable; using its own step() on flat gradient views",
                         type(optimizer).__name__)
         self.records[id(optimizer)] = rec
         return optimizer
 
+    def sync_params_from_chief(self, models: List[torch.nn.Module]) -> None:
+        """Rank 0's weights reach every rank through the in-kernel broadcast (K8): the flat parameter buffer is staged in
+        the (still empty) symmetric gradient buffer, pulled from rank 0 over NVLink by one kernel, and copied back.
+        Buffers and parameters outside any optimizer go through one coalesced NCCL broadcast."""
+        if self.dist.size < 2:
+            return
+        from determined_b200.ops import comm
+
+        covered = set()
+        with torch.no_grad():
+            for rec in self.records.values():
+                if rec.group is None or rec.layout is None:
+                    continue
+                lay = rec.layout
+                lay.flat_grad.copy_(lay.flat_param)
+                comm.broadcast(rec.group, rec.peer_bufs, 0, lay.total, root=0, timeout_s=self.timeout_s)
+                lay.flat_param.copy_(lay.flat_grad)
+                lay.flat_grad.zero_()
+                covered.update(id(s.param) for s in lay.slots)
+            rest = [t for m in models for t in ([p.data for p in m.parameters() if id(p) not in covered] + [b.data for b in m.buffers()])]
+            if rest:
+                self._broadcast_tensors(rest)
+        torch.cuda.synchronize(self.device)
+
     # ------------------------------------------------------------------ backward-time overlap
     def _make_hook(self, rec: _OptRecord) -> Callable[[torch.Tensor], None]:
         def hook(p: torch.Tensor) -> None:
-            if not self._communicating:
+            if not self._communicating or rec.passes_seen < rec.backward_passes:
                 return
             b = rec.bucket_of.get(id(p))
             if b is None:
                 return
             if b.launched:
                 raise errors.InvalidExperimentException(
-                    "a parameter received a second gradient in the same batch after its bucket was already "
-                    "all-reduced; with distributed training each parameter's gradient may be computed once per "
-                    "batch (use optimizations.aggregation_frequency for accumulation)")
+                    "a parameter received a second gradient inside one backward pass after its bucket was already "
+                    "all-reduced (a weight used by two branches whose gradients arrive far apart); run the backward "
+                    "passes through context.backward(), which re-reduces buckets touched by a later pass, or turn the "
+                    "fused engine off with context.experimental.use_fused_engine(False)")
             b.pending -= 1
             if b.pending == 0:
                 self._launch_ready(rec)
@@ -234,8 +308,17 @@ class FusedGradEngine(GradEngineBase):
             b.pending = len(b.owned)
             b.launched = False
         rec.next_bucket = 0
+        rec.passes_seen = 0
+        rec.stats_stale = False
+        rec.unscaled_in_flight = False
         if rec.group is not None:
             rec.group.begin_step()
+
+    def _scale_of(self, rec: _OptRecord) -> float:
+        scale = 1.0 / self.dist.size
+        if rec.average_aggregated_gradients:
+            scale /= self.agg
+        return scale
 
     def _launch_bucket(self, rec: _OptRecord, b: Bucket) -> None:
         from determined_b200.ops import comm
@@ -244,23 +327,70 @@ class FusedGradEngine(GradEngineBase):
         ev = torch.cuda.Event()
         ev.record(cur)
         self.comm_stream.wait_event(ev)
-        scale = 1.0 / self.dist.size
-        if rec.average_aggregated_gradients:
-            scale /= self.agg
-        comm.allreduce_fused(rec.group, rec.peer_bufs, b.offset, b.numel, scale, stream=self.comm_stream,
-                             timeout_s=self.timeout_s)
+        scale = self._scale_of(rec)
+        ils = rec.inv_scale if rec.unscaled_in_flight else None
+        finf = rec.found_inf if rec.unscaled_in_flight else None
+        if rec.wire_bf16:
+            grad = rec.layout.flat_grad[b.offset:b.offset + b.numel]
+            stage = rec.stage[b.offset:b.offset + b.numel]
+            comm.narrow_bf16(grad, stage, stream=self.comm_stream)
+            comm.allreduce_bf16(rec.group, rec.peer_stage, b.offset, b.numel, scale, inv_loss_scale=ils, found_inf=finf,
+                                stream=self.comm_stream, timeout_s=self.timeout_s, mc_ptr=rec.mc_stage)
+            comm.widen_bf16(stage, grad, stream=self.comm_stream)
+        else:
+            comm.allreduce_fused(rec.group, rec.peer_bufs, b.offset, b.numel, scale, inv_loss_scale=ils, found_inf=finf,
+                                 stream=self.comm_stream, timeout_s=self.timeout_s, mc_ptr=rec.mc_ptr)
         b.launched = True
 
     def _launch_ready(self, rec: _OptRecord) -> None:
         while rec.next_bucket < len(rec.buckets):
             b = rec.buckets[rec.next_bucket]
-            if b.pending > 0:
+            if b.pending > 0 or b.launched:
+                if b.launched:
+                    rec.next_bucket += 1
+                    continue
                 return
             self._launch_bucket(rec, b)
             rec.next_bucket += 1
 
-    def backward_begin(self, communicate: bool) -> None:
+    def _rearm_for_another_pass(self, rec: _OptRecord, scaler_scale: Optional[torch.Tensor]) -> None:
+        """A second communicating backward pass in one optimizer step (two losses flowing into the same parameters, the
+        GAN pattern; torch DDP reduces every backward).  Buckets already reduced hold A = c * sum_r(g_r) on every rank with
+        c = scale [/ loss_scale]; multiplying them by 1/(world*c) makes the next reduction of (that + new local gradient)
+        come out as A + c * sum_r(g2_r): the sum stays linear.  All buckets are then re-armed."""
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_stream(self.comm_stream)
+        factor = 1.0 / (self.dist.size * self._scale_of(rec))
+        for b in rec.buckets:
+            if b.launched:
+                region = rec.layout.flat_grad[b.offset:b.offset + b.numel]
+                if rec.unscaled_in_flight and scaler_scale is not None:
+                    region.mul_(scaler_scale.to(torch.float32) * factor)
+                elif factor != 1.0:
+                    region.mul_(factor)
+                rec.stats_stale = True
+            b.launched = False
+            b.pending = len(b.owned)
+        rec.next_bucket = 0
+
+    def backward_begin(self, communicate: bool, scaler: Any = None) -> None:
         self._communicating = communicate and self.dist.size > 1
+        if not self._communicating:
+            return
+        amp = scaler is not None and scaler.is_enabled() and getattr(scaler, "_scale", None) is not None
+        for rec in self.records.values():
+            if not rec.buckets:
+                continue
+            rec.passes_seen += 1
+            if rec.passes_seen < rec.backward_passes:
+                continue
+            if amp and rec.fused_step and not rec.unscaled_in_flight and not any(b.launched for b in rec.buckets):
+                # K4: the all-reduce epilogue unscales and checks for inf/nan; the optimizer reads the flag
+                torch.reciprocal(scaler._scale.reshape(1).to(torch.float32), out=rec.inv_scale)
+                rec.found_inf.zero_()
+                rec.unscaled_in_flight = True
+            if any(b.launched for b in rec.buckets):
+                self._rearm_for_another_pass(rec, scaler._scale if amp else None)
 
     def _flush(self, rec: _OptRecord) -> None:
         """Launch whatever has not been launched yet (buckets holding parameters that received no
@@ -268,11 +398,10 @@ class FusedGradEngine(GradEngineBase):
         stepped without a communicating backward), then make the compute stream wait."""
         if not rec.buckets:
             return
-        while rec.next_bucket < len(rec.buckets):
-            b = rec.buckets[rec.next_bucket]
+        for b in rec.buckets:
             if not b.launched:
                 self._launch_bucket(rec, b)
-            rec.next_bucket += 1
+        rec.next_bucket = len(rec.buckets)
         torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
 
     # ------------------------------------------------------------------ optimizer step
@@ -291,33 +420,61 @@ class FusedGradEngine(GradEngineBase):
             static_scale = (1.0 / self.agg) if (rec.average_aggregated_gradients and self.agg > 1) else 1.0
 
         params = [p for g in optimizer.param_groups for p in g["params"]]
+        amp = scaler is not None and scaler.is_enabled()
+        if scaler is not None and not amp:
+            scaler = None           # a disabled GradScaler is a pass-through
+        # Fused AMP (K4): no scaler.unscale_ / scaler.step.  Multi-GPU: the all-reduce already unscaled the gradients and
+        # raised found_inf.  One GPU: a sum-of-squares pass finds non-finite values (and gives the norm), and the
+        # optimizer kernel multiplies by 1/loss_scale.
+        fused_amp = amp and rec.fused_step and (rec.unscaled_in_flight or world == 1) \
+            and (clip_grads is None or isinstance(clip_grads, FusedClipGradNorm)) and getattr(scaler, "_scale", None) is not None
+        use_fused_step = rec.fused_step and (scaler is None or fused_amp)
         grad_scale = None
-        use_fused_step = rec.fused_step and scaler is None
+        skip = None
+        if fused_amp:
+            skip = rec.found_inf
+            if world == 1:
+                torch.reciprocal(scaler._scale.reshape(1).to(torch.float32), out=rec.inv_scale)
+                rec.scratch.nonfinite.zero_()
+                optim.sumsq(lay.flat_grad, rec.scratch, check_finite=True)
+                skip = rec.scratch.nonfinite
+                grad_scale = rec.inv_scale
         if isinstance(clip_grads, FusedClipGradNorm) and use_fused_step:
-            if world > 1:
+            if world > 1 and not rec.stats_stale:
                 terms = rec.group.stats_tensor()[0, :world]
                 grad_scale = optim.clip_coef(terms, clip_grads.max_norm, rec.scratch)
             else:
-                optim.sumsq(lay.flat_grad, rec.scratch)
-                # the norm is of the *averaged* gradient: fold static_scale^2 in through extra handling
+                if not (fused_amp and world == 1):
+                    optim.sumsq(lay.flat_grad, rec.scratch)
+                # the norm is of the *averaged*, unscaled gradient: fold the pending factors in
                 if static_scale != 1.0:
                     rec.scratch.sumsq.mul_(static_scale * static_scale)
+                if fused_amp and world == 1:
+                    rec.scratch.sumsq.mul_(rec.inv_scale * rec.inv_scale)
                 grad_scale = optim.clip_coef(rec.scratch.sumsq, clip_grads.max_norm, rec.scratch)
+                if fused_amp and world == 1:
+                    grad_scale = grad_scale.mul_(rec.inv_scale)
             clip_grads.last_norm = rec.scratch.norm
         elif clip_grads is not None:
             if static_scale != 1.0:
                 lay.flat_grad.mul_(static_scale)
                 static_scale = 1.0
-            if scaler is not None and unscale_for_clip:
+            if scaler is not None and unscale_for_clip and not rec.unscaled_in_flight:
                 scaler.unscale_(optimizer)
             clip_grads(params)
 
         if use_fused_step:
-            optimizer.step(grad_scale=grad_scale, static_scale=static_scale, zero_grad=auto_zero_grads)
+            optimizer.step(grad_scale=grad_scale, skip=skip, static_scale=static_scale, zero_grad=auto_zero_grads)
+            if fused_amp:
+                self._record_inf_check(scaler, optimizer, skip)
         else:
             if static_scale != 1.0:
                 lay.flat_grad.mul_(static_scale)
-            if scaler is not None:
+            if scaler is not None and rec.unscaled_in_flight:
+                # gradients are already unscaled and checked: tell the scaler so, then let it decide about the step
+                self._record_inf_check(scaler, optimizer, rec.found_inf, stepped=False)
+                scaler.step(optimizer)
+            elif scaler is not None:
                 scaler.step(optimizer)
             else:
                 optimizer.step()
@@ -325,6 +482,18 @@ class FusedGradEngine(GradEngineBase):
                 lay.flat_grad.zero_()
         if world > 1:
             self._arm(rec)
+
+    def _record_inf_check(self, scaler: Any, optimizer: torch.optim.Optimizer, flag: torch.Tensor, stepped: bool = True) -> None:
+        """Give ``scaler.update()`` what ``unscale_`` + ``step`` would have left behind: the found-inf tensor of this
+        optimizer and its stage (reference flow ``_pytorch_context.py:886-897``; torch ``GradScaler.update`` reads
+        ``_per_optimizer_states[id(opt)]["found_inf_per_device"]``)."""
+        from torch.amp.grad_scaler import OptState
+
+        rec = self.records[id(optimizer)]
+        rec.found_inf_f.copy_(flag)
+        st = scaler._per_optimizer_states[id(optimizer)]
+        st["found_inf_per_device"] = {self.device: rec.found_inf_f}
+        st["stage"] = OptState.STEPPED if stepped else OptState.UNSCALED
 
     def close(self) -> None:
         for rec in self.records.values():

@@ -114,10 +114,14 @@ class FlatLayout:
                     gwant.copy_(s.param.grad)
                     s.param.grad = gwant
 
-    def make_buckets(self, cap_bytes: int, multiple: int) -> List["Bucket"]:
+    def make_buckets(self, cap_bytes: int, multiple: int, tail_cap_bytes: int = 0) -> List["Bucket"]:
         """Partition [0,total) into buckets of about ``cap_bytes``, cut at parameter boundaries,
         in *reverse* parameter order (gradients become ready roughly last-layer-first).  Bucket
-        boundaries are multiples of ``multiple`` elements."""
+        boundaries are multiples of ``multiple`` elements.
+
+        ``tail_cap_bytes`` > 0 additionally splits off the *last-ready* bucket (the first parameters of the model) at
+        about that size: it can only be reduced once backward is over, so it is the part of the exchange nothing can
+        hide, and it should be small (torch DDP makes its first-ready bucket 1 MB for the mirror-image reason)."""
         cap = max(cap_bytes // 4, multiple)
         bounds = [self.total]
         cur_hi = self.total
@@ -126,6 +130,14 @@ class FlatLayout:
             if cur_hi - lo >= cap and lo < cur_hi and lo > 0:
                 bounds.append(lo)
                 cur_hi = lo
+        if tail_cap_bytes > 0 and self.slots:
+            tail = max(tail_cap_bytes // 4, multiple)
+            for s in self.slots:
+                lo = s.offset // multiple * multiple
+                if lo >= tail:
+                    if lo < self.total:
+                        bounds.append(lo)
+                    break
         bounds.append(0)
         bounds = sorted(set(bounds))
         buckets = []

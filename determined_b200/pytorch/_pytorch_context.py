@@ -257,7 +257,9 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
             "fp16_compression": bool(fp16_compression),
             "average_aggregated_gradients": bool(average_aggregated_gradients),
         }
-        optimizer = self._get_engine().add_optimizer(optimizer, bool(average_aggregated_gradients))
+        optimizer = self._get_engine().add_optimizer(optimizer, bool(average_aggregated_gradients),
+                                                     backward_passes_per_step=backward_passes_per_step,
+                                                     fp16_compression=bool(fp16_compression))
         self.optimizers.append(optimizer)
         return optimizer
 
@@ -326,7 +328,7 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
         if self._scaler is not None and self.experimental._auto_amp:
             loss = self._scaler.scale(loss)
         engine = self._get_engine()
-        engine.backward_begin(self._should_communicate_and_update())
+        engine.backward_begin(self._should_communicate_and_update(), scaler=self._scaler)
         loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)
         engine.backward_end()
 

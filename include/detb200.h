@@ -67,7 +67,8 @@ int detb200_sumsq(const float* x, int64_t n, void* scratch, float* out, int* non
  * native code at all).  n <= detb200_sumsq_noalloc_max_elems() (2^30) or DETB200_ERR_TOO_LARGE.
  * Allocates nothing.  Calls on one device share the array: order them on the GPU, overlapping
  * calls race.  The first call on a device resolves the array's address; do it before any stream
- * capture. */
+ * capture.  The device that owns `stream` must be the current device (DETB200_ERR_BAD_ARG
+ * otherwise): the array is per GPU and the address is looked up for the current one. */
 int64_t detb200_sumsq_noalloc_max_elems(void);
 int detb200_sumsq_noalloc(const float* x, int64_t n, float* out, int* nonfinite_flag /* nullable */, int accumulate,
                           detb200_stream_t stream);
@@ -109,9 +110,58 @@ int detb200_rs_adam_ag(void* const* peer_grad_bufs, void* const* peer_ctrls, voi
                        float scale, const float* lr, const int* step, const float* grad_scale, const int* skip,
                        float beta1, float beta2, float eps, float weight_decay, int mode, int first_of_step,
                        int phases, double timeout_s, detb200_stream_t stream);
+/* Extended forms.  mc_buf / mc_grad / mc_param: this rank's mapping of an NVSwitch multicast object bound to every
+ * rank's buffer (detb200_mc_*), or NULL for peer-to-peer loads and stores; with it the reduction happens inside the
+ * switch (multimem.ld_reduce) and the result is written to all ranks by one multimem.st.  max_ctas <= 0: default
+ * budget (32 CTAs; the rest of the GPU stays with the backward pass the collective overlaps). */
+int detb200_allreduce_fused_ex(void* const* peer_bufs, void* const* peer_ctrls, void* mc_buf, int rank, int world,
+                               int64_t offset_elems, int64_t n_elems, float scale, const float* inv_loss_scale,
+                               int* found_inf, int first_of_step, int phases, int max_ctas, double timeout_s,
+                               detb200_stream_t stream);
+/* Test entry point: all `world` ranks of the all-reduce in one cooperative launch on ONE GPU (bufs / ctrls are `world`
+ * allocations of that GPU; found_inf is int[world] or NULL): the flag / epoch / barrier protocol without a second GPU. */
+int detb200_allreduce_fused_emulated(void* const* bufs, void* const* ctrls, int world, int64_t offset_elems,
+                                     int64_t n_elems, float scale, const float* inv_loss_scale, int* found_inf,
+                                     int first_of_step, int ctas_per_rank, double timeout_s, detb200_stream_t stream);
+/* 16-bit wire format (reference hvd.Compression.fp16, _pytorch_context.py:367; expconf optimizations.gradient_compression):
+ * narrow (local) -> allreduce_bf16 over the symmetric bf16 staging buffers -> widen (local).  Lengths multiples of 8. */
+int detb200_narrow_bf16(const float* x, void* y_bf16, int64_t n, detb200_stream_t stream);
+int detb200_widen_bf16(const void* x_bf16, float* y, int64_t n, detb200_stream_t stream);
+int detb200_allreduce_bf16(void* const* peer_stage, void* const* peer_ctrls, void* mc_stage, int rank, int world,
+                           int64_t offset_elems, int64_t n_elems, float scale, const float* inv_loss_scale,
+                           int* found_inf, int first_of_step, int phases, int max_ctas, double timeout_s,
+                           detb200_stream_t stream);
+/* rs_adam_ag with separate gradient / parameter offsets (ZeRO-2 reduces out of a landing buffer), gradient
+ * accumulation into grad_shard in mode 1 (accumulate != 0) and the multicast variants. */
+int detb200_rs_adam_ag_ex(void* const* peer_grad_bufs, void* const* peer_ctrls, void* const* peer_param_bufs /* nullable in mode 1 */,
+                          void* mc_grad, void* mc_param, int param_is_bf16, int rank, int world,
+                          int64_t grad_offset_elems, int64_t param_offset_elems, int64_t n_elems,
+                          float* master_shard, float* m_shard, float* v_shard, float* grad_shard,
+                          float scale, const float* lr, const int* step, const float* grad_scale, const int* skip,
+                          float beta1, float beta2, float eps, float weight_decay, int mode, int accumulate,
+                          int first_of_step, int phases, int max_ctas, double timeout_s, detb200_stream_t stream);
 int detb200_broadcast(void* const* peer_bufs, void* const* peer_ctrls, int rank, int world, int root,
                       int64_t offset_elems, int64_t n_elems, int phases, double timeout_s,
                       detb200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Symmetric memory on the CUDA virtual-memory API and NVSwitch multicast objects (csrc/symm.cpp).
+ * Reference: none of its own; NCCL's NVLS algorithm is what its DDP / DeepSpeed paths use on an NVSwitch box.
+ * File descriptors returned here are passed to the peer processes over a unix socket (SCM_RIGHTS) by the caller.
+ * A multicast mapping is for multimem.* instructions only; never build a tensor map over it.
+ * ------------------------------------------------------------------------------------------- */
+int detb200_vmm_query(int* caps /* host int[2]: exportable VMM allocations, multicast objects */);
+int detb200_vmm_granularity(int world, int64_t* bytes_out);
+int detb200_vmm_alloc(int64_t bytes, void** ptr, int* fd_out);          /* zero-filled; synchronises */
+int detb200_vmm_import(int fd, int64_t bytes, void** ptr_out);          /* map a peer's allocation */
+int detb200_vmm_free(void* ptr);
+int detb200_mc_create(int world, int64_t bytes, int64_t* mc_out, int* fd_out);   /* one rank */
+int detb200_mc_import(int fd, int64_t* mc_out);                                   /* the others */
+int detb200_mc_add_device(int64_t mc);                                            /* all, before any bind */
+int detb200_mc_bind(int64_t mc, void* local_ptr /* from detb200_vmm_alloc */, int64_t bytes);
+int detb200_mc_map(int64_t mc, int64_t bytes, void** mc_ptr_out);
+int detb200_mc_free(int64_t mc, void* mc_ptr, int64_t bytes);
+int detb200_close_fd(int fd);
 
 /* ---------------------------------------------------------------------------------------------
  * LayerNorm / RMSNorm (csrc/norm.cu).  Reference: ATen/apex/Megatron fused LN used by the GPT-2 and

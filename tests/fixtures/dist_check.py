@@ -61,6 +61,235 @@ def check_allreduce(rank, world, dev):
     group.close()
 
 
+def check_allreduce_nvls(rank, world, dev):
+    """VMM symmetric buffers (fd exchange) + the multicast object: in-switch reduction and the bf16 wire format against
+    NCCL, over several CTA budgets.  Where the box has no NVLS the same calls run peer-to-peer (and say so)."""
+    from determined_b200.ops import comm
+
+    group = comm.PeerGroup.from_torch_distributed(dev)
+    assert group.vmm_ok, "VMM file-descriptor handles should be available on the B200 boxes"
+    n = 8 * world * 200_000 + 8 * world * 5
+    buf = group.alloc(4 * n)
+    assert buf.vmm
+    t = buf.tensor(torch.float32, n)
+    peers = group.map(buf)
+    mc = group.multicast(buf)
+    if rank == 0:
+        print("NVLS multicast mapping:", "yes" if mc else "no (peer-to-peer fallback)", flush=True)
+    stage_buf = group.alloc(2 * n)
+    stage = stage_buf.tensor(torch.bfloat16, n)
+    peer_stage = group.map(stage_buf)
+    mc_stage = group.multicast(stage_buf)
+    for it, (ctas, use_mc) in enumerate([(0, True), (4, True), (148, True), (8, False), (0, False)]):
+        torch.manual_seed(7 * it + rank)
+        t.copy_(torch.randn(n, device=dev))
+        ref = t.clone()
+        dist.all_reduce(ref)
+        ref.mul_(0.5 / world)
+        group.begin_step()
+        group.found_inf.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        half = (n // 2) // (8 * world) * (8 * world)
+        m = mc if use_mc else None
+        comm.allreduce_fused(group, peers, 0, half, 0.5 / world, found_inf=group.found_inf, timeout_s=20, mc_ptr=m, max_ctas=ctas)
+        comm.allreduce_fused(group, peers, half, n - half, 0.5 / world, found_inf=group.found_inf, timeout_s=20, mc_ptr=m, max_ctas=ctas)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(t, ref, rtol=1e-5, atol=1e-5)
+        sumsq = float(group.stats_tensor()[0, :world].sum())
+        torch.testing.assert_close(torch.tensor(sumsq), ref.double().pow(2).sum().float().cpu(), rtol=1e-3, atol=1e-3)
+        assert int(group.found_inf.item()) == 0
+        # every rank holds the same bits
+        chk = t[:1024].clone()
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert torch.equal(lo, hi), "ranks disagree after the all-reduce"
+    # bf16 wire format: narrow -> reduce -> widen, both transports
+    for use_mc in (True, False):
+        torch.manual_seed(99 + rank)
+        t.copy_(torch.randn(n, device=dev))
+        ref = t.to(torch.bfloat16).float()
+        dist.all_reduce(ref)
+        ref.mul_(1.0 / world)
+        group.begin_step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.narrow_bf16(t, stage)
+        comm.allreduce_bf16(group, peer_stage, 0, n, 1.0 / world, found_inf=group.found_inf, timeout_s=20,
+                            mc_ptr=mc_stage if use_mc else None)
+        comm.widen_bf16(stage, t)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(t, ref, rtol=2e-2, atol=2e-2)
+        sumsq = float(group.stats_tensor()[0, :world].sum())
+        torch.testing.assert_close(torch.tensor(sumsq), ref.double().pow(2).sum().float().cpu(), rtol=2e-2, atol=1e-2)
+    # inf on one rank reaches everybody through the switch as well
+    t.zero_()
+    if rank == world - 1:
+        t[13] = float("nan")
+    group.begin_step()
+    group.found_inf.zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    comm.allreduce_fused(group, peers, 0, n, 1.0, found_inf=group.found_inf, timeout_s=20, mc_ptr=mc)
+    torch.cuda.synchronize()
+    assert int(group.found_inf.item()) == 1, "non-finite value not detected"
+    dist.barrier()
+    group.close()
+
+
+def _two_net_setup(dev, seed=0):
+    torch.manual_seed(seed)
+    gen = torch.nn.Sequential(torch.nn.Linear(16, 64), torch.nn.Tanh(), torch.nn.Linear(64, 32)).to(dev)
+    dis = torch.nn.Sequential(torch.nn.Linear(32, 64), torch.nn.Tanh(), torch.nn.Linear(64, 1)).to(dev)
+    return gen, dis
+
+
+def check_gan_two_optimizers(rank, world, dev):
+    """The GAN pattern the reference supports through torch DDP: g_loss.backward() flows into the discriminator's
+    parameters, then d_loss.backward() adds to them before opt_d steps.  Every backward is reduced; the sums must match
+    DDP's.  Also ``backward_passes_per_step=2`` (communicate on the second pass only) on a third optimizer."""
+    import copy
+
+    from determined_b200 import core, pytorch
+
+    torch.backends.cuda.matmul.allow_tf32 = False
+    gen0, dis0 = _two_net_setup(dev)
+    ref_g = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(gen0), device_ids=[dev.index])
+    ref_d = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(dis0), device_ids=[dev.index])
+    ro_g = torch.optim.SGD(ref_g.parameters(), lr=0.05)
+    ro_d = torch.optim.SGD(ref_d.parameters(), lr=0.05)
+    dctx = core.DistributedContext.from_torch_distributed()
+    with pytorch.init(hparams={"global_batch_size": 8 * world}, distributed=dctx) as ctx:
+        ctx.experimental.use_fused_engine(True, bucket_cap_mb=0.004)     # several buckets per net
+        g = ctx.wrap_model(copy.deepcopy(gen0))
+        d = ctx.wrap_model(copy.deepcopy(dis0))
+        og = ctx.wrap_optimizer(torch.optim.SGD(g.parameters(), lr=0.05))
+        od = ctx.wrap_optimizer(torch.optim.SGD(d.parameters(), lr=0.05))
+        assert type(og).__name__ == "FusedSGD" and type(od).__name__ == "FusedSGD"
+        rng = torch.Generator().manual_seed(77 + rank)
+        for i in range(4):
+            ctx._current_batch_idx = i
+            z = torch.randn(8, 16, generator=rng).to(dev)
+            real = torch.randn(8, 32, generator=rng).to(dev)
+            # ours
+            g_loss = -d(g(z)).mean()
+            ctx.backward(g_loss)                      # also fills the discriminator's gradients
+            ctx.step_optimizer(og)
+            d_loss = d(real).mean() - d(g(z).detach()).mean()
+            ctx.backward(d_loss)                      # second gradient for the same parameters in this step
+            ctx.step_optimizer(od)
+            # reference
+            ro_g.zero_grad()
+            rg = -ref_d(ref_g(z)).mean()
+            rg.backward()
+            ro_g.step()
+            rd = ref_d(real).mean() - ref_d(ref_g(z).detach()).mean()
+            rd.backward()                             # d grads = g_loss part + d_loss part, both reduced
+            ro_d.step()
+            ro_d.zero_grad()
+        for a, b in zip(list(g.parameters()) + list(d.parameters()), list(ref_g.module.parameters()) + list(ref_d.module.parameters())):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
+
+    # backward_passes_per_step=2: two backward passes per optimizer step, exchange on the second
+    torch.manual_seed(3)
+    net0 = torch.nn.Linear(32, 8).to(dev)
+    ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(net0), device_ids=[dev.index])
+    ro = torch.optim.SGD(ref.parameters(), lr=0.1)
+    with pytorch.init(hparams={"global_batch_size": 4 * world}, distributed=dctx) as ctx:
+        net = ctx.wrap_model(copy.deepcopy(net0))
+        opt = ctx.wrap_optimizer(torch.optim.SGD(net.parameters(), lr=0.1), backward_passes_per_step=2)
+        rng = torch.Generator().manual_seed(5 + rank)
+        for i in range(3):
+            ctx._current_batch_idx = i
+            xa, xb = torch.randn(4, 32, generator=rng).to(dev), torch.randn(4, 32, generator=rng).to(dev)
+            ctx.backward(net(xa).pow(2).mean())
+            ctx.backward(net(xb).pow(2).mean())
+            ctx.step_optimizer(opt)
+            ro.zero_grad()
+            with ref.no_sync():
+                ref(xa).pow(2).mean().backward()
+            ref(xb).pow(2).mean().backward()
+            ro.step()
+        for a, b in zip(net.parameters(), ref.module.parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
+
+
+def check_amp_and_compression(rank, world, dev):
+    """K4: with a GradScaler the fused path stays on (unscale + inf check inside the all-reduce, skip flag into the fused
+    optimizer, scaler.update() fed by the engine) and never calls scaler.unscale_.  K7: fp16_compression = bf16 wire."""
+    import copy
+
+    from determined_b200 import core, pytorch
+
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(11)
+    net0 = torch.nn.Sequential(torch.nn.Linear(24, 48), torch.nn.ReLU(), torch.nn.Linear(48, 4)).to(dev)
+    ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(net0), device_ids=[dev.index])
+    ro = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    rs = torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=2)
+    dctx = core.DistributedContext.from_torch_distributed()
+    calls = {"unscale": 0}
+    with pytorch.init(hparams={"global_batch_size": 8 * world}, distributed=dctx) as ctx:
+        net = ctx.wrap_model(copy.deepcopy(net0))
+        opt = ctx.wrap_optimizer(torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9))
+        scaler = ctx.wrap_scaler(torch.amp.GradScaler("cuda", init_scale=1024.0, growth_interval=2))
+        orig = scaler.unscale_
+        def counting(o):  # noqa: E306
+            calls["unscale"] += 1
+            return orig(o)
+        scaler.unscale_ = counting
+        assert type(opt).__name__ == "FusedSGD"
+        rng = torch.Generator().manual_seed(21 + rank)
+        for i in range(6):
+            ctx._current_batch_idx = i
+            x = torch.randn(8, 24, generator=rng).to(dev)
+            if i == 3 and rank == world - 1:
+                x[0, 0] = float("inf")           # one rank overflows: every rank must skip this step
+            loss = net(x).pow(2).mean()
+            ctx.backward(scaler.scale(loss))
+            ctx.step_optimizer(opt, clip_grads=pytorch.FusedClipGradNorm(0.5), scaler=scaler)
+            scaler.update()
+            ro.zero_grad()
+            rl = ref(x).pow(2).mean()
+            rs.scale(rl).backward()
+            rs.unscale_(ro)
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
+            rs.step(ro)
+            rs.update()
+            assert float(scaler.get_scale()) == float(rs.get_scale()), (i, scaler.get_scale(), rs.get_scale())
+        for a, b in zip(net.parameters(), ref.module.parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
+        assert calls["unscale"] == 0, "the fused AMP path must not fall back to scaler.unscale_"
+        assert type(opt).__name__ == "FusedSGD"
+
+    # bf16 wire format through the engine
+    torch.manual_seed(12)
+    net0 = torch.nn.Linear(64, 64).to(dev)
+    with pytorch.init(hparams={"global_batch_size": 8 * world}, distributed=dctx) as ctx:
+        a = ctx.wrap_model(copy.deepcopy(net0))
+        b = ctx.wrap_model(copy.deepcopy(net0))
+        oa = ctx.wrap_optimizer(torch.optim.SGD(a.parameters(), lr=0.1))
+        ob = ctx.wrap_optimizer(torch.optim.SGD(b.parameters(), lr=0.1), fp16_compression=True)
+        assert ctx._get_engine().records[id(ob)].wire_bf16
+        rng = torch.Generator().manual_seed(31 + rank)
+        for i in range(3):
+            ctx._current_batch_idx = i
+            x = torch.randn(8, 64, generator=rng).to(dev)
+            ctx.backward(a(x).pow(2).mean() + b(x).pow(2).mean())
+            ctx.step_optimizer(oa)
+            ctx.step_optimizer(ob)
+        for pa, pb in zip(a.parameters(), b.parameters()):
+            torch.testing.assert_close(pa, pb, rtol=2e-2, atol=2e-3)
+            assert not torch.equal(pa, pb) or pa.numel() < 8      # it really went through bf16
+        ws = [p.detach().clone() for p in b.parameters()]
+        for w in ws:
+            lo, hi = w.clone(), w.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            assert torch.equal(lo, hi), "ranks diverged under the bf16 wire format"
+
+
 def check_engine(rank, world, dev):
     """One-variable model, aggregation_frequency=2: weights on every rank must follow the analytic
     trajectory of averaged gradients (reference test_pytorch_trial.py:980-1001,1604-1642)."""
@@ -400,6 +629,12 @@ def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     if which in ("all", "allreduce"):
         check_allreduce(rank, world, dev)
+    if which in ("all", "allreduce_nvls"):
+        check_allreduce_nvls(rank, world, dev)
+    if which in ("all", "gan"):
+        check_gan_two_optimizers(rank, world, dev)
+    if which in ("all", "amp"):
+        check_amp_and_compression(rank, world, dev)
     if which in ("all", "engine"):
         check_engine(rank, world, dev)
     if which in ("all", "resnet"):

@@ -184,6 +184,51 @@ def test_allreduce_fused_emulated_ranks(world):
         torch.testing.assert_close(t.double(), expect, rtol=1e-5, atol=1e-6)
 
 
+@pytest.mark.parametrize("world,cpr", [(2, 3), (4, 2), (8, 1), (8, 4)])
+def test_allreduce_full_protocol_emulated_in_one_cooperative_launch(world, cpr):
+    """The whole collective (start barrier, reduce + scatter, statistics exchange, end barrier, epoch advance) for `world`
+    ranks on ONE GPU: the CTAs of all ranks form one cooperative grid, so the flag spins are between co-resident CTAs of
+    one kernel.  Several buckets back to back and two steps exercise the epoch counters and the running statistics."""
+    from determined_b200.ops import _lib, comm
+
+    lib = _lib.load()
+    dev = torch.device("cuda")
+    n = 4 * world * 3001
+    groups = [comm.PeerGroup(0, 1, None, dev) for _ in range(world)]
+    bufs = [comm.SymmetricBuffer(4 * n, dev) for _ in range(world)]
+    tens = [b.tensor(torch.float32, n) for b in bufs]
+    ptrs = (ctypes.c_void_p * world)(*[b.ptr for b in bufs])
+    ctrls = (ctypes.c_void_p * world)(*[g.ctrl.ptr for g in groups])
+    found = torch.zeros(world, dtype=torch.int32, device=dev)
+    inv = torch.full((1,), 0.25, device=dev)
+    scale = 1.0 / world
+    cut = (n // 3) // (4 * world) * (4 * world)
+    for step in range(2):
+        torch.manual_seed(10 + step)
+        for t in tens:
+            t.copy_(torch.randn(n, device=dev))
+        expect = torch.stack([t.clone() for t in tens]).double().sum(0) * (scale * 0.25)
+        for bi, (off, cnt) in enumerate([(0, cut), (cut, n - cut)]):
+            _lib.check(lib.detb200_allreduce_fused_emulated(ptrs, ctrls, world, off, cnt, scale, inv.data_ptr(), found.data_ptr(),
+                                                            int(bi == 0), cpr, 20.0, _lib.stream_ptr()), "allreduce_emulated")
+        torch.cuda.synchronize()
+        for t in tens:
+            torch.testing.assert_close(t.double(), expect, rtol=1e-5, atol=1e-6)
+        # every rank's table holds every rank's slice statistics: their sum is the squared norm of the result
+        for g in groups:
+            tot = float(g.stats_tensor()[0, :world].sum())
+            torch.testing.assert_close(torch.tensor(tot), expect.pow(2).sum().float().cpu(), rtol=1e-3, atol=1e-3)
+        assert int(found.sum()) == 0
+    # a non-finite value in ONE rank's buffer raises found_inf on EVERY rank
+    for t in tens:
+        t.zero_()
+    tens[world - 1][7] = float("inf")
+    _lib.check(lib.detb200_allreduce_fused_emulated(ptrs, ctrls, world, 0, n, scale, None, found.data_ptr(), 1, cpr, 20.0,
+                                                    _lib.stream_ptr()), "allreduce_emulated")
+    torch.cuda.synchronize()
+    assert found.tolist() == [1] * world
+
+
 def test_resnet_step_fused_vs_torch():
     """One optimizer's worth of ResNet-18 params: fused engine (world=1) must track torch SGD."""
     from determined_b200 import core, pytorch

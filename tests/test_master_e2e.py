@@ -189,6 +189,43 @@ def test_validation_errors_and_auth(cluster):
     assert r["experiment"] is None and r["config"]["max_restarts"] == 2
 
 
+def test_non_admin_cannot_escalate_and_checkpoint_ids_must_be_uuids(cluster):
+    """Reference api_user.go:429-466 (admin / active / username need an admin) and the uuid-typed checkpoint id."""
+    m, _, tmp = cluster
+    sess = api.authentication.login(m.url, "admin", "")
+    uid = sess.post("/api/v1/users", json={"user": {"username": "mallory", "active": True}, "password": "pw"}).json()["user"]["id"]
+    mal = api.authentication.login(m.url, "mallory", "pw")
+    for patch in ({"user": {"admin": True}}, {"admin": True}, {"user": {"active": False}}, {"user": {"username": "root"}}):
+        with pytest.raises(api.errors.APIException) as e:
+            mal.patch(f"/api/v1/users/{uid}", json=patch)
+        assert e.value.status_code == 403, patch
+    assert not mal.get("/api/v1/me").json()["user"]["admin"]
+    with pytest.raises(api.errors.APIException) as e:
+        mal.post("/api/v1/users", json={"user": {"username": "x"}})
+    assert e.value.status_code == 403
+    # its own display name and password are its to change; the password is stored hashed
+    assert mal.patch(f"/api/v1/users/{uid}", json={"user": {"displayName": "M", "password": "pw2"}}).json()["user"]["displayName"] == "M"
+    api.authentication.login(m.url, "mallory", "pw2")
+    # an admin setting a password through the dict body gets it hashed as well
+    sess.patch(f"/api/v1/users/{uid}", json={"user": {"password": "pw3"}})
+    api.authentication.login(m.url, "mallory", "pw3")
+    # a reported checkpoint id names a directory that GC will rmtree: only UUIDs are taken
+    outside = tmp / "precious"
+    outside.mkdir()
+    (outside / "f").write_text("x")
+    for bad in ("../precious", "/etc", "not-a-uuid", "../../x"):
+        with pytest.raises(api.errors.APIException) as e:
+            sess.post("/api/v1/checkpoints", json={"checkpoint": {"uuid": bad, "resources": {}, "metadata": {"steps_completed": 1}}})
+        assert e.value.status_code == 400, bad
+    from determined_b200.common.storage import shared
+    sm = shared.SharedFSStorageManager(str(tmp / "ckpt"))
+    (tmp / "ckpt").mkdir(exist_ok=True)
+    for bad in ("../precious", "..", ".", str(outside)):
+        with pytest.raises(ValueError):
+            sm.delete(bad, ["**/*"])
+    assert (outside / "f").exists()
+
+
 def test_master_restart_restores_experiments(tmp_path):
     dbp = str(tmp_path / "m.db")
     m = core.Master(db_path=dbp, num_slots=2, launch=False, work_dir=str(tmp_path / "w"),

@@ -25,7 +25,7 @@ def _ngpu() -> int:
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("which", ["allreduce", "engine", "resnet", "gemm_comm", "gpt_tp", "zero3", "zero3_engine"])
+@pytest.mark.parametrize("which", ["allreduce", "allreduce_nvls", "engine", "gan", "amp", "resnet", "gemm_comm", "gpt_tp", "zero3", "zero3_engine"])
 def test_two_ranks(which):
     _run(which, 2)
 
@@ -35,4 +35,5 @@ def test_all_ranks_allreduce_and_engine():
     if n < 4:
         pytest.skip("needs >= 4 GPUs")
     _run("allreduce", n)
+    _run("allreduce_nvls", n)
     _run("engine", n)

@@ -110,3 +110,27 @@ def test_noalloc_refuses_sizes_beyond_its_limit():
     assert "exceeds" in msg and str(limit) in msg
     torch.cuda.synchronize()
     assert float(out.item()) == 0.0
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs a second GPU")
+def test_noalloc_keeps_one_scratch_address_per_gpu():
+    """The library caches the array's device address per GPU.  Use it on cuda:0, then on cuda:1, then on cuda:0 again,
+    and compare each with the ordinary entry point on the same device; finally hand it a stream of the other device,
+    which it must refuse on the host instead of launching with the wrong GPU's scratch."""
+    lib = _load()
+    torch.manual_seed(5)
+    for d in (0, 1, 0):
+        dev = torch.device("cuda", d)
+        torch.cuda.set_device(dev)
+        x = torch.randn((1 << 20) + 3, device=dev) * (d + 1)
+        want, _ = _reference(lib, x)
+        got, bad = _noalloc(lib, x)
+        torch.testing.assert_close(torch.tensor(got), torch.tensor(want), rtol=1e-5, atol=1e-6)
+        assert bad == 0
+    torch.cuda.set_device(0)
+    foreign = torch.cuda.Stream(device=1)
+    x = torch.zeros(16, device="cuda:0")
+    out = torch.zeros(1, device="cuda:0")
+    rc = lib.detb200_sumsq_noalloc(x.data_ptr(), 16, out.data_ptr(), None, 0, foreign.cuda_stream)
+    assert rc == -1, rc
+    assert "current" in lib.detb200_last_error().decode()
