@@ -233,7 +233,8 @@ def run_ours(args, on_device: bool, sampler):
             eng = ctx._get_engine()
             rec = next(iter(eng.records.values()))
             info = {"optimizer": fused, "buckets": len(rec.buckets),
-                    "transport": ("nvls" if rec.mc_ptr else "p2p") if args.world > 1 else "none"}
+                    "transport": (("nvls" if rec.transport_nvls else "p2p") + (", overlapped with backward" if rec.overlapped
+                                  else ", one launch at step time")) if args.world > 1 else "none"}
             info["allreduce_check"] = getattr(args, "_checked", None)
     finally:
         os.chdir(cwd)
@@ -295,6 +296,67 @@ def run_reference(args, sampler):
     return ms, None
 
 
+def main_neox(args, rank: int, local: int, world: int, requested_warmup: int) -> None:
+    """BASELINE config #4: GPT-NeoX DeepSpeedTrial, ZeRO-3, bf16 (see benchmarks/bench_neox.py)."""
+    import torch
+
+    from benchmarks import bench_neox
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
+        return
+    torch.cuda.set_device(local % torch.cuda.device_count())
+    args.warmup = max(args.warmup, 3)
+    model = args.model or "neox-1.3b"
+    batch, seq = args.micro_batch, args.seq
+    # the LM head only splits into 256-row shards per rank when the vocabulary is a multiple of 256*world: pad it the
+    # way Megatron / gpt-neox pad theirs (make_vocab_size_divisible_by)
+    vocab = 50304 if world == 1 else (50304 + 256 * world - 1) // (256 * world) * (256 * world)
+    sampler = ClockSampler(local) if rank == 0 else None
+    bracket = Bracket(args.warmup, args.steps, sampler)
+    tokens = batch * seq * world * args.steps
+    config = {"model": f"gpt-{model} (GPT-NeoX architecture: rotary, parallel residual, untied embeddings), vocab {vocab}",
+              "global_batch": batch * world, "micro_batch_per_gpu": batch, "seq_len": seq, "gradient_accumulation": 1,
+              "optimizer": "AdamW, gradient clipping 1.0", "parallelism": f"dp{world} ZeRO stage {args.zero_stage}",
+              "l2_policy": "16 distinct token batches; weights + activations of a step (tens of GB) >> 126 MB L2"}
+    if args.impl == "reference":
+        ms, info = bench_neox.run_reference(args, bracket, model, batch, seq, vocab)
+        if ms is None:
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": info}))
+            return
+        clocks = sampler.stop() if sampler is not None else None
+        if rank == 0:
+            v = tokens / (ms / 1e3)
+            print(json.dumps({"impl": "reference", "metric": "tokens/sec per trial", "value": v, "unit": "tokens/s",
+                              "samples_per_s": v / seq, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                              "warmup_requested": requested_warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                              "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+                              "harness": "reference determined 0.31.1-dev0 (baseline/_ref, unmodified) PyTorchTrial + torch DDP/NCCL + "
+                                         "AdamW(fused=True) on the stock-torch twin of the network: DeepSpeed is not installable "
+                                         "offline, so the reference's DeepSpeedTrial (ZeRO-3) itself cannot run on this box",
+                              "peak_mem_gb": info.get("peak_mem_gb"),
+                              "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": batch * (seq + 1) * 8, "d2h_bytes_per_step": 4},
+                              "clocks": clocks}))
+        return
+    ms, info = bench_neox.run_ours(args, bracket, model, batch, seq, vocab, args.zero_stage)
+    clocks = sampler.stop() if sampler is not None else None
+    if rank == 0:
+        v = tokens / (ms / 1e3)
+        print(json.dumps({"impl": "ours", "metric": "tokens/sec per trial", "value": v, "unit": "tokens/s", "samples_per_s": v / seq,
+                          "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "warmup_requested": requested_warmup,
+                          "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "bf16", "data": "synthetic", "config": config,
+                          "harness": f"determined_b200 DeepSpeedTrial + native ZeRO engine (stage {args.zero_stage}: {info['partitioned_weights']} "
+                                     f"weight matrices partitioned, gradients {'partitioned' if info['grad_partitioned'] else 'replicated'}, "
+                                     f"reduce-scatter {'overlapped with backward' if info['overlap'] else 'at step time'}, transport "
+                                     f"{info['transport']}); host-fed through pytorch.deepspeed.init + Trainer.fit: value == e2e",
+                          "model_tflops_per_gpu": v / world * info["flops_per_token"] / 1e12, "params": info["params"],
+                          "peak_mem_gb": info.get("peak_mem_gb"), "losses_first_last": [info["losses"][0], info["losses"][-1]],
+                          "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": batch * (seq + 1) * 8, "d2h_bytes_per_step": 4},
+                          "gpu_launches": info.get("zero_kernel_launches"), "clocks": clocks}))
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -303,6 +365,13 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graphs", action="store_true", help="ours: disable CUDA-graph replay of train_batch")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--config", default="cifar_resnet", choices=["cifar_resnet", "neox_zero3", "gpt2_medium_hf", "asha_pack"],
+                    help="BASELINE.json config: cifar_resnet = #2 (default, the headline), neox_zero3 = #4, gpt2_medium_hf = #3, "
+                         "asha_pack = #5")
+    ap.add_argument("--model", default=None, help="neox_zero3: neox-1.3b (default) | neox-2.7b | ...")
+    ap.add_argument("--micro-batch", type=int, default=4)
+    ap.add_argument("--seq", type=int, default=2048)
+    ap.add_argument("--zero-stage", type=int, default=3)
     args = ap.parse_args()
     rank, local, world = _dist_env()
     args.world = world
@@ -313,6 +382,16 @@ def main() -> None:
                os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
     requested_warmup = args.warmup
+    if args.config == "neox_zero3":
+        return main_neox(args, rank, local, world, requested_warmup)
+    if args.config == "gpt2_medium_hf":
+        from benchmarks import bench_hf
+
+        return bench_hf.main(args, rank, local, world, requested_warmup, ClockSampler, Bracket)
+    if args.config == "asha_pack":
+        from benchmarks import bench_asha
+
+        return bench_asha.main(args)
     args.warmup = max(args.warmup, 4)
     args.warmup += args.warmup % AGG_FREQ          # start the bracket on an aggregation boundary
     args.steps += args.steps % AGG_FREQ

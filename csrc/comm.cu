@@ -408,7 +408,8 @@ __global__ void __launch_bounds__(256) narrow_bf16_kernel(const float* __restric
 // -> write the updated weights (bf16 and/or fp32) into EVERY peer's parameter buffer.  The reduced
 // gradient shard never goes back to HBM.  With clipping enabled the caller runs it as two phases
 // (mode 1: reduce + sum-of-squares into `gshard`; mode 2: Adam from `gshard` + push weights).
-// mode 1 may *accumulate* into gshard (gradient accumulation over micro-batches with partitioned gradients: ZeRO-2).
+// mode 1 may *accumulate* into gshard (gradient accumulation over micro-batches with partitioned gradients: ZeRO-2);
+// mode 3 is mode 1 without statistics (the micro-batches before the last one of an accumulation window).
 // With kNvls the reduction is one multimem.ld_reduce per vector and the push one multimem.st.
 // ------------------------------------------------------------------------------------------
 struct ParamPeers {
@@ -432,8 +433,9 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, float* mc_grad, void* mc_param
   float sq = 0.f;
   int bad = 0;
   if (phases & 2) {
-    const bool do_reduce = (mode == 0 || mode == 1);
+    const bool do_reduce = (mode == 0 || mode == 1 || mode == 3);
     const bool do_update = (mode == 0 || mode == 2);
+    const bool to_shard = (mode == 1 || mode == 3);
     const bool skip = skip_p != nullptr && *skip_p != 0;
     const float lr = lr_p ? *lr_p : 0.f;
     const int step = step_p ? *step_p : 1;
@@ -468,7 +470,7 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, float* mc_grad, void* mc_param
             if (r < world) { g.x += vv[r].x; g.y += vv[r].y; g.z += vv[r].z; g.w += vv[r].w; }
         }
         g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
-        if (mode == 1) {
+        if (to_shard) {
           if (accumulate) {
             float4 o = reinterpret_cast<const float4*>(gshard)[li];
             g.x += o.x; g.y += o.y; g.z += o.z; g.w += o.w;
@@ -528,12 +530,12 @@ rs_adam_ag_kernel(Peers peers, ParamPeers ppeers, float* mc_grad, void* mc_param
     }
     float tot = block_sum(sq, red);
     int anybad = __syncthreads_or(bad);
-    if (threadIdx.x == 0 && do_reduce) {
+    if (threadIdx.x == 0 && do_reduce && mode != 3) {
       atomicAdd(&me->acc[0], tot);
       if (anybad) atomicAdd(&me->acc[1], 1.f);
     }
   }
-  comm_exit(peers, pt, epoch, phases, mode != 2, first_of_step, nullptr, &s_last);
+  comm_exit(peers, pt, epoch, phases, mode == 0 || mode == 1, first_of_step, nullptr, &s_last);
 }
 
 // Broadcast rank `root`'s buffer to all peers (parameter sync at start; reference
@@ -798,12 +800,15 @@ DETB200_API int detb200_rs_adam_ag_ex(void* const* peer_grad_bufs, void* const* 
   if (n_elems % (4 * world) != 0 || grad_offset_elems % 4 != 0 || param_offset_elems % 4 != 0) {
     detb200_set_error("rs_adam_ag: bucket length must be a multiple of 4*world floats"); return DETB200_ERR_BAD_ARG;
   }
-  if ((mode == 1 || mode == 2) && !grad_shard) { detb200_set_error("rs_adam_ag: two-phase mode needs grad_shard"); return DETB200_ERR_BAD_ARG; }
-  if (mode != 1 && !peer_param_bufs) { detb200_set_error("rs_adam_ag: parameter buffers required unless mode 1"); return DETB200_ERR_BAD_ARG; }
+  if ((mode == 1 || mode == 2 || mode == 3) && !grad_shard) { detb200_set_error("rs_adam_ag: two-phase mode needs grad_shard"); return DETB200_ERR_BAD_ARG; }
+  if (mode != 1 && mode != 3 && !peer_param_bufs) { detb200_set_error("rs_adam_ag: parameter buffers required unless mode 1/3"); return DETB200_ERR_BAD_ARG; }
+  if (mode < 0 || mode > 3) { detb200_set_error("rs_adam_ag: bad mode %d", mode); return DETB200_ERR_BAD_ARG; }
   if (n_elems == 0) return 0;
   long long cycles = (long long)(timeout_s * 1.9e9);
   int grid = comm_grid(n_elems / 4 / world, 2, max_ctas);
-  const bool nvls = mc_grad != nullptr && (mode == 1 || mc_param != nullptr) && world > 1;
+  // mode 2 reads no gradients over the wire: only the parameter mapping matters there
+  const bool nvls = world > 1 && ((mode == 2) ? mc_param != nullptr
+                                              : (mc_grad != nullptr && (mode == 1 || mode == 3 || mc_param != nullptr)));
 #define DETB200_RS_LAUNCH(LOWP, NVLS)                                                                                      \
   rs_adam_ag_kernel<LOWP, NVLS><<<grid, kCommThreads, 0, stream>>>(P, PP, (float*)mc_grad, mc_param, rank, world,          \
       grad_offset_elems, param_offset_elems, n_elems, master_shard, m_shard, v_shard, grad_shard, scale, lr, step,        \

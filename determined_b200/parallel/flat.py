@@ -58,7 +58,8 @@ class FlatLayout:
     per-rank float4 slices)."""
 
     def __init__(self, param_groups: Sequence[Dict[str, Any]], device: torch.device, align: int = 4,
-                 segment_align: int = 4, grad_alloc: Optional[Any] = None, param_alloc: Optional[Any] = None) -> None:
+                 segment_align: int = 4, grad_alloc: Optional[Any] = None, param_alloc: Optional[Any] = None,
+                 bind_grads: bool = True) -> None:
         self.device = device
         self.slots: List[Slot] = []
         self.segments: List[Segment] = []
@@ -80,13 +81,18 @@ class FlatLayout:
         self.total = max(off, segment_align)
         alloc = lambda n: torch.zeros(n, dtype=torch.float32, device=device)  # noqa: E731
         self.flat_param = (param_alloc or alloc)(self.total)
-        self.flat_grad = (grad_alloc or alloc)(self.total)
+        # bind_grads=False: no full-size gradient buffer at all (ZeRO-2/3: gradients live in a small landing ring and in
+        # the owner's shard); .grad stays None between backward passes
+        self.flat_grad = (grad_alloc or alloc)(self.total) if bind_grads else None
         self._by_param = {id(s.param): s for s in self.slots}
         with torch.no_grad():
             for s in self.slots:
                 view = _dense_view(self.flat_param, s.offset, s.param.data)
                 view.copy_(s.param.data)
                 s.param.data = view
+                if not bind_grads:
+                    s.param.grad = None
+                    continue
                 gview = _dense_view(self.flat_grad, s.offset, s.param.data)
                 if s.param.grad is not None:
                     gview.copy_(s.param.grad)
@@ -107,6 +113,8 @@ class FlatLayout:
                 if s.param.data.data_ptr() != want.data_ptr():
                     want.copy_(s.param.data)
                     s.param.data = want
+                if self.flat_grad is None:
+                    continue
                 gwant = _dense_view(self.flat_grad, s.offset, s.param.data)
                 if s.param.grad is None:
                     s.param.grad = gwant

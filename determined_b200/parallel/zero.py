@@ -47,6 +47,13 @@ from determined_b200.parallel.flat import FlatLayout
 logger = logging.getLogger("determined.parallel.zero")
 
 
+def _use_nvls(world: int) -> bool:
+    """Transport of the ZeRO collectives: in-switch reduction + multicast parameter push from four ranks on (the push is
+    where it pays most: a rank sends its updated shard once instead of world-1 times)."""
+    env = os.environ.get("DETB200_NVLS_MIN_WORLD")
+    return world >= (int(env) if env else 4)
+
+
 def _load_config(config: Union[str, os.PathLike, Dict[str, Any], None]) -> Dict[str, Any]:
     if config is None:
         return {}
@@ -172,56 +179,245 @@ class ZeroEngine:
         logger.info("ZeRO-3: partitioned %d weight matrices over %d ranks", self.partitioned, self.world)
 
     def _setup_native(self) -> None:
+        """Buffers of the native path (see the module docstring for the memory plan per stage)."""
         from determined_b200.ops import _lib, comm, optim
 
         _lib.load()
         world = self.world
         align = 4 * world
         self._bufs: Dict[str, Any] = {}
-
-        def symm(name: str):
-            def alloc(n: int) -> torch.Tensor:
-                b = comm.SymmetricBuffer(4 * n, self.device)
-                self._bufs[name] = b
-                return b.tensor(torch.float32, n)
-            return alloc
+        zo = self.config.get("zero_optimization") or {}
+        zo = zo if isinstance(zo, dict) else {}
+        # stage >= 2 partitions the gradients: no full-size gradient buffer, a ring of landing slots instead
+        self._grad_partitioned = self._stage >= 2 and world > 1 and bool(zo.get("partition_gradients", True))
+        self._ring_slots = int(zo.get("landing_slots", 2))
+        self._max_ctas = zo.get("comm_ctas")
 
         with torch.cuda.device(self.device):
-            self.layout = FlatLayout([{"params": self._replicated}], self.device, align=align, segment_align=align,
-                                     grad_alloc=symm("grad"), param_alloc=symm("param"))
             if getattr(self, "group", None) is None:
                 self.group = comm.PeerGroup.from_torch_distributed(self.device)
+
+            def symm(name: str):
+                def alloc(n: int) -> torch.Tensor:
+                    b = self.group.alloc(4 * n)
+                    self._bufs[name] = b
+                    return b.tensor(torch.float32, n)
+                return alloc
+
+            self.layout = FlatLayout([{"params": self._replicated}], self.device, align=align, segment_align=align,
+                                     grad_alloc=symm("grad"), param_alloc=symm("param"), bind_grads=not self._grad_partitioned)
             self.shard_layout: Optional[FlatLayout] = None
             if self._sharded:
                 self.shard_layout = FlatLayout([{"params": self._sharded}], self.device, align=4, segment_align=4)
                 self.shard_m = torch.zeros(self.shard_layout.total, dtype=torch.float32, device=self.device)
                 self.shard_v = torch.zeros(self.shard_layout.total, dtype=torch.float32, device=self.device)
                 self._norm_scratch = optim.NormScratch(self.device) if self._clip > 0 else None
-            self.peer_grads = self.group.map(self._bufs["grad"])
-            self.peer_params = self.group.map(self._bufs["param"])
             total = self.layout.total
-            cap = max(min(self._bucket_elems, total) // align * align, align)
-            self.buckets: List[Tuple[int, int]] = []
-            off = 0
-            while off < total:
-                n = min(cap, total - off)
-                self.buckets.append((off, n))
-                off += n
-            shard_total = sum(n // world for _, n in self.buckets)
+            # buckets in reverse parameter order (bucket 0 = last layers = first gradients), cut at parameter boundaries
+            cap_elems = max(min(self._bucket_elems, 1 << 26), align)
+            self._zbuckets = self.layout.make_buckets(4 * cap_elems, align)
+            self.buckets: List[Tuple[int, int]] = [(b.offset, b.numel) for b in self._zbuckets]
+            self._soff: List[int] = []
+            soff = 0
+            for _, n in self.buckets:
+                self._soff.append(soff)
+                soff += n // world
+            shard_total = soff
+            self.peer_params = self.group.map(self._bufs["param"])
+            self.mc_param = self.group.multicast(self._bufs["param"]) if world > 1 else None
+            if self._grad_partitioned:
+                self._slot_elems = max(n for _, n in self.buckets)
+                self._bufs["land"] = self.group.alloc(4 * self._slot_elems * self._ring_slots)
+                self.landing = self._bufs["land"].tensor(torch.float32, self._slot_elems * self._ring_slots)
+                self.peer_grads = self.group.map(self._bufs["land"])
+                self.mc_grad = self.group.multicast(self._bufs["land"])
+            else:
+                self.peer_grads = self.group.map(self._bufs["grad"])
+                self.mc_grad = self.group.multicast(self._bufs["grad"]) if world > 1 else None
+            if not _use_nvls(world):
+                self.mc_grad = self.mc_param = None
             self.m = torch.zeros(shard_total, dtype=torch.float32, device=self.device)
             self.v = torch.zeros(shard_total, dtype=torch.float32, device=self.device)
-            self.gshard = torch.zeros(shard_total, dtype=torch.float32, device=self.device) if self._clip > 0 else None
+            # the reduced gradient shard: its own buffer when gradients are partitioned; with replicated gradients the
+            # owner's slice of the gradient buffer itself (only the owner ever reads that slice) takes the result in place
+            self.gshard = torch.zeros(shard_total, dtype=torch.float32, device=self.device) if self._grad_partitioned else None
             self.lr_dev = torch.full((), self._hp["lr"], dtype=torch.float32, device=self.device)
             self.step_dev = torch.zeros((), dtype=torch.int32, device=self.device)
             self.coef = torch.ones(1, dtype=torch.float32, device=self.device)
             self.norm = torch.zeros(1, dtype=torch.float32, device=self.device)
             self._lr_host = self._hp["lr"]
-            self.comm_stream = torch.cuda.Stream(device=self.device)
+            _, hi = torch.cuda.Stream.priority_range()
+            self.comm_stream = torch.cuda.Stream(device=self.device, priority=hi)
+            if self._sharded and world > 1 and self._clip > 0:
+                # every rank's weight-shard gradient norm reaches every rank through one tiny in-kernel all-reduce
+                self._bufs["nx"] = self.group.alloc(4 * 4 * world)
+                self._nx = self._bufs["nx"].tensor(torch.float32, 4 * world)
+                self._nx_peers = self.group.map(self._bufs["nx"])
         if world > 1:
             # identical starting weights everywhere (DeepSpeed broadcasts from rank 0 too)
             comm.broadcast(self.group, self.peer_params, 0, self.layout.total, root=0)
             torch.cuda.synchronize()
         self.kernel_launches = 0
+        # --- overlap of the reduce-scatter with backward: gradient hooks count bucket readiness
+        seen: Dict[int, int] = {}
+        for mod in self.module.modules():
+            for p in mod._parameters.values():
+                if p is not None:
+                    seen[id(p)] = seen.get(id(p), 0) + 1
+        tied = any(seen.get(id(p), 0) > 1 for p in self._replicated)
+        self._overlap = world > 1 and bool(zo.get("overlap_comm", True)) and (not tied or self._grad_partitioned)
+        if tied and self._overlap:
+            raise ValueError("ZeRO stage >= 2 on the native path needs untied parameters (a tied weight receives its gradient "
+                             "in two pieces far apart in backward); untie them or set zero_optimization.partition_gradients=false")
+        self._bucket_of: Dict[int, int] = {}
+        for bi, b in enumerate(self._zbuckets):
+            for sl in b.owned:
+                self._bucket_of[id(sl.param)] = bi
+        self._slot_of_param = {id(sl.param): sl for sl in self.layout.slots}
+        self._hooks: List[Any] = []
+        if self._overlap or self._grad_partitioned:
+            for sl in self.layout.slots:
+                self._hooks.append(sl.param.register_post_accumulate_grad_hook(self._grad_hook))
+        self._arm_micro_step()
+        self._first_kernel_of_step = True
+        self._comm_this_pass = False
+        self._boundary_pass = False
+        self._micro_in_window = 0
+        self._ticked = False
+        logger.info("ZeRO stage %d native path: %d replicated-path params in %d buckets (%s gradients, %s, %s), %d partitioned weights",
+                    self._stage, len(self._replicated), len(self.buckets),
+                    "partitioned: landing ring of %d x %.0f MB" % (self._ring_slots, 4 * self._slot_elems / 2**20) if self._grad_partitioned else "replicated",
+                    "reduce-scatter overlapped with backward" if self._overlap else "reduce-scatter at step time",
+                    "NVLS" if self.mc_param else "peer-to-peer", len(self._sharded))
+
+    # ------------------------------------------------------------------ gradient hooks (native path)
+    def _arm_micro_step(self) -> None:
+        nb = len(self.buckets)
+        self._fired: List[set] = [set() for _ in range(nb)]
+        self._launched = [False] * nb
+        self._next_bucket = 0
+        self._deferred: List[List[Any]] = [[] for _ in range(nb)]
+        self._slot_owner: List[Optional[int]] = [None] * max(1, getattr(self, "_ring_slots", 1))
+        if not hasattr(self, "_slot_free"):
+            self._slot_free: List[Optional[torch.cuda.Event]] = [None] * max(1, getattr(self, "_ring_slots", 1))
+
+    def _landing_view(self, bi: int, sl: Any) -> torch.Tensor:
+        off, _ = self.buckets[bi]
+        base = (bi % self._ring_slots) * self._slot_elems + (sl.offset - off)
+        return self.landing[base: base + sl.numel]
+
+    def _claim_slot(self, bi: int) -> bool:
+        """Make bucket ``bi`` the owner of its landing slot if the slot is free (the compute stream then waits for the
+        reduce-scatter that last read it)."""
+        slot = bi % self._ring_slots
+        if self._slot_owner[slot] == bi:
+            return True
+        if self._slot_owner[slot] is not None:
+            return False
+        self._slot_owner[slot] = bi
+        ev = self._slot_free[slot]
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
+        return True
+
+    def _land(self, bi: int, p: torch.nn.Parameter) -> None:
+        sl = self._slot_of_param[id(p)]
+        self._landing_view(bi, sl).copy_(p.grad.reshape(-1))
+        p.grad = None
+        self._fired[bi].add(id(p))
+
+    def _grad_hook(self, p: torch.nn.Parameter) -> None:
+        bi = self._bucket_of.get(id(p))
+        if bi is None:
+            return
+        if self._grad_partitioned:
+            if self._launched[bi]:
+                raise RuntimeError("a parameter received a second gradient after its bucket was reduce-scattered in this "
+                                   "micro-batch; ZeRO stage >= 2 needs one gradient per parameter per backward pass")
+            if self._claim_slot(bi):
+                self._land(bi, p)
+            else:
+                self._deferred[bi].append(p)       # its slot still holds an earlier bucket: keep .grad until it is free
+                return
+        else:
+            if not self._comm_this_pass:
+                return
+            self._fired[bi].add(id(p))
+        if self._overlap:
+            self._launch_ready()
+
+    def _bucket_complete(self, bi: int) -> bool:
+        return len(self._fired[bi]) == len(self._zbuckets[bi].owned)
+
+    def _launch_ready(self) -> None:
+        """Launch, strictly in bucket order (every rank issues the same sequence of collectives), whatever is complete."""
+        progressed = True
+        while progressed and self._next_bucket < len(self.buckets):
+            progressed = False
+            bi = self._next_bucket
+            if self._grad_partitioned and self._deferred[bi] and self._claim_slot(bi):
+                for p in self._deferred[bi]:
+                    self._land(bi, p)
+                self._deferred[bi] = []
+            if self._bucket_complete(bi) and (not self._grad_partitioned or self._slot_owner[bi % self._ring_slots] == bi):
+                self._launch_bucket(bi)
+                self._next_bucket += 1
+                progressed = True
+
+    def _rs_mode_in_backward(self) -> int:
+        if self._grad_partitioned:
+            return 1 if self._boundary_pass else 3
+        return 1 if self._clip > 0 else 0
+
+    def _launch_bucket(self, bi: int) -> None:
+        """Reduce-scatter of bucket ``bi`` on the communication stream (mode 1/3: into the owner's gradient shard; mode 0:
+        fused with AdamW and the parameter push)."""
+        from determined_b200.ops import _lib
+
+        lib = _lib.load()
+        cur = torch.cuda.current_stream(self.device)
+        mode = self._rs_mode_in_backward()
+        if mode == 0 and self._first_kernel_of_step:
+            self._sync_lr()                 # (a fill on the compute stream: before the event the other stream waits for)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.comm_stream.wait_event(ev)
+        if mode == 0 and self._first_kernel_of_step:
+            with torch.cuda.stream(self.comm_stream):
+                _lib.check(lib.detb200_optim_tick(self.step_dev.data_ptr(), None, _lib.stream_ptr(self.comm_stream)), "tick")
+            self._ticked = True
+        off, n = self.buckets[bi]
+        goff = (bi % self._ring_slots) * self._slot_elems if self._grad_partitioned else off
+        accumulate = 1 if (self._grad_partitioned and self._micro_in_window > 0) else 0
+        first = 1 if (self._first_kernel_of_step and mode != 3) else 0
+        self._rs_call(bi, mode, goff, off, n, accumulate, first, None, self.comm_stream)
+        if mode != 3:
+            self._first_kernel_of_step = False
+        self._launched[bi] = True
+        if self._grad_partitioned:
+            slot = bi % self._ring_slots
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+            self._slot_free[slot] = done
+            self._slot_owner[slot] = None
+
+    def _rs_call(self, bi: int, mode: int, goff: int, poff: int, n: int, accumulate: int, first: int, grad_scale_ptr: Any,
+                 stream: torch.cuda.Stream) -> None:
+        from determined_b200.ops import _lib
+
+        lib = _lib.load()
+        world, rank, hp = self.world, self.rank, self._hp
+        shard = n // world
+        so = self._soff[bi]
+        _lib.check(lib.detb200_rs_adam_ag_ex(
+            self.peer_grads, self.group.ctrl_ptrs, self.peer_params, self.mc_grad, self.mc_param, 0, rank, world, goff, poff, n,
+            self.layout.flat_param.data_ptr() + 4 * (poff + rank * shard),
+            self.m.data_ptr() + 4 * so, self.v.data_ptr() + 4 * so,
+            (self.gshard.data_ptr() + 4 * so) if self.gshard is not None else (self.layout.flat_grad.data_ptr() + 4 * (poff + rank * shard)),
+            1.0 / world, self.lr_dev.data_ptr(), self.step_dev.data_ptr(), grad_scale_ptr, None,
+            float(hp["betas"][0]), float(hp["betas"][1]), float(hp["eps"]), float(hp["weight_decay"]),
+            mode, accumulate, first, 7 if world > 1 else 2, int(self._max_ctas or 0), 120.0, _lib.stream_ptr(stream)), "rs_adam_ag")
+        self.kernel_launches += 1
 
     def _setup_fallback(self) -> None:
         self.shard_layout = None
@@ -331,8 +527,40 @@ class ZeroEngine:
 
     def backward(self, loss: torch.Tensor, **kw: Any) -> torch.Tensor:
         scaled = loss / self._ga if self._ga > 1 else loss
+        if self._native:
+            self._boundary_pass = self.is_gradient_accumulation_boundary()
+            self._micro_in_window = self.micro_steps % self._ga
+            # replicated gradients: only the last micro-batch of the window communicates (the others accumulate locally);
+            # partitioned gradients: every micro-batch is reduce-scattered into the owner's shard
+            self._comm_this_pass = self._boundary_pass
+            if self._grad_partitioned:
+                self._arm_micro_step()
         scaled.backward()
+        if self._native and self._grad_partitioned:
+            self._drain()
         return loss
+
+    def _drain(self) -> None:
+        """Reduce-scatter whatever the hooks could not launch: buckets whose parameters got no gradient in this pass
+        (their landing region is zero-filled) and buckets that were waiting for a slot."""
+        nb = len(self.buckets)
+        while self._next_bucket < nb:
+            bi = self._next_bucket
+            if self._grad_partitioned:
+                if not self._claim_slot(bi):
+                    raise RuntimeError("landing slot still owned by an earlier bucket while draining")     # cannot happen in order
+                for p in self._deferred[bi]:
+                    self._land(bi, p)
+                self._deferred[bi] = []
+                for sl in self._zbuckets[bi].owned:
+                    if id(sl.param) not in self._fired[bi]:
+                        if sl.param.grad is not None:
+                            self._land(bi, sl.param)
+                        else:
+                            self._landing_view(bi, sl).zero_()
+                            self._fired[bi].add(id(sl.param))
+            self._launch_bucket(bi)
+            self._next_bucket += 1
 
     # ------------------------------------------------------------------ step
     def _sync_lr(self) -> None:
@@ -382,36 +610,28 @@ class ZeroEngine:
         self._torch_opt.zero_grad(set_to_none=False)
 
     def _native_step(self) -> None:
-        from determined_b200.ops import _lib, comm, optim
+        from determined_b200.ops import _lib, optim
 
         lib = _lib.load()
         self._sync_lr()
-        cur = torch.cuda.current_stream(self.device)
-        self.comm_stream.wait_stream(cur)
-        st = self.comm_stream
-        sp = _lib.stream_ptr(st)
-        world, rank = self.world, self.rank
+        world = self.world
         hp = self._hp
-        scale = 1.0 / world
+        cur = torch.cuda.current_stream(self.device)
+        # whatever the hooks did not launch during backward
+        if not self._grad_partitioned:
+            if not getattr(self, "_boundary_pass", False):
+                # step() without a backward through the engine (gradients were filled some other way)
+                self._first_kernel_of_step = True
+            while self._next_bucket < len(self.buckets):
+                self._launch_bucket(self._next_bucket)
+                self._next_bucket += 1
+        st = self.comm_stream
+        st.wait_stream(cur)
+        sp = _lib.stream_ptr(st)
         with torch.cuda.stream(st):
-            _lib.check(lib.detb200_optim_tick(self.step_dev.data_ptr(), None, sp), "tick")
-            self.group.begin_step()
-
-            def run(mode: int, grad_scale_ptr: Any) -> None:
-                soff = 0
-                for bi, (off, n) in enumerate(self.buckets):
-                    shard = n // world
-                    first = 1 if (bi == 0 and mode != 2) else 0
-                    _lib.check(lib.detb200_rs_adam_ag(
-                        self.peer_grads, self.group.ctrl_ptrs, self.peer_params, 0, rank, world, off, n,
-                        self.layout.flat_param.data_ptr() + 4 * (off + rank * shard),
-                        self.m.data_ptr() + 4 * soff, self.v.data_ptr() + 4 * soff,
-                        (self.gshard.data_ptr() + 4 * soff) if self.gshard is not None else None,
-                        scale, self.lr_dev.data_ptr(), self.step_dev.data_ptr(), grad_scale_ptr, None,
-                        float(hp["betas"][0]), float(hp["betas"][1]), float(hp["eps"]), float(hp["weight_decay"]),
-                        mode, first, 7 if world > 1 else 2, 120.0, sp), "rs_adam_ag")
-                    self.kernel_launches += 1
-                    soff += shard
+            if not getattr(self, "_ticked", False):
+                _lib.check(lib.detb200_optim_tick(self.step_dev.data_ptr(), None, sp), "tick")
+            self._ticked = False
 
             def shard_update(grad_scale_ptr: Any) -> None:
                 # partitioned weights: their gradient shards are already reduced (wgrad GEMM epilogue), so the update is local
@@ -422,26 +642,40 @@ class ZeroEngine:
                                                  float(hp["weight_decay"]), 1, 1.0, 1, 0, sp), "adam_flat")
                 self.kernel_launches += 1
 
+            second_phase = self._clip > 0 or self._grad_partitioned
+            gs_ptr = None
             if self._clip > 0:
-                run(1, None)
                 terms = self.group.stats_tensor()[0, :world]
                 if self.shard_layout is not None:
                     # global norm = replicated part (per-rank slices, exchanged by the kernel) + every rank's weight shards
                     mine = optim.sumsq(self.shard_layout.flat_grad, self._norm_scratch)
                     if world > 1:
-                        dist.all_reduce(mine)
-                    terms = torch.cat([terms, mine])
+                        from determined_b200.ops import comm
+
+                        self._nx.zero_()
+                        self._nx[self.rank:self.rank + 1].copy_(mine)
+                        saved_first = self.group._first_of_step
+                        # statistics of this helper collective must not disturb the step's table: read the table first
+                        terms = terms.clone()
+                        comm.allreduce_fused(self.group, self._nx_peers, 0, 4 * world, 1.0, stream=st, timeout_s=120.0)
+                        self.group._first_of_step = saved_first
+                        terms = torch.cat([terms, self._nx[:world]])
+                    else:
+                        terms = torch.cat([terms, mine])
                 _lib.check(lib.detb200_clip_coef(terms.data_ptr(), terms.numel(), self._clip, 1.0, self.coef.data_ptr(), self.norm.data_ptr(), sp), "clip")
-                run(2, self.coef.data_ptr())
-                if self.shard_layout is not None:
-                    shard_update(self.coef.data_ptr())
-            else:
-                run(0, None)
-                if self.shard_layout is not None:
-                    shard_update(None)
-            # every peer finished reading our gradients (end barrier of the last bucket): clear them
-            self.layout.flat_grad.zero_()
+                gs_ptr = self.coef.data_ptr()
+            if second_phase:
+                for bi, (off, n) in enumerate(self.buckets):
+                    self._rs_call(bi, 2, off, off, n, 0, 0, gs_ptr, st)
+            if self.shard_layout is not None:
+                shard_update(gs_ptr)
+            if not self._grad_partitioned:
+                # every peer finished reading our gradients (end barrier of the last bucket): clear them
+                self.layout.flat_grad.zero_()
         cur.wait_stream(st)
+        self._arm_micro_step()
+        self._first_kernel_of_step = True
+        self._boundary_pass = False
 
     def get_global_grad_norm(self) -> Optional[float]:
         if self._native and self._clip > 0:
@@ -453,7 +687,8 @@ class ZeroEngine:
 
     def zero_grad(self, set_to_none: bool = False) -> None:
         if self._native:
-            self.layout.flat_grad.zero_()
+            if self.layout.flat_grad is not None:
+                self.layout.flat_grad.zero_()
         else:
             self._torch_opt.zero_grad(set_to_none=False)
 

@@ -19,6 +19,7 @@ class PyTorchExperimentalContext:
         self._fused_engine: Optional[bool] = None     # None = auto (on when CUDA + native lib)
         self._cuda_graphs = False
         self._bucket_cap_mb = 25.0
+        self._grad_overlap: Optional[bool] = None
         self._wire_dtype: Optional[torch.dtype] = None
         self._async_checkpoint = False
 
@@ -44,7 +45,7 @@ class PyTorchExperimentalContext:
 
     # ---- B200 engine -------------------------------------------------------------------------
     def use_fused_engine(self, enabled: bool = True, bucket_cap_mb: float = 25.0,
-                         wire_dtype: Optional[torch.dtype] = None) -> None:
+                         wire_dtype: Optional[torch.dtype] = None, overlap: Optional[bool] = None) -> None:
         """Force the flat-bucket engine on/off.  On: gradients live in one symmetric flat buffer,
         the bucketed all-reduce is our P2P kernel fused with averaging / unscale / inf-check /
         norm partials, and ``torch.optim.{SGD,Adam,AdamW,Adadelta}`` steps run as one fused
@@ -53,6 +54,8 @@ class PyTorchExperimentalContext:
         self._fused_engine = enabled
         self._bucket_cap_mb = bucket_cap_mb
         self._wire_dtype = wire_dtype
+        # True: bucketed all-reduces overlapped with backward; False: one all-reduce at step time; None: by gradient volume
+        self._grad_overlap = overlap
 
     def enable_async_checkpoint(self, enabled: bool = True) -> None:
         """Checkpoint fast path: at a checkpoint boundary the chief snapshots models / optimizers / schedulers into pinned host

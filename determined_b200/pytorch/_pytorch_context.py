@@ -175,7 +175,8 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
     def _get_engine(self) -> ddp.GradEngineBase:
         if self._engine is None:
             self._engine = ddp.make_engine(self.distributed, self.device, self._aggregation_frequency,
-                                           self.experimental._fused_engine, self.experimental._bucket_cap_mb)
+                                           self.experimental._fused_engine, self.experimental._bucket_cap_mb,
+                                           overlap=self.experimental._grad_overlap)
         return self._engine
 
     def _check_pre_wrap(self, what: str) -> None:
@@ -242,7 +243,7 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
         if backward_passes_per_step < 1:
             raise errors.InvalidExperimentException("backward_passes_per_step for local gradient aggregation must be >= 1")
         if fp16_compression is None:
-            fp16_compression = self._fp16_compression_default
+            fp16_compression = self._fp16_compression_default or self.experimental._wire_dtype in (torch.bfloat16, torch.float16)
         if average_aggregated_gradients is None:
             average_aggregated_gradients = self._average_aggregated_gradients_default
         model_params = {id(p) for m in self.models for p in m.parameters()}

@@ -6,9 +6,10 @@ through ``checkpoint.download`` ``:158-180``; searcher progress/completion ``:18
 preemption → ``control.should_save`` ``:97-103``; searcher/TrainingArguments compatibility checks
 ``:267-317``.
 
-HF's own DDP wrapper does the gradient exchange inside ``Trainer``; to route it through this
-repository's fused all-reduce instead, pass ``ddp_comm_hook=determined_b200.parallel.comm_hook``
-style integration via ``determined_b200.parallel.ddp.install_hf_comm_hook(trainer)`` (optional).
+HF's own DDP wrapper does the gradient exchange inside ``Trainer``; ``determined_b200.parallel.ddp.install_hf_comm_hook(trainer)``
+adds a callback that registers a DDP communication hook on the wrapped model, so that every gradient bucket goes through
+this repository's fused all-reduce instead of NCCL (``FusedAllReduceHook``; any ``DistributedDataParallel`` module can use it
+directly through ``install_comm_hook(ddp_model)``).
 """
 import logging
 import os

@@ -25,7 +25,7 @@ def _ngpu() -> int:
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("which", ["allreduce", "allreduce_nvls", "engine", "gan", "amp", "resnet", "gemm_comm", "gpt_tp", "zero3", "zero3_engine"])
+@pytest.mark.parametrize("which", ["allreduce", "allreduce_nvls", "engine", "gan", "amp", "ddp_hook", "resnet", "gemm_comm", "gpt_tp", "zero3", "zero3_engine"])
 def test_two_ranks(which):
     _run(which, 2)
 
