@@ -173,7 +173,8 @@ def run_reference(args, bracket, model_name: str, batch: int, seq: int, vocab: i
             src = TokenPool(vocab, batch, seq, seed=99)
             return torch.utils.data.DataLoader(src.batches[:2], batch_size=None, shuffle=False)
 
-        def train_batch(self, batch_: Any, epoch_idx: int, batch_idx: int) -> Dict[str, Any]:
+        def train_batch(self, batch: Any, epoch_idx: int, batch_idx: int) -> Dict[str, Any]:
+            batch_ = batch
             if batch_idx == bracket.first:
                 torch.cuda.reset_peak_memory_stats()
                 bracket.begin()
@@ -187,9 +188,9 @@ def run_reference(args, bracket, model_name: str, batch: int, seq: int, vocab: i
             self.context.step_optimizer(self.opt, clip_grads=lambda ps: torch.nn.utils.clip_grad_norm_(ps, 1.0))
             return {"lm_loss": loss}
 
-        def evaluate_batch(self, batch_: Any, batch_idx: int) -> Dict[str, Any]:
+        def evaluate_batch(self, batch: Any, batch_idx: int) -> Dict[str, Any]:
             with torch.autocast("cuda", dtype=torch.bfloat16):
-                _, loss = self.model(batch_[:, :-1], batch_[:, 1:])
+                _, loss = self.model(batch[:, :-1], batch[:, 1:])
             return {"lm_loss": loss}
 
     total = args.warmup + args.steps + 1

@@ -12,6 +12,7 @@ from determined_b200.errors import InvalidHP
 from determined_b200._experiment_config import ExperimentConfig
 from determined_b200._import import import_from_path
 from determined_b200._trial_context import EnvContext, LegacyTrial, TrialContext, TrialController
+from determined_b200._trial_controller import _DistributedBackend
 from determined_b200 import constants, errors, util, gpu, core
 
 LOG_FORMAT = "%(levelname)s: [%(process)s] %(name)s: %(message)s"

@@ -58,10 +58,12 @@ def validate_manager(manager: StorageManager) -> None:
     sid = str(uuid.uuid4())
     with manager.store_path(sid) as p:
         p.mkdir(parents=True, exist_ok=True)
-        (p / "VALIDATE.txt").write_text(sid)
+        with (p / "VALIDATE.txt").open("w") as f:
+            f.write(sid)
     with manager.restore_path(sid) as p:
-        if (p / "VALIDATE.txt").read_text() != sid:
-            raise ValueError("Unable to properly load from storage")
+        with (p / "VALIDATE.txt").open("r") as f:
+            if f.read() != sid:
+                raise ValueError("Unable to properly load from storage")
     manager.delete(sid, ["**/*"])
 
 

@@ -53,11 +53,16 @@ def _glob_to_regex(glob: str) -> "re.Pattern[str]":
     i, n, out = 0, len(glob), []
     while i < n:
         c = glob[i]
-        if glob.startswith("**/", i):
+        # ``**`` is recursive only as a whole path component (glob.glob's rule): ``**.txt`` is just ``*.txt``
+        at_component_start = i == 0 or glob[i - 1] == "/"
+        if at_component_start and glob.startswith("**/", i):
             out.append("(?:[^/]+/)*")
             i += 3
-        elif glob.startswith("**", i):
+        elif at_component_start and glob.startswith("**", i) and i + 2 == n:
             out.append(".*")
+            i += 2
+        elif glob.startswith("**", i):
+            out.append("[^/]*")
             i += 2
         elif c == "*":
             out.append("[^/]*")

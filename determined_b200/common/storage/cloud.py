@@ -188,6 +188,8 @@ class AzureStorageManager(CloudStorageManager):
     def upload(self, src: Union[str, os.PathLike], dst: str, paths: Optional[base.Paths] = None) -> None:
         for rel in self._iter_upload(src, paths):
             if rel.endswith("/"):
+                # blob stores have no directories: an empty blob whose name ends in "/" marks one (reference azure.py:50-54)
+                self._c().upload_blob(f"{dst}/{rel}", b"", overwrite=True)
                 continue
             with open(os.path.join(os.fspath(src), rel), "rb") as f:
                 self._c().upload_blob(f"{dst}/{rel}", f, overwrite=True)
@@ -201,6 +203,9 @@ class AzureStorageManager(CloudStorageManager):
             if not rel or (selector is not None and not selector(rel)):
                 continue
             target = os.path.join(os.fspath(dst), rel)
+            if rel.endswith("/"):
+                os.makedirs(target, exist_ok=True)
+                continue
             os.makedirs(os.path.dirname(target), exist_ok=True)
             with open(target, "wb") as f:
                 self._c().download_blob(b["name"]).readinto(f)

@@ -13,6 +13,7 @@ import shutil
 from typing import Any, Dict, Iterator, List, Optional, Union
 
 from determined_b200 import errors
+from determined_b200.common import check
 from determined_b200 import util
 from determined_b200.common.storage import base
 
@@ -21,52 +22,66 @@ logger = logging.getLogger("determined.storage")
 
 def copytree(src: str, dst: str, selector: Optional[base.Selector] = None,
              paths: Optional[base.Paths] = None) -> None:
-    """Selector/paths-aware recursive copy.  ``paths`` contains relative names (dirs end in ``/``);
-    a selected directory is created even if none of its children are selected."""
+    """Copy the tree under ``src`` into ``dst``, optionally only what ``selector`` / ``paths`` pick.
+
+    Relative names are what both see: files as ``sub/file``, directories as ``sub/``.  Every directory is visited
+    whatever the selection says; a directory that is itself selected is created even when empty; a selected file brings
+    its parent directories with it; nothing selected means ``dst`` is not created at all.  Symbolic links are followed, so
+    a linked directory arrives as a real directory with its contents (the behaviour of the reference's
+    ``common/storage/shared.py:copytree``, which its storage conformance tests pin down)."""
     src = os.fspath(src)
-    os.makedirs(dst, exist_ok=True)
-    for cur, dirs, files in os.walk(src):
+    dst = os.fspath(dst)
+
+    def wanted(rel: str) -> bool:
+        if paths is not None and rel not in paths:
+            return False
+        return selector is None or bool(selector(rel))
+
+    unselected = selector is None and paths is None
+    if unselected:
+        os.makedirs(dst, exist_ok=True)
+    touched = []          # (source dir, destination dir) of every directory that now exists under dst
+    for cur, dirs, files in os.walk(src, followlinks=True):
         rel_cur = os.path.relpath(cur, src)
-        rel_cur = "" if rel_cur == "." else rel_cur + "/"
-        keep_dirs = []
-        for d in dirs:
-            rel = rel_cur + d + "/"
-            if paths is not None and rel not in paths:
-                # still descend if any selected path lives below
-                if not any(p.startswith(rel) for p in paths):
-                    continue
-            if selector is not None and not selector(rel):
+        prefix = "" if rel_cur == "." else rel_cur.replace(os.sep, "/") + "/"
+        here = dst if rel_cur == "." else os.path.join(dst, rel_cur)
+        for d in sorted(dirs):
+            if wanted(prefix + d + "/"):
+                os.makedirs(os.path.join(here, d), exist_ok=True)
+                touched.append((os.path.join(cur, d), os.path.join(here, d)))
+        for f in sorted(files):
+            if not wanted(prefix + f):
                 continue
-            keep_dirs.append(d)
-            os.makedirs(os.path.join(dst, rel), exist_ok=True)
-        dirs[:] = keep_dirs
-        for f in files:
-            rel = rel_cur + f
-            if paths is not None and rel not in paths:
-                continue
-            if selector is not None and not selector(rel):
-                continue
-            s, t = os.path.join(cur, f), os.path.join(dst, rel)
-            os.makedirs(os.path.dirname(t), exist_ok=True)
-            if os.path.islink(s):
-                if os.path.lexists(t):
-                    os.unlink(t)
-                os.symlink(os.readlink(s), t)
-            else:
-                shutil.copy2(s, t)
+            if not os.path.isdir(here):
+                os.makedirs(here, exist_ok=True)
+                touched.append((cur, here))
+            shutil.copy2(os.path.join(cur, f), os.path.join(here, f))
+    for s_dir, d_dir in reversed(touched):
+        with contextlib.suppress(OSError):
+            shutil.copystat(s_dir, d_dir)
 
 
 def full_storage_path(host_path: str, storage_path: Optional[str] = None,
                       container_path: Optional[str] = None) -> str:
+    """Where checkpoints live as seen by this process (reference ``common/storage/shared.py:_full_storage_path``):
+    ``storage_path`` may be relative to ``host_path`` or an absolute path below it; with ``container_path`` the result is
+    re-rooted there (the reference's containers bind ``host_path`` at ``container_path``)."""
     if not os.path.isabs(host_path):
-        raise ValueError("`host_path` must be an absolute path.")
+        raise _PathError("`host_path` must be an absolute path.")
     root = host_path if container_path is None else container_path
     if storage_path is None:
         return root
     ab = os.path.normpath(os.path.join(host_path, storage_path))
     if not (ab == host_path or ab.startswith(host_path.rstrip("/") + "/")):
-        raise ValueError("storage path must be a subdirectory of host path.")
+        raise _PathError("storage path must be a subdirectory of host path.")
     return os.path.join(root, os.path.relpath(ab, host_path))
+
+
+class _PathError(check.CheckFailedError, ValueError):
+    """Both what the reference raises (``check.CheckFailedError``) and what a Python caller expects (``ValueError``)."""
+
+
+_full_storage_path = full_storage_path      # the reference's (private) name, which its own tests import
 
 
 class SharedFSStorageManager(base.StorageManager):
@@ -99,6 +114,8 @@ class SharedFSStorageManager(base.StorageManager):
     @contextlib.contextmanager
     def restore_path(self, src: str, selector: Optional[base.Selector] = None) -> Iterator[pathlib.Path]:
         # Zero-copy: hand out the real directory.  (selector is irrelevant: nothing is copied.)
+        if selector is not None:
+            logger.warning("Ignoring partial checkpoint download from shared_fs; all files will be directly accessible from shared_fs.")
         d = self._confined(src)
         if not os.path.isdir(d):
             raise errors.CheckpointNotFound(f"checkpoint directory not found: {d}")

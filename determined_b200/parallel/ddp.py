@@ -22,7 +22,7 @@ aggregation window one parameter at a time (``:805-812``).  Here the harness own
 """
 import logging
 import os
-from typing import Any, Callable, Dict, Iterator, List, Optional
+from typing import Any, Callable, Dict, Iterator, List, Optional, Tuple
 
 import torch
 
@@ -566,13 +566,18 @@ class FusedAllReduceHook:
 
     HuggingFace ``Trainer`` (BASELINE config #3; reference ``examples/hf_trainer_api/hf_language_modeling/run_clm.py:711-735``
     with ``harness/determined/transformers/_hf_callback.py:14-47``) wraps the model in torch DDP itself, so the harness
-    cannot hand the optimizer to :class:`FusedGradEngine`.  DDP does let a hook replace its NCCL all-reduce per bucket:
-    this one copies the bucket into a symmetric staging buffer, runs ``detb200_allreduce_fused`` (in-switch reduction from
-    four ranks on, two-shot peer-to-peer below; averaging folded in) on a communication stream and copies the result
-    back, while backward continues on the compute stream.  The compute stream joins the communication stream after the
-    last bucket.  Staging slots are sized on first use (DDP's bucket sizes are fixed after its first iteration)."""
+    cannot hand the optimizer to :class:`FusedGradEngine`.  DDP does let a hook replace its NCCL all-reduce per bucket.
+    DDP owns the bucket tensors (ordinary torch allocations the peers cannot map), so every bucket is staged: copied into
+    its range of ONE symmetric buffer as it becomes ready (a local copy on a side stream, overlapping backward), reduced
+    there by ``detb200_allreduce_fused`` (in-switch reduction from four ranks on, two-shot peer-to-peer below; averaging
+    folded in), and copied back.
 
-    def __init__(self, device: Optional[torch.device] = None, timeout_s: float = 120.0) -> None:
+    ``overlap=True`` reduces each bucket as soon as it is staged, on the side stream with a small CTA budget;
+    ``overlap=False`` (default) stages during backward and runs ONE all-reduce over all buckets with the whole GPU when the
+    last bucket arrives.  The bucket layout is learned during the first backward pass, which runs bucket by bucket."""
+
+    def __init__(self, device: Optional[torch.device] = None, timeout_s: float = 120.0, overlap: Optional[bool] = None,
+                 overlap_ctas: int = 8) -> None:
         from determined_b200.ops import _lib, comm
 
         _lib.load()
@@ -580,27 +585,84 @@ class FusedAllReduceHook:
         self.group = comm.PeerGroup.from_torch_distributed(self.device)
         self.world = self.group.world
         self.timeout_s = timeout_s
+        env = os.environ.get("DETB200_HOOK_OVERLAP", "")
+        self.overlap = (env == "1") if env in ("0", "1") else bool(overlap)
+        self.overlap_ctas = int(os.environ.get("DETB200_HOOK_CTAS", overlap_ctas))
         _, hi = torch.cuda.Stream.priority_range()
         self.stream = torch.cuda.Stream(device=self.device, priority=hi)
-        self.slots: Dict[int, Any] = {}        # bucket index -> (SymmetricBuffer, tensor, peer pointers, mc pointer)
         self.use_nvls = _prefer_nvls(self.world)
         self.launches = 0
+        self.layout: Dict[int, Tuple[int, int]] = {}      # bucket index -> (offset, numel) in the staging buffer
+        self.buf: Any = None
+        self.stage: Optional[torch.Tensor] = None
+        self.peers: Any = None
+        self.mc: Optional[int] = None
+        self._seen: List[Tuple[int, int]] = []
+        self._pending: List[Tuple[int, torch.Tensor]] = []
+        self._tmp: List[Any] = []
+        self._learn_passes = 0
+        self.total = 0
 
-    def _slot(self, index: int, numel: int) -> Any:
-        from determined_b200.ops import comm  # noqa: F401
+    # -- learning passes: DDP rebuilds its buckets once, before the second backward pass, so the layout is only stable from
+    #    then on; until it is known each bucket goes through a throw-away symmetric slot, one collective per bucket
+    def _learning_bucket(self, bucket: Any, grad: torch.Tensor) -> None:
+        from determined_b200.ops import comm
 
+        n = grad.numel()
         align = 4 * self.world
-        padded = (numel + align - 1) // align * align
-        cur = self.slots.get(index)
-        if cur is not None and cur[1].numel() >= padded:
-            return cur
-        # collective: every rank sees the same bucket layout, so every rank (re)allocates at the same call
+        padded = (n + align - 1) // align * align
         buf = self.group.alloc(4 * padded)
         t = buf.tensor(torch.float32, padded)
         peers = self.group.map(buf)
-        mc = self.group.multicast(buf) if self.use_nvls else None
-        self.slots[index] = (buf, t, peers, mc)
-        return self.slots[index]
+        self._tmp.append(buf)
+        t[:n].copy_(grad)
+        self.group.begin_step()
+        comm.allreduce_fused(self.group, peers, 0, padded, 1.0 / self.world, timeout_s=self.timeout_s)
+        grad.copy_(t[:n])
+        self.launches += 1
+        self._seen.append((bucket.index(), n))
+        if bucket.is_last():
+            torch.cuda.synchronize(self.device)
+            for tb in self._tmp:
+                tb.free()
+            self._tmp = []
+            self._learn_passes += 1
+            if self._learn_passes >= 2:
+                # every rank saw the same buckets in the same order: build the single staging buffer
+                off = 0
+                self.layout = {}
+                for idx, numel in sorted(self._seen):
+                    self.layout[idx] = (off, numel)
+                    off += (numel + align - 1) // align * align
+                self.buf = self.group.alloc(4 * off)
+                self.stage = self.buf.tensor(torch.float32, off)
+                self.peers = self.group.map(self.buf)
+                self.mc = self.group.multicast(self.buf) if self.use_nvls else None
+                self.total = off
+            self._seen = []
+
+    def _invalidate(self, mid_pass: bool = False) -> None:
+        """The bucket layout changed under us (DDP rebuilt its buckets again): finish what is staged, bucket by bucket,
+        and learn the new layout."""
+        from determined_b200.ops import comm
+
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_stream(self.stream)
+        if not self.overlap:
+            align = 4 * self.world
+            for idx, g in self._pending:
+                o, m = self.layout[idx]
+                self.group.begin_step()
+                comm.allreduce_fused(self.group, self.peers, o, (m + align - 1) // align * align, 1.0 / self.world, stream=cur,
+                                     timeout_s=self.timeout_s, mc_ptr=self.mc)
+                g.copy_(self.stage[o:o + m])
+        self._pending = []
+        torch.cuda.synchronize(self.device)
+        if self.buf is not None:
+            self.buf.free()
+        self.buf = self.stage = self.peers = self.mc = None
+        self.layout = {}
+        self._learn_passes = 0 if mid_pass else 1       # a layout is only built from a pass seen from its first bucket
 
     def __call__(self, bucket: Any) -> "torch.futures.Future[torch.Tensor]":
         from determined_b200.ops import comm
@@ -608,26 +670,42 @@ class FusedAllReduceHook:
         grad = bucket.buffer()
         if grad.dtype != torch.float32:
             raise TypeError(f"fused all-reduce hook handles fp32 gradient buckets, got {grad.dtype}")
-        n = grad.numel()
-        buf, stage, peers, mc = self._slot(bucket.index(), n)
-        padded = stage.numel()
+        fut: "torch.futures.Future[torch.Tensor]" = torch.futures.Future()
+        if self.stage is not None and (bucket.index() not in self.layout or self.layout[bucket.index()][1] != grad.numel()):
+            self._invalidate(mid_pass=bool(self._pending))
+        if self.stage is None:
+            self._learning_bucket(bucket, grad)
+            fut.set_result(grad)
+            return fut
+        off, n = self.layout[bucket.index()]
         cur = torch.cuda.current_stream(self.device)
         ev = torch.cuda.Event()
         ev.record(cur)
         self.stream.wait_event(ev)
+        align = 4 * self.world
+        padded = (n + align - 1) // align * align
         with torch.cuda.stream(self.stream):
-            stage[:n].copy_(grad, non_blocking=True)
-            if padded > n:
-                stage[n:].zero_()
-            if bucket.index() == 0:
-                self.group.begin_step()
-            comm.allreduce_fused(self.group, peers, 0, padded, 1.0 / self.world, stream=self.stream, timeout_s=self.timeout_s,
-                                 mc_ptr=mc)
-            grad.copy_(stage[:n], non_blocking=True)
-        self.launches += 1
+            self.stage[off:off + n].copy_(grad, non_blocking=True)
+            if self.overlap:
+                if not self._pending:
+                    self.group.begin_step()
+                comm.allreduce_fused(self.group, self.peers, off, padded, 1.0 / self.world, stream=self.stream,
+                                     timeout_s=self.timeout_s, mc_ptr=self.mc, max_ctas=self.overlap_ctas)
+                grad.copy_(self.stage[off:off + n], non_blocking=True)
+                self.launches += 1
+        self._pending.append((bucket.index(), grad))
         if bucket.is_last():
             cur.wait_stream(self.stream)
-        fut: "torch.futures.Future[torch.Tensor]" = torch.futures.Future()
+            if not self.overlap:
+                # everything is staged: one collective over the whole buffer with every SM, then scatter the result back
+                self.group.begin_step()
+                comm.allreduce_fused(self.group, self.peers, 0, self.total, 1.0 / self.world, stream=cur,
+                                     timeout_s=self.timeout_s, mc_ptr=self.mc, max_ctas=148)
+                self.launches += 1
+                for idx, g in self._pending:
+                    o, m = self.layout[idx]
+                    g.copy_(self.stage[o:o + m], non_blocking=True)
+            self._pending = []
         fut.set_result(grad)
         return fut
 
@@ -635,7 +713,9 @@ class FusedAllReduceHook:
         self.group.close()
 
 
-def fused_allreduce_hook(state: FusedAllReduceHook, bucket: Any) -> "torch.futures.Future[torch.Tensor]":
+def fused_allreduce_hook(state, bucket):  # type: ignore[no-untyped-def]
+    """(state: FusedAllReduceHook, bucket: dist.GradBucket) -> Future[Tensor].  Left unannotated on purpose: DDP compares
+    the annotations of a hook by identity with its own classes when the hook is registered."""
     return state(bucket)
 
 

@@ -72,6 +72,10 @@ def load_trial_from_checkpoint_path(path: str, trial_class: Optional[Type[PyTorc
     hparams: Dict[str, Any] = {}
     exp_conf: Optional[Dict[str, Any]] = None
     spec: Optional[str] = None
+    # ``PyTorchTrial.build_model()`` is the pre-0.12.13 API (gone after 0.14.0).  Only checkpoints old enough to lack
+    # load_data.json can come from it; newer ones may use that method name for their own purposes (reference
+    # ``pytorch/_load.py:118-122,213-232``).
+    detect_build_model = not load_data_path.exists()
     if load_data_path.exists():
         ld = json.loads(load_data_path.read_text())
         if ld.get("trial_type") not in (None, "PyTorchTrial"):
@@ -101,6 +105,11 @@ def load_trial_from_checkpoint_path(path: str, trial_class: Optional[Type[PyTorc
     if sd_path is None:
         raise errors.InvalidCheckpointException(f"no state_dict.pth under {ckpt_dir}")
     checkpoint = torch.load(str(sd_path), **torch_load_kwargs)
+    if detect_build_model and callable(getattr(trial, "build_model", None)):
+        # with these very old checkpoints the caller gets the bare model back, as the reference does
+        model = trial.build_model()
+        model.load_state_dict(checkpoint["model_state_dict"] if "model_state_dict" in checkpoint else checkpoint["models_state_dict"][0])
+        return model  # type: ignore[return-value]
     if "model_state_dict" in checkpoint:
         states = [checkpoint["model_state_dict"]]
     else:

@@ -280,8 +280,9 @@ class _PyTorchTrialController:
             if not self.context.experimental._data_repro_checks_disabled:
                 raise RuntimeError(
                     "build_training_data_loader() must return a determined.pytorch.DataLoader (which shards, repeats "
-                    "and skips reproducibly); call context.experimental.disable_dataset_reproducibility_checks() to "
-                    "use a plain torch DataLoader and own those properties yourself")
+                    "and skips reproducibly); you can disable this check by calling "
+                    "context.experimental.disable_dataset_reproducibility_checks() to use a plain torch DataLoader and "
+                    "own those properties yourself")
             self.training_loader = train
             self.context._epoch_len = len(train)
         if not self.context._epoch_len:
@@ -297,6 +298,21 @@ class _PyTorchTrialController:
         elif self.is_chief:
             self.validation_loader = (val.get_data_loader(repeat=False, skip=0, num_replicas=1, rank=0)
                                       if isinstance(val, _data.DataLoader) else val)
+
+    _restored_rng: Optional[Dict[str, Any]] = None
+
+    def _apply_rng_state(self, rng: Dict[str, Any]) -> None:
+        ctx = self.context
+        np.random.set_state(rng["np_rng_state"])
+        random.setstate(rng["random_rng_state"])
+        torch.random.set_rng_state(rng["cpu_rng_state"])
+        if torch.cuda.is_available() and ctx.device.type == "cuda":
+            if "gpu_rng_state" in rng:
+                torch.cuda.set_rng_state(rng["gpu_rng_state"], device=ctx.device)
+            else:
+                logger.warning("The system has a gpu but no gpu_rng_state exists in the checkpoint.")
+        elif "gpu_rng_state" in rng:
+            logger.warning("There exists gpu_rng_state in checkpoint but the system has no gpu.")
 
     def _make_enumerator(self) -> Iterator:
         loader = self.training_loader
@@ -337,6 +353,12 @@ class _PyTorchTrialController:
                 self._set_data_loaders()
             self.state.batches_trained = self.start_from_batch
             self.training_enumerator = self._make_enumerator()
+            if self._restored_rng is not None:
+                # building the loader iterator draws from the torch generator (worker base seed, shuffling); the
+                # reference builds it before it restores the checkpoint's random state (``_pytorch_trial.py:572-579``), so
+                # that the first batch after a restart sees exactly the state that was saved: same effect here
+                self._apply_rng_state(self._restored_rng)
+                self._restored_rng = None
             if self.context.distributed.size > 1:
                 self.context._get_engine().sync_params_from_chief(self.context.models)
             for cb in self.callbacks.values():
@@ -990,16 +1012,8 @@ class _PyTorchTrialController:
 
         rng = checkpoint.get("rng_state")
         if rng is not None:
-            np.random.set_state(rng["np_rng_state"])
-            random.setstate(rng["random_rng_state"])
-            torch.random.set_rng_state(rng["cpu_rng_state"])
-            if torch.cuda.is_available() and ctx.device.type == "cuda":
-                if "gpu_rng_state" in rng:
-                    torch.cuda.set_rng_state(rng["gpu_rng_state"], device=ctx.device)
-                else:
-                    logger.warning("The system has a gpu but no gpu_rng_state exists in the checkpoint.")
-            elif "gpu_rng_state" in rng:
-                logger.warning("There exists gpu_rng_state in checkpoint but the system has no gpu.")
+            self._apply_rng_state(rng)
+            self._restored_rng = rng
         else:
             logger.warning("The checkpoint has no random state to restore.")
 

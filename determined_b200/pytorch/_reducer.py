@@ -144,8 +144,9 @@ class _PyTorchReducerContext:
             else:
                 if isinstance(out, dict):
                     raise AssertionError(
-                        f"The custom reduction {what} was wrapped with name={w.name!r} but returned a dict. "
-                        "Leave name=None to return several metrics, or return a single value.")
+                        f"The custom reduction {what} was wrapped by a call to wrap_reducer() with name set but it "
+                        f"returned a dict anyway (name={w.name!r}).  Leave name=None to return a dict of several "
+                        "metrics, or return a single value (not a dict) for a single named metric.")
                 metrics[w.name] = out
         return metrics
 

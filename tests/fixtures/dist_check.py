@@ -318,12 +318,22 @@ def check_ddp_comm_hook(rank, world, dev):
     from determined_b200.parallel import ddp as pddp
 
     torch.backends.cuda.matmul.allow_tf32 = False
+    for overlap in (False, True):
+        _ddp_hook_case(rank, world, dev, overlap)
+
+
+def _ddp_hook_case(rank, world, dev, overlap):
+    import copy
+
+    from determined_b200.parallel import ddp as pddp
+
     torch.manual_seed(4)
     net0 = torch.nn.Sequential(torch.nn.Linear(96, 512), torch.nn.GELU(), torch.nn.Linear(512, 512), torch.nn.GELU(),
                                torch.nn.Linear(512, 10)).to(dev)
     a = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(net0), device_ids=[dev.index], bucket_cap_mb=0.5)
     b = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(net0), device_ids=[dev.index], bucket_cap_mb=0.5)
-    state = pddp.install_comm_hook(a, dev)
+    state = pddp.FusedAllReduceHook(dev, overlap=overlap)
+    a.register_comm_hook(state, pddp.fused_allreduce_hook)
     oa = torch.optim.AdamW(a.parameters(), lr=1e-3)
     ob = torch.optim.AdamW(b.parameters(), lr=1e-3)
     rng = torch.Generator().manual_seed(50 + rank)
@@ -336,7 +346,7 @@ def check_ddp_comm_hook(rank, world, dev):
             o.step()
     for pa, pb in zip(a.parameters(), b.parameters()):
         torch.testing.assert_close(pa, pb, rtol=1e-4, atol=1e-6)
-    assert state.launches >= 5 and len(state.slots) >= 2, (state.launches, len(state.slots))
+    assert state.launches >= 5 and len(state.layout) >= 2, (state.launches, len(state.layout))
     dist.barrier()
     state.close()
 

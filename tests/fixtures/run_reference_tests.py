@@ -12,6 +12,7 @@ sys.path[:] = [p for p in sys.path if pathlib.Path(p or ".").resolve() != pathli
 sys.path.insert(0, repo)
 os.chdir(ref)                        # the reference's `tests` package is imported from here (rootdir-relative)
 sys.path.insert(0, ref)
+sys.path.append(str(pathlib.Path(__file__).resolve().parent / "ref_shims"))   # stand-ins for test-only imports the image lacks
 
 import determined_b200  # noqa: E402
 
