@@ -89,6 +89,16 @@ class Allocation:
         self.state = "RUNNING"
         exp = t.experiment
         remote = m.agents.is_remote(agent_id)
+        # Where the new run starts is where the trial's latest checkpoint ends, not how far metrics were reported before a
+        # crash (reference master/internal/trial.go:489-520 buildTaskSpecifier: StepsCompleted comes with LatestCheckpoint);
+        # a trial restarted before its first checkpoint starts from zero.
+        steps_done = 0
+        if t.latest_checkpoint:
+            row = m.db.one("SELECT steps_completed FROM checkpoints WHERE uuid=?", (t.latest_checkpoint,))
+            steps_done = int(row["steps_completed"] or 0) if row is not None else 0
+        if t.total_batches != steps_done:
+            t.total_batches = steps_done
+            t.persist()
         # what the master decides; the host running the task (this process, or an agent) layers it over its own environment
         task_env: Dict[str, str] = dict(exp.environment_variables())
         task_env.update({
@@ -97,7 +107,7 @@ class Allocation:
             "DET_TASK_ID": t.task_id, "DET_ALLOCATION_ID": self.id, "DET_SESSION_TOKEN": self.token,
             "DET_TASK_TYPE": "TRIAL", "DET_TRIAL_ID": str(t.id), "DET_EXPERIMENT_ID": str(exp.id),
             "DET_TRIAL_SEED": str(t.seed), "DET_HPARAMS": util.json_encode(t.hparams),
-            "DET_EXPERIMENT_CONFIG": util.json_encode(exp.config), "DET_STEPS_COMPLETED": str(t.total_batches),
+            "DET_EXPERIMENT_CONFIG": util.json_encode(exp.config), "DET_STEPS_COMPLETED": str(steps_done),
             "DET_TRIAL_RUN_ID": str(t.run_id), "DET_RESOURCES_ID": f"{self.id}-box", "DET_CONTAINER_ID": self.id,
             "DET_USER": exp.owner_name, "PYTHONUNBUFFERED": "1",
         })

@@ -168,6 +168,42 @@ def test_adaptive_asha_packs_trials_and_finishes(cluster):
         assert 1 <= len(alive) <= 2
 
 
+def test_adaptive_asha_survives_chaos_with_max_restarts(cluster):
+    """The reference's ``adaptive_chaos`` experiment (``e2e_tests/tests/fixtures/no_op/adaptive_chaos.yaml``: adaptive ASHA,
+    ``max_restarts`` high, every batch may kill the trial process) scaled to the test box: scheduler packing, promotions,
+    crash -> restart from the latest checkpoint and searcher bookkeeping all at once.  Every trial must end closed."""
+    m, sess, tmp = cluster
+    cfg = json.loads(json.dumps(BASE))
+    cfg["searcher"] = {"name": "adaptive_asha", "metric": "val_loss", "max_length": {"batches": 48}, "max_trials": 8,
+                       "max_concurrent_trials": 4, "divisor": 2, "max_rungs": 3}
+    cfg["hyperparameters"]["learning_rate"] = {"type": "log", "minval": -3, "maxval": -0.5, "base": 10}
+    cfg["hyperparameters"]["chaos_probability"] = 0.02
+    cfg["min_validation_period"] = {"batches": 0}
+    cfg["min_checkpoint_period"] = {"batches": 8}
+    cfg["scheduling_unit"] = 8
+    cfg["max_restarts"] = 1000
+    eid = create(sess, cfg)
+    st = wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR", "STATE_CANCELED"}, timeout=900)
+    assert st == "STATE_COMPLETED", dump_logs(sess, eid)
+    trials = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"]
+    assert len(trials) == 8 and all(t["state"] == "STATE_COMPLETED" for t in trials), [(t["id"], t["state"]) for t in trials]
+    restarts = sum(t["restarts"] for t in trials)
+    assert restarts >= 1, "with p=0.02 per batch over a few hundred batches at least one trial must have been restarted"
+    # Restarted or not, every trial ends exactly on a rung boundary of its bracket: its last validation and its last
+    # checkpoint are both at its final length.  Rung lengths are cumulative in ASHA (reference
+    # master/pkg/searcher/asha.go:56-78: unitsNeeded += max_length / divisor^(rungs-i-1)): 12, 36, 84 in the 3-rung bracket,
+    # 24, 72 in the 2-rung one, 48 in the 1-rung one.
+    boundaries = {12, 36, 84, 24, 72, 48}
+    for t in trials:
+        total = t["totalBatchesProcessed"]
+        vals = [r["steps_completed"] for r in m.db.all("SELECT steps_completed FROM metrics WHERE trial_id=? AND grp='validation' ORDER BY id", (t["id"],))]
+        cks = [c["metadata"].get("steps_completed") for c in sess.get(f"/api/v1/trials/{t['id']}/checkpoints").json()["checkpoints"]]
+        assert total in boundaries and vals and vals[-1] == total and max(cks) == total, (t["id"], total, vals, cks)
+        assert set(vals) <= boundaries, (t["id"], vals)
+    assert max(t["totalBatchesProcessed"] for t in trials) in (84, 72, 48)
+    assert not m.allocations
+
+
 def test_invalid_hp_trial_is_closed_gracefully(cluster):
     m, sess, tmp = cluster
     cfg = json.loads(json.dumps(BASE))
