@@ -28,7 +28,6 @@ if ROOT not in sys.path:
 MODEL_DEF = '''
 import sys
 sys.path.insert(0, {root!r})
-import torch
 from benchmarks import cifar_trial
 from determined_b200 import pytorch
 
@@ -41,21 +40,6 @@ class CIFARTrial(_Base):
         lr = float(context.get_hparams().get("learning_rate", 0.05))
         for g in self.opt.param_groups:
             g["lr"] = lr
-
-    def build_validation_data_loader(self):
-        src = cifar_trial.SyntheticCIFAR({batch}, 2, None, seed=99)
-        return pytorch.DataLoader(_Pairs(src.batches), batch_size=None)
-
-
-class _Pairs(torch.utils.data.Dataset):
-    def __init__(self, batches):
-        self.b = batches
-
-    def __len__(self):
-        return len(self.b)
-
-    def __getitem__(self, i):
-        return self.b[i]
 '''
 
 
@@ -109,6 +93,12 @@ def main(args: Any) -> None:
         eid = sess.post("/api/v1/experiments", json={"config": yaml.safe_dump(cfg), "modelDefinition": _files(batch, gpu), "activate": True}).json()["experiment"]["id"]
         st = _wait(sess, eid, {"STATE_COMPLETED", "STATE_ERROR", "STATE_CANCELED"}, 3600)
         wall = time.time() - t0
+        print(f"[asha_pack] search finished: {st} in {wall:.1f}s", file=sys.stderr, flush=True)
+        if st != "STATE_COMPLETED":
+            for t in sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"][:2]:
+                for ln in sess.get(f"/api/v1/trials/{t['id']}/logs").json()["logs"][-25:]:
+                    print(f"[trial {t['id']}] {ln['log'].rstrip()}", file=sys.stderr)
+            raise RuntimeError(f"the search ended in {st}")
         trials = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"]
         total_batches = sum(t["totalBatchesProcessed"] for t in trials)
         allocs = m.db.all("SELECT a.trial_id, a.slots, a.start_time, a.end_time FROM allocations a JOIN trials t ON t.id=a.trial_id "
@@ -145,6 +135,7 @@ def main(args: Any) -> None:
                 tr = sess.get(f"/api/v1/experiments/{e2}/trials").json()["trials"]
                 return tr[0]["totalBatchesProcessed"] if tr else 0
 
+            print(f"[asha_pack] preempt/resume probe ({mode})", file=sys.stderr, flush=True)
             t1 = time.time()
             while batches() < max(max_len // 2, 8) and time.time() - t1 < 600:
                 time.sleep(0.05)

@@ -103,7 +103,77 @@ add_bf16_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __rest
   }
 }
 
+// Multi-tensor gradient accumulation: dst[k] (fp32, inside the flat gradient buffer) += src[k] (bf16 or fp32) for up to
+// kAccumMax tensors in one launch.  The table travels by value in the kernel parameters (no device-side table to keep in
+// sync, and CUDA-graph capture records it).  blockIdx.y picks the tensor, blockIdx.x strides over it.
+constexpr int kAccumMax = 48;
+struct AccumTable {
+  const void* src[kAccumMax];
+  float* dst[kAccumMax];
+  int64_t n[kAccumMax];
+  unsigned char is_bf16[kAccumMax];
+};
+
+__global__ void __launch_bounds__(256) accum_multi_kernel(AccumTable t) {
+  const int k = blockIdx.y;
+  const int64_t n = t.n[k];
+  float* __restrict__ dst = t.dst[k];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t.is_bf16[k]) {
+    const __nv_bfloat16* __restrict__ src = reinterpret_cast<const __nv_bfloat16*>(t.src[k]);
+    const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
+    const int64_t n8 = vec ? (n >> 3) : 0;
+    for (int64_t v = tid; v < n8; v += stride) {
+      const uint4 u = ldg_stream_u4(reinterpret_cast<const uint4*>(src) + v);
+      float4 a = reinterpret_cast<const float4*>(dst)[2 * v], b = reinterpret_cast<const float4*>(dst)[2 * v + 1];
+      a.x += bf16lo(u.x); a.y += bf16hi(u.x); a.z += bf16lo(u.y); a.w += bf16hi(u.y);
+      b.x += bf16lo(u.z); b.y += bf16hi(u.z); b.z += bf16lo(u.w); b.w += bf16hi(u.w);
+      reinterpret_cast<float4*>(dst)[2 * v] = a;
+      reinterpret_cast<float4*>(dst)[2 * v + 1] = b;
+    }
+    for (int64_t i = n8 * 8 + tid; i < n; i += stride) dst[i] += __bfloat162float(src[i]);
+  } else {
+    const float* __restrict__ src = reinterpret_cast<const float*>(t.src[k]);
+    const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
+    const int64_t n4 = vec ? (n >> 2) : 0;
+    for (int64_t v = tid; v < n4; v += stride) {
+      const float4 s4 = ldg_stream(reinterpret_cast<const float4*>(src) + v);
+      float4 a = reinterpret_cast<const float4*>(dst)[v];
+      a.x += s4.x; a.y += s4.y; a.z += s4.z; a.w += s4.w;
+      reinterpret_cast<float4*>(dst)[v] = a;
+    }
+    for (int64_t i = n4 * 4 + tid; i < n; i += stride) dst[i] += src[i];
+  }
+}
+
 }  // namespace
+
+// dst[k][0:n[k]) += src[k][0:n[k]) for k < count.  srcs / dsts / numels / is_bf16 are HOST arrays; dst is fp32, src is
+// bf16 (is_bf16[k] != 0) or fp32.  Replaces the one-add-kernel-per-parameter gradient accumulation of autograd
+// (AccumulateGrad) and the bf16 -> fp32 gradient casts of autocast: reference `loss.backward()` under
+// harness/determined/pytorch/_pytorch_context.py:786-803.  Any count: launched in groups of 48 tensors.
+DETB200_API int detb200_accum_multi(const void* const* srcs, float* const* dsts, const int64_t* numels, const unsigned char* is_bf16,
+                                    int count, cudaStream_t stream) {
+  if (count <= 0) return 0;
+  if (!srcs || !dsts || !numels || !is_bf16) { detb200_set_error("accum_multi: null table"); return DETB200_ERR_BAD_ARG; }
+  for (int base = 0; base < count; base += kAccumMax) {
+    AccumTable t;
+    const int m = (count - base < kAccumMax) ? count - base : kAccumMax;
+    int64_t nmax = 0;
+    for (int k = 0; k < m; ++k) {
+      if (!srcs[base + k] || !dsts[base + k] || numels[base + k] < 0) { detb200_set_error("accum_multi: bad entry %d", base + k); return DETB200_ERR_BAD_ARG; }
+      t.src[k] = srcs[base + k]; t.dst[k] = dsts[base + k]; t.n[k] = numels[base + k]; t.is_bf16[k] = is_bf16[base + k];
+      if (t.n[k] > nmax) nmax = t.n[k];
+    }
+    for (int k = m; k < kAccumMax; ++k) { t.src[k] = nullptr; t.dst[k] = nullptr; t.n[k] = 0; t.is_bf16[k] = 0; }
+    // enough CTAs along x for the largest tensor at 8 elements per thread per trip, capped so that a group fills the GPU a few times
+    int gx = grid_for(nmax, 256, 16, (kNumSMs * 8 + m - 1) / m);
+    accum_multi_kernel<<<dim3(gx, m), 256, 0, stream>>>(t);
+    DETB200_LAUNCH_CHECK();
+  }
+  return 0;
+}
 
 // qkv: bf16 packed projection addressed as (b, s, which in {q,k,v}, h, d) with element strides sb, ss, sw, sh (d contiguous).
 // cos/sin: fp32 [S, rot/2].  rot/2 must be a multiple of 8.  conj != 0 applies the inverse rotation (the backward).

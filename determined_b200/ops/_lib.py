@@ -123,6 +123,7 @@ def load() -> ctypes.CDLL:
     _sig(lib, "detb200_colsum_bf16", i, [p, p, i64, i, i64, i, p])
     _sig(lib, "detb200_cast_bf16", i, [p, p, i64, p])
     _sig(lib, "detb200_add_bf16", i, [p, p, p, p, i64, p])
+    _sig(lib, "detb200_accum_multi", i, [POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int64), ctypes.c_char_p, i, p])
     _lib = lib
     return lib
 

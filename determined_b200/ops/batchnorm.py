@@ -13,6 +13,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from determined_b200.ops import _lib
+from determined_b200.parallel import sink as _sink
 
 _WS = {}
 
@@ -62,6 +63,7 @@ class _BNTrainFn(torch.autograd.Function):
         ctx.has_w, ctx.has_b, ctx.has_res = weight is not None, bias is not None, residual is not None
         ctx.wdtype = weight.dtype if weight is not None else None
         ctx.bdtype = bias.dtype if bias is not None else None
+        ctx.wparam, ctx.bparam = weight, bias
         ctx.mark_non_differentiable(*(t for t in (running_mean, running_var, nbt) if t is not None))
         return y
 
@@ -87,6 +89,18 @@ class _BNTrainFn(torch.autograd.Function):
                                             _lib.dtype_code(x.dtype), _lib.stream_ptr()), "bn_bwd")
         dw = grads[0].to(ctx.wdtype) if ctx.has_w else None
         db = grads[1].to(ctx.bdtype) if ctx.has_b else None
+        # inside context.backward the engine adds all parameter gradients into its flat buffer in one launch
+        # (parallel/sink.py) instead of one AccumulateGrad add per tensor
+        if dw is not None:
+            s = _sink.sink_of(ctx.wparam)
+            if s is not None and s.accepts(ctx.wparam, dw):
+                s.add(ctx.wparam, dw)
+                dw = None
+        if db is not None:
+            s = _sink.sink_of(ctx.bparam)
+            if s is not None and s.accepts(ctx.bparam, db):
+                s.add(ctx.bparam, db)
+                db = None
         return dx, dres, dw, db, None, None, None, None, None, None
 
 

@@ -81,6 +81,8 @@ class _OptRecord:
         self.found_inf: Optional[torch.Tensor] = None   # int32[1], device
         self.unscaled_in_flight = False        # this step's buckets were unscaled + inf-checked by the all-reduce
         self.overlapped = True                 # bucketed exchange during backward (False: one all-reduce at step time)
+        self.sink: Any = None                  # parallel.sink.GradSink: deferred multi-tensor gradient accumulation
+        self.shadow: Any = None                # parallel.sink.LowpShadow: bf16 mirror of the flat parameters (conv weights)
         self.transport_nvls = False
 
 
@@ -95,7 +97,8 @@ class GradEngineBase:
         self._communicating = True
 
     def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool,
-                      backward_passes_per_step: int = 1, fp16_compression: bool = False) -> torch.optim.Optimizer:
+                      backward_passes_per_step: int = 1, fp16_compression: bool = False,
+                      models: Optional[List[torch.nn.Module]] = None) -> torch.optim.Optimizer:
         raise NotImplementedError
 
     def backward_begin(self, communicate: bool, scaler: Any = None) -> None:
@@ -143,7 +146,8 @@ class GradEngineBase:
 
 class GenericGradEngine(GradEngineBase):
     def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool,
-                      backward_passes_per_step: int = 1, fp16_compression: bool = False) -> torch.optim.Optimizer:
+                      backward_passes_per_step: int = 1, fp16_compression: bool = False,
+                      models: Optional[List[torch.nn.Module]] = None) -> torch.optim.Optimizer:
         rec = _OptRecord()
         rec.optimizer = optimizer
         rec.average_aggregated_gradients = average_aggregated_gradients
@@ -236,8 +240,11 @@ class FusedGradEngine(GradEngineBase):
 
     # ------------------------------------------------------------------ set-up
     def add_optimizer(self, optimizer: torch.optim.Optimizer, average_aggregated_gradients: bool,
-                      backward_passes_per_step: int = 1, fp16_compression: bool = False) -> torch.optim.Optimizer:
+                      backward_passes_per_step: int = 1, fp16_compression: bool = False,
+                      models: Optional[List[torch.nn.Module]] = None) -> torch.optim.Optimizer:
         from determined_b200.ops import comm, optim
+        from determined_b200.ops import conv as conv_ops
+        from determined_b200.parallel import sink as sink_mod
 
         world = self.dist.size
         rec = _OptRecord()
@@ -258,6 +265,15 @@ class FusedGradEngine(GradEngineBase):
                                     grad_alloc=grad_alloc)
             rec.fused_step = optim.fuse_optimizer_(optimizer, rec.layout)
             rec.scratch = optim.NormScratch(self.device)
+            # native modules hand their parameter gradients to the sink; converted convolutions read bf16 weights from the shadow
+            rec.sink = sink_mod.GradSink(rec.layout)
+            for sl in rec.layout.slots:
+                sl.param._detb200_sink = rec.sink            # type: ignore[attr-defined]
+            if models and os.environ.get("DETB200_LOWP_SHADOW", "1") != "0":
+                owned = {id(sl.param) for sl in rec.layout.slots}
+                if any(isinstance(mm, conv_ops.FusedConv2d) and id(mm.weight) in owned for md in models for mm in md.modules()):
+                    rec.shadow = sink_mod.LowpShadow(rec.layout)
+                    conv_ops.attach_shadow_(models, rec.shadow)
             rec.found_inf = torch.zeros(1, dtype=torch.int32, device=self.device)
             rec.found_inf_f = torch.zeros(1, dtype=torch.float32, device=self.device)
             rec.inv_scale = torch.ones(1, dtype=torch.float32, device=self.device)
@@ -310,6 +326,8 @@ class FusedGradEngine(GradEngineBase):
                 comm.broadcast(rec.group, rec.peer_bufs, 0, lay.total, root=0, timeout_s=self.timeout_s)
                 lay.flat_param.copy_(lay.flat_grad)
                 lay.flat_grad.zero_()
+                if rec.shadow is not None:
+                    rec.shadow.invalidate()
                 covered.update(id(s.param) for s in lay.slots)
             rest = [t for m in models for t in ([p.data for p in m.parameters() if id(p) not in covered] + [b.data for b in m.buffers()])]
             if rest:
@@ -416,6 +434,9 @@ class FusedGradEngine(GradEngineBase):
         rec.next_bucket = 0
 
     def backward_begin(self, communicate: bool, scaler: Any = None) -> None:
+        for rec in self.records.values():
+            if rec.sink is not None:
+                rec.sink.active = True
         self._communicating = communicate and self.dist.size > 1
         if not self._communicating:
             return
@@ -433,6 +454,31 @@ class FusedGradEngine(GradEngineBase):
                 rec.unscaled_in_flight = True
             if any(b.launched for b in rec.buckets):
                 self._rearm_for_another_pass(rec, scaler._scale if amp else None)
+
+    def backward_end(self) -> None:
+        """One multi-tensor kernel adds the gradients that native modules handed to the sinks during this pass into the flat
+        buffers; their parameters then count as ready for the bucketed exchange."""
+        for rec in self.records.values():
+            if rec.sink is None:
+                continue
+            touched = rec.sink.flush()
+            rec.sink.active = False
+            if touched and rec.overlapped and rec.hooks and self._communicating and rec.passes_seen >= rec.backward_passes:
+                hook = self._make_hook(rec)
+                for p in touched:
+                    b = rec.bucket_of.get(id(p))
+                    if b is not None and not b.launched:
+                        hook(p)
+
+    def invalidate_shadows(self) -> None:
+        """Parameters may have changed behind the engine's back (or a CUDA graph is about to be captured and must contain
+        its own refresh): the next module that reads a bf16 weight refreshes the mirror first."""
+        for rec in self.records.values():
+            if rec.shadow is not None:
+                rec.shadow.invalidate()
+
+    def shadows_stale(self) -> bool:
+        return any(rec.shadow is not None and rec.shadow.stale() for rec in self.records.values())
 
     def _flush(self, rec: _OptRecord) -> None:
         """Launch whatever has not been launched yet (buckets holding parameters that received no
@@ -523,6 +569,8 @@ class FusedGradEngine(GradEngineBase):
                 optimizer.step()
             if auto_zero_grads:
                 lay.flat_grad.zero_()
+        if rec.shadow is not None:
+            rec.shadow.invalidate()          # the parameters just changed: the next forward refreshes the bf16 mirror
         if world > 1:
             self._arm(rec)
 

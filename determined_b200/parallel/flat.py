@@ -79,6 +79,7 @@ class FlatLayout:
             off = seg_start + (off - seg_start + segment_align - 1) // segment_align * segment_align
             self.segments.append(Segment(gi, seg_start, off - seg_start))
         self.total = max(off, segment_align)
+        self.generation = 0          # bumped whenever parameters are re-homed (rebind): mirrors of the buffer are then stale
         alloc = lambda n: torch.zeros(n, dtype=torch.float32, device=device)  # noqa: E731
         self.flat_param = (param_alloc or alloc)(self.total)
         # bind_grads=False: no full-size gradient buffer at all (ZeRO-2/3: gradients live in a small landing ring and in
@@ -107,6 +108,7 @@ class FlatLayout:
     def rebind(self) -> None:
         """Re-point ``.data``/``.grad`` at the flat buffers (after something replaced them, e.g.
         ``model.load_state_dict(assign=True)`` or ``zero_grad(set_to_none=True)``)."""
+        self.generation += 1
         with torch.no_grad():
             for s in self.slots:
                 want = _dense_view(self.flat_param, s.offset, s.param.data)

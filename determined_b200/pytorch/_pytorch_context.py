@@ -219,7 +219,12 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
             # module-level fusion pass of the B200 engine: hot library ops whose ATen kernels are far
             # off the HBM roofline are swapped for native ones (same parameters / state-dict keys)
             from determined_b200.ops import batchnorm
+            from determined_b200.ops import conv as conv_ops
 
+            nc = conv_ops.convert_conv_(model)
+            if nc:
+                logger.info("fused engine: %d Conv2d modules read bf16 weights from the engine's mirror under bf16 autocast and "
+                            "hand their weight gradients to the engine's multi-tensor accumulation", nc)
             n = batchnorm.convert_batchnorm_(model)
             if n:
                 nb = batchnorm.fuse_residual_blocks_(model)
@@ -260,7 +265,7 @@ class PyTorchTrialContext(_reducer._PyTorchReducerContext):
         }
         optimizer = self._get_engine().add_optimizer(optimizer, bool(average_aggregated_gradients),
                                                      backward_passes_per_step=backward_passes_per_step,
-                                                     fp16_compression=bool(fp16_compression))
+                                                     fp16_compression=bool(fp16_compression), models=self.models)
         self.optimizers.append(optimizer)
         return optimizer
 

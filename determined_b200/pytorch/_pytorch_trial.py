@@ -615,6 +615,9 @@ class _PyTorchTrialController:
 
     def _capture(self, gs: _GraphedStep, batch: Any, epoch_idx: int, batch_idx: int) -> Dict[str, Any]:
         torch.cuda.synchronize()
+        inval = getattr(self.context._get_engine(), "invalidate_shadows", None)
+        if inval is not None:
+            inval()      # a captured step refreshes the bf16 weight mirror itself, whatever preceded the capture
         gs.static_in = _clone_tree(batch)
         for opt in self.context.optimizers:
             sync = getattr(opt, "sync_hparams", None)

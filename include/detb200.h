@@ -279,6 +279,11 @@ int detb200_rotary_qkv(void* qkv, const float* cos_t, const float* sin_t, int64_
 int detb200_colsum_bf16(const void* x, float* out, int64_t M, int N, int64_t ld, int accumulate, detb200_stream_t stream);
 int detb200_cast_bf16(const float* x, void* y, int64_t n, detb200_stream_t stream);
 int detb200_add_bf16(const void* a, const void* b, const void* c /* nullable */, void* y, int64_t n, detb200_stream_t stream);
+/* Multi-tensor gradient accumulation: dsts[k][0:numels[k]) (fp32) += srcs[k] (bf16 where is_bf16[k], else fp32), all k in
+ * one launch per 48 tensors; the four tables are HOST arrays.  Reference: autograd's one-add-per-parameter accumulation
+ * plus autocast's bf16 -> fp32 gradient casts inside loss.backward() (_pytorch_context.py:786-803). */
+int detb200_accum_multi(const void* const* srcs, float* const* dsts, const int64_t* numels, const unsigned char* is_bf16,
+                        int count, detb200_stream_t stream);
 
 /* Backward of detb200_attn_fwd on tcgen05 (H_kv == H, S_q == S_kv, D == 128): five GEMMs per (key block, query block)
  * pair, dK/dV accumulated in tensor memory, dQ through fp32 atomics into `dq_acc` ([B,S,H,D], zeroed here) and converted

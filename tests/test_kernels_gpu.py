@@ -386,3 +386,102 @@ def test_fused_glue_kernels():
     a, b, c = (torch.randn(4, 100, 64, device="cuda").to(torch.bfloat16) for _ in range(3))
     torch.testing.assert_close(fused.add(a, b, c).float(), a.float() + b.float() + c.float(), rtol=1e-2, atol=3e-2)
     torch.testing.assert_close(fused.add(a, b), a + b)
+
+
+def test_accum_multi_adds_many_tensors_in_one_launch():
+    """fp32 destinations inside one flat buffer += bf16 / fp32 sources of assorted sizes (vector bodies, scalar tails,
+    misaligned starts, more tensors than one launch holds) against a plain PyTorch loop."""
+    from determined_b200.ops import _lib
+
+    lib = _lib.load()
+    dev = torch.device("cuda")
+    torch.manual_seed(5)
+    sizes = [1, 7, 8, 9, 64, 1000, 4099, 36864, 3 * 3 * 64 * 128 + 5] * 7        # 63 tensors > 48 per launch
+    flat = torch.randn(sum(s + 3 for s in sizes) + 16, device=dev)
+    want = flat.clone()
+    srcs, dsts = [], []
+    off = 1                                                                          # misaligned on purpose
+    for i, n in enumerate(sizes):
+        dt = torch.bfloat16 if i % 3 else torch.float32
+        g = (torch.randn(n + 1, device=dev) * 3).to(dt)[1:] if i % 5 == 0 else (torch.randn(n, device=dev) * 3).to(dt)
+        srcs.append(g)
+        dsts.append(flat[off:off + n])
+        want[off:off + n] += g.float()
+        off += n + 3
+    k = len(srcs)
+    sp = (ctypes.c_void_p * k)(*[g.data_ptr() for g in srcs])
+    dp = (ctypes.c_void_p * k)(*[d.data_ptr() for d in dsts])
+    nn_ = (ctypes.c_int64 * k)(*[g.numel() for g in srcs])
+    kinds = bytes(1 if g.dtype == torch.bfloat16 else 0 for g in srcs)
+    _lib.check(lib.detb200_accum_multi(sp, dp, nn_, kinds, k, _lib.stream_ptr()), "accum_multi")
+    torch.cuda.synchronize()
+    torch.testing.assert_close(flat, want, rtol=1e-6, atol=1e-6)
+
+
+def test_conv_pass_bf16_shadow_and_gradient_sink_match_autocast():
+    """A small conv net under bf16 autocast: the engine's path (bf16 weight mirror, weight gradients through the
+    multi-tensor accumulation) against stock modules + AccumulateGrad, over aggregation, an optimizer step, a weight clamp
+    written through ``.data`` between steps (WGAN style) and an eval forward."""
+    import copy
+
+    from determined_b200 import pytorch
+    from determined_b200.ops import conv as conv_ops
+
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+
+    def make():
+        return torch.nn.Sequential(torch.nn.Conv2d(3, 32, 3, padding=1, bias=False), torch.nn.BatchNorm2d(32), torch.nn.ReLU(),
+                                   torch.nn.Conv2d(32, 64, 3, stride=2, padding=1, bias=False), torch.nn.BatchNorm2d(64), torch.nn.ReLU(),
+                                   torch.nn.Conv2d(64, 64, 1, bias=True), torch.nn.AdaptiveAvgPool2d(1), torch.nn.Flatten(),
+                                   torch.nn.Linear(64, 10)).to(dev).to(memory_format=torch.channels_last)
+
+    base = make()
+    ref = copy.deepcopy(base)
+    ro = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+    with pytorch.init(hparams={"global_batch_size": 16}, aggregation_frequency=2) as ctx:
+        model = ctx.wrap_model(copy.deepcopy(base))
+        opt = ctx.wrap_optimizer(torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9))
+        convs = [m for m in model.modules() if isinstance(m, conv_ops.FusedConv2d)]
+        assert len(convs) == 3 and convs[0]._detb200_lowp_weight is not None and convs[0]._detb200_lowp_weight.dtype == torch.bfloat16
+        eng = ctx._get_engine()
+        rec = next(iter(eng.records.values()))
+        assert rec.sink is not None and rec.shadow is not None
+        g = torch.Generator().manual_seed(3)
+        for i in range(6):
+            ctx._current_batch_idx = i
+            x = torch.randn(16, 3, 16, 16, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
+            y = torch.randint(0, 10, (16,), generator=g).to(dev)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = torch.nn.functional.cross_entropy(model(x).float(), y)
+                rl = torch.nn.functional.cross_entropy(ref(x).float(), y)
+            ctx.backward(loss)
+            (rl / 2).backward()
+            if i % 2 == 1:
+                # compare the accumulated gradients before they are consumed (ours are averaged by the step: x2 here)
+                for (n1, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+                    torch.testing.assert_close(p.grad / 2, q.grad, rtol=3e-2, atol=3e-3, msg=lambda m, n1=n1: f"{n1}: {m}")
+                ctx.step_optimizer(opt)
+                ro.step()
+                ro.zero_grad()
+                with torch.no_grad():               # WGAN-style clamp through .data: invisible to version counters
+                    for p, q in zip(model.parameters(), ref.parameters()):
+                        p.data.clamp_(-0.5, 0.5)
+                        q.data.clamp_(-0.5, 0.5)
+            else:
+                ctx.step_optimizer(opt)             # not a boundary: a no-op
+            torch.testing.assert_close(loss, rl, rtol=2e-2, atol=2e-2)
+        for p, q in zip(model.parameters(), ref.parameters()):
+            torch.testing.assert_close(p, q, rtol=2e-2, atol=3e-3)
+        # the mirror is what the convolutions read: after the clamp + refresh it equals the rounded parameters
+        model.eval()
+        ref.eval()
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            xe = torch.randn(4, 3, 16, 16, device=dev).contiguous(memory_format=torch.channels_last)
+            torch.testing.assert_close(model(xe).float(), ref(xe).float(), rtol=3e-2, atol=3e-2)
+        torch.testing.assert_close(convs[0]._detb200_lowp_weight.float(), convs[0].weight.detach().to(torch.bfloat16).float())
+        # outside autocast, and for a bare loss.backward(), the module is a plain Conv2d again
+        model.train()
+        out = model(xe)
+        assert out.dtype == torch.float32
+        out.sum().backward()
