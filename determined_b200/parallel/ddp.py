@@ -383,7 +383,10 @@ class FusedGradEngine(GradEngineBase):
             ctas = None                      # default budget: the rest of the GPU is busy with backward
         else:
             stream = cur
-            ctas = 148
+            # nothing else is running: the peer-to-peer kernel wants every SM (its loads are latency-bound), the in-switch
+            # reduction is fastest from 8-16 CTAs (8 x B200, 45 MB: 0.127 ms with 16 CTAs, 0.154 ms with 148;
+            # profiles/r2_allreduce_sweep_n8.json)
+            ctas = 16 if rec.transport_nvls else 148
         scale = self._scale_of(rec)
         ils = rec.inv_scale if rec.unscaled_in_flight else None
         finf = rec.found_inf if rec.unscaled_in_flight else None
@@ -748,7 +751,7 @@ class FusedAllReduceHook:
                 # everything is staged: one collective over the whole buffer with every SM, then scatter the result back
                 self.group.begin_step()
                 comm.allreduce_fused(self.group, self.peers, 0, self.total, 1.0 / self.world, stream=cur,
-                                     timeout_s=self.timeout_s, mc_ptr=self.mc, max_ctas=148)
+                                     timeout_s=self.timeout_s, mc_ptr=self.mc, max_ctas=16 if self.mc else 148)
                 self.launches += 1
                 for idx, g in self._pending:
                     o, m = self.layout[idx]
