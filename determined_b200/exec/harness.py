@@ -23,7 +23,11 @@ def _run_pytorch_trial(trial_class: Type[Any], info: det.ClusterInfo) -> int:
     with pytorch.init() as ctx:
         if ctx.distributed.rank != 0:
             logging.getLogger().setLevel(logging.WARNING)
-        if (cfg.get("optimizations") or {}).get("cuda_graphs"):
+        opt = cfg.get("optimizations") or {}
+        if opt.get("fused_engine") is not None or opt.get("bucket_cap_mb") is not None or opt.get("grad_overlap") is not None:
+            ctx.experimental.use_fused_engine(opt.get("fused_engine"), bucket_cap_mb=float(opt.get("bucket_cap_mb") or 25.0),
+                                              overlap=opt.get("grad_overlap"))
+        if opt.get("cuda_graphs"):
             ctx.experimental.enable_cuda_graphs(True)
         if (cfg.get("optimizations") or {}).get("async_checkpoint"):
             ctx.experimental.enable_async_checkpoint(True)

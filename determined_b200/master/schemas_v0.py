@@ -238,7 +238,10 @@ obj("optimizations", {"aggregation_frequency": n("integer", 1, minimum=1), "auto
                       "tensor_fusion_cycle_time": n("integer", 1, minimum=0), "tensor_fusion_threshold": n("integer", 64, minimum=0),
                       # this build's own switches (no counterpart in the reference schema): replay train_batch as a CUDA graph,
                       # write periodic checkpoints from a background thread
-                      "cuda_graphs": n("boolean"), "async_checkpoint": n("boolean")})
+                      "cuda_graphs": n("boolean"), "async_checkpoint": n("boolean"),
+                      # the gradient engine: force the flat-buffer engine on/off (default: on for CUDA), bucket size of the overlapped
+                      # exchange, and whether to overlap it with backward at all (default: by gradient volume)
+                      "fused_engine": n("boolean"), "bucket_cap_mb": n("number", None, exclusiveMinimum=0), "grad_overlap": n("boolean")})
 obj("profiling", {"enabled": n("boolean", False), "begin_on_batch": n("integer", 0, minimum=0), "end_after_batch": n("integer", None, minimum=0),
                   "sync_timings": n("boolean", True)}, compareProperties={"type": "a<=b", "a": "begin_on_batch", "b": "end_after_batch"})
 obj("reproducibility", {"experiment_seed": n("integer", None, minimum=0)}, later=["experiment_seed"])

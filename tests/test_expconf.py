@@ -35,11 +35,11 @@ def test_adaptive_asha_defaults():
     ("resources: {slots_per_trial: two}", "slots_per_trial"),
     ("optimizations: {mixed_precision: O9}", "mixed_precision"),
     ("checkpoint_policy: sometimes", "checkpoint_policy"),
-    ("bogus_key: 1", "unknown field"),
+    ("bogus_key: 1", "additional property 'bogus_key'"),
     ("optimizations: {aggregation_frequency: 0}", "aggregation_frequency"),
     ("hyperparameters: {lr: {type: double, minval: 3, maxval: 1}}", "minval"),
-    ("hyperparameters: {lr: {type: weird}}", "unknown hyperparameter type"),
-    ("min_validation_period: {batches: 1, epochs: 2}", "exactly one"),
+    ("hyperparameters: {lr: {type: weird}}", "it must be one of"),
+    ("min_validation_period: {batches: 1, epochs: 2}", "must have one attribute"),
 ])
 def test_sanity_errors(bad, frag):
     with pytest.raises(expconf.ConfigError) as e:
