@@ -94,7 +94,8 @@ def flash_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: b
     if not q.is_cuda:
         return _sdpa(q, k, v, causal, scale, layout)
     if q.dtype != torch.bfloat16 or D not in (64, 128):
-        raise ValueError(f"flash_attention: bf16 inputs with head dim 64 or 128 required on CUDA (got {q.dtype}, D={D})")
+        _warn_fallback(D, q.dtype)
+        return _sdpa(q, k, v, causal, scale, layout)
     return _FlashAttnFn.apply(q, k, v, causal, scale, layout)
 
 
@@ -169,5 +170,37 @@ def attention_qkvpacked(qkv: torch.Tensor, rope: Optional[Tuple[torch.Tensor, to
     scale = float(scale) if scale is not None else 1.0 / math.sqrt(D)
     cos, sin = (rope if (rope is not None and rot) else (None, None))
     if qkv.is_cuda and (qkv.dtype != torch.bfloat16 or D not in (64, 128)):
-        raise ValueError(f"attention_qkvpacked: bf16 with head dim 64 or 128 required on CUDA (got {qkv.dtype}, D={D})")
+        # the tcgen05 kernels are built for head dims 64 and 128 (TMEM column budget); anything else (GPT-NeoX 2.7B: 80)
+        # goes through torch's attention with a differentiable rotary, so the model still trains, at library speed
+        _warn_fallback(D, qkv.dtype)
+        return _qkvpacked_torch(qkv, cos, sin, rot if cos is not None else 0, causal, scale)
     return _QKVPackedFn.apply(qkv, cos, sin, rot if cos is not None else 0, causal, scale)
+
+
+_warned = set()
+
+
+def _warn_fallback(D: int, dtype: torch.dtype) -> None:
+    if (D, dtype) not in _warned:
+        _warned.add((D, dtype))
+        import logging
+
+        logging.getLogger("determined.ops").warning(
+            "attention: head dim %d / %s is outside the native kernels (bf16, 64 or 128): using torch scaled_dot_product_attention", D, dtype)
+
+
+def _rope_torch(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, rot: int) -> torch.Tensor:
+    """Out-of-place, differentiable form of ``fused.rotary_qkv_`` for one of Q / K: ``x`` is ``[B, S, H, D]``."""
+    half = rot // 2
+    c = cos[None, :, None, :].to(x.dtype)
+    s_ = sin[None, :, None, :].to(x.dtype)
+    x1, x2 = x[..., :half], x[..., half:rot]
+    return torch.cat([x1 * c - x2 * s_, x2 * c + x1 * s_, x[..., rot:]], dim=-1)
+
+
+def _qkvpacked_torch(qkv: torch.Tensor, cos: Optional[torch.Tensor], sin: Optional[torch.Tensor], rot: int, causal: bool,
+                     scale: float) -> torch.Tensor:
+    q, k, v = qkv.unbind(2)
+    if rot:
+        q, k = _rope_torch(q, cos, sin, rot), _rope_torch(k, cos, sin, rot)
+    return _sdpa(q, k, v, causal, scale, "bshd").contiguous()

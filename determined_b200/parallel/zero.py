@@ -706,7 +706,11 @@ class ZeroEngine:
             if save_latest:
                 (pathlib.Path(save_dir) / "latest").write_text(str(tag))
         if self._native:
-            opt = {"m": self.m.cpu(), "v": self.v.cpu(), "step": int(self.step_dev.item()), "buckets": self.buckets, "world": self.world}
+            opt = {"m": self.m.cpu(), "v": self.v.cpu(), "step": int(self.step_dev.item()), "buckets": self.buckets, "world": self.world,
+                   # where every parameter sits in the flat buffer (the padding depends on the world size): what a run with
+                   # another world size needs to find its own slices in these shards
+                   "slots": [(sl.offset, sl.numel) for sl in self.layout.slots],
+                   "shard_slots": [(sl.offset, sl.numel) for sl in self.shard_layout.slots] if self.shard_layout is not None else []}
             if self.shard_layout is not None:
                 opt.update(shard_m=self.shard_m.cpu(), shard_v=self.shard_v.cpu(), shard_total=self.shard_layout.total)
         else:
@@ -735,20 +739,74 @@ class ZeroEngine:
         if load_optimizer_states and of.exists():
             opt = torch.load(of, map_location="cpu", weights_only=False)
             if self._native and "m" in opt:
-                if opt.get("world") != self.world or [tuple(b) for b in opt.get("buckets", [])] != [tuple(b) for b in self.buckets]:
-                    raise RuntimeError("optimizer shards were saved with a different world size / bucket plan; "
-                                       "re-sharding is not supported yet")
-                self.m.copy_(opt["m"])
-                self.v.copy_(opt["v"])
-                if self.shard_layout is not None and "shard_m" in opt:
-                    if int(opt.get("shard_total", -1)) != self.shard_layout.total:
-                        raise RuntimeError("weight-shard optimizer state was saved for a different partitioning")
-                    self.shard_m.copy_(opt["shard_m"])
-                    self.shard_v.copy_(opt["shard_v"])
+                same = opt.get("world") == self.world and [tuple(b) for b in opt.get("buckets", [])] == [tuple(b) for b in self.buckets]
+                if same:
+                    self.m.copy_(opt["m"])
+                    self.v.copy_(opt["v"])
+                    if self.shard_layout is not None and "shard_m" in opt:
+                        if int(opt.get("shard_total", -1)) != self.shard_layout.total:
+                            raise RuntimeError("weight-shard optimizer state was saved for a different partitioning")
+                        self.shard_m.copy_(opt["shard_m"])
+                        self.shard_v.copy_(opt["shard_v"])
+                else:
+                    # saved by another world size (or bucket plan): rebuild the full moments from every rank's file and cut
+                    # this rank's slices out of them
+                    old_world = int(opt["world"])
+                    files = [torch.load(d / f"zero_pp_rank_{r}_mp_rank_00_optim_states.pt", map_location="cpu", weights_only=False)
+                             for r in range(old_world)]
+                    new_slots = [(sl.offset, sl.numel) for sl in self.layout.slots]
+                    for name, dst in (("m", self.m), ("v", self.v)):
+                        dst.copy_(reshard_flat_state([f[name] for f in files], files[0]["buckets"], files[0]["slots"], old_world,
+                                                     self.buckets, new_slots, self.layout.total, self.rank, self.world))
+                    if self.shard_layout is not None and "shard_m" in files[0]:
+                        ns = [(sl.offset, sl.numel) for sl in self.shard_layout.slots]
+                        for name, dst in (("shard_m", self.shard_m), ("shard_v", self.shard_v)):
+                            dst.copy_(reshard_row_shards([f[name] for f in files], files[0]["shard_slots"], ns, self.shard_layout.total,
+                                                         self.rank, self.world))
                 self.step_dev.fill_(int(opt["step"]))
             elif not self._native and "torch_opt" in opt:
                 self._torch_opt.load_state_dict(opt["torch_opt"])
         return str(d), ms.get("client_state", {})
+
+
+def reshard_flat_state(shards: List[torch.Tensor], old_buckets: Any, old_slots: Any, old_world: int, new_buckets: Any, new_slots: Any,
+                       new_total: int, rank: int, world: int) -> torch.Tensor:
+    """Optimizer state of the replicated-path parameters, saved as per-rank bucket shards by ``old_world`` ranks, re-cut for
+    rank ``rank`` of ``world``.  Within a bucket ``(off, n)`` rank r holds elements ``[off + r n/W, off + (r+1) n/W)`` of the flat
+    buffer; parameters sit at different flat offsets under another world size (alignment is 4 x world), so the state goes
+    shards -> old flat buffer -> per parameter -> new flat buffer -> new shards."""
+    old_total = max(off + n for off, n in old_buckets)
+    full_old = torch.zeros(old_total, dtype=shards[0].dtype)
+    cursor = [0] * old_world
+    for off, n in old_buckets:
+        per = n // old_world
+        for r in range(old_world):
+            full_old[off + r * per: off + (r + 1) * per] = shards[r][cursor[r]: cursor[r] + per]
+            cursor[r] += per
+    if len(old_slots) != len(new_slots) or any(a[1] != b[1] for a, b in zip(old_slots, new_slots)):
+        raise RuntimeError("optimizer shards belong to a different set of parameters")
+    full_new = torch.zeros(new_total, dtype=shards[0].dtype)
+    for (oo, n), (no, _) in zip(old_slots, new_slots):
+        full_new[no: no + n] = full_old[oo: oo + n]
+    out = []
+    for off, n in new_buckets:
+        per = n // world
+        out.append(full_new[off + rank * per: off + (rank + 1) * per])
+    return torch.cat(out) if out else full_new[:0]
+
+
+def reshard_row_shards(shards: List[torch.Tensor], old_slots: Any, new_slots: Any, new_total: int, rank: int, world: int) -> torch.Tensor:
+    """State of row-partitioned weights (stage 3): rank r of W holds rows ``[r rows/W, (r+1) rows/W)`` of every weight,
+    flattened row-major, so the full state of a weight is the concatenation of the old ranks' slots."""
+    out = torch.zeros(new_total, dtype=shards[0].dtype)
+    if len(old_slots) != len(new_slots):
+        raise RuntimeError("weight-shard optimizer state belongs to a different set of partitioned weights")
+    for (oo, on), (no, nn_) in zip(old_slots, new_slots):
+        full = torch.cat([s[oo: oo + on] for s in shards])
+        if full.numel() != nn_ * world:
+            raise RuntimeError("a partitioned weight changed size between save and load")
+        out[no: no + nn_] = full[rank * nn_: (rank + 1) * nn_]
+    return out
 
 
 def initialize(args: Any = None, model: Optional[torch.nn.Module] = None, optimizer: Optional[torch.optim.Optimizer] = None,

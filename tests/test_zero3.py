@@ -140,3 +140,61 @@ def test_partition_pass_single_process():
     x = torch.randn(4, 16)
     m(x).sum().backward()
     assert m.wide.weight_shard.grad is not None and m.mlp2.fc1.weight_shard.grad.shape == m.mlp2.fc1.weight_shard.shape
+
+
+def test_optimizer_shards_are_recut_for_another_world_size():
+    """Save at world 8, load at world 4 (and 3 -> 2 with awkward sizes): the full moments rebuilt from the new shards equal the
+    full moments the old shards were cut from.  Pure tensor logic of the native path's checkpoint loader, on CPU."""
+    from determined_b200.parallel import zero
+
+    def layout(sizes, world):
+        align = 4 * world
+        slots, off = [], 0
+        for n in sizes:
+            slots.append((off, n))
+            off += (n + align - 1) // align * align
+        total = max(off, align)
+        # two buckets cut at a parameter boundary, listed last-layers-first like the engine does
+        cut = slots[len(slots) // 2][0]
+        return slots, total, [(cut, total - cut), (0, cut)]
+
+    def shards_of(full, buckets, world):
+        out = []
+        for r in range(world):
+            out.append(torch.cat([full[off + r * (n // world): off + (r + 1) * (n // world)] for off, n in buckets]))
+        return out
+
+    sizes = [5, 1000, 37, 4096, 129, 64]
+    for old_w, new_w in ((8, 4), (3, 2), (2, 8)):
+        o_slots, o_total, o_buckets = layout(sizes, old_w)
+        n_slots, n_total, n_buckets = layout(sizes, new_w)
+        per_param = [torch.randn(n) for n in sizes]
+        full_old = torch.zeros(o_total)
+        for (off, n), t in zip(o_slots, per_param):
+            full_old[off:off + n] = t
+        old = shards_of(full_old, o_buckets, old_w)
+        full_new = torch.zeros(n_total)
+        for r in range(new_w):
+            mine = zero.reshard_flat_state(old, o_buckets, o_slots, old_w, n_buckets, n_slots, n_total, r, new_w)
+            cur = 0
+            for off, n in n_buckets:
+                per = n // new_w
+                full_new[off + r * per: off + (r + 1) * per] = mine[cur:cur + per]
+                cur += per
+        for (off, n), t in zip(n_slots, per_param):
+            assert torch.equal(full_new[off:off + n], t)
+    # row-partitioned weights: 2 weights of 16x6 and 8x4 rows x cols, saved by 4 ranks, loaded by 2
+    ws = [torch.randn(16, 6), torch.randn(8, 4)]
+    def row_shards(world):
+        slots, off, per_rank = [], 0, [[] for _ in range(world)]
+        for w in ws:
+            rows = w.shape[0] // world
+            slots.append((off, rows * w.shape[1]))
+            off += rows * w.shape[1]
+            for r in range(world):
+                per_rank[r].append(w[r * rows:(r + 1) * rows].reshape(-1))
+        return slots, off, [torch.cat(p) for p in per_rank]
+    o_slots, _, old = row_shards(4)
+    n_slots, n_total, want = row_shards(2)
+    for r in range(2):
+        assert torch.equal(zero.reshard_row_shards(old, o_slots, n_slots, n_total, r, 2), want[r])
