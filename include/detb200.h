@@ -132,7 +132,9 @@ int detb200_allreduce_bf16(void* const* peer_stage, void* const* peer_ctrls, voi
                            int* found_inf, int first_of_step, int phases, int max_ctas, double timeout_s,
                            detb200_stream_t stream);
 /* rs_adam_ag with separate gradient / parameter offsets (ZeRO-2 reduces out of a landing buffer), gradient
- * accumulation into grad_shard in mode 1 (accumulate != 0) and the multicast variants. */
+ * accumulation into grad_shard in mode 1 (accumulate != 0) and the multicast variants.  mode 3: reduce into grad_shard like
+ * mode 1 but leave the step's statistics (sum of squares, non-finite count) alone and skip their exchange: for the
+ * non-final micro-steps of gradient accumulation, whose partial sums are not what the optimizer will see. */
 int detb200_rs_adam_ag_ex(void* const* peer_grad_bufs, void* const* peer_ctrls, void* const* peer_param_bufs /* nullable in mode 1 */,
                           void* mc_grad, void* mc_param, int param_is_bf16, int rank, int world,
                           int64_t grad_offset_elems, int64_t param_offset_elems, int64_t n_elems,
