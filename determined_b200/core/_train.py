@@ -96,7 +96,7 @@ class TrainContext:
             raise RuntimeError("report_early_exit() may only be called by the chief")
         reason = EarlyExitReason(reason)
         try:
-            self._session.post(f"/api/v1/trials/{self._trial_id}/early_exit", json={"earlyExit": {"reason": reason.value}, "reason": reason.value})
+            self._session.post(f"/api/v1/trials/{self._trial_id}/early_exit", json={"reason": reason.value})
         except api_errors.APIException as e:
             if e.status_code != 400:   # already reported
                 raise

@@ -39,6 +39,8 @@ class HTTPError(Exception):
 
 
 ROUTES: List[Tuple[str, "re.Pattern[str]", Callable, bool]] = []
+# conformance tests set this to see every (method, route pattern, request body, handler result) the server answers with 200
+RECORDER: Optional[Callable[[str, str, Any, Any], None]] = None
 
 
 def route(method: str, pattern: str, auth_required: bool = True) -> Callable:
@@ -769,19 +771,28 @@ def compare_trials(ctx: Ctx) -> Any:
 # -- custom searcher events ------------------------------------------------------------------------
 @route("GET", "/api/v1/experiments/{eid}/searcher_events")
 def searcher_events(ctx: Ctx, eid: str) -> Any:
-    deadline = time.time() + min(ctx.qi("timeout_seconds", 60), 120)
+    """Long poll for a client-side search method.  Pending events, oldest first; an experiment that is finished (or
+    paused with nothing pending when the poll runs out) answers with one ``experimentInactive`` event, which is how the
+    runner learns that it can stop (or should tell its user to activate the experiment)."""
+    deadline = time.time() + min(ctx.qi("timeoutSeconds", ctx.qi("timeout_seconds", 60)), 120)
+    inactive_id = 2 ** 31 - 1          # not part of the numbered queue: never acknowledged, never replayed
     while True:
         with ctx.m.lock:
             exp = ctx.m.experiments.get(int(eid))
             if exp is None:
-                _exp_row(ctx, eid)
-                return {"searcherEvents": []}
+                row = _exp_row(ctx, eid)
+                return {"searcherEvents": [{"id": inactive_id, "experimentInactive": {"experimentState": _state("STATE", row["state"])}}]}
             meth = exp.searcher.method
             if not isinstance(meth, S.CustomSearch):
                 raise HTTPError(400, "experiment does not use a custom searcher")
             if meth.events:
                 return {"searcherEvents": list(meth.events)}
+            if exp.state in core.TERMINAL:
+                return {"searcherEvents": [{"id": inactive_id, "experimentInactive": {"experimentState": _state("STATE", exp.state)}}]}
+            paused = exp.state == core.PAUSED
         if time.time() > deadline:
+            if paused:
+                return {"searcherEvents": [{"id": inactive_id, "experimentInactive": {"experimentState": "STATE_PAUSED"}}]}
             return {"searcherEvents": []}
         time.sleep(0.2)
 
@@ -1231,7 +1242,7 @@ def _agent_json(m: core.Master) -> Dict[str, Any]:
         g = m.gpus[i] if i < len(m.gpus) else None
         owner = ag.used.get(i)
         slots[str(i)] = {"id": str(i), "enabled": (ag.slot_enabled or [True] * ag.num_slots)[i],
-                         "device": {"id": i, "brand": g.name if g else "cpu", "uuid": g.uuid if g else f"cpu-{i}", "type": "TYPE_CUDA" if g else "TYPE_CPU"},
+                         "device": {"id": i, "brand": g.name if g else "cpu", "uuid": g.uuid if g else f"cpu-{i}", "type": "DEVICE_TYPE_CUDA" if g else "DEVICE_TYPE_CPU"},
                          "container": {"id": owner, "state": "STATE_RUNNING"} if owner else None, "draining": False}
     return {"id": m.agent_id, "registeredTime": _ts(m.start_time), "slots": slots, "resourcePools": [m.pool.name], "enabled": ag.enabled,
             "draining": False, "addresses": ["127.0.0.1"], "version": __version__, "label": ag.label}
@@ -1929,6 +1940,8 @@ class Handler(BaseHTTPRequestHandler):
             try:
                 with tracing.span(f"{method} {rx.pattern[1:-3]}", traceparent=self.headers.get("traceparent"), **{"http.method": method, "http.target": path}):
                     out = fn(ctx, **{k: urllib.parse.unquote(v) for k, v in mt.groupdict().items()})
+                if RECORDER is not None:
+                    RECORDER(method, rx.pattern[1:-3], body, out)
                 if isinstance(out, tuple):
                     self._send(200, out[1], out[0])
                 else:

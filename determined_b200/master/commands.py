@@ -30,6 +30,12 @@ from determined_b200.master import scheduler
 
 logger = logging.getLogger("determined.master.commands")
 
+
+def _iso(t: Optional[float]) -> Optional[str]:
+    if t is None:
+        return None
+    return time.strftime("%Y-%m-%dT%H:%M:%S", time.gmtime(t)) + (".%06dZ" % int((t % 1) * 1e6))
+
 TYPES = {"command": "COMMAND", "shell": "SHELL", "notebook": "NOTEBOOK", "tensorboard": "TENSORBOARD"}
 
 
@@ -94,7 +100,7 @@ class CommandTask:
         return f"cmd-{self.id}"
 
     def to_json(self) -> Dict[str, Any]:
-        return {"id": self.id, "description": self.description, "state": "STATE_" + self.state, "startTime": self.start_time, "endTime": self.end_time,
+        return {"id": self.id, "description": self.description, "state": "STATE_" + self.state, "startTime": _iso(self.start_time), "endTime": _iso(self.end_time),
                 "username": self.owner_name, "userId": self.owner_id, "resourcePool": (self.config.get("resources") or {}).get("resource_pool") or "default", "exitStatus": self.exit_code,
                 "jobId": self.id, "type": self.kind, "slots": self.slots, "slotIds": self.slot_ids, "config": self.config,
                 "serviceAddress": f"/proxy/{self.id}/" if self.service_port else None}

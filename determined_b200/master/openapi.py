@@ -20,7 +20,41 @@ def _operation_id(method: str, path: str) -> str:
     return (method.lower() + "_" + "_".join(words)).strip("_")
 
 
+def _shape(path: str) -> str:
+    """Route with parameter names blanked, for matching the route table against the rpc paths."""
+    return re.sub(r"\{[^}]*\}", "{}", path.rstrip("/"))
+
+
+def _typed(op: Dict[str, Any], rpc: Any, reg: Any) -> None:
+    from determined_b200.common.api import protolite
+
+    op["x-rpc"] = rpc.name
+    if rpc.doc:
+        op["summary"] = rpc.doc
+    ref = lambda full: {"$ref": "#/components/schemas/" + reg.binding_name(full)}  # noqa: E731
+    if rpc.response in reg.messages:
+        op["responses"]["200"]["content"]["application/json"]["schema"] = ref(rpc.response)
+    req = reg.messages.get(rpc.request)
+    if req is None:
+        return
+    top = {p.split(".")[0] for p in rpc.path_params if "." not in p}
+    if rpc.body == "*":
+        op["requestBody"] = {"required": True, "content": {"application/json": {"schema": ref(rpc.request)}}}
+        return
+    if rpc.body:
+        bf = next(f for f in req.fields if f.name == rpc.body)
+        op["requestBody"] = {"required": True, "content": {"application/json": {"schema": reg.field_schema(bf)}}}
+    for f in req.fields:
+        if f.name in top or f.name == rpc.body or (f.type in reg.messages and not f.repeated):
+            continue
+        op["parameters"].append({"name": protolite.json_name(f.name), "in": "query", "required": False, "schema": reg.field_schema(f)})
+
+
 def build(routes: Any) -> Dict[str, Any]:
+    from determined_b200.common.api import protolite
+
+    reg = protolite.load()
+    rpc_by_route = {(r.method.upper(), _shape(r.path)): r for r in reg.rpcs}
     paths: Dict[str, Dict[str, Any]] = {}
     seen = set()
     for method, rx, fn, need_auth in routes:
@@ -40,6 +74,10 @@ def build(routes: Any) -> Dict[str, Any]:
             op["requestBody"] = {"required": False, "content": {"application/json": {"schema": {"type": "object"}}}}
         if need_auth:
             op["security"] = [{"bearer": []}]
+        rpc = rpc_by_route.get((method, _shape(path)))
+        if rpc is not None:
+            _typed(op, rpc, reg)
         paths.setdefault(path, {})[method.lower()] = op
     return {"openapi": "3.0.3", "info": {"title": "determined_b200 master API", "version": __version__},
-            "components": {"securitySchemes": {"bearer": {"type": "http", "scheme": "bearer"}}}, "paths": dict(sorted(paths.items()))}
+            "components": {"securitySchemes": {"bearer": {"type": "http", "scheme": "bearer"}}, "schemas": reg.schemas()},
+            "paths": dict(sorted(paths.items()))}

@@ -528,7 +528,9 @@ class CustomSearch(SearchMethod):
         return self._push("trialClosed", requestId=request_id)
 
     def trial_exited_early(self, ctx: Context, request_id: str, reason: str) -> List[Op]:
-        return self._push("trialExitedEarly", requestId=request_id, exitedReason=f"EXITED_REASON_{reason}")
+        # the wire enum knows INVALID_HP / USER_REQUESTED_STOP / USER_CANCELED; a crash travels as UNSPECIFIED
+        wire = reason if reason in ("INVALID_HP", "USER_REQUESTED_STOP", "USER_CANCELED") else ("INVALID_HP" if reason == "INIT_INVALID_HP" else "UNSPECIFIED")
+        return self._push("trialExitedEarly", requestId=request_id, exitedReason=f"EXITED_REASON_{wire}")
 
     def trial_progress(self, request_id: str, partial_units: float) -> None:
         self._push("trialProgress", requestId=request_id, partialUnits=partial_units)
