@@ -21,7 +21,7 @@ import pathlib
 import pickle
 import time
 import uuid
-from typing import Any, Dict, List, Optional, Set, Tuple
+from typing import Any, Dict, List, Optional, Sequence, Set, Tuple
 
 import yaml
 
@@ -42,6 +42,7 @@ class SearcherState:
         self.trials_closed: Set[uuid.UUID] = set()
         self.trials_created: Set[uuid.UUID] = set()
         self.last_event_id: int = 0
+        self.experiment_id: Optional[int] = None
         self.experiment_completed: bool = False
         self.experiment_failed: bool = False
 
@@ -73,11 +74,23 @@ class ExitedReason(enum.Enum):
             s = "INVALID_HP"
         return cls(s)
 
+    @classmethod
+    def _from_bindings(cls, reason: Any) -> "ExitedReason":
+        """``v1TrialExitedEarlyExitedReason`` -> the method-facing reason (an unspecified reason is a crash)."""
+        name = getattr(reason, "name", str(reason))
+        return {"INVALID_HP": cls.INVALID_HP, "USER_REQUESTED_STOP": cls.USER_CANCELED, "USER_CANCELED": cls.USER_CANCELED}.get(name, cls.ERRORED)
+
 
 class Operation(metaclass=abc.ABCMeta):
     @abc.abstractmethod
     def _to_wire(self) -> Dict[str, Any]:
         ...
+
+    def _to_searcher_operation(self) -> Any:
+        """The typed form (``bindings.v1SearcherOperation``) of this operation."""
+        from determined_b200.common.api import bindings
+
+        return bindings.v1SearcherOperation.from_json(self._to_wire())
 
 
 class ValidateAfter(Operation):
@@ -171,92 +184,151 @@ class SearchMethod:
 
 
 class _ExperimentInactive(Exception):
-    def __init__(self, state: str) -> None:
+    def __init__(self, state: Any) -> None:
         self.exp_state = state
 
 
+def _rid(sub: Any) -> uuid.UUID:
+    return uuid.UUID(sub.requestId)
+
+
 class SearchRunner:
+    """The event loop between the master's queue of searcher events and a :class:`SearchMethod`.
+
+    Events and operations travel as the typed messages of ``common.api.bindings`` (``v1SearcherEvent`` in,
+    ``v1PostSearcherOperationsRequest`` out); ``get_events`` / ``post_operations`` are the two places that touch the
+    network and can be replaced (the reference's mock-master tests do exactly that)."""
+
+    poll_timeout = 30          # seconds the master may hold an idle GetSearcherEvents
+
     def __init__(self, search_method: SearchMethod) -> None:
         self.search_method = search_method
         self.state = SearcherState()
 
-    def _ops_for_event(self, ev: Dict[str, Any]) -> List[Operation]:
-        m, st = self.search_method, self.state
-        if "initialOperations" in ev:
-            return m.initial_operations(st)
-        if "trialCreated" in ev:
-            rid = uuid.UUID(ev["trialCreated"]["requestId"])
-            st.trials_created.add(rid)
-            st.trial_progress[rid] = 0.0
-            return m.on_trial_created(st, rid)
-        if "trialClosed" in ev:
-            rid = uuid.UUID(ev["trialClosed"]["requestId"])
-            st.trials_closed.add(rid)
-            ops = m.on_trial_closed(st, rid)
-            if not ops and st.trials_created and st.trials_closed >= st.trials_created and not st.experiment_completed:
-                pass
-            return ops
-        if "trialExitedEarly" in ev:
-            rid = uuid.UUID(ev["trialExitedEarly"]["requestId"])
-            reason = ExitedReason._from_wire(ev["trialExitedEarly"].get("exitedReason", "ERRORED"))
-            if reason == ExitedReason.INVALID_HP:
-                st.trial_progress.pop(rid, None)
-            elif reason == ExitedReason.ERRORED:
-                st.failures.add(rid)
-            return m.on_trial_exited_early(st, rid, reason)
-        if "validationCompleted" in ev:
-            v = ev["validationCompleted"]
-            rid = uuid.UUID(v["requestId"])
-            return m.on_validation_completed(st, rid, v.get("metric"), int(v.get("validateAfterLength", 0)))
-        if "trialProgress" in ev:
-            rid = uuid.UUID(ev["trialProgress"]["requestId"])
-            st.trial_progress[rid] = float(ev["trialProgress"].get("partialUnits", 0))
-            return [Progress(m.progress(st))]
-        if "experimentInactive" in ev:
-            raise _ExperimentInactive(ev["experimentInactive"].get("experimentState", ""))
-        raise RuntimeError(f"Unsupported searcher event: {ev}")
+    # ---- one event -> the method's answer ----------------------------------------------------------------------------------
+    def _on_initial(self, sub: Any) -> List[Operation]:
+        return self.search_method.initial_operations(self.state)
 
+    def _on_created(self, sub: Any) -> List[Operation]:
+        rid = _rid(sub)
+        self.state.trials_created.add(rid)
+        self.state.trial_progress[rid] = 0.0
+        return self.search_method.on_trial_created(self.state, rid)
+
+    def _on_closed(self, sub: Any) -> List[Operation]:
+        rid = _rid(sub)
+        self.state.trials_closed.add(rid)
+        return self._with_progress(self.search_method.on_trial_closed(self.state, rid))
+
+    def _on_exited_early(self, sub: Any) -> List[Operation]:
+        from determined_b200.common.api import bindings
+
+        if sub.exitedReason is None:
+            raise RuntimeError("trialExitedEarly event is invalid without exitedReason")
+        rid = _rid(sub)
+        if sub.exitedReason == bindings.v1TrialExitedEarlyExitedReason.INVALID_HP:
+            self.state.trial_progress.pop(rid, None)          # the trial never counted
+        elif sub.exitedReason == bindings.v1TrialExitedEarlyExitedReason.UNSPECIFIED:
+            self.state.failures.add(rid)
+        return self._with_progress(self.search_method.on_trial_exited_early(self.state, rid, exited_reason=ExitedReason._from_bindings(sub.exitedReason)))
+
+    def _on_validation(self, sub: Any) -> List[Operation]:
+        if sub.metric is None:
+            raise RuntimeError("validationCompleted event is invalid without a metric")
+        ops = self.search_method.on_validation_completed(self.state, _rid(sub), sub.metric, int(sub.validateAfterLength))
+        return self._with_progress(ops)
+
+    def _on_progress(self, sub: Any) -> List[Operation]:
+        self.state.trial_progress[_rid(sub)] = float(sub.partialUnits)
+        return self._with_progress([])
+
+    def _on_inactive(self, sub: Any) -> List[Operation]:
+        raise _ExperimentInactive(sub.experimentState)
+
+    def _with_progress(self, ops: List[Operation]) -> List[Operation]:
+        return list(ops) + [Progress(self.search_method.progress(self.state))]
+
+    _HANDLERS = (("initialOperations", "_on_initial"), ("trialCreated", "_on_created"), ("trialClosed", "_on_closed"),
+                 ("trialExitedEarly", "_on_exited_early"), ("validationCompleted", "_on_validation"),
+                 ("experimentInactive", "_on_inactive"), ("trialProgress", "_on_progress"))
+
+    def _get_operations(self, event: Any) -> List[Operation]:
+        for member, handler in self._HANDLERS:
+            sub = getattr(event, member)
+            if sub:
+                logger.debug("searcher event %s: %s", event.id, member)
+                return getattr(self, handler)(sub)
+        raise RuntimeError(f"Unsupported event {event}")
+
+    # ---- the loop -----------------------------------------------------------------------------------------------------------
     def run_experiment(self, experiment_id: int, session: api.Session, prior_operations: Optional[List[Operation]] = None,
-                       poll_timeout: int = 30) -> None:
-        done = False
-        while not done:
-            events = self.get_events(session, experiment_id, poll_timeout)
-            if not events:
-                e = session.get(f"/api/v1/experiments/{experiment_id}").json()["experiment"]
-                if e["state"] in ("STATE_COMPLETED", "STATE_CANCELED", "STATE_ERROR"):
-                    self.state.experiment_completed = True
-                    return
-                if e["state"] == "STATE_PAUSED":
-                    self._show_experiment_paused_msg()
-                    time.sleep(2)
-                continue
-            for ev in events:
-                if ev["id"] <= self.state.last_event_id:
-                    ops: List[Operation] = list(prior_operations or [])     # replay after a crash between save and post
-                else:
-                    ops = self._ops_for_event(ev)
-                    self.state.last_event_id = ev["id"]
-                    self.save_state(experiment_id, ops)
-                if any(isinstance(o, Shutdown) for o in ops):
-                    done = True
-                    self.state.experiment_completed = True
-                self.post_operations(session, experiment_id, ev, ops)
+                       sleep_time: float = 0.0) -> None:
+        """Until the experiment goes inactive: fetch the pending events, answer each one.  The state is saved BEFORE the
+        answer is posted; if the process died in between, the first event of the next fetch is one the saved state has seen,
+        and the saved ``prior_operations`` are posted again instead of asking the method twice."""
+        from determined_b200.common.api import bindings
+
+        self.state.experiment_id = experiment_id
+        active = True
+        try:
+            while active:
+                if sleep_time:
+                    time.sleep(sleep_time)
+                events = self.get_events(session, experiment_id)
+                if not events:
+                    continue
+                seen_before = self.state.last_event_id
+                for n, event in enumerate(events):
+                    if n == 0 and prior_operations is not None and 0 <= event.id <= seen_before and seen_before != 0:
+                        logger.info("re-posting the saved operations for event %d", event.id)
+                        ops = prior_operations
+                    elif event.experimentInactive:
+                        st = event.experimentInactive.experimentState
+                        logger.info("experiment %s is inactive: %s", experiment_id, st)
+                        self.state.experiment_completed = self.state.experiment_completed or st == bindings.experimentv1State.COMPLETED
+                        self.state.experiment_failed = self.state.experiment_failed or st == bindings.experimentv1State.ERROR
+                        if st == bindings.experimentv1State.PAUSED:
+                            self._show_experiment_paused_msg()
+                        else:
+                            active = False
+                        break
+                    else:
+                        ops = self._get_operations(event)
+                        self.state.last_event_id = event.id
+                        self.save_state(experiment_id, ops)
+                    self.post_operations(session, experiment_id, event, ops)
                 prior_operations = None
+        except KeyboardInterrupt:
+            print("Runner interrupted")
 
-    def post_operations(self, session: api.Session, experiment_id: int, event: Dict[str, Any], operations: List[Operation]) -> None:
-        session.post(f"/api/v1/experiments/{experiment_id}/searcher_operations",
-                     json={"experimentId": experiment_id, "searcherOperations": [o._to_wire() for o in operations],
-                           "triggeredByEvent": {"id": event["id"]}})
+    def post_operations(self, session: api.Session, experiment_id: int, event: Any, operations: List[Operation]) -> None:
+        from determined_b200.common.api import bindings
 
-    def get_events(self, session: api.Session, experiment_id: int, timeout: int = 30) -> List[Dict[str, Any]]:
-        r = session.get(f"/api/v1/experiments/{experiment_id}/searcher_events", params={"timeout_seconds": timeout}, timeout=timeout + 15)
-        return r.json().get("searcherEvents", [])
+        body = bindings.v1PostSearcherOperationsRequest(experimentId=experiment_id, triggeredByEvent=event,
+                                                        searcherOperations=[o._to_searcher_operation() for o in operations])
+        try:
+            bindings.post_PostSearcherOperations(session, body=body, experimentId=experiment_id)
+        except api.errors.APIException as e:
+            # a trial that exits on its own (an autotuning probe) can be gone before its Close arrives: not an error
+            if any(isinstance(o, Close) for o in operations) and "could not be found" in str(e):
+                logger.warning("ignoring %s", e)
+            else:
+                raise
+
+    def get_events(self, session: api.Session, experiment_id: int) -> Optional[Sequence[Any]]:
+        from determined_b200.common.api import bindings
+
+        return bindings.get_GetSearcherEvents(session, experimentId=experiment_id, timeoutSeconds=self.poll_timeout).searcherEvents or []
 
     def save_state(self, experiment_id: int, operations: List[Operation]) -> None:
         pass
 
     def _show_experiment_paused_msg(self) -> None:
         logger.warning("Experiment is paused; activate it to continue the search.")
+
+    @staticmethod
+    def _searcher_event_as_dict(event: Any) -> Dict[str, Any]:
+        return {k: v for k, v in event.to_json().items() if v is not None}
 
 
 class LocalSearchRunner(SearchRunner):
@@ -268,7 +340,8 @@ class LocalSearchRunner(SearchRunner):
         self.session = session
         self.searcher_dir.mkdir(parents=True, exist_ok=True)
 
-    def run(self, exp_config: Any, model_dir: Optional[str] = None, includes: Any = None) -> int:
+    def run(self, exp_config: Any, context_dir: Optional[str] = None, includes: Any = None, model_dir: Optional[str] = None) -> int:
+        model_dir = model_dir or context_dir
         sess = self.session or api.authentication.login_with_cache(os.environ.get("DET_MASTER", "http://127.0.0.1:8080"))
         marker = self.searcher_dir / "experiment_id"
         prior: Optional[List[Operation]] = None
@@ -286,18 +359,18 @@ class LocalSearchRunner(SearchRunner):
         self.run_experiment(eid, sess, prior)
         return eid
 
-    def _state_path(self, experiment_id: int) -> pathlib.Path:
+    def _get_state_path(self, experiment_id: int) -> pathlib.Path:
         return self.searcher_dir / f"exp_{experiment_id}"
 
     def load_state(self, experiment_id: int) -> Tuple[int, List[Operation]]:
-        p = self._state_path(experiment_id)
+        p = self._get_state_path(experiment_id)
         self.state, eid = self.search_method.load(p)
         with (p / "ops").open("rb") as f:
             ops = pickle.load(f)
         return eid, ops
 
     def save_state(self, experiment_id: int, operations: List[Operation]) -> None:
-        p = self._state_path(experiment_id)
+        p = self._get_state_path(experiment_id)
         self.search_method.save(self.state, p, experiment_id=experiment_id)
         tmp = p / "ops.tmp"
         with tmp.open("wb") as f:
@@ -314,8 +387,10 @@ class RemoteSearchRunner(SearchRunner):
         self.context = context
         self.latest_checkpoint: Optional[str] = None
 
-    def run(self, exp_config: Any, model_dir: Optional[str] = None, includes: Any = None) -> int:
+    def run(self, exp_config: Any, context_dir: Optional[str] = None, includes: Any = None, model_dir: Optional[str] = None) -> int:
         import determined_b200 as det
+
+        model_dir = model_dir or context_dir
 
         info = det.get_cluster_info()
         assert info is not None, "RemoteSearchRunner only runs on-cluster"

@@ -56,6 +56,8 @@ REF_TESTS = [
     ("tests/experiment/pytorch/test_pytorch_trial.py",
      "not gpu_parallel and not test_onevar_single and not test_training_metrics and not test_variable_workload_size and not "
      "test_reject_unnamed_nondict_metric and not test_trainer_disable_tb_logging", 36),
+    # client-side custom search: the runner loop against the reference's mock master (typed searcher events from the bindings)
+    ("tests/test_custom_searcher.py", "", 2),
     ("tests/common/test_yaml.py", "", 4),
     ("tests/common/test_api.py", "", 15),                                       # master URL canonicalisation
     ("tests/launch/test_wrap_rank.py", "", 1),
