@@ -14,7 +14,7 @@ import pickle
 from typing import Any, Dict, Type
 
 import determined_b200 as det
-from determined_b200 import core, searcher
+from determined_b200 import core, searcher, util
 from determined_b200.pytorch.dsat import _dsat_search_method as sm
 from determined_b200.pytorch.dsat import _utils, defaults
 
@@ -38,8 +38,11 @@ def get_custom_dsat_exp_conf_from_args(args: argparse.Namespace) -> Dict[str, An
     conf["name"] = f"{conf['name']} (autotune trials)"
     conf["searcher"] = {"name": "custom", "metric": args.metric, "smaller_is_better": _utils.smaller_is_better(args.metric)}
     conf["max_restarts"] = 0
-    conf.setdefault("hyperparameters", {})
     conf.setdefault("resources", {}).setdefault("slots_per_trial", 1)
+    # every trial runs the engine's probe between these steps, and the trial controller takes its autotuning path
+    probe = {"autotuning": dict(defaults.AUTOTUNING_DICT["autotuning"], start_profile_step=args.start_profile_step, end_profile_step=args.end_profile_step)}
+    conf["hyperparameters"] = util.merge_dicts(conf.get("hyperparameters") or {}, {defaults.OVERWRITE_KEY: probe})
+    conf["hyperparameters"][defaults.USE_DSAT_MODE_KEY] = True
     return conf
 
 

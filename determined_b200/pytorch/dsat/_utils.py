@@ -79,35 +79,47 @@ def get_dict_from_yaml_or_json_path(path: str) -> Dict[str, Any]:
 
 @contextlib.contextmanager
 def dsat_reporting_context(core_context: core.Context, op: core.SearcherOperation, steps_completed: Optional[int] = None) -> Generator[None, None, None]:
-    """Wrap the training loop of an autotune trial: when the engine's profiling run ends (it
-    raises ``SystemExit`` after writing its result JSON) the result is reported as validation
-    metrics and the searcher op completed; out-of-memory errors are reported as such so the search
-    method can shrink the batch size instead of the trial being retried."""
+    """Wrap the training loop of an autotuning trial (``engine.forward`` / ``backward`` / ``step`` inside).  When the
+    engine's probe ends it writes its result file and exits the process; the ``SystemExit`` is caught here, the file is
+    reported as the trial's validation metrics and its searcher operation completed, and the exit continues.  A crash (out
+    of memory, typically) is NOT caught: with ``max_restarts: 0`` it reaches the search method as an early exit, which is
+    the signal to lower the micro-batch ceiling."""
     steps_completed = op.length if steps_completed is None else steps_completed
     try:
         yield
-    except SystemExit as e:
-        p = next((pathlib.Path(x) for x in (defaults.MODEL_INFO_PROFILING_PATH, defaults.AUTOTUNING_RESULTS_PATH) if pathlib.Path(x).exists()), None)
-        if p is None:
-            raise
-        report_json_results(core_context, op, steps_completed, p)
-        raise e
-    except RuntimeError as e:
-        if "out of memory" in str(e).lower():
-            if core_context.distributed.rank == 0:
-                core_context.train.report_validation_metrics(steps_completed=steps_completed, metrics={"OOM": True})
-                op.report_completed({"OOM": True})
+    except SystemExit:
+        found = [pathlib.Path(x) for x in (defaults.MODEL_INFO_PROFILING_PATH, defaults.AUTOTUNING_RESULTS_PATH) if pathlib.Path(x).exists()]
+        if len(found) == 1:          # a properly ended probe leaves exactly one of them
+            report_json_results(core_context, op, steps_completed, found[0], add_gpu_info=found[0].name == defaults.MODEL_INFO_PROFILING_PATH)
         raise
 
 
-def report_json_results(core_context: core.Context, op: core.SearcherOperation, steps_completed: int, path: Union[str, pathlib.Path]) -> None:
-    if core_context.distributed.rank != 0:
-        return
-    results = json.loads(pathlib.Path(path).read_text())
-    core_context.train.report_validation_metrics(steps_completed=steps_completed, metrics=results)
-    op.report_completed(results)
+def device_memory_bytes() -> int:
+    """Memory of the device a trial runs on: HBM of GPU 0, or the host's RAM for CPU trials."""
+    import torch
+
+    if torch.cuda.is_available():
+        return int(torch.cuda.get_device_properties(0).total_memory)
     try:
-        core_context.searcher.acknowledge_out_of_ops()
+        import psutil
+
+        return int(psutil.virtual_memory().total)
+    except Exception:
+        return 0
+
+
+def report_json_results(core_context: core.Context, op: core.SearcherOperation, steps_completed: int, path: Union[str, pathlib.Path],
+                        add_gpu_info: bool = False) -> None:
+    if core_context.distributed.rank == 0:
+        results = json.loads(pathlib.Path(path).read_text())
+        if add_gpu_info:
+            results["gpu_mem"] = device_memory_bytes()
+        core_context.train.report_validation_metrics(steps_completed=steps_completed, metrics=results)
+        op.report_completed(results)
+    try:           # a probe trial has exactly one operation: drain the generator so the master sees it acknowledged
+        next(core_context.searcher.operations())
+    except StopIteration:
+        pass
     except Exception:
         pass
 

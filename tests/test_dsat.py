@@ -60,14 +60,17 @@ def drive(method, cluster, max_events=500):
             res = cluster.run(trial)
             if res is None:
                 pending += method.on_trial_exited_early(st, op.request_id, searcher.ExitedReason.ERRORED)
+                st.trials_closed.add(op.request_id)
                 pending += method.on_trial_closed(st, op.request_id)
             else:
                 pending += method.on_validation_completed(st, op.request_id, res, op.length)
         elif isinstance(op, searcher.Close):
+            st.trials_closed.add(op.request_id)
             pending += method.on_trial_closed(st, op.request_id)
         elif isinstance(op, searcher.Shutdown):
             shutdown = op
             break
+    method.last_state = st
     return shutdown, created
 
 
@@ -102,7 +105,7 @@ def test_search_finds_feasible_best_and_shuts_down(tmp_path, name):
     assert tr.num_running_trials == 0
     best = tr.best_trial
     assert best is not None and not best.error and best.mbs <= c.limit(best.stage)
-    assert 0.0 < m.progress(searcher.SearcherState()) <= 1.0
+    assert 0.0 < m.progress(m.last_state) <= 1.0
     # every trial's overwrite block is a consistent batch config
     for _, t in tr:
         ow = t.hparams[defaults.OVERWRITE_KEY]
@@ -127,7 +130,13 @@ def test_profile_trial_failure_fails_search(tmp_path):
     m = dsat.RandomDSATSearchMethod(args, dsat.get_custom_dsat_exp_conf_from_args(args))
     st = searcher.SearcherState()
     ops = m.initial_operations(st)
-    out = m.on_trial_exited_early(st, ops[0].request_id, searcher.ExitedReason.ERRORED)
+    assert m.on_trial_exited_early(st, ops[0].request_id, searcher.ExitedReason.ERRORED) == []      # a crash: handled when the trial closes
+    out = m.on_trial_closed(st, ops[0].request_id)
+    assert len(out) == 1 and isinstance(out[0], searcher.Shutdown) and out[0].failure
+    # an invalid hyperparameter or a user's cancel ends the job at once
+    m2 = dsat.RandomDSATSearchMethod(args, dsat.get_custom_dsat_exp_conf_from_args(args))
+    ops = m2.initial_operations(st)
+    out = m2.on_trial_exited_early(st, ops[0].request_id, searcher.ExitedReason.INVALID_HP)
     assert len(out) == 1 and isinstance(out[0], searcher.Shutdown) and out[0].failure
 
 

@@ -58,6 +58,9 @@ REF_TESTS = [
      "test_reject_unnamed_nondict_metric and not test_trainer_disable_tb_logging", 36),
     # client-side custom search: the runner loop against the reference's mock master (typed searcher events from the bindings)
     ("tests/test_custom_searcher.py", "", 2),
+    # the DSAT simulation suite: trial / tracker bookkeeping, random / binary / ASHA methods end to end against a mock master,
+    # lineage pruning rules, rung promotion, HF argument overwriting
+    ("tests/experiment/pytorch/test_deepspeed_autotuning.py", "", 46),
     ("tests/common/test_yaml.py", "", 4),
     ("tests/common/test_api.py", "", 15),                                       # master URL canonicalisation
     ("tests/launch/test_wrap_rank.py", "", 1),
