@@ -124,6 +124,12 @@ class ZeroEngine:
         self.global_steps = 0
         self.global_samples = 0
         self.skipped_steps = 0
+        at = self.config.get("autotuning") or {}
+        self._probe: Any = None
+        if isinstance(at, dict) and at.get("enabled"):
+            from determined_b200.parallel import autotune_probe
+
+            self._probe = autotune_probe.EngineProbe(self, at)
         params = [p for p in (model_parameters if model_parameters is not None else module.parameters()) if p.requires_grad]
         ocfg = self.config.get("optimizer") or {}
         op = dict(ocfg.get("params") or {})
@@ -520,12 +526,26 @@ class ZeroEngine:
         return self.forward(*args, **kwargs)
 
     def forward(self, *args: Any, **kwargs: Any) -> Any:
+        if self._probe is not None:
+            return self._probe.forward(self._forward, args, kwargs)
+        return self._forward(*args, **kwargs)
+
+    def _forward(self, *args: Any, **kwargs: Any) -> Any:
         if self._bf16 and self.device.type == "cuda":
             with torch.autocast("cuda", dtype=torch.bfloat16):
                 return self.module(*args, **kwargs)
         return self.module(*args, **kwargs)
 
     def backward(self, loss: torch.Tensor, **kw: Any) -> torch.Tensor:
+        if self._probe is not None:
+            self._probe.backward_begin()
+            try:
+                return self._backward(loss)
+            finally:
+                self._probe.backward_end()
+        return self._backward(loss)
+
+    def _backward(self, loss: torch.Tensor) -> torch.Tensor:
         scaled = loss / self._ga if self._ga > 1 else loss
         if self._native:
             self._boundary_pass = self.is_gradient_accumulation_boundary()
@@ -586,6 +606,8 @@ class ZeroEngine:
             self.param_groups[0]["lr"] = float(self._sched_fn(self.global_steps))
         elif self.lr_scheduler is not None and self.lr_scheduler is not self:
             self.lr_scheduler.step()
+        if self._probe is not None:
+            self._probe.step_done()          # autotuning probe: may write its result file and exit the process
 
     def _fallback_step(self) -> None:
         if self.world > 1:

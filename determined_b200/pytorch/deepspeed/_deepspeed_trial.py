@@ -69,6 +69,15 @@ class DeepSpeedTrialController:
             raise TypeError("DeepSpeedTrialController needs a DeepSpeedTrial")
         self.trial, self.context, self.core_context = trial_inst, context, context._core
         self.is_chief = context.distributed.rank == 0
+        # autotuning probe trials (``pytorch.dsat``): one searcher operation, trained batch by batch under the reporting
+        # context until the engine's probe exits the process (reference ``_deepspeed_trial.py:46-51,298-308``)
+        from determined_b200.pytorch.dsat import defaults as _dsat_defaults
+
+        self._dsat_mode = bool((context.get_hparams() or {}).get(_dsat_defaults.USE_DSAT_MODE_KEY, False))
+        if self._dsat_mode and not local_training:
+            name = (context.get_experiment_config().get("searcher") or {}).get("name")
+            if name != "custom":
+                raise errors.InvalidExperimentException("`_use_dsat_mode` can only be set for trials of a custom-searcher experiment")
         self.callbacks = self.trial.build_callbacks()
         self.max_length = max_length
         self.validation_period = validation_period or Batch(sys.maxsize)
@@ -174,11 +183,33 @@ class DeepSpeedTrialController:
                     ops: Iterator = iter([core.DummySearcherOperation(self.max_length.value, self.is_chief)])
                 else:
                     ops = self.core_context.searcher.operations()
+                if self._dsat_mode:
+                    self._run_dsat_probe(ops)
                 for op in ops:
                     self._train_for_op(op)
             except ShouldExit as e:
                 if not e.skip_exit_checkpoint and self.state.last_ckpt != self.state.batches_trained:
                     self._checkpoint(already_exiting=True)
+
+    def _run_dsat_probe(self, ops: Iterator) -> None:
+        """Train the one operation of a probe trial a batch at a time, each inside ``dsat_reporting_context``: when the
+        engine's probe is done it exits the process and the context reports its result.  A probe that never exits (an
+        engine without autotuning support) falls through to the normal loop with the operation still open."""
+        from determined_b200.pytorch import dsat
+
+        op = next(ops, None)
+        if op is None:
+            return
+        for m in self.context.models:
+            m.train()
+        epoch_len = self.context._epoch_len or sys.maxsize
+        for _ in range(int(op.length)):
+            batch_idx = self.state.batches_trained
+            self.context._current_batch_idx = batch_idx
+            with dsat.dsat_reporting_context(core_context=self.core_context, op=op):
+                self.trial.train_batch(self.training_iterator, batch_idx // epoch_len, batch_idx)
+            self.state.batches_trained += 1
+        self._train_for_op(op)
 
     def _op_length(self, op: core.SearcherOperation) -> TrainUnit:
         if self.test_mode:

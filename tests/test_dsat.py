@@ -165,3 +165,132 @@ def test_hf_args_rewrite(tmp_path):
     out = dsat.get_hf_args_with_overwrites(argv, hp)
     i = out.index("--per_device_train_batch_size")
     assert out[i + 1] == "16"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the engine half: "autotuning": {"enabled": true} makes the ZeRO engine measure, write its result file and exit
+# ---------------------------------------------------------------------------------------------------------------------
+def _mlp(width=32):
+    import torch
+
+    torch.manual_seed(0)
+    return torch.nn.Sequential(torch.nn.Linear(8, width), torch.nn.GELU(), torch.nn.Linear(width, 4))
+
+
+def _steps(engine, n, batch):
+    import torch
+
+    for _ in range(n):
+        x = torch.randn(batch, 8)
+        loss = engine(x).square().mean()
+        engine.backward(loss)
+        engine.step()
+
+
+def test_engine_model_info_probe_counts_parameters_and_saved_activations(tmp_path, monkeypatch):
+    from determined_b200.parallel import zero
+
+    monkeypatch.chdir(tmp_path)
+    sizes = {}
+    for batch in (1, 4):
+        cfg = {"train_micro_batch_size_per_gpu": batch, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+               "autotuning": {"enabled": True, "model_info_path": f"info{batch}.json", "model_info": {"profile": True}}}
+        model = _mlp()
+        engine, *_ = zero.initialize(model=model, config=cfg)
+        with pytest.raises(SystemExit):
+            _steps(engine, 3, batch)
+        assert engine.global_steps == 1, "the model-info probe needs exactly one step"
+        info = json.loads((tmp_path / f"info{batch}.json").read_text())
+        n = sum(p.numel() for p in model.parameters())
+        assert info["num_params"] == info["trainable_num_params"] == n and info["rank"] == 0
+        sizes[batch] = info["activation_mem_per_gpu"]
+    # what autograd keeps between forward and backward: input, pre-activation and activation of the hidden layer, the
+    # output (saved by the loss) -- a few hundred bytes per sample here, proportional to the batch, parameters excluded
+    assert 4 * (8 + 32 + 32) <= sizes[1] <= 4 * (8 + 3 * 32 + 2 * 4) and sizes[4] == 4 * sizes[1]
+
+
+def test_engine_metric_probe_times_the_profile_window_and_exits(tmp_path, monkeypatch):
+    from determined_b200.parallel import zero
+
+    monkeypatch.chdir(tmp_path)
+    cfg = {"train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+           "autotuning": {"enabled": True, "start_profile_step": 2, "end_profile_step": 4}}
+    model = _mlp()
+    engine, *_ = zero.initialize(model=model, config=cfg)
+    with pytest.raises(SystemExit):
+        _steps(engine, 2 * 10, 2)               # two micro-batches per optimizer step
+    assert engine.global_steps == 4, "the probe exits when the step counter reaches end_profile_step"
+    res = json.loads((tmp_path / defaults.AUTOTUNING_RESULTS_PATH).read_text())
+    assert set(res) == {"latency", "throughput", "FLOPS_per_gpu", "forward", "backward"}
+    assert res["latency"] > 0 and res["throughput"] == pytest.approx(engine.train_batch_size() / res["latency"])
+    n = sum(p.numel() for p in model.parameters())
+    assert res["FLOPS_per_gpu"] == pytest.approx(6.0 * n * 4 / res["latency"])       # 2 micro-batches x 2 samples per step
+    assert 0 < res["forward"] < res["latency"] and 0 < res["backward"] < res["latency"]
+    # an engine without the switch never exits
+    engine2, *_ = zero.initialize(model=_mlp(), config={k: v for k, v in cfg.items() if k != "autotuning"})
+    _steps(engine2, 12, 2)
+    assert engine2.global_steps == 6
+
+
+def test_trial_controller_runs_a_probe_trial_and_reports_its_result(tmp_path, monkeypatch):
+    """The controller's autotuning path end to end on one process: hyperparameters carry the dsat switch and the overwrite
+    section, the engine's probe exits the process inside ``dsat_reporting_context``, which reports the result file as
+    validation metrics and completes the searcher operation."""
+    import torch
+
+    from determined_b200 import pytorch
+    from determined_b200.parallel import zero
+    from determined_b200.pytorch import deepspeed as det_ds
+
+    monkeypatch.chdir(tmp_path)
+
+    class DS(torch.utils.data.Dataset):
+        def __len__(self):
+            return 64
+
+        def __getitem__(self, i):
+            return torch.full((8,), float(i) / 64)
+
+    class ProbeTrial(det_ds.DeepSpeedTrial):
+        def __init__(self, context):
+            self.context = context
+            base = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}}}
+            cfg = det_ds.overwrite_deepspeed_config(base, context.get_hparams()[defaults.OVERWRITE_KEY])
+            engine, *_ = zero.initialize(model=_mlp(), config=cfg)
+            self.engine = context.wrap_model_engine(engine)
+
+        def train_batch(self, it, epoch_idx, batch_idx):
+            loss = self.engine(next(it)).square().mean()
+            self.engine.backward(loss)
+            self.engine.step()
+            return {"loss": loss}
+
+        def evaluate_batch(self, it, batch_idx):
+            return {"val_loss": self.engine(next(it)).square().mean()}
+
+        def build_training_data_loader(self):
+            return pytorch.DataLoader(DS(), batch_size=self.engine.train_micro_batch_size_per_gpu())
+
+        def build_validation_data_loader(self):
+            return pytorch.DataLoader(DS(), batch_size=self.engine.train_micro_batch_size_per_gpu())
+
+    reported = {}
+
+    def run(overwrite, length):
+        hp = {defaults.USE_DSAT_MODE_KEY: True, defaults.OVERWRITE_KEY: overwrite}
+        with det_ds.init(hparams=hp, exp_conf={}, require_gpu=False) as ctx:
+            monkeypatch.setattr(ctx._core.train, "report_validation_metrics", lambda steps_completed, metrics: reported.update(metrics, steps=steps_completed))
+            trial = ProbeTrial(ctx)
+            with pytest.raises(SystemExit):
+                det_ds.Trainer(trial, ctx).fit(max_length=pytorch.Batch(length))
+            return trial
+
+    t = run({"train_micro_batch_size_per_gpu": 1, "autotuning": {"enabled": True, "model_info_path": defaults.MODEL_INFO_PROFILING_PATH,
+                                                                   "model_info": {"profile": True}}}, 1)
+    assert t.engine.global_steps == 1 and t.engine.train_micro_batch_size_per_gpu() == 1
+    assert reported["num_params"] > 0 and reported["activation_mem_per_gpu"] > 0 and reported["gpu_mem"] > 0 and reported["steps"] == 1
+    (tmp_path / defaults.MODEL_INFO_PROFILING_PATH).unlink()
+    reported.clear()
+    t = run({"train_micro_batch_size_per_gpu": 8, "autotuning": {"enabled": True, "start_profile_step": 2, "end_profile_step": 3}}, 4)
+    assert t.engine.global_steps == 3 and t.engine.train_micro_batch_size_per_gpu() == 8
+    assert reported["throughput"] > 0 and reported["FLOPS_per_gpu"] > 0 and reported["steps"] == 4 and "gpu_mem" not in reported
