@@ -17,10 +17,13 @@ def main(argv=None) -> int:
     ap.add_argument("--resource-pool", default="default")
     ap.add_argument("--work-dir", default=None, help="task run directories and the re-attachment state live here")
     ap.add_argument("--agent-token", default=None, help="shared secret if the master sets DET_AGENT_TOKEN")
+    ap.add_argument("--master-cert-file", default=None, help="PEM certificate of an https master to trust, or 'noverify' (default: $DET_MASTER_CERT_FILE)")
+    ap.add_argument("--master-cert-name", default=None, help="host name in the master's certificate when it differs from the URL's")
     ap.add_argument("--log-level", default="INFO")
     a = ap.parse_args(argv)
     logging.basicConfig(level=getattr(logging, a.log_level.upper(), logging.INFO), format="%(asctime)s %(levelname)s %(name)s: %(message)s")
-    agent = Agent(a.master_url, a.agent_id, a.slots, a.slot_type, a.resource_pool, a.work_dir, a.agent_token)
+    agent = Agent(a.master_url, a.agent_id, a.slots, a.slot_type, a.resource_pool, a.work_dir, a.agent_token,
+                  a.master_cert_file, a.master_cert_name)
 
     def on_signal(signum, frame):  # noqa: ARG001
         # SIGTERM / SIGINT: leave tasks running (they re-attach when the agent comes back), like `systemctl restart`

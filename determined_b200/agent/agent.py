@@ -112,6 +112,8 @@ class ProcessRuntime:
             env = dict(os.environ)
             env.pop("DET_LATEST_CHECKPOINT", None)
             env.update({str(k): str(v) for k, v in (action.get("env") or {}).items()})
+            if env.get("DET_MASTER_CERT_FILE") and not os.path.exists(env["DET_MASTER_CERT_FILE"]) and getattr(self, "master_cert_file", None):
+                env["DET_MASTER_CERT_FILE"] = self.master_cert_file        # the master named ITS file; tasks here use this host's copy
             slot_ids = [int(s) for s in action.get("slot_ids") or []]
             env.update({"DET_AGENT_ID": agent_id, "DET_RUN_DIR": run_dir, "DET_INFO_DIR": info_dir, "DET_MODEL_DIR": model_dir,
                         "DET_SLOT_IDS": json.dumps(slot_ids)})
@@ -203,8 +205,12 @@ def _signal_group(pid: int, sig: int) -> None:
 
 class Agent:
     def __init__(self, master_url: str, agent_id: Optional[str] = None, slots: Optional[int] = None, slot_type: str = "auto",
-                 resource_pool: str = "default", work_dir: Optional[str] = None, token: Optional[str] = None) -> None:
+                 resource_pool: str = "default", work_dir: Optional[str] = None, token: Optional[str] = None,
+                 master_cert_file: Optional[str] = None, master_cert_name: Optional[str] = None) -> None:
         self.master_url = master_url.rstrip("/")
+        # an https master: the certificate to trust (a PEM file, or "noverify"), and the name it carries if not the URL's
+        self.master_cert_file = master_cert_file or os.environ.get("DET_MASTER_CERT_FILE")
+        self.master_cert_name = master_cert_name or os.environ.get("DET_MASTER_CERT_NAME")
         self.id = agent_id or socket.gethostname()
         self.slots = detect_slots(slots, slot_type)
         self.resource_pool = resource_pool
@@ -216,6 +222,16 @@ class Agent:
         self._stop = threading.Event()
         self.runtime = ProcessRuntime(self.work_dir, self._emit)
         self.http = requests.Session()
+        self._verify_kw: Dict[str, Any] = {}
+        if self.master_url.startswith("https://"):
+            from determined_b200.common.api import certs
+
+            cert = certs.default_load(self.master_url, self.master_cert_file, self.master_cert_name)
+            if cert.bundle is not None:
+                self._verify_kw = {"verify": cert.bundle}
+            if cert.name:
+                self.http.mount("https://", certs.host_name_adapter(cert.name))
+        self.runtime.master_cert_file = self.master_cert_file
         self.poll_timeout = 10.0
         self.registered = False
 
@@ -226,7 +242,7 @@ class Agent:
     def _post(self, path: str, body: Dict[str, Any], timeout: float) -> Dict[str, Any]:
         if self.token:
             body = {**body, "token": self.token}
-        r = self.http.post(self.master_url + path, json=body, timeout=timeout)
+        r = self.http.post(self.master_url + path, json=body, timeout=timeout, **self._verify_kw)
         if r.status_code >= 400:
             raise RuntimeError(f"{path}: HTTP {r.status_code}: {r.text[:200]}")
         return r.json()

@@ -44,9 +44,31 @@ def _table(rows: List[Sequence[Any]], headers: Sequence[str], as_json: bool = Fa
             print(" | ".join(str(x) for x in r))
 
 
+def _master_of(args: argparse.Namespace) -> str:
+    return args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
+
+
+def _setup_cert(args: argparse.Namespace) -> None:
+    """For an https master: the certificate every session of this process uses, from ``--cert-file`` / ``--cert-name`` /
+    ``--noverify``, the environment, or the store of accepted certificates."""
+    from determined_b200.common.api import certs
+
+    master = _master_of(args)
+    try:
+        https = api.canonicalize_master_url(master).startswith("https://")
+    except ValueError:
+        return
+    if https:
+        certs.cli_cert = certs.default_load(master, getattr(args, "cert_file", None), getattr(args, "cert_name", None),
+                                            bool(getattr(args, "noverify", False)))
+        if certs.cli_cert.bundle is False:
+            import urllib3
+
+            urllib3.disable_warnings(urllib3.exceptions.InsecureRequestWarning)      # the user asked for exactly this
+
+
 def _session(args: argparse.Namespace) -> api.Session:
-    master = args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
-    return api.authentication.login_with_cache(master, args.user, None)
+    return api.authentication.login_with_cache(_master_of(args), args.user, None)
 
 
 def _sdk(args: argparse.Namespace) -> sdk.Determined:
@@ -865,6 +887,9 @@ def make_parser() -> argparse.ArgumentParser:
     p = argparse.ArgumentParser(prog="det", description="determined_b200 command line client")
     p.add_argument("-m", "--master", help="master address (default: $DET_MASTER or localhost:8080)")
     p.add_argument("-u", "--user", help="run as this user")
+    p.add_argument("--cert-file", help="PEM certificate (or CA bundle) to trust for an https master (default: $DET_MASTER_CERT_FILE)")
+    p.add_argument("--cert-name", help="host name the master's certificate carries, when not the one in the URL")
+    p.add_argument("--noverify", action="store_true", help="do not verify the master's certificate")
     p.add_argument("-v", "--version", action="version", version=f"det {det.__version__}")
     sub = p.add_subparsers(dest="cmd")
 
@@ -1224,8 +1249,26 @@ def main(argv: Optional[List[str]] = None) -> int:
     if fn is None:
         parser.print_help()
         return 2
+    import requests
+
+    from determined_b200.common.api import certs
+
+    _setup_cert(args)
     try:
-        return int(fn(args) or 0)
+        try:
+            return int(fn(args) or 0)
+        except requests.exceptions.SSLError as e:
+            # a certificate nobody vouches for: show its fingerprint and, if the user agrees, remember it (trust on first use)
+            if not sys.stdin or not sys.stdin.isatty():
+                print(f"Failed: the certificate of {_master_of(args)} is not trusted ({e}); pass --cert-file, set "
+                      "DET_MASTER_CERT_FILE, or run det in a terminal once to accept it", file=sys.stderr)
+                return 1
+            try:
+                certs.cli_cert = certs.trust_on_first_use(_master_of(args))
+            except PermissionError as pe:
+                print(f"Failed: {pe}", file=sys.stderr)
+                return 1
+            return int(fn(args) or 0)
     except api.errors.APIException as e:
         print(f"Failed: {e.message}", file=sys.stderr)
         return 1

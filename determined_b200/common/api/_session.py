@@ -43,13 +43,38 @@ class BaseSession:
         self._max_retries = max_retries
         self._timeout = timeout
         self._http = None
+        self._verify_kw: Dict[str, Any] = {}
 
     def _client(self) -> Any:
         if self._http is None:
             import requests
 
             self._http = requests.Session()
+            cert = self._effective_cert()
+            self._verify_kw = {}
+            if cert is not None:
+                if cert.bundle is not None:
+                    # per request, not on the session: REQUESTS_CA_BUNDLE / CURL_CA_BUNDLE in the environment would
+                    # otherwise replace a session-level setting
+                    self._verify_kw = {"verify": cert.bundle}
+                if cert.name:
+                    from determined_b200.common.api import certs
+
+                    self._http.mount("https://", certs.host_name_adapter(cert.name))
         return self._http
+
+    def _effective_cert(self) -> Any:
+        """The ``cert=`` given, else the process-wide default (``certs.cli_cert``), else — for an https master — whatever
+        ``certs.default_load`` finds (environment, accepted-certificate store)."""
+        if self.cert is not None:
+            return self.cert
+        from determined_b200.common.api import certs
+
+        if certs.cli_cert is not None:
+            return certs.cli_cert
+        if self.master.startswith("https://"):
+            return certs.default_load(self.master)
+        return None
 
     def _headers(self, extra: Optional[Dict[str, str]]) -> Dict[str, str]:
         h = {"Content-Type": "application/json"}
@@ -78,7 +103,9 @@ class BaseSession:
         while True:
             try:
                 r = self._client().request(method, url, params=params, data=data, headers=self._headers(headers),
-                                           timeout=timeout or self._timeout, stream=stream)
+                                           timeout=timeout or self._timeout, stream=stream, **self._verify_kw)
+            except requests.exceptions.SSLError:
+                raise                    # a certificate problem does not go away by retrying; the CLI offers to trust it
             except (requests.ConnectionError, requests.Timeout) as e:
                 if attempt >= self._max_retries:
                     raise errors.MasterNotFoundException(f"cannot reach master at {self.master}: {e}") from e

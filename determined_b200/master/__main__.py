@@ -23,6 +23,8 @@ def main(argv=None) -> int:
     ap.add_argument("--slots", type=int, default=None, help="override detected slot count (CPU testing)")
     ap.add_argument("--agent-token", default=None, help="shared secret agents must present (default: $DET_AGENT_TOKEN, none)")
     ap.add_argument("--otel-endpoint", default=None, help="OTLP/HTTP collector (or file://path) for request traces; config: telemetry.otel_endpoint")
+    ap.add_argument("--tls-cert", default=None, help="PEM certificate: serve HTTPS (config: security.tls.cert)")
+    ap.add_argument("--tls-key", default=None, help="PEM private key of --tls-cert (config: security.tls.key)")
     ap.add_argument("--log-level", default="INFO")
     args = ap.parse_args(argv)
     logging.basicConfig(level=getattr(logging, args.log_level.upper()), format="%(asctime)s %(levelname)s: %(name)s: %(message)s")
@@ -49,7 +51,9 @@ def main(argv=None) -> int:
         from determined_b200.common import tracing
 
         tracing.configure("determined-master", otel)
-    srv = api.APIServer(m, host, port).start()
+    tls = (cfg.get("security") or {}).get("tls") or {}
+    m.tls_cert_name = tls.get("name")
+    srv = api.APIServer(m, host, port, tls_cert=args.tls_cert or tls.get("cert"), tls_key=args.tls_key or tls.get("key")).start()
     m.start()
     logging.getLogger("determined.master").info("master %s listening on %s (%d slots, scheduler=%s)", m.cluster_id, m.url,
                                                  m.pool.agents[m.agent_id].num_slots, m.pool.scheduler)

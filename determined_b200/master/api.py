@@ -13,6 +13,8 @@ Built on ``http.server.ThreadingHTTPServer`` (stdlib only).
 """
 import base64
 import json
+import os
+import sys
 import logging
 import re
 import secrets
@@ -2020,11 +2022,36 @@ class Handler(BaseHTTPRequestHandler):
         self._dispatch("DELETE")
 
 
+class _QuietServer(ThreadingHTTPServer):
+    def handle_error(self, request: Any, client_address: Any) -> None:
+        """A client that goes away, or one that rejects our certificate during the handshake, is its own business: one
+        debug line instead of a traceback on stderr."""
+        import ssl
+
+        e = sys.exc_info()[1]
+        if isinstance(e, (ssl.SSLError, ConnectionError, TimeoutError)):
+            logger.debug("connection from %s dropped: %s", client_address, e)
+            return
+        super().handle_error(request, client_address)
+
+
 class APIServer:
-    def __init__(self, master: core.Master, host: str = "127.0.0.1", port: int = 8080) -> None:
+    def __init__(self, master: core.Master, host: str = "127.0.0.1", port: int = 8080,
+                 tls_cert: Optional[str] = None, tls_key: Optional[str] = None) -> None:
+        """``tls_cert`` / ``tls_key`` (PEM files; master config ``security.tls.cert`` / ``.key``) make the server speak
+        HTTPS; tasks then get ``DET_MASTER_CERT_FILE`` so that the harness trusts exactly this certificate."""
         handler = type("BoundHandler", (Handler,), {"master": master})
-        self.httpd = ThreadingHTTPServer((host, port), handler)
+        self.httpd = _QuietServer((host, port), handler)
         self.httpd.daemon_threads = True
+        if tls_cert:
+            import ssl
+
+            ctx = ssl.SSLContext(ssl.PROTOCOL_TLS_SERVER)
+            ctx.minimum_version = ssl.TLSVersion.TLSv1_2
+            ctx.load_cert_chain(tls_cert, tls_key or None)
+            # handshake in the worker thread, not in accept(): a client that connects and stays silent must not block others
+            self.httpd.socket = ctx.wrap_socket(self.httpd.socket, server_side=True, do_handshake_on_connect=False)
+            master.tls_cert_file = os.path.abspath(tls_cert)
         master.host, master.port = host, self.httpd.server_address[1]
         self.thread: Optional[threading.Thread] = None
 

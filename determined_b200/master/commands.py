@@ -122,7 +122,7 @@ class CommandTask:
             if isinstance(kv, str) and "=" in kv:
                 k, v = kv.split("=", 1)
                 task_env[k] = v
-        task_env.update({"DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port), "DET_CLUSTER_ID": m.cluster_id,
+        task_env.update({**m.master_env(), "DET_CLUSTER_ID": m.cluster_id,
                          "DET_AGENT_ID": self.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids), "DET_TASK_ID": self.id,
                          "DET_ALLOCATION_ID": self.id + ".1", "DET_SESSION_TOKEN": self.token, "DET_TASK_TYPE": self.kind,
                          "DET_USER": self.owner_name, "PYTHONUNBUFFERED": "1"})

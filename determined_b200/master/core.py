@@ -102,7 +102,7 @@ class Allocation:
         # what the master decides; the host running the task (this process, or an agent) layers it over its own environment
         task_env: Dict[str, str] = dict(exp.environment_variables())
         task_env.update({
-            "DET_MASTER": m.url, "DET_MASTER_HOST": m.host, "DET_MASTER_PORT": str(m.port),
+            **m.master_env(),
             "DET_CLUSTER_ID": m.cluster_id, "DET_AGENT_ID": self.agent_id, "DET_SLOT_IDS": json.dumps(slot_ids),
             "DET_TASK_ID": t.task_id, "DET_ALLOCATION_ID": self.id, "DET_SESSION_TOKEN": self.token,
             "DET_TASK_TYPE": "TRIAL", "DET_TRIAL_ID": str(t.id), "DET_EXPERIMENT_ID": str(exp.id),
@@ -605,9 +605,21 @@ class Master:
                 self.backends[name] = slurm.SlurmBackend(self, name, prov)
         self._restore()
 
+    tls_cert_file: Optional[str] = None       # set by the API server when it serves HTTPS
+    tls_cert_name: Optional[str] = None       # host name in the certificate, when tasks reach the master by another name
+
     @property
     def url(self) -> str:
-        return f"http://{self.host}:{self.port}"
+        return f"{'https' if self.tls_cert_file else 'http'}://{self.host}:{self.port}"
+
+    def master_env(self) -> Dict[str, str]:
+        """How a task finds (and, over TLS, trusts) this master."""
+        env = {"DET_MASTER": self.url, "DET_MASTER_HOST": self.host, "DET_MASTER_PORT": str(self.port)}
+        if self.tls_cert_file:
+            env["DET_MASTER_CERT_FILE"] = self.tls_cert_file
+            if self.tls_cert_name:
+                env["DET_MASTER_CERT_NAME"] = self.tls_cert_name
+        return env
 
     @property
     def pool(self) -> scheduler.ResourcePool:
