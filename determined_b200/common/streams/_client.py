@@ -3,9 +3,11 @@
 Parity: reference ``harness/determined/common/streams/_client.py``: ``Stream`` (subscribe / iterate,
 ``Sync(complete=False)`` ... offline messages ... ``Sync(complete=True)`` ... online messages, automatic
 resubscribe from a primary-key cache), ``ProjectSpec`` / ``ModelSpec`` / ``ModelVersionSpec``,
-``KeyCache``, ``StreamWebSocket`` transport ABC.  The reference speaks a websocket (lomond); the
-single-box master exposes the same message protocol over ``POST /stream`` long-polls, implemented by
-``PollingStreamTransport`` — any other ``StreamWebSocket`` (e.g. a real websocket) plugs in unchanged.
+``KeyCache``, ``StreamWebSocket`` transport ABC.  Two transports: ``WebSocketStreamTransport`` speaks a websocket to
+``GET /stream`` like the reference's lomond client (own RFC 6455 code in ``common/websocket.py``; TLS through the session's
+``Cert``; reconnects and re-sends the last startup message, which the ``Stream`` builds from its key cache so that nothing is
+missed and nothing is repeated), and ``PollingStreamTransport`` runs the same messages over ``POST /stream`` for places a
+websocket cannot go.  ``Stream.connect(session)`` picks the websocket.
 """
 import abc
 import collections
@@ -56,6 +58,100 @@ class PollingStreamTransport(StreamWebSocket):
             if r["messages"] or time.time() >= deadline:
                 return r["messages"]
             time.sleep(min(self._interval, max(deadline - time.time(), 0)))
+
+
+class WebSocketStreamTransport(StreamWebSocket):
+    """A reader thread turns frames into a queue of messages; ``recv`` drains the queue.  When the connection is lost the
+    next ``recv`` reconnects (with back-off) and replays the last startup message."""
+
+    def __init__(self, session: api.Session, reconnect: bool = True, max_backoff: float = 10.0) -> None:
+        import queue
+
+        self._session = session
+        self._reconnect = reconnect
+        self._max_backoff = max_backoff
+        self._ws: Any = None
+        self._q: "queue.Queue[Any]" = queue.Queue()
+        self._last_startup: Optional[Dict[str, Any]] = None
+        self._closed = False
+        self.reconnects = 0
+        # called with the transport before a lost connection is re-opened; returns the startup message to send (the Stream
+        # sets this to rebuild `known` / `since` from its caches); default: the last one sent, unchanged
+        self.on_reconnect: Any = None
+
+    def _connect(self) -> None:
+        import threading
+
+        from determined_b200.common import websocket
+
+        master = self._session.master
+        cert = self._session._effective_cert()
+        ctx = cert.ssl_context() if (cert is not None and master.startswith("https://")) else None
+        headers = {"Authorization": f"Bearer {self._session.token}"} if self._session.token else {}
+        ws = websocket.connect(master + "/stream", headers=headers, ssl_context=ctx, server_hostname=getattr(cert, "name", None))
+        self._ws = ws
+        q = self._q
+
+        def reader() -> None:
+            try:
+                while True:
+                    q.put(ws.recv_json())
+            except Exception as e:  # noqa: BLE001
+                q.put(e)
+
+        threading.Thread(target=reader, daemon=True, name="stream-ws-reader").start()
+
+    def send(self, msg: Dict[str, Any]) -> None:
+        self._last_startup = msg
+        if self._ws is None or self._ws.closed:
+            self._connect()
+        self._ws.send_json(msg)
+
+    def _recover(self) -> None:
+        delay = 0.2
+        while not self._closed:
+            try:
+                self._connect()
+                startup = self.on_reconnect(self) if self.on_reconnect is not None else self._last_startup
+                if startup is not None:
+                    self._last_startup = startup
+                    self._ws.send_json(startup)
+                self.reconnects += 1
+                return
+            except (OSError, Exception) as e:  # noqa: BLE001
+                if not self._reconnect:
+                    raise
+                time.sleep(delay)
+                delay = min(delay * 2, self._max_backoff)
+                last = e  # noqa: F841
+
+    def recv(self, timeout: Optional[float] = None) -> List[Dict[str, Any]]:
+        import queue
+
+        out: List[Dict[str, Any]] = []
+        try:
+            item = self._q.get(timeout=timeout) if timeout is not None else self._q.get()
+        except queue.Empty:
+            return out
+        while True:
+            if isinstance(item, Exception):
+                if self._closed:
+                    return out
+                if not self._reconnect:
+                    raise item
+                self._q = queue.Queue()
+                self._recover()
+                return out
+            out.append(item)
+            try:
+                item = self._q.get_nowait()
+            except queue.Empty:
+                return out
+
+    def close(self) -> None:
+        self._closed = True
+        if self._ws is not None:
+            self._ws.close()
 
 
 def int_or_list(x: Optional[Union[int, Sequence[int]]]) -> Optional[List[int]]:
@@ -132,21 +228,32 @@ class Stream:
         self._user_sync_id: Any = None
         self._sync_sent: Optional[str] = None
         self._closed = False
+        self._specs: Dict[str, Any] = {}
+        if hasattr(ws, "on_reconnect"):
+            ws.on_reconnect = lambda _t: self._startup_message()      # after a lost connection: resume from the caches
+
+    @classmethod
+    def connect(cls, session: api.Session, websocket: bool = True) -> "Stream":
+        """A stream on the master behind ``session``: over a websocket, or over long polls with ``websocket=False``."""
+        return cls(WebSocketStreamTransport(session) if websocket else PollingStreamTransport(session))
+
+    def _startup_message(self) -> Dict[str, Any]:
+        spec: Dict[str, Any] = {}
+        known: Dict[str, str] = {}
+        for name, s in self._specs.items():
+            w = s.to_wire()
+            w.since = self._caches[name].maxseq
+            spec[name] = w.to_json()
+            known[name] = self._caches[name].known()
+        return {"sync_id": self._sync_sent, "known": known, "subscribe": spec}
 
     def subscribe(self, sync_id: Any = None, projects: Optional[ProjectSpec] = None, models: Optional[ModelSpec] = None,
                   model_versions: Optional[ModelVersionSpec] = None) -> "Stream":
-        spec: Dict[str, Any] = {}
-        known: Dict[str, str] = {}
-        for name, s in (("projects", projects), ("models", models), ("model_versions", model_versions)):
-            if s is not None:
-                w = s.to_wire()
-                w.since = self._caches[name].maxseq
-                spec[name] = w.to_json()
-                known[name] = self._caches[name].known()
+        self._specs = {name: s for name, s in (("projects", projects), ("models", models), ("model_versions", model_versions)) if s is not None}
         self._user_sync_id = sync_id
         self._sync_sent = str(uuid.uuid4())
         self._pending.clear()
-        self._ws.send({"sync_id": self._sync_sent, "known": known, "subscribe": spec})
+        self._ws.send(self._startup_message())
         return self
 
     def _parse(self, msg: Dict[str, Any]) -> None:

@@ -1802,34 +1802,115 @@ def _stream_match(kind: str, row: Dict[str, Any], spec: Dict[str, Any]) -> bool:
     return hit("model_id", "model_ids") or hit("id", "model_version_ids") or hit("user_id", "user_ids")
 
 
-@route("POST", "/stream")
-def stream(ctx: Ctx) -> Any:
-    from determined_b200.common.streams import _util as su
+_WIRE_NAME = {"projects": "project", "models": "model", "model_versions": "modelversion"}
 
-    b = ctx.body or {}
-    sub = b.get("subscribe") or {}
-    cur = _stream_scan(ctx)
-    wire_name = {"projects": "project", "models": "model", "model_versions": "modelversion"}
-    msgs: List[Dict[str, Any]] = []
-    polling = "poll_since" in b
-    if not polling:
-        msgs.append({"sync_msg": {"sync_id": b.get("sync_id"), "complete": False}})
-    for kind, spec in sub.items():
-        if kind not in cur:
-            continue
-        since = int(b["poll_since"]) if polling else int(spec.get("since") or 0)
-        known = set(su.range_encoded_keys((b.get("known") or {}).get(kind, ""))) if not polling else set()
-        visible = {i: r for i, r in cur[kind].items() if _stream_match(kind, r, spec)}
-        if not polling:
-            gone = known - set(visible)
+
+class _StreamSession:
+    """One subscriber of the streaming-updates channel: what it subscribed to and which rows it has been told about.
+
+    ``startup(msg)`` answers a startup message: ``sync_msg(complete=False)``, deletions of rows the client knows
+    (``known``: range-encoded ids per kind) that it may no longer see, every visible row that is new to it or changed
+    after ``since``, ``sync_msg(complete=True)``.  ``tick()`` is the online phase: rows that changed since the last
+    message, and deletions of rows that disappeared or fell out of the subscription."""
+
+    def __init__(self, ctx: Ctx) -> None:
+        self.ctx = ctx
+        self.sub: Dict[str, Dict[str, Any]] = {}
+        self.seq = 0
+        self.sent: Dict[str, set] = {}
+
+    def _visible(self, cur: Dict[str, Dict[int, Dict[str, Any]]]) -> Dict[str, Dict[int, Dict[str, Any]]]:
+        return {kind: {i: r for i, r in cur[kind].items() if _stream_match(kind, r, spec)} for kind, spec in self.sub.items() if kind in cur}
+
+    def startup(self, b: Dict[str, Any]) -> List[Dict[str, Any]]:
+        from determined_b200.common.streams import _util as su
+
+        self.sub = {k: v for k, v in (b.get("subscribe") or {}).items() if isinstance(v, dict)}
+        cur = _stream_scan(self.ctx)
+        msgs: List[Dict[str, Any]] = [{"sync_msg": {"sync_id": b.get("sync_id"), "complete": False}}]
+        self.sent = {}
+        for kind, rows in self._visible(cur).items():
+            since = int(self.sub[kind].get("since") or 0)
+            known = set(su.range_encoded_keys((b.get("known") or {}).get(kind, "")))
+            gone = known - set(rows)
             if gone:
                 msgs.append({kind + "_deleted": su.encode_keys(gone)})
-        for i, r in sorted(visible.items()):
-            if r["seq"] > since or (not polling and i not in known):
-                msgs.append({wire_name[kind]: r})
-    if not polling:
+            for i, r in sorted(rows.items()):
+                if r["seq"] > since or i not in known:
+                    msgs.append({_WIRE_NAME[kind]: r})
+            self.sent[kind] = set(rows)
         msgs.append({"sync_msg": {"sync_id": b.get("sync_id"), "complete": True}})
-    return {"messages": msgs, "seq": _StreamState.seq}
+        self.seq = _StreamState.seq
+        return msgs
+
+    def tick(self) -> List[Dict[str, Any]]:
+        from determined_b200.common.streams import _util as su
+
+        if not self.sub:
+            return []
+        cur = _stream_scan(self.ctx)
+        msgs: List[Dict[str, Any]] = []
+        for kind, rows in self._visible(cur).items():
+            gone = self.sent.get(kind, set()) - set(rows)
+            if gone:
+                msgs.append({kind + "_deleted": su.encode_keys(gone)})
+            for i, r in sorted(rows.items()):
+                if r["seq"] > self.seq:
+                    msgs.append({_WIRE_NAME[kind]: r})
+            self.sent[kind] = set(rows)
+        self.seq = _StreamState.seq
+        return msgs
+
+
+@route("POST", "/stream")
+def stream(ctx: Ctx) -> Any:
+    """The streaming-updates protocol for clients that cannot hold a websocket: a startup message gets its whole offline
+    answer at once; ``poll_since`` asks for rows that changed after a sequence number (no online deletions in this form:
+    the websocket at ``GET /stream`` has them)."""
+    b = ctx.body or {}
+    sess = _StreamSession(ctx)
+    if "poll_since" not in b:
+        return {"messages": sess.startup(b), "seq": _StreamState.seq}
+    sess.sub = {k: v for k, v in (b.get("subscribe") or {}).items() if isinstance(v, dict)}
+    sess.seq = int(b["poll_since"])
+    sess.sent = {}
+    return {"messages": [m for m in sess.tick() if not any(k.endswith("_deleted") for k in m)], "seq": _StreamState.seq}
+
+
+def _ws_stream(handler: Any, user: Dict[str, Any]) -> None:
+    """``GET /stream`` with ``Upgrade: websocket`` (reference ``master/internal/stream/publisher_set.go``): JSON text
+    frames both ways; the client may send a new startup message at any time to change its subscription."""
+    import queue
+
+    from determined_b200.common import websocket
+
+    ws = websocket.server_handshake(handler)
+    sess = _StreamSession(Ctx(handler.master, user, {}, None, b""))
+    inbox: "queue.Queue[Any]" = queue.Queue()
+
+    def reader() -> None:
+        try:
+            while True:
+                inbox.put(ws.recv_json())
+        except Exception as e:  # noqa: BLE001  (closed, lost, malformed: all end the session)
+            inbox.put(e)
+
+    threading.Thread(target=reader, daemon=True, name="ws-stream-reader").start()
+    try:
+        while not handler.master._stop.is_set():
+            try:
+                msg = inbox.get(timeout=0.25)
+            except queue.Empty:
+                msg = None
+            if isinstance(msg, Exception):
+                break
+            out = sess.startup(msg) if isinstance(msg, dict) else sess.tick()
+            for m in out:
+                ws.send_json(m)
+    except (OSError, websocket.WebSocketError):
+        pass
+    finally:
+        ws.close()
 
 
 @route("GET", "/metrics", auth_required=False)
@@ -1928,6 +2009,16 @@ class Handler(BaseHTTPRequestHandler):
         if path.startswith("/proxy/"):
             self._proxy(method, path, u.query, raw)
             return
+        if method == "GET" and path.rstrip("/") == "/stream":
+            from determined_b200.common import websocket
+
+            if websocket.is_upgrade(self.headers):
+                user = self._user()
+                if user is None:
+                    self._send(401, {"error": {"code": 16, "message": "unauthenticated"}, "message": "unauthenticated"})
+                    return
+                _ws_stream(self, user)
+                return
         for meth, rx, fn, need_auth in ROUTES:
             if meth != method:
                 continue
@@ -1984,6 +2075,11 @@ class Handler(BaseHTTPRequestHandler):
             return
         t.last_activity = time.time()
         fwd_q = urllib.parse.urlencode([(k, v) for k, vs in qs.items() if k != "token" for v in vs])
+        from determined_b200.common import websocket as _ws
+
+        if _ws.is_upgrade(self.headers):
+            self._proxy_tunnel(t, method, rest + ("?" + fwd_q if fwd_q else ""), task_id)
+            return
         hdrs = {k: v for k, v in self.headers.items() if k.lower() not in ("host", "authorization", "connection", "content-length")}
         hdrs["X-Forwarded-Prefix"] = f"/proxy/{task_id}"
         try:
@@ -2005,6 +2101,50 @@ class Handler(BaseHTTPRequestHandler):
         except (BrokenPipeError, ConnectionResetError):
             pass
         conn.close()
+
+    def _proxy_tunnel(self, t: Any, method: str, target: str, task_id: str) -> None:
+        """An upgraded connection (a websocket of a notebook kernel, of tensorboard's live reload): replay the request to
+        the task's service and then copy bytes both ways until either side closes.  The master does not look inside."""
+        import select
+        import socket as _socket
+
+        try:
+            back = _socket.create_connection((t.service_host, t.service_port), timeout=30)
+        except OSError as e:
+            self._send(502, {"message": f"service of task {task_id} is not answering: {e}"})
+            return
+        lines = [f"{method} {target} HTTP/1.1"]
+        for k, v in self.headers.items():
+            if k.lower() in ("authorization",):
+                continue
+            lines.append(f"{k}: {f'{t.service_host}:{t.service_port}' if k.lower() == 'host' else v}")
+        lines.append(f"X-Forwarded-Prefix: /proxy/{task_id}")
+        back.sendall(("\r\n".join(lines) + "\r\n\r\n").encode())
+        self.close_connection = True
+        front = self.connection
+        # bytes the client sent right behind its request sit in rfile's buffer, where select() cannot see them
+        front.settimeout(0)
+        try:
+            pending = self.rfile.peek(1) if hasattr(self.rfile, "peek") else b""
+        except (BlockingIOError, OSError):
+            pending = b""
+        if pending:
+            back.sendall(self.rfile.read(len(pending)))
+        front.settimeout(None)
+        back.settimeout(None)
+        try:
+            while not self.master._stop.is_set():
+                ready, _, _ = select.select([front, back], [], [], 1.0)
+                for src in ready:
+                    data = src.recv(65536)
+                    if not data:
+                        return
+                    (back if src is front else front).sendall(data)
+                    t.last_activity = time.time()
+        except OSError:
+            pass
+        finally:
+            back.close()
 
     def do_GET(self) -> None:
         self._dispatch("GET")
