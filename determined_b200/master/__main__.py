@@ -9,7 +9,7 @@ import threading
 
 import yaml
 
-from determined_b200.master import api, core
+from determined_b200.master import api, config, core
 
 
 def main(argv=None) -> int:
@@ -25,37 +25,36 @@ def main(argv=None) -> int:
     ap.add_argument("--otel-endpoint", default=None, help="OTLP/HTTP collector (or file://path) for request traces; config: telemetry.otel_endpoint")
     ap.add_argument("--tls-cert", default=None, help="PEM certificate: serve HTTPS (config: security.tls.cert)")
     ap.add_argument("--tls-key", default=None, help="PEM private key of --tls-cert (config: security.tls.key)")
-    ap.add_argument("--log-level", default="INFO")
+    ap.add_argument("--root", default=None, help="work directory for task run directories (config: root)")
+    ap.add_argument("--print-config", action="store_true", help="print the merged configuration (secrets masked) and exit")
+    ap.add_argument("--log-level", default=None)
     args = ap.parse_args(argv)
-    logging.basicConfig(level=getattr(logging, args.log_level.upper()), format="%(asctime)s %(levelname)s: %(name)s: %(message)s")
-    cfg = {}
-    if args.config_file:
-        with open(args.config_file) as f:
-            cfg = yaml.safe_load(f) or {}
-    rm = (cfg.get("resource_manager") or {})
-    sch = rm.get("scheduler") or {}
-    host = args.host or cfg.get("host") or "127.0.0.1"
-    port = args.port or int(cfg.get("port") or 8080)
-    dbp = args.db or (cfg.get("db") or {}).get("path") or os.path.expanduser("~/.local/share/determined_b200/master.db")
-    defaults = {}
-    if cfg.get("checkpoint_storage"):
-        defaults["checkpoint_storage"] = cfg["checkpoint_storage"]
-    m = core.Master(db_path=dbp, host=host, port=port, scheduler_type=args.scheduler or sch.get("type", "fair_share"),
-                    fitting_policy=args.fitting_policy or sch.get("fitting_policy", "best"),
-                    preemption=bool((sch.get("preemption") or {}).get("enabled", True)), num_slots=args.slots,
-                    cluster_defaults=defaults, resource_pools=cfg.get("resource_pools") or None)
-    m.agent_token = args.agent_token or (cfg.get("security") or {}).get("agent_token")
-    tel = cfg.get("telemetry") or {}
-    otel = args.otel_endpoint or (tel.get("otel_endpoint") if tel.get("otel_enabled", True) else None)
-    if otel:
+    try:
+        cfg = config.load(args.config_file, flags={
+            "host": args.host, "port": args.port, "db.path": args.db, "resource_manager.scheduler.type": args.scheduler,
+            "resource_manager.scheduler.fitting_policy": args.fitting_policy, "security.agent_token": args.agent_token,
+            "telemetry.otel_endpoint": args.otel_endpoint, "security.tls.cert": args.tls_cert, "security.tls.key": args.tls_key,
+            "log.level": args.log_level.lower() if args.log_level else None, "root": args.root})
+    except config.MasterConfigError as e:
+        print(e, file=sys.stderr)
+        return 2
+    if args.print_config:
+        print(yaml.safe_dump(cfg.printable(), default_flow_style=False, sort_keys=True))
+        return 0
+    level = {"trace": "DEBUG", "warn": "WARNING", "fatal": "CRITICAL"}.get(cfg["log.level"], cfg["log.level"].upper())
+    logging.basicConfig(level=getattr(logging, level), format="%(asctime)s %(levelname)s: %(name)s: %(message)s")
+    sch = cfg["resource_manager.scheduler"]
+    m = core.Master(db_path=cfg.db_path, host=cfg["host"], port=cfg["port"], scheduler_type=sch["type"], fitting_policy=sch["fitting_policy"],
+                    preemption=bool(sch["preemption"]["enabled"]), num_slots=args.slots, work_dir=cfg["root"],
+                    cluster_defaults=cfg.cluster_defaults(), resource_pools=cfg["resource_pools"] or None)
+    m.apply_config(cfg)
+    if cfg["telemetry.otel_endpoint"] and cfg["telemetry.otel_enabled"]:
         from determined_b200.common import tracing
 
-        tracing.configure("determined-master", otel)
-    tls = (cfg.get("security") or {}).get("tls") or {}
-    m.tls_cert_name = tls.get("name")
-    srv = api.APIServer(m, host, port, tls_cert=args.tls_cert or tls.get("cert"), tls_key=args.tls_key or tls.get("key")).start()
+        tracing.configure("determined-master", cfg["telemetry.otel_endpoint"])
+    srv = api.APIServer(m, cfg["host"], cfg["port"], tls_cert=cfg["security.tls.cert"], tls_key=cfg["security.tls.key"]).start()
     m.start()
-    logging.getLogger("determined.master").info("master %s listening on %s (%d slots, scheduler=%s)", m.cluster_id, m.url,
+    logging.getLogger("determined.master").info("master %s (%s) listening on %s (%d slots, scheduler=%s)", m.cluster_id, m.cluster_name, m.url,
                                                  m.pool.agents[m.agent_id].num_slots, m.pool.scheduler)
     stop = threading.Event()
     for s in (signal.SIGINT, signal.SIGTERM):

@@ -181,19 +181,26 @@ def me(ctx: Ctx) -> Any:
 @route("GET", "/api/v1/master", auth_required=False)
 @route("GET", "/info", auth_required=False)
 def master_info(ctx: Ctx) -> Any:
-    return {"version": __version__, "masterId": ctx.m.cluster_id, "clusterId": ctx.m.cluster_id, "clusterName": "b200-box",
+    return {"version": __version__, "masterId": ctx.m.cluster_id, "clusterId": ctx.m.cluster_id, "clusterName": ctx.m.cluster_name,
             "telemetryEnabled": False, "ssoProviders": [], "externalLoginUri": "", "rbacEnabled": False, "branding": "determined_b200",
             "strictJobQueueControl": False, "userManagementEnabled": True, "product": "PRODUCT_COMMUNITY"}
 
 
 @route("GET", "/api/v1/master/config")
 def master_config(ctx: Ctx) -> Any:
-    return {"config": {"resource_manager": {"type": "agent", "scheduler": {"type": ctx.m.pool.scheduler, "fitting_policy": ctx.m.pool.policy,
-                                                                            "preemption": {"enabled": ctx.m.pool.preemption}}},
-                       "resource_pools": [{"pool_name": pl.name, "description": ctx.m.pool_descriptions.get(pl.name, ""),
-                                           "scheduler": {"type": pl.scheduler, "fitting_policy": pl.policy, "preemption": {"enabled": pl.preemption}}}
-                                          for pl in ctx.m.pools.values()],
-                       "checkpoint_storage": ctx.m.cluster_defaults.get("checkpoint_storage")}}
+    """The configuration the master runs with, secrets masked; the scheduler / pool sections always describe the live pools."""
+    live = {"resource_manager": {"type": "agent", "scheduler": {"type": ctx.m.pool.scheduler, "fitting_policy": ctx.m.pool.policy,
+                                                                 "preemption": {"enabled": ctx.m.pool.preemption}}},
+            "resource_pools": [{"pool_name": pl.name, "description": ctx.m.pool_descriptions.get(pl.name, ""),
+                                "scheduler": {"type": pl.scheduler, "fitting_policy": pl.policy, "preemption": {"enabled": pl.preemption}}}
+                               for pl in ctx.m.pools.values()],
+            "checkpoint_storage": ctx.m.cluster_defaults.get("checkpoint_storage")}
+    if ctx.m.config is not None:
+        out = ctx.m.config.printable()
+        out["resource_manager"] = dict(out.get("resource_manager") or {}, **live["resource_manager"])
+        out["resource_pools"] = live["resource_pools"]
+        return {"config": out}
+    return {"config": live}
 
 
 # -- users ---------------------------------------------------------------------------------------

@@ -93,6 +93,9 @@ class CommandTask:
         self.service_host = "127.0.0.1"
         # reference notebook / tensorboard configs: ``idle_timeout`` kills a service nobody has talked to for that long
         self.idle_timeout: Optional[float] = parse_duration(config.get("idle_timeout"))
+        if self.idle_timeout is None:                # the master's notebook_timeout / tensorboard_timeout, when configured
+            dflt = (getattr(mgr, "default_idle_timeout", None) or {}).get(kind)
+            self.idle_timeout = float(dflt) if dflt else None
         self.last_activity = time.time()
 
     @property

@@ -605,6 +605,8 @@ class Master:
                 self.backends[name] = slurm.SlurmBackend(self, name, prov)
         self._restore()
 
+    config: Any = None                         # master.config.MasterConfig when started from a configuration (``apply_config``)
+    cluster_name = "b200-box"
     tls_cert_file: Optional[str] = None       # set by the API server when it serves HTTPS
     tls_cert_name: Optional[str] = None       # host name in the certificate, when tasks reach the master by another name
 
@@ -620,6 +622,41 @@ class Master:
             if self.tls_cert_name:
                 env["DET_MASTER_CERT_NAME"] = self.tls_cert_name
         return env
+
+    def apply_config(self, cfg: Any) -> None:
+        """The parts of a :class:`master.config.MasterConfig` that are not constructor arguments: cluster name, agent token,
+        TLS name, the initial password of the built-in users (only while they still have the blank one), default idle
+        timeouts of notebooks / tensorboards, log retention."""
+        from determined_b200.common.api import authentication as auth
+
+        self.config = cfg
+        self.cluster_name = cfg["cluster_name"]
+        self.agent_token = cfg["security.agent_token"]
+        self.tls_cert_name = cfg["security.tls.name"]
+        pw = cfg["security.initial_user_password"]
+        if pw:
+            blank = auth.salt_and_hash("")
+            self.db.exec("UPDATE users SET password_hash=?, modified_at=? WHERE username IN ('admin','determined') AND password_hash=?",
+                         (auth.salt_and_hash(pw), time.time(), blank))
+        self.commands.default_idle_timeout = {"NOTEBOOK": cfg["notebook_timeout"], "TENSORBOARD": cfg["tensorboard_timeout"]}
+        self.log_retention_days = int(cfg["retention_policy.log_retention_days"])
+        if cfg["webhooks.signing_key"]:
+            self.db.set_meta("webhook_signing_key", cfg["webhooks.signing_key"])
+
+    log_retention_days = -1
+    _last_retention_sweep = 0.0
+
+    def sweep_old_logs(self, now: Optional[float] = None) -> int:
+        """Delete task logs older than ``retention_policy.log_retention_days`` (reference ``master/internal/logretention``);
+        returns how many lines went.  Called from the scheduler loop at most once an hour."""
+        if self.log_retention_days < 0:
+            return 0
+        now = time.time() if now is None else now
+        self._last_retention_sweep = now
+        n = self.db.delete_logs_before(now - 86400.0 * self.log_retention_days)
+        if n:
+            logger.info("log retention: deleted %d task log lines older than %d days", n, self.log_retention_days)
+        return n
 
     @property
     def pool(self) -> scheduler.ResourcePool:
@@ -837,6 +874,8 @@ class Master:
             self._kick.clear()
             try:
                 self.schedule_once()
+                if self.log_retention_days >= 0 and time.time() - self._last_retention_sweep > 3600:
+                    self.sweep_old_logs()
             except Exception:
                 logger.exception("scheduler tick failed")
 

@@ -133,5 +133,10 @@ class DB:
             self._conn.executemany(
                 "INSERT INTO task_logs(task_id,allocation_id,ts,level,rank_id,stdtype,source,log) VALUES(?,?,?,?,?,?,?,?)", rows)
 
+    def delete_logs_before(self, ts: float) -> int:
+        with self._lock:
+            cur = self._conn.execute("DELETE FROM task_logs WHERE ts < ?", (ts,))
+            return int(cur.rowcount or 0)
+
     def get_logs(self, task_id: str, after_id: int = 0, limit: int = 1000) -> List[sqlite3.Row]:
         return self.all("SELECT * FROM task_logs WHERE task_id=? AND id>? ORDER BY id LIMIT ?", (task_id, after_id, limit))
