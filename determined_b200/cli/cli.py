@@ -295,6 +295,9 @@ def experiment_set(args: argparse.Namespace) -> int:
         sess.patch(f"/api/v1/experiments/{eid}", json={"resources": {"weight": float(args.value)}})
     elif args.attr == "max-slots":
         sess.patch(f"/api/v1/experiments/{eid}", json={"resources": {"maxSlots": int(args.value)}})
+    elif args.attr == "log-retention":
+        days = -1 if str(args.value).lower() in ("forever", "-1") else int(args.value)
+        sess.put(f"/api/v1/experiments/{eid}/retain_logs", json={"numDays": days})
     elif args.attr == "gc-policy":
         a, b, c = (int(x) for x in args.value.split(","))
         sess.patch(f"/api/v1/experiments/{eid}", json={"checkpointStorage": {"saveExperimentBest": a, "saveTrialBest": b, "saveTrialLatest": c}})
@@ -942,7 +945,7 @@ def make_parser() -> argparse.ArgumentParser:
     a.add_argument("--smaller-is-better", type=lambda s: s.lower() in ("1", "true", "yes"), default=None)
     a.set_defaults(fn=experiment_download)
     a = e.add_parser("set")
-    a.add_argument("attr", choices=["name", "description", "priority", "weight", "max-slots", "gc-policy"])
+    a.add_argument("attr", choices=["name", "description", "priority", "weight", "max-slots", "gc-policy", "log-retention"])
     a.add_argument("experiment_id", type=int)
     a.add_argument("value")
     a.set_defaults(fn=experiment_set)
@@ -1223,7 +1226,7 @@ def make_parser() -> argparse.ArgumentParser:
     outfmt(a)
     a.set_defaults(fn=rbac_cmd, action="list-users-roles")
 
-    dp = sub.add_parser("deploy").add_subparsers(dest="sub")
+    dp = sub.add_parser("deploy", aliases=["d"]).add_subparsers(dest="sub")
     lo = dp.add_parser("local")
     lo.add_argument("action", choices=["cluster-up", "cluster-down", "master-up", "master-down", "agent-up", "agent-down", "logs"])
     lo.add_argument("--master-port", type=int, default=8080)
@@ -1239,6 +1242,9 @@ def make_parser() -> argparse.ArgumentParser:
 
     a = sub.add_parser("version")
     a.set_defaults(fn=version)
+    from determined_b200.cli import more
+
+    more.extend(p)
     return p
 
 

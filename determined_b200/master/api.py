@@ -415,6 +415,23 @@ def create_experiment(ctx: Ctx) -> Any:
                 ti.mtime = int(f.get("mtime", time.time()))
                 tf.addfile(ti, io.BytesIO(data))
         blob = buf.getvalue()
+    from determined_b200.master import api_more
+
+    try:
+        early = expconf.parse(b.get("config", "")) if b.get("config") else {}
+    except Exception:  # noqa: BLE001  (reported properly by create_experiment below)
+        early = {}
+    pid = int(b.get("projectId") or 1)
+    res = (early.get("resources") or {}) if isinstance(early, dict) else {}
+    if isinstance(early, dict) and not res.get("resource_pool"):
+        dflt = api_more.default_pool_for_project(ctx.m, pid, int(res.get("slots_per_trial", 1) or 0))
+        if dflt:
+            early.setdefault("resources", {})["resource_pool"] = dflt
+            b = dict(b, config=early)
+            res = early["resources"]
+    pool_name = res.get("resource_pool") or "default"
+    if pool_name in ctx.m.pools and not api_more.pool_allowed_for_project(ctx.m, pool_name, pid):
+        raise HTTPError(400, f"resource pool {pool_name!r} is not bound to the workspace of project {pid}")
     try:
         exp, cfg = ctx.m.create_experiment(b.get("config", ""), blob, owner=ctx.user["username"], activate=bool(b.get("activate", True)),
                                            parent_id=b.get("parentId"), template=b.get("template"), validate_only=bool(b.get("validateOnly")),
@@ -1018,13 +1035,46 @@ def kill_trial(ctx: Ctx, tid: str) -> Any:
     return {}
 
 
+def _log_time(s: Optional[str]) -> Optional[float]:
+    if not s:
+        return None
+    try:
+        return float(s)
+    except ValueError:
+        import datetime
+
+        try:
+            d = datetime.datetime.fromisoformat(s.replace("Z", "+00:00"))
+        except ValueError:
+            raise HTTPError(400, f"cannot parse time {s!r}")
+        return (d if d.tzinfo else d.replace(tzinfo=datetime.timezone.utc)).timestamp()
+
+
 def _logs(ctx: Ctx, task_id: str) -> Any:
     follow = ctx.q("follow") in ("true", "1")
     after = ctx.qi("offset", 0)
     limit = ctx.qi("limit", 0) or 5000
     deadline = time.time() + (min(ctx.qi("timeout_seconds", 20), 60) if follow else 0)
+    # filters (reference TrialLogs / TaskLogs request fields): levels, rankIds, sources, stdtypes, allocationIds (containerIds
+    # is accepted as a synonym: one process group per allocation here), timestampAfter / timestampBefore, searchText
+    levels = {x.replace("LOG_LEVEL_", "") for x in ctx.query.get("levels", [])}
+    ranks = {int(x) for x in ctx.query.get("rankIds", []) if str(x).lstrip("-").isdigit()}
+    sources, stdtypes = set(ctx.query.get("sources", [])), set(ctx.query.get("stdtypes", []))
+    allocs = set(ctx.query.get("allocationIds", [])) | set(ctx.query.get("containerIds", []))
+    t_after = _log_time(ctx.q("timestampAfter"))
+    t_before = _log_time(ctx.q("timestampBefore"))
+    needle = ctx.q("searchText")
+    filtered = bool(levels or ranks or sources or stdtypes or allocs or t_after or t_before or needle)
+
+    def keep(r: Any) -> bool:
+        return ((not levels or (r["level"] or "INFO") in levels) and (not ranks or r["rank_id"] in ranks) and (not sources or r["source"] in sources)
+                and (not stdtypes or r["stdtype"] in stdtypes) and (not allocs or r["allocation_id"] in allocs)
+                and (t_after is None or r["ts"] > t_after) and (t_before is None or r["ts"] < t_before) and (not needle or needle in (r["log"] or "")))
+
     while True:
-        rows = ctx.m.db.get_logs(task_id, after, limit)
+        rows = ctx.m.db.get_logs(task_id, after, limit if not filtered else 1_000_000)
+        if filtered:
+            rows = [r for r in rows if keep(r)][:limit]
         if rows or not follow or time.time() > deadline:
             break
         running = ctx.m.db.one("SELECT COUNT(*) c FROM allocations WHERE task_id=? AND state='RUNNING'", (task_id,))["c"]
@@ -1494,6 +1544,16 @@ def patch_model(ctx: Ctx, name: str) -> Any:
     for col, key, enc in (("description", "description", None), ("metadata", "metadata", dbmod.J), ("labels", "labels", dbmod.J), ("notes", "notes", None), ("name", "name", None)):
         if key in b and b[key] is not None:
             ctx.m.db.exec(f"UPDATE models SET {col}=?, last_updated_time=? WHERE id=?", (enc(b[key]) if enc else b[key], time.time(), r["id"]))
+    wid = b.get("workspaceId")
+    if wid is None and b.get("workspaceName"):
+        w = ctx.m.db.one("SELECT id FROM workspaces WHERE name=?", (b["workspaceName"],))
+        if w is None:
+            raise HTTPError(404, f"workspace {b['workspaceName']!r} not found")
+        wid = w["id"]
+    if wid is not None:             # move the model (reference MoveModel)
+        if ctx.m.db.one("SELECT id FROM workspaces WHERE id=?", (int(wid),)) is None:
+            raise HTTPError(404, f"workspace {wid} not found")
+        ctx.m.db.exec("UPDATE models SET workspace_id=?, last_updated_time=? WHERE id=?", (int(wid), time.time(), r["id"]))
     return {"model": _model_json(ctx.m, ctx.m.db.one("SELECT * FROM models WHERE id=?", (r["id"],)))}
 
 
@@ -1582,7 +1642,9 @@ def get_workspace(ctx: Ctx, wid: str) -> Any:
     r = ctx.m.db.one("SELECT * FROM workspaces WHERE id=?", (int(wid),))
     if r is None:
         raise HTTPError(404, "workspace not found")
-    return {"workspace": {"id": r["id"], "name": r["name"], "archived": bool(r["archived"]), "immutable": bool(r["immutable"]), "userId": r["user_id"]}}
+    from determined_b200.master import api_more
+
+    return {"workspace": api_more.workspace_json(ctx, r)}
 
 
 @route("DELETE", "/api/v1/workspaces/{wid}")
@@ -2214,3 +2276,6 @@ class APIServer:
     def stop(self) -> None:
         self.httpd.shutdown()
         self.httpd.server_close()
+
+
+from determined_b200.master import api_more  # noqa: E402,F401  (registers its routes)

@@ -82,7 +82,10 @@ class CommandTask:
         self.slot_ids: List[int] = []
         self.token = secrets.token_hex(16)
         self.killed = False
+        # the context directory shipped with the task (``det cmd run --context DIR`` / ``--include``): v1 file entries
+        self.files: List[Dict[str, Any]] = list(body.get("files") or [])
         self.context: Optional[bytes] = body.get("_context")
+        self.paused = False
         ep = config.get("entrypoint")
         if not ep:
             ep = default_entrypoint(kind, body)
@@ -136,13 +139,17 @@ class CommandTask:
             self.state, self.last_activity = "RUNNING", time.time()
             m.db.exec("UPDATE tasks SET state=? WHERE id=?", (self.state, self.id))
             argv = [agents_mod.PYTHON_PLACEHOLDER if a == sys.executable else a for a in self.argv]
+            if self.files and not self.context:
+                from determined_b200.common import context as det_context
+
+                self.context = det_context.v1_context_to_tarball(self.files)
             m.agents.start(self.agent_id, self.id, self, argv, task_env, slot_ids, archive=self.context, workdir="model")
             return
         self.run_dir = tempfile.mkdtemp(prefix=f"detb200-{self.kind.lower()}-{self.id[:8]}-", dir=m.work_dir)
-        if self.context:
+        if self.files:
             from determined_b200.common import context as det_context
 
-            det_context.extract_tarball(self.context, self.run_dir) if hasattr(det_context, "extract_tarball") else None
+            det_context.write_v1_context(self.files, pathlib.Path(self.run_dir))
         env = dict(os.environ)
         env.update(task_env)
         env["DET_RUN_DIR"] = self.run_dir
@@ -164,14 +171,28 @@ class CommandTask:
         assert self.proc is not None and self.proc.stdout is not None
         m = self.mgr.master
         batch: List[Any] = []
-        last = time.time()
+        lock = threading.Lock()
+        done = threading.Event()
+
+        def flush() -> None:
+            with lock:
+                rows, batch[:] = list(batch), []
+            if rows:
+                m.db.add_logs(rows)
+
+        def ticker() -> None:          # a line must not wait for the next one to be written: flush on a clock as well
+            while not done.wait(0.3):
+                flush()
+
+        threading.Thread(target=ticker, daemon=True, name=f"cmdflush-{self.id[:8]}").start()
         for line in self.proc.stdout:
-            batch.append((self.id, self.id + ".1", time.time(), "INFO", None, "stdout", "task", line if line.endswith("\n") else line + "\n"))
-            if len(batch) >= 100 or time.time() - last > 0.3:
-                m.db.add_logs(batch)
-                batch, last = [], time.time()
-        if batch:
-            m.db.add_logs(batch)
+            with lock:
+                batch.append((self.id, self.id + ".1", time.time(), "INFO", None, "stdout", "task", line if line.endswith("\n") else line + "\n"))
+                full = len(batch) >= 100
+            if full:
+                flush()
+        done.set()
+        flush()
         code = self.proc.wait()
         self.finish(code)
 

@@ -53,6 +53,9 @@ CREATE TABLE IF NOT EXISTS trial_source_infos (id INTEGER PRIMARY KEY AUTOINCREM
     type TEXT, model_id INTEGER, model_version INTEGER);
 CREATE TABLE IF NOT EXISTS groups (id INTEGER PRIMARY KEY AUTOINCREMENT, name TEXT UNIQUE);
 CREATE TABLE IF NOT EXISTS group_members (group_id INTEGER, user_id INTEGER, UNIQUE(group_id, user_id));
+CREATE TABLE IF NOT EXISTS attrs (kind TEXT, id TEXT, key TEXT, value TEXT, PRIMARY KEY(kind, id, key));
+CREATE TABLE IF NOT EXISTS rp_bindings (pool TEXT, workspace_id INTEGER, UNIQUE(pool, workspace_id));
+CREATE TABLE IF NOT EXISTS oauth_clients (id TEXT PRIMARY KEY, name TEXT, domain TEXT, secret TEXT, created REAL);
 CREATE TABLE IF NOT EXISTS role_assignments (id INTEGER PRIMARY KEY AUTOINCREMENT, role TEXT, user_id INTEGER, group_id INTEGER, workspace_id INTEGER);
 """
 
