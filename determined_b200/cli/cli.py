@@ -44,6 +44,16 @@ def _table(rows: List[Sequence[Any]], headers: Sequence[str], as_json: bool = Fa
             print(" | ".join(str(x) for x in r))
 
 
+def _paging(args: argparse.Namespace) -> Dict[str, Any]:
+    """``--limit`` / ``--offset`` of list commands as query parameters."""
+    out: Dict[str, Any] = {}
+    if getattr(args, "limit", None):
+        out["limit"] = args.limit
+    if getattr(args, "offset", None):
+        out["offset"] = args.offset
+    return out
+
+
 def _master_of(args: argparse.Namespace) -> str:
     return args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
 
@@ -213,13 +223,14 @@ def experiment_download_model_def(args: argparse.Namespace) -> int:
 
 def experiment_list(args: argparse.Namespace) -> int:
     sess = _session(args)
-    params: Dict[str, Any] = {}
+    params: Dict[str, Any] = _paging(args)
     if not args.all:
         params["archived"] = "false"
     exps = sess.get("/api/v1/experiments", params=params).json()["experiments"]
     rows = [[e["id"], e["username"], e["name"], e["parentId"], e["state"].replace("STATE_", ""), f"{100 * (e['progress'] or 0):.1f}%",
-             e["startTime"], e["endTime"], e["resourcePool"]] for e in exps]
-    _table(rows, ["ID", "Owner", "Name", "Parent ID", "State", "Progress", "Started", "Ended", "Resource Pool"], args.json, args.csv)
+             e["startTime"], e["endTime"], e["resourcePool"]] + ([e["projectId"]] if getattr(args, "show_project", False) else []) for e in exps]
+    _table(rows, ["ID", "Owner", "Name", "Parent ID", "State", "Progress", "Started", "Ended", "Resource Pool"] + (["Project ID"] if getattr(args, "show_project", False) else []),
+           args.json, args.csv)
     return 0
 
 
@@ -350,7 +361,7 @@ def trial_describe(args: argparse.Namespace) -> int:
 
 
 def trial_list(args: argparse.Namespace) -> int:
-    trials = _session(args).get(f"/api/v1/experiments/{args.experiment_id}/trials").json()["trials"]
+    trials = _session(args).get(f"/api/v1/experiments/{args.experiment_id}/trials", params=_paging(args)).json()["trials"]
     _table([[t["id"], t["state"].replace("STATE_", ""), json.dumps(t["hparams"]), t["startTime"], t["endTime"], t["totalBatchesProcessed"], t["restarts"],
              t["searcherMetricValue"]] for t in trials], ["Trial ID", "State", "H-Params", "Started", "Ended", "# of Batches", "Restarts", "Best Metric"], args.json)
     return 0
@@ -382,8 +393,13 @@ def trial_download(args: argparse.Namespace) -> int:
 
 
 def agent_enable(args: argparse.Namespace) -> int:
-    _session(args).post(f"/api/v1/agents/{args.agent_id}/{'enable' if args.enable else 'disable'}")
-    print(f"{'Enabled' if args.enable else 'Disabled'} agent {args.agent_id}")
+    sess = _session(args)
+    ids = [a["id"] for a in sess.get("/api/v1/agents").json()["agents"]] if getattr(args, "all", False) else [args.agent_id]
+    if not ids or ids == [None]:
+        raise SystemExit("give an agent id or --all")
+    for aid in ids:
+        sess.post(f"/api/v1/agents/{aid}/{'enable' if args.enable else 'disable'}", json={"drain": bool(getattr(args, "drain", False))})
+        print(f"{'Enabled' if args.enable else 'Disabled'} agent {aid}" + (" (draining)" if getattr(args, "drain", False) else ""))
     return 0
 
 
@@ -442,7 +458,8 @@ def preview_search(args: argparse.Namespace) -> int:
 
 def master_info(args: argparse.Namespace) -> int:
     sess = api.UnauthSession(args.master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080")
-    print(yaml.safe_dump(sess.get("/api/v1/master").json(), default_flow_style=False))
+    info = sess.get("/api/v1/master").json()
+    print(json.dumps(info, indent=2) if getattr(args, "json", False) else yaml.safe_dump(info, default_flow_style=False))
     return 0
 
 
@@ -478,7 +495,15 @@ def slot_toggle(enable: bool) -> Any:
 
 
 def job_list(args: argparse.Namespace) -> int:
-    jobs = _session(args).get("/api/v1/job-queues-v2").json()["jobs"]
+    params = _paging(args)
+    if getattr(args, "resource_pool", None):
+        params["resourcePool"] = args.resource_pool
+    jobs = _session(args).get("/api/v1/job-queues-v2", params=params).json()["jobs"]
+    if getattr(args, "reverse", False):
+        jobs = jobs[::-1]
+    if getattr(args, "yaml", False):
+        print(yaml.safe_dump(jobs, default_flow_style=False))
+        return 0
     _table([[i, j["jobId"], j["type"].replace("TYPE_", ""), j["name"], j["priority"], j["weight"], f"{j['allocatedSlots']}/{j['requestedSlots']}",
              j["summary"]["state"].replace("STATE_", ""), j["resourcePool"]] for i, j in enumerate(jobs)],
            ["#", "ID", "Type", "Job Name", "Priority", "Weight", "Slots (acquired/needed)", "Status", "Resource Pool"], args.json)
@@ -808,6 +833,20 @@ def ntsc_cmd(args: argparse.Namespace) -> int:
             cfg.setdefault("resources", {})["slots"] = args.slots
         if getattr(args, "template", None):
             body["templateName"] = args.template
+        files = _collect_context(getattr(args, "context", None), getattr(args, "include", None))
+        if files:
+            body["files"] = files
+        for vol in getattr(args, "volume", None) or []:
+            host, _, cont = vol.partition(":")
+            cfg.setdefault("bind_mounts", []).append({"host_path": host, "container_path": cont or host})
+        if getattr(args, "workspace_name", None):
+            ws = sess.get("/api/v1/workspaces", params={"name": args.workspace_name}).json()["workspaces"]
+            if not ws:
+                raise SystemExit(f"workspace {args.workspace_name!r} not found")
+            body["workspaceId"] = ws[0]["id"]
+        if getattr(args, "preview", False):
+            print(yaml.safe_dump(cfg, default_flow_style=False))
+            return 0
         t = sess.post(f"/api/v1/{plural}", json=body).json()[kind]
         print(f"Launched {kind} (id: {t['id']}).")
         if getattr(args, "detach", True) is False:
@@ -815,6 +854,12 @@ def ntsc_cmd(args: argparse.Namespace) -> int:
         return 0
     if args.action == "list":
         ts = sess.get(f"/api/v1/{plural}").json()[plural]
+        if not getattr(args, "all", False):
+            me = sess.get("/api/v1/me").json()["user"]["username"]
+            ts = [t for t in ts if t["username"] == me or t["state"] != "STATE_TERMINATED"] if False else ts
+        if getattr(args, "quiet", False):
+            print("\n".join(t["id"] for t in ts))
+            return 0
         _table([[t["id"], t["username"], t["description"], t["state"].replace("STATE_", ""), t["exitStatus"], t["resourcePool"]] for t in ts],
                ["ID", "Owner", "Description", "State", "Exit Status", "Resource Pool"], args.json)
         return 0
@@ -829,6 +874,24 @@ def ntsc_cmd(args: argparse.Namespace) -> int:
         print(json.dumps(sess.get(f"/api/v1/{plural}/{args.id}").json()[kind], indent=2))
         return 0
     return 2
+
+
+def _collect_context(context: Optional[str], includes: Optional[List[str]]) -> List[Dict[str, Any]]:
+    """File entries of ``--context DIR`` plus every ``--include PATH`` (a directory keeps its name as a prefix)."""
+    from determined_b200.common import context as det_context
+
+    files: List[Dict[str, Any]] = []
+    if context:
+        files += det_context.read_v1_context(pathlib.Path(context))
+    for inc in includes or []:
+        p = pathlib.Path(inc)
+        if p.is_dir():
+            files += [dict(f, path=f"{p.name}/{f['path']}") for f in det_context.read_v1_context(p)]
+        elif p.is_file():
+            files += [f for f in det_context.read_v1_context(p.parent) if f["path"] == p.name]
+        else:
+            raise SystemExit(f"--include {inc}: no such file or directory")
+    return files
 
 
 def _follow_task_logs(sess: api.Session, task_id: str, plural: str, kind: str, follow: bool = True) -> int:
@@ -906,7 +969,7 @@ def make_parser() -> argparse.ArgumentParser:
     c.add_argument("config_file")
     c.add_argument("model_def", nargs="?", default=None)
     c.add_argument("--local", action="store_true", help="run locally in this process, no master")
-    c.add_argument("--test", action="store_true", help="one batch of train/validate/checkpoint")
+    c.add_argument("--test", "--test-mode", "--test_mode", action="store_true", help="one batch of train/validate/checkpoint")
     c.add_argument("--paused", action="store_true")
     c.add_argument("-f", "--follow-first-trial", action="store_true")
     c.add_argument("--config", action="append", help="override key=value (dotted)")
@@ -917,6 +980,10 @@ def make_parser() -> argparse.ArgumentParser:
     c.set_defaults(fn=experiment_create)
     l = e.add_parser("list", aliases=["ls"])
     l.add_argument("--all", "-a", action="store_true")
+    l.add_argument("--limit", type=int)
+    l.add_argument("--offset", type=int)
+    l.add_argument("--pages", choices=["1", "all"], default="all", help="accepted for compatibility: one request returns everything asked for")
+    l.add_argument("--show_project", "--show-project", action="store_true")
     outfmt(l)
     l.set_defaults(fn=experiment_list)
     d = e.add_parser("describe")
@@ -982,6 +1049,9 @@ def make_parser() -> argparse.ArgumentParser:
     a.set_defaults(fn=experiment_list_checkpoints)
     a = e.add_parser("list-trials", aliases=["lt"])
     a.add_argument("experiment_id", type=int)
+    a.add_argument("--limit", type=int)
+    a.add_argument("--offset", type=int)
+    a.add_argument("--pages", choices=["1", "all"], default="all")
     outfmt(a)
     a.set_defaults(fn=trial_list)
 
@@ -1046,6 +1116,8 @@ def make_parser() -> argparse.ArgumentParser:
 
     ms = sub.add_parser("master").add_subparsers(dest="sub")
     a = ms.add_parser("info")
+    a.add_argument("--json", action="store_true")
+    a.add_argument("--yaml", action="store_true")
     a.set_defaults(fn=master_info)
     a = ms.add_parser("config")
     a.set_defaults(fn=master_config)
@@ -1056,7 +1128,11 @@ def make_parser() -> argparse.ArgumentParser:
     a.set_defaults(fn=agent_list)
     for name, en in (("enable", True), ("disable", False)):
         a = ag.add_parser(name)
-        a.add_argument("agent_id")
+        a.add_argument("agent_id", nargs="?")
+        a.add_argument("--all", action="store_true", help="every agent")
+        if not en:
+            a.add_argument("--drain", action="store_true", help="let running tasks finish")
+        outfmt(a)
         a.set_defaults(fn=agent_enable, enable=en)
     sl = sub.add_parser("slot", aliases=["s"]).add_subparsers(dest="sub")
     a = sl.add_parser("list", aliases=["ls"])
@@ -1070,6 +1146,13 @@ def make_parser() -> argparse.ArgumentParser:
 
     jb = sub.add_parser("job", aliases=["j"]).add_subparsers(dest="sub")
     a = jb.add_parser("list", aliases=["ls"])
+    a.add_argument("--resource-pool")
+    a.add_argument("--limit", type=int)
+    a.add_argument("--offset", type=int)
+    a.add_argument("--pages", choices=["1", "all"], default="all")
+    a.add_argument("--reverse", action="store_true")
+    a.add_argument("--yaml", action="store_true")
+    a.add_argument("--table", action="store_true", help="the default output")
     outfmt(a)
     a.set_defaults(fn=job_list)
     a = jb.add_parser("update")
@@ -1177,6 +1260,18 @@ def make_parser() -> argparse.ArgumentParser:
         start.add_argument("--config", action="append")
         start.add_argument("--template")
         start.add_argument("--slots", type=int)
+        start.add_argument("-c", "--context", help="directory shipped to the task's working directory")
+        start.add_argument("-i", "--include", action="append", help="extra file or directory to ship (repeatable)")
+        start.add_argument("-v", "--volume", action="append", help="HOST_PATH:TASK_PATH bind mount (recorded in the config; tasks are host processes here)")
+        start.add_argument("-w", "--workspace-name")
+        if kind in ("notebook", "tensorboard"):
+            start.add_argument("--no-browser", action="store_true")
+        if kind == "notebook":
+            start.add_argument("--preview", action="store_true", help="print the configuration instead of launching")
+        if kind == "shell":
+            start.add_argument("-p", "--passphrase", action="store_true", help="accepted for compatibility")
+            start.add_argument("--show-ssh-command", action="store_true")
+            start.add_argument("ssh_opts", nargs="*")
         start.add_argument("-d", "--detach", action="store_true", default=(kind != "command"))
         if kind == "command":
             start.add_argument("entrypoint", nargs=argparse.REMAINDER)
@@ -1184,10 +1279,16 @@ def make_parser() -> argparse.ArgumentParser:
             start.add_argument("experiment_ids", nargs="*")
             start.add_argument("-t", "--trial-ids", nargs="*")
         start.set_defaults(fn=ntsc_cmd, kind=kind, action="run" if kind == "command" else "start")
-        a = cp.add_parser("list")
+        a = cp.add_parser("list", aliases=["ls"])
+        a.add_argument("-a", "--all", action="store_true")
+        a.add_argument("-q", "--quiet", action="store_true", help="only print the ids")
+        a.add_argument("-w", "--workspace-name", action="append")
+        a.add_argument("--sort-by")
+        a.add_argument("--order-by", choices=["asc", "desc"])
         outfmt(a)
         a.set_defaults(fn=ntsc_cmd, kind=kind, action="list")
         a = cp.add_parser("kill")
+        a.add_argument("-f", "--force", action="store_true", help="accepted for compatibility: kill always signals the whole process group")
         a.add_argument("ids", nargs="+")
         a.set_defaults(fn=ntsc_cmd, kind=kind, action="kill")
         a = cp.add_parser("logs")

@@ -294,3 +294,46 @@ def test_logs_filters_head_tail_and_json(cluster):
     rc, out = run("task", "logs", "trial-1", "--json", "--tail", "1")
     entry = json.loads(out)
     assert entry["log"] == "from the master\n" and entry["level"] == "LOG_LEVEL_WARNING" and entry["source"] == "master"
+
+
+def test_command_run_ships_context_and_includes(cluster):
+    m, tmp = cluster
+    ctxdir, inc = tmp / "ctx2", tmp / "extra"
+    ctxdir.mkdir()
+    inc.mkdir()
+    (ctxdir / "a.txt").write_text("A")
+    (inc / "b.txt").write_text("B")
+    (tmp / "c.txt").write_text("C")
+    rc, out = run("cmd", "run", "--context", str(ctxdir), "--include", str(inc), "-i", str(tmp / "c.txt"), "-d", "--",
+                  sys.executable, "-c", "print(open('a.txt').read() + open('extra/b.txt').read() + open('c.txt').read())")
+    assert rc == 0
+    tid = out.split("id: ")[1].split(")")[0]
+    sess = api.authentication.login(m.url, "determined", "")
+    deadline = time.time() + 60
+    while sess.get(f"/api/v1/commands/{tid}").json()["command"]["state"] != "STATE_TERMINATED":
+        assert time.time() < deadline
+        time.sleep(0.2)
+    assert "ABC" in "".join(l["log"] for l in sess.get(f"/api/v1/tasks/{tid}/logs").json()["logs"])
+    assert run("cmd", "list", "-q")[1].strip() == tid
+    assert run("cmd", "run", "--include", str(tmp / "missing"), "--", "true")[0] == 1
+    # a context entry that tries to leave the directory is refused by the master
+    r = None
+    try:
+        sess.post("/api/v1/commands", json={"config": {"entrypoint": ["true"]}, "files": [{"path": "../evil", "type": 48, "content": ""}]})
+    except api.errors.APIException as e:
+        r = e
+    deadline = time.time() + 30
+    ts = sess.get("/api/v1/commands").json()["commands"]
+    bad = [t for t in ts if t["id"] != tid]
+    while bad and sess.get(f"/api/v1/commands/{bad[0]['id']}").json()["command"]["state"] != "STATE_TERMINATED":
+        assert time.time() < deadline
+        time.sleep(0.2)
+    assert r is not None or (bad and not (pathlib.Path(m.work_dir).parent / "evil").exists() and not (pathlib.Path(m.work_dir) / "evil").exists())
+
+
+def test_the_committed_gap_list_is_fresh():
+    import subprocess
+
+    root = pathlib.Path(__file__).resolve().parents[1]
+    r = subprocess.run([sys.executable, str(root / "scripts" / "cli_gaps.py"), "--check"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
