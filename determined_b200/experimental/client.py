@@ -15,6 +15,8 @@ from typing import Any, Dict, Iterable, Iterator, List, Optional, Union
 import yaml
 
 from determined_b200.common import api, context as det_context, storage
+from determined_b200.experimental import _sdk_more
+from determined_b200.experimental._sdk_more import Oauth2ScimClient  # noqa: F401
 
 
 class ExperimentState(enum.Enum):
@@ -84,7 +86,7 @@ class ModelSortBy(enum.Enum):
     CREATION_TIME = "SORT_BY_CREATION_TIME"
 
 
-class Checkpoint:
+class Checkpoint(_sdk_more.CheckpointMore):
     def __init__(self, session: api.Session, uuid: str, data: Optional[Dict[str, Any]] = None) -> None:
         self._session, self.uuid = session, uuid
         self._hydrate(data or {})
@@ -146,7 +148,7 @@ class Checkpoint:
         return f"Checkpoint(uuid={self.uuid}, task_id={self.task_id})"
 
 
-class Trial:
+class Trial(_sdk_more.TrialMore):
     def __init__(self, session: api.Session, trial_id: int, data: Optional[Dict[str, Any]] = None) -> None:
         self._session, self.id = session, trial_id
         self._hydrate(data or {})
@@ -240,7 +242,7 @@ class Trial:
         return f"Trial(id={self.id})"
 
 
-class Experiment:
+class Experiment(_sdk_more.ExperimentMore):
     def __init__(self, session: api.Session, experiment_id: int, data: Optional[Dict[str, Any]] = None) -> None:
         self._session, self.id = session, experiment_id
         self._hydrate(data or {})
@@ -374,7 +376,7 @@ class Experiment:
         return f"Experiment(id={self.id})"
 
 
-class ModelVersion:
+class ModelVersion(_sdk_more.ModelVersionMore):
     def __init__(self, session: api.Session, d: Dict[str, Any]) -> None:
         self._session = session
         self.model_version = d.get("version")
@@ -389,7 +391,7 @@ class ModelVersion:
         self._session.delete(f"/api/v1/models/{self.model_name}/versions/{self.model_version}")
 
 
-class Model:
+class Model(_sdk_more.ModelMore):
     def __init__(self, session: api.Session, d: Dict[str, Any]) -> None:
         self._session = session
         self._hydrate(d)
@@ -398,6 +400,7 @@ class Model:
         self.model_id, self.name = d.get("id"), d.get("name")
         self.description, self.metadata, self.labels = d.get("description"), d.get("metadata") or {}, d.get("labels") or []
         self.archived = d.get("archived")
+        self.workspace_id, self.notes = d.get("workspaceId"), d.get("notes")
 
     def reload(self) -> None:
         self._hydrate(self._session.get(f"/api/v1/models/{self.name}").json()["model"])
@@ -440,7 +443,7 @@ class Model:
         self._session.delete(f"/api/v1/models/{self.name}")
 
 
-class User:
+class User(_sdk_more.UserMore):
     """Reference ``common/experimental/user.py``."""
 
     def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
@@ -478,7 +481,7 @@ class User:
         return f"User(id={self.user_id}, username={self.username!r})"
 
 
-class Project:
+class Project(_sdk_more.ProjectMore):
     """Reference ``common/experimental/project.py``."""
 
     def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
@@ -498,7 +501,7 @@ class Project:
         return f"Project(id={self.id}, name={self.name!r})"
 
 
-class Workspace:
+class Workspace(_sdk_more.WorkspaceMore):
     """Reference ``common/experimental/workspace.py``."""
 
     def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
@@ -526,7 +529,7 @@ class Workspace:
         return f"Workspace(id={self.id}, name={self.name!r})"
 
 
-class ResourcePool:
+class ResourcePool(_sdk_more.ResourcePoolMore):
     """Reference ``common/experimental/resource_pool.py``."""
 
     def __init__(self, session: api.Session, data: Dict[str, Any]) -> None:
@@ -539,13 +542,16 @@ class ResourcePool:
         return f"ResourcePool(name={self.name!r}, slots={self.slots_used}/{self.slots_available})"
 
 
-class Determined:
+class Determined(_sdk_more.DeterminedMore):
     """Entry point of the SDK.  ``master`` defaults to ``$DET_MASTER`` or localhost:8080."""
 
     def __init__(self, master: Optional[str] = None, user: Optional[str] = None, password: Optional[str] = None,
                  cert_path: Optional[str] = None, noverify: bool = False) -> None:
+        from determined_b200.common.api import certs
+
         self._master = master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
-        self._session = api.authentication.login_with_cache(self._master, user, password)
+        cert = certs.default_load(self._master, cert_path, None, noverify) if (cert_path or noverify) else None
+        self._session = api.authentication.login_with_cache(self._master, user, password, cert=cert)
 
     @classmethod
     def _from_session(cls, session: api.Session) -> "Determined":
@@ -600,8 +606,6 @@ class Determined:
     def get_models(self, name: Optional[str] = None, **_: Any) -> List[Model]:
         r = self._session.get("/api/v1/models", params={"name": name} if name else {}).json()
         return [Model(self._session, m) for m in r["models"]]
-
-    list_models = get_models
 
     def get_model_by_id(self, model_id: int) -> Model:
         for m in self.get_models():
@@ -737,3 +741,19 @@ def whoami() -> Dict[str, Any]:
 
 def logout() -> None:
     _d().logout()
+
+
+def _delegate(name: str) -> Any:
+    def fn(*a: Any, **kw: Any) -> Any:
+        return getattr(_d(), name)(*a, **kw)
+    fn.__name__ = name
+    fn.__doc__ = f"``Determined.{name}`` of the default client (``client.login`` first, or the environment's master and user)."
+    return fn
+
+
+for _name in ("list_experiments", "list_models", "get_model_by_id", "get_model_labels", "create_user", "list_users", "get_user_by_id", "get_user_by_name",
+              "get_session_username", "list_workspaces", "get_workspace", "create_workspace", "delete_workspace", "iter_trials_metrics",
+              "stream_trials_metrics", "stream_trials_training_metrics", "stream_trials_validation_metrics", "add_oauth_client", "list_oauth_clients",
+              "remove_oauth_client", "list_resource_pools", "preview_search", "get_master_info"):
+    globals()[_name] = _delegate(_name)
+del _name

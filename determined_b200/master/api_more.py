@@ -676,3 +676,22 @@ def oauth_remove(ctx: Ctx, cid: str) -> Any:
         raise HTTPError(404, "client not found")
     ctx.m.db.exec("DELETE FROM oauth_clients WHERE id=?", (cid,))
     return {}
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# model versions: rename, annotate
+# ---------------------------------------------------------------------------------------------------------------------
+@route("PATCH", "/api/v1/models/{name}/versions/{version}")
+def patch_model_version(ctx: Ctx, name: str, version: str) -> Any:
+    from determined_b200.master.api import _model, _mv_json
+
+    mdl = _model(ctx, name)
+    v = ctx.m.db.one("SELECT * FROM model_versions WHERE model_id=? AND version=?", (mdl["id"], int(version)))
+    if v is None:
+        raise HTTPError(404, f"model {name!r} has no version {version}")
+    b = (ctx.body or {}).get("modelVersion", ctx.body or {})
+    for col, enc in (("name", None), ("comment", None), ("notes", None), ("metadata", dbmod.J), ("labels", dbmod.J)):
+        if b.get(col) is not None:
+            ctx.m.db.exec(f"UPDATE model_versions SET {col}=? WHERE id=?", (enc(b[col]) if enc else b[col], v["id"]))
+    ctx.m.db.exec("UPDATE models SET last_updated_time=? WHERE id=?", (time.time(), mdl["id"]))
+    return {"modelVersion": _mv_json(ctx.m, ctx.m.db.one("SELECT * FROM model_versions WHERE id=?", (v["id"],)))}

@@ -1,0 +1,130 @@
+"""The wider SDK object model (``experimental/_sdk_more.py``) against an in-process master without trial processes: metrics
+and checkpoints are reported through the REST API the way a harness would."""
+import pathlib
+import time
+import uuid
+
+import pytest
+import yaml
+
+from determined_b200.common import api
+from determined_b200.experimental import client
+from determined_b200.master import api as mapi
+from determined_b200.master import core
+
+FIX = pathlib.Path(__file__).parent / "fixtures" / "onevar_exp"
+CFG = {"name": "sdk-exp", "entrypoint": "model_def:OneVarTrial", "searcher": {"name": "random", "metric": "val_loss", "max_length": 20, "max_trials": 3, "max_concurrent_trials": 3},
+       "hyperparameters": {"learning_rate": {"type": "double", "minval": 0.01, "maxval": 0.1}, "global_batch_size": 8}}
+
+
+@pytest.fixture()
+def det(tmp_path, monkeypatch):
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=4, launch=False, work_dir=str(tmp_path / "w"),
+                    cluster_defaults={"checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ck")}},
+                    resource_pools=[{"pool_name": "default"}, {"pool_name": "aux"}])
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    monkeypatch.setenv("DET_CONFIG_DIR", str(tmp_path / "config"))
+    monkeypatch.delenv("DET_SESSION_TOKEN", raising=False)
+    d = client.Determined(m.url, "admin", "")
+    yield d, m, tmp_path
+    m.stop()
+    srv.stop()
+
+
+def test_experiment_trial_checkpoint_extras(det):
+    d, m, tmp = det
+    exp = d.create_experiment(CFG, str(FIX), activate=False)
+    exp.set_labels(["b", "a", "a"])
+    exp.set_notes("remember this")
+    exp.reload()
+    assert exp.labels == ["a", "b"] and d._session.get(f"/api/v1/experiments/{exp.id}").json()["experiment"]["notes"] == "remember this"
+    code = exp.download_code(str(tmp / "code"))
+    assert (pathlib.Path(code) / "model_def.py").exists()
+    trials = exp.get_trials()
+    assert len(trials) == 3 and [t.id for t in exp.iter_trials(limit=2)] == [t.id for t in trials]
+    t = trials[0]
+    sess = d._session
+    for steps, v in ((10, 0.5), (20, 0.25)):
+        sess.post(f"/api/v1/trials/{t.id}/metrics", json={"group": "validation", "metrics": {"trialId": t.id, "trialRunId": 0, "stepsCompleted": steps,
+                                                                                                "metrics": {"avgMetrics": {"val_loss": v}}}})
+    ck_uuid = str(uuid.uuid4())
+    sess.post("/api/v1/checkpoints", json={"uuid": ck_uuid, "taskId": f"trial-{t.id}", "allocationId": None, "reportTime": "2024-01-01T00:00:00Z",
+                                           "state": "STATE_COMPLETED", "resources": {"w.bin": "3"}, "metadata": {"steps_completed": 20}, "training": {}})
+    ck = d.get_checkpoint(ck_uuid)
+    got = list(ck.get_metrics("validation"))
+    assert [g["steps_completed"] for g in got] == [20] and got[0]["metrics"] == {"val_loss": 0.25}
+    assert [x["steps_completed"] for x in t.stream_metrics("validation")] == [10, 20]
+    # logs with filters
+    now = time.time()
+    m.db.add_logs([(f"trial-{t.id}", "a", now - 5 + i, "ERROR" if i == 3 else "INFO", i % 2, "stdout", "task", f"l{i}\n") for i in range(6)])
+    assert list(t.iter_logs(head=2)) == ["l0\n", "l1\n"] and list(t.iter_logs(tail=1)) == ["l5\n"]
+    assert list(t.iter_logs(min_level="WARNING")) == ["l3\n"] and list(t.iter_logs(rank_ids=[1], search_text="l5")) == ["l5\n"]
+    tb = tmp / "ck" / "tensorboard" / f"experiment-{exp.id}"
+    tb.mkdir(parents=True)
+    (tb / "events").write_bytes(b"x")
+    exp.delete_tensorboard_files()
+    assert not tb.exists()
+    # model registry extras
+    model = d.create_model("sdk-model", metadata={"a": 1, "b": 2})
+    v = model.register_version(ck_uuid)
+    v.set_name("first")
+    v.set_notes("notes!")
+    v.reload()
+    assert (v.name, v.notes) == ("first", "notes!") and [g["steps_completed"] for g in v.iter_metrics("validation")] == [20]
+    model.remove_metadata(["a"])
+    model.reload()
+    assert model.metadata == {"b": 2}
+    ws = d.create_workspace("sdk-ws")
+    model.move_to_workspace("sdk-ws")
+    model.reload()
+    assert model.workspace_id == ws.id
+    assert [x.name for x in d.list_models(workspace_names=["sdk-ws"])] == ["sdk-model"] and d.list_models(workspace_ids=[1]) == []
+
+
+def test_projects_workspaces_pools_users_oauth(det):
+    d, m, tmp = det
+    ws = d.create_workspace("team")
+    p = ws.create_project("vision", "images")
+    p.set_name("vision2")
+    p.set_description("pictures")
+    p.add_note("todo", "label more data")
+    p.add_note("done", "cleaned set A")
+    p.remove_note("todo")
+    with pytest.raises(ValueError):
+        p.remove_note("nope")
+    p.reload()
+    assert (p.name, p.description, p.notes) == ("vision2", "pictures", [{"name": "done", "contents": "cleaned set A"}])
+    p.archive()
+    p.reload()
+    assert p.archived
+    p.unarchive()
+    pool = next(x for x in d.list_resource_pools() if x.name == "aux")
+    pool.add_bindings(["team"])
+    assert [w.name for w in pool.list_workspaces()] == ["team"]
+    other = d.create_workspace("other")
+    assert {x.name for x in ws.list_pools()} == {"default", "aux"} and {x.name for x in other.list_pools()} == {"default"}
+    pool.replace_bindings(["other"])
+    assert [w.name for w in pool.list_workspaces()] == ["other"]
+    pool.remove_bindings(["other"])
+    assert pool.list_workspaces() == []
+    ws.set_default_pools(compute="aux")
+    ws.reload()
+    assert ws.default_compute_pool == "aux"
+    ws.archive()
+    ws.reload()
+    assert ws.archived
+    ws.unarchive()
+    ws.delete_project("vision2")
+    assert ws.list_projects() == []
+    u = d.create_user("bob")
+    u.link_with_agent(agent_uid=1500, agent_gid=1500, agent_user="bob", agent_group="staff")
+    assert d._session.get("/api/v1/users/bob").json()["user"]["agentUserGroup"] == {"agentUid": 1500, "agentGid": 1500, "agentUser": "bob", "agentGroup": "staff"}
+    c = d.add_oauth_client("https://idp.example.com", "idp")
+    assert c.secret and [x.id for x in d.list_oauth_clients()] == [c.id]
+    d.remove_oauth_client(c.id)
+    assert d.list_oauth_clients() == []
+    # module-level shortcuts use the default client
+    client._determined = d
+    assert "team" in [w.name for w in client.list_workspaces()] and client.get_session_username() == "admin"
+    assert client.get_user_by_name("bob").username == "bob"
