@@ -62,10 +62,17 @@ class TrainContext:
         }
         self._session.post(f"/api/v1/trials/{self._trial_id}/metrics", data=util.json_encode(body))
         if self._tbd_writer is not None and group in ("training", "validation"):
-            prefix = "Determined/" if group == "training" else "Determined/val_"
-            for k, v in metrics.items():
-                if util.is_numerical_scalar(v):
-                    self._tbd_writer.add_scalar(prefix + k, float(v), steps_completed)
+            w = self._tbd_writer
+            if hasattr(w, "on_train_step_end"):          # tensorboard.metric_writers.BatchMetricWriter
+                if group == "training":
+                    w.on_train_step_end(steps_completed, metrics, batch_metrics)
+                else:
+                    w.on_validation_step_end(steps_completed, metrics)
+            else:                                        # a bare SummaryWriter
+                prefix = "Determined/" if group == "training" else "Determined/val_"
+                for k, v in metrics.items():
+                    if util.is_numerical_scalar(v):
+                        w.add_scalar(prefix + k, float(v), steps_completed)
         if self._tensorboard_mode == TensorboardMode.AUTO and self._tensorboard_manager is not None:
             self._tensorboard_manager.sync()
 

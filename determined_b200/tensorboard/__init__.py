@@ -187,4 +187,6 @@ def get_metric_writer() -> Any:
     """A ``torch.utils.tensorboard.SummaryWriter``-backed batch metric writer, if available."""
     from determined_b200.tensorboard.metric_writers import BatchMetricWriter
 
-    return BatchMetricWriter.try_build()
+    # the directory the TensorboardManager built with the default configuration watches and syncs (reference
+    # ``tensorboard/__init__.py:get_metric_writer`` -> ``get_base_path({})``)
+    return BatchMetricWriter.try_build(get_base_path({}))
