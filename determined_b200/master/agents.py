@@ -155,16 +155,17 @@ class AgentRegistry:
 
     # -- master -> agent -----------------------------------------------------------------------------
     def start(self, agent_id: str, container_id: str, sink: Any, argv: List[str], env: Dict[str, str], slot_ids: List[int],
-              archive: Optional[bytes] = None, workdir: str = "") -> None:
+              archive: Optional[bytes] = None, workdir: str = "", hpc: Optional[Dict[str, Any]] = None) -> None:
         """Queue a ``start`` for the agent.  ``archive`` (a tarball) is unpacked into ``<run dir>/model`` on the agent, the
         process starts in ``<run dir>/<workdir>``; ``env`` holds only what the master decides (``DET_*``, user variables):
-        the agent layers it over its own environment and adds the per-host paths."""
+        the agent layers it over its own environment and adds the per-host paths.  ``hpc`` carries the experiment's ``slurm`` /
+        ``pbs`` sections for pools backed by a workload manager."""
         ag = self.agents.get(agent_id)
         if ag is None or not ag.connected:
             raise RuntimeError(f"agent {agent_id} is not connected")
         ag.containers[container_id] = sink
         ag.push({"type": "start", "container_id": container_id, "argv": argv, "env": env, "slot_ids": slot_ids, "workdir": workdir,
-                 "archive": base64.b64encode(archive).decode() if archive else None})
+                 "archive": base64.b64encode(archive).decode() if archive else None, "hpc": hpc or {}})
 
     def kill(self, agent_id: str, container_id: str, sig: str = "TERM") -> None:
         ag = self.agents.get(agent_id)

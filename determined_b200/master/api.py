@@ -1395,7 +1395,8 @@ def resource_pools(ctx: Ctx) -> Any:
         out.append({"name": p.name, "description": ctx.m.pool_descriptions.get(p.name, ""), "type": "RESOURCE_POOL_TYPE_STATIC", "numAgents": len(live),
                     "slotsAvailable": sum(a.num_slots for a in live), "slotsUsed": sum(a.num_used() for a in p.agents.values()),
                     "slotType": "DEVICE_TYPE_CUDA" if ctx.m.num_gpus else "DEVICE_TYPE_CPU", "defaultComputePool": p.name == "default",
-                    "defaultAuxPool": p.name == "default", "preemptible": p.preemption, "schedulerType": "SCHEDULER_TYPE_" + p.scheduler.upper(),
+                    "defaultAuxPool": p.name == "default", "preemptible": p.preemption,
+                    "schedulerType": "SCHEDULER_TYPE_" + (ctx.m.backends[p.name].NAME if p.name in getattr(ctx.m, "backends", {}) else p.scheduler).upper(),
                     "schedulerFittingPolicy": "FITTING_POLICY_" + p.policy.upper(), "slotsPerAgent": max((a.num_slots for a in p.agents.values()), default=0),
                     "location": "on-prem", "auxContainerCapacity": 100 * max(len(p.agents), 1),
                     "auxContainersRunning": sum(len(a.zero_slot_tasks) for a in p.agents.values())})

@@ -121,7 +121,8 @@ class Allocation:
         if remote:
             row = m.db.one("SELECT model_definition FROM experiments WHERE id=?", (exp.id,))
             m.agents.start(self.agent_id, self.id, self, [agents_mod.PYTHON_PLACEHOLDER, "-m", "determined_b200.exec.launch"], task_env, slot_ids,
-                           archive=row["model_definition"] if row is not None else None, workdir="model")
+                           archive=row["model_definition"] if row is not None else None, workdir="model",
+                           hpc={k: exp.config[k] for k in ("slurm", "pbs") if isinstance(exp.config.get(k), dict)})
             return
         self.run_dir = tempfile.mkdtemp(prefix=f"detb200-alloc-{self.id[:8]}-", dir=m.work_dir)
         model_dir = os.path.join(self.run_dir, "model")
@@ -598,11 +599,12 @@ class Master:
         self.backends: Dict[str, Any] = {}
         for rp in resource_pools or []:
             prov = rp.get("provider") or {}
-            if str(prov.get("type", "")).lower() == "slurm":
-                from determined_b200.master import slurm
+            kind = str(prov.get("type", "")).lower()
+            if kind in ("slurm", "pbs"):
+                from determined_b200.master import pbs, slurm
 
                 name = str(rp.get("pool_name") or rp.get("name"))
-                self.backends[name] = slurm.SlurmBackend(self, name, prov)
+                self.backends[name] = (slurm.SlurmBackend if kind == "slurm" else pbs.PBSBackend)(self, name, prov)
         self._restore()
 
     config: Any = None                         # master.config.MasterConfig when started from a configuration (``apply_config``)

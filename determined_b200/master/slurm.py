@@ -34,9 +34,9 @@ logger = logging.getLogger("determined.master.slurm")
 
 
 class _Job:
-    def __init__(self, cid: str, job_id: str, run_dir: str) -> None:
+    def __init__(self, cid: str, job_id: str, run_dir: str, out_file: str = "slurm.out") -> None:
         self.cid, self.job_id, self.run_dir = cid, job_id, run_dir
-        self.out_path = os.path.join(run_dir, "slurm.out")
+        self.out_path = os.path.join(run_dir, out_file)
         self.exit_path = os.path.join(run_dir, "exit_code")
         self.offset = 0
         self.cancelled = False
@@ -46,34 +46,57 @@ class _Job:
 class SlurmBackend:
     def __init__(self, master: Any, pool_name: str, cfg: Dict[str, Any]) -> None:
         self.master, self.pool_name, self.cfg = master, pool_name, dict(cfg)
-        self.id = str(cfg.get("agent_id") or f"slurm-{pool_name}")
+        self.id = str(cfg.get("agent_id") or f"{self.NAME.lower()}-{pool_name}")
         self.slots = int(cfg.get("slots", 8))
         self.poll_s = float(cfg.get("poll_seconds", 2.0))
-        self.work_dir = str(cfg.get("work_dir") or os.path.join(master.work_dir, f"slurm-{pool_name}"))
+        self.work_dir = str(cfg.get("work_dir") or os.path.join(master.work_dir, f"{self.NAME.lower()}-{pool_name}"))
         os.makedirs(self.work_dir, exist_ok=True)
         self.jobs: Dict[str, _Job] = {}
         self._stop = threading.Event()
-        info = {"id": self.id, "resourcePool": pool_name, "version": "slurm", "addresses": ["slurm"],
-                "slots": [{"type": "DEVICE_TYPE_CUDA", "brand": f"slurm:{cfg.get('partition', 'default')}", "uuid": f"{self.id}-{i}"} for i in range(self.slots)]}
+        kind = self.NAME.lower()
+        info = {"id": self.id, "resourcePool": pool_name, "version": kind, "addresses": [kind],
+                "slots": [{"type": "DEVICE_TYPE_CUDA", "brand": f"{kind}:{cfg.get('partition') or cfg.get('queue') or 'default'}", "uuid": f"{self.id}-{i}"}
+                          for i in range(self.slots)]}
         master.agents.register(info)
         self.agent = master.agents.get(self.id)
-        self._thread = threading.Thread(target=self._run, daemon=True, name=f"slurm-{pool_name}")
+        self._thread = threading.Thread(target=self._run, daemon=True, name=f"{kind}-{pool_name}")
         self._thread.start()
 
     # -- Slurm command line ----------------------------------------------------------------------------
     def _cmd(self, name: str) -> str:
         return str(self.cfg.get(name) or name)
 
-    def script(self, action: Dict[str, Any], run_dir: str) -> str:
-        n = len(action.get("slot_ids") or [])
-        lines = ["#!/bin/bash", f"#SBATCH --job-name=det-{action['container_id'][:24]}", f"#SBATCH --output={os.path.join(run_dir, 'slurm.out')}",
+    NAME = "Slurm"
+    OUT_FILE = "slurm.out"
+    DONE_STATES = ("COMPLETED", "FAILED", "CANCELLED", "TIMEOUT", "NODE_FAIL", "OUT_OF_MEMORY")
+
+    def directives(self, action: Dict[str, Any], run_dir: str, n: int) -> List[str]:
+        """The ``#SBATCH`` header of a job that needs ``n`` slots."""
+        lines = [f"#SBATCH --job-name=det-{action['container_id'][:24]}", f"#SBATCH --output={os.path.join(run_dir, self.OUT_FILE)}",
                  "#SBATCH --open-mode=append", "#SBATCH --nodes=1"]
         if self.cfg.get("partition"):
             lines.append(f"#SBATCH --partition={self.cfg['partition']}")
         if n and self.cfg.get("gres", "gpu:{slots}"):
             lines.append("#SBATCH --gres=" + str(self.cfg.get("gres", "gpu:{slots}")).format(slots=n))
-        for a in self.cfg.get("sbatch_args") or []:
+        mine = (action.get("hpc") or {}).get("slurm") or {}          # the experiment's own ``slurm:`` section
+        if mine.get("gpu_type") and n:
+            lines = [l for l in lines if not l.startswith("#SBATCH --gres=")] + [f"#SBATCH --gres=gpu:{mine['gpu_type']}:{n}"]
+        for a in list(self.cfg.get("sbatch_args") or []) + list(mine.get("sbatch_args") or []):
             lines.append(f"#SBATCH {a}")
+        return lines
+
+    def submit(self, path: str) -> str:
+        r = subprocess.run([self._cmd("sbatch"), "--parsable", path], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
+        if r.returncode != 0:
+            raise RuntimeError(f"sbatch failed ({r.returncode}): {r.stderr.strip() or r.stdout.strip()}")
+        return r.stdout.strip().split(";")[0]
+
+    def cancel(self, job_id: str) -> None:
+        subprocess.run([self._cmd("scancel"), job_id], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=60)
+
+    def script(self, action: Dict[str, Any], run_dir: str) -> str:
+        n = len(action.get("slot_ids") or [])
+        lines = ["#!/bin/bash"] + self.directives(action, run_dir, n)
         env = {str(k): str(v) for k, v in (action.get("env") or {}).items()}
         model_dir, info_dir = os.path.join(run_dir, "model"), os.path.join(run_dir, "info")
         env.update({"DET_AGENT_ID": self.id, "DET_RUN_DIR": run_dir, "DET_INFO_DIR": info_dir, "DET_MODEL_DIR": model_dir,
@@ -101,12 +124,9 @@ class SlurmBackend:
             path = os.path.join(run_dir, "job.sh")
             with open(path, "w") as f:
                 f.write(self.script(action, run_dir))
-            r = subprocess.run([self._cmd("sbatch"), "--parsable", path], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
-            if r.returncode != 0:
-                raise RuntimeError(f"sbatch failed ({r.returncode}): {r.stderr.strip() or r.stdout.strip()}")
-            job_id = r.stdout.strip().split(";")[0]
-            self.jobs[cid] = _Job(cid, job_id, run_dir)
-            self._emit({"type": "log", "container_id": cid, "lines": [f"submitted Slurm job {job_id}"]})
+            job_id = self.submit(path)
+            self.jobs[cid] = _Job(cid, job_id, run_dir, self.OUT_FILE)
+            self._emit({"type": "log", "container_id": cid, "lines": [f"submitted {self.NAME} job {job_id}"]})
         except Exception as e:  # noqa: BLE001
             logger.exception("could not submit %s", cid)
             self._emit({"type": "start_failed", "container_id": cid, "error": str(e)})
@@ -115,7 +135,7 @@ class SlurmBackend:
         j = self.jobs.get(cid)
         if j is not None:
             j.cancelled = True
-            subprocess.run([self._cmd("scancel"), j.job_id], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=60)
+            self.cancel(j.job_id)
 
     def _in_queue(self, job_ids: List[str]) -> Dict[str, str]:
         """job id -> Slurm state for the jobs Slurm still knows (PENDING, RUNNING, COMPLETING...)."""
@@ -151,7 +171,7 @@ class SlurmBackend:
         states = self._in_queue([j.job_id for j in self.jobs.values()])
         for cid, j in list(self.jobs.items()):
             self._ship_output(j)
-            if j.job_id in states and states[j.job_id] not in ("COMPLETED", "FAILED", "CANCELLED", "TIMEOUT", "NODE_FAIL", "OUT_OF_MEMORY"):
+            if j.job_id in states and states[j.job_id] not in self.DONE_STATES:
                 j.gone_since = None
                 continue
             # out of the queue: give the shared filesystem a moment to show the exit file, then settle
@@ -164,7 +184,7 @@ class SlurmBackend:
                     continue
             self._ship_output(j)
             if code is None:
-                self._emit({"type": "log", "container_id": cid, "lines": [f"Slurm job {j.job_id} left the queue as {states.get(j.job_id, 'gone')} without an exit code"]})
+                self._emit({"type": "log", "container_id": cid, "lines": [f"{self.NAME} job {j.job_id} left the queue as {states.get(j.job_id, 'gone')} without an exit code"]})
                 code = 143 if j.cancelled else 1
             del self.jobs[cid]
             self._emit({"type": "exit", "container_id": cid, "exit_code": code})

@@ -55,7 +55,7 @@ def test_trial_runs_as_a_batch_job(cluster):
     m, sess, tmp = cluster
     pools = {p["name"]: p for p in sess.get("/api/v1/resource-pools").json()["resourcePools"]}
     assert pools["hpc"]["slotsAvailable"] == 4
-    eid = create(sess, dict(BASE, resources={"slots_per_trial": 2, "resource_pool": "hpc"}))
+    eid = create(sess, dict(BASE, resources={"slots_per_trial": 2, "resource_pool": "hpc"}, slurm={"sbatch_args": ["--exclusive"]}))
     assert wait_state(sess, eid, {"STATE_COMPLETED", "STATE_ERROR"}) == "STATE_COMPLETED", dump_logs(sess, eid)
     t = sess.get(f"/api/v1/experiments/{eid}/trials").json()["trials"][0]
     assert t["totalBatchesProcessed"] == 24
@@ -63,6 +63,7 @@ def test_trial_runs_as_a_batch_job(cluster):
     assert "submitted Slurm job" in logs and len(logs.splitlines()) > 3, "the job's own output must come back through slurm.out"
     job_sh = next((tmp / "work" / "slurm-hpc").glob("job-*/job.sh")).read_text()
     assert "#SBATCH --partition=gpu" in job_sh and "#SBATCH --gres=gpu:2" in job_sh and "#SBATCH --time=00:10:00" in job_sh
+    assert "#SBATCH --exclusive" in job_sh, "the experiment's own slurm section adds directives"
     assert "export DET_SLOT_IDS='[0, 1]'" in job_sh and "determined_b200.exec.launch" in job_sh
     assert "--parsable" in (tmp / "bin" / "sbatch.calls").read_text()
 
