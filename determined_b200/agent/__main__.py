@@ -19,11 +19,16 @@ def main(argv=None) -> int:
     ap.add_argument("--agent-token", default=None, help="shared secret if the master sets DET_AGENT_TOKEN")
     ap.add_argument("--master-cert-file", default=None, help="PEM certificate of an https master to trust, or 'noverify' (default: $DET_MASTER_CERT_FILE)")
     ap.add_argument("--master-cert-name", default=None, help="host name in the master's certificate when it differs from the URL's")
+    ap.add_argument("--container-runtime", choices=["process", "docker", "podman", "apptainer", "singularity"],
+                    default=os.environ.get("DET_CONTAINER_RUNTIME", "process"), help="run tasks on the host (process) or inside containers of this runtime")
+    ap.add_argument("--default-image", default=os.environ.get("DET_DEFAULT_IMAGE", ""), help="image of tasks that name none (environment.image)")
+    ap.add_argument("--container-exe", default=None, help="path of the runtime's command-line client when it is not on PATH")
+    ap.add_argument("--container-arg", action="append", default=[], help="extra argument for every container run (repeatable)")
     ap.add_argument("--log-level", default="INFO")
     a = ap.parse_args(argv)
     logging.basicConfig(level=getattr(logging, a.log_level.upper(), logging.INFO), format="%(asctime)s %(levelname)s %(name)s: %(message)s")
     agent = Agent(a.master_url, a.agent_id, a.slots, a.slot_type, a.resource_pool, a.work_dir, a.agent_token,
-                  a.master_cert_file, a.master_cert_name)
+                  a.master_cert_file, a.master_cert_name, a.container_runtime, a.default_image, a.container_exe, a.container_arg)
 
     def on_signal(signum, frame):  # noqa: ARG001
         # SIGTERM / SIGINT: leave tasks running (they re-attach when the agent comes back), like `systemctl restart`

@@ -34,6 +34,18 @@ DISCONNECT_AFTER_S = 30.0
 PYTHON_PLACEHOLDER = "{python}"        # argv[0] the agent replaces by its own interpreter
 
 
+def container_spec(config: Dict[str, Any]) -> Dict[str, Any]:
+    """The container-facing part of an experiment / command config (reference ``master/pkg/tasks/task.go`` ToDockerSpec:
+    image, mounts, shm size, devices, capabilities, pull policy and registry credentials)."""
+    env = config.get("environment") or {}
+    res = config.get("resources") or {}
+    out = {"image": env.get("image"), "bind_mounts": list(config.get("bind_mounts") or []), "shm_size": res.get("shm_size"),
+           "devices": list(res.get("devices") or []), "add_capabilities": list(env.get("add_capabilities") or []),
+           "drop_capabilities": list(env.get("drop_capabilities") or []), "force_pull_image": bool(env.get("force_pull_image")),
+           "registry_auth": env.get("registry_auth")}
+    return {k: v for k, v in out.items() if v not in (None, [], False)}
+
+
 class RemoteAgent:
     def __init__(self, agent_id: str, info: Dict[str, Any]) -> None:
         self.id = agent_id
@@ -155,17 +167,19 @@ class AgentRegistry:
 
     # -- master -> agent -----------------------------------------------------------------------------
     def start(self, agent_id: str, container_id: str, sink: Any, argv: List[str], env: Dict[str, str], slot_ids: List[int],
-              archive: Optional[bytes] = None, workdir: str = "", hpc: Optional[Dict[str, Any]] = None) -> None:
+              archive: Optional[bytes] = None, workdir: str = "", hpc: Optional[Dict[str, Any]] = None,
+              container: Optional[Dict[str, Any]] = None) -> None:
         """Queue a ``start`` for the agent.  ``archive`` (a tarball) is unpacked into ``<run dir>/model`` on the agent, the
         process starts in ``<run dir>/<workdir>``; ``env`` holds only what the master decides (``DET_*``, user variables):
         the agent layers it over its own environment and adds the per-host paths.  ``hpc`` carries the experiment's ``slurm`` /
-        ``pbs`` sections for pools backed by a workload manager."""
+        ``pbs`` sections for pools backed by a workload manager, ``container`` what an agent with a container runtime needs
+        (:func:`container_spec`)."""
         ag = self.agents.get(agent_id)
         if ag is None or not ag.connected:
             raise RuntimeError(f"agent {agent_id} is not connected")
         ag.containers[container_id] = sink
         ag.push({"type": "start", "container_id": container_id, "argv": argv, "env": env, "slot_ids": slot_ids, "workdir": workdir,
-                 "archive": base64.b64encode(archive).decode() if archive else None, "hpc": hpc or {}})
+                 "archive": base64.b64encode(archive).decode() if archive else None, "hpc": hpc or {}, "container": container or {}})
 
     def kill(self, agent_id: str, container_id: str, sig: str = "TERM") -> None:
         ag = self.agents.get(agent_id)

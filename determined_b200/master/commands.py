@@ -143,7 +143,8 @@ class CommandTask:
                 from determined_b200.common import context as det_context
 
                 self.context = det_context.v1_context_to_tarball(self.files)
-            m.agents.start(self.agent_id, self.id, self, argv, task_env, slot_ids, archive=self.context, workdir="model")
+            m.agents.start(self.agent_id, self.id, self, argv, task_env, slot_ids, archive=self.context, workdir="model",
+                           container=agents_mod.container_spec(self.config))
             return
         self.run_dir = tempfile.mkdtemp(prefix=f"detb200-{self.kind.lower()}-{self.id[:8]}-", dir=m.work_dir)
         if self.files:

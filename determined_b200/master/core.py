@@ -122,7 +122,8 @@ class Allocation:
             row = m.db.one("SELECT model_definition FROM experiments WHERE id=?", (exp.id,))
             m.agents.start(self.agent_id, self.id, self, [agents_mod.PYTHON_PLACEHOLDER, "-m", "determined_b200.exec.launch"], task_env, slot_ids,
                            archive=row["model_definition"] if row is not None else None, workdir="model",
-                           hpc={k: exp.config[k] for k in ("slurm", "pbs") if isinstance(exp.config.get(k), dict)})
+                           hpc={k: exp.config[k] for k in ("slurm", "pbs") if isinstance(exp.config.get(k), dict)},
+                           container=agents_mod.container_spec(exp.config))
             return
         self.run_dir = tempfile.mkdtemp(prefix=f"detb200-alloc-{self.id[:8]}-", dir=m.work_dir)
         model_dir = os.path.join(self.run_dir, "model")

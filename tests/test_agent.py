@@ -86,7 +86,8 @@ def test_kill_goes_through_the_agent(cluster):
 
 def test_command_runs_on_remote_agent(cluster):
     m, sess, tmp, agent = cluster
-    agent()
+    a, _ = agent()
+    _wait(lambda: a.registered, 30, "agent registration")
     r = sess.post("/api/v1/commands", json={"config": {"entrypoint": ["/bin/sh", "-c", "echo agent=$DET_AGENT_ID; echo done"], "resources": {"slots": 0}}}).json()
     cid = r["command"]["id"]
     _wait(lambda: sess.get(f"/api/v1/commands/{cid}").json()["command"]["state"] == "STATE_TERMINATED", 30, "command exit")
