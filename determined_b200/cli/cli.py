@@ -23,7 +23,14 @@ from determined_b200.common import api, context as det_context
 from determined_b200.experimental import client as sdk
 
 
+VIEW: Dict[str, Any] = {}      # --sort-by / --order-by / --limit / --offset of the running command (cli/flags.py), applied to what it prints
+
+
 def _table(rows: List[Sequence[Any]], headers: Sequence[str], as_json: bool = False, as_csv: bool = False) -> None:
+    if VIEW:
+        from determined_b200.cli import flags
+
+        rows = flags.apply_view(rows, headers, VIEW)
     if as_json:
         print(json.dumps([dict(zip(headers, r)) for r in rows], indent=2, default=str))
         return
@@ -1346,6 +1353,9 @@ def make_parser() -> argparse.ArgumentParser:
     from determined_b200.cli import more
 
     more.extend(p)
+    from determined_b200.cli import flags
+
+    flags.extend(p)
     return p
 
 
@@ -1361,6 +1371,10 @@ def main(argv: Optional[List[str]] = None) -> int:
     from determined_b200.common.api import certs
 
     _setup_cert(args)
+    from determined_b200.cli import flags
+
+    VIEW.clear()
+    VIEW.update(flags.view_of(args))
     try:
         try:
             return int(fn(args) or 0)

@@ -10,7 +10,7 @@ import hashlib
 import json
 import os
 import pathlib
-from typing import Any, Dict, Optional
+from typing import Any, Dict, List, Optional
 
 from determined_b200.common.api import _session, errors
 
@@ -64,6 +64,9 @@ class TokenStore:
 
     def get_token(self, user: str) -> Optional[str]:
         return self._m()["tokens"].get(user)
+
+    def get_all_users(self) -> List[str]:
+        return sorted(self._m()["tokens"])
 
     def set_token(self, user: str, token: str) -> None:
         self._m()["tokens"][user] = token

@@ -136,9 +136,12 @@ def ckpt_json(m: core.Master, row: Any) -> Dict[str, Any]:
                          "searcherMetric": vm.get(metric_name) if metric_name else None}}
 
 
+REMOTE_USER_MARK = "!remote:"           # password_hash of a user who signs in through an identity provider only: no hash looks like it
+
+
 def user_json(row: Any) -> Dict[str, Any]:
     return {"id": row["id"], "username": row["username"], "admin": bool(row["admin"]), "active": bool(row["active"]),
-            "displayName": row["display_name"], "modifiedAt": _ts(row["modified_at"])}
+            "displayName": row["display_name"], "modifiedAt": _ts(row["modified_at"]), "remote": str(row["password_hash"] or "").startswith(REMOTE_USER_MARK)}
 
 
 def page(items: List[Any], ctx: Ctx) -> Tuple[List[Any], Dict[str, Any]]:
@@ -160,6 +163,8 @@ def login(ctx: Ctx) -> Any:
     pw = b.get("password") or ""
     if not b.get("isHashed", False) and pw:
         pw = auth.salt_and_hash(pw)
+    if row is not None and str(row["password_hash"] or "").startswith(REMOTE_USER_MARK):
+        raise HTTPError(401, "this user signs in through the identity provider, not with a password")
     if row is None or not row["active"] or (row["password_hash"] or "") != (pw or auth.salt_and_hash("")) and (row["password_hash"] or "") != pw:
         raise HTTPError(401, "invalid credentials")
     tok = secrets.token_hex(24)
@@ -220,6 +225,8 @@ def create_user(ctx: Ctx) -> Any:
     pw = b.get("password") or ""
     if not b.get("isHashed", False) and pw:
         pw = auth.salt_and_hash(pw)
+    if u.get("remote"):
+        pw = REMOTE_USER_MARK + secrets.token_hex(16)
     try:
         uid = ctx.m.db.exec("INSERT INTO users(username,password_hash,admin,active,display_name,modified_at) VALUES(?,?,?,?,?,?)",
                             (u.get("username"), pw or auth.salt_and_hash(""), int(bool(u.get("admin"))), int(u.get("active", True)), u.get("displayName"), time.time()))
@@ -1433,6 +1440,22 @@ def update_job_queue(ctx: Ctx) -> Any:
                     p.set_priority(jid, int(u["priority"]))
                 if u.get("weight") is not None:
                     p.set_weight(jid, float(u["weight"]))
+            if u.get("resourcePool"):
+                # queued requests of the job change queues now; what is running stays where it is and asks the new pool next time
+                dst = ctx.m.pools.get(str(u["resourcePool"]))
+                if dst is None:
+                    raise HTTPError(404, f"resource pool {u['resourcePool']} not found")
+                for p in ctx.m.pools.values():
+                    if p is dst:
+                        continue
+                    for aid, req in list(p.pending.items()):
+                        if req.job_id == jid:
+                            del p.pending[aid]
+                            dst.allocate(req)
+                for exp in ctx.m.experiments.values():
+                    if exp.job_id == jid:
+                        exp.config.setdefault("resources", {})["resource_pool"] = dst.name
+                        ctx.m.db.exec("UPDATE experiments SET config=? WHERE id=?", (dbmod.J(exp.config), exp.id))
             ahead, behind = u.get("aheadOf") or (u.get("queuePosition") or {}).get("aheadOf"), u.get("behindOf") or (u.get("queuePosition") or {}).get("behindOf")
             if ahead or behind:
                 moved = False
@@ -1481,7 +1504,13 @@ def put_template(ctx: Ctx, name: str) -> Any:
     if isinstance(cfg, str):
         cfg = expconf.parse(cfg)
     ctx.m.db.exec("INSERT INTO templates(name,config) VALUES(?,?) ON CONFLICT(name) DO UPDATE SET config=excluded.config", (name, dbmod.J(cfg)))
-    return {"template": {"name": name, "config": cfg}}
+    wid = b.get("workspaceId") or (b.get("template") or {}).get("workspaceId")
+    if wid:
+        if ctx.m.db.one("SELECT id FROM workspaces WHERE id=?", (int(wid),)) is None:
+            raise HTTPError(404, f"workspace {wid} not found")
+        ctx.m.db.exec("UPDATE templates SET workspace_id=? WHERE name=?", (int(wid), name))
+    r = ctx.m.db.one("SELECT * FROM templates WHERE name=?", (name,))
+    return {"template": {"name": name, "config": cfg, "workspaceId": r["workspace_id"]}}
 
 
 @route("DELETE", "/api/v1/templates/{name}")

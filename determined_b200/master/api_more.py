@@ -613,6 +613,35 @@ def _signal_task(ctx: Ctx, task_id: str, sig: int, state_word: str) -> Any:
     return {}
 
 
+@route("POST", "/api/v1/tasks/{task_id}/kill")
+def kill_generic_task(ctx: Ctx, task_id: str) -> Any:
+    """Kill a task and every task forked from it (reference ``KillGenericTask``); ``killFromRoot`` starts at the first
+    ancestor instead, taking the whole tree down."""
+    tasks = ctx.m.commands.tasks
+    _any_task(ctx, task_id)
+    parent_of = {tid: (getattr(t, "parent_id", None) or get_attr(ctx.m, "task", tid, "parentId")) for tid, t in tasks.items()}
+    root = task_id
+    if (ctx.body or {}).get("killFromRoot"):
+        seen = {root}
+        while parent_of.get(root) in tasks and parent_of[root] not in seen:
+            root = parent_of[root]
+            seen.add(root)
+    tree, frontier = [root], [root]
+    while frontier:
+        cur = frontier.pop()
+        for tid, par in parent_of.items():
+            if par == cur and tid not in tree:
+                tree.append(tid)
+                frontier.append(tid)
+    killed = []
+    for tid in tree:
+        t = tasks[tid]
+        if t.state not in ("TERMINATED",):
+            t.kill()
+            killed.append(tid)
+    return {"killed": killed}
+
+
 route("POST", "/api/v1/tasks/{task_id}/pause")(lambda ctx, task_id: _signal_task(ctx, task_id, signal.SIGSTOP, "paused"))
 route("POST", "/api/v1/tasks/{task_id}/unpause")(lambda ctx, task_id: _signal_task(ctx, task_id, signal.SIGCONT, "resumed"))
 
