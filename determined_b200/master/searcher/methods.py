@@ -15,8 +15,9 @@ batch and survive restarts (reference ``experiment.go:778,980-998``).  ``Validat
 *incremental*; the trial state machine accumulates it into the absolute length the harness sees.
 """
 import bisect
+import collections
 import math
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Set, Tuple
 
 from determined_b200.master import nprand
 from determined_b200.master.searcher import hparams as hp
@@ -172,216 +173,210 @@ class GridSearch(SearchMethod):
 
 
 # ------------------------------------------------------------------------------------------------
-class _Rung:
-    def __init__(self, units_needed: int) -> None:
-        self.units_needed = units_needed
-        self.metrics: List[List[Any]] = []   # sorted by metric: [metric, request_id, promoted]
-        self.outstanding = 0
+class _Board:
+    """The leaderboard of one budget level: every score reported at this budget, best (smallest) first, and which of those
+    trials have moved on to the next level.  ``in_flight`` counts trials currently training towards this level."""
 
-    def _insert(self, rid: str, metric: float, strict: bool) -> int:
-        keys = [m[0] for m in self.metrics]
-        i = bisect.bisect_right(keys, metric) if strict else bisect.bisect_left(keys, metric)
-        self.metrics.insert(i, [metric, rid, False])
-        return i
+    def __init__(self, budget: int) -> None:
+        self.budget = budget
+        self.scores: List[float] = []         # ascending
+        self.ids: List[str] = []              # parallel to scores
+        self.advanced: Set[str] = set()
+        self.in_flight = 0
 
-    def promotions(self, rid: str, metric: float, divisor: float) -> List[str]:
-        """Promotion flavour: top 1/divisor of everything seen so far in this rung gets promoted,
-        each trial at most once."""
-        old_n = int(len(self.metrics) / divisor)
-        new_n = int((len(self.metrics) + 1) / divisor)
-        i = self._insert(rid, metric, strict=True)
-        if i < new_n:
-            self.metrics[i][2] = True
-            return [rid]
-        if new_n != old_n and not self.metrics[old_n][2]:
-            self.metrics[old_n][2] = True
-            return [self.metrics[old_n][1]]
-        return []
+    def __len__(self) -> int:
+        return len(self.ids)
 
-    def continue_training(self, rid: str, metric: float, divisor: float) -> bool:
-        """Stopping flavour: a trial continues iff it is in the top 1/divisor when it reports."""
-        n = max(int((len(self.metrics) + 1) / divisor), 1)
-        i = self._insert(rid, metric, strict=False)
-        ok = i < n
-        self.metrics[i][2] = ok
-        return ok
+    def add(self, rid: str, score: float, ahead_of_ties: bool) -> int:
+        """File a score; returns its rank.  A newcomer that ties goes behind the incumbents unless ``ahead_of_ties``."""
+        rank = (bisect.bisect_left if ahead_of_ties else bisect.bisect_right)(self.scores, score)
+        self.scores.insert(rank, score)
+        self.ids.insert(rank, rid)
+        return rank
 
-    def drop(self, rid: str) -> None:
-        self.metrics = [m for m in self.metrics if m[1] != rid]
+    def owed(self, divisor: float) -> List[str]:
+        """Trials inside the top ``1/divisor`` of this board that have not moved on yet, best first."""
+        return [rid for rid in self.ids[:int(len(self.ids) / divisor)] if rid not in self.advanced]
+
+    def forget(self, rid: str) -> None:
+        for i in reversed([i for i, x in enumerate(self.ids) if x == rid]):
+            del self.ids[i], self.scores[i]
+        self.advanced.discard(rid)
 
     def to_json(self) -> Dict[str, Any]:
-        return {"units_needed": self.units_needed, "metrics": [list(m) for m in self.metrics], "outstanding": self.outstanding}
+        return {"budget": self.budget, "scores": list(self.scores), "ids": list(self.ids), "advanced": sorted(self.advanced), "in_flight": self.in_flight}
 
     @classmethod
-    def from_json(cls, d: Dict[str, Any]) -> "_Rung":
-        r = cls(int(d["units_needed"]))
-        r.metrics = [list(m) for m in d["metrics"]]
-        r.outstanding = int(d["outstanding"])
-        return r
+    def from_json(cls, d: Dict[str, Any]) -> "_Board":
+        b = cls(int(d["budget"]))
+        b.scores, b.ids, b.advanced, b.in_flight = [float(x) for x in d["scores"]], [str(x) for x in d["ids"]], set(d["advanced"]), int(d["in_flight"])
+        return b
 
 
 class ASHASearch(SearchMethod):
-    """Asynchronous successive halving.  ``num_rungs`` rungs; rung ``i`` trains to
-    ``sum_{j<=i} max(max_length / divisor^(num_rungs-j-1), 1)`` units.  ``stop_once=False``:
-    promotion ASHA (trials pause at a rung and may be resumed from their checkpoint later);
-    ``stop_once=True``: stopping ASHA (a trial either continues immediately or is closed)."""
+    """Asynchronous successive halving (Li et al., "A System for Massively Parallel Hyperparameter Tuning") over a ladder of
+    ``num_rungs`` budget levels; level ``i`` is reached after ``sum_{j<=i} max(max_length / divisor^(num_rungs-1-j), 1)`` units.
+
+    The rule is the paper's, stated on leaderboards: whenever a score is filed at a level, every trial inside the top
+    ``1/divisor`` of that level's board that has not moved on yet is *owed* a promotion and gets it now (promotion flavour:
+    the others wait, parked on their checkpoint).  ``stop_once`` is the stopping flavour: the reporting trial itself
+    continues iff it ranks inside the top ``1/divisor`` at that moment, otherwise it is closed for good.  A trial that died
+    is scored with the worst value wherever it would have reported next, so the ladder never waits for it.  Reports are
+    settled from a work list, so a dead trial that is owed a promotion is carried upward in the same pass.
+
+    Behaviour parity: reference ``master/pkg/searcher/asha.go`` / ``asha_stopping.go`` (same promotions, same trial counts).
+    """
 
     name = "async_halving"
 
     def __init__(self, cfg: Dict[str, Any], smaller_is_better: bool) -> None:
-        self.num_rungs = int(cfg["num_rungs"])
         self.max_length, self._unit = length_units(cfg["max_length"])
         self.max_trials = int(cfg["max_trials"])
         self.divisor = float(cfg.get("divisor", 4))
         self.max_concurrent = int(cfg.get("max_concurrent_trials", 16) or 0)
         self.stop_once = bool(cfg.get("stop_once", False))
-        self.smaller_is_better = smaller_is_better
-        self.rungs: List[_Rung] = []
-        need = 0
-        for i in range(self.num_rungs):
-            need += max(int(self.max_length / math.pow(self.divisor, self.num_rungs - i - 1)), 1)
-            self.rungs.append(_Rung(need))
-        self.trial_rungs: Dict[str, int] = {}
-        self.early_exit: Dict[str, bool] = {}
-        self.closed: Dict[str, bool] = {}
-        self.trials_completed = 0
-        self.invalid_trials = 0
-        self.pending_trials = 0
+        self.sign = 1.0 if smaller_is_better else -1.0
+        levels = int(cfg["num_rungs"])
+        self.boards: List[_Board] = []
+        budget = 0
+        for i in range(levels):
+            budget += max(int(self.max_length / math.pow(self.divisor, levels - 1 - i)), 1)
+            self.boards.append(_Board(budget))
+        self.level: Dict[str, int] = {}        # trial -> the level it is training towards / parked at
+        self.dead: Set[str] = set()            # exited early: never gets another operation
+        self.shut: Set[str] = set()            # a Close has been issued (or the trial is dead)
+        self.finished = 0                      # trials the master reported closed
+        self.rejected = 0                      # invalid hyperparameter samples, replaced by fresh ones
+        self.waiting = 0                       # ValidateAfter operations not answered yet
 
-    # -- helpers -----------------------------------------------------------------------------------
-    def _new_trial(self, ctx: Context) -> List[Op]:
+    @property
+    def num_rungs(self) -> int:
+        return len(self.boards)
+
+    # -- operations ---------------------------------------------------------------------------------
+    def _spawn(self, ctx: Context) -> List[Op]:
         c = new_create(ctx.rand, hp.sample_all(ctx.hparams, ctx.rand))
-        self.trial_rungs[c.request_id] = 0
-        self.pending_trials += 1
-        return [c, ValidateAfter(c.request_id, self.rungs[0].units_needed)]
+        self.level[c.request_id] = 0
+        self.waiting += 1
+        return [c, ValidateAfter(c.request_id, self.boards[0].budget)]
+
+    def _climb(self, rid: str, frm: int, ops: List[Op]) -> None:
+        self.level[rid] = frm + 1
+        self.boards[frm + 1].in_flight += 1
+        if rid not in self.dead:
+            ops.append(ValidateAfter(rid, max(self.boards[frm + 1].budget - self.boards[frm].budget, 1)))
+            self.waiting += 1
+
+    def _close(self, rid: str, ops: List[Op]) -> None:
+        if rid not in self.shut:
+            self.shut.add(rid)
+            ops.append(Close(rid))
 
     def initial_operations(self, ctx: Context) -> List[Op]:
         if self.max_concurrent > 0:
             n = min(self.max_concurrent, self.max_trials)
-        else:
+        else:       # unlimited: enough starters that one of them can be owed the top level
             n = max(1, min(int(math.pow(self.divisor, self.num_rungs - 1)), self.max_trials))
-        ops: List[Op] = []
-        for _ in range(n):
-            ops += self._new_trial(ctx)
-        return ops
+        return [op for _ in range(n) for op in self._spawn(ctx)]
 
     def trial_created(self, ctx: Context, request_id: str) -> List[Op]:
-        self.rungs[0].outstanding += 1
-        self.trial_rungs[request_id] = 0
+        self.boards[0].in_flight += 1
+        self.level[request_id] = 0
         return []
 
     def trial_closed(self, ctx: Context, request_id: str) -> List[Op]:
-        self.trials_completed += 1
-        self.closed[request_id] = True
+        self.finished += 1
+        self.shut.add(request_id)
         return []
 
     def validation_completed(self, ctx: Context, request_id: str, metric: Any, op: ValidateAfter) -> List[Op]:
-        self.pending_trials -= 1
+        self.waiting -= 1
         try:
-            value = float(metric)
+            score = self.sign * float(metric)
         except (TypeError, ValueError):
             raise ValueError(f"unexpected metric type for ASHA built-in search method: {metric!r}")
-        if not self.smaller_is_better:
-            value = -value
-        return self._promote(ctx, request_id, value)
-
-    def _promote(self, ctx: Context, rid: str, metric: float) -> List[Op]:
-        ri = self.trial_rungs[rid]
-        rung = self.rungs[ri]
-        rung.outstanding -= 1
-        added = False
-        ops: List[Op] = []
-        if ri == self.num_rungs - 1:
-            rung.metrics.append([metric, rid, False])
-            if not self.early_exit.get(rid):
-                ops.append(Close(rid))
-                self.closed[rid] = True
-        elif self.stop_once:
-            nxt = self.rungs[ri + 1]
-            keep = rung.continue_training(rid, metric, self.divisor)
-            if not self.early_exit.get(rid):
-                if keep:
-                    self.trial_rungs[rid] = ri + 1
-                    nxt.outstanding += 1
-                    ops.append(ValidateAfter(rid, max(nxt.units_needed - rung.units_needed, 1)))
-                    self.pending_trials += 1
-                    added = True
-                else:
-                    ops.append(Close(rid))
-                    self.closed[rid] = True
-        else:
-            nxt = self.rungs[ri + 1]
-            for pid in rung.promotions(rid, metric, self.divisor):
-                self.trial_rungs[pid] = ri + 1
-                nxt.outstanding += 1
-                if not self.early_exit.get(pid):
-                    ops.append(ValidateAfter(pid, max(nxt.units_needed - rung.units_needed, 1)))
-                    self.pending_trials += 1
-                    added = True
-                else:
-                    # behave as if the promoted-but-dead trial ran and came back with the worst metric
-                    return ops + self._promote(ctx, pid, EXITED_METRIC)
-        all_trials = len(self.trial_rungs) - self.invalid_trials
-        if not added and all_trials < self.max_trials:
-            ops += self._new_trial(ctx)
-        if not self.stop_once and len(self.rungs[0].metrics) == self.max_trials:
-            ops += self._close_out_rungs()
-        return ops
-
-    def _close_out_rungs(self) -> List[Op]:
-        """Once every trial has reported in rung 0: close the never-promoted trials of each rung
-        that has nothing outstanding (bottom-up, stopping at the first busy rung)."""
-        ops: List[Op] = []
-        for rung in self.rungs:
-            if rung.outstanding > 0:
-                break
-            for metric, rid, promoted in rung.metrics:
-                if not promoted and not self.closed.get(rid) and not self.early_exit.get(rid):
-                    ops.append(Close(rid))
-                    self.closed[rid] = True
-        return ops
+        return self._settle(ctx, request_id, score)
 
     def trial_exited_early(self, ctx: Context, request_id: str, reason: str) -> List[Op]:
-        self.pending_trials -= 1
+        self.waiting -= 1
+        self.dead.add(request_id)
+        self.shut.add(request_id)
         if reason in (ExitedReason.INVALID_HP, ExitedReason.INIT_INVALID_HP):
-            self.early_exit[request_id] = True
-            self.closed[request_id] = True
-            self.invalid_trials += 1
-            top = self.trial_rungs.get(request_id, 0)
-            self.rungs[top].outstanding -= 1
-            for i in range(top + 1):
-                self.rungs[i].drop(request_id)
-            return [Close(request_id)] + self._new_trial(ctx)    # replace the invalid sample
-        self.early_exit[request_id] = True
-        self.closed[request_id] = True
-        return self._promote(ctx, request_id, EXITED_METRIC)
+            # the sample was never a candidate: erase it from the ladder and draw a replacement
+            self.rejected += 1
+            at = self.level.get(request_id, 0)
+            self.boards[at].in_flight -= 1
+            for b in self.boards[:at + 1]:
+                b.forget(request_id)
+            return [Close(request_id)] + self._spawn(ctx)
+        return self._settle(ctx, request_id, EXITED_METRIC)
+
+    # -- the rule ------------------------------------------------------------------------------------
+    def _settle(self, ctx: Context, rid: str, score: float) -> List[Op]:
+        ops: List[Op] = []
+        before = self.waiting
+        work = collections.deque([(rid, score)])
+        top = self.num_rungs - 1
+        while work:
+            rid, score = work.popleft()
+            at = self.level[rid]
+            board = self.boards[at]
+            board.in_flight -= 1
+            if at == top:
+                board.add(rid, score, ahead_of_ties=False)
+                self._close(rid, ops)
+            elif self.stop_once:
+                rank = board.add(rid, score, ahead_of_ties=True)
+                if rank < max(int(len(board) / self.divisor), 1):
+                    board.advanced.add(rid)
+                    if rid not in self.dead:
+                        self._climb(rid, at, ops)
+                else:
+                    self._close(rid, ops)
+            else:
+                board.add(rid, score, ahead_of_ties=False)
+                for pid in board.owed(self.divisor):
+                    board.advanced.add(pid)
+                    self._climb(pid, at, ops)
+                    if pid in self.dead:
+                        work.append((pid, EXITED_METRIC))
+        if self.waiting <= before and len(self.level) - self.rejected < self.max_trials:
+            ops += self._spawn(ctx)                   # nobody moved up: the free slot goes to a new sample
+        if not self.stop_once and len(self.boards[0]) == self.max_trials:
+            self._sweep(ops)
+        return ops
+
+    def _sweep(self, ops: List[Op]) -> None:
+        """Every sample has reported at the first level: trials parked on a level that nothing can reach any more will
+        never be owed anything.  Close them level by level from the bottom, up to the first level still awaited."""
+        for board in self.boards:
+            if board.in_flight > 0:
+                return
+            for rid in board.ids:
+                if rid not in board.advanced:
+                    self._close(rid, ops)
 
     def progress(self, trial_progress: Dict[str, float], trials_closed: Dict[str, bool]) -> float:
-        seen = len(self.rungs[0].metrics)
+        seen = len(self.boards[0])
         p = seen / (1.2 * self.max_trials)          # 20 % head-room for promotions
         if seen == self.max_trials:
-            p = max(p, (self.trials_completed - self.invalid_trials) / float(self.max_trials))
+            p = max(p, (self.finished - self.rejected) / float(self.max_trials))
         return p
 
     def unit(self) -> Optional[str]:
         return self._unit
 
     def snapshot(self) -> Dict[str, Any]:
-        return {"rungs": [r.to_json() for r in self.rungs], "trial_rungs": dict(self.trial_rungs),
-                "early_exit_trials": dict(self.early_exit), "closed_trials": dict(self.closed),
-                "trials_completed": self.trials_completed, "invalid_trials": self.invalid_trials,
-                "pending_trials": self.pending_trials}
+        return {"boards": [b.to_json() for b in self.boards], "level": dict(self.level), "dead": sorted(self.dead), "shut": sorted(self.shut),
+                "finished": self.finished, "rejected": self.rejected, "waiting": self.waiting}
 
     def restore(self, state: Dict[str, Any]) -> None:
         if not state:
             return
-        self.rungs = [_Rung.from_json(r) for r in state["rungs"]]
-        self.trial_rungs = dict(state["trial_rungs"])
-        self.early_exit = dict(state["early_exit_trials"])
-        self.closed = dict(state["closed_trials"])
-        self.trials_completed = int(state["trials_completed"])
-        self.invalid_trials = int(state["invalid_trials"])
-        self.pending_trials = int(state["pending_trials"])
+        self.boards = [_Board.from_json(b) for b in state["boards"]]
+        self.level = {str(k): int(v) for k, v in state["level"].items()}
+        self.dead, self.shut = set(state["dead"]), set(state["shut"])
+        self.finished, self.rejected, self.waiting = int(state["finished"]), int(state["rejected"]), int(state["waiting"])
 
 
 # ------------------------------------------------------------------------------------------------
