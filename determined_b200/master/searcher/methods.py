@@ -373,6 +373,12 @@ class ASHASearch(SearchMethod):
     def restore(self, state: Dict[str, Any]) -> None:
         if not state:
             return
+        if "rungs" in state:        # snapshots written before the leaderboard form: same facts, other names
+            state = {"boards": [{"budget": r["units_needed"], "scores": [m[0] for m in r["metrics"]], "ids": [m[1] for m in r["metrics"]],
+                                 "advanced": [m[1] for m in r["metrics"] if m[2]], "in_flight": r["outstanding"]} for r in state["rungs"]],
+                     "level": state["trial_rungs"], "dead": [k for k, v in state["early_exit_trials"].items() if v],
+                     "shut": [k for k, v in state["closed_trials"].items() if v], "finished": state["trials_completed"],
+                     "rejected": state["invalid_trials"], "waiting": state["pending_trials"]}
         self.boards = [_Board.from_json(b) for b in state["boards"]]
         self.level = {str(k): int(v) for k, v in state["level"].items()}
         self.dead, self.shut = set(state["dead"]), set(state["shut"])
