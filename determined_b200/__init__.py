@@ -19,15 +19,19 @@ LOG_FORMAT = "%(levelname)s: [%(process)s] %(name)s: %(message)s"
 
 
 def install_alias(name: str = "determined") -> None:
-    """Make ``import determined`` (and submodules) resolve to this package."""
+    """Make ``import determined`` (and submodules) resolve to this package, and ``import model_hub`` to ``model_hub`` here."""
     import importlib
     import sys
+
+    if name == "determined":
+        install_alias("model_hub")
+    real_root = "determined_b200.model_hub" if name == "model_hub" else "determined_b200"
 
     class _AliasFinder:
         def find_spec(self, fullname, path=None, target=None):  # type: ignore
             if fullname != name and not fullname.startswith(name + "."):
                 return None
-            real = "determined_b200" + fullname[len(name):]
+            real = real_root + fullname[len(name):]
             try:
                 mod = importlib.import_module(real)
             except ImportError:
@@ -49,9 +53,10 @@ def install_alias(name: str = "determined") -> None:
 
     import importlib.util
 
-    if not any(type(f).__name__ == "_AliasFinder" for f in sys.meta_path):
+    _AliasFinder.alias_of = name
+    if not any(getattr(f, "alias_of", None) == name for f in sys.meta_path):
         sys.meta_path.insert(0, _AliasFinder())
-    sys.modules.setdefault(name, sys.modules[__name__])
+    sys.modules.setdefault(name, importlib.import_module(real_root))
 
 
 def __getattr__(attr: str):  # lazy heavy submodules (torch import) – keeps `import determined_b200` light

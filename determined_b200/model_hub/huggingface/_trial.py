@@ -128,3 +128,11 @@ class BaseTransformerTrial(det_torch.PyTorchTrial):
         self.context.backward(loss)
         self.context.step_optimizer(self.optimizer, self.grad_clip_fn)
         return {"loss": loss}
+
+
+def default_load_dataset(data_config_input: Any) -> Any:
+    """See :func:`determined_b200.model_hub.huggingface._utils.default_load_dataset` (kept importable from here, where the
+    reference defines it)."""
+    from determined_b200.model_hub.huggingface import _utils
+
+    return _utils.default_load_dataset(data_config_input)

@@ -30,6 +30,28 @@ def numpify(x: Union[List, np.ndarray, torch.Tensor]) -> np.ndarray:
     raise TypeError(f"expected List, np.ndarray or torch.Tensor, got {type(x)}")
 
 
+def download_url(download_directory: str, url: str) -> str:
+    """Fetch ``url`` into ``download_directory`` (kept under the URL's file name; an existing file is reused)."""
+    import os
+    import urllib.parse
+
+    import requests
+
+    name = os.path.basename(urllib.parse.urlparse(url).path) or "download"
+    os.makedirs(download_directory, exist_ok=True)
+    path = os.path.join(download_directory, name)
+    if os.path.exists(path):
+        return path
+    tmp = path + ".part"
+    with requests.get(url, stream=True, timeout=60) as r:
+        r.raise_for_status()
+        with open(tmp, "wb") as f:
+            for chunk in r.iter_content(1 << 20):
+                f.write(chunk)
+    os.replace(tmp, path)
+    return path
+
+
 def compute_num_training_steps(experiment_config: Dict[str, Any], global_batch_size: int) -> int:
     max_length = experiment_config["searcher"]["max_length"]
     if isinstance(max_length, int):
@@ -41,7 +63,7 @@ def compute_num_training_steps(experiment_config: Dict[str, Any], global_batch_s
         if "records_per_epoch" not in experiment_config:
             raise ValueError("Missing num_training_steps hyperparameter in the experiment configuration, which is needed to configure the "
                              "learning rate scheduler when max_length is given in epochs without records_per_epoch.")
-        return int(value * experiment_config["records_per_epoch"] / global_batch_size)
+        return int(value) * (int(experiment_config["records_per_epoch"]) // global_batch_size)      # whole batches per epoch
     if unit == "records":
         return int(value / global_batch_size)
     raise ValueError(f"unknown max_length unit {unit}")

@@ -505,3 +505,57 @@ def test_install_alias_never_executes_a_module_twice(tmp_path):
     r = subprocess.run([sys.executable, "-c", code], cwd=tmp_path, env=dict(__import__("os").environ, PYTHONPATH=str(pathlib.Path(__file__).resolve().parents[1])),
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
     assert "ALIAS_OK" in r.stdout, r.stdout[-2000:]
+
+
+def test_model_hub_dataset_helpers_and_download(tmp_path):
+    """default_load_dataset from local files without the `datasets` package, column pruning against forward(), download_url
+    from a local HTTP server, and the reference's own model_hub unit tests through the `model_hub` alias."""
+    import http.server
+    import subprocess
+    import sys
+    import threading
+
+    import torch
+
+    from determined_b200.model_hub import huggingface as hf, utils as mh_utils
+
+    (tmp_path / "train.csv").write_text("text,label\n" + "".join(f"row {i},{i % 2}\n" for i in range(10)))
+    ds = hf.default_load_dataset({"train_file": str(tmp_path / "train.csv"), "validation_split_percentage": 20})
+    assert len(ds["train"]) == 8 and len(ds["validation"]) == 2 and ds["train"].column_names == ["text", "label"]
+    (tmp_path / "v.jsonl").write_text('{"text": "a", "label": 1}\n{"text": "b", "label": 0}\n')
+    (tmp_path / "t.jsonl").write_text('{"text": "c", "label": 1}\n')
+    ds = hf.default_load_dataset({"train_file": str(tmp_path / "t.jsonl"), "validation_file": str(tmp_path / "v.jsonl")})
+    assert len(ds["validation"]) == 2 and ds["validation"][1] == {"text": "b", "label": 0}
+    # the built-in column store (what loads the files when the `datasets` package is absent)
+    val = hf.ColumnDataset.from_file(str(tmp_path / "v.jsonl"))
+    assert len(val) == 2 and val[1] == {"text": "b", "label": 0} and val.select([1])[0]["text"] == "b"
+    assert hf.ColumnDataset.from_file(str(tmp_path / "train.csv"))[3] == {"text": "row 3", "label": "1"}
+    tok = val.map(lambda r: {"input_ids": [ord(c) for c in r["text"]], "labels": int(r["label"])})
+
+    class M(torch.nn.Module):
+        def forward(self, input_ids, attention_mask=None, labels=None):
+            return input_ids
+
+    tok.set_format("torch", tok.column_names)
+    hf.remove_unused_columns(M(), tok)
+    assert set(tok[0]) == {"input_ids", "labels", "label"} and torch.is_tensor(tok[0]["input_ids"]) and tok.format["type"] == "torch"
+    grouped = val.map(lambda b: {"chunk": ["".join(b["text"])]}, batched=True)
+    assert grouped.column_names == ["chunk"] and len(grouped) == 1
+
+    (tmp_path / "www").mkdir()
+    (tmp_path / "www" / "weights.bin").write_bytes(b"x" * 3000)
+    handler = lambda *a, **kw: http.server.SimpleHTTPRequestHandler(*a, directory=str(tmp_path / "www"), **kw)  # noqa: E731
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), handler)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    try:
+        p = mh_utils.download_url(str(tmp_path / "dl"), f"http://127.0.0.1:{srv.server_address[1]}/weights.bin?sig=1")
+        assert p.endswith("/dl/weights.bin") and open(p, "rb").read() == b"x" * 3000
+        srv.shutdown()
+        assert mh_utils.download_url(str(tmp_path / "dl"), f"http://127.0.0.1:{srv.server_address[1]}/weights.bin") == p, "a file already there is reused"
+    finally:
+        srv.server_close()
+
+    runner = pathlib.Path(__file__).parent / "fixtures" / "run_reference_tests.py"
+    r = subprocess.run([sys.executable, str(runner), "/root/reference/model_hub", "tests/test_hf.py", "tests/test_utils.py", "-k", "not download_url"],
+                       cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "4 passed" in r.stdout, r.stdout[-2000:]
