@@ -101,12 +101,74 @@ def _out(obj: Any, as_json: bool = False, as_yaml: bool = False) -> None:
 # --------------------------------------------------------------------------------------------------------------------- auth
 def auth_login(args: argparse.Namespace) -> int:
     if getattr(args, "provider", None):
-        raise SystemExit(f"this master has no single sign-on provider {args.provider!r} (see `det auth list-providers`)")
+        return sso_login(args)
     c = _cli()
     user = args.username or args.user or input("Username: ")
     sess = api.authentication.login_with_cache(c._master_of(args), user, None)
     store = api.authentication.TokenStore(c._master_of(args))
     store.set_token(user, sess.token or "")
+    store.set_active(user)
+    print(f"Logged in as {user}")
+    return 0
+
+
+def sso_login(args: argparse.Namespace, open_url: Optional[Callable[[str], Any]] = None) -> int:
+    """Sign in through the master's identity provider: a listener on this machine's loopback is the relay target; the
+    browser ends up there with the session token (reference ``cli/sso.py``).  ``--headless`` prints the URL and reads the
+    address the browser ended on (or the bare token) from stdin."""
+    import http.server
+    import threading
+    import urllib.parse
+
+    c = _cli()
+    master = c._master_of(args).rstrip("/")
+    provs = api.UnauthSession(master).get("/api/v1/master").json().get("ssoProviders") or []
+    match = [p for p in provs if p.get("name", "").lower() == args.provider.lower()]
+    if not match:
+        raise SystemExit(f"this master has no single sign-on provider {args.provider!r} (see `det auth list-providers`)")
+    got: Dict[str, str] = {}
+
+    class H(http.server.BaseHTTPRequestHandler):
+        def do_GET(self) -> None:  # noqa: N802
+            q = urllib.parse.parse_qs(urllib.parse.urlparse(self.path).query)
+            if q.get("jwt"):
+                got["token"], got["user"] = q["jwt"][0], (q.get("user") or [""])[0]
+            body = b"Signed in; you can close this window." if got else b"No token in this request."
+            self.send_response(200)
+            self.send_header("Content-Length", str(len(body)))
+            self.end_headers()
+            self.wfile.write(body)
+
+        def log_message(self, *a: Any) -> None:
+            pass
+
+    if getattr(args, "headless", False):
+        url = f"{master}{match[0]['ssoUrl']}?" + urllib.parse.urlencode({"relayState": "http://127.0.0.1:1/"})
+        print(f"Open this address in a browser, sign in, then paste the address it ends on (or its jwt value):\n  {url}")
+        pasted = input("> ").strip()
+        q = urllib.parse.parse_qs(urllib.parse.urlparse(pasted).query)
+        got["token"] = (q.get("jwt") or [pasted])[0]
+        got["user"] = (q.get("user") or [""])[0]
+    else:
+        srv = http.server.HTTPServer(("127.0.0.1", 0), H)
+        url = f"{master}{match[0]['ssoUrl']}?" + urllib.parse.urlencode({"relayState": f"http://127.0.0.1:{srv.server_address[1]}/"})
+        th = threading.Thread(target=srv.serve_forever, daemon=True)
+        th.start()
+        try:
+            print(f"Waiting for the sign-in to finish in the browser:\n  {url}")
+            (open_url or (lambda u: webbrowser.open(u) if os.environ.get("DISPLAY") else None))(url)
+            t0 = time.time()
+            while not got and time.time() - t0 < float(getattr(args, "timeout", None) or 300):
+                time.sleep(0.1)
+        finally:
+            srv.shutdown()
+            srv.server_close()
+    if not got.get("token"):
+        raise SystemExit("the sign-in did not finish")
+    sess = api.Session(master, got.get("user") or "", got["token"])
+    user = sess.get("/api/v1/me").json()["user"]["username"]
+    store = api.authentication.TokenStore(master)
+    store.set_token(user, got["token"])
     store.set_active(user)
     print(f"Logged in as {user}")
     return 0

@@ -40,6 +40,14 @@ class HTTPError(Exception):
         self.status, self.message = status, message
 
 
+class Redirect(Exception):
+    """A handler answers with ``302 Location: <to>``."""
+
+    def __init__(self, to: str) -> None:
+        super().__init__(to)
+        self.to = to
+
+
 ROUTES: List[Tuple[str, "re.Pattern[str]", Callable, bool]] = []
 # conformance tests set this to see every (method, route pattern, request body, handler result) the server answers with 200
 RECORDER: Optional[Callable[[str, str, Any, Any], None]] = None
@@ -186,8 +194,11 @@ def me(ctx: Ctx) -> Any:
 @route("GET", "/api/v1/master", auth_required=False)
 @route("GET", "/info", auth_required=False)
 def master_info(ctx: Ctx) -> Any:
+    from determined_b200.master import sso
+
+    tel = getattr(ctx.m, "telemetry", None)
     return {"version": __version__, "masterId": ctx.m.cluster_id, "clusterId": ctx.m.cluster_id, "clusterName": ctx.m.cluster_name,
-            "telemetryEnabled": False, "ssoProviders": [], "externalLoginUri": "", "rbacEnabled": False, "branding": "determined_b200",
+            "telemetryEnabled": bool(tel and tel.enabled), "ssoProviders": sso.providers(ctx.m), "externalLoginUri": "", "rbacEnabled": False, "branding": "determined_b200",
             "strictJobQueueControl": False, "userManagementEnabled": True, "product": "PRODUCT_COMMUNITY"}
 
 
@@ -2118,12 +2129,10 @@ class Handler(BaseHTTPRequestHandler):
                     return
                 _ws_stream(self, user)
                 return
-        for meth, rx, fn, need_auth in ROUTES:
-            if meth != method:
-                continue
-            mt = rx.match(path)
-            if mt is None:
-                continue
+        # the most literal pattern that matches wins (/users/setting before /users/{uid}), whatever the registration order
+        hits = [(rx.groups, i, rx, fn, need_auth, mt) for i, (meth, rx, fn, need_auth) in enumerate(ROUTES)
+                if meth == method for mt in (rx.match(path),) if mt is not None]
+        for _, _, rx, fn, need_auth, mt in sorted(hits, key=lambda h: h[:2])[:1]:
             user = self._user()
             if need_auth and user is None:
                 self._send(401, {"error": {"code": 16, "message": "unauthenticated"}, "message": "unauthenticated"})
@@ -2138,6 +2147,11 @@ class Handler(BaseHTTPRequestHandler):
                     self._send(200, out[1], out[0])
                 else:
                     self._send(200, out)
+            except Redirect as r:
+                self.send_response(302)
+                self.send_header("Location", r.to)
+                self.send_header("Content-Length", "0")
+                self.end_headers()
             except HTTPError as e:
                 self._send(e.status, {"error": {"code": e.status, "message": e.message}, "message": e.message})
             except core.NotFound as e:
@@ -2309,3 +2323,5 @@ class APIServer:
 
 
 from determined_b200.master import api_more  # noqa: E402,F401  (registers its routes)
+from determined_b200.master import api_rest  # noqa: E402,F401  (the rest of the REST surface)
+from determined_b200.master import sso  # noqa: E402,F401  (/oidc/sso, /oidc/callback)

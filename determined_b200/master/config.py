@@ -74,8 +74,17 @@ SCHEMA: Dict[str, Any] = {
                 "strict_job_queue_control": {"type": "boolean", "default": False}}}}},
         "telemetry": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
             "enabled": {"type": "boolean", "default": False},
+            "segment_url": {"type": ["string", "null"], "default": None, "description": "collector that receives the usage events; none are sent without it"},
+            "segment_master_key": {"type": ["string", "null"], "default": None},
             "otel_enabled": {"type": "boolean", "default": True},
             "otel_endpoint": {"type": ["string", "null"], "default": None}}},
+        "oidc": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
+            "enabled": {"type": "boolean", "default": False}, "provider": {"type": "string", "default": "oidc"},
+            "client_id": {"type": ["string", "null"], "default": None}, "client_secret": {"type": ["string", "null"], "default": None},
+            "idp_sso_url": {"type": ["string", "null"], "default": None}, "token_url": {"type": ["string", "null"], "default": None},
+            "userinfo_url": {"type": ["string", "null"], "default": None}, "idp_recipient_url": {"type": ["string", "null"], "default": None},
+            "authentication_claim": {"type": "string", "default": "email"}, "scope": {"type": "string", "default": "openid profile email"},
+            "auto_provision_users": {"type": "boolean", "default": False}, "always_redirect": {"type": "boolean", "default": False}}},
         "observability": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
             "enable_prometheus": {"type": "boolean", "default": True}}},
         "webhooks": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
@@ -92,7 +101,7 @@ SCHEMA: Dict[str, Any] = {
 }
 REGISTRY = {SCHEMA["$id"]: SCHEMA}
 
-SECRET_KEYS = ("security.agent_token", "security.initial_user_password", "security.tls.key", "webhooks.signing_key",
+SECRET_KEYS = ("oidc.client_secret", "telemetry.segment_master_key", "security.agent_token", "security.initial_user_password", "security.tls.key", "webhooks.signing_key",
                "checkpoint_storage.secret_key", "checkpoint_storage.access_key", "checkpoint_storage.connection_string",
                "checkpoint_storage.credentials")
 

@@ -452,6 +452,8 @@ class Experiment:
     def _set_terminal(self, state: str) -> None:
         self.state = state
         logger.info("experiment %d: finished as %s", self.id, state)
+        if getattr(self.master, "telemetry", None) is not None:
+            self.master.telemetry.track("experiment_state_changed", experiment_id=self.id, state=state, num_trials=len(self.trials))
         self.master.fire_webhooks("EXPERIMENT_STATE_CHANGE", {"experiment_id": self.id, "state": state})
         self.master.schedule_gc(self)
 
@@ -645,6 +647,18 @@ class Master:
         self.log_retention_days = int(cfg["retention_policy.log_retention_days"])
         if cfg["webhooks.signing_key"]:
             self.db.set_meta("webhook_signing_key", cfg["webhooks.signing_key"])
+        from determined_b200 import __version__
+        from determined_b200.master import telemetry
+
+        self.telemetry = telemetry.Telemetry(self.cluster_id, cfg["telemetry.enabled"], cfg["telemetry.segment_url"], cfg["telemetry.segment_master_key"], __version__)
+        self.telemetry.track("master_started", num_pools=len(self.pools), num_slots=sum(a.num_slots for p in self.pools.values() for a in p.agents.values()),
+                             scheduler=self.pool.scheduler)
+        oidc = dict(cfg.data.get("oidc") or {})
+        if oidc.get("enabled"):
+            missing = [k for k in ("client_id", "idp_sso_url", "token_url", "userinfo_url", "idp_recipient_url") if not oidc.get(k)]
+            if missing:
+                raise ValueError("oidc.enabled needs: " + ", ".join("oidc." + k for k in missing))
+        self.oidc = oidc
 
     log_retention_days = -1
     _last_retention_sweep = 0.0
@@ -767,6 +781,9 @@ class Master:
             exp = Experiment(self, {"id": eid, "state": ACTIVE if activate else PAUSED, "config": cfg,
                                     "owner_id": owner_id, "owner_name": owner})
             self.experiments[eid] = exp
+            if getattr(self, "telemetry", None) is not None:
+                self.telemetry.track("experiment_created", experiment_id=eid, searcher=(cfg.get("searcher") or {}).get("name"),
+                                     slots_per_trial=(cfg.get("resources") or {}).get("slots_per_trial", 1), unmanaged=bool(unmanaged))
             if not unmanaged:
                 exp.start()
         return exp, cfg
