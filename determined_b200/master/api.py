@@ -578,7 +578,7 @@ def delete_experiment(ctx: Ctx, eid: str) -> Any:
     for t in tids:
         ctx.m.db.exec("DELETE FROM metrics WHERE trial_id=?", (t,))
         ctx.m.db.exec("DELETE FROM checkpoints WHERE trial_id=?", (t,))
-        ctx.m.db.exec("DELETE FROM task_logs WHERE task_id=?", (f"trial-{t}",))
+        ctx.m.db.delete_task_logs(f"trial-{t}")
     ctx.m.db.exec("DELETE FROM trials WHERE experiment_id=?", (e,))
     ctx.m.db.exec("DELETE FROM experiments WHERE id=?", (e,))
     ctx.m.experiments.pop(e, None)

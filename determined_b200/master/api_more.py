@@ -531,9 +531,7 @@ def sweep_trial_logs(m: core.Master, now: Optional[float] = None) -> int:
         days = json.loads(r["value"])
         if days is None or days < 0:
             continue
-        with m.db._lock:
-            cur = m.db._conn.execute("DELETE FROM task_logs WHERE task_id=? AND ts < ?", (f"trial-{int(r['id'])}", now - 86400.0 * days))
-            n += int(cur.rowcount or 0)
+        n += m.db.delete_task_logs(f"trial-{int(r['id'])}", now - 86400.0 * days)
     return n
 
 

@@ -456,10 +456,9 @@ def get_task(ctx: Ctx, task_id: str) -> Any:
 def _log_fields(ctx: Ctx, task_id: str) -> Any:
     """The values the log filters of this task can take (one snapshot: a finished stream in the reference's terms)."""
     f: Dict[str, set] = {"agentIds": set(), "containerIds": set(), "rankIds": set(), "stdtypes": set(), "sources": set()}
-    for r in ctx.m.db.all("SELECT DISTINCT allocation_id, rank_id, stdtype, source FROM task_logs WHERE task_id=?", (task_id,)):
-        for k, col in (("containerIds", "allocation_id"), ("rankIds", "rank_id"), ("stdtypes", "stdtype"), ("sources", "source")):
-            if r[col] is not None:
-                f[k].add(r[col])
+    vals = ctx.m.db.log_field_values(task_id)
+    for k, col in (("containerIds", "allocation_id"), ("rankIds", "rank_id"), ("stdtypes", "stdtype"), ("sources", "source")):
+        f[k].update(v for v in vals.get(col, []) if v is not None)
     for r in ctx.m.db.all("SELECT DISTINCT id FROM allocations WHERE task_id=?", (task_id,)):
         aid = r["id"]
         live = ctx.m.allocations.get(aid) if hasattr(ctx.m, "allocations") else None

@@ -653,6 +653,19 @@ class Master:
         self.telemetry = telemetry.Telemetry(self.cluster_id, cfg["telemetry.enabled"], cfg["telemetry.segment_url"], cfg["telemetry.segment_master_key"], __version__)
         self.telemetry.track("master_started", num_pools=len(self.pools), num_slots=sum(a.num_slots for p in self.pools.values() for a in p.agents.values()),
                              scheduler=self.pool.scheduler)
+        lg = cfg.data.get("logging") or {}
+        if lg.get("type") == "elastic":
+            if not lg.get("host"):
+                raise ValueError("logging.type elastic needs logging.host")
+            from determined_b200.master import elastic
+
+            self.db.log_backend = elastic.ElasticLogs.from_config(lg)
+            try:
+                self.db.log_backend.ensure_template()
+            except Exception as e:  # noqa: BLE001  (a cluster that is down now may be up when the first line arrives)
+                logger.warning("could not install the Elasticsearch index template: %s", e)
+        else:
+            self.db.log_backend = None
         oidc = dict(cfg.data.get("oidc") or {})
         if oidc.get("enabled"):
             missing = [k for k in ("client_id", "idp_sso_url", "token_url", "userinfo_url", "idp_recipient_url") if not oidc.get(k)]

@@ -131,15 +131,43 @@ class DB:
             self._conn.close()
 
     # -- logs ----------------------------------------------------------------------------------------
+    # -- task logs: here, or in ``log_backend`` (master/elastic.py) when one is configured --------------------------------
+    log_backend: Any = None
+
     def add_logs(self, rows: List[Tuple[Any, ...]]) -> None:
+        if self.log_backend is not None:
+            return self.log_backend.add_logs(rows)
         with self._lock:
             self._conn.executemany(
                 "INSERT INTO task_logs(task_id,allocation_id,ts,level,rank_id,stdtype,source,log) VALUES(?,?,?,?,?,?,?,?)", rows)
 
     def delete_logs_before(self, ts: float) -> int:
+        if self.log_backend is not None:
+            return self.log_backend.delete_logs_before(ts)
         with self._lock:
             cur = self._conn.execute("DELETE FROM task_logs WHERE ts < ?", (ts,))
             return int(cur.rowcount or 0)
 
-    def get_logs(self, task_id: str, after_id: int = 0, limit: int = 1000) -> List[sqlite3.Row]:
+    def delete_task_logs(self, task_id: str, before_ts: Optional[float] = None) -> int:
+        if self.log_backend is not None:
+            return self.log_backend.delete_task_logs(task_id, before_ts)
+        with self._lock:
+            if before_ts is None:
+                cur = self._conn.execute("DELETE FROM task_logs WHERE task_id=?", (task_id,))
+            else:
+                cur = self._conn.execute("DELETE FROM task_logs WHERE task_id=? AND ts < ?", (task_id, before_ts))
+            return int(cur.rowcount or 0)
+
+    def log_field_values(self, task_id: str) -> Dict[str, List[Any]]:
+        """Distinct values of the filterable columns of one task's logs."""
+        if self.log_backend is not None:
+            return self.log_backend.log_field_values(task_id)
+        out: Dict[str, List[Any]] = {}
+        for col in ("allocation_id", "rank_id", "stdtype", "source"):
+            out[col] = [r[0] for r in self.all(f"SELECT DISTINCT {col} FROM task_logs WHERE task_id=? AND {col} IS NOT NULL", (task_id,))]
+        return out
+
+    def get_logs(self, task_id: str, after_id: int = 0, limit: int = 1000) -> List[Any]:
+        if self.log_backend is not None:
+            return self.log_backend.get_logs(task_id, after_id, limit)
         return self.all("SELECT * FROM task_logs WHERE task_id=? AND id>? ORDER BY id LIMIT ?", (task_id, after_id, limit))
