@@ -51,12 +51,23 @@ def install_alias(name: str = "determined") -> None:
         def exec_module(self, module):  # type: ignore
             pass
 
+        # runpy (`python -m determined.exec.launch`, runpy.run_module) asks the loader for the code of the module
+        def get_code(self, fullname):  # type: ignore
+            return self.mod.__spec__.loader.get_code(self.mod.__name__)
+
+        def get_source(self, fullname):  # type: ignore
+            return self.mod.__spec__.loader.get_source(self.mod.__name__)
+
+        def is_package(self, fullname):  # type: ignore
+            return hasattr(self.mod, "__path__")
+
     import importlib.util
 
     _AliasFinder.alias_of = name
     if not any(getattr(f, "alias_of", None) == name for f in sys.meta_path):
         sys.meta_path.insert(0, _AliasFinder())
-    sys.modules.setdefault(name, importlib.import_module(real_root))
+    if real_root in sys.modules:      # `determined` is this (already imported) package; `model_hub` loads on first import, it pulls in torch
+        sys.modules.setdefault(name, sys.modules[real_root])
 
 
 def __getattr__(attr: str):  # lazy heavy submodules (torch import) – keeps `import determined_b200` light

@@ -12,6 +12,9 @@ import sys
 from typing import Iterator, Set
 
 
+_active = False
+
+
 def modules_from_dir(path: str) -> Set[str]:
     """Top-level module names importable from ``path``."""
     names = set()
@@ -25,9 +28,14 @@ def import_from_path(path: os.PathLike) -> Iterator[None]:
     """Within the block, ``import x`` resolves ``x`` from ``path`` first, fresh (no cached module
     of the same name is reused), and whatever was imported from ``path`` is evicted on exit so a
     second checkpoint with different code can be loaded next."""
+    global _active
+    if _active:
+        raise RuntimeError("import_from_path does not support nesting")
     p = str(pathlib.Path(path).resolve())
     local = modules_from_dir(p)
     saved = {}
+    _active = True
+    write_bytecode, sys.dont_write_bytecode = sys.dont_write_bytecode, True     # a checkpoint directory stays as it was stored
     for name in list(sys.modules):
         if name.split(".")[0] in local:
             saved[name] = sys.modules.pop(name)
@@ -36,6 +44,8 @@ def import_from_path(path: os.PathLike) -> Iterator[None]:
     try:
         yield
     finally:
+        _active = False
+        sys.dont_write_bytecode = write_bytecode
         with contextlib.suppress(ValueError):
             sys.path.remove(p)
         for name in list(sys.modules):

@@ -25,7 +25,7 @@ def salt_and_hash(password: str) -> str:
 
 
 def _config_dir() -> pathlib.Path:
-    base = os.environ.get("DET_CONFIG_DIR") or os.path.join(
+    base = os.environ.get("DET_DEBUG_CONFIG_PATH") or os.environ.get("DET_CONFIG_DIR") or os.path.join(
         os.environ.get("XDG_CONFIG_HOME", os.path.expanduser("~/.config")), "determined_b200")
     return pathlib.Path(base)
 
@@ -41,13 +41,24 @@ class TokenStore:
     def _load(self) -> Dict[str, Any]:
         try:
             d = json.loads(self.path.read_text())
-            if not isinstance(d, dict) or "masters" not in d:
-                raise errors.CorruptTokenCacheException()
-            return d
         except FileNotFoundError:
             return {"version": 2, "masters": {}}
         except json.JSONDecodeError:
             raise errors.CorruptTokenCacheException()
+        if not isinstance(d, dict):
+            raise errors.CorruptTokenCacheException()
+        version = d.get("version", 0)
+        if version == 0 and "masters" not in d:
+            # the oldest layout knew one master only: {"active_user": ..., "tokens": {...}} belongs to the master asked for
+            entry = {"tokens": dict(d.get("tokens") or {})}
+            if d.get("active_user"):
+                entry["active_user"] = d["active_user"]
+            d = {"version": 2, "masters": {self.master_url: entry}}
+        elif version == 1:
+            d = {"version": 2, "masters": _merge_v1_masters(d.get("masters") or {})}
+        if "masters" not in d or not isinstance(d["masters"], dict):
+            raise errors.CorruptTokenCacheException()
+        return d
 
     def _save(self) -> None:
         self.path.parent.mkdir(parents=True, exist_ok=True)
@@ -85,6 +96,34 @@ class TokenStore:
     def clear_active(self) -> None:
         self._m().pop("active_user", None)
         self._save()
+
+
+def _merge_v1_masters(masters: Dict[str, Any]) -> Dict[str, Any]:
+    """Version 1 keyed masters by whatever the user had typed (``host``, ``http://host:80#x``, ``https://host/?k=v``); version
+    2 keys by the canonical URL.  Entries that meet under one key are merged: tokens are united (either one wins on a clash),
+    one of the active users survives.  URLs nobody can parse are dropped rather than failing the whole file."""
+    import urllib.parse
+
+    out: Dict[str, Any] = {}
+    for raw, entry in masters.items():
+        try:
+            bare = "://" not in raw
+            u = urllib.parse.urlparse(("http://" + raw) if bare else raw)
+            host = u.hostname or ""
+            if ":" in host:
+                host = f"[{host}]"
+            port = f":{u.port}" if u.port else ""
+            key = _session.canonicalize_master_url((f"{host}{port}" if bare else f"{u.scheme}://{host}{port}") + u.path)
+        except ValueError:
+            continue
+        if not isinstance(entry, dict):
+            continue
+        dst = out.setdefault(key, {"tokens": {}})
+        for user, tok in (entry.get("tokens") or {}).items():
+            dst["tokens"].setdefault(user, tok)
+        if entry.get("active_user") and "active_user" not in dst:
+            dst["active_user"] = entry["active_user"]
+    return out
 
 
 def login(master: str, username: str, password: str, cert: Any = None) -> _session.Session:

@@ -137,6 +137,11 @@ def default_load(master_url: str, explicit_path: Optional[str] = None, explicit_
     if path:
         return Cert(cert_pem=pathlib.Path(path).read_text(), name=name)
     with contextlib.suppress(OSError, ValueError):
+        old_file = _config_dir() / "master.crt"          # the layout before the per-master store: one certificate, one master
+        if old_file.exists():
+            CertStore().set_cert(master_url, old_file.read_text())
+            old_file.unlink()
+    with contextlib.suppress(OSError, ValueError):
         got = CertStore().get_cert(master_url)
         if got is not None:
             return Cert(cert_pem=got[0], name=name or got[1])

@@ -41,6 +41,24 @@ def _alias_modules(s: str) -> str:
     return s
 
 
+def launch(experiment_config) -> int:  # noqa: ANN001
+    """Run the experiment's entrypoint as a child process and return its exit code (reference ``exec/launch.py:launch``)."""
+    cfg = experiment_config if isinstance(experiment_config, dict) else dict(experiment_config)
+    cmd = entrypoint_to_cmd(cfg.get("entrypoint"))
+    logger.info("launching: %s", cmd)
+    p = subprocess.Popen(cmd)
+    return _wait_forwarding_signals(p)
+
+
+def _wait_forwarding_signals(p, on_term=None) -> int:  # noqa: ANN001
+    try:
+        signal.signal(signal.SIGTERM, on_term or (lambda s, f: util.signal_process_tree(p, signal.SIGTERM)))
+        signal.signal(signal.SIGINT, lambda s, f: util.signal_process_tree(p, signal.SIGINT))
+    except ValueError:       # not the main thread: the caller owns signal handling
+        pass
+    return p.wait()
+
+
 def main() -> int:
     logging.basicConfig(level=logging.INFO, format=det.LOG_FORMAT)
     info = det.get_cluster_info()
@@ -68,9 +86,7 @@ def main() -> int:
             pass
         util.signal_process_tree(p, signal.SIGTERM)
 
-    signal.signal(signal.SIGTERM, on_term)
-    signal.signal(signal.SIGINT, lambda s, f: util.signal_process_tree(p, signal.SIGINT))
-    return p.wait()
+    return _wait_forwarding_signals(p, on_term)
 
 
 if __name__ == "__main__":

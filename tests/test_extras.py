@@ -559,3 +559,20 @@ def test_model_hub_dataset_helpers_and_download(tmp_path):
     r = subprocess.run([sys.executable, str(runner), "/root/reference/model_hub", "tests/test_hf.py", "tests/test_utils.py", "-k", "not download_url"],
                        cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert r.returncode == 0 and "4 passed" in r.stdout, r.stdout[-2000:]
+
+
+def test_import_from_path_refuses_nesting_and_writes_no_bytecode(tmp_path):
+    import determined_b200 as det
+
+    for name in ("a", "b"):
+        (tmp_path / name).mkdir()
+        (tmp_path / name / "model_def_x.py").write_text(f"val = {name!r}\n")
+    with det.import_from_path(tmp_path / "a"):
+        import model_def_x as a
+        with pytest.raises(RuntimeError, match="does not support nesting"):
+            with det.import_from_path(tmp_path / "b"):
+                pass
+    with det.import_from_path(tmp_path / "b"):
+        import model_def_x as b
+    assert (a.val, b.val) == ("a", "b") and "model_def_x" not in sys.modules
+    assert not (tmp_path / "a" / "__pycache__").exists() and not (tmp_path / "b" / "__pycache__").exists()
