@@ -36,7 +36,7 @@ def main(core_context: core.Context, a: argparse.Namespace) -> None:
         model = transformers.GPT2LMHeadModel(cfg)
     args = transformers.TrainingArguments(output_dir=a.output_dir, max_steps=a.max_steps, per_device_train_batch_size=a.per_device_train_batch_size,
                                           eval_strategy="steps", eval_steps=a.eval_steps, save_steps=a.eval_steps, logging_steps=a.logging_steps, bf16=a.bf16,
-                                          report_to=[], save_safetensors=False)
+                                          report_to=[])
     cb = DetCallback(core_context, args)
     trainer = transformers.Trainer(model=model, args=args, train_dataset=Tokens(model.config.vocab_size, a.block_size, 4096, 0),
                                    eval_dataset=Tokens(model.config.vocab_size, a.block_size, 256, 1), callbacks=[cb])

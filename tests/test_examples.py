@@ -142,3 +142,65 @@ def test_dsat_torchvision_examples(tmp_path, monkeypatch):
     env = dict(os.environ, PYTHONPATH=str(ROOT), CUDA_VISIBLE_DEVICES="")
     r = subprocess.run([sys.executable, "script.py"], cwd=d / "core_api", env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:]
+
+
+@pytest.mark.parametrize("script", ["1_metrics.py", "2_checkpoints.py", "3_hpsearch.py", "4_distributed.py"])
+def test_core_api_tutorial_stages_run_off_cluster(script, tmp_path):
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    r = subprocess.run([sys.executable, str(EX / "tutorials" / "core_api" / script)], cwd=tmp_path, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                       text=True, timeout=120)
+    assert r.returncode == 0 and "report_metrics(group=validation" in r.stdout, r.stdout[-2000:]
+
+
+def test_core_api_pytorch_mnist_trains_checkpoints_and_reports(tmp_path):
+    env = dict(os.environ, PYTHONPATH=str(ROOT), MNIST_MAX_BATCHES="5", MNIST_SYNTHETIC="512")
+    r = subprocess.run([sys.executable, str(EX / "tutorials" / "core_api_pytorch_mnist" / "model_def.py")], cwd=tmp_path, env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0 and "saved checkpoint" in r.stdout and "SearcherOperation Complete" in r.stdout and "'accuracy'" in r.stdout, r.stdout[-2000:]
+
+
+def test_inference_examples_score_every_record(tmp_path):
+    env = dict(os.environ, PYTHONPATH=str(ROOT))
+    r = subprocess.run([sys.executable, str(EX / "features" / "inference_mnist_pytorch" / "inference.py")], cwd=tmp_path, env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0 and "scored 1000 records" in r.stdout, r.stdout[-2000:]
+    comp = EX / "features" / "torch_batch_process_core_api_comparison"
+    for script, words in (("torch_batch_process_inference.py", "torch_batch_process variant scored 1000 records"), ("core_api_inference.py", "core api variant scored 1000 records")):
+        r = subprocess.run([sys.executable, str(comp / script)], cwd=tmp_path, env=dict(env, PYTHONPATH=f"{ROOT}{os.pathsep}{comp}"), stdout=subprocess.PIPE,
+                           stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert r.returncode == 0 and words in r.stdout, r.stdout[-2000:]
+    import json
+
+    a = sorted((tmp_path / "comparison_out" / "tbp").glob("*.json"))
+    b = sorted((tmp_path / "comparison_out" / "core_api").glob("*.json"))
+    assert sum(len(json.loads(f.read_text())) for f in a) == sum(len(json.loads(f.read_text())) for f in b) == 1000
+    assert sorted(sum((json.loads(f.read_text()) for f in a), [])) == sorted(sum((json.loads(f.read_text()) for f in b), [])), "both variants make the same predictions"
+
+
+def test_unmanaged_checkpoint_example_resumes_in_the_same_trial(tmp_path):
+    from determined_b200.common import api
+    from determined_b200.master import api as mapi
+    from determined_b200.master import core
+
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=1, launch=False, work_dir=str(tmp_path / "w"))
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    try:
+        env = dict(os.environ, PYTHONPATH=str(ROOT), DET_MASTER=m.url, HOME=str(tmp_path))
+        script = str(EX / "features" / "unmanaged" / "2_checkpoints.py")
+        r1 = subprocess.run([sys.executable, script, "--steps", "40", "--checkpoint-dir", str(tmp_path / "ck")], cwd=tmp_path, env=env,
+                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert r1.returncode == 0 and "resumed" not in r1.stdout, r1.stdout[-2000:]
+        r2 = subprocess.run([sys.executable, script, "--steps", "80", "--checkpoint-dir", str(tmp_path / "ck")], cwd=tmp_path, env=env,
+                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert r2.returncode == 0 and "at step 40" in r2.stdout, r2.stdout[-2000:]
+        sess = api.authentication.login(m.url, "determined", "")
+        exps = sess.get("/api/v1/experiments").json()["experiments"]
+        assert len(exps) == 1, "the second run finds the first one's experiment by its external id"
+        trials = sess.get(f"/api/v1/experiments/{exps[0]['id']}/trials").json()["trials"]
+        assert len(trials) == 1
+        steps = [x["totalBatches"] for x in sess.get(f"/api/v1/trials/{trials[0]['id']}/metrics").json()["metrics"] if x["group"] == "training"]
+        assert steps == [10, 20, 30, 40, 50, 60, 70, 80]
+    finally:
+        m.stop()
+        srv.stop()
