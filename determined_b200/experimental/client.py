@@ -30,6 +30,13 @@ class ExperimentState(enum.Enum):
     CANCELED = "STATE_CANCELED"
     ERROR = "STATE_ERROR"
     DELETED = "STATE_DELETED"
+    DELETING = "STATE_DELETING"
+    DELETE_FAILED = "STATE_DELETE_FAILED"
+    # sub-states of ACTIVE that the job queue reports
+    QUEUED = "STATE_QUEUED"
+    PULLING = "STATE_PULLING"
+    STARTING = "STATE_STARTING"
+    RUNNING = "STATE_RUNNING"
 
 
 TERMINAL = {ExperimentState.COMPLETED, ExperimentState.CANCELED, ExperimentState.ERROR}
@@ -83,7 +90,11 @@ class TrialSortBy(enum.Enum):
 
 class ModelSortBy(enum.Enum):
     NAME = "SORT_BY_NAME"
+    DESCRIPTION = "SORT_BY_DESCRIPTION"
     CREATION_TIME = "SORT_BY_CREATION_TIME"
+    LAST_UPDATED_TIME = "SORT_BY_LAST_UPDATED_TIME"
+    NUM_VERSIONS = "SORT_BY_NUM_VERSIONS"
+    WORKSPACE = "SORT_BY_WORKSPACE"
 
 
 class Checkpoint(_sdk_more.CheckpointMore):

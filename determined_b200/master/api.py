@@ -152,6 +152,14 @@ def user_json(row: Any) -> Dict[str, Any]:
             "displayName": row["display_name"], "modifiedAt": _ts(row["modified_at"]), "remote": str(row["password_hash"] or "").startswith(REMOTE_USER_MARK)}
 
 
+def sort_rows(rows: List[Any], key: Callable[[Any], Any], order_by: Optional[str]) -> List[Any]:
+    """Stable sort on ``key``; rows without a value go last whatever the direction."""
+    have = [r for r in rows if key(r) is not None]
+    none = [r for r in rows if key(r) is None]
+    have.sort(key=key, reverse=order_by == "ORDER_BY_DESC")
+    return have + none
+
+
 def page(items: List[Any], ctx: Ctx) -> Tuple[List[Any], Dict[str, Any]]:
     off, lim = ctx.qi("offset", 0), ctx.qi("limit", 0)
     total = len(items)
@@ -633,7 +641,26 @@ def patch_experiment(ctx: Ctx, eid: str) -> Any:
 def exp_trials(ctx: Ctx, eid: str) -> Any:
     _exp_row(ctx, eid)
     rows = ctx.m.db.all("SELECT * FROM trials WHERE experiment_id=? ORDER BY id", (int(eid),))
-    items, pg = page([trial_json(ctx.m, r) for r in rows], ctx)
+    trials = [trial_json(ctx.m, r) for r in rows]
+    states = set(ctx.query.get("states", []))
+    if states:
+        trials = [t for t in trials if t["state"] in states]
+    smaller = bool((dbmod.U(_exp_row(ctx, eid)["config"], {}).get("searcher") or {}).get("smaller_is_better", True))
+
+    def duration(t: Dict[str, Any]) -> Optional[float]:
+        a, b = _log_time(t.get("startTime")), _log_time(t.get("endTime"))
+        return (b if b is not None else time.time()) - a if a is not None else None
+
+    keys: Dict[str, Callable[[Dict[str, Any]], Any]] = {
+        "SORT_BY_ID": lambda t: t["id"], "SORT_BY_START_TIME": lambda t: t.get("startTime"), "SORT_BY_END_TIME": lambda t: t.get("endTime"),
+        "SORT_BY_STATE": lambda t: t["state"], "SORT_BY_BATCHES_PROCESSED": lambda t: t.get("totalBatchesProcessed"), "SORT_BY_DURATION": duration,
+        "SORT_BY_RESTARTS": lambda t: t.get("restarts"), "SORT_BY_CHECKPOINT_SIZE": lambda t: t.get("totalCheckpointSize"),
+        "SORT_BY_BEST_VALIDATION_METRIC": lambda t: (t.get("searcherMetricValue") if smaller else (-t["searcherMetricValue"] if t.get("searcherMetricValue") is not None else None)),
+        "SORT_BY_LATEST_VALIDATION_METRIC": lambda t: ((t.get("latestValidation") or {}).get("metrics", {}).get("avgMetrics", {}) or {}).get(
+            (dbmod.U(_exp_row(ctx, eid)["config"], {}).get("searcher") or {}).get("metric")),
+        "SORT_BY_LOG_RETENTION_DAYS": lambda t: t.get("logRetentionDays")}
+    trials = sort_rows(trials, keys.get(ctx.q("sortBy") or "", keys["SORT_BY_ID"]), ctx.q("orderBy"))
+    items, pg = page(trials, ctx)
     return {"trials": items, "pagination": pg}
 
 
@@ -1558,6 +1585,19 @@ def list_models(ctx: Ctx) -> Any:
     rows = [_model_json(ctx.m, r) for r in ctx.m.db.all("SELECT * FROM models ORDER BY id")]
     if ctx.q("name"):
         rows = [r for r in rows if ctx.q("name") in r["name"]]
+    if ctx.q("description"):
+        rows = [r for r in rows if ctx.q("description") in (r["description"] or "")]
+    if ctx.query.get("labels"):
+        rows = [r for r in rows if set(ctx.query["labels"]) <= set(r["labels"])]
+    if ctx.q("archived") is not None:
+        rows = [r for r in rows if r["archived"] == (ctx.q("archived") in ("true", "1"))]
+    if ctx.query.get("workspaceIds"):
+        rows = [r for r in rows if r["workspaceId"] in {int(x) for x in ctx.query["workspaceIds"]}]
+    ws_names = {w["id"]: w["name"] for w in ctx.m.db.all("SELECT id, name FROM workspaces")}
+    keys = {"SORT_BY_NAME": lambda r: r["name"], "SORT_BY_DESCRIPTION": lambda r: r["description"], "SORT_BY_CREATION_TIME": lambda r: r["creationTime"],
+            "SORT_BY_LAST_UPDATED_TIME": lambda r: r["lastUpdatedTime"], "SORT_BY_NUM_VERSIONS": lambda r: r["numVersions"],
+            "SORT_BY_WORKSPACE": lambda r: ws_names.get(r["workspaceId"], "")}
+    rows = sort_rows(rows, keys.get(ctx.q("sortBy") or "", lambda r: r["id"]), ctx.q("orderBy"))
     items, pg = page(rows, ctx)
     return {"models": items, "pagination": pg}
 

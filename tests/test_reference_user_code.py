@@ -64,6 +64,7 @@ REF_TESTS = [
     ("tests/common/api/test_certs.py", "", 1),                                  # the one-certificate layout moves into the per-master store
     ("tests/common/api/test_authentication.py", "", 2),                         # auth.json of versions 0 and 1 are read and merged
     ("tests/launch/test_launch.py", "not launch_trial", 3),                     # that one pins the Horovod command line; the launch script runs through runpy
+    ("tests/test_sdk.py", "", 6),                                               # SDK enums cover exactly the values of the bindings' enums
     ("tests/common/test_yaml.py", "", 4),
     ("tests/common/test_api.py", "", 15),                                       # master URL canonicalisation
     ("tests/launch/test_wrap_rank.py", "", 1),
