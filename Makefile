@@ -21,6 +21,7 @@ bindings:         ## regenerate common/api/bindings.py from the master's route t
 check: bindings   ## what CI runs before the tests
 	git diff --exit-code determined_b200/common/api/bindings.py
 	$(PY) scripts/cli_gaps.py --check
+	$(PY) scripts/lint_names.py
 	$(PY) -m compileall -q determined_b200 tests benchmarks examples bench.py __graft_entry__.py
 
 tsan:             ## race check of the C++ host runtime (shared-memory collectives) under ThreadSanitizer

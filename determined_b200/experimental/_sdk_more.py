@@ -31,8 +31,9 @@ class CheckpointMore:
         params = {"group": group} if group else {}
         for m in self._session.get(f"/api/v1/trials/{tid}/metrics", params=params).json()["metrics"]:
             if steps is None or m["totalBatches"] == steps:
-                yield {"trial_id": m["trialId"], "group": m["group"], "steps_completed": m["totalBatches"], "metrics": m["metrics"]["avgMetrics"],
-                       "batch_metrics": m["metrics"].get("batchMetrics"), "end_time": m["endTime"]}
+                from determined_b200.experimental import client as _client
+
+                yield _client.TrialMetrics._from_json(m)
 
 
 class TrialMore:

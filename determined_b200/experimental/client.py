@@ -97,6 +97,89 @@ class ModelSortBy(enum.Enum):
     WORKSPACE = "SORT_BY_WORKSPACE"
 
 
+class CheckpointSortBy(enum.Enum):
+    """Field a listing of checkpoints is sorted on."""
+
+    UUID = "SORT_BY_UUID"
+    TRIAL_ID = "SORT_BY_TRIAL_ID"
+    BATCH_NUMBER = "SORT_BY_BATCH_NUMBER"
+    END_TIME = "SORT_BY_END_TIME"
+    STATE = "SORT_BY_STATE"
+    SEARCHER_METRIC = "SORT_BY_SEARCHER_METRIC"
+
+
+class ExperimentSortBy(enum.Enum):
+    """Field a listing of experiments is sorted on."""
+
+    ID = "SORT_BY_ID"
+    DESCRIPTION = "SORT_BY_DESCRIPTION"
+    START_TIME = "SORT_BY_START_TIME"
+    END_TIME = "SORT_BY_END_TIME"
+    STATE = "SORT_BY_STATE"
+    NUM_TRIALS = "SORT_BY_NUM_TRIALS"
+    PROGRESS = "SORT_BY_PROGRESS"
+    USER = "SORT_BY_USER"
+    NAME = "SORT_BY_NAME"
+    FORKED_FROM = "SORT_BY_FORKED_FROM"
+    RESOURCE_POOL = "SORT_BY_RESOURCE_POOL"
+    PROJECT_ID = "SORT_BY_PROJECT_ID"
+    CHECKPOINT_SIZE = "SORT_BY_CHECKPOINT_SIZE"
+    CHECKPOINT_COUNT = "SORT_BY_CHECKPOINT_COUNT"
+    SEARCHER_METRIC_VAL = "SORT_BY_SEARCHER_METRIC_VAL"
+
+
+ExperimentOrderBy = OrderBy
+
+
+class TrialMetrics:
+    """One metrics report of a trial (reference ``determined.experimental.TrialMetrics``): ``trial_id``, ``trial_run_id``,
+    ``steps_completed``, ``end_time``, ``metrics``, ``group``, ``batch_metrics``.  Also readable like the dict earlier
+    versions of this SDK yielded (``m["metrics"]``)."""
+
+    _FIELDS = ("trial_id", "trial_run_id", "steps_completed", "end_time", "metrics", "group", "batch_metrics")
+    __slots__ = _FIELDS
+
+    def __init__(self, trial_id: int, trial_run_id: int, steps_completed: int, end_time: Any, metrics: Dict[str, Any], group: str,
+                 batch_metrics: Optional[List[Dict[str, Any]]] = None) -> None:
+        self.trial_id, self.trial_run_id, self.steps_completed, self.end_time = trial_id, trial_run_id, steps_completed, end_time
+        self.metrics, self.group, self.batch_metrics = metrics, group, batch_metrics
+
+    @classmethod
+    def _from_json(cls, m: Dict[str, Any]) -> "TrialMetrics":
+        kind = {"training": TrainingMetrics, "validation": ValidationMetrics}.get(m.get("group", ""), cls)
+        return kind(int(m["trialId"]), int(m.get("trialRunId") or 0), int(m["totalBatches"]), m.get("endTime"), (m.get("metrics") or {}).get("avgMetrics") or {},
+                    m.get("group", ""), (m.get("metrics") or {}).get("batchMetrics"))
+
+    def keys(self) -> List[str]:
+        return list(self._FIELDS)
+
+    def __getitem__(self, k: str) -> Any:
+        if k not in self._FIELDS:
+            raise KeyError(k)
+        return getattr(self, k)
+
+    def get(self, k: str, default: Any = None) -> Any:
+        return getattr(self, k, default) if k in self._FIELDS else default
+
+    def __eq__(self, other: Any) -> bool:
+        return isinstance(other, TrialMetrics) and all(getattr(self, k) == getattr(other, k) for k in self._FIELDS)
+
+    def __repr__(self) -> str:
+        return f"{type(self).__name__}(" + ", ".join(f"{k}={getattr(self, k)!r}" for k in self._FIELDS) + ")"
+
+
+class TrainingMetrics(TrialMetrics):
+    """A report of the ``training`` group."""
+
+    __slots__ = ()
+
+
+class ValidationMetrics(TrialMetrics):
+    """A report of the ``validation`` group."""
+
+    __slots__ = ()
+
+
 class Checkpoint(_sdk_more.CheckpointMore):
     def __init__(self, session: api.Session, uuid: str, data: Optional[Dict[str, Any]] = None) -> None:
         self._session, self.uuid = session, uuid
@@ -200,11 +283,10 @@ class Trial(_sdk_more.TrialMore):
         if tail is not None:
             yield from buf[-tail:]
 
-    def iter_metrics(self, group: Optional[str] = None) -> Iterator[Dict[str, Any]]:
+    def iter_metrics(self, group: Optional[str] = None) -> Iterator[TrialMetrics]:
         params = {"group": group} if group else {}
         for m in self._session.get(f"/api/v1/trials/{self.id}/metrics", params=params).json()["metrics"]:
-            yield {"trial_id": m["trialId"], "group": m["group"], "steps_completed": m["totalBatches"], "metrics": m["metrics"]["avgMetrics"],
-                   "batch_metrics": m["metrics"].get("batchMetrics"), "end_time": m["endTime"]}
+            yield TrialMetrics._from_json(m)
 
     def stream_training_metrics(self) -> Iterator[Dict[str, Any]]:
         return self.iter_metrics("training")
@@ -679,12 +761,11 @@ class Determined(_sdk_more.DeterminedMore):
         return [ResourcePool(self._session, p) for p in self._session.get("/api/v1/resource-pools").json()["resourcePools"]]
 
     # -- metrics across trials ---------------------------------------------------------------------
-    def iter_trials_metrics(self, trial_ids: List[int], group: str) -> Iterator[Dict[str, Any]]:
+    def iter_trials_metrics(self, trial_ids: List[int], group: str) -> Iterator[TrialMetrics]:
         """Metrics of several trials in one call (reference ``Determined.iter_trials_metrics``)."""
         r = self._session.get("/api/v1/trials/metrics/trial_metrics", params={"trialIds": list(trial_ids), "group": group}).json()
         for m in r["metrics"]:
-            yield {"trial_id": m["trialId"], "group": m["group"], "steps_completed": m["totalBatches"], "metrics": m["metrics"]["avgMetrics"],
-                   "batch_metrics": m["metrics"].get("batchMetrics"), "end_time": m["endTime"]}
+            yield TrialMetrics._from_json(m)
 
     def stream_trials_metrics(self, trial_ids: List[int], group: str) -> Iterator[Dict[str, Any]]:
         return self.iter_trials_metrics(trial_ids, group)
@@ -768,3 +849,7 @@ for _name in ("list_experiments", "list_models", "get_model_by_id", "get_model_l
               "remove_oauth_client", "list_resource_pools", "preview_search", "get_master_info"):
     globals()[_name] = _delegate(_name)
 del _name
+
+
+ExperimentReference = Experiment          # names of earlier releases of the reference SDK
+TrialReference = Trial

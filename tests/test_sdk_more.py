@@ -128,3 +128,22 @@ def test_projects_workspaces_pools_users_oauth(det):
     client._determined = d
     assert "team" in [w.name for w in client.list_workspaces()] and client.get_session_username() == "admin"
     assert client.get_user_by_name("bob").username == "bob"
+
+
+def test_reference_import_paths_and_metric_objects():
+    """``determined.common.experimental.*`` modules resolve to the SDK classes; metric reports are objects with the
+    reference's attribute names that still read like the dicts this SDK used to yield."""
+    import determined_b200
+
+    determined_b200.install_alias()
+    from determined.common.experimental import checkpoint, experiment, metrics, model, trial  # type: ignore
+    from determined.experimental import client  # type: ignore
+
+    assert checkpoint.Checkpoint is client.Checkpoint and experiment.ExperimentReference is client.Experiment and trial.TrialSortBy is client.TrialSortBy
+    assert model.ModelOrderBy is client.OrderBy and checkpoint.DownloadMode.AUTO.value == "auto"
+    m = client.TrialMetrics._from_json({"trialId": 3, "trialRunId": 1, "totalBatches": 20, "endTime": "2026-01-01T00:00:00Z", "group": "validation",
+                                        "metrics": {"avgMetrics": {"loss": 0.5}, "batchMetrics": None}})
+    assert isinstance(m, metrics.ValidationMetrics) and (m.trial_id, m.steps_completed, m.metrics) == (3, 20, {"loss": 0.5})
+    assert m["metrics"] == {"loss": 0.5} and m.get("group") == "validation" and m.get("nope", 7) == 7 and "trial_run_id" in m.keys()
+    t = client.TrialMetrics._from_json({"trialId": 3, "totalBatches": 10, "group": "training", "metrics": {"avgMetrics": {}}})
+    assert isinstance(t, metrics.TrainingMetrics) and not isinstance(t, metrics.ValidationMetrics)
