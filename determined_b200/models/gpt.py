@@ -120,6 +120,16 @@ class Block(nn.Module):
         B, S, E = x.shape
         H, D = self.cfg.n_head, self.cfg.head_dim
         qkv = self.qkv(x).view(B, S, 3, H, D)
+        if getattr(self, "cp_group", None) is not None:
+            # the sequence is sharded over the context-parallel group: K/V shards travel the ring (parallel/context_parallel.py);
+            # `rope` already holds the tables of this rank's global positions
+            from determined_b200.parallel import context_parallel as cp
+
+            q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+            if self.rot and rope is not None:
+                q, k = apply_rotary(q, rope[0], rope[1], self.rot), apply_rotary(k, rope[0], rope[1], self.rot)
+            o = cp.ring_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), self.cp_group, causal=True).transpose(1, 2)
+            return self.proj(o.reshape(B, S, E))
         if self.native:
             # rotary in place on the packed projection, attention reads the strided slices, one packed dqkv comes back
             o = attn_ops.attention_qkvpacked(qkv, (rope[2], rope[3]) if rope is not None else None, self.rot, causal=True)
@@ -185,6 +195,25 @@ class GPT(nn.Module):
         n += c.vocab_size * c.n_embd            # LM head matmul (tied or not)
         return 6.0 * n + 12.0 * c.n_layer * c.n_embd * seq * 0.5
 
+    cp_group: Any = None
+
+    def set_context_parallel(self, group: Any) -> None:
+        """Shard the sequence over ``group``: ``forward`` then takes this rank's contiguous slice of the tokens (and targets),
+        attention runs as a ring over the group, positions are the global ones.  The loss returned is the mean over the local
+        tokens; with equal shards the mean over the group's ranks is the loss of the whole sequence, and parameter gradients
+        are averaged over the group like over data-parallel replicas.  ``None`` turns it off."""
+        self.cp_group = group
+        for blk in self.blocks:
+            blk.cp_group = group
+
+    def _cp_offset(self, S: int) -> Tuple[int, int]:
+        """(first global position of the local shard, global sequence length)."""
+        if self.cp_group is None:
+            return 0, S
+        import torch.distributed as dist
+
+        return dist.get_rank(self.cp_group) * S, dist.get_world_size(self.cp_group) * S
+
     def rope(self, S: int, device: torch.device) -> Optional[Tuple[torch.Tensor, ...]]:
         rot = int(self.cfg.head_dim * self.cfg.rotary_pct) // 2 * 2
         if rot == 0:
@@ -198,13 +227,16 @@ class GPT(nn.Module):
         """Returns (logits, loss).  With ``targets`` the logits are consumed by the fused
         cross-entropy and not returned (saves a [B*S, V] round trip)."""
         B, S = idx.shape
-        if S > self.cfg.block_size:
-            raise ValueError(f"sequence length {S} exceeds block size {self.cfg.block_size}")
+        first, total = self._cp_offset(S)
+        if total > self.cfg.block_size:
+            raise ValueError(f"sequence length {total} exceeds block size {self.cfg.block_size}")
         x = self.wte(idx)
         if self.wpe is not None:
-            x = x + self.wpe(torch.arange(S, device=idx.device))[None]
+            x = x + self.wpe(torch.arange(first, first + S, device=idx.device))[None]
         x = x.to(torch.bfloat16) if (idx.is_cuda and self.native) else x
-        rope = self.rope(S, idx.device)
+        rope = self.rope(total, idx.device)
+        if rope is not None and total != S:
+            rope = tuple(t[first:first + S] for t in rope)
         for blk in self.blocks:
             x = blk(x, rope)
         x = self.ln_f(x)
