@@ -281,6 +281,49 @@ def test_the_master_answers_what_the_definition_says(recorded_cluster):
 
     b.post_ArchiveExperiment(sess, id=eid)
     b.post_UnarchiveExperiment(sess, id=eid)
+
+    # ---- the wider surface (master/api_rest.py) --------------------------------------------------------------------------------
+    assert b.post_ArchiveExperiments(sess, body=b.v1ArchiveExperimentsRequest(experimentIds=[eid, 424242])).results[1].error
+    assert b.post_UnarchiveExperiments(sess, body=b.v1UnarchiveExperimentsRequest(filters=b.v1BulkExperimentFilters(name="typed", projectId=pr.id))).results[0].id == eid
+    for fn, req in ((b.post_ActivateExperiments, b.v1ActivateExperimentsRequest), (b.post_PauseExperiments, b.v1PauseExperimentsRequest),
+                    (b.post_CancelExperiments, b.v1CancelExperimentsRequest), (b.post_KillExperiments, b.v1KillExperimentsRequest)):
+        assert fn(sess, body=req(experimentIds=[eid])).results[0].id == eid
+    assert b.post_MoveExperiments(sess, body=b.v1MoveExperimentsRequest(experimentIds=[eid], destinationProjectId=pr.id)).results[0].error == ""
+    assert b.put_PutExperimentLabel(sess, experimentId=eid, label="typed-label").labels == ["a", "typed-label"]
+    assert "typed-label" in b.get_GetExperimentLabels(sess, projectId=pr.id).labels
+    assert b.delete_DeleteExperimentLabel(sess, experimentId=eid, label="typed-label").labels == ["a"]
+    tree = b.get_GetModelDefTree(sess, experimentId=eid).files
+    assert any(f.name == "model_def.py" and not f.isDir for f in tree)
+    assert base64.b64decode(b.post_GetModelDefFile(sess, experimentId=eid, body=b.v1GetModelDefFileRequest(experimentId=eid, path="model_def.py")).file)
+    hist = b.get_GetExperimentValidationHistory(sess, experimentId=eid).validationHistory
+    assert hist and hist[0].trialId == trial.id
+    assert b.get_CurrentUser(sess).user.username == "admin" and b.get_GetUser(sess, userId=u.id).user.username == "typed-user"
+    assert b.get_GetUserByUsername(sess, username="typed-user").user.id == u.id
+    assert b.patch_PatchUsers(sess, body=b.v1PatchUsersRequest(userIds=[u.id], activate=True)).results[0].error == ""
+    g2 = b.post_CreateGroup(sess, body=b.v1CreateGroupRequest(name="typed-group-2")).group
+    b.patch_AssignMultipleGroups(sess, body=b.v1AssignMultipleGroupsRequest(userIds=[u.id], addGroups=[g2.groupId], removeGroups=[]))
+    assert b.get_GetGroup(sess, groupId=g2.groupId).group.users[0].id == u.id
+    b.post_PostUserSetting(sess, body=b.v1PostUserSettingRequest(settings=[b.v1UserWebSetting(key="k", storagePath="p", value="v")]))
+    assert b.get_GetUserSetting(sess).settings[0].value == "v"
+    b.post_ResetUserSetting(sess)
+    assert b.post_AddProjectNote(sess, projectId=pr.id, body=b.v1Note(name="n", contents="c")).notes[0].name == "n"
+    assert b.put_PutProjectNotes(sess, projectId=pr.id, body=b.v1PutProjectNotesRequest(projectId=pr.id, notes=[])).notes == []
+    assert any(c.column == "hp.learning_rate" for c in b.get_GetProjectColumns(sess, id=pr.id).columns)
+    assert any(r.metricsName == "validation.val_loss" for r in b.get_GetProjectNumericMetricsRange(sess, id=pr.id).ranges)
+    ws2 = b.post_PostWorkspace(sess, body=b.v1PostWorkspaceRequest(name="typed-ws-2")).workspace
+    pr2 = b.post_PostProject(sess, workspaceId=ws.id, body=b.v1PostProjectRequest(name="typed-proj-2", workspaceId=ws.id)).project
+    b.post_MoveProject(sess, projectId=pr2.id, body=b.v1MoveProjectRequest(projectId=pr2.id, destinationWorkspaceId=ws2.id))
+    assert b.get_GetProject(sess, id=pr2.id).project.workspaceId == ws2.id
+    b.post_PinWorkspace(sess, id=ws2.id)
+    b.post_UnpinWorkspace(sess, id=ws2.id)
+    b.post_PostModel(sess, body=b.v1PostModelRequest(name="typed-model-2", labels=["lab"]))
+    b.post_MoveModel(sess, modelName="typed-model-2", body=b.v1MoveModelRequest(modelName="typed-model-2", destinationWorkspaceId=ws2.id))
+    assert b.get_GetModel(sess, modelName="typed-model-2").model.workspaceId == ws2.id and b.get_GetModelLabels(sess, workspaceId=ws2.id).labels == ["lab"]
+    assert b.get_GetSlot(sess, agentId=agents[0].id, slotId="0").slot.id == "0"
+    assert b.get_GetTelemetry(sess).enabled is False and b.get_GetActiveTasksCount(sess).commands >= 0
+    assert b.get_GetTask(sess, taskId=trial.taskId).task.allocations and b.get_GetTask(sess, taskId=cmd.id).task.taskType == "TASK_TYPE_COMMAND"
+    assert b.get_GetJobQueueStats(sess).results[0].resourcePool == "default"
+    assert b.delete_DeleteExperiments(sess, experimentIds=[424242]).results[0].error
     b.delete_DeleteCheckpoints(sess, body=b.v1DeleteCheckpointsRequest(checkpointUuids=[cks[-1].uuid]))
     b.delete_DeleteTemplate(sess, templateName="typed-tpl")
     with pytest.raises(api.errors.NotFoundException):
@@ -317,4 +360,4 @@ def test_the_master_answers_what_the_definition_says(recorded_cluster):
     for name in ("GetCurrentTrialSearcherOperation", "CompleteTrialSearcherValidation", "ReportTrialMetrics",
                  "ReportCheckpoint", "PostTrialRunnerMetadata", "AllocationPreemptionSignal"):
         assert seen[name] > 0, f"no {name} call was recorded"
-    assert len(seen) >= 80, sorted(seen)
+    assert len(seen) >= 115, sorted(seen)
