@@ -470,7 +470,7 @@ def create_experiment(ctx: Ctx) -> Any:
         raise HTTPError(400, f"invalid experiment: {e}")
     if exp is None:
         return {"experiment": None, "config": cfg, "warnings": []}
-    row = ctx.m.db.one("SELECT * FROM experiments WHERE id=?", (exp.id,))
+    row = ctx.m.db.one("SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments WHERE id=?", (exp.id,))
     return {"experiment": exp_json(ctx.m, row), "config": cfg, "warnings": []}
 
 
@@ -484,7 +484,7 @@ def list_experiments(ctx: Ctx) -> Any:
         where.append("project_id=?")
         args.append(ctx.qi("projectId"))
     states = ctx.query.get("states") or []
-    rows = ctx.m.db.all(f"SELECT * FROM experiments WHERE {' AND '.join(where)} ORDER BY id " + ("DESC" if ctx.q("orderBy") == "ORDER_BY_DESC" else "ASC"), args)
+    rows = ctx.m.db.all(f"SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments WHERE {' AND '.join(where)} ORDER BY id " + ("DESC" if ctx.q("orderBy") == "ORDER_BY_DESC" else "ASC"), args)
     out = [exp_json(ctx.m, r) for r in rows]
     if states:
         out = [e for e in out if e["state"] in states]
@@ -498,7 +498,7 @@ def list_experiments(ctx: Ctx) -> Any:
 
 
 def _exp_row(ctx: Ctx, eid: str) -> Any:
-    row = ctx.m.db.one("SELECT * FROM experiments WHERE id=?", (int(eid),))
+    row = ctx.m.db.one("SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments WHERE id=?", (int(eid),))
     if row is None:
         raise HTTPError(404, f"experiment {eid} not found")
     return row
@@ -537,7 +537,7 @@ def continue_experiment(ctx: Ctx) -> Any:
         exp = ctx.m.continue_experiment(int(b.get("id")), b.get("overrideConfig") or None)
     except core.Conflict as e:
         raise HTTPError(409, str(e))
-    row = ctx.m.db.one("SELECT * FROM experiments WHERE id=?", (exp.id,))
+    row = ctx.m.db.one("SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments WHERE id=?", (exp.id,))
     return {"experiment": exp_json(ctx.m, row), "warnings": []}
 
 
@@ -703,7 +703,8 @@ def best_metric(ctx: Ctx, eid: str) -> Any:
 
 @route("GET", "/api/v1/experiments/{eid}/model_def")
 def model_def(ctx: Ctx, eid: str) -> Any:
-    row = _exp_row(ctx, eid)
+    _exp_row(ctx, eid)
+    row = ctx.m.db.one("SELECT model_definition FROM experiments WHERE id=?", (int(eid),))
     return {"b64Tgz": base64.b64encode(row["model_definition"] or b"").decode()}
 
 
@@ -2112,6 +2113,9 @@ def openapi_doc(ctx: Ctx) -> Any:
 
 class Handler(BaseHTTPRequestHandler):
     protocol_version = "HTTP/1.1"
+    # headers and body leave in separate writes: with Nagle's algorithm on, the second waits for the client's delayed ACK of the
+    # first (~40 ms per request on a kept-alive connection)
+    disable_nagle_algorithm = True
     master: core.Master = None  # type: ignore
 
     def log_message(self, fmt: str, *args: Any) -> None:

@@ -391,6 +391,9 @@ def allocation_aggregated(ctx: Ctx) -> Any:
     except (ValueError, TypeError):
         raise HTTPError(400, "dates must look like YYYY-MM-DD (or YYYY-MM)")
     entries = []
+    # one look at the table says where there is anything to add up: periods outside that span are written without a query
+    span = ctx.m.db.one("SELECT MIN(start_time) lo, MAX(COALESCE(end_time, ?)) hi FROM allocations WHERE start_time IS NOT NULL", (time.time(),))
+    lo, hi = (span["lo"], span["hi"]) if span is not None and span["lo"] is not None else (None, None)
     cur = d0
     while cur <= d1:
         if monthly:
@@ -399,7 +402,8 @@ def allocation_aggregated(ctx: Ctx) -> Any:
         else:
             nxt = cur + datetime.timedelta(days=1)
             label = cur.strftime("%Y-%m-%d")
-        rows = _allocation_rows(ctx, cur.timestamp(), min(nxt, d1 + datetime.timedelta(days=1)).timestamp())
+        p0, p1 = cur.timestamp(), min(nxt, d1 + datetime.timedelta(days=1)).timestamp()
+        rows = _allocation_rows(ctx, p0, p1) if lo is not None and p1 > lo and p0 < hi else []
         agg: Dict[str, Dict[str, float]] = {k: collections.defaultdict(float) for k in ("byUsername", "byExperimentLabel", "byResourcePool", "byAgentLabel")}
         total = 0.0
         for r in rows:

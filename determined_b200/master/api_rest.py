@@ -32,7 +32,7 @@ def _ids(ctx: Ctx, key: str = "experimentIds") -> List[int]:
 def _filter_experiments(ctx: Ctx, flt: Dict[str, Any]) -> List[Dict[str, Any]]:
     """``BulkExperimentFilters`` / search filters: description, name, labels, archived, states, userIds, projectId, excludedExperimentIds."""
     out = []
-    for r in ctx.m.db.all("SELECT * FROM experiments ORDER BY id"):
+    for r in ctx.m.db.all("SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments ORDER BY id"):
         e = A.exp_json(ctx.m, r)
         if flt.get("name") and str(flt["name"]).lower() not in str(e["name"] or "").lower():
             continue
@@ -516,7 +516,7 @@ def telemetry(ctx: Ctx) -> Any:
 
 # ------------------------------------------------------------------------------------------------ unmanaged experiments / trials
 def _by_external(ctx: Ctx, ext_exp: str) -> Optional[Any]:
-    for r in ctx.m.db.all("SELECT * FROM experiments WHERE unmanaged=1 ORDER BY id"):
+    for r in ctx.m.db.all("SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments WHERE unmanaged=1 ORDER BY id"):
         if (dbmod.U(r["config"], {}).get("data") or {}).get("external_experiment_id") == ext_exp:
             return r
     return None
@@ -835,7 +835,7 @@ def _searched(ctx: Ctx) -> List[Dict[str, Any]]:
     pid = ctx.qi("projectId", 0)
     flt = json.loads(ctx.q("filter")) if ctx.q("filter") else None
     out = []
-    for r in ctx.m.db.all("SELECT * FROM experiments ORDER BY id"):
+    for r in ctx.m.db.all("SELECT id, state, config, original_config, owner_id, start_time, end_time, progress, archived, parent_id, notes, project_id, unmanaged, job_id FROM experiments ORDER BY id"):
         if pid and r["project_id"] != pid:
             continue
         e = A.exp_json(ctx.m, r)

@@ -43,6 +43,8 @@ CREATE TABLE IF NOT EXISTS tasks (id TEXT PRIMARY KEY, type TEXT, start_time REA
 CREATE TABLE IF NOT EXISTS task_logs (id INTEGER PRIMARY KEY AUTOINCREMENT, task_id TEXT, allocation_id TEXT, ts REAL, level TEXT,
     rank_id INTEGER, stdtype TEXT, source TEXT, log TEXT);
 CREATE INDEX IF NOT EXISTS logs_task ON task_logs(task_id, id);
+CREATE INDEX IF NOT EXISTS alloc_task ON allocations(task_id);
+CREATE INDEX IF NOT EXISTS alloc_time ON allocations(start_time);
 CREATE TABLE IF NOT EXISTS templates (name TEXT PRIMARY KEY, config TEXT, workspace_id INTEGER DEFAULT 1);
 CREATE TABLE IF NOT EXISTS models (id INTEGER PRIMARY KEY AUTOINCREMENT, name TEXT UNIQUE, description TEXT, metadata TEXT DEFAULT '{}',
     labels TEXT DEFAULT '[]', user_id INTEGER, creation_time REAL, last_updated_time REAL, archived INTEGER DEFAULT 0, workspace_id INTEGER DEFAULT 1, notes TEXT DEFAULT '');
