@@ -76,6 +76,7 @@ class Ctx:
     def __init__(self, master: core.Master, user: Optional[Dict[str, Any]], query: Dict[str, List[str]], body: Any,
                  raw: bytes) -> None:
         self.m, self.user, self.query, self.body, self.raw = master, user, query, body, raw
+        self.headers: Any = {}
 
     def q(self, name: str, default: Any = None) -> Any:
         v = self.query.get(name)
@@ -2182,12 +2183,20 @@ class Handler(BaseHTTPRequestHandler):
                 self._send(401, {"error": {"code": 16, "message": "unauthenticated"}, "message": "unauthenticated"})
                 return
             ctx = Ctx(self.master, user, urllib.parse.parse_qs(u.query), body, raw)
+            ctx.headers = self.headers
             try:
                 with tracing.span(f"{method} {rx.pattern[1:-3]}", traceparent=self.headers.get("traceparent"), **{"http.method": method, "http.target": path}):
                     out = fn(ctx, **{k: urllib.parse.unquote(v) for k, v in mt.groupdict().items()})
                 if RECORDER is not None:
                     RECORDER(method, rx.pattern[1:-3], body, out)
-                if isinstance(out, tuple):
+                if isinstance(out, tuple) and isinstance(out[0], int):          # (status, JSON payload or None)
+                    if out[1] is None:
+                        self.send_response(out[0])
+                        self.send_header("Content-Length", "0")
+                        self.end_headers()
+                    else:
+                        self._send(out[0], out[1])
+                elif isinstance(out, tuple):                                     # (content type, payload)
                     self._send(200, out[1], out[0])
                 else:
                     self._send(200, out)
@@ -2197,7 +2206,7 @@ class Handler(BaseHTTPRequestHandler):
                 self.send_header("Content-Length", "0")
                 self.end_headers()
             except HTTPError as e:
-                self._send(e.status, {"error": {"code": e.status, "message": e.message}, "message": e.message})
+                self._send(e.status, getattr(e, "body", None) or {"error": {"code": e.status, "message": e.message}, "message": e.message})
             except core.NotFound as e:
                 self._send(404, {"error": {"code": 5, "message": str(e)}, "message": str(e)})
             except expconf.ConfigError as e:
@@ -2369,3 +2378,4 @@ class APIServer:
 from determined_b200.master import api_more  # noqa: E402,F401  (registers its routes)
 from determined_b200.master import api_rest  # noqa: E402,F401  (the rest of the REST surface)
 from determined_b200.master import sso  # noqa: E402,F401  (/oidc/sso, /oidc/callback)
+from determined_b200.master import scim  # noqa: E402,F401  (/scim/v2/*, /oauth2/token)

@@ -85,6 +85,11 @@ SCHEMA: Dict[str, Any] = {
             "userinfo_url": {"type": ["string", "null"], "default": None}, "idp_recipient_url": {"type": ["string", "null"], "default": None},
             "authentication_claim": {"type": "string", "default": "email"}, "scope": {"type": "string", "default": "openid profile email"},
             "auto_provision_users": {"type": "boolean", "default": False}, "always_redirect": {"type": "boolean", "default": False}}},
+        "scim": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
+            "enabled": {"type": "boolean", "default": False},
+            "auth": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
+                "type": {"enum": ["basic", "oauth"], "default": "basic"},
+                "username": {"type": ["string", "null"], "default": None}, "password": {"type": ["string", "null"], "default": None}}}}},
         "logging": {"type": "object", "additionalProperties": False, "default": {}, "properties": {
             "type": {"enum": ["default", "elastic"], "default": "default", "description": "where task logs live: the master's database, or Elasticsearch"},
             "host": {"type": ["string", "null"], "default": None}, "port": {"type": "integer", "default": 9200},
@@ -110,7 +115,7 @@ SCHEMA: Dict[str, Any] = {
 }
 REGISTRY = {SCHEMA["$id"]: SCHEMA}
 
-SECRET_KEYS = ("logging.security.password", "oidc.client_secret", "telemetry.segment_master_key", "security.agent_token", "security.initial_user_password", "security.tls.key", "webhooks.signing_key",
+SECRET_KEYS = ("scim.auth.password", "logging.security.password", "oidc.client_secret", "telemetry.segment_master_key", "security.agent_token", "security.initial_user_password", "security.tls.key", "webhooks.signing_key",
                "checkpoint_storage.secret_key", "checkpoint_storage.access_key", "checkpoint_storage.connection_string",
                "checkpoint_storage.credentials")
 

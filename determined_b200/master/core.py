@@ -672,6 +672,10 @@ class Master:
             if missing:
                 raise ValueError("oidc.enabled needs: " + ", ".join("oidc." + k for k in missing))
         self.oidc = oidc
+        sc = dict(cfg.data.get("scim") or {})
+        if sc.get("enabled") and (sc.get("auth") or {}).get("type", "basic") == "basic" and not (sc.get("auth") or {}).get("password"):
+            raise ValueError("scim.enabled with basic auth needs scim.auth.username and scim.auth.password")
+        self.scim = sc
 
     log_retention_days = -1
     _last_retention_sweep = 0.0
