@@ -1,7 +1,7 @@
 # Developer entry points (reference: top-level Makefile + tools/devcluster + .circleci).
 PY ?= python
 
-.PHONY: build test test-gpu bench bindings check tsan devcluster clean
+.PHONY: build test test-gpu bench bindings check tsan asan devcluster clean
 
 build:            ## compile the native library for sm_100a (nvcc cross-compiles without a GPU)
 	$(PY) -c "import __graft_entry__ as g; g.build()"
@@ -27,6 +27,9 @@ check: bindings   ## what CI runs before the tests
 tsan:             ## race check of the C++ host runtime (shared-memory collectives) under ThreadSanitizer
 	g++ -std=c++17 -O1 -g -fsanitize=thread -pthread csrc/host/shm_collective.cpp csrc/host/shm_collective_test.cpp -lrt -o /tmp/detb200_shm_tsan
 	TSAN_OPTIONS=exitcode=66 /tmp/detb200_shm_tsan 4 500
+
+asan:             ## the C++ launcher under AddressSanitizer + UBSan (rank contract and kill-a-rank)
+	$(PY) -m pytest tests/test_launch.py -q -k sanitizers
 
 devcluster:       ## a master without own slots plus one agent, in the foreground of two background daemons
 	$(PY) -m determined_b200.cli deploy local master-up --slots 0
