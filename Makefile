@@ -22,6 +22,7 @@ check: bindings   ## what CI runs before the tests
 	git diff --exit-code determined_b200/common/api/bindings.py
 	$(PY) scripts/cli_gaps.py --check
 	$(PY) scripts/lint_names.py
+	$(PY) scripts/gen_docs.py --check
 	$(PY) -m compileall -q determined_b200 tests benchmarks examples bench.py __graft_entry__.py
 
 tsan:             ## race check of the C++ host runtime (shared-memory collectives) under ThreadSanitizer

@@ -60,3 +60,11 @@ def test_helm_chart_renders_to_manifests_the_programs_accept(tmp_path):
             assert flag in help_text, f"{module} has no {flag}"
     svc = next(d for d in docs if d["kind"] == "Service")
     assert svc["spec"]["ports"][0]["port"] == 8080
+
+
+def test_generated_reference_pages_are_fresh():
+    """docs/reference/*.md are generated from the parser, the proto files and the two config schemas."""
+    r = subprocess.run([sys.executable, str(ROOT / "scripts" / "gen_docs.py"), "--check"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=ROOT, timeout=300)
+    assert r.returncode == 0, r.stdout
+    r = subprocess.run([sys.executable, str(ROOT / "scripts" / "lint_names.py")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=ROOT, timeout=300)
+    assert r.returncode == 0, r.stdout
