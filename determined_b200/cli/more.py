@@ -523,6 +523,24 @@ def task_fork(args: argparse.Namespace) -> int:
     return _follow_task(sess, r["taskId"]) if args.follow else 0
 
 
+def task_forward(args: argparse.Namespace) -> int:
+    """``det task forward TASK_ID LOCAL[:REMOTE]``: connections to the local port reach the task's service port (or a port it
+    declared in ``proxy_ports``) through the master; runs until interrupted."""
+    from determined_b200.cli import proxy
+
+    local, _, remote = str(args.ports).partition(":")
+    sess = _cli()._session(args)
+    cfg = proxy.ListenerConfig(args.task_id, int(local), remote_port=int(remote) if remote else None)
+    with proxy.http_tunnel_listener(sess, [cfg]) as ports:
+        print(f"forwarding 127.0.0.1:{ports[0]} to task {args.task_id}" + (f" port {remote}" if remote else ""), flush=True)
+        try:
+            while getattr(args, "_once", None) is None:
+                time.sleep(1)
+        except KeyboardInterrupt:
+            pass
+    return 0
+
+
 def task_pause(flag: bool) -> Callable[[argparse.Namespace], int]:
     def fn(args: argparse.Namespace) -> int:
         _cli()._session(args).post(f"/api/v1/tasks/{args.task_id}/{'pause' if flag else 'unpause'}")
@@ -867,6 +885,9 @@ def extend(parser: argparse.ArgumentParser) -> None:
     a.add_argument("--parent", help="parent task")
     a.add_argument("--inherit_context", "--inherit-context", action="store_true")
     a.add_argument("--no_pause", "--no-pause", action="store_true")
+    a = _cmd(tk, "forward", task_forward, "forward a local port to a port of a running task, through the master")
+    a.add_argument("task_id")
+    a.add_argument("ports", metavar="LOCAL[:REMOTE]")
     a = _cmd(tk, "fork", task_fork, "run a task again, with its configuration and context")
     a.add_argument("parent_task_id")
     a.add_argument("-f", "--follow", action="store_true")

@@ -2164,6 +2164,9 @@ class Handler(BaseHTTPRequestHandler):
         if path.startswith("/proxy/"):
             self._proxy(method, path, u.query, raw)
             return
+        if method == "GET" and path.startswith("/tunnel/"):
+            self._tunnel(path)
+            return
         if method == "GET" and path.rstrip("/") == "/stream":
             from determined_b200.common import websocket
 
@@ -2267,6 +2270,86 @@ class Handler(BaseHTTPRequestHandler):
         except (BrokenPipeError, ConnectionResetError):
             pass
         conn.close()
+
+    def _tunnel(self, path: str) -> None:
+        """``GET /tunnel/<task id>[/<port>]`` with ``Upgrade: websocket``: the binary frames of the websocket are the bytes of one
+        TCP connection to the task's service port, or to a port it declared in ``proxy_ports`` (reference ``master/internal/proxy``
+        TCP proxying behind ``python -m determined.cli.tunnel``)."""
+        import socket as _socket
+        import threading as _threading
+
+        from determined_b200.common import websocket
+
+        parts = path.strip("/").split("/")
+        task_id = parts[1] if len(parts) > 1 else ""
+        if self._user() is None:
+            self._send(401, {"message": "unauthenticated"})
+            return
+        if not websocket.is_upgrade(self.headers):
+            self._send(400, {"message": "the tunnel is a websocket: send an Upgrade request"})
+            return
+        t = self.master.commands.tasks.get(task_id)
+        if t is None or t.state != "RUNNING":
+            self._send(404, {"message": f"task {task_id} is not running"})
+            return
+        allowed = {int(t.service_port)} if t.service_port else set()
+        for pp in (t.config.get("proxy_ports") or []) if isinstance(t.config.get("proxy_ports"), list) else []:
+            if isinstance(pp, dict) and pp.get("proxy_port"):
+                allowed.add(int(pp["proxy_port"]))
+        port = int(parts[2]) if len(parts) > 2 and parts[2].isdigit() else (int(t.service_port) if t.service_port else 0)
+        if not port or port not in allowed:
+            self._send(403, {"message": f"task {task_id} exposes no port {port or ''}: declare it in proxy_ports".replace("  ", " ")})
+            return
+        try:
+            back = _socket.create_connection((t.service_host, port), timeout=15)
+        except OSError as e:
+            self._send(502, {"message": f"port {port} of task {task_id} is not answering: {e}"})
+            return
+        back.setsockopt(_socket.IPPROTO_TCP, _socket.TCP_NODELAY, 1)
+        ws = websocket.server_handshake(self)
+        wlock = _threading.Lock()
+        done = _threading.Event()
+
+        def down() -> None:                      # task -> client
+            try:
+                while not done.is_set():
+                    data = back.recv(65536)
+                    if not data:
+                        break
+                    with wlock:
+                        ws.send_binary(data)
+                    t.last_activity = time.time()
+            except (OSError, websocket.WebSocketError):
+                pass
+            finally:
+                done.set()
+
+        th = _threading.Thread(target=down, daemon=True, name=f"tunnel-{task_id[:8]}")
+        th.start()
+        try:
+            while not done.is_set() and not self.master._stop.is_set():
+                try:
+                    _, data = ws.recv(timeout=1.0)
+                except (_socket.timeout, TimeoutError):
+                    continue
+                if data:
+                    back.sendall(data)
+                    t.last_activity = time.time()
+        except (websocket.WebSocketError, OSError):
+            pass
+        finally:
+            done.set()
+            for c in (back,):
+                try:
+                    c.shutdown(_socket.SHUT_RDWR)
+                except OSError:
+                    pass
+                c.close()
+            try:
+                with wlock:
+                    ws.close()
+            except Exception:  # noqa: BLE001
+                pass
 
     def _proxy_tunnel(self, t: Any, method: str, target: str, task_id: str) -> None:
         """An upgraded connection (a websocket of a notebook kernel, of tensorboard's live reload): replay the request to
