@@ -207,7 +207,7 @@ def master_info(ctx: Ctx) -> Any:
 
     tel = getattr(ctx.m, "telemetry", None)
     return {"version": __version__, "masterId": ctx.m.cluster_id, "clusterId": ctx.m.cluster_id, "clusterName": ctx.m.cluster_name,
-            "telemetryEnabled": bool(tel and tel.enabled), "ssoProviders": sso.providers(ctx.m), "externalLoginUri": "", "rbacEnabled": False, "branding": "determined_b200",
+            "telemetryEnabled": bool(tel and tel.enabled), "ssoProviders": sso.providers(ctx.m), "externalLoginUri": "", "rbacEnabled": authz.enabled(ctx.m), "branding": "determined_b200",
             "strictJobQueueControl": False, "userManagementEnabled": True, "product": "PRODUCT_COMMUNITY"}
 
 
@@ -373,7 +373,7 @@ def list_roles(ctx: Ctx) -> Any:
 
 @route("POST", "/api/v1/roles/add-assignments")
 def assign_roles(ctx: Ctx) -> Any:
-    if not ctx.user["admin"]:
+    if not authz.can_assign_roles(ctx.m, ctx.user, ctx.body):
         raise HTTPError(403, "admin only")
     b = ctx.body or {}
     names = {r["roleId"]: r["name"] for r in ROLES}
@@ -390,7 +390,7 @@ def assign_roles(ctx: Ctx) -> Any:
 
 @route("POST", "/api/v1/roles/remove-assignments")
 def remove_roles(ctx: Ctx) -> Any:
-    if not ctx.user["admin"]:
+    if not authz.can_assign_roles(ctx.m, ctx.user, ctx.body):
         raise HTTPError(403, "admin only")
     b = ctx.body or {}
     names = {r["roleId"]: r["name"] for r in ROLES}
@@ -1612,6 +1612,16 @@ def create_model(ctx: Ctx) -> Any:
                             (b.get("name"), b.get("description", ""), dbmod.J(b.get("metadata") or {}), dbmod.J(b.get("labels") or []), ctx.user["id"], time.time(), time.time(), b.get("notes", "")))
     except Exception as e:
         raise HTTPError(409, f"cannot create model: {e}")
+    wid = b.get("workspaceId")
+    if not wid and b.get("workspaceName"):
+        w = ctx.m.db.one("SELECT id FROM workspaces WHERE name=?", (b["workspaceName"],))
+        if w is None:
+            raise HTTPError(404, f"workspace {b['workspaceName']!r} not found")
+        wid = w["id"]
+    if wid:
+        if ctx.m.db.one("SELECT id FROM workspaces WHERE id=?", (int(wid),)) is None:
+            raise HTTPError(404, f"workspace {wid} not found")
+        ctx.m.db.exec("UPDATE models SET workspace_id=? WHERE id=?", (int(wid), mid))
     return {"model": _model_json(ctx.m, ctx.m.db.one("SELECT * FROM models WHERE id=?", (mid,)))}
 
 
@@ -2127,10 +2137,10 @@ class Handler(BaseHTTPRequestHandler):
         tok = h[7:] if h.startswith("Bearer ") else None
         if not tok:
             return None
-        r = self.master.db.one("SELECT s.token, s.expiry, u.* FROM sessions s JOIN users u ON u.id=s.user_id WHERE s.token=?", (tok,))
+        r = self.master.db.one("SELECT s.token, s.expiry, s.task_id session_task, u.* FROM sessions s JOIN users u ON u.id=s.user_id WHERE s.token=?", (tok,))
         if r is None or (r["expiry"] or 0) < time.time() or not r["active"]:
             return None
-        return {"id": r["id"], "username": r["username"], "admin": bool(r["admin"]), "token": tok}
+        return {"id": r["id"], "username": r["username"], "admin": bool(r["admin"]), "token": tok, "task_id": r["session_task"]}
 
     def _send(self, status: int, payload: Any, ctype: str = "application/json") -> None:
         if isinstance(payload, (dict, list)) or payload is None:
@@ -2187,11 +2197,18 @@ class Handler(BaseHTTPRequestHandler):
                 return
             ctx = Ctx(self.master, user, urllib.parse.parse_qs(u.query), body, raw)
             ctx.headers = self.headers
+            if need_auth and user is not None and authz.enabled(self.master):
+                denied = authz.check(self.master, user, method, path, body)
+                if denied:
+                    self._send(403, {"error": {"code": 7, "message": denied}, "message": denied})
+                    return
             try:
                 with tracing.span(f"{method} {rx.pattern[1:-3]}", traceparent=self.headers.get("traceparent"), **{"http.method": method, "http.target": path}):
                     out = fn(ctx, **{k: urllib.parse.unquote(v) for k, v in mt.groupdict().items()})
                 if RECORDER is not None:
                     RECORDER(method, rx.pattern[1:-3], body, out)
+                if need_auth and user is not None:
+                    out = authz.filter_listing(self.master, user, method, path, out)
                 if isinstance(out, tuple) and isinstance(out[0], int):          # (status, JSON payload or None)
                     if out[1] is None:
                         self.send_response(out[0])
@@ -2458,6 +2475,7 @@ class APIServer:
         self.httpd.server_close()
 
 
+from determined_b200.master import authz  # noqa: E402
 from determined_b200.master import api_more  # noqa: E402,F401  (registers its routes)
 from determined_b200.master import api_rest  # noqa: E402,F401  (the rest of the REST surface)
 from determined_b200.master import sso  # noqa: E402,F401  (/oidc/sso, /oidc/callback)
