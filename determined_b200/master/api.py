@@ -208,7 +208,7 @@ def master_info(ctx: Ctx) -> Any:
     tel = getattr(ctx.m, "telemetry", None)
     return {"version": __version__, "masterId": ctx.m.cluster_id, "clusterId": ctx.m.cluster_id, "clusterName": ctx.m.cluster_name,
             "telemetryEnabled": bool(tel and tel.enabled), "ssoProviders": sso.providers(ctx.m), "externalLoginUri": "", "rbacEnabled": authz.enabled(ctx.m), "branding": "determined_b200",
-            "strictJobQueueControl": False, "userManagementEnabled": True, "product": "PRODUCT_COMMUNITY"}
+            "strictJobQueueControl": bool(getattr(ctx.m, "strict_job_queue_control", False)), "userManagementEnabled": True, "product": "PRODUCT_COMMUNITY"}
 
 
 @route("GET", "/api/v1/master/config")
@@ -1472,6 +1472,11 @@ def job_queue(ctx: Ctx) -> Any:
 
 @route("POST", "/api/v1/job-queues")
 def update_job_queue(ctx: Ctx) -> Any:
+    # security.authz.strict_job_queue_control: only administrators (or, under rbac, holders of control_strict_job_queue) reorder jobs
+    # or change their priority / weight; otherwise owners may tune their own jobs like any other field of their experiments
+    if getattr(ctx.m, "strict_job_queue_control", False) and not (
+            ctx.user["admin"] or authz.allowed(ctx.m, ctx.user, "PERMISSION_TYPE_CONTROL_STRICT_JOB_QUEUE", None) and authz.enabled(ctx.m)):
+        raise HTTPError(403, "the job queue is under strict control: only administrators change priorities, weights and positions")
     with ctx.m.lock:
         for u in (ctx.body or {}).get("updates", []):
             jid = u.get("jobId")

@@ -638,6 +638,7 @@ class Master:
         self.cluster_name = cfg["cluster_name"]
         self.agent_token = cfg["security.agent_token"]
         self.tls_cert_name = cfg["security.tls.name"]
+        self.strict_job_queue_control = bool(cfg["security.authz.strict_job_queue_control"])
         self.authz_type = cfg["security.authz.type"]            # "basic", or "rbac": master/authz.py restricts requests by role
         pw = cfg["security.initial_user_password"]
         if pw:

@@ -118,3 +118,17 @@ def test_roles_decide_under_rbac(cluster):
     harness = api.Session(m.url, "nobody", "task-token")
     assert harness.get(f"/api/v1/experiments/{eb}").json()["experiment"]["id"] == eb
     assert s["nobody"].get("/api/v1/permissions/summary").status_code == 200
+
+
+def test_strict_job_queue_control_reserves_the_queue_for_administrators(cluster):
+    m, admin = cluster
+    admin.post("/api/v1/users", json={"user": {"username": "u"}})
+    u = api.authentication.login(m.url, "u", "")
+    eid = _create(u, 1)
+    assert u.post("/api/v1/job-queues", json={"updates": [{"jobId": f"exp-{eid}", "priority": 10}]}).status_code == 200
+    m.apply_config(mconfig.load(None, {}, {"security.authz.strict_job_queue_control": True}))
+    assert admin.get("/api/v1/master").json()["strictJobQueueControl"] is True
+    with pytest.raises(api.errors.APIException) as e:
+        u.post("/api/v1/job-queues", json={"updates": [{"jobId": f"exp-{eid}", "priority": 1}]})
+    assert e.value.status_code == 403
+    assert admin.post("/api/v1/job-queues", json={"updates": [{"jobId": f"exp-{eid}", "priority": 1}]}).status_code == 200
