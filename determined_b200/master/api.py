@@ -32,6 +32,7 @@ from determined_b200.master import core, db as dbmod, expconf
 from determined_b200.master import searcher as S
 
 logger = logging.getLogger("determined.master.api")
+audit_logger = logging.getLogger("determined.master.audit")
 
 
 class HTTPError(Exception):
@@ -2142,6 +2143,14 @@ class Handler(BaseHTTPRequestHandler):
         tok = h[7:] if h.startswith("Bearer ") else None
         if not tok:
             return None
+        seen = getattr(self, "_user_seen", None)
+        if seen is not None and seen[0] == tok:          # asked more than once per request (dispatch, rbac, audit)
+            return seen[1]
+        out = self._lookup_user(tok)
+        self._user_seen = (tok, out)
+        return out
+
+    def _lookup_user(self, tok: str) -> Optional[Dict[str, Any]]:
         r = self.master.db.one("SELECT s.token, s.expiry, s.task_id session_task, u.* FROM sessions s JOIN users u ON u.id=s.user_id WHERE s.token=?", (tok,))
         if r is None or (r["expiry"] or 0) < time.time() or not r["active"]:
             return None
@@ -2417,20 +2426,43 @@ class Handler(BaseHTTPRequestHandler):
         finally:
             back.close()
 
+    def send_response(self, code: int, message: Optional[str] = None) -> None:
+        self._status = code
+        super().send_response(code, message)
+
+    def _audited(self, method: str) -> None:
+        """Every API request leaves an audit line (reference ``master/internal/audit.go``): who, from where, what, with which
+        outcome — at INFO for writes and failures, at DEBUG for reads; static pages and proxied task traffic are left out."""
+        self._status = 0
+        self._user_seen = None
+        try:
+            self._dispatch(method)
+        finally:
+            path = self.path.split("?", 1)[0]
+            if path.startswith(("/api/", "/oauth2/", "/scim/", "/oidc/", "/stream", "/tunnel/")) and not path.startswith("/api/v1/agents/"):
+                try:
+                    u = self._user()
+                except Exception:  # noqa: BLE001
+                    u = None
+                status = getattr(self, "_status", 0)
+                audit_logger.log(logging.INFO if method != "GET" or status >= 400 else logging.DEBUG,
+                                 "audit: user=%s remote_ip=%s method=%s path=%s status=%s unauthorized=%s", (u or {}).get("username"),
+                                 self.client_address[0], method, path, status, status in (401, 403))
+
     def do_GET(self) -> None:
-        self._dispatch("GET")
+        self._audited("GET")
 
     def do_POST(self) -> None:
-        self._dispatch("POST")
+        self._audited("POST")
 
     def do_PATCH(self) -> None:
-        self._dispatch("PATCH")
+        self._audited("PATCH")
 
     def do_PUT(self) -> None:
-        self._dispatch("PUT")
+        self._audited("PUT")
 
     def do_DELETE(self) -> None:
-        self._dispatch("DELETE")
+        self._audited("DELETE")
 
 
 class _QuietServer(ThreadingHTTPServer):

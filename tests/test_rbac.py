@@ -132,3 +132,26 @@ def test_strict_job_queue_control_reserves_the_queue_for_administrators(cluster)
         u.post("/api/v1/job-queues", json={"updates": [{"jobId": f"exp-{eid}", "priority": 1}]})
     assert e.value.status_code == 403
     assert admin.post("/api/v1/job-queues", json={"updates": [{"jobId": f"exp-{eid}", "priority": 1}]}).status_code == 200
+
+
+def test_api_requests_leave_audit_lines(cluster, caplog):
+    import logging
+
+    m, admin = cluster
+    with caplog.at_level(logging.DEBUG, logger="determined.master.audit"):
+        admin.post("/api/v1/workspaces", json={"name": "audited"})
+        admin.get("/api/v1/workspaces")
+        with pytest.raises(api.errors.APIException):
+            api.Session(m.url, "x", "bad-token").get("/api/v1/me")
+    import time
+
+    for _ in range(40):           # the line is written after the answer has left: give the server thread a moment
+        lines = [(r.levelname, r.getMessage()) for r in caplog.records if r.name == "determined.master.audit"]
+        if sum("status=401" in msg for _, msg in lines):
+            break
+        time.sleep(0.05)
+    assert ("INFO", "audit: user=admin remote_ip=127.0.0.1 method=POST path=/api/v1/workspaces status=200 unauthorized=False") in lines
+    assert ("DEBUG", "audit: user=admin remote_ip=127.0.0.1 method=GET path=/api/v1/workspaces status=200 unauthorized=False") in lines
+    assert ("INFO", "audit: user=None remote_ip=127.0.0.1 method=GET path=/api/v1/me status=401 unauthorized=True") in lines
+    # and they are part of what `det master logs` shows
+    assert any("audit: user=admin" in e["message"] and "POST" in e["message"] for e in admin.get("/api/v1/master/logs", params={"limit": 1000}).json()["logs"])
