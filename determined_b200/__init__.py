@@ -18,6 +18,24 @@ from determined_b200 import constants, errors, util, gpu, core
 LOG_FORMAT = "%(levelname)s: [%(process)s] %(name)s: %(message)s"
 
 
+# reference module path (below ``determined.``) -> the module here that defines the same public names
+_REFERENCE_MODULE_PATHS = {
+    "common.storage.s3": "common.storage.cloud", "common.storage.gcs": "common.storage.cloud", "common.storage.azure": "common.storage.cloud",
+    "common.storage.azure_client": "common.storage.cloud", "common.storage.boto3_credential_manager": "common.storage.cloud",
+    "common.storage._util": "common.storage.base",
+    "tensorboard.base": "tensorboard", "tensorboard.build": "tensorboard", "tensorboard.shared": "tensorboard", "tensorboard.directory": "tensorboard",
+    "tensorboard.s3": "tensorboard", "tensorboard.gcs": "tensorboard", "tensorboard.azure": "tensorboard",
+    "tensorboard.fetchers.s3": "tensorboard.fetchers.cloud", "tensorboard.fetchers.gcs": "tensorboard.fetchers.cloud",
+    "tensorboard.fetchers.azure": "tensorboard.fetchers.cloud", "tensorboard.fetchers.directory": "tensorboard.fetchers.shared",
+    "tensorboard.metric_writers.pytorch": "tensorboard.metric_writers", "tensorboard.metric_writers.callback": "tensorboard.metric_writers",
+    "searcher._search_method": "searcher", "searcher._search_runner": "searcher", "searcher._remote_search_runner": "searcher",
+    "common.constants": "constants", "common.experimental.checkpoint._checkpoint": "common.experimental.checkpoint",
+    "common.api._util": "common.api", "common.api.metric": "common.api", "common.api._rbac": "common.api", "common.api.analytics": "common.api",
+    "common.v1file_utils": "common.context", "common.detignore": "common.context",
+    "_env_context": "_trial_context", "_trial": "_trial_context", "experimental._native": "experimental",
+}
+
+
 def install_alias(name: str = "determined") -> None:
     """Make ``import determined`` (and submodules) resolve to this package, and ``import model_hub`` to ``model_hub`` here."""
     import importlib
@@ -35,7 +53,14 @@ def install_alias(name: str = "determined") -> None:
             try:
                 mod = importlib.import_module(real)
             except ImportError:
-                return None
+                # a module path of the reference whose contents live in another module here
+                moved = _REFERENCE_MODULE_PATHS.get(fullname[len(name) + 1:]) if name == "determined" else None
+                if moved is None:
+                    return None
+                try:
+                    mod = importlib.import_module("determined_b200." + moved if moved else "determined_b200")
+                except ImportError:
+                    return None
             # Do NOT put the module into sys.modules here: importlib's _find_spec would then take the module's own spec (real name,
             # source loader) instead of ours and execute the package a second time under its real name -> duplicate classes.
             # _load_unlocked registers sys.modules[fullname] itself, with the object create_module hands back.

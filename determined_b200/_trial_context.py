@@ -141,3 +141,6 @@ class TrialController(metaclass=abc.ABCMeta):
 
     def close(self) -> None:
         pass
+
+
+Trial = LegacyTrial          # the reference's name for the base class of trial definitions (determined._trial.Trial)

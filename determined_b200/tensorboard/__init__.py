@@ -190,3 +190,6 @@ def get_metric_writer() -> Any:
     # the directory the TensorboardManager built with the default configuration watches and syncs (reference
     # ``tensorboard/__init__.py:get_metric_writer`` -> ``get_base_path({})``)
     return BatchMetricWriter.try_build(get_base_path({}))
+
+
+from determined_b200.tensorboard.metric_writers import BatchMetricWriter, MetricWriter  # noqa: E402,F401

@@ -9,6 +9,19 @@ from determined_b200 import util
 logger = logging.getLogger("determined.tensorboard")
 
 
+class MetricWriter:
+    """What a scalar writer offers (reference ``tensorboard/base.py`` ``MetricWriter``)."""
+
+    def add_scalar(self, name: str, value: Any, step: int) -> None:
+        raise NotImplementedError
+
+    def reset(self) -> None:
+        raise NotImplementedError
+
+    def flush(self) -> None:
+        pass
+
+
 class _NullWriter:
     def add_scalar(self, *a: Any, **k: Any) -> None:
         pass

@@ -147,3 +147,70 @@ def test_reference_import_paths_and_metric_objects():
     assert m["metrics"] == {"loss": 0.5} and m.get("group") == "validation" and m.get("nope", 7) == 7 and "trial_run_id" in m.keys()
     t = client.TrialMetrics._from_json({"trialId": 3, "totalBatches": 10, "group": "training", "metrics": {"avgMetrics": {}}})
     assert isinstance(t, metrics.TrainingMetrics) and not isinstance(t, metrics.ValidationMetrics)
+
+
+def test_module_paths_of_the_reference_resolve_under_the_alias(tmp_path, monkeypatch):
+    """Code written for the reference imports from its module layout (``determined.common.storage.s3``,
+    ``determined.tensorboard.metric_writers.pytorch`` ...): those paths resolve to the modules that hold the names here."""
+    import importlib
+    import pathlib
+
+    import determined_b200
+
+    determined_b200.install_alias()
+    ref = pathlib.Path("/root/reference/harness/determined")
+    if not ref.is_dir():
+        pytest.skip("reference tree not present")
+    missing = []
+    for f in sorted(ref.rglob("*.py")):
+        mod = ".".join(f.relative_to(ref).with_suffix("").parts)
+        mod = mod[:-len(".__init__")] if mod.endswith(".__init__") else mod
+        if mod == "__init__" or mod.startswith(("keras", "deploy", "cli.")) or "tensorflow" in mod:
+            continue
+        try:
+            importlib.import_module("determined." + mod)
+        except ImportError:
+            missing.append(mod)
+    # private plumbing of the reference's own client stack (its logging setup, its websocket and requests wrappers, the Horovod shim)
+    assert set(missing) <= {"common._logging", "common.detlomond", "common.requests", "horovod"}, missing
+    from determined.common.storage.s3 import S3StorageManager  # type: ignore  # noqa: F401
+    from determined.searcher._search_method import SearchMethod  # type: ignore  # noqa: F401
+    from determined.tensorboard.metric_writers.pytorch import TorchWriter  # type: ignore
+
+    monkeypatch.chdir(tmp_path)
+    w = TorchWriter()
+    w.add_scalar("x", 1.0, 1)
+    w.reset()
+    from determined_b200 import tensorboard as det_tb
+
+    assert any(p.name.startswith("events.out.tfevents") for p in det_tb.get_base_path({}).rglob("*")), "written where the sync thread looks"
+
+
+def test_api_logs_module_reads_and_filters(tmp_path):
+    import time
+
+    from determined_b200.common import api
+    from determined_b200.common.api import bindings, logs
+    from determined_b200.master import api as mapi
+    from determined_b200.master import core
+
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=0, work_dir=str(tmp_path / "w"))
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    try:
+        sess = api.authentication.login(m.url, "admin", "")
+        now = time.time()
+        m.db.add_logs([("task-x", "task-x.1", now - 10 + i, "ERROR" if i == 2 else "INFO", i % 2, "stdout", "task", f"l{i}\n") for i in range(5)])
+        got = list(logs.task_logs(sess, "task-x"))
+        assert [e.log for e in got] == [f"l{i}\n" for i in range(5)] and isinstance(got[0], bindings.v1LogEntry)
+        assert [e.log for e in logs.task_logs(sess, "task-x", tail=2)] == ["l3\n", "l4\n"]
+        assert [e.log for e in logs.task_logs(sess, "task-x", head=2)] == ["l0\n", "l1\n"]
+        assert [e.log for e in logs.task_logs(sess, "task-x", min_level=bindings.v1LogLevel.ERROR)] == ["l2\n"]
+        assert [e.log for e in logs.task_logs(sess, "task-x", rank_ids=[1])] == ["l1\n", "l3\n"]
+        assert [e.log for e in logs.task_logs(sess, "task-x", timestamp_after=now - 7.5)] == ["l3\n", "l4\n"]
+        with pytest.raises(ValueError):
+            list(logs.task_logs(sess, "task-x", timestamp_before="2021-10-26 23:17:12Z"))
+        assert list(logs.task_logs(sess, "task-x", follow=True))[-1].log == "l4\n", "follow ends when the task is not running"
+    finally:
+        m.stop()
+        srv.stop()
