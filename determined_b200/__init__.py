@@ -18,12 +18,14 @@ from determined_b200 import constants, errors, util, gpu, core
 LOG_FORMAT = "%(levelname)s: [%(process)s] %(name)s: %(message)s"
 
 
-# reference module path (below ``determined.``) -> the module here that defines the same public names
+# reference module path (below ``determined.``) -> the module here that defines the same public names.  A path whose last
+# component is also a function of its parent here (``tensorboard.build``) cannot be mapped: importing a submodule rebinds
+# that attribute of the parent to the module.
 _REFERENCE_MODULE_PATHS = {
     "common.storage.s3": "common.storage.cloud", "common.storage.gcs": "common.storage.cloud", "common.storage.azure": "common.storage.cloud",
     "common.storage.azure_client": "common.storage.cloud", "common.storage.boto3_credential_manager": "common.storage.cloud",
     "common.storage._util": "common.storage.base",
-    "tensorboard.base": "tensorboard", "tensorboard.build": "tensorboard", "tensorboard.shared": "tensorboard", "tensorboard.directory": "tensorboard",
+    "tensorboard.base": "tensorboard", "tensorboard.shared": "tensorboard", "tensorboard.directory": "tensorboard",
     "tensorboard.s3": "tensorboard", "tensorboard.gcs": "tensorboard", "tensorboard.azure": "tensorboard",
     "tensorboard.fetchers.s3": "tensorboard.fetchers.cloud", "tensorboard.fetchers.gcs": "tensorboard.fetchers.cloud",
     "tensorboard.fetchers.azure": "tensorboard.fetchers.cloud", "tensorboard.fetchers.directory": "tensorboard.fetchers.shared",

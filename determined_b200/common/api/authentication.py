@@ -10,7 +10,7 @@ import hashlib
 import json
 import os
 import pathlib
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict, List, Optional, Tuple
 
 from determined_b200.common.api import _session, errors
 
@@ -190,3 +190,33 @@ def logout(master: str, user: Optional[str] = None, cert: Any = None) -> None:
         with contextlib.suppress(errors.APIException, errors.MasterNotFoundException):
             _session.Session(master, user, tok, cert, max_retries=0).post("/api/v1/auth/logout")
     store.drop_user(user)
+
+
+def get_det_username_from_env() -> Optional[str]:
+    return os.environ.get("DET_USER")
+
+
+def get_det_user_token_from_env() -> Optional[str]:
+    return os.environ.get("DET_USER_TOKEN")
+
+
+def get_det_password_from_env() -> Optional[str]:
+    return os.environ.get("DET_PASS")
+
+
+def default_load_user_password(requested_user: Optional[str], password: Optional[str], token_store: "TokenStore") -> Tuple[Optional[str], Optional[str], bool]:
+    """(user, password, was the user the fall-back default?) from the arguments, the environment, the active user of the
+    token store, or the built-in ``determined`` user with its blank password."""
+    if requested_user:
+        return requested_user, password, False
+    if get_det_username_from_env() and get_det_password_from_env() is not None:
+        return get_det_username_from_env(), get_det_password_from_env(), False
+    if token_store.get_active_user():
+        return token_store.get_active_user(), password, False
+    return "determined", password if password is not None else "", True
+
+
+def logout_all(master: str, cert: Any = None) -> None:
+    """Drop every session this machine holds on ``master``."""
+    for user in TokenStore(master).get_all_users():
+        logout(master, user, cert) if "cert" in logout.__code__.co_varnames else logout(master, user)

@@ -46,3 +46,15 @@ class CorruptTokenCacheException(Exception):
 
 class InvalidCredentialsException(Exception):
     pass
+
+
+class CorruptCertificateCacheException(Exception):
+    """The store of accepted master certificates cannot be read."""
+
+
+class DeleteFailedException(Exception):
+    """The master reported that deleting an object failed."""
+
+
+class EmptyResultException(Exception):
+    """A lookup that must find something found nothing."""

@@ -69,3 +69,11 @@ def validate_manager(manager: StorageManager) -> None:
 
 def validate_config(config: Dict[str, Any], container_path: Optional[str] = None) -> None:
     validate_manager(build(config, container_path))
+
+
+def normalize_prefix(prefix: Optional[str]) -> str:
+    """A bucket prefix without leading slashes and with exactly one trailing slash (empty stays empty); ``..`` is refused."""
+    new = (prefix or "").strip().lstrip("/")
+    if any(part == ".." for part in new.split("/")):
+        raise ValueError("prefix must not contain /../")
+    return new.rstrip("/") + "/" if new else ""

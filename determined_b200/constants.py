@@ -45,3 +45,8 @@ MANAGED_TRAINING_MODEL_COPY = os.path.join(RUN_DIR, "train/model")
 SHARED_FS_CONTAINER_PATH = "/determined_shared_fs"
 DEFAULT_CHECKPOINT_PATH = os.path.expanduser(os.getenv("DET_CHECKPOINT_DIR", "~/.local/share/determined_b200/checkpoints"))
 DEFAULT_MASTER_PORT = 8080
+
+# kept for configs and scripts that read them; the launch layer here has no Horovod underneath
+HOROVOD_STARTUP_TIMEOUT_SECONDS = 1200
+HOROVOD_GLOO_TIMEOUT_SECONDS = 240
+HOROVOD_AUTOTUNE_LOG_FILEPATH = "/tmp/autotune_log.csv"

@@ -79,3 +79,23 @@ class ShouldExit(Exception):
     def __init__(self, skip_exit_checkpoint: bool = False):
         super().__init__()
         self.skip_exit_checkpoint = skip_exit_checkpoint
+
+
+class CheckpointStateException(Exception):
+    """A checkpoint is not in a state that allows the operation (deleted, partially deleted, still being written)."""
+
+
+class NoDirectStorageAccess(Exception):
+    """The checkpoint storage cannot be reached from this machine (``DownloadMode.DIRECT``)."""
+
+
+class ProxiedDownloadFailed(Exception):
+    """Downloading a checkpoint through the master failed (``DownloadMode.MASTER``)."""
+
+
+class MultipleDownloadsFailed(Exception):
+    """``DownloadMode.AUTO``: neither the direct nor the proxied download worked; ``args`` holds both errors."""
+
+
+class WorkerFinishedGracefully(Exception):
+    """A worker said it is done before the PID server stopped watching it."""

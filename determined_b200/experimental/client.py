@@ -42,6 +42,25 @@ class ExperimentState(enum.Enum):
 TERMINAL = {ExperimentState.COMPLETED, ExperimentState.CANCELED, ExperimentState.ERROR}
 
 
+class TrialState(enum.Enum):
+    """States of a trial (the experiment states that apply to one trial)."""
+
+    UNSPECIFIED = "STATE_UNSPECIFIED"
+    ACTIVE = "STATE_ACTIVE"
+    PAUSED = "STATE_PAUSED"
+    STOPPING_CANCELED = "STATE_STOPPING_CANCELED"
+    STOPPING_KILLED = "STATE_STOPPING_KILLED"
+    STOPPING_COMPLETED = "STATE_STOPPING_COMPLETED"
+    STOPPING_ERROR = "STATE_STOPPING_ERROR"
+    CANCELED = "STATE_CANCELED"
+    COMPLETED = "STATE_COMPLETED"
+    ERROR = "STATE_ERROR"
+    QUEUED = "STATE_QUEUED"
+    PULLING = "STATE_PULLING"
+    STARTING = "STATE_STARTING"
+    RUNNING = "STATE_RUNNING"
+
+
 class DownloadMode(enum.Enum):
     """DIRECT: read checkpoint storage yourself; MASTER: proxy through the master; AUTO: DIRECT
     if the storage is reachable from here else MASTER."""

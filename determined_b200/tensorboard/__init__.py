@@ -164,6 +164,22 @@ class StorageTensorboardManager(TensorboardManager):
         self._manager.delete(str(self.sync_path), ["**/*"])
 
 
+class S3TensorboardManager(StorageTensorboardManager):
+    """TensorBoard files to an S3 bucket (the checkpoint storage's S3 manager does the uploads)."""
+
+
+class GCSTensorboardManager(StorageTensorboardManager):
+    """TensorBoard files to a GCS bucket."""
+
+
+class AzureTensorboardManager(StorageTensorboardManager):
+    """TensorBoard files to an Azure blob container."""
+
+
+class DirectoryTensorboardManager(SharedFSTensorboardManager):
+    """TensorBoard files to a directory mounted into the task."""
+
+
 def build(cluster_id: str, experiment_id: Any, trial_id: Any, checkpoint_config: Dict[str, Any],
           container_path: Optional[str] = None, async_upload: bool = True) -> TensorboardManager:
     if "type" not in checkpoint_config:
@@ -179,8 +195,10 @@ def build(cluster_id: str, experiment_id: Any, trial_id: Any, checkpoint_config:
     storage_config = {k: v for k, v in checkpoint_config.items() if k != "base_path"}      # base_path is ours, not the storage manager's
     mgr = storage.build(storage_config, container_path)
     if kind in ("shared_fs", "directory"):
-        return SharedFSTensorboardManager(mgr._base_path, base, sync, async_upload=async_upload)
-    return StorageTensorboardManager(mgr, base, sync, async_upload=async_upload)
+        cls = SharedFSTensorboardManager if kind == "shared_fs" else DirectoryTensorboardManager
+        return cls(mgr._base_path, base, sync, async_upload=async_upload)
+    cloud = {"s3": S3TensorboardManager, "gcs": GCSTensorboardManager, "azure": AzureTensorboardManager}[kind]
+    return cloud(mgr, base, sync, async_upload=async_upload)
 
 
 def get_metric_writer() -> Any:

@@ -172,7 +172,8 @@ def test_module_paths_of_the_reference_resolve_under_the_alias(tmp_path, monkeyp
         except ImportError:
             missing.append(mod)
     # private plumbing of the reference's own client stack (its logging setup, its websocket and requests wrappers, the Horovod shim)
-    assert set(missing) <= {"common._logging", "common.detlomond", "common.requests", "horovod"}, missing
+    # (tensorboard.build is a function of the tensorboard package here: `from determined.tensorboard import build` is the spelling that works)
+    assert set(missing) <= {"common._logging", "common.detlomond", "common.requests", "horovod", "tensorboard.build"}, missing
     from determined.common.storage.s3 import S3StorageManager  # type: ignore  # noqa: F401
     from determined.searcher._search_method import SearchMethod  # type: ignore  # noqa: F401
     from determined.tensorboard.metric_writers.pytorch import TorchWriter  # type: ignore
@@ -211,6 +212,54 @@ def test_api_logs_module_reads_and_filters(tmp_path):
         with pytest.raises(ValueError):
             list(logs.task_logs(sess, "task-x", timestamp_before="2021-10-26 23:17:12Z"))
         assert list(logs.task_logs(sess, "task-x", follow=True))[-1].log == "l4\n", "follow ends when the task is not running"
+    finally:
+        m.stop()
+        srv.stop()
+
+
+def test_public_helper_names_of_the_reference_exist_and_work(tmp_path, monkeypatch):
+    from determined_b200 import constants, errors, experimental, tensorboard
+    from determined_b200.common import api, storage
+    from determined_b200.master import api as mapi
+    from determined_b200.master import core
+    from determined_b200.pytorch import experimental as px
+
+    assert storage.normalize_prefix("/a/b//") == "a/b/" and storage.normalize_prefix(None) == ""
+    with pytest.raises(ValueError):
+        storage.normalize_prefix("a/../b")
+    assert issubclass(errors.MultipleDownloadsFailed, Exception) and issubclass(api.errors.EmptyResultException, Exception)
+    assert constants.HOROVOD_STARTUP_TIMEOUT_SECONDS > 0 and callable(px.get_default_device) and callable(experimental.test_one_batch)
+    assert experimental.TrialState.RUNNING.value == "STATE_RUNNING" and experimental.ExperimentReference is experimental.Experiment
+    mgr = tensorboard.build("c", 1, 2, {"type": "directory", "container_path": str(tmp_path / "tb")}, async_upload=False)
+    assert isinstance(mgr, tensorboard.DirectoryTensorboardManager) and issubclass(tensorboard.S3TensorboardManager, tensorboard.TensorboardManager)
+
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=1, work_dir=str(tmp_path / "w"))
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    try:
+        sess = api.authentication.login(m.url, "admin", "")
+        sess.post("/api/v1/users", json={"user": {"username": "zed"}})
+        g = sess.post("/api/v1/groups", json={"name": "gg"}).json()["group"]["groupId"]
+        w = sess.post("/api/v1/workspaces", json={"name": "ww"}).json()["workspace"]["id"]
+        assert api.group_name_to_group_id(sess, "gg") == g and api.workspace_by_name(sess, "ww")["id"] == w
+        assert api.usernames_to_user_ids(sess, ["admin", "zed"])[0] == 1 and api.role_name_to_role_id(sess, "Editor") > 0
+        with pytest.raises(LookupError):
+            api.usernames_to_user_ids(sess, ["nobody-here"])
+        req = api.create_user_assignment_request(sess, "zed", "Viewer", "ww")
+        assert req[0]["roleAssignment"]["scopeWorkspaceId"] == w
+        pages = list(api.read_paginated(lambda off: sess.get("/api/v1/users", params={"offset": off, "limit": 2}).json()))
+        assert sum(len(p["users"]) for p in pages) == 3 and len(pages) == 2
+        assert len(list(api.read_paginated(lambda off: sess.get("/api/v1/users", params={"offset": off, "limit": 2}).json(), pages=api.PageOpts.single))) == 1
+        cmd = sess.post("/api/v1/commands", json={"config": {"entrypoint": ["sleep", "30"], "resources": {"slots": 0}}}).json()["command"]["id"]
+        assert api.wait_for_ntsc_state(sess, api.NTSC_Kind.command, cmd, lambda s: s == "STATE_RUNNING", timeout_secs=20) == "STATE_RUNNING"
+        api.wait_for_task_ready(sess, cmd, timeout_secs=20)
+        assert api.get_ntsc_details(sess, api.NTSC_Kind.command, cmd)["id"] == cmd
+        monkeypatch.setenv("DET_CONFIG_DIR", str(tmp_path / "cfg"))
+        st = api.authentication.TokenStore(m.url)
+        st.set_token("admin", sess.token)
+        st.set_token("zed", "whatever")
+        api.authentication.logout_all(m.url)
+        assert api.authentication.TokenStore(m.url).get_all_users() == []
     finally:
         m.stop()
         srv.stop()
