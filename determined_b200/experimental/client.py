@@ -278,29 +278,20 @@ class Trial(_sdk_more.TrialMore):
     def reload(self) -> None:
         self._hydrate(self._session.get(f"/api/v1/trials/{self.id}").json()["trial"])
 
-    def logs(self, follow: bool = False, head: Optional[int] = None, tail: Optional[int] = None) -> Iterator[str]:
-        off = 0
-        buf: List[str] = []
-        while True:
-            r = self._session.get(f"/api/v1/trials/{self.id}/logs", params={"offset": off, "follow": str(follow).lower(), "limit": 1000}).json()["logs"]
-            for l in r:
-                off = max(off, l["id"])
-                if tail is not None:
-                    buf.append(l["log"])
-                else:
-                    yield l["log"]
-                    if head is not None:
-                        head -= 1
-                        if head <= 0:
-                            return
-            if not r:
-                if not follow:
-                    break
-                self.reload()
-                if self.state in ("STATE_COMPLETED", "STATE_CANCELED", "STATE_ERROR"):
-                    break
-        if tail is not None:
-            yield from buf[-tail:]
+    def logs(self, follow: bool = False, head: Optional[int] = None, tail: Optional[int] = None, container_ids: Optional[List[str]] = None,
+             rank_ids: Optional[List[int]] = None, stdtypes: Optional[List[str]] = None, min_level: Any = None, timestamp_before: Any = None,
+             timestamp_after: Any = None, sources: Optional[List[str]] = None, search_text: Optional[str] = None) -> Iterator[str]:
+        """Log lines of the trial (oldest first); filters as in the reference's ``Trial.logs`` / ``det trial logs``."""
+        from determined_b200.common.api import logs as api_logs
+
+        if isinstance(min_level, str):
+            min_level = min_level.replace("LOG_LEVEL_", "").upper()
+        for e in api_logs.trial_logs(self._session, self.id, head=head, tail=tail, follow=follow, container_ids=container_ids, rank_ids=rank_ids,
+                                     sources=sources, stdtypes=stdtypes, min_level=min_level, timestamp_before=timestamp_before,
+                                     timestamp_after=timestamp_after):
+            line = e.log or e.message or ""
+            if search_text is None or search_text in line:
+                yield line
 
     def iter_metrics(self, group: Optional[str] = None) -> Iterator[TrialMetrics]:
         params = {"group": group} if group else {}
@@ -313,9 +304,23 @@ class Trial(_sdk_more.TrialMore):
     def stream_validation_metrics(self) -> Iterator[Dict[str, Any]]:
         return self.iter_metrics("validation")
 
-    def list_checkpoints(self, order_desc: bool = False) -> List[Checkpoint]:
-        r = self._session.get(f"/api/v1/trials/{self.id}/checkpoints", params={"orderBy": "ORDER_BY_DESC" if order_desc else "ORDER_BY_ASC"}).json()
-        return [Checkpoint(self._session, c["uuid"], c) for c in r["checkpoints"] if c["state"] == "STATE_COMPLETED"]
+    def list_checkpoints(self, order_desc: bool = False, sort_by: Any = None, order_by: Any = None, max_results: Optional[int] = None) -> List[Checkpoint]:
+        """Completed checkpoints of the trial.  ``sort_by``: a :class:`CheckpointSortBy` member, or the name of a validation
+        metric; ``order_by``: :class:`OrderBy` (both or neither); ``max_results`` cuts the list."""
+        if (sort_by is None) != (order_by is None):
+            raise AssertionError("sort_by and order_by must be either both set, or neither.")
+        desc = order_desc if order_by is None else getattr(order_by, "value", order_by) == "ORDER_BY_DESC"
+        params: Dict[str, Any] = {"orderBy": "ORDER_BY_DESC" if desc else "ORDER_BY_ASC"}
+        if isinstance(sort_by, CheckpointSortBy):
+            params["sortBy"] = sort_by.value
+        r = self._session.get(f"/api/v1/trials/{self.id}/checkpoints", params=params).json()
+        cks = [Checkpoint(self._session, c["uuid"], c) for c in r["checkpoints"] if c["state"] == "STATE_COMPLETED"]
+        if isinstance(sort_by, str):
+            key = lambda c: (c.training.get("validationMetrics", {}).get("avgMetrics") or {}).get(sort_by)  # noqa: E731
+            cks = sorted((c for c in cks if key(c) is not None), key=key, reverse=desc)
+        elif sort_by is CheckpointSortBy.SEARCHER_METRIC:
+            cks = sorted((c for c in cks if c.training.get("searcherMetric") is not None), key=lambda c: c.training["searcherMetric"], reverse=desc)
+        return cks[:max_results] if max_results else cks
 
     get_checkpoints = list_checkpoints
 
@@ -463,7 +468,15 @@ class Experiment(_sdk_more.ExperimentMore):
                 raise TimeoutError(f"experiment {self.id} still {self.state} after {timeout}s")
             time.sleep(interval)
 
-    def list_checkpoints(self, sort_by: Optional[str] = None, smaller_is_better: Optional[bool] = None, limit: Optional[int] = None) -> List[Checkpoint]:
+    def list_checkpoints(self, sort_by: Any = None, smaller_is_better: Optional[bool] = None, limit: Optional[int] = None, order_by: Any = None,
+                         max_results: Optional[int] = None) -> List[Checkpoint]:
+        """``sort_by``: the name of a validation metric (default: the searcher metric); ``order_by`` (:class:`OrderBy`) is the
+        reference's spelling of ``smaller_is_better`` (ascending = smaller first), ``max_results`` of ``limit``."""
+        if order_by is not None and smaller_is_better is None:
+            smaller_is_better = getattr(order_by, "value", order_by) != "ORDER_BY_DESC"
+        limit = limit if limit is not None else max_results
+        if isinstance(sort_by, CheckpointSortBy):
+            sort_by = None if sort_by is CheckpointSortBy.SEARCHER_METRIC else sort_by
         params: Dict[str, Any] = {"states": "STATE_COMPLETED"}
         if sort_by is not None:
             params["sortByMetric"] = sort_by
@@ -527,7 +540,9 @@ class Model(_sdk_more.ModelMore):
             return vs[0] if vs else None
         return ModelVersion(self._session, self._session.get(f"/api/v1/models/{self.name}/versions/{version}").json()["modelVersion"])
 
-    def list_versions(self, order_desc: bool = True) -> List[ModelVersion]:
+    def list_versions(self, order_desc: bool = True, order_by: Any = None) -> List[ModelVersion]:
+        if order_by is not None:
+            order_desc = getattr(order_by, "value", order_by) == "ORDER_BY_DESC"
         r = self._session.get(f"/api/v1/models/{self.name}/versions", params={"orderBy": "ORDER_BY_DESC" if order_desc else "ORDER_BY_ASC"}).json()
         return [ModelVersion(self._session, v) for v in r["modelVersions"]]
 
@@ -658,11 +673,11 @@ class Determined(_sdk_more.DeterminedMore):
     """Entry point of the SDK.  ``master`` defaults to ``$DET_MASTER`` or localhost:8080."""
 
     def __init__(self, master: Optional[str] = None, user: Optional[str] = None, password: Optional[str] = None,
-                 cert_path: Optional[str] = None, noverify: bool = False) -> None:
+                 cert_path: Optional[str] = None, cert_name: Optional[str] = None, noverify: bool = False) -> None:
         from determined_b200.common.api import certs
 
         self._master = master or os.environ.get("DET_MASTER") or "http://127.0.0.1:8080"
-        cert = certs.default_load(self._master, cert_path, None, noverify) if (cert_path or noverify) else None
+        cert = certs.default_load(self._master, cert_path, cert_name, noverify) if (cert_path or cert_name or noverify) else None
         self._session = api.authentication.login_with_cache(self._master, user, password, cert=cert)
 
     @classmethod
@@ -708,8 +723,12 @@ class Determined(_sdk_more.DeterminedMore):
     def get_checkpoint(self, uuid: str) -> Checkpoint:
         return Checkpoint(self._session, uuid, self._session.get(f"/api/v1/checkpoints/{uuid}").json()["checkpoint"])
 
-    def create_model(self, name: str, description: str = "", metadata: Optional[Dict[str, Any]] = None, labels: Optional[List[str]] = None) -> Model:
-        r = self._session.post("/api/v1/models", json={"name": name, "description": description, "metadata": metadata or {}, "labels": labels or []}).json()
+    def create_model(self, name: str, description: str = "", metadata: Optional[Dict[str, Any]] = None, labels: Optional[List[str]] = None,
+                     workspace_name: Optional[str] = None) -> Model:
+        body: Dict[str, Any] = {"name": name, "description": description, "metadata": metadata or {}, "labels": labels or []}
+        if workspace_name:
+            body["workspaceName"] = workspace_name
+        r = self._session.post("/api/v1/models", json=body).json()
         return Model(self._session, r["model"])
 
     def get_model(self, identifier: Union[str, int]) -> Model:
@@ -735,8 +754,8 @@ class Determined(_sdk_more.DeterminedMore):
         return self._session.get("/api/v1/me").json()["user"]
 
     # -- users ---------------------------------------------------------------------------------
-    def create_user(self, username: str, admin: bool = False, password: Optional[str] = None, active: bool = True) -> User:
-        body: Dict[str, Any] = {"user": {"username": username, "admin": admin, "active": active}}
+    def create_user(self, username: str, admin: bool = False, password: Optional[str] = None, active: bool = True, remote: bool = False) -> User:
+        body: Dict[str, Any] = {"user": {"username": username, "admin": admin, "active": active, "remote": remote}}
         if password is not None:
             body.update(password=api.authentication.salt_and_hash(password), isHashed=True)
         return User(self._session, self._session.post("/api/v1/users", json=body).json()["user"])
@@ -834,8 +853,9 @@ def get_checkpoint(uuid: str) -> Checkpoint:
     return _d().get_checkpoint(uuid)
 
 
-def create_model(name: str, description: str = "", metadata: Optional[Dict[str, Any]] = None, labels: Optional[List[str]] = None) -> Model:
-    return _d().create_model(name, description, metadata, labels)
+def create_model(name: str, description: str = "", metadata: Optional[Dict[str, Any]] = None, labels: Optional[List[str]] = None,
+                 workspace_name: Optional[str] = None) -> Model:
+    return _d().create_model(name, description, metadata, labels, workspace_name)
 
 
 def get_model(identifier: Union[str, int]) -> Model:

@@ -263,3 +263,52 @@ def test_public_helper_names_of_the_reference_exist_and_work(tmp_path, monkeypat
     finally:
         m.stop()
         srv.stop()
+
+
+def test_sdk_signatures_of_the_reference_are_accepted(tmp_path):
+    """``order_by`` / ``sort_by`` / ``max_results`` on checkpoint and version listings, filtered ``Trial.logs``, ``workspace_name``
+    on ``create_model``, ``remote`` on ``create_user``: the reference's keyword arguments."""
+    import time
+    import uuid as _uuid
+
+    from determined_b200.common import api
+    from determined_b200.experimental import client
+    from determined_b200.master import api as mapi
+    from determined_b200.master import core
+
+    m = core.Master(db_path=str(tmp_path / "m.db"), num_slots=0, work_dir=str(tmp_path / "w"))
+    srv = mapi.APIServer(m, "127.0.0.1", 0).start()
+    m.start()
+    try:
+        sess = api.authentication.login(m.url, "admin", "")
+        d = client.Determined._from_session(sess)
+        cfg = {"name": "x", "entrypoint": "y", "searcher": {"name": "single", "metric": "val_loss", "max_length": 1}, "hyperparameters": {}}
+        eid = sess.post("/api/v1/experiments", json={"config": __import__("json").dumps(cfg), "unmanaged": True}).json()["experiment"]["id"]
+        tid = sess.post(f"/api/v1/experiments/{eid}/trials", json={"hparams": {}}).json()["trial"]["id"]
+        for steps, loss in ((10, 0.5), (20, 0.2), (30, 0.4)):
+            sess.post(f"/api/v1/trials/{tid}/metrics", json={"group": "validation", "metrics": {"stepsCompleted": steps, "metrics": {"avgMetrics": {"val_loss": loss, "acc": steps}}}})
+            sess.post("/api/v1/checkpoints", json={"uuid": str(_uuid.uuid4()), "taskId": f"trial-{tid}", "allocationId": None, "reportTime": "2026-01-01T00:00:00Z",
+                                                   "state": "STATE_COMPLETED", "resources": {}, "metadata": {"steps_completed": steps}, "training": {}})
+        t, e = d.get_trial(tid), d.get_experiment(eid)
+        steps_of = lambda cks: [c.metadata["steps_completed"] for c in cks]  # noqa: E731
+        assert steps_of(t.list_checkpoints(sort_by=client.CheckpointSortBy.SEARCHER_METRIC, order_by=client.OrderBy.ASC)) == [20, 30, 10]
+        assert steps_of(t.list_checkpoints(sort_by="acc", order_by=client.OrderBy.DESC, max_results=2)) == [30, 20]
+        assert steps_of(t.get_checkpoints(sort_by=client.CheckpointSortBy.BATCH_NUMBER, order_by=client.OrderBy.DESC))[0] == 30
+        with pytest.raises(AssertionError):
+            t.list_checkpoints(sort_by="acc")
+        assert steps_of(e.list_checkpoints(order_by=client.OrderBy.ASC, max_results=1)) == [20]
+        assert steps_of(e.list_checkpoints(sort_by="acc", order_by=client.OrderBy.DESC, max_results=1)) == [30]
+        now = time.time()
+        m.db.add_logs([(f"trial-{tid}", "a", now - 5 + i, "ERROR" if i == 3 else "INFO", i % 2, "stdout", "task", f"l{i}\n") for i in range(6)])
+        assert list(t.logs(min_level="ERROR")) == ["l3\n"] and list(t.logs(rank_ids=[0], tail=2)) == ["l2\n", "l4\n"]
+        assert list(t.logs(search_text="l5")) == ["l5\n"] and list(t.logs(head=1)) == ["l0\n"]
+        sess.post("/api/v1/workspaces", json={"name": "regws"})
+        mod = d.create_model("sig-model", workspace_name="regws")
+        assert mod.workspace_id != 1 if hasattr(mod, "workspace_id") else True
+        assert sess.get("/api/v1/models/sig-model").json()["model"]["workspaceId"] != 1
+        assert [v.model_version for v in mod.list_versions(order_by=client.OrderBy.ASC)] == []
+        u = d.create_user("sso-only", remote=True)
+        assert sess.get(f"/api/v1/users/{u.user_id if hasattr(u, 'user_id') else u.id}").json()["user"]["remote"] is True
+    finally:
+        m.stop()
+        srv.stop()
