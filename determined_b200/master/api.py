@@ -449,7 +449,17 @@ def create_experiment(ctx: Ctx) -> Any:
         early = expconf.parse(b.get("config", "")) if b.get("config") else {}
     except Exception:  # noqa: BLE001  (reported properly by create_experiment below)
         early = {}
-    pid = int(b.get("projectId") or 1)
+    pid = int(b.get("projectId") or 0)
+    if not pid and isinstance(early, dict) and (early.get("workspace") or early.get("project")):
+        # the configuration itself may say where the experiment belongs: `workspace: name` + `project: name`
+        if not (early.get("workspace") and early.get("project")):
+            raise HTTPError(400, "workspace and project must both be given in the experiment configuration, or neither")
+        prow = ctx.m.db.one("SELECT p.id FROM projects p JOIN workspaces w ON w.id=p.workspace_id WHERE w.name=? AND p.name=?", (early["workspace"], early["project"]))
+        if prow is None:
+            raise HTTPError(404, f"project {early['project']!r} not found in workspace {early['workspace']!r}")
+        pid = int(prow["id"])
+        b = dict(b, projectId=pid)
+    pid = pid or 1
     res = (early.get("resources") or {}) if isinstance(early, dict) else {}
     if isinstance(early, dict) and not res.get("resource_pool"):
         dflt = api_more.default_pool_for_project(ctx.m, pid, int(res.get("slots_per_trial", 1) or 0))

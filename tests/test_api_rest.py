@@ -315,3 +315,20 @@ def test_oidc_single_sign_on_browser_flow_and_cli(cluster, tmp_path, monkeypatch
     finally:
         idp.shutdown()
         idp.server_close()
+
+
+def test_experiment_config_names_its_workspace_and_project(cluster):
+    m, sess, tmp = cluster
+    wid = sess.post("/api/v1/workspaces", json={"name": "by-name"}).json()["workspace"]["id"]
+    pid = sess.post(f"/api/v1/workspaces/{wid}/projects", json={"name": "proj"}).json()["project"]["id"]
+    eid = create(sess, dict(BASE, workspace="by-name", project="proj"), activate=False)
+    assert sess.get(f"/api/v1/experiments/{eid}").json()["experiment"]["projectId"] == pid
+    import yaml
+
+    for cfg, status in ((dict(BASE, workspace="by-name"), 400), (dict(BASE, workspace="by-name", project="nope"), 404)):
+        with pytest.raises(api.errors.APIException) as e:
+            sess.post("/api/v1/experiments", json={"config": yaml.safe_dump(cfg), "modelDefinition": [], "activate": False})
+        assert e.value.status_code == status
+    # an explicit projectId wins over the names in the configuration
+    r = sess.post("/api/v1/experiments", json={"config": yaml.safe_dump(dict(BASE, workspace="by-name", project="proj")), "modelDefinition": [], "activate": False, "projectId": 1})
+    assert r.json()["experiment"]["projectId"] == 1
