@@ -143,13 +143,13 @@ def test_api_requests_leave_audit_lines(cluster, caplog):
         admin.get("/api/v1/workspaces")
         with pytest.raises(api.errors.APIException):
             api.Session(m.url, "x", "bad-token").get("/api/v1/me")
-    import time
+        import time
 
-    for _ in range(40):           # the line is written after the answer has left: give the server thread a moment
-        lines = [(r.levelname, r.getMessage()) for r in caplog.records if r.name == "determined.master.audit"]
-        if sum("status=401" in msg for _, msg in lines):
-            break
-        time.sleep(0.05)
+        for _ in range(60):       # a line is written after its answer has left: wait (with the level still lowered) for the last one
+            lines = [(r.levelname, r.getMessage()) for r in caplog.records if r.name == "determined.master.audit"]
+            if sum("status=401" in msg for _, msg in lines):
+                break
+            time.sleep(0.05)
     assert ("INFO", "audit: user=admin remote_ip=127.0.0.1 method=POST path=/api/v1/workspaces status=200 unauthorized=False") in lines
     assert ("DEBUG", "audit: user=admin remote_ip=127.0.0.1 method=GET path=/api/v1/workspaces status=200 unauthorized=False") in lines
     assert ("INFO", "audit: user=None remote_ip=127.0.0.1 method=GET path=/api/v1/me status=401 unauthorized=True") in lines
